@@ -1,0 +1,247 @@
+"""GPT-2 with a language-modelling head and a multiple-choice head
+("double heads"), the model the reference fine-tunes on PersonaChat through the
+external ``pytorch_transformers`` package
+(/root/reference/CommEfficient/gpt2_train.py:4-6,77-112,262-285).
+
+This is a self-contained implementation: the package is not installed here and
+the installed ``transformers`` uses different keyword names.
+Kept compatible:
+  * call signature ``model(input_ids, token_type_ids=, mc_token_ids=, lm_labels=,
+    mc_labels=)`` and tuple return ``(lm_loss, mc_loss, lm_logits, mc_logits)``
+    (losses present only when the labels are given);
+  * LM loss = shifted cross-entropy with ``ignore_index=-1``; MC loss =
+    cross-entropy over the candidates of ``Linear(n_embd -> 1)`` applied to the
+    hidden state at ``mc_token_ids``;
+  * Hugging Face ``state_dict`` key names and ``Conv1D`` (in, out) weight layout, so
+    ``save_pretrained`` output loads into HF GPT2DoubleHeadsModel and vice versa;
+  * ``resize_token_embeddings`` (+5 special tokens => d = 124 444 417 for GPT-2 small).
+"""
+from __future__ import annotations
+
+import json
+import math
+import os
+from dataclasses import asdict, dataclass
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..ops import nn as nnops
+
+__all__ = ["GPT2Config", "GPT2DoubleHeadsModel", "OpenAIGPTDoubleHeadsModel"]
+
+CONFIG_NAME = "config.json"
+WEIGHTS_NAME = "pytorch_model.bin"
+
+
+@dataclass
+class GPT2Config:
+    vocab_size: int = 50257
+    n_positions: int = 1024
+    n_ctx: int = 1024
+    n_embd: int = 768
+    n_layer: int = 12
+    n_head: int = 12
+    resid_pdrop: float = 0.1
+    embd_pdrop: float = 0.1
+    attn_pdrop: float = 0.1
+    layer_norm_epsilon: float = 1e-5
+    initializer_range: float = 0.02
+    summary_first_dropout: float = 0.1
+
+    def to_json_file(self, path):
+        with open(path, "w") as f:
+            json.dump(asdict(self), f, indent=2)
+
+    @classmethod
+    def from_json_file(cls, path):
+        with open(path) as f:
+            raw = json.load(f)
+        known = {k: v for k, v in raw.items() if k in cls.__dataclass_fields__}
+        return cls(**known)
+
+
+class Conv1D(nn.Module):
+    """Linear layer with the (in_features, out_features) weight layout of GPT-2."""
+
+    def __init__(self, nf, nx, std=0.02):
+        super().__init__()
+        self.nf = nf
+        self.weight = nn.Parameter(torch.empty(nx, nf).normal_(0.0, std))
+        self.bias = nn.Parameter(torch.zeros(nf))
+
+    def forward(self, x):
+        shape = x.shape[:-1] + (self.nf,)
+        y = nnops.linear(x.reshape(-1, x.shape[-1]), self.weight.t(), self.bias)
+        return y.view(shape)
+
+
+class Attention(nn.Module):
+    def __init__(self, cfg: GPT2Config):
+        super().__init__()
+        self.n_head = cfg.n_head
+        self.c_attn = Conv1D(3 * cfg.n_embd, cfg.n_embd, cfg.initializer_range)
+        self.c_proj = Conv1D(cfg.n_embd, cfg.n_embd, cfg.initializer_range)
+        self.attn_pdrop = cfg.attn_pdrop
+        self.resid_dropout = nn.Dropout(cfg.resid_pdrop)
+
+    def forward(self, x):
+        B, T, E = x.shape
+        q, k, v = self.c_attn(x).split(E, dim=2)
+        hd = E // self.n_head
+        q = q.view(B, T, self.n_head, hd).transpose(1, 2)
+        k = k.view(B, T, self.n_head, hd).transpose(1, 2)
+        v = v.view(B, T, self.n_head, hd).transpose(1, 2)
+        y = F.scaled_dot_product_attention(q, k, v, is_causal=True,
+                                           dropout_p=self.attn_pdrop if self.training else 0.0)
+        y = y.transpose(1, 2).reshape(B, T, E)
+        return self.resid_dropout(self.c_proj(y))
+
+
+class MLP(nn.Module):
+    def __init__(self, cfg: GPT2Config):
+        super().__init__()
+        self.c_fc = Conv1D(4 * cfg.n_embd, cfg.n_embd, cfg.initializer_range)
+        self.c_proj = Conv1D(cfg.n_embd, 4 * cfg.n_embd, cfg.initializer_range)
+        self.dropout = nn.Dropout(cfg.resid_pdrop)
+
+    def forward(self, x):
+        return self.dropout(self.c_proj(F.gelu(self.c_fc(x), approximate="tanh")))
+
+
+class Block(nn.Module):
+    def __init__(self, cfg: GPT2Config):
+        super().__init__()
+        self.ln_1 = nn.LayerNorm(cfg.n_embd, eps=cfg.layer_norm_epsilon)
+        self.attn = Attention(cfg)
+        self.ln_2 = nn.LayerNorm(cfg.n_embd, eps=cfg.layer_norm_epsilon)
+        self.mlp = MLP(cfg)
+
+    def forward(self, x):
+        x = x + self.attn(self.ln_1(x))
+        return x + self.mlp(self.ln_2(x))
+
+
+class GPT2Model(nn.Module):
+    def __init__(self, cfg: GPT2Config):
+        super().__init__()
+        self.wte = nn.Embedding(cfg.vocab_size, cfg.n_embd)
+        self.wpe = nn.Embedding(cfg.n_positions, cfg.n_embd)
+        self.drop = nn.Dropout(cfg.embd_pdrop)
+        self.h = nn.ModuleList([Block(cfg) for _ in range(cfg.n_layer)])
+        self.ln_f = nn.LayerNorm(cfg.n_embd, eps=cfg.layer_norm_epsilon)
+        nn.init.normal_(self.wte.weight, 0.0, cfg.initializer_range)
+        nn.init.normal_(self.wpe.weight, 0.0, cfg.initializer_range)
+
+    def forward(self, input_ids, token_type_ids=None):
+        T = input_ids.shape[-1]
+        pos = torch.arange(T, device=input_ids.device)
+        x = self.wte(input_ids) + self.wpe(pos)
+        if token_type_ids is not None:
+            x = x + self.wte(token_type_ids)
+        x = self.drop(x)
+        for block in self.h:
+            x = block(x)
+        return self.ln_f(x)
+
+
+class SequenceSummary(nn.Module):
+    """Hidden state at a given token -> dropout -> Linear(n_embd, 1)."""
+
+    def __init__(self, cfg: GPT2Config):
+        super().__init__()
+        self.first_dropout = nn.Dropout(cfg.summary_first_dropout)
+        self.summary = nn.Linear(cfg.n_embd, 1)
+        nn.init.normal_(self.summary.weight, 0.0, cfg.initializer_range)
+        nn.init.zeros_(self.summary.bias)
+
+    def forward(self, hidden, cls_index):
+        # hidden (N, T, E), cls_index (N,)
+        gathered = hidden[torch.arange(hidden.shape[0], device=hidden.device), cls_index]
+        return self.summary(self.first_dropout(gathered)).squeeze(-1)
+
+
+class GPT2DoubleHeadsModel(nn.Module):
+    def __init__(self, config: Optional[GPT2Config] = None):
+        super().__init__()
+        self.config = config or GPT2Config()
+        self.transformer = GPT2Model(self.config)
+        self.lm_head = nn.Linear(self.config.n_embd, self.config.vocab_size, bias=False)
+        self.multiple_choice_head = SequenceSummary(self.config)
+        self.tie_weights()
+
+    # -- HF-style utilities --------------------------------------------------------
+    def tie_weights(self):
+        self.lm_head.weight = self.transformer.wte.weight
+
+    def resize_token_embeddings(self, new_num_tokens: int):
+        old = self.transformer.wte
+        if new_num_tokens == old.num_embeddings:
+            return old
+        new = nn.Embedding(new_num_tokens, old.embedding_dim).to(old.weight.device)
+        nn.init.normal_(new.weight, 0.0, self.config.initializer_range)
+        n = min(old.num_embeddings, new_num_tokens)
+        with torch.no_grad():
+            new.weight[:n] = old.weight[:n]
+        self.transformer.wte = new
+        self.lm_head = nn.Linear(old.embedding_dim, new_num_tokens, bias=False)
+        self.config.vocab_size = new_num_tokens
+        self.tie_weights()
+        return new
+
+    @classmethod
+    def from_pretrained(cls, path_or_name, **kw):
+        """Load ``config.json`` + ``pytorch_model.bin`` from a directory; any other
+        argument (e.g. the hub name ``gpt2`` -- there is no network) builds a
+        randomly initialised GPT-2 small."""
+        if isinstance(path_or_name, str) and os.path.isdir(path_or_name):
+            cfg = GPT2Config.from_json_file(os.path.join(path_or_name, CONFIG_NAME))
+            model = cls(cfg)
+            state = torch.load(os.path.join(path_or_name, WEIGHTS_NAME), map_location="cpu")
+            state = {k: v for k, v in state.items() if not k.endswith(".attn.bias")
+                     and not k.endswith(".attn.masked_bias")}
+            model.load_state_dict(state, strict=False)
+            model.tie_weights()
+            return model
+        return cls(GPT2Config(**kw))
+
+    def save_pretrained(self, save_directory):
+        os.makedirs(save_directory, exist_ok=True)
+        self.config.to_json_file(os.path.join(save_directory, CONFIG_NAME))
+        torch.save(self.state_dict(), os.path.join(save_directory, WEIGHTS_NAME))
+
+    # -- forward -------------------------------------------------------------------
+    def forward(self, input_ids, token_type_ids=None, mc_token_ids=None, lm_labels=None, mc_labels=None,
+                **_ignored):
+        shape = input_ids.shape                      # (B, C, T)
+        T = shape[-1]
+        flat_ids = input_ids.reshape(-1, T)
+        flat_types = token_type_ids.reshape(-1, T) if token_type_ids is not None else None
+        hidden = self.transformer(flat_ids, flat_types)          # (B*C, T, E)
+        lm_logits = nnops.linear(hidden.reshape(-1, hidden.shape[-1]), self.lm_head.weight, None)
+        lm_logits = lm_logits.view(*shape, -1)
+        outputs = [lm_logits]
+        mc_logits = None
+        if mc_token_ids is not None:
+            mc_logits = self.multiple_choice_head(hidden, mc_token_ids.reshape(-1)).view(shape[:-1])
+        outputs.append(mc_logits)
+        if mc_labels is not None:
+            mc_loss = F.cross_entropy(mc_logits.float().view(-1, mc_logits.shape[-1]), mc_labels.view(-1))
+            outputs.insert(0, mc_loss)
+        if lm_labels is not None:
+            logits = lm_logits[..., :-1, :].reshape(-1, lm_logits.shape[-1])
+            labels = lm_labels[..., 1:].reshape(-1)
+            lm_loss = F.cross_entropy(logits.float(), labels, ignore_index=-1)
+            outputs.insert(0, lm_loss)
+        return tuple(outputs)
+
+
+class OpenAIGPTDoubleHeadsModel(GPT2DoubleHeadsModel):
+    """The reference falls back to the GPT-1 class when ``--model_checkpoint`` does not
+    contain "gpt2" (gpt2_train.py:263-268).  Same double-head interface; the GPT-1
+    sizes (40 478 BPE tokens, 512 positions) are the defaults."""
+
+    def __init__(self, config: Optional[GPT2Config] = None):
+        super().__init__(config or GPT2Config(vocab_size=40478, n_positions=512, n_ctx=512))

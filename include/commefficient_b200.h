@@ -1,0 +1,115 @@
+/* commefficient_b200 -- C ABI of the native sm_100a library (libceb200.so).
+ *
+ * Conventions
+ *   - every function returns 0 on success; on failure a non-zero code, and
+ *     ceb_last_error() describes what went wrong (thread-local string);
+ *   - pointers are device pointers unless a comment says "host";
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - nothing here allocates or frees device memory: callers pass every buffer,
+ *     including scratch (sizes via the *_bytes() queries), so the library can be
+ *     driven from PyTorch's caching allocator without fragmenting it;
+ *   - top-k results are unordered; which of several equal-magnitude entries at
+ *     the threshold are kept is unspecified (as with torch.topk).
+ *
+ * "Reference" below is pursueorigin/CommEfficient (paths relative to
+ * CommEfficient/ in that repository).
+ */
+#ifndef COMMEFFICIENT_B200_H
+#define COMMEFFICIENT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ---------------------------------------------------------------- */
+const char* ceb_last_error(void);
+int ceb_version(void);
+/* Kernel launches issued by this library since the last reset (host counter). */
+unsigned long long ceb_launch_count(void);
+void ceb_reset_launch_count(void);
+
+/* ---- exact top-k by magnitude (reference: utils.py:232-252 `_topk`) ---------- */
+/* Bytes of zero-initialisable scratch every top-k style call needs (~26 KB). */
+int64_t ceb_select_scratch_bytes(void);
+/* out_idx/out_val receive the k largest-|v| entries of vec[0..n). 0 < k <= n < 2^31. */
+int ceb_topk_select(const float* vec, int64_t n, int64_t k, void* scratch, int64_t scratch_bytes,
+                    int32_t* out_idx, float* out_val, void* stream);
+
+/* ---- count sketch (reference: external csvec.CSVec; fed_worker.py:312-320,
+ *      fed_aggregator.py:568-613).  packed: [r][n_tokens] int32, blk: [num_blocks]
+ *      int32 -- layout documented in commefficient_b200/ops/hashing.py ---------- */
+/* table[r][bucket(i)] += sign(i) * scale * (g[i] + wd * w[i]); w may be NULL. */
+int ceb_sketch_accumulate(const float* g, const float* w, float wd, float scale, int64_t d,
+                          const int32_t* packed, int64_t n_tokens, const int32_t* blk, int num_blocks,
+                          float* table, int r, int64_t c, void* stream);
+/* out2[1] = l2 estimate sqrt(median_r sum_c T^2); out2[0] = clip/l2 if l2 >= clip > 0 else 1.
+ * rowsq_tmp: r floats of scratch.  (reference: utils.py:305-313 on a CSVec) */
+int ceb_sketch_l2_scale(const float* table, int r, int64_t c, float clip, float* rowsq_tmp, float* out2,
+                        void* stream);
+/* y += alpha * (dev_scale ? *dev_scale : 1) * x; zero_x != 0 clears x afterwards. */
+int ceb_axpy_dev(float* y, float* x, int64_t n, float alpha, const float* dev_scale, int zero_x,
+                 void* stream);
+/* Vv = rho*Vv + g*inv_n; error_mode 2: Ve += Vv, 1: Ve = Vv, 0: Ve untouched.
+ * (reference: fed_aggregator.py:578-582) */
+int ceb_sketch_server_update(float* Vv, float* Ve, const float* g, float inv_n, float rho, int error_mode,
+                             int64_t n, void* stream);
+/* est[i] = median_r(table[r][bucket(i)]*sign(i)) for all i<d, then exact top-k of |est|.
+ * (reference: CSVec.unSketch(k), fed_aggregator.py:584-590) */
+int ceb_sketch_unsketch_topk(const float* table, const int32_t* packed, int64_t n_tokens,
+                             const int32_t* blk, int num_blocks, int r, int64_t c, int64_t d, int64_t k,
+                             float* est, void* scratch, int64_t scratch_bytes, int32_t* out_idx,
+                             float* out_val, void* stream);
+/* out[j] = estimate of coordinate idx[j] (idx NULL: coordinates 0..count-1). */
+int ceb_sketch_query(const float* table, const int32_t* packed, int64_t n_tokens, const int32_t* blk,
+                     int num_blocks, int r, int64_t c, int64_t d, const int32_t* idx, int64_t count,
+                     float* out, void* stream);
+/* For every selected (idx,val) with val != 0: zero its r buckets in Vv / Ve (either may be
+ * NULL) and apply w[idx] -= lr*val (lr_vec[idx] when non-NULL); changed[idx] = 1 when
+ * non-NULL.  (reference: fed_aggregator.py:593-613, :455) */
+int ceb_sketch_apply_zero(const int32_t* idx, const float* val, int64_t k, const int32_t* packed,
+                          int64_t n_tokens, const int32_t* blk, int r, int64_t c, float* Vv, float* Ve,
+                          float* w, float lr, const float* lr_vec, uint8_t* changed, void* stream);
+
+/* ---- dense modes (reference: fed_aggregator.py:483-566) ---------------------- */
+/* Vv = rho*Vv + g*inv_n (+ N(0,noise_std^2)); w -= lr*Vv.  uncompressed / local_topk / fedavg. */
+int ceb_dense_server_update(float* Vv, const float* g, float inv_n, float rho, int64_t n, float* w,
+                            float lr, const float* lr_vec, float noise_std, unsigned long long seed,
+                            unsigned long long noise_offset, uint8_t* changed, void* stream);
+/* true_topk server step in one call (momentum, virtual error, exact top-k, zeroing, apply). */
+int ceb_true_topk_step(float* Vv, float* Ve, const float* g, float inv_n, float rho, int64_t n, int64_t k,
+                       float* w, float lr, const float* lr_vec, uint8_t* changed, void* scratch,
+                       int64_t scratch_bytes, int32_t* out_idx, float* out_val, float* client_vel,
+                       const int64_t* vel_rows, int n_vel_rows, void* stream);
+int ceb_dense_apply_zero(const int32_t* idx, const float* val, int64_t k, float* Vv, float* Ve, float* w,
+                         float lr, const float* lr_vec, uint8_t* changed, float* client_vel,
+                         const int64_t* vel_rows, int n_vel_rows, int64_t d, void* stream);
+
+/* ---- per-client state (reference: fed_worker.py:190-216) --------------------- */
+/* transmit = [err +=] [vel = rho*vel +] scale*g; k == 0: acc += transmit; k > 0: acc[idx] +=
+ * topk_k(transmit) and err[idx] = vel[idx] = 0.  vel/err may be NULL. */
+int ceb_client_step(float* g, float scale, float* vel, float rho, float* err, int64_t n, int64_t k,
+                    float* acc, void* scratch, int64_t scratch_bytes, int32_t* out_idx, float* out_val,
+                    void* stream);
+int ceb_scatter_add_zero(const int32_t* idx, const float* val, int64_t k, float* acc, float* err,
+                         float* vel, void* stream);
+
+/* ---- clipping, DP noise, fedavg, accounting ---------------------------------- */
+/* x *= min(1, clip/(||x||+eps)) when eps > 0 (torch clip_grad_norm_, fed_worker.py:290-292);
+ * eps == 0: x *= clip/||x|| only when ||x|| >= clip (utils.py:305-313).  sumsq_out: 1 float. */
+int ceb_clip_by_norm(float* x, int64_t n, float clip, float eps, float* sumsq_out, void* stream);
+/* x += N(0, std^2), Philox4x32-10 (reference: fed_worker.py:306-309). */
+int ceb_add_gaussian_noise(float* x, int64_t n, float std, unsigned long long seed,
+                           unsigned long long offset, void* stream);
+/* acc += weight * (w0 - wloc)   (reference: fed_worker.py:104-108) */
+int ceb_fedavg_delta(float* acc, const float* w0, const float* wloc, float weight, int64_t n, void* stream);
+/* mask |= (w != prev); prev = w; *count = popcount(mask).  prev/mask may be NULL.
+ * (reference: fed_aggregator.py:244-250) */
+int ceb_count_changed(const float* w, float* prev, uint8_t* mask, int64_t n, unsigned long long* count,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COMMEFFICIENT_B200_H */
