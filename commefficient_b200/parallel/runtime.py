@@ -1,0 +1,195 @@
+"""SPMD runtime: one rank per GPU (or per CPU process), no parameter-server rank.
+
+The reference is a parameter server + worker processes joined by NCCL ``reduce`` and
+host shared memory (/root/reference/CommEfficient/fed_aggregator.py:136-164,301-332,
+fed_worker.py:18-35,134-138).  Here every rank is a worker for its share of the
+round's clients *and* an aggregator; the only per-round communication is the sum of
+the per-rank transmit buffers plus a few hundred bytes of per-client results.
+
+Backends
+  ``b200``   peer-memory kernels over NVLink (``parallel.symm`` / ``csrc/peer.cu``)
+  ``nccl``   ``torch.distributed`` NCCL -- the baseline the fused path is compared against
+  ``gloo``   CPU plumbing / tests (BASELINE.json config 1)
+  ``single`` one process, no communication
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+_RUNTIME: Optional["Runtime"] = None
+
+
+class Runtime:
+    def __init__(self, rank: int, world_size: int, device: torch.device, backend: str):
+        self.rank = rank
+        self.world_size = world_size
+        self.device = device
+        self.backend = backend
+        self.peer = None        # parallel.symm.PeerGroup when backend == "b200"
+        self.collective_calls = 0
+
+    @property
+    def is_distributed(self) -> bool:
+        return self.world_size > 1
+
+    # -- collectives ---------------------------------------------------------------
+    def all_reduce_sum_(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place sum over ranks; identical result (bitwise) on every rank."""
+        if self.world_size == 1:
+            return t
+        self.collective_calls += 1
+        if self.backend == "b200" and self.peer is not None and t.is_cuda:
+            return self.peer.all_reduce_sum_(t)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t
+
+    def all_gather_cat(self, t: torch.Tensor, sizes: Optional[List[int]] = None) -> torch.Tensor:
+        """Concatenate per-rank 2-D tensors (variable first dimension) on every rank."""
+        if self.world_size == 1:
+            return t
+        self.collective_calls += 1
+        if sizes is None:
+            n = torch.tensor([t.shape[0]], device=t.device, dtype=torch.int64)
+            all_n = [torch.zeros_like(n) for _ in range(self.world_size)]
+            dist.all_gather(all_n, n)
+            sizes = [int(x.item()) for x in all_n]
+        mx = max(sizes) if sizes else 0
+        pad = torch.zeros((mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        pad[: t.shape[0]] = t
+        outs = [torch.zeros_like(pad) for _ in range(self.world_size)]
+        dist.all_gather(outs, pad)
+        return torch.cat([o[:s] for o, s in zip(outs, sizes)], dim=0)
+
+    def broadcast_(self, t: torch.Tensor, src: int = 0) -> torch.Tensor:
+        if self.world_size > 1:
+            dist.broadcast(t, src)
+        return t
+
+    def barrier(self):
+        if self.world_size > 1:
+            if self.device.type == "cuda":
+                dist.barrier(device_ids=[self.device.index])
+            else:
+                dist.barrier()
+
+    def max_over_ranks(self, value: float) -> float:
+        if self.world_size == 1:
+            return float(value)
+        t = torch.tensor([float(value)], dtype=torch.float64,
+                         device=self.device if self.device.type == "cuda" else "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def shutdown(self):
+        global _RUNTIME
+        if self.peer is not None:
+            self.peer.close()
+            self.peer = None
+        if self.world_size > 1 and dist.is_initialized():
+            dist.destroy_process_group()
+        _RUNTIME = None
+
+
+def get_runtime() -> Optional[Runtime]:
+    return _RUNTIME
+
+
+def init_runtime(args=None, rank: Optional[int] = None, world_size: Optional[int] = None,
+                 backend: Optional[str] = None, device: Optional[str] = None, port: Optional[int] = None,
+                 timeout_s: float = 1800.0) -> Runtime:
+    """Create (or return) the process-wide runtime.  Rank / world size come from the
+    arguments or from the torchrun environment (RANK / WORLD_SIZE / LOCAL_RANK /
+    MASTER_ADDR / MASTER_PORT); a plain ``python script.py`` is a 1-rank job."""
+    global _RUNTIME
+    if _RUNTIME is not None:
+        return _RUNTIME
+    env = os.environ
+    if rank is None:
+        rank = int(env.get("RANK", "0"))
+    if world_size is None:
+        world_size = int(env.get("WORLD_SIZE", "1"))
+    dev_kind = device or (getattr(args, "device", None) if args is not None else None)
+    if dev_kind is None:
+        dev_kind = "cuda" if torch.cuda.is_available() else "cpu"
+    if dev_kind.startswith("cuda"):
+        local = int(env.get("LOCAL_RANK", str(rank % max(1, torch.cuda.device_count()))))
+        torch.cuda.set_device(local)
+        dev = torch.device("cuda", local)
+    else:
+        dev = torch.device("cpu")
+    want = backend or (getattr(args, "backend", "auto") if args is not None else "auto")
+    if world_size == 1:
+        chosen = "single"
+    elif want == "auto":
+        chosen = "b200" if dev.type == "cuda" else "gloo"
+    else:
+        chosen = want
+    if dev.type == "cpu" and chosen in ("b200", "nccl"):
+        chosen = "gloo"
+    rt = Runtime(rank, world_size, dev, chosen)
+    if world_size > 1 and not dist.is_initialized():
+        import datetime
+        env.setdefault("MASTER_ADDR", "127.0.0.1")
+        if port is None and args is not None and "MASTER_PORT" not in env:
+            port = getattr(args, "port", None)
+        if port is not None:
+            env["MASTER_PORT"] = str(port)
+        env.setdefault("MASTER_PORT", "5315")
+        dist.init_process_group(
+            backend="gloo" if dev.type == "cpu" else "nccl",
+            rank=rank, world_size=world_size,
+            timeout=datetime.timedelta(seconds=timeout_s),
+            **({"device_id": dev} if dev.type == "cuda" else {}))
+    if chosen == "b200":
+        try:
+            from .symm import PeerGroup
+            rt.peer = PeerGroup(rt)
+        except Exception as exc:  # fall back to NCCL but say so loudly
+            import warnings
+            warnings.warn("peer-memory backend unavailable (%s); using NCCL collectives" % (exc,))
+            rt.backend = "nccl"
+    _RUNTIME = rt
+    return rt
+
+
+def spawn(fn, nprocs: int, args=(), port: Optional[int] = None, device: str = "cpu"):
+    """Run ``fn(rank, world_size, *args)`` in ``nprocs`` processes with the rendezvous
+    environment prepared (used by tests and by the drivers for ``--num_devices > 1``
+    when not started under torchrun)."""
+    import torch.multiprocessing as mp
+    from ..utils import free_port
+    port = port or free_port(29500 + os.getpid() % 2000)
+    ctx = mp.get_context("spawn")
+    procs = []
+    err_q = ctx.SimpleQueue()
+    for rank in range(nprocs):
+        p = ctx.Process(target=_spawn_entry, args=(fn, rank, nprocs, port, device, args, err_q))
+        p.start()
+        procs.append(p)
+    failed = False
+    for p in procs:
+        p.join()
+        failed = failed or p.exitcode != 0
+    if failed:
+        msgs = []
+        while not err_q.empty():
+            msgs.append(err_q.get())
+        raise RuntimeError("spawned rank failed:\n" + "\n".join(msgs))
+
+
+def _spawn_entry(fn, rank, world_size, port, device, args, err_q):
+    os.environ["RANK"] = str(rank)
+    os.environ["WORLD_SIZE"] = str(world_size)
+    os.environ["LOCAL_RANK"] = str(rank)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    try:
+        fn(rank, world_size, *args)
+    except Exception:
+        import traceback
+        err_q.put("rank %d:\n%s" % (rank, traceback.format_exc()))
+        raise
