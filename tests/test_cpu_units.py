@@ -1,0 +1,158 @@
+"""CPU unit tests: CLI, schedules, flat buffers, oracles, sampler, datasets, CSVec API."""
+import numpy as np
+import pytest
+import torch
+
+from commefficient_b200 import data_utils as du
+from commefficient_b200 import models
+from commefficient_b200.csvec import CSVec
+from commefficient_b200.ops import ref
+from commefficient_b200.ops.hashing import LARGEPRIME, make_hashes
+from commefficient_b200.utils import (FlatParams, PiecewiseLinear, Exp, TableLogger, get_grad, get_param_vec,
+                                      make_args, parse_args, set_param_vec, _topk, clip_grad)
+
+
+def test_cli_defaults_match_reference():
+    a = parse_args(argv=["--mode", "uncompressed", "--dataset_name", "CIFAR10"])
+    assert (a.k, a.num_cols, a.num_rows, a.num_blocks) == (50000, 500000, 5, 20)
+    assert (a.local_momentum, a.virtual_momentum, a.weight_decay, a.num_epochs) == (0.9, 0.0, 5e-4, 24)
+    assert (a.port, a.num_workers, a.local_batch_size, a.valid_batch_size, a.seed) == (5315, 1, 8, 8, 21)
+    assert a.model == "ResNet9" and a.error_type == "none" and a.max_grad_norm is None
+    assert a.do_test is False and a.do_topk_down is False and a.do_dp is False
+
+
+@pytest.mark.parametrize("bad", [
+    dict(mode="fedavg", local_batch_size=8, local_momentum=0.0),
+    dict(mode="fedavg", local_batch_size=-1, local_momentum=0.9),
+    dict(mode="sketch", local_momentum=0.9, error_type="virtual"),
+    dict(mode="sketch", local_momentum=0.0, error_type="none"),
+    dict(mode="true_topk", error_type="none"),
+    dict(mode="local_topk", error_type="virtual"),
+])
+def test_cli_rejects_bad_combinations(bad):
+    with pytest.raises(ValueError):
+        make_args(**bad)
+
+
+def test_schedules():
+    tri = PiecewiseLinear([0, 5, 24], [0, 0.4, 0])
+    assert tri(0) == 0 and tri(5) == pytest.approx(0.4) and tri(24) == 0 and tri(2.5) == pytest.approx(0.2)
+    assert tri(100) == 0
+    e = Exp(2, 1.0, 10)
+    assert e(1) == pytest.approx(0.5) and e(12) == pytest.approx(0.1)
+
+
+def test_flat_params_are_views():
+    m = models.ResNet9(num_classes=10, channels={"prep": 4, "layer1": 4, "layer2": 4, "layer3": 4})
+    ref_vec = torch.cat([p.data.reshape(-1) for p in m.parameters()])
+    fp = FlatParams(m, "cpu")
+    m._flat_params = fp
+    assert torch.equal(fp.flat, ref_vec)
+    fp.flat.mul_(2)
+    assert torch.equal(get_param_vec(m), 2 * ref_vec)
+    out = m(torch.randn(2, 3, 32, 32)).sum()
+    out.backward()
+    assert fp.grad.abs().sum() > 0
+    args = make_args(mode="uncompressed", weight_decay=0.1, num_workers=4, device="cpu")
+    g = get_grad(m, args)
+    torch.testing.assert_close(g, fp.grad + 0.025 * fp.flat)
+    set_param_vec(m, ref_vec)
+    assert torch.equal(next(m.parameters()).data.reshape(-1), ref_vec[: next(m.parameters()).numel()])
+    sd = m.state_dict()
+    assert "n.prep.conv.weight" in sd and "n.linear.weight" in sd
+
+
+def test_hashes_follow_csvec_recipe():
+    h = make_hashes(1003, 97, 3, 20)
+    assert h.n_tokens == 51 and h.buckets.shape == (3, 51) and h.packed.dtype == torch.int32
+    assert int(h.buckets.max()) < 97 and int(h.buckets.min()) >= 0
+    assert set(h.signs.unique().tolist()) <= {-1.0, 1.0}
+    # recompute row 0 by hand with python ints wrapped to int64
+    st = torch.random.get_rng_state()
+    torch.random.manual_seed(42)
+    hh = torch.randint(0, LARGEPRIME, (3, 6), dtype=torch.int64)
+    torch.random.set_rng_state(st)
+
+    def wrap(x):
+        x &= (1 << 64) - 1
+        return x - (1 << 64) if x >= (1 << 63) else x
+
+    for t in (0, 1, 17, 50):
+        a = [int(v) for v in hh[0]]
+        b = wrap(wrap(a[0] * t) + a[1]) % LARGEPRIME % 97
+        assert b == int(h.buckets[0, t])
+        s = wrap(wrap(wrap(wrap(wrap(wrap(a[2] * t) + a[3]) * t) + a[4]) * t) + a[5]) % LARGEPRIME % 2 * 2 - 1
+        assert s == int(h.signs[0, t])
+        packed = int(h.packed[0, t])
+        assert (packed & 0x7FFFFFFF) == b and ((packed < 0) == (s < 0))
+
+
+def test_csvec_api_roundtrip():
+    d, c, r = 5000, 2000, 5
+    v = torch.zeros(d)
+    hot = torch.randperm(d)[:20]
+    v[hot] = torch.randn(20) * 10 + 20 * torch.randn(20).sign()
+    s = CSVec(d, c, r, device="cpu", numBlocks=4)
+    s.accumulateVec(v)
+    rec = s.unSketch(k=20)
+    assert set(rec.nonzero().view(-1).tolist()) == set(hot.tolist())
+    torch.testing.assert_close(rec[hot], v[hot])
+    assert s.l2estimate() == pytest.approx(v.norm().item(), rel=0.2)
+    s2 = CSVec(d, c, r, device="cpu", numBlocks=4)
+    s2.accumulateTable(s.table)
+    s2 += s
+    torch.testing.assert_close(s2.table, 2 * s.table)
+    out = clip_grad(1.0, s2)
+    assert out is s2 and s2.l2estimate() == pytest.approx(1.0, rel=1e-4)
+    s2.zero()
+    assert float(s2.table.abs().sum()) == 0
+
+
+def test_topk_oracle():
+    v = torch.tensor([1.0, -5.0, 3.0, float("nan"), 0.5])
+    out = _topk(v, 2)
+    assert out.tolist() == [0.0, -5.0, 3.0, 0.0, 0.0]
+    m = _topk(torch.tensor([[1.0, 2.0, -3.0], [4.0, -1.0, 0.0]]), 1)
+    assert m.tolist() == [[0.0, 0.0, -3.0], [4.0, 0.0, 0.0]]
+
+
+def test_server_rules_oracle_sketch_zeroes_buckets():
+    d, c, r = 2000, 500, 5
+    h = make_hashes(d, c, r, 1)
+    g = torch.zeros(d)
+    g[7] = 10.0
+    table = torch.zeros(r, c)
+    ref.sketch_accum_ref(table, g, h)
+    Vv, Ve = torch.zeros(r, c), torch.zeros(r, c)
+    _, (idx, val) = ref.server_update_ref("sketch", table, Vv, Ve, rho=0.9, lr=0.1, k=1, error_type="virtual", hashes=h)
+    assert idx.tolist() == [7] and val.item() == pytest.approx(1.0)
+    assert float(Ve.abs().sum()) == 0 and float(Vv.abs().sum()) == 0
+
+
+def test_sampler_and_datasets(tmp_path):
+    du.write_synthetic_cifar(str(tmp_path / "c"), images_per_class=20, num_val=30)
+    np.random.seed(0)
+    ds = du.FedCIFAR10(str(tmp_path / "c"), "CIFAR10", None, False, 40, train=True)
+    assert len(ds) == 200 and ds.num_clients == 40 and ds.data_per_client.tolist() == [5] * 40
+    cid, img, y = ds[0]
+    assert cid == 0 and y == 0
+    cid, img, y = ds[199]
+    assert cid == 39 and y == 9
+    sampler = du.FedSampler(ds, 8, -1, seed=3)
+    rounds = list(iter(sampler))
+    assert len(rounds) == 5 and all(len(r) == 40 for r in rounds)
+    assert sorted(np.concatenate(rounds).tolist()) == list(range(200))
+    again = list(iter(du.FedSampler(ds, 8, -1, seed=3)))
+    assert all((a == b).all() for a, b in zip(rounds, again))       # every rank derives the same schedule
+    iid = du.FedCIFAR10(str(tmp_path / "c"), "CIFAR10", None, True, 7, train=True)
+    assert iid.data_per_client.sum() == 200 and iid.num_clients == 7
+    val = du.FedCIFAR10(str(tmp_path / "c"), "CIFAR10", None, train=False)
+    assert len(val) == 30 and val[3][0] == -1
+
+
+def test_table_logger_prints(capsys):
+    t = TableLogger()
+    t.append({"epoch": 1, "lr": 0.1, "acc": np.float32(0.5)})
+    t.append({"epoch": 2, "lr": 0.2, "acc": np.float32(0.75)})
+    out = capsys.readouterr().out.splitlines()
+    assert len(out) == 3 and "epoch" in out[0] and "0.7500" in out[2]

@@ -1,0 +1,77 @@
+"""End-to-end rounds on the GPU (native kernels) against the same rounds on the CPU
+(torch oracles)."""
+import numpy as np
+import pytest
+import torch
+
+from commefficient_b200 import models
+from commefficient_b200.cv_train import compute_loss_train, compute_loss_val
+from commefficient_b200.data_utils import synthetic_image_batch
+from commefficient_b200.fed_aggregator import FedModel, FedOptimizer
+from commefficient_b200.ops import native
+from commefficient_b200.utils import make_args
+
+pytestmark = pytest.mark.gpu
+
+SMALL = {"prep": 8, "layer1": 16, "layer2": 16, "layer3": 32}
+
+
+def _run(device, mode, rounds=3, **kw):
+    torch.manual_seed(0)
+    base = dict(mode=mode, num_workers=4, num_clients=32, local_batch_size=-1, k=300, num_cols=4000, num_rows=5,
+                num_blocks=4, device=device, dataset_name="CIFAR10", precision="fp32", weight_decay=5e-4,
+                local_momentum=0.0, virtual_momentum=0.9,
+                error_type="virtual" if mode in ("sketch", "true_topk") else "none")
+    base.update(kw)
+    args = make_args(**base)
+    model = models.ResNet9(num_classes=10, channels=SMALL)
+    fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+    opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+    opt.param_groups[0]["lr"] = 0.05
+    losses = []
+    for step in range(rounds):
+        fed.train(True)
+        out = fed(synthetic_image_batch(4, 6, seed=step, first_client=4 * step))
+        opt.step()
+        losses.append(float(np.mean(out[0])))
+    w = fed.fp.flat.detach().cpu().clone()
+    fed.rt.shutdown()
+    return w, losses, out
+
+
+@pytest.mark.parametrize("mode,kw", [
+    ("uncompressed", {}),
+    ("uncompressed", {"local_momentum": 0.9}),
+    ("sketch", {}),
+    ("sketch", {"max_grad_norm": 1.0}),
+    ("true_topk", {}),
+    ("local_topk", {"error_type": "local", "local_momentum": 0.9}),
+    ("fedavg", {"num_fedavg_epochs": 2, "fedavg_batch_size": 3}),
+])
+def test_round_matches_cpu(mode, kw):
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        native.reset_launch_count()
+        wg, lg, out = _run("cuda", mode, **kw)
+        assert native.launch_count() > 0, "native kernels did not run"
+        wc, lc, _ = _run("cpu", mode, **kw)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    np.testing.assert_allclose(lg, lc, rtol=2e-3, atol=2e-3)
+    # sparse modes may pick different near-tie coordinates; compare in aggregate
+    rel = (wg - wc).norm() / wc.norm()
+    assert rel < (5e-2 if mode in ("sketch", "true_topk", "local_topk") else 1e-3), rel
+    assert out[-1].sum() > 0 and out[-2].shape == out[-1].shape
+
+
+def test_client_batching_equals_per_client():
+    w1, l1, _ = _run("cuda", "sketch")
+    w2, l2, _ = _run("cuda", "sketch", no_client_batching=True)
+    np.testing.assert_allclose(l1, l2, rtol=1e-3, atol=1e-3)
+    assert (w1 - w2).norm() / w2.norm() < 5e-2
+
+
+def test_smoke_entry():
+    import __graft_entry__ as g
+    g.smoke()
