@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""Headline benchmark: clients/sec per federated round (BASELINE.json), ResNet-9 on
+CIFAR-10-shaped synthetic data, FetchSGD sketch mode (5 x 500 000 sketch, k = 50 000,
+virtual momentum 0.9, virtual error), 100 clients per round per GPU, 5 images per client.
+
+  python bench.py --gpus 1 --steps K --warmup W                       (ours, 1 GPU)
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...   (ours, N GPUs)
+  python bench.py --impl reference --gpus N ...                        (unmodified reference)
+
+Prints ONE JSON line on rank 0.  Timing: CUDA events on the compute stream around exactly K
+rounds, barrier + synchronize on both sides, max over ranks.  ``value`` is timed with the
+round's inputs already on the device; ``e2e`` is the same public API call
+(``model(batch); opt.step()``) with every round's inputs copied from pinned host memory and the
+per-client results read back to the host, as a user runs it.  Scaling is weak: each GPU
+simulates 100 clients per round, so N GPUs run 100*N clients per round.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "clients/sec per FL round (device-timed, max over ranks)"
+CLIENTS_PER_GPU = 100
+IMAGES_PER_CLIENT = 5
+NUM_CLIENTS = 10000
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--mode", default="sketch")
+    ap.add_argument("--model", default="ResNet9")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--backend", default="auto")
+    ap.add_argument("--native_nn", action="store_true")
+    ap.add_argument("--clients_per_gpu", type=int, default=CLIENTS_PER_GPU)
+    ap.add_argument("--phases", action="store_true", help="also print a per-phase breakdown to stderr")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------- clocks
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.proc = None
+        self.path = "/tmp/ceb_clocks_%d.csv" % os.getpid()
+        self.gpu_index = gpu_index
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_index), "--query-gpu=" + self.QUERY,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        try:
+            for line in open(self.path):
+                parts = [p.strip() for p in line.split(",")]
+                if len(parts) < 9:
+                    continue
+                try:
+                    sm.append(float(parts[1]))
+                    mx.append(float(parts[2]))
+                except ValueError:
+                    continue
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"),
+                                     parts[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+            os.remove(self.path)
+        except Exception:
+            pass
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ---------------------------------------------------------------------------- reference arm
+def run_reference(cfg):
+    ref_dir = os.path.join(ROOT, "baseline", "_ref", "CommEfficient")
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0            # the reference spawns its own worker processes from rank 0
+    if not os.path.exists(os.path.join(ref_dir, "fed_aggregator.py")):
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is not installed (see DESIGN.md)"}))
+        return 0
+    env = dict(os.environ)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "LOCAL_WORLD_SIZE",
+              "GROUP_RANK", "ROLE_RANK", "TORCHELASTIC_RUN_ID"):
+        env.pop(k, None)
+    clients = cfg.clients_per_gpu * cfg.gpus
+    cmd = [sys.executable, os.path.join(ROOT, "baseline", "run_ref.py"), "--gpus", str(cfg.gpus),
+           "--steps", str(cfg.steps), "--warmup", str(cfg.warmup), "--clients_per_round", str(clients),
+           "--per_client", str(IMAGES_PER_CLIENT), "--num_clients", str(NUM_CLIENTS),
+           "--port", str(5315 + os.getpid() % 500)]
+    sampler = ClockSampler(0)
+    sampler.start()
+    try:
+        res = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                             timeout=3000)
+    except subprocess.TimeoutExpired:
+        sampler.stop()
+        print(json.dumps({"impl": "reference", "unavailable": "reference run exceeded 3000 s"}))
+        return 0
+    clocks = sampler.stop()
+    line = [l for l in res.stdout.splitlines() if l.startswith("REF_RESULT ")]
+    if res.returncode != 0 or not line:
+        tail = (res.stderr or res.stdout).strip().splitlines()[-3:]
+        print(json.dumps({"impl": "reference", "unavailable": "reference run failed: " + " | ".join(tail)[:400]}))
+        return 0
+    r = json.loads(line[-1][len("REF_RESULT "):])
+    value = r["clients_per_sec"]
+    out = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "clients/s", "n_gpus": cfg.gpus,
+        "steps": cfg.steps, "warmup": cfg.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+        "config": {"model": "ResNet9", "mode": "sketch", "num_rows": 5, "num_cols": 500000, "k": 50000,
+                   "global_batch": clients * IMAGES_PER_CLIENT, "clients_per_round": clients,
+                   "clients_processed_per_round": r["clients_processed_per_round"],
+                   "images_per_client": IMAGES_PER_CLIENT,
+                   "parallelism": "ps+%dworkers" % r["worker_procs"],
+                   "l2": "inputs + activations exceed L2; fresh inputs every round",
+                   "one_gpu_transport_gloo": r["one_gpu_transport"]},
+        "e2e": {"value": value, "unit": "clients/s", "h2d_bytes_per_step": r["h2d_bytes_per_step"],
+                "d2h_bytes_per_step": r["d2h_bytes_per_step"]},
+        "gpu_launches": 0, "clocks": clocks, "last_loss": r["last_loss"],
+    }
+    print(json.dumps(out))
+    return 0
+
+
+# ---------------------------------------------------------------------------- our arm
+def run_ours(cfg):
+    import torch
+    from commefficient_b200 import models
+    from commefficient_b200.cv_train import compute_loss_train, compute_loss_val
+    from commefficient_b200.data_utils import synthetic_image_batch
+    from commefficient_b200.fed_aggregator import FedModel, FedOptimizer
+    from commefficient_b200.ops import native
+    from commefficient_b200.ops import nn as nnops
+    from commefficient_b200.parallel.runtime import init_runtime
+    from commefficient_b200.utils import make_args
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"metric": METRIC, "error": "no CUDA device"}))
+        return 1
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != cfg.gpus:
+        if world == 1 and cfg.gpus > 1:
+            # convenience: relaunch ourselves under torchrun
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(cfg.gpus),
+                   "--master-addr", "127.0.0.1", "--master-port", str(29400 + os.getpid() % 500)] + sys.argv
+            return subprocess.call(cmd)
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (cfg.gpus, world))
+    clients = cfg.clients_per_gpu * cfg.gpus
+    args = make_args(mode=cfg.mode, error_type="virtual" if cfg.mode in ("sketch", "true_topk") else "none",
+                     local_momentum=0.0, virtual_momentum=0.9, num_workers=clients, num_clients=NUM_CLIENTS,
+                     local_batch_size=-1, num_epochs=1.0, dataset_name="CIFAR10", device="cuda",
+                     precision=cfg.precision, backend=cfg.backend, model=cfg.model)
+    rt = init_runtime(args)
+    torch.manual_seed(args.seed)
+    torch.backends.cudnn.benchmark = True
+    if cfg.native_nn:
+        nnops.set_native(True)
+    model = getattr(models, cfg.model)(num_classes=10)
+    fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+    opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+    opt.param_groups[0]["lr"] = 0.05
+    fed.train(True)
+
+    n_distinct = 4
+    host_rounds = [synthetic_image_batch(clients, IMAGES_PER_CLIENT, seed=s, first_client=(s * clients) % (NUM_CLIENTS - clients),
+                                         pin=True) for s in range(n_distinct)]
+    dev = rt.device
+    dev_rounds = [(ids, img.to(dev), lab.to(dev)) for ids, img, lab in host_rounds]
+    per_rank_samples = cfg.clients_per_gpu * IMAGES_PER_CLIENT
+    h2d = per_rank_samples * (3 * 32 * 32 * 4 + 8)
+    d2h = clients * (args.num_results_train + 1) * 4
+
+    def one_round(batch):
+        out = fed(batch)
+        opt.step()
+        return out
+
+    def timed(rounds, steps, warmup):
+        for i in range(warmup):
+            one_round(rounds[i % len(rounds)])
+        rt.barrier()
+        torch.cuda.synchronize()
+        native.reset_launch_count()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = None
+        for i in range(steps):
+            out = one_round(rounds[(warmup + i) % len(rounds)])
+        b.record()
+        rt.barrier()
+        torch.cuda.synchronize()
+        ms = rt.max_over_ranks(a.elapsed_time(b))
+        return ms / steps, native.launch_count(), out
+
+    sampler = ClockSampler(dev.index or 0)
+    if rt.rank == 0:
+        sampler.start()
+    ms_dev, launches_dev, _ = timed(dev_rounds, cfg.steps, cfg.warmup)
+    ms_e2e, launches, out = timed(host_rounds, cfg.steps, max(3, cfg.warmup))
+    clocks = sampler.stop() if rt.rank == 0 else None
+    last_loss = float(out[0].mean())
+
+    if cfg.phases and rt.rank == 0:
+        _phase_breakdown(fed, opt, dev_rounds, torch)
+
+    if rt.rank == 0:
+        value = clients / (ms_dev / 1e3)
+        e2e = clients / (ms_e2e / 1e3)
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": "clients/s", "n_gpus": cfg.gpus, "steps": cfg.steps,
+            "warmup": cfg.warmup, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": cfg.precision, "data": "synthetic",
+            "config": {"model": cfg.model, "mode": cfg.mode, "num_rows": args.num_rows, "num_cols": args.num_cols,
+                       "k": args.k, "global_batch": clients * IMAGES_PER_CLIENT, "clients_per_round": clients,
+                       "images_per_client": IMAGES_PER_CLIENT, "seq_len": None,
+                       "parallelism": "dp%d" % cfg.gpus, "backend": rt.backend,
+                       "client_batching": fed.worker.can_batch_clients(), "native_nn": bool(cfg.native_nn),
+                       "l2": "weights+grads+sketch+activations (>300 MB/round) exceed the 126 MB L2; "
+                             "%d distinct input batches rotate" % n_distinct},
+            "e2e": {"value": e2e, "unit": "clients/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches), "clocks": clocks, "last_loss": last_loss,
+        }))
+    rt.shutdown()
+    return 0
+
+
+def _phase_breakdown(fed, opt, rounds, torch):
+    """Per-phase device times of one round (stderr; not part of the JSON contract)."""
+    import numpy as np
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    acc = {}
+    for i in range(5):
+        e = [ev() for _ in range(3)]
+        e[0].record()
+        fed(rounds[i % len(rounds)])
+        e[1].record()
+        opt.step()
+        e[2].record()
+        torch.cuda.synchronize()
+        acc.setdefault("clients+sketch+reduce", []).append(e[0].elapsed_time(e[1]))
+        acc.setdefault("server_step", []).append(e[1].elapsed_time(e[2]))
+    print("phase ms: " + ", ".join("%s=%.3f" % (k, float(np.median(v))) for k, v in acc.items()), file=sys.stderr)
+
+
+def main():
+    cfg = parse()
+    if cfg.impl == "reference":
+        return run_reference(cfg)
+    return run_ours(cfg)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -192,8 +192,11 @@ class FedModel:
             starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
             pos = np.searchsorted(unique, mine)
             sorted_already = bool(np.all(order == np.arange(len(order))))
-            if sorted_already and len(mine) == len(unique):
-                dev_cols = [self._to_device(t) for t in cols]
+            if sorted_already and int(pos[-1] - pos[0]) + 1 == len(pos):
+                # this rank's clients are one contiguous run of samples: slice (views of the
+                # caller's -- ideally pinned -- tensors), then one async H2D per column
+                a, b = int(starts[pos[0]]), int(starts[pos[-1]] + counts[pos[-1]])
+                dev_cols = [self._to_device(t[a:b]) for t in cols]
             else:
                 sel = np.concatenate([order[starts[p]:starts[p] + counts[p]] for p in pos])
                 sel_t = torch.from_numpy(sel)
