@@ -359,3 +359,78 @@ CEB_API int ceb_sketch_apply_zero(const int32_t* idx, const float* val, int64_t 
   CEB_CHECK_LAUNCH();
   return 0;
 }
+
+// ------------------------------------------------------------------ heavy-hitter recovery without any allocation
+// ceb_sketch_unsketch_topk needs two pieces of scratch from its caller: the d-float
+// estimate vector and the radix-select block.  Some hosts of this library cannot supply
+// them: an aggregation service whose device memory was carved up once at start-up and
+// handed to other owners, a plug-in living inside another framework's memory pool with
+// no right to ask it for more, or a latency-critical loop that must not risk the
+// device-wide synchronisation a cudaMalloc can cause.  For them the variant below keeps
+// its scratch in one file-scope device array that is part of the loaded module.
+//
+// Cost and limits, stated plainly:
+//   * the array is CEB_STATIC_UNSKETCH_MAX_D floats (8 Mi coordinates = 32 MiB) plus the
+//     ~26 KB select block; every GPU on which this library is loaded holds it until the
+//     process exits, whether or not this entry point is ever called;
+//   * d above that maximum is refused with an error (use ceb_sketch_unsketch_topk);
+//   * all calls on a device share the one array: it still holds the previous call's
+//     contents, so the select block is re-zeroed here on every call, and two calls that
+//     overlap on the GPU (different streams, no ordering between them) race on it.
+#include <mutex>
+
+constexpr int64_t kStaticMaxCoords = (int64_t)CEB_STATIC_UNSKETCH_MAX_D;
+constexpr size_t kStaticSelectBytes = (sizeof(CebSelectScratch) + 255) / 256 * 256;
+static __device__ __align__(256) unsigned char
+    g_static_unsketch_scratch[kStaticSelectBytes + (size_t)kStaticMaxCoords * sizeof(float)];
+
+// In host code the array's name is only a handle for the runtime, not an address a kernel
+// can use; the real device address is looked up once per device (that device current).
+static unsigned char* g_static_scratch_addr[64] = {nullptr};
+static std::mutex g_static_scratch_mutex;
+
+static int static_scratch_for_current_device(unsigned char** out) {
+  int dev = -1;
+  CEB_CHECK_CUDA(cudaGetDevice(&dev));
+  CEB_REQUIRE(dev >= 0 && dev < 64, "static scratch: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (g_static_scratch_addr[dev] == nullptr) {
+    unsigned char* p = nullptr;
+    CEB_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_static_unsketch_scratch));
+    CEB_REQUIRE(p != nullptr, "static scratch: cudaGetSymbolAddress returned a null address");
+    g_static_scratch_addr[dev] = p;
+  }
+  *out = g_static_scratch_addr[dev];
+  return 0;
+}
+
+// Same result as ceb_sketch_unsketch_topk (out_idx/out_val: the k largest-magnitude median
+// estimates, unordered) with no scratch arguments and no allocation of any kind.  The first
+// call on each device resolves the scratch address (cudaGetSymbolAddress); make that first
+// call outside any stream capture.
+CEB_API int ceb_sketch_unsketch_topk_static(const float* table, const int32_t* packed, int64_t n_tokens,
+                                            const int32_t* blk, int num_blocks, int r, int64_t c,
+                                            int64_t d, int64_t k, int32_t* out_idx, float* out_val,
+                                            void* stream) {
+  CEB_REQUIRE(d <= kStaticMaxCoords,
+              "ceb_sketch_unsketch_topk_static: d=%lld exceeds the built-in scratch (%lld coordinates); "
+              "use ceb_sketch_unsketch_topk with caller-provided scratch",
+              (long long)d, (long long)kStaticMaxCoords);
+  CEB_REQUIRE(table && packed && blk && out_idx && out_val, "ceb_sketch_unsketch_topk_static: null pointer");
+  if (int e = check_sketch_dims("ceb_sketch_unsketch_topk_static", r, c, d, n_tokens, num_blocks)) return e;
+  CEB_REQUIRE(k > 0 && k <= d, "ceb_sketch_unsketch_topk_static: need 0 < k <= d (k=%lld d=%lld)",
+              (long long)k, (long long)d);
+  unsigned char* base = nullptr;
+  if (int e = static_scratch_for_current_device(&base)) return e;
+  CebSelectScratch* s = (CebSelectScratch*)base;
+  float* est = (float*)(base + kStaticSelectBytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  // histograms, tickets and counters must start at zero; est is fully overwritten for i < d
+  CEB_CHECK_CUDA(cudaMemsetAsync(s, 0, sizeof(CebSelectScratch), st));
+  dim3 grid = token_grid(n_tokens, num_blocks, kSelThreads);
+  CEB_DISPATCH_ROWS(r, (unsketch_est_kernel<R><<<grid, kSelThreads, 0, st>>>(
+                           table, (uint32_t)c, packed, n_tokens, blk, num_blocks, d, est, s, (uint32_t)k)));
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return ceb_select_run(est, d, k, s, out_idx, out_val, true, st);
+}

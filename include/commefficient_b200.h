@@ -61,6 +61,18 @@ int ceb_sketch_unsketch_topk(const float* table, const int32_t* packed, int64_t 
                              const int32_t* blk, int num_blocks, int r, int64_t c, int64_t d, int64_t k,
                              float* est, void* scratch, int64_t scratch_bytes, int32_t* out_idx,
                              float* out_val, void* stream);
+/* Allocation-free variant of ceb_sketch_unsketch_topk (no counterpart in the reference:
+ * it exists for hosts of this library that may not allocate device memory -- a service whose
+ * GPU memory was partitioned once at start-up, a plug-in inside another framework's pool, a
+ * latency-critical loop that must avoid cudaMalloc's device-wide synchronisation).  Scratch
+ * lives in a device array built into the library: CEB_STATIC_UNSKETCH_MAX_D floats + ~26 KB
+ * on every GPU that loads the library, held until exit.  d above the maximum is an error.
+ * All calls on a device share that array (overlapping calls race; serialise them), and the
+ * first call on a device looks up its address -- do that call outside stream capture. */
+#define CEB_STATIC_UNSKETCH_MAX_D (8 * 1024 * 1024)
+int ceb_sketch_unsketch_topk_static(const float* table, const int32_t* packed, int64_t n_tokens,
+                                    const int32_t* blk, int num_blocks, int r, int64_t c, int64_t d,
+                                    int64_t k, int32_t* out_idx, float* out_val, void* stream);
 /* out[j] = estimate of coordinate idx[j] (idx NULL: coordinates 0..count-1). */
 int ceb_sketch_query(const float* table, const int32_t* packed, int64_t n_tokens, const int32_t* blk,
                      int num_blocks, int r, int64_t c, int64_t d, const int32_t* idx, int64_t count,
