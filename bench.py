@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--native_nn", action="store_true")
     ap.add_argument("--clients_per_gpu", type=int, default=CLIENTS_PER_GPU)
     ap.add_argument("--phases", action="store_true", help="also print a per-phase breakdown to stderr")
+    ap.add_argument("--profile", action="store_true",
+                    help="profiling aid: device-resident phase only, wrapped in cudaProfilerStart/Stop "
+                         "(use with ncu --profile-from-start off); the printed number is NOT a bench value")
     return ap.parse_args()
 
 
@@ -229,8 +232,20 @@ def run_ours(cfg):
         return ms / steps, native.launch_count(), out
 
     sampler = ClockSampler(dev.index or 0)
-    if rt.rank == 0:
+    if rt.rank == 0 and not cfg.profile:
         sampler.start()
+    if cfg.profile:
+        for i in range(cfg.warmup):
+            one_round(dev_rounds[i % n_distinct])
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        for i in range(cfg.steps):
+            one_round(dev_rounds[i % n_distinct])
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        print(json.dumps({"profile_run": True, "steps": cfg.steps}))
+        rt.shutdown()
+        return 0
     ms_dev, launches_dev, _ = timed(dev_rounds, cfg.steps, cfg.warmup)
     ms_e2e, launches, out = timed(host_rounds, cfg.steps, max(3, cfg.warmup))
     clocks = sampler.stop() if rt.rank == 0 else None

@@ -215,7 +215,11 @@ class ClientWorker:
         self.args = args
         self.device = torch.device(device)
         self.model = model
-        self.fp = FlatParams(model, self.device)
+        layout = getattr(args, "flat_layout", "auto")
+        if layout == "auto":
+            layout = "nhwc" if self.device.type == "cuda" else "reference"
+        self.channels_last = layout == "nhwc"
+        self.fp = FlatParams(model, self.device, layout=layout)
         model._flat_params = self.fp
         self.compute_loss_train = compute_loss_train
         self.compute_loss_val = compute_loss_val or compute_loss_train
@@ -243,6 +247,14 @@ class ClientWorker:
         self._ps_copy = None
         self.has_bn = _has_batchnorm(model)
         self.last_clients: List[int] = []
+
+    def _prep(self, cols: Sequence[torch.Tensor]) -> List[torch.Tensor]:
+        """Image batches go channels_last when the weights are stored NHWC, so cuDNN / the
+        native kernels never insert layout transposes."""
+        if not self.channels_last:
+            return list(cols)
+        return [t.contiguous(memory_format=torch.channels_last)
+                if (t.dim() == 4 and t.is_floating_point()) else t for t in cols]
 
     # -- which path ----------------------------------------------------------------
     def can_batch_clients(self) -> bool:
@@ -287,7 +299,7 @@ class ClientWorker:
         a, fp = self.args, self.fp
         sizes = [b[0].shape[0] for _, b in client_batches]
         ncols = len(client_batches[0][1])
-        cat = [torch.cat([b[j] for _, b in client_batches]) for j in range(ncols)]
+        cat = self._prep([torch.cat([b[j] for _, b in client_batches]) for j in range(ncols)])
         seg = torch.repeat_interleave(torch.arange(len(sizes), device=self.device),
                                       torch.tensor(sizes, device=self.device))
         total = int(sum(sizes))
@@ -336,7 +348,7 @@ class ClientWorker:
         if self.client_weights is not None:
             stale, new = self._client_weights_in(cid)
         fp.zero_grad()
-        results, num_iters = _run_microbatches(self.model, batch, self.compute_loss_train, a, True)
+        results, num_iters = _run_microbatches(self.model, self._prep(batch), self.compute_loss_train, a, True)
         sketch_fold = a.mode == "sketch" and not a.do_dp
         _finish_client_grad(fp, a, num_iters, fold_weight_decay=not sketch_fold)
         if a.mode == "sketch":
@@ -378,6 +390,7 @@ class ClientWorker:
         for cid, batch in client_batches:
             n_i = batch[0].shape[0]
             bs = n_i if a.fedavg_batch_size == -1 else a.fedavg_batch_size
+            batch = self._prep(batch)
             chunks = [[t[lo:lo + bs] for t in batch] for lo in range(0, n_i, bs)]
             step, acc = 0, None
             for _epoch in range(a.num_fedavg_epochs):
@@ -404,7 +417,7 @@ class ClientWorker:
                 if self.args.do_test:
                     out.append(torch.ones(self.args.num_results_val, device=self.device))
                     continue
-                res, _ = _run_microbatches(self.model, shard, self.compute_loss_val, self.args, False)
+                res, _ = _run_microbatches(self.model, self._prep(shard), self.compute_loss_val, self.args, False)
                 out.append(res)
         return torch.stack(out)
 

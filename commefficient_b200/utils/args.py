@@ -125,6 +125,9 @@ _FLAGS = [
               help="always run one backward per client (disables the linearity fast path)"),
         _flag("resume", None, str, help="path of a *.fedstate.pt sidecar to resume from"),
         _flag("watchdog_timeout", 600.0, float, help="seconds before a hung round aborts all ranks"),
+        _flag("flat_layout", "auto", str, choices=("auto", "reference", "nhwc"),
+              help="coordinate order of conv weights in the flat buffer: reference = (out,in,kh,kw); "
+                   "nhwc = (out,kh,kw,in), channels_last end to end (auto: nhwc on CUDA)"),
         _flag("native_nn", store_true=True,
               help="route conv/linear through the hand-written tcgen05 kernels"),
     ]),

@@ -24,7 +24,18 @@ import torch
 class FlatParams:
     """Owns ``flat`` (weights) and ``grad`` (gradients) for one module replica."""
 
-    def __init__(self, model: torch.nn.Module, device=None, align: int = 1):
+    def __init__(self, model: torch.nn.Module, device=None, align: int = 1, layout: str = "reference"):
+        """``layout="reference"``: every parameter occupies its slice in C-contiguous
+        (out, in, kh, kw) order -- coordinate i of the flat vector is coordinate i of the
+        reference's.  ``layout="nhwc"``: 4-D (convolution) weights are stored
+        (out, kh, kw, in) -- the K-major "KRSC" layout tensor-core implicit GEMM wants -- and
+        exposed to the module as channels_last views of the usual logical shape, so neither
+        cuDNN nor the native kernels ever transpose weights or weight gradients.  Only the
+        order of coordinates *inside* a conv weight changes (a relabelling the sketch and
+        top-k are indifferent to); ``state_dict`` keys, shapes and values are unchanged."""
+        if layout not in ("reference", "nhwc"):
+            raise ValueError("layout must be 'reference' or 'nhwc'")
+        self.layout = layout
         params = [p for p in model.parameters() if p.requires_grad]
         if not params:
             raise ValueError("model has no trainable parameters")
@@ -46,33 +57,49 @@ class FlatParams:
         self.flat = self._flat_store[:off]
         self.grad = self._grad_store[:off]
         with torch.no_grad():
-            for p, o, n in zip(params, self.offsets, self.sizes):
-                self.flat[o:o + n].copy_(p.data.reshape(-1).to(device=device, dtype=torch.float32))
+            for p, o, n, shp in zip(params, self.offsets, self.sizes, self.shapes):
+                self._view(self.flat, o, n, shp).copy_(p.data.to(device=device, dtype=torch.float32))
         model.to(device)
         self._bind()
 
+    def _view(self, store: torch.Tensor, o: int, n: int, shp):
+        """Logical-shape view of one parameter's slice of ``store``."""
+        flat = store[o:o + n]
+        if self.layout == "nhwc" and len(shp) == 4:
+            co, ci, kh, kw = shp
+            return flat.view(co, kh, kw, ci).permute(0, 3, 1, 2)
+        return flat.view(shp)
+
     def _bind(self):
         for p, o, n, shp in zip(self.params, self.offsets, self.sizes, self.shapes):
-            p.data = self.flat[o:o + n].view(shp)
-            p.grad = self.grad[o:o + n].view(shp)
+            p.data = self._view(self.flat, o, n, shp)
+            p.grad = self._view(self.grad, o, n, shp)
 
     def rebind(self):
         """Re-establish the views (after ``model.to()`` / ``load_state_dict`` with
         ``assign=True`` or anything else that swapped ``p.data``)."""
         with torch.no_grad():
-            for p, o, n in zip(self.params, self.offsets, self.sizes):
+            for p, o, n, shp in zip(self.params, self.offsets, self.sizes, self.shapes):
                 if p.data.data_ptr() != self.flat[o:o + n].data_ptr():
-                    self.flat[o:o + n].copy_(p.data.reshape(-1))
+                    self._view(self.flat, o, n, shp).copy_(p.data)
         self._bind()
 
     def zero_grad(self):
         self.grad.zero_()
         for p, o, n, shp in zip(self.params, self.offsets, self.sizes, self.shapes):
             if p.grad is None or p.grad.data_ptr() != self.grad[o:o + n].data_ptr():
-                p.grad = self.grad[o:o + n].view(shp)
+                p.grad = self._view(self.grad, o, n, shp)
 
     def set_weights(self, vec: torch.Tensor):
+        """``vec`` is in this buffer's own coordinate order."""
         self.flat.copy_(vec.reshape(-1))
+
+    def to_reference_order(self, store: torch.Tensor) -> torch.Tensor:
+        """Copy of ``store`` (weights- or gradient-shaped) in the reference's coordinate order."""
+        if self.layout == "reference":
+            return store.clone()
+        return torch.cat([self._view(store, o, n, shp).reshape(-1)
+                          for o, n, shp in zip(self.offsets, self.sizes, self.shapes)])
 
     def segment_vector(self, values) -> torch.Tensor:
         """Expand one scalar per parameter tensor into a length-d vector in flat

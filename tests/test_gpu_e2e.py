@@ -20,7 +20,7 @@ def _run(device, mode, rounds=3, **kw):
     torch.manual_seed(0)
     base = dict(mode=mode, num_workers=4, num_clients=32, local_batch_size=-1, k=300, num_cols=4000, num_rows=5,
                 num_blocks=4, device=device, dataset_name="CIFAR10", precision="fp32", weight_decay=5e-4,
-                local_momentum=0.0, virtual_momentum=0.9,
+                local_momentum=0.0, virtual_momentum=0.9, flat_layout="reference",
                 error_type="virtual" if mode in ("sketch", "true_topk") else "none")
     base.update(kw)
     args = make_args(**base)
@@ -34,7 +34,7 @@ def _run(device, mode, rounds=3, **kw):
         out = fed(synthetic_image_batch(4, 6, seed=step, first_client=4 * step))
         opt.step()
         losses.append(float(np.mean(out[0])))
-    w = fed.fp.flat.detach().cpu().clone()
+    w = fed.fp.to_reference_order(fed.fp.flat).detach().cpu()
     fed.rt.shutdown()
     return w, losses, out
 
@@ -70,6 +70,19 @@ def test_client_batching_equals_per_client():
     w2, l2, _ = _run("cuda", "sketch", no_client_batching=True)
     np.testing.assert_allclose(l1, l2, rtol=1e-3, atol=1e-3)
     assert (w1 - w2).norm() / w2.norm() < 5e-2
+
+
+def test_nhwc_flat_layout_is_a_relabelling():
+    """Storing conv weights (out,kh,kw,in) changes no maths: dense modes give the same weights."""
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        w1, l1, _ = _run("cuda", "uncompressed", flat_layout="reference")
+        w2, l2, _ = _run("cuda", "uncompressed", flat_layout="nhwc")
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    np.testing.assert_allclose(l1, l2, rtol=1e-4, atol=1e-4)
+    assert (w1 - w2).norm() / w1.norm() < 1e-4
 
 
 def test_smoke_entry():
