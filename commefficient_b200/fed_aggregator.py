@@ -108,7 +108,13 @@ class FedModel:
         self.compute_loss_train = compute_loss
         self.compute_loss_val = compute_loss_val if compute_loss_val is not None else compute_loss
         self.worker = worker.ClientWorker(input_model, args, self.compute_loss_train, self.compute_loss_val,
-                                          self.device, self.num_clients)
+                                          self.device, self.num_clients, peer=self.rt.peer)
+        # With the peer-memory backend the cross-rank sum is fused into the server kernel
+        # (FedOptimizer.step); otherwise it happens here, right after the clients ran.
+        self.fused_reduce = (self.rt.peer is not None and args.mode in ("sketch", "uncompressed", "local_topk", "fedavg")
+                             and not (args.mode == "uncompressed" and args.do_dp and args.dp_mode == "server")
+                             and not getattr(args, "p2", 0))
+        self.reduce_pending = False
         self.fp = self.worker.fp
         if self.rt.world_size > 1:
             # replicas must start identical: take rank 0's initial weights
@@ -208,7 +214,10 @@ class FedModel:
                 client_batches.append((int(cid), [t[lo:lo + n] for t in dev_cols]))
                 lo += n
         local = self.worker.run_round(client_batches, fedavg_lr=self.fedavg_lr)
-        self.rt.all_reduce_sum_(self.worker.transmit)
+        if self.fused_reduce:
+            self.reduce_pending = True
+        else:
+            self.rt.all_reduce_sum_(self.worker.transmit)
         self.pending_samples = int(ids.shape[0])
         self.last_unique_clients = unique
         self.rounds += 1
@@ -304,8 +313,19 @@ class FedOptimizer(torch.optim.Optimizer):
         fm = self.fed_model
         device = fm.device
         shape = (args.num_rows, args.num_cols) if args.mode == "sketch" else (fm.fp.numel,)
-        self.Vvelocity = torch.zeros(shape, dtype=torch.float32, device=device)
-        self.Verror = torch.zeros(shape, dtype=torch.float32, device=device)
+        peer = fm.rt.peer
+        numel = int(np.prod(shape))
+        self.Vvelocity = torch.zeros(numel + 4, dtype=torch.float32, device=device)[:numel].view(shape)
+        self.verror_buf = None
+        if fm.fused_reduce and args.mode == "sketch":
+            # Verror lives in symmetric memory: the fused kernel all-gathers the updated error
+            # table straight into every rank's copy.  Vvelocity is only maintained on this
+            # rank's shard [shard_lo, shard_hi) of the flattened table.
+            self.verror_buf = peer.symm_empty(peer.padded(numel))
+            self.Verror = self.verror_buf.tensor[:numel].view(shape)
+        else:
+            self.Verror = torch.zeros(shape, dtype=torch.float32, device=device)
+        self.shard_lo, self.shard_hi = (peer.shard_range(peer.padded(numel)) if fm.fused_reduce else (0, numel))
         self._lr_vec = None
         self._lr_vec_key = None
         self._noise_calls = 0
@@ -353,9 +373,14 @@ class FedOptimizer(torch.optim.Optimizer):
         w = fm.fp.flat
         g = fm.worker.transmit
         rho = args.virtual_momentum
+        if fm.reduce_pending:
+            fm.reduce_pending = False
+            if self._step_fused(inv_n, rho, lr):
+                return
         if args.mode == "sketch":
             plan = fm.worker.plan
-            sk.server_update(self.Vvelocity, self.Verror, g, inv_n, rho, args.error_type)
+            if self.verror_buf is None:
+                sk.server_update(self.Vvelocity, self.Verror, g, inv_n, rho, args.error_type)
             src = self.Verror if args.error_type != "none" else self.Vvelocity
             if getattr(args, "p2", 0) and args.p2 > 0:
                 idx, val = self._second_round(plan, src, g, inv_n)
@@ -381,6 +406,23 @@ class FedOptimizer(torch.optim.Optimizer):
             dn.dense_server_update(self.Vvelocity, g, inv_n, rho, w, 1.0 if args.mode == "fedavg" else lr,
                                    noise_std=noise, seed=args.seed + 7, noise_offset=self._noise_calls << 20)
             fm.tracker.record_dense()
+
+    def _step_fused(self, inv_n, rho, lr) -> bool:
+        """Peer-memory path: the cross-rank reduce-scatter, the momentum/error (or momentum +
+        apply) update of this rank's shard and the all-gather run as ONE kernel over NVLink
+        (``csrc/peer.cu``).  Returns True when the whole server step is done."""
+        fm, args = self.fed_model, self.args
+        peer, w = fm.rt.peer, fm.worker
+        lo = self.shard_lo
+        vv_shard = self.Vvelocity.view(-1)[lo:]
+        if args.mode == "sketch":
+            ve_shard = self.Verror.view(-1)[lo:]
+            peer.fused_sketch(w.transmit_buf, self.verror_buf, vv_shard, ve_shard, inv_n, rho, args.error_type)
+            return False        # unsketch / top-k / zeroing / apply follow, replicated on every rank
+        peer.fused_dense(w.transmit_buf, w.weights_buf, vv_shard, inv_n, rho,
+                         1.0 if args.mode == "fedavg" else lr)
+        fm.tracker.record_dense()
+        return True
 
     def _second_round(self, plan, table, g_table, inv_n):
         """FetchSGD second round (``--p2``): recover ``p2*k`` candidates from the sketch,

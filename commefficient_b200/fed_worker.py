@@ -211,7 +211,7 @@ class ClientWorker:
     MAX_BATCHED_SAMPLES = 4096
 
     def __init__(self, model: torch.nn.Module, args, compute_loss_train: Callable,
-                 compute_loss_val: Optional[Callable], device, num_clients: Optional[int]):
+                 compute_loss_val: Optional[Callable], device, num_clients: Optional[int], peer=None):
         self.args = args
         self.device = torch.device(device)
         self.model = model
@@ -219,7 +219,14 @@ class ClientWorker:
         if layout == "auto":
             layout = "nhwc" if self.device.type == "cuda" else "reference"
         self.channels_last = layout == "nhwc"
-        self.fp = FlatParams(model, self.device, layout=layout)
+        self.peer = peer
+        self.weights_buf = None
+        flat_alloc = None
+        if peer is not None:
+            def flat_alloc(numel):
+                self.weights_buf = peer.symm_empty(numel)
+                return self.weights_buf.tensor
+        self.fp = FlatParams(model, self.device, layout=layout, flat_alloc=flat_alloc)
         model._flat_params = self.fp
         self.compute_loss_train = compute_loss_train
         self.compute_loss_val = compute_loss_val or compute_loss_train
@@ -232,7 +239,13 @@ class ClientWorker:
             self.transmit_shape = (args.num_rows, args.num_cols)
         else:
             self.transmit_shape = (self.d,)
-        self.transmit = torch.zeros(self.transmit_shape, dtype=torch.float32, device=self.device)
+        self.transmit_buf = None
+        if peer is not None:
+            numel = int(np.prod(self.transmit_shape))
+            self.transmit_buf = peer.symm_empty(peer.padded(numel))
+            self.transmit = self.transmit_buf.tensor[:numel].view(self.transmit_shape)
+        else:
+            self.transmit = torch.zeros(self.transmit_shape, dtype=torch.float32, device=self.device)
         self._tmp_table = None
         self.velocities = self.errors = self.client_weights = None
         persistent = not getattr(args, "compat_nonpersistent_client_state", False)

@@ -1,0 +1,173 @@
+"""Symmetric (peer-mapped) device buffers and the fused NVLink collectives built on them.
+
+Every rank ``cudaMalloc``s a buffer of the same size, exports it as a CUDA IPC handle, and
+maps every other rank's buffer (``csrc/peer.cu``).  Kernels then read and write peer memory
+directly over NVLink / NVSwitch; ranks synchronise through flags in that same memory.
+``torch.distributed`` is used once, at set-up, to exchange the 64-byte handles.
+
+Reference counterpart: the NCCL ``reduce`` + host-shm weight traffic of
+/root/reference/CommEfficient/fed_aggregator.py:301-332,455 and fed_worker.py:41,138.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import native
+
+native.register_signatures({
+    "ceb_peer_shard_elems": ([native.c_i64, native.c_i32], native.c_i64),
+    "ceb_peer_fused_reduce": ([native.c_i32, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                               native.c_i32, native.c_i32, ctypes.c_uint, native.c_i64, native.c_ptr,
+                               native.c_ptr, native.c_f32, native.c_f32, native.c_i32, native.c_f32,
+                               native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_peer_handle_bytes": ([], native.c_i32),
+    "ceb_peer_alloc": ([native.c_i64, ctypes.POINTER(ctypes.c_void_p), native.c_ptr], native.c_i32),
+    "ceb_peer_open": ([native.c_ptr, ctypes.POINTER(ctypes.c_void_p)], native.c_i32),
+    "ceb_peer_release": ([native.c_ptr, native.c_i32], native.c_i32),
+})
+
+
+class _RawCuda:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can wrap a raw device pointer."""
+
+    def __init__(self, ptr: int, numel: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+class SymmBuffer:
+    """One symmetric allocation: ``tensor`` is this rank's memory, ``ptrs[q]`` rank q's."""
+
+    def __init__(self, group: "PeerGroup", numel: int, dtype=torch.float32):
+        lib = native.lib()
+        self.group = group
+        self.numel = int(numel)
+        itemsize = torch.empty((), dtype=dtype).element_size()
+        nbytes = max(256, self.numel * itemsize)
+        hb = int(lib.ceb_peer_handle_bytes())
+        handle = ctypes.create_string_buffer(hb)
+        local = ctypes.c_void_p()
+        native.check(lib.ceb_peer_alloc(nbytes, ctypes.byref(local), handle), "ceb_peer_alloc")
+        self.local_ptr = int(local.value)
+        handles: List[Optional[bytes]] = [None] * group.world
+        dist.all_gather_object(handles, bytes(handle.raw))
+        self.ptrs: List[int] = []
+        for q, h in enumerate(handles):
+            if q == group.rank:
+                self.ptrs.append(self.local_ptr)
+                continue
+            p = ctypes.c_void_p()
+            native.check(lib.ceb_peer_open(ctypes.create_string_buffer(h, hb), ctypes.byref(p)), "ceb_peer_open")
+            self.ptrs.append(int(p.value))
+        typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+        self.tensor = torch.as_tensor(_RawCuda(self.local_ptr, self.numel, typestr), device=group.device)
+        self.ptr_array = (ctypes.c_void_p * group.world)(*self.ptrs)
+        self._closed = False
+
+    def close(self):
+        if self._closed:
+            return
+        self._closed = True
+        lib = native.lib()
+        for q, p in enumerate(self.ptrs):
+            if q != self.group.rank:
+                lib.ceb_peer_release(ctypes.c_void_p(p), 0)
+        self.tensor = None
+        lib.ceb_peer_release(ctypes.c_void_p(self.local_ptr), 1)
+
+
+class PeerGroup:
+    """All ranks of one NVLink-connected box (<= 8)."""
+
+    MAX_WORLD = 8
+
+    def __init__(self, rt):
+        if rt.device.type != "cuda":
+            raise RuntimeError("peer-memory collectives need CUDA devices")
+        if rt.world_size > self.MAX_WORLD:
+            raise RuntimeError("peer-memory collectives support at most %d ranks" % self.MAX_WORLD)
+        self.rt = rt
+        self.rank, self.world, self.device = rt.rank, rt.world_size, rt.device
+        for q in range(torch.cuda.device_count()):
+            if q != self.device.index and q < self.world and not torch.cuda.can_device_access_peer(self.device.index, q):
+                raise RuntimeError("GPU %d cannot access GPU %d over P2P" % (self.device.index, q))
+        self.buffers: List[SymmBuffer] = []
+        self.flags = self.symm_empty(64, torch.int32)
+        self.ticket = torch.zeros(4, dtype=torch.int32, device=self.device)
+        self.epoch = 0
+        self._staging: Optional[SymmBuffer] = None
+        dist.barrier(device_ids=[self.device.index])
+
+    # -- allocation ----------------------------------------------------------------------
+    def symm_empty(self, numel: int, dtype=torch.float32) -> SymmBuffer:
+        buf = SymmBuffer(self, numel, dtype)
+        self.buffers.append(buf)
+        return buf
+
+    @staticmethod
+    def padded(numel: int) -> int:
+        return (int(numel) + 3) // 4 * 4
+
+    def shard_elems(self, n: int) -> int:
+        return int(native.lib().ceb_peer_shard_elems(n, self.world))
+
+    def shard_range(self, n: int):
+        per = self.shard_elems(n)
+        return min(per * self.rank, n), min(per * (self.rank + 1), n)
+
+    # -- collectives -----------------------------------------------------------------------
+    def _launch(self, mode: int, src: SymmBuffer, dst: SymmBuffer, n: int, Vv=None, Ve=None, inv_n=1.0,
+                rho=0.0, error_mode=0, lr=0.0, lr_vec=None):
+        self.epoch += 1
+        native.call("ceb_peer_fused_reduce", mode, src.ptr_array, dst.ptr_array, self.flags.ptr_array,
+                    native.ptr(self.ticket), self.rank, self.world, self.epoch & 0xFFFFFFFF, n,
+                    native.ptr(Vv), native.ptr(Ve), float(inv_n), float(rho), int(error_mode), float(lr),
+                    native.ptr(lr_vec), native.stream_ptr(self.device))
+
+    def all_reduce_buffer_(self, buf: SymmBuffer) -> torch.Tensor:
+        """In-place sum over ranks of a symmetric buffer (bitwise identical on all ranks)."""
+        self._launch(0, buf, buf, self.padded(buf.numel))
+        return buf.tensor
+
+    def all_reduce_sum_(self, t: torch.Tensor) -> torch.Tensor:
+        """Sum an arbitrary float32 CUDA tensor over ranks (staged through a symmetric buffer
+        unless ``t`` already is one)."""
+        for buf in self.buffers:
+            if buf.tensor is not None and buf.tensor.data_ptr() == t.data_ptr() and buf.numel >= t.numel():
+                return self.all_reduce_buffer_(buf)
+        n = t.numel()
+        if self._staging is None or self._staging.numel < self.padded(n):
+            self._staging = self.symm_empty(self.padded(n))
+        stage = self._staging.tensor[:n]
+        stage.copy_(t.reshape(-1))
+        self._launch(0, self._staging, self._staging, self.padded(n))
+        t.copy_(stage.view_as(t))
+        return t
+
+    def fused_sketch(self, transmit: SymmBuffer, gathered: SymmBuffer, Vv_shard, Ve_shard, inv_n, rho,
+                     error_type: str):
+        """reduce-scatter(transmit) -> momentum/error on this rank's shard -> all-gather into
+        every rank's ``gathered`` buffer (the table the unsketch reads)."""
+        mode = {"none": 0, "local": 1, "virtual": 2}[error_type]
+        self._launch(1, transmit, gathered, self.padded(transmit.numel), Vv_shard, Ve_shard, inv_n, rho, mode)
+
+    def fused_dense(self, transmit: SymmBuffer, weights: SymmBuffer, Vv_shard, inv_n, rho, lr):
+        """reduce-scatter(transmit) -> momentum -> w_shard -= lr*Vv -> all-gather of the new
+        weights into every replica."""
+        lr_vec = lr if torch.is_tensor(lr) else None
+        self._launch(2, transmit, weights, self.padded(transmit.numel), Vv_shard, None, inv_n, rho, 0,
+                     0.0 if lr_vec is not None else lr, lr_vec)
+
+    def close(self):
+        torch.cuda.synchronize(self.device)
+        try:
+            dist.barrier(device_ids=[self.device.index])
+        except Exception:
+            pass
+        for buf in self.buffers:
+            buf.close()
+        self.buffers = []

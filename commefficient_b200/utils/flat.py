@@ -24,7 +24,8 @@ import torch
 class FlatParams:
     """Owns ``flat`` (weights) and ``grad`` (gradients) for one module replica."""
 
-    def __init__(self, model: torch.nn.Module, device=None, align: int = 1, layout: str = "reference"):
+    def __init__(self, model: torch.nn.Module, device=None, align: int = 1, layout: str = "reference",
+                 flat_alloc=None):
         """``layout="reference"``: every parameter occupies its slice in C-contiguous
         (out, in, kh, kw) order -- coordinate i of the flat vector is coordinate i of the
         reference's.  ``layout="nhwc"``: 4-D (convolution) weights are stored
@@ -52,7 +53,9 @@ class FlatParams:
         device = torch.device(device) if device is not None else params[0].device
         # Padded allocation so 16-byte vector accesses at the tail stay in bounds.
         pad = (-off) % 1024
-        self._flat_store = torch.zeros(off + pad, dtype=torch.float32, device=device)
+        # ``flat_alloc(numel) -> tensor`` lets the weights live in peer-mapped (symmetric) memory
+        self._flat_store = (flat_alloc(off + pad) if flat_alloc is not None
+                            else torch.zeros(off + pad, dtype=torch.float32, device=device))
         self._grad_store = torch.zeros(off + pad, dtype=torch.float32, device=device)
         self.flat = self._flat_store[:off]
         self.grad = self._grad_store[:off]
@@ -105,7 +108,7 @@ class FlatParams:
         """Expand one scalar per parameter tensor into a length-d vector in flat
         order (used for per-group learning rates; fixes reference quirk Q9 where
         the LR vector was laid out in param-group order)."""
-        out = torch.empty(self.numel, dtype=torch.float32, device=self.flat.device)
+        out = torch.zeros(self._flat_store.numel(), dtype=torch.float32, device=self.flat.device)[: self.numel]
         for v, o, n in zip(values, self.offsets, self.sizes):
             out[o:o + n] = float(v)
         return out

@@ -1,0 +1,239 @@
+// Peer-memory collectives over NVLink 5 / NVSwitch, fused with the server update (sm_100a).
+//
+// The reference aggregates with one NCCL `reduce` to a parameter-server rank, updates the
+// weights on the CPU and re-downloads them to every worker through host shared memory
+// (/root/reference/CommEfficient/fed_worker.py:41,138, fed_aggregator.py:327-332,455).  Here
+// every rank owns 1/W of the server state.  ONE kernel per round
+//   1. waits until every rank's transmit buffer is complete (flag barrier in peer memory),
+//   2. pulls its shard of every rank's buffer with 16-byte peer loads and sums them in rank
+//      order (reduce-scatter; the sum of a shard is computed once, so replicas agree bitwise),
+//   3. applies the server rule to the shard while it is in registers
+//        sketch : Vv = rho*Vv + s/N ; Ve += Vv            -> broadcasts Ve
+//        dense  : Vv = rho*Vv + s/N ; w -= lr*Vv           -> broadcasts w
+//        plain  : broadcasts s                             (all-reduce),
+//   4. pushes the result into every rank's destination buffer with 16-byte peer stores
+//      (all-gather), and
+//   5. signals completion and waits for the other ranks' pushes to land.
+// No NCCL call is involved.  Buffers are cudaMalloc'd once and exchanged as CUDA IPC handles.
+#include "common.cuh"
+
+constexpr int kMaxPeers = 8;
+constexpr int kPeerThreads = 256;
+constexpr int kFlagStride = 32;   // uint32 slots per phase (>= kMaxPeers, keeps phases on separate lines)
+
+struct CebPeerCtx {
+  float* src[kMaxPeers];        // every rank's transmit (staging) buffer, peer-mapped
+  float* dst[kMaxPeers];        // every rank's destination buffer, peer-mapped
+  uint32_t* flags[kMaxPeers];   // every rank's flag block: [2 phases][kFlagStride]
+  uint32_t* ticket;             // local: finished-block counter
+  int rank, world;
+  uint32_t epoch;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// serial-number comparison so the 32-bit epoch may wrap
+__device__ __forceinline__ bool epoch_reached(uint32_t seen, uint32_t want) { return (int32_t)(seen - want) >= 0; }
+
+__device__ __forceinline__ void peer_wait_all(const CebPeerCtx& c, int phase) {
+  if ((int)threadIdx.x < c.world) {
+    const uint32_t* slot = c.flags[c.rank] + phase * kFlagStride + threadIdx.x;
+    while (!epoch_reached(ld_acquire_sys(slot), c.epoch)) __nanosleep(20);
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void peer_signal_all(const CebPeerCtx& c, int phase) {
+  if ((int)threadIdx.x < c.world)
+    st_release_sys(c.flags[threadIdx.x] + phase * kFlagStride + c.rank, c.epoch);
+}
+
+struct OpSum {
+  __device__ __forceinline__ float4 operator()(int64_t, float4 s) const { return s; }
+};
+struct OpSketch {   // Vv/Ve are this rank's shards, indexed from the shard start
+  float* Vv; float* Ve; float inv_n, rho; int error_mode; int64_t lo;
+  __device__ __forceinline__ float4 operator()(int64_t i, float4 s) const {
+    float4 v = *reinterpret_cast<float4*>(Vv + (i - lo));
+    v.x = fmaf(rho, v.x, s.x * inv_n); v.y = fmaf(rho, v.y, s.y * inv_n);
+    v.z = fmaf(rho, v.z, s.z * inv_n); v.w = fmaf(rho, v.w, s.w * inv_n);
+    *reinterpret_cast<float4*>(Vv + (i - lo)) = v;
+    if (error_mode == 0) return v;
+    float4 e = v;
+    if (error_mode == 2) {
+      e = *reinterpret_cast<float4*>(Ve + (i - lo));
+      e.x += v.x; e.y += v.y; e.z += v.z; e.w += v.w;
+    }
+    *reinterpret_cast<float4*>(Ve + (i - lo)) = e;
+    return e;
+  }
+};
+struct OpDense {    // Vv is a shard; w is read from this rank's own replica (dst[rank])
+  float* Vv; const float* w; const float* lr_vec; float inv_n, rho, lr; int64_t lo;
+  __device__ __forceinline__ float4 operator()(int64_t i, float4 s) const {
+    float4 v = *reinterpret_cast<float4*>(Vv + (i - lo));
+    v.x = fmaf(rho, v.x, s.x * inv_n); v.y = fmaf(rho, v.y, s.y * inv_n);
+    v.z = fmaf(rho, v.z, s.z * inv_n); v.w = fmaf(rho, v.w, s.w * inv_n);
+    *reinterpret_cast<float4*>(Vv + (i - lo)) = v;
+    float4 x = *reinterpret_cast<const float4*>(w + i);
+    float4 l = lr_vec ? *reinterpret_cast<const float4*>(lr_vec + i) : make_float4(lr, lr, lr, lr);
+    x.x -= l.x * v.x; x.y -= l.y * v.y; x.z -= l.z * v.z; x.w -= l.w * v.w;
+    return x;
+  }
+};
+
+// n is a multiple of 4 (callers pad); shard bounds are multiples of 4.
+template <class Op>
+__global__ void __launch_bounds__(kPeerThreads)
+peer_rs_op_ag_kernel(CebPeerCtx c, int64_t lo, int64_t hi, Op op) {
+  __shared__ bool is_last;
+  if (blockIdx.x == 0) peer_signal_all(c, 0);     // "my transmit buffer is complete"
+  peer_wait_all(c, 0);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+  for (int64_t i = lo + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < hi; i += stride) {
+    float4 part[kMaxPeers];
+#pragma unroll
+    for (int q = 0; q < kMaxPeers; ++q)
+      if (q < c.world) part[q] = ld_peer_f4(c.src[q] + i);   // all loads in flight before the adds
+    float4 s = part[0];
+#pragma unroll
+    for (int q = 1; q < kMaxPeers; ++q)
+      if (q < c.world) { s.x += part[q].x; s.y += part[q].y; s.z += part[q].z; s.w += part[q].w; }
+    const float4 out = op(i, s);
+#pragma unroll
+    for (int q = 0; q < kMaxPeers; ++q)
+      if (q < c.world) st_peer_f4(c.dst[q] + i, out);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = atomicAdd(c.ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+    if (is_last) *c.ticket = 0;
+  }
+  __syncthreads();
+  if (is_last) {                                  // "my pushes have landed everywhere"
+    __threadfence_system();
+    peer_signal_all(c, 1);
+    peer_wait_all(c, 1);
+  }
+}
+
+static int peer_grid(int64_t shard_elems) {
+  int64_t need = ceb_cdiv(shard_elems / 4 + 1, kPeerThreads);
+  int64_t cap = (int64_t)ceb_num_sms() * 2;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
+static int fill_ctx(CebPeerCtx& c, const void* const* src, const void* const* dst, const void* const* flags,
+                    void* ticket, int rank, int world, uint32_t epoch) {
+  CEB_REQUIRE(world >= 1 && world <= kMaxPeers, "peer collective: world=%d outside [1,%d]", world, kMaxPeers);
+  CEB_REQUIRE(rank >= 0 && rank < world, "peer collective: rank=%d outside [0,%d)", rank, world);
+  CEB_REQUIRE(src && dst && flags && ticket, "peer collective: null pointer table");
+  for (int q = 0; q < kMaxPeers; ++q) {
+    c.src[q] = q < world ? (float*)src[q] : nullptr;
+    c.dst[q] = q < world ? (float*)dst[q] : nullptr;
+    c.flags[q] = q < world ? (uint32_t*)flags[q] : nullptr;
+  }
+  c.ticket = (uint32_t*)ticket;
+  c.rank = rank;
+  c.world = world;
+  c.epoch = epoch;
+  return 0;
+}
+
+static void shard_bounds(int64_t n, int rank, int world, int64_t* lo, int64_t* hi) {
+  int64_t per = ceb_cdiv(ceb_cdiv(n, world), 4) * 4;
+  *lo = per * rank < n ? per * rank : n;
+  *hi = per * (rank + 1) < n ? per * (rank + 1) : n;
+}
+
+CEB_API int64_t ceb_peer_shard_elems(int64_t n, int world) {
+  return ceb_cdiv(ceb_cdiv(n, world), 4) * 4;
+}
+
+// src/dst/flags: host arrays of `world` device pointers (peer-mapped).  n % 4 == 0.
+// mode 0: dst = sum(src)                                      (all-reduce; dst may equal src)
+// mode 1: sketch -- Vv,Ve shards updated, dst = Ve             (error_mode 0: dst = Vv)
+// mode 2: dense  -- Vv shard updated, dst (= weights) -= lr*Vv
+CEB_API int ceb_peer_fused_reduce(int mode, const void* const* src, const void* const* dst,
+                                  const void* const* flags, void* ticket, int rank, int world,
+                                  unsigned int epoch, int64_t n, float* Vv_shard, float* Ve_shard,
+                                  float inv_n, float rho, int error_mode, float lr, const float* lr_vec,
+                                  void* stream) {
+  CEB_REQUIRE(n > 0 && n % 4 == 0, "ceb_peer_fused_reduce: n=%lld must be a positive multiple of 4", (long long)n);
+  CebPeerCtx c;
+  if (int e = fill_ctx(c, src, dst, flags, ticket, rank, world, epoch)) return e;
+  int64_t lo, hi;
+  shard_bounds(n, rank, world, &lo, &hi);
+  const int grid = peer_grid(hi - lo);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == 0) {
+    peer_rs_op_ag_kernel<OpSum><<<grid, kPeerThreads, 0, st>>>(c, lo, hi, OpSum{});
+  } else if (mode == 1) {
+    CEB_REQUIRE(Vv_shard && (error_mode == 0 || Ve_shard), "ceb_peer_fused_reduce: sketch mode needs state shards");
+    peer_rs_op_ag_kernel<OpSketch><<<grid, kPeerThreads, 0, st>>>(
+        c, lo, hi, OpSketch{Vv_shard, Ve_shard, inv_n, rho, error_mode, lo});
+  } else if (mode == 2) {
+    CEB_REQUIRE(Vv_shard, "ceb_peer_fused_reduce: dense mode needs the momentum shard");
+    peer_rs_op_ag_kernel<OpDense><<<grid, kPeerThreads, 0, st>>>(
+        c, lo, hi, OpDense{Vv_shard, (const float*)dst[rank], lr_vec, inv_n, rho, lr, lo});
+  } else {
+    CEB_REQUIRE(false, "ceb_peer_fused_reduce: unknown mode %d", mode);
+  }
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ symmetric allocation (CUDA IPC)
+// These three are the only entry points of the library that allocate: symmetric buffers must be
+// whole cudaMalloc allocations to be exportable.  handle_out/handle: 64 bytes (cudaIpcMemHandle_t).
+CEB_API int ceb_peer_alloc(int64_t bytes, void** ptr_out, void* handle_out) {
+  CEB_REQUIRE(bytes > 0 && ptr_out && handle_out, "ceb_peer_alloc: bad arguments");
+  void* p = nullptr;
+  CEB_CHECK_CUDA(cudaMalloc(&p, (size_t)bytes));
+  CEB_CHECK_CUDA(cudaMemset(p, 0, (size_t)bytes));
+  cudaIpcMemHandle_t h;
+  CEB_CHECK_CUDA(cudaIpcGetMemHandle(&h, p));
+  memcpy(handle_out, &h, sizeof(h));
+  *ptr_out = p;
+  return 0;
+}
+
+CEB_API int ceb_peer_open(const void* handle, void** ptr_out) {
+  CEB_REQUIRE(handle && ptr_out, "ceb_peer_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  void* p = nullptr;
+  CEB_CHECK_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *ptr_out = p;
+  return 0;
+}
+
+CEB_API int ceb_peer_release(void* ptr, int is_owner) {
+  if (!ptr) return 0;
+  if (is_owner) CEB_CHECK_CUDA(cudaFree(ptr));
+  else CEB_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+
+CEB_API int ceb_peer_handle_bytes() { return (int)sizeof(cudaIpcMemHandle_t); }

@@ -5,9 +5,10 @@
  *     ceb_last_error() describes what went wrong (thread-local string);
  *   - pointers are device pointers unless a comment says "host";
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
- *   - nothing here allocates or frees device memory: callers pass every buffer,
- *     including scratch (sizes via the *_bytes() queries), so the library can be
- *     driven from PyTorch's caching allocator without fragmenting it;
+ *   - compute entry points never allocate or free device memory: callers pass every
+ *     buffer, including scratch (sizes via the *_bytes() queries), so the library can be
+ *     driven from PyTorch's caching allocator without fragmenting it (the ceb_peer_alloc
+ *     family, which creates IPC-exportable buffers, is the exception);
  *   - top-k results are unordered; which of several equal-magnitude entries at
  *     the threshold are kept is unspecified (as with torch.topk).
  *
@@ -120,6 +121,29 @@ int ceb_fedavg_delta(float* acc, const float* w0, const float* wloc, float weigh
  * (reference: fed_aggregator.py:244-250) */
 int ceb_count_changed(const float* w, float* prev, uint8_t* mask, int64_t n, unsigned long long* count,
                       void* stream);
+
+/* ---- peer-memory collectives over NVLink, fused with the server update ---------
+ * (reference: the single NCCL reduce + host-side weight update/download,
+ *  fed_worker.py:41,138, fed_aggregator.py:327-332,455).  src/dst/flags are HOST arrays of
+ *  `world` device pointers, entry q being rank q's buffer mapped into this process
+ *  (ceb_peer_open).  n % 4 == 0.  flags: 64 zeroed uint32 per rank; ticket: one zeroed
+ *  uint32 (local).  epoch: 1, 2, 3, ... identical on every rank for the same call.
+ *  Every rank must issue the same call; the kernel spins on its peers.
+ *    mode 0  dst = sum_q src[q]                              (all-reduce)
+ *    mode 1  Vv = rho*Vv + sum/N; Ve += Vv (error_mode 2) or Ve = Vv (1); dst = Ve (or Vv)
+ *    mode 2  Vv = rho*Vv + sum/N; dst (= every replica's weights) -= lr * Vv
+ *  Vv_shard / Ve_shard hold this rank's ceb_peer_shard_elems(n, world) entries. */
+int64_t ceb_peer_shard_elems(int64_t n, int world);
+int ceb_peer_fused_reduce(int mode, const void* const* src, const void* const* dst,
+                          const void* const* flags, void* ticket, int rank, int world, unsigned int epoch,
+                          int64_t n, float* Vv_shard, float* Ve_shard, float inv_n, float rho,
+                          int error_mode, float lr, const float* lr_vec, void* stream);
+/* Symmetric buffers (the only allocating entry points: CUDA IPC needs whole cudaMalloc
+ * allocations).  handle: ceb_peer_handle_bytes() (= 64) bytes, host memory. */
+int ceb_peer_handle_bytes(void);
+int ceb_peer_alloc(int64_t bytes, void** ptr_out, void* handle_out);
+int ceb_peer_open(const void* handle, void** ptr_out);
+int ceb_peer_release(void* ptr, int is_owner);
 
 #ifdef __cplusplus
 }

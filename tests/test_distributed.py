@@ -1,0 +1,154 @@
+"""Multi-rank tests: gloo on CPU (host-side protocol; BASELINE.json config 1) and, on a box
+with >= 2 GPUs, the peer-memory kernels against NCCL."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+
+from commefficient_b200.parallel import runtime
+
+SMALL = {"prep": 8, "layer1": 16, "layer2": 16, "layer3": 32}
+
+
+def _fed_run(device, mode, backend, rounds=3, **kw):
+    from commefficient_b200 import models
+    from commefficient_b200.cv_train import compute_loss_train, compute_loss_val
+    from commefficient_b200.data_utils import synthetic_image_batch
+    from commefficient_b200.fed_aggregator import FedModel, FedOptimizer
+    from commefficient_b200.utils import make_args
+    torch.manual_seed(0)
+    base = dict(mode=mode, num_workers=6, num_clients=36, local_batch_size=-1, k=300, num_cols=4000, num_rows=5,
+                num_blocks=4, device=device, dataset_name="CIFAR10", precision="fp32", weight_decay=5e-4,
+                local_momentum=0.0, virtual_momentum=0.9, flat_layout="reference", backend=backend,
+                error_type="virtual" if mode in ("sketch", "true_topk") else "none")
+    base.update(kw)
+    args = make_args(**base)
+    model = models.ResNet9(num_classes=10, channels=SMALL)
+    fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+    opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+    opt.param_groups[0]["lr"] = 0.05
+    losses = []
+    for step in range(rounds):
+        fed.train(True)
+        out = fed(synthetic_image_batch(6, 4, seed=step, first_client=6 * step))
+        opt.step()
+        losses.append([float(x) for x in out[0]])
+    fed.train(False)
+    val = fed(synthetic_image_batch(4, 8, seed=99))
+    w = fed.fp.to_reference_order(fed.fp.flat).detach().cpu()
+    return w, losses, [float(x) for x in val[0]], fed
+
+
+def _rank_main(rank, world, device, mode, backend, out_dir, kw):
+    rt = runtime.init_runtime(rank=rank, world_size=world, device=device, backend=backend)
+    w, losses, val, fed = _fed_run(device, mode, backend, **kw)
+    torch.save({"w": w, "losses": losses, "val": val, "backend": rt.backend}, os.path.join(out_dir, "r%d.pt" % rank))
+    rt.shutdown()
+
+
+def _spawn(world, device, mode, backend, **kw):
+    out_dir = tempfile.mkdtemp()
+    runtime.spawn(_rank_main, world, args=(device, mode, backend, out_dir, kw), device=device)
+    return [torch.load(os.path.join(out_dir, "r%d.pt" % r)) for r in range(world)]
+
+
+@pytest.mark.parametrize("mode,kw", [("sketch", {}), ("uncompressed", {}), ("true_topk", {}),
+                                     ("local_topk", {"error_type": "local", "local_momentum": 0.9}),
+                                     ("fedavg", {})])
+def test_gloo_two_ranks_match_single_rank(mode, kw):
+    ranks = _spawn(2, "cpu", mode, "gloo", **kw)
+    assert ranks[0]["backend"] == "gloo"
+    torch.testing.assert_close(ranks[0]["w"], ranks[1]["w"], rtol=0, atol=0)      # replicas stay identical
+    assert ranks[0]["losses"] == ranks[1]["losses"]
+    w1, l1, v1, fed = _fed_run("cpu", mode, "auto", **kw)
+    fed.rt.shutdown()
+    np.testing.assert_allclose(ranks[0]["losses"], l1, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(ranks[0]["val"], v1, rtol=1e-4, atol=1e-5)
+    assert (ranks[0]["w"] - w1).norm() / w1.norm() < 1e-3
+
+
+def test_gloo_three_ranks_uneven_clients():
+    # 6 clients over 3 ranks with per-client state: owner = client id mod 3; nothing is dropped (Q1)
+    ranks = _spawn(3, "cpu", "local_topk", "gloo", error_type="local", local_momentum=0.9)
+    for r in ranks[1:]:
+        torch.testing.assert_close(ranks[0]["w"], r["w"], rtol=0, atol=0)
+    assert len(ranks[0]["losses"][0]) == 6
+
+
+def _need_gpus(n):
+    if not torch.cuda.is_available() or torch.cuda.device_count() < n:
+        pytest.skip("needs %d GPUs" % n)
+
+
+def _peer_kernel_main(rank, world, out_dir):
+    rt = runtime.init_runtime(rank=rank, world_size=world, device="cuda", backend="b200")
+    assert rt.backend == "b200" and rt.peer is not None, "peer backend did not come up"
+    peer, dev = rt.peer, rt.device
+    gen = torch.Generator(device=dev).manual_seed(100 + rank)
+    ok = {}
+    # all-reduce of an arbitrary tensor (staged) against NCCL
+    for n in (5, 4096, 1_000_003):
+        x = torch.randn(n, device=dev, generator=gen)
+        want = x.clone()
+        torch.distributed.all_reduce(want)
+        got = peer.all_reduce_sum_(x.clone())
+        ok["allreduce_%d" % n] = float((got - want).abs().max())
+    # fused sketch: reduce-scatter + momentum/error + all-gather
+    n = 5 * 4000
+    tr = peer.symm_empty(peer.padded(n))
+    ve = peer.symm_empty(peer.padded(n))
+    tr.tensor[:n].copy_(torch.randn(n, device=dev, generator=gen))
+    total = tr.tensor[:n].clone()
+    torch.distributed.all_reduce(total)
+    g2 = torch.Generator(device=dev).manual_seed(7)          # same state on every rank
+    Vv = torch.randn(n + 4, device=dev, generator=g2)[:n]
+    ve.tensor[:n].copy_(torch.randn(n, device=dev, generator=g2))
+    Vv_ref = 0.9 * Vv + total * 0.25
+    Ve_ref = ve.tensor[:n] + Vv_ref
+    lo, hi = peer.shard_range(peer.padded(n))
+    peer.fused_sketch(tr, ve, Vv[lo:], ve.tensor[lo:], 0.25, 0.9, "virtual")
+    torch.cuda.synchronize()
+    ok["sketch_Ve"] = float((ve.tensor[:n] - Ve_ref).abs().max())
+    ok["sketch_Vv_shard"] = float((Vv[lo:min(hi, n)] - Vv_ref[lo:min(hi, n)]).abs().max())
+    # fused dense: reduce-scatter + momentum + apply + all-gather of weights
+    n = 100_003
+    tr2 = peer.symm_empty(peer.padded(n))
+    wb = peer.symm_empty(peer.padded(n))
+    tr2.tensor[:n].copy_(torch.randn(n, device=dev, generator=gen))
+    total = tr2.tensor[:n].clone()
+    torch.distributed.all_reduce(total)
+    Vv = torch.randn(peer.padded(n) + 4, device=dev, generator=g2)[:peer.padded(n)]
+    wb.tensor[:n].copy_(torch.randn(n, device=dev, generator=g2))
+    Vv_ref = 0.9 * Vv[:n] + total * 0.5
+    w_ref = wb.tensor[:n] - 0.1 * Vv_ref
+    lo, hi = peer.shard_range(peer.padded(n))
+    peer.fused_dense(tr2, wb, Vv[lo:], 0.5, 0.9, 0.1)
+    torch.cuda.synchronize()
+    ok["dense_w"] = float((wb.tensor[:n] - w_ref).abs().max())
+    torch.save(ok, os.path.join(out_dir, "r%d.pt" % rank))
+    rt.shutdown()
+
+
+@pytest.mark.gpu
+def test_peer_kernels_two_gpus():
+    _need_gpus(2)
+    out_dir = tempfile.mkdtemp()
+    runtime.spawn(_peer_kernel_main, 2, args=(out_dir,), device="cuda")
+    for r in range(2):
+        res = torch.load(os.path.join(out_dir, "r%d.pt" % r))
+        for name, err in res.items():
+            assert err < 1e-4, (r, name, err)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["sketch", "uncompressed", "true_topk"])
+def test_peer_backend_matches_nccl_backend(mode):
+    _need_gpus(2)
+    a = _spawn(2, "cuda", mode, "b200")
+    b = _spawn(2, "cuda", mode, "nccl")
+    assert a[0]["backend"] == "b200" and b[0]["backend"] == "nccl"
+    torch.testing.assert_close(a[0]["w"], a[1]["w"], rtol=0, atol=0)            # replicas identical
+    np.testing.assert_allclose(a[0]["losses"], b[0]["losses"], rtol=2e-3, atol=2e-3)
+    assert (a[0]["w"] - b[0]["w"]).norm() / b[0]["w"].norm() < (5e-2 if mode != "uncompressed" else 1e-3)
