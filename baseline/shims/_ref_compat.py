@@ -24,6 +24,10 @@ def install():
     if _done:
         return
     _done = True
+    trace_after = int(os.environ.get("CEB_REF_TRACE_AFTER", "0") or 0)
+    if trace_after > 0:
+        import faulthandler                      # debugging aid: dump stacks if a process hangs
+        faulthandler.dump_traceback_later(trace_after, exit=False)
     import numpy as np
     if not hasattr(np, "float"):
         np.float = float

@@ -117,9 +117,13 @@ def run_reference(cfg):
         print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is not installed (see DESIGN.md)"}))
         return 0
     env = dict(os.environ)
-    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "LOCAL_WORLD_SIZE",
-              "GROUP_RANK", "ROLE_RANK", "TORCHELASTIC_RUN_ID"):
-        env.pop(k, None)
+    # The reference does its own rendezvous; scrub everything torchrun exported (in particular
+    # TORCHELASTIC_USE_AGENT_STORE, which would make its rank 0 wait for an agent-hosted store).
+    for k in list(env):
+        if k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "LOCAL_WORLD_SIZE",
+                 "GROUP_RANK", "ROLE_RANK", "ROLE_NAME", "GROUP_WORLD_SIZE", "ROLE_WORLD_SIZE",
+                 "OMP_NUM_THREADS", "NCCL_ASYNC_ERROR_HANDLING") or k.startswith(("TORCHELASTIC", "TORCH_NCCL")):
+            env.pop(k, None)
     clients = cfg.clients_per_gpu * cfg.gpus
     cmd = [sys.executable, os.path.join(ROOT, "baseline", "run_ref.py"), "--gpus", str(cfg.gpus),
            "--steps", str(cfg.steps), "--warmup", str(cfg.warmup), "--clients_per_round", str(clients),

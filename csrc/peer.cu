@@ -99,27 +99,41 @@ struct OpDense {    // Vv is a shard; w is read from this rank's own replica (ds
   }
 };
 
-// n is a multiple of 4 (callers pad); shard bounds are multiples of 4.
-template <class Op>
+// n is a multiple of 4 (callers pad); shard bounds are multiples of 4.  W = world size
+// (compile time, so the per-peer loads unroll), U = float4s per thread per step chosen so
+// that U*W ~ 8 sixteen-byte peer loads are in flight per thread: NVLink needs ~2-3 us x
+// 770 GB/s ~ 2 MB outstanding per GPU to run at link speed.
+template <class Op, int W, int U>
 __global__ void __launch_bounds__(kPeerThreads)
 peer_rs_op_ag_kernel(CebPeerCtx c, int64_t lo, int64_t hi, Op op) {
   __shared__ bool is_last;
   if (blockIdx.x == 0) peer_signal_all(c, 0);     // "my transmit buffer is complete"
   peer_wait_all(c, 0);
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
-  for (int64_t i = lo + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < hi; i += stride) {
-    float4 part[kMaxPeers];
+  const int64_t lane_step = (int64_t)blockDim.x * 4;
+  const int64_t stride = (int64_t)gridDim.x * lane_step * U;
+  for (int64_t base = lo + (int64_t)blockIdx.x * lane_step * U + (int64_t)threadIdx.x * 4; base < hi;
+       base += stride) {
+    float4 part[W][U];
 #pragma unroll
-    for (int q = 0; q < kMaxPeers; ++q)
-      if (q < c.world) part[q] = ld_peer_f4(c.src[q] + i);   // all loads in flight before the adds
-    float4 s = part[0];
+    for (int q = 0; q < W; ++q)
 #pragma unroll
-    for (int q = 1; q < kMaxPeers; ++q)
-      if (q < c.world) { s.x += part[q].x; s.y += part[q].y; s.z += part[q].z; s.w += part[q].w; }
-    const float4 out = op(i, s);
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = base + u * lane_step;
+        part[q][u] = i < hi ? ld_peer_f4(c.src[q] + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
 #pragma unroll
-    for (int q = 0; q < kMaxPeers; ++q)
-      if (q < c.world) st_peer_f4(c.dst[q] + i, out);
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = base + u * lane_step;
+      if (i >= hi) break;
+      float4 s = part[0][u];
+#pragma unroll
+      for (int q = 1; q < W; ++q) {
+        s.x += part[q][u].x; s.y += part[q][u].y; s.z += part[q][u].z; s.w += part[q][u].w;
+      }
+      const float4 out = op(i, s);
+#pragma unroll
+      for (int q = 0; q < W; ++q) st_peer_f4(c.dst[q] + i, out);
+    }
   }
   __threadfence_system();
   __syncthreads();
@@ -136,11 +150,22 @@ peer_rs_op_ag_kernel(CebPeerCtx c, int64_t lo, int64_t hi, Op op) {
   }
 }
 
-static int peer_grid(int64_t shard_elems) {
-  int64_t need = ceb_cdiv(shard_elems / 4 + 1, kPeerThreads);
-  int64_t cap = (int64_t)ceb_num_sms() * 2;
-  if (need < 1) need = 1;
-  return (int)(need < cap ? need : cap);
+template <class Op>
+static void launch_peer(const CebPeerCtx& c, int64_t lo, int64_t hi, Op op, cudaStream_t st) {
+  auto grid_for = [&](int U) {
+    int64_t need = ceb_cdiv((hi - lo) / 4 + 1, (int64_t)kPeerThreads * U);
+    int64_t cap = (int64_t)ceb_num_sms() * 4;
+    if (need < 1) need = 1;
+    return (int)(need < cap ? need : cap);
+  };
+  switch (c.world) {
+#define CEB_PEER_CASE(W_, U_) \
+    case W_: peer_rs_op_ag_kernel<Op, W_, U_><<<grid_for(U_), kPeerThreads, 0, st>>>(c, lo, hi, op); break;
+    CEB_PEER_CASE(1, 4) CEB_PEER_CASE(2, 4) CEB_PEER_CASE(3, 2) CEB_PEER_CASE(4, 2)
+    CEB_PEER_CASE(5, 1) CEB_PEER_CASE(6, 1) CEB_PEER_CASE(7, 1) CEB_PEER_CASE(8, 1)
+#undef CEB_PEER_CASE
+    default: break;
+  }
 }
 
 static int fill_ctx(CebPeerCtx& c, const void* const* src, const void* const* dst, const void* const* flags,
@@ -184,18 +209,15 @@ CEB_API int ceb_peer_fused_reduce(int mode, const void* const* src, const void* 
   if (int e = fill_ctx(c, src, dst, flags, ticket, rank, world, epoch)) return e;
   int64_t lo, hi;
   shard_bounds(n, rank, world, &lo, &hi);
-  const int grid = peer_grid(hi - lo);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 0) {
-    peer_rs_op_ag_kernel<OpSum><<<grid, kPeerThreads, 0, st>>>(c, lo, hi, OpSum{});
+    launch_peer(c, lo, hi, OpSum{}, st);
   } else if (mode == 1) {
     CEB_REQUIRE(Vv_shard && (error_mode == 0 || Ve_shard), "ceb_peer_fused_reduce: sketch mode needs state shards");
-    peer_rs_op_ag_kernel<OpSketch><<<grid, kPeerThreads, 0, st>>>(
-        c, lo, hi, OpSketch{Vv_shard, Ve_shard, inv_n, rho, error_mode, lo});
+    launch_peer(c, lo, hi, OpSketch{Vv_shard, Ve_shard, inv_n, rho, error_mode, lo}, st);
   } else if (mode == 2) {
     CEB_REQUIRE(Vv_shard, "ceb_peer_fused_reduce: dense mode needs the momentum shard");
-    peer_rs_op_ag_kernel<OpDense><<<grid, kPeerThreads, 0, st>>>(
-        c, lo, hi, OpDense{Vv_shard, (const float*)dst[rank], lr_vec, inv_n, rho, lr, lo});
+    launch_peer(c, lo, hi, OpDense{Vv_shard, (const float*)dst[rank], lr_vec, inv_n, rho, lr, lo}, st);
   } else {
     CEB_REQUIRE(false, "ceb_peer_fused_reduce: unknown mode %d", mode);
   }
