@@ -4,9 +4,10 @@
   python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 bench/bench_collectives.py
 
 Sizes: 5x500 000 sketch table (10 MB), ResNet-9 dense (26.3 MB), GPT-2 dense (497.8 MB).
-Per rank a two-shot all-reduce moves 2*(N-1)/N * bytes over NVLink; the roofline uses the
-measured 770 GB/s per direction (B200_PROFILING.md), i.e. ideal = (N-1)/N * bytes / 770e9
-(pull and push overlap in opposite directions)."""
+A two-shot all-reduce brings 2*(N-1)/N * bytes INTO every GPU (its own pulls of the other
+ranks' shard copies plus the other ranks' pushes of their reduced shards) and sends the same
+amount out; the roofline uses the measured 770 GB/s per direction (B200_PROFILING.md):
+ideal = 2*(N-1)/N * bytes / 770e9."""
 import json
 import os
 import sys
@@ -56,7 +57,7 @@ def main():
             Vv2.mul_(0.9).add_(x, alpha=0.01)
             Ve2.add_(Vv2)
         t_unfused = timed(unfused, rt)
-        ideal = (W - 1) / W * n * 4 / (LINK_GBS * 1e9) * 1e6
+        ideal = 2 * (W - 1) / W * n * 4 / (LINK_GBS * 1e9) * 1e6
         rows.append({"buffer": name, "bytes": n * 4, "nccl_allreduce_us": t_nccl, "peer_allreduce_us": t_peer,
                      "peer_fused_rs_update_ag_us": t_fused, "nccl_plus_update_us": t_unfused,
                      "ideal_us": ideal, "fused_fraction_of_roofline": ideal / t_fused})

@@ -1,0 +1,45 @@
+"""GPT-2 double-heads: model contract and the PersonaChat driver end to end (tiny config, CPU)."""
+import os
+
+import torch
+
+from commefficient_b200 import models
+from commefficient_b200.gpt2_train import train
+
+
+def test_gpt2_param_count_matches_reference():
+    m = models.GPT2DoubleHeadsModel()
+    m.resize_token_embeddings(50257 + 5)
+    d = sum(p.numel() for p in m.parameters() if p.requires_grad)
+    assert d == 124_444_417          # SURVEY.md section 0 / BASELINE.md
+    keys = m.state_dict().keys()
+    for k in ("transformer.wte.weight", "transformer.h.0.attn.c_attn.weight", "transformer.h.11.mlp.c_proj.bias",
+              "transformer.ln_f.weight", "lm_head.weight", "multiple_choice_head.summary.weight"):
+        assert k in keys
+    assert m.state_dict()["transformer.h.0.attn.c_attn.weight"].shape == (768, 2304)   # Conv1D (in, out)
+    assert m.lm_head.weight.data_ptr() == m.transformer.wte.weight.data_ptr()
+
+
+def test_gpt2_save_load_roundtrip(tmp_path):
+    cfg = models.GPT2Config(vocab_size=100, n_positions=32, n_ctx=32, n_embd=32, n_layer=2, n_head=2)
+    m = models.GPT2DoubleHeadsModel(cfg)
+    m.save_pretrained(str(tmp_path))
+    m2 = models.GPT2DoubleHeadsModel.from_pretrained(str(tmp_path))
+    ids = torch.randint(0, 100, (2, 2, 8))
+    m.eval(), m2.eval()
+    a = m(ids, mc_token_ids=torch.full((2, 2), 7))
+    b = m2(ids, mc_token_ids=torch.full((2, 2), 7))
+    torch.testing.assert_close(a[0], b[0])
+    torch.testing.assert_close(a[1], b[1])
+
+
+def test_gpt2_driver_end_to_end(tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)
+    out = train(["--dataset_name", "PERSONA", "--synthetic", "--dataset_dir", str(tmp_path / "persona"),
+                 "--num_clients", "8", "--model_checkpoint", "gpt2-tiny", "--num_workers", "2",
+                 "--local_batch_size", "2", "--mode", "sketch", "--error_type", "virtual", "--local_momentum", "0",
+                 "--virtual_momentum", "0.9", "--num_epochs", "1", "--k", "2000", "--num_cols", "20000",
+                 "--device", "cpu", "--valid_batch_size", "2", "--lr_scale", "0.1"])
+    assert out["val_ppl"] < 512 and 0.0 <= out["val_acc"] <= 1.0
+    runs = os.listdir(tmp_path / "runs")
+    assert runs, "save_pretrained did not write the run directory"
