@@ -1,0 +1,297 @@
+// tcgen05 / TMEM / TMA tile kernel (sm_100a): one 128 x BN output tile per CTA,
+//   D[128 x BN] (fp32, TMEM) = sum over k-steps of A_tile[128 x 64] * B_tile[BN x 64]^T   (bf16)
+// A and B tiles are staged by TMA (128-byte swizzle) through a 4-deep mbarrier ring; one elected
+// thread issues tcgen05.mma; four epilogue warps read the accumulator with tcgen05.ld and fuse
+// bias / ReLU / dtype conversion into the store.  The same kernel is
+//   * a plain "TN" GEMM  C[M,N] = A[M,K] * B[N,K]^T      (linear layers; A tile = 2-D TMA box), and
+//   * a 3x3 / stride 1 / pad 1 implicit-GEMM convolution over NHWC activations: the A tile of
+//     k-step (r, s, c0) is a 4-D TMA box (64 channels x tile_w x tile_h x tile_n) fetched at the
+//     shifted coordinate (c0, s-1, h0+r-1, n0); TMA zero-fills out-of-bounds elements, which IS
+//     the padding.  Weights are K-major "KRSC" ([Cout][3][3][Cin]) -- exactly how the flat
+//     parameter buffer stores them (utils/flat.py, layout="nhwc").
+// Replaces the cuDNN / cuBLAS calls behind the reference's nn.Conv2d / nn.Linear layers
+// (/root/reference/CommEfficient/models/resnet9.py:36-37, fixup_resnet18.py:144-154).
+#include "tc_common.cuh"
+
+using namespace tc;
+
+constexpr int BM = 128;
+constexpr int BK = 64;          // bf16 elements per k-step = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kStages = 4;
+constexpr int kTcThreads = 192; // warp 0: TMA, warp 1: MMA + TMEM alloc, warps 2-5: epilogue
+
+struct TcParams {
+  void* C;               // output [M][ldc]
+  const float* bias;     // per output column (nullable)
+  int M, N, ldc;
+  int k_steps;
+  int relu;
+  int out_fp32;          // 0: bf16 store, 1: fp32 store, 2: fp32 atomic add
+  // convolution geometry (mode 1)
+  int conv;
+  int H, W, cin_steps;   // cin_steps = Cin / 64
+  int tile_h;            // rows of the image covered by one M tile (tile_w == W)
+};
+
+template <int BN>
+struct SmemLayout {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kTotal = kStages * kStageBytes + 1024 /* align */ + 256 /* barriers */;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kTcThreads, 1)
+tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, TcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  using L = SmemLayout<BN>;
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B needs 1024 B
+  uint64_t* full_bar = (uint64_t*)(smem + kStages * L::kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full_bar = empty_bar + kStages;
+  uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m_tile = blockIdx.x;
+  const int n_tile = blockIdx.y;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmapA);
+    tma_prefetch_desc(&tmapB);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<BN>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int n0 = 0, h0 = 0;
+      if (p.conv) {
+        const int pix0 = m_tile * BM;
+        const int hw = p.H * p.W;
+        n0 = pix0 / hw;
+        h0 = (pix0 - n0 * hw) / p.W;
+      }
+      for (int ks = 0; ks < p.k_steps; ++ks) {
+        const int s = ks % kStages;
+        const uint32_t phase = (ks / kStages) & 1;
+        mbar_wait(empty_bar + s, phase ^ 1);
+        uint8_t* a_dst = smem + s * L::kStageBytes;
+        uint8_t* b_dst = a_dst + L::kABytes;
+        mbar_expect_tx(full_bar + s, L::kStageBytes);
+        if (p.conv) {
+          const int tap = ks / p.cin_steps;
+          const int c0 = (ks - tap * p.cin_steps) * BK;
+          const int r = tap / 3, sft = tap - r * 3;
+          tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 + r - 1, n0);
+        } else {
+          tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BK, m_tile * BM);
+        }
+        tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BK, n_tile * BN);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one elected thread) =====
+    constexpr uint32_t idesc = idesc_bf16(BM, BN, 0, 0);
+    for (int ks = 0; ks < p.k_steps; ++ks) {
+      const int s = ks % kStages;
+      const uint32_t phase = (ks / kStages) & 1;
+      mbar_wait(full_bar + s, phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
+        const uint32_t b_addr = a_addr + L::kABytes;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          const uint64_t da = smem_desc_sw128(a_addr + k * UMMA_K * 2, 16, 1024);
+          const uint64_t db = smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
+          umma_bf16(tmem_base, da, db, idesc, (ks | k) != 0);
+        }
+        umma_commit(empty_bar + s);                       // frees this smem stage when the MMAs retire
+        if (ks == p.k_steps - 1) umma_commit(tmem_full_bar);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===== epilogue: TMEM -> registers -> global =====
+    const int q = warp & 3;                               // TMEM lane quarter this warp may access
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int m = m_tile * BM + q * 32 + lane;
+    const int n_base = n_tile * BN;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      float v[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, v);
+      const int n0 = n_base + c * 32;
+      if (m < p.M && n0 < p.N) {
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (n0 + j < p.N) v[j] += __ldg(p.bias + n0 + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
+        const bool full = (n0 + 32 <= p.N);
+        if (p.out_fp32 == 0) {
+          __nv_bfloat16* dst = (__nv_bfloat16*)p.C + (int64_t)m * p.ldc + n0;
+          if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 pk;
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+              pk.x = *(uint32_t*)&h0; pk.y = *(uint32_t*)&h1; pk.z = *(uint32_t*)&h2; pk.w = *(uint32_t*)&h3;
+              *(uint4*)(dst + j) = pk;
+            }
+          } else {
+            for (int j = 0; j < 32 && n0 + j < p.N; ++j) dst[j] = __float2bfloat16(v[j]);
+          }
+        } else {
+          float* dst = (float*)p.C + (int64_t)m * p.ldc + n0;
+          if (p.out_fp32 == 1) {
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) *(float4*)(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              for (int j = 0; j < 32 && n0 + j < p.N; ++j) dst[j] = v[j];
+            }
+          } else {
+            for (int j = 0; j < 32 && n0 + j < p.N; ++j) red_add_f32(dst + j, v[j]);
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<BN>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  }
+  return fn;
+}
+
+int ceb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                       const uint64_t* strides_bytes, const uint32_t* box) {
+  PFN_encodeTiled enc = get_encode_fn();
+  CEB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t gdims[5], gstr[5];
+  cuuint32_t gbox[5], estr[5];
+  for (int i = 0; i < rank; ++i) { gdims[i] = dims[i]; gbox[i] = box[i]; estr[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, (void*)base, gdims, gstr, gbox, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CEB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rank %d, dims %llu/%llu, box %u/%u)",
+              (int)r, rank, (unsigned long long)dims[0], (unsigned long long)dims[1], box[0], box[1]);
+  return 0;
+}
+
+template <int BN>
+static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+  using L = SmemLayout<BN>;
+  static bool configured = false;
+  if (!configured) {
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    configured = true;
+  }
+  dim3 grid((unsigned)ceb_cdiv(p.M, BM), (unsigned)ceb_cdiv(p.N, BN), 1);
+  tc_tile_kernel<BN><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, p);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+static int pick_bn(int N) { return N <= 64 ? 64 : (N <= 128 ? 128 : 256); }
+
+static int dispatch_tile(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+  switch (bn) {
+    case 64: return launch_tile<64>(ta, tb, p, st);
+    case 128: return launch_tile<128>(ta, tb, p, st);
+    case 256: return launch_tile<256>(ta, tb, p, st);
+  }
+  CEB_REQUIRE(false, "unsupported N tile %d", bn);
+}
+
+// C[M,N] = act(A[M,K] * B[N,K]^T + bias).  A, B bf16 row-major (K contiguous), K % 8 == 0,
+// N % 8 == 0.  out_mode 0: bf16 C, 1: fp32 C, 2: fp32 C += (atomic).
+CEB_API int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, const float* bias,
+                             int relu, int out_mode, void* stream) {
+  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_tn: bad arguments");
+  CEB_REQUIRE(K % 8 == 0 && N % 8 == 0, "ceb_gemm_bf16_tn: K and N must be multiples of 8 (K=%d N=%d)", K, N);
+  const int bn = pick_bn(N);
+  CUtensorMap ta, tb;
+  uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)K * 2};
+  uint32_t ba[2] = {BK, BM};
+  if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
+  uint64_t db[2] = {(uint64_t)K, (uint64_t)N}, sb[1] = {(uint64_t)K * 2};
+  uint32_t bb[2] = {BK, (uint32_t)bn};
+  if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, bb)) return e;
+  TcParams p{};
+  p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = N; p.k_steps = (int)ceb_cdiv(K, BK);
+  p.relu = relu; p.out_fp32 = out_mode; p.conv = 0;
+  return dispatch_tile(bn, ta, tb, p, (cudaStream_t)stream);
+}
+
+// y[N,H,W,Cout] = act(conv3x3_s1_p1(x[N,H,W,Cin], w[Cout,3,3,Cin])), all bf16 NHWC / KRSC.
+// Cin % 64 == 0, Cout % 8 == 0, W <= 128 and 128 % W == 0, H % (128/W) == 0 or (128/W) % H == 0.
+CEB_API int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin,
+                                  int Cout, const float* bias, int relu, int out_mode, void* stream) {
+  CEB_REQUIRE(x && w && y && Nimg > 0, "ceb_conv3x3_bf16_nhwc: bad arguments");
+  CEB_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "ceb_conv3x3_bf16_nhwc: need Cin %% 64 == 0, Cout %% 8 == 0 (Cin=%d Cout=%d)", Cin, Cout);
+  CEB_REQUIRE(W <= BM && BM % W == 0, "ceb_conv3x3_bf16_nhwc: W=%d must divide %d", W, BM);
+  int tile_h = BM / W, tile_n = 1;
+  if (tile_h > H) {
+    CEB_REQUIRE(tile_h % H == 0, "ceb_conv3x3_bf16_nhwc: H=%d W=%d does not tile %d pixels", H, W, BM);
+    tile_n = tile_h / H;
+    tile_h = H;
+  } else {
+    CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_bf16_nhwc: H=%d not a multiple of the %d-row tile", H, tile_h);
+  }
+  const int bn = pick_bn(Cout);
+  CUtensorMap ta, tb;
+  uint64_t da[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
+  uint64_t sa[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
+  uint32_t ba[4] = {BK, (uint32_t)W, (uint32_t)tile_h, (uint32_t)tile_n};
+  if (int e = ceb_make_tmap_bf16(&ta, x, 4, da, sa, ba)) return e;
+  const int K = 9 * Cin;
+  uint64_t db[2] = {(uint64_t)K, (uint64_t)Cout}, sb[1] = {(uint64_t)K * 2};
+  uint32_t bb[2] = {BK, (uint32_t)bn};
+  if (int e = ceb_make_tmap_bf16(&tb, w, 2, db, sb, bb)) return e;
+  TcParams p{};
+  p.C = y; p.bias = bias; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout; p.k_steps = 9 * (Cin / BK);
+  p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = H; p.W = W; p.cin_steps = Cin / BK; p.tile_h = tile_h;
+  return dispatch_tile(bn, ta, tb, p, (cudaStream_t)stream);
+}

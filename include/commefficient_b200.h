@@ -122,6 +122,19 @@ int ceb_fedavg_delta(float* acc, const float* w0, const float* wloc, float weigh
 int ceb_count_changed(const float* w, float* prev, uint8_t* mask, int64_t n, unsigned long long* count,
                       void* stream);
 
+/* ---- tensor-core layers: tcgen05.mma + TMEM accumulators + TMA-staged operands --
+ * (reference: the cuBLAS / cuDNN calls behind nn.Linear / nn.Conv2d, models/resnet9.py:36-37,
+ *  models/fixup_resnet18.py:144-154, GPT-2 linears).  bf16 operands, fp32 accumulation.
+ *  out_mode 0: bf16 output, 1: fp32 output, 2: fp32 output += result (atomic). */
+/* C[M,N] = act(A[M,K] * B[N,K]^T + bias); A, B row-major with K contiguous; K % 8 == N % 8 == 0. */
+int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, const float* bias,
+                     int relu, int out_mode, void* stream);
+/* y[N,H,W,Cout] = act(conv3x3 stride 1 pad 1 (x[N,H,W,Cin], w[Cout,3,3,Cin]) + bias), NHWC / KRSC.
+ * Implicit GEMM: the im2col tile of tap (r,s) is a shifted 4-D TMA box, padding = TMA zero fill.
+ * Cin % 64 == 0, Cout % 8 == 0, W divides 128. */
+int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout,
+                          const float* bias, int relu, int out_mode, void* stream);
+
 /* ---- peer-memory collectives over NVLink, fused with the server update ---------
  * (reference: the single NCCL reduce + host-side weight update/download,
  *  fed_worker.py:41,138, fed_aggregator.py:327-332,455).  src/dst/flags are HOST arrays of
