@@ -19,6 +19,8 @@ native.register_signatures({
     "ceb_conv3x3_bf16_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
                                native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
                                native.c_ptr], native.c_i32),
+    "ceb_conv3x3_wgrad_bf16_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32,
+                                     native.c_i32, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
 })
 
 _OUT = {torch.bfloat16: 0, torch.float32: 1}
@@ -49,6 +51,17 @@ def conv3x3_nhwc(x: torch.Tensor, w: torch.Tensor, relu=False, out_dtype=torch.b
     native.call("ceb_conv3x3_bf16_nhwc", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, None,
                 1 if relu else 0, _OUT[out_dtype], native.stream_ptr(x.device))
     return y
+
+
+def conv3x3_wgrad_nhwc(dz: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
+    """``dw[Cout,3,3,Cin] (fp32, contiguous) += wgrad(dz[N,H,W,Cout], x[N,H,W,Cin])`` (bf16 inputs)."""
+    assert dz.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and dz.is_contiguous() and x.is_contiguous()
+    assert dw.dtype == torch.float32 and dw.is_contiguous()
+    n, h, wd, cin = x.shape
+    cout = dz.shape[3]
+    native.call("ceb_conv3x3_wgrad_bf16_nhwc", native.ptr(dz), native.ptr(x), native.ptr(dw), n, h, wd, cin, cout,
+                native.stream_ptr(x.device))
+    return dw
 
 
 def conv_supported(x, weight, stride, padding) -> bool:

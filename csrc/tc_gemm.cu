@@ -18,8 +18,13 @@ using namespace tc;
 constexpr int BM = 128;
 constexpr int BK = 64;          // bf16 elements per k-step = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kStages = 4;
+// 3 stages of (16 KB + BN*128 B): two CTAs fit in one SM's 227 KB for BN <= 128, so one CTA's
+// epilogue overlaps the other's main loop without a persistent scheduler.
+// Operand ring depth: as many 16 KB + BN*128 B stages as fit beside the epilogue staging area
+// (~200 KB per SM, one persistent CTA per SM).
+template <int BN> struct StagesFor { static constexpr int value = BN <= 64 ? 8 : (BN <= 128 ? 6 : 4); };
 constexpr int kTcThreads = 192; // warp 0: TMA, warp 1: MMA + TMEM alloc, warps 2-5: epilogue
+constexpr int kEpiStageBytes = 4 * 32 * 17 * 4;   // per epilogue warp: [32 rows][16 words + 1 pad]
 
 struct TcParams {
   void* C;               // output [M][ldc]
@@ -28,7 +33,8 @@ struct TcParams {
   int k_steps;
   int relu;
   int out_fp32;          // 0: bf16 store, 1: fp32 store, 2: fp32 atomic add
-  // convolution geometry (mode 1)
+  int m_tiles, n_tiles;
+  // convolution geometry
   int conv;
   int H, W, cin_steps;   // cin_steps = Cin / 64
   int tile_h;            // rows of the image covered by one M tile (tile_w == W)
@@ -36,27 +42,35 @@ struct TcParams {
 
 template <int BN>
 struct SmemLayout {
+  static constexpr int kStages = StagesFor<BN>::value;
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kTotal = kStages * kStageBytes + 1024 /* align */ + 256 /* barriers */;
+  static constexpr int kTotal = kStages * kStageBytes + kEpiStageBytes + 1024 /* align */ + 256 /* barriers */;
 };
 
+// Persistent: grid = min(#tiles, #SMs).  Tiles are walked M-fastest so CTAs running at the same
+// time share the B (weight) tile in L2.  The accumulator is double buffered in TMEM (2 x BN
+// columns): the epilogue warps drain tile i while the MMA thread already accumulates tile i+1,
+// and the TMA producer runs ahead across tile boundaries, so operand latency is hidden even
+// for short K loops (3x3 conv with 64 input channels has only 9 k-steps).
 template <int BN>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   using L = SmemLayout<BN>;
+  constexpr int kStages = L::kStages;
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B needs 1024 B
-  uint64_t* full_bar = (uint64_t*)(smem + kStages * L::kStageBytes);
+  uint8_t* epi_smem = smem + kStages * L::kStageBytes;
+  uint64_t* full_bar = (uint64_t*)(epi_smem + kEpiStageBytes);
   uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* tmem_full_bar = empty_bar + kStages;
-  uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+  uint64_t* tmem_full_bar = empty_bar + kStages;      // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;       // [2]
+  uint32_t* tmem_slot = (uint32_t*)(tmem_empty_bar + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m_tile = blockIdx.x;
-  const int n_tile = blockIdx.y;
+  const int num_tiles = p.m_tiles * p.n_tiles;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmapA);
@@ -65,10 +79,13 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       mbar_init(full_bar + s, 1);
       mbar_init(empty_bar + s, 1);
     }
-    mbar_init(tmem_full_bar, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tmem_full_bar + a, 1);
+      mbar_init(tmem_empty_bar + a, 4);               // one arrive per epilogue warp
+    }
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc<BN>(tmem_slot);
+  if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -77,66 +94,83 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      int n0 = 0, h0 = 0;
-      if (p.conv) {
-        const int pix0 = m_tile * BM;
-        const int hw = p.H * p.W;
-        n0 = pix0 / hw;
-        h0 = (pix0 - n0 * hw) / p.W;
-      }
-      for (int ks = 0; ks < p.k_steps; ++ks) {
-        const int s = ks % kStages;
-        const uint32_t phase = (ks / kStages) & 1;
-        mbar_wait(empty_bar + s, phase ^ 1);
-        uint8_t* a_dst = smem + s * L::kStageBytes;
-        uint8_t* b_dst = a_dst + L::kABytes;
-        mbar_expect_tx(full_bar + s, L::kStageBytes);
+      uint32_t it = 0;                                   // global k-step counter (ring position)
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
+        int n0 = 0, h0 = 0;
         if (p.conv) {
-          const int tap = ks / p.cin_steps;
-          const int c0 = (ks - tap * p.cin_steps) * BK;
-          const int r = tap / 3, sft = tap - r * 3;
-          tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 + r - 1, n0);
-        } else {
-          tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BK, m_tile * BM);
+          const int pix0 = m_tile * BM;
+          const int hw = p.H * p.W;
+          n0 = pix0 / hw;
+          h0 = (pix0 - n0 * hw) / p.W;
         }
-        tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BK, n_tile * BN);
+        for (int ks = 0; ks < p.k_steps; ++ks, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          mbar_wait(empty_bar + s, phase ^ 1);
+          uint8_t* a_dst = smem + s * L::kStageBytes;
+          uint8_t* b_dst = a_dst + L::kABytes;
+          mbar_expect_tx(full_bar + s, L::kStageBytes);
+          if (p.conv) {
+            const int tap = ks / p.cin_steps;
+            const int c0 = (ks - tap * p.cin_steps) * BK;
+            const int r = tap / 3, sft = tap - r * 3;
+            tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 + r - 1, n0);
+          } else {
+            tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BK, m_tile * BM);
+          }
+          tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BK, n_tile * BN);
+        }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one elected thread) =====
     constexpr uint32_t idesc = idesc_bf16(BM, BN, 0, 0);
-    for (int ks = 0; ks < p.k_steps; ++ks) {
-      const int s = ks % kStages;
-      const uint32_t phase = (ks / kStages) & 1;
-      mbar_wait(full_bar + s, phase);
+    uint32_t it = 0, local = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
+      const int acc = local & 1;
+      mbar_wait(tmem_empty_bar + acc, ((local >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
       tc_fence_after();
-      if (elect_one()) {
-        const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
-        const uint32_t b_addr = a_addr + L::kABytes;
+      const uint32_t tmem_d = tmem_base + acc * BN;
+      for (int ks = 0; ks < p.k_steps; ++ks, ++it) {
+        const int s = it % kStages;
+        const uint32_t phase = (it / kStages) & 1;
+        mbar_wait(full_bar + s, phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
+          const uint32_t b_addr = a_addr + L::kABytes;
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          const uint64_t da = smem_desc_sw128(a_addr + k * UMMA_K * 2, 16, 1024);
-          const uint64_t db = smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
-          umma_bf16(tmem_base, da, db, idesc, (ks | k) != 0);
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t da = smem_desc_sw128(a_addr + k * UMMA_K * 2, 16, 1024);
+            const uint64_t db = smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
+            umma_bf16(tmem_d, da, db, idesc, (ks | k) != 0);
+          }
+          umma_commit(empty_bar + s);                     // frees this smem stage when the MMAs retire
+          if (ks == p.k_steps - 1) umma_commit(tmem_full_bar + acc);
         }
-        umma_commit(empty_bar + s);                       // frees this smem stage when the MMAs retire
-        if (ks == p.k_steps - 1) umma_commit(tmem_full_bar);
+        __syncwarp();
       }
-      __syncwarp();
     }
   } else {
-    // ===== epilogue: TMEM -> registers -> global =====
+    // ===== epilogue: TMEM -> registers -> (smem transpose) -> global =====
     const int q = warp & 3;                               // TMEM lane quarter this warp may access
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    const int m = m_tile * BM + q * 32 + lane;
-    const int n_base = n_tile * BN;
+    uint32_t* stage = (uint32_t*)(epi_smem + (warp - 2) * (32 * 17 * 4));
+    uint32_t local = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
+      const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
+      const int acc = local & 1;
+      mbar_wait(tmem_full_bar + acc, (local >> 1) & 1);
+      tc_fence_after();
+      const int row0 = m_tile * BM + q * 32;              // first output row of this warp
+      const int m = row0 + lane;
+      const int n_base = n_tile * BN;
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      float v[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, v);
-      const int n0 = n_base + c * 32;
-      if (m < p.M && n0 < p.N) {
+      for (int c = 0; c < BN / 32; ++c) {
+        float v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c * 32, v);
+        const int n0 = n_base + c * 32;
+        if (n0 >= p.N) break;
         if (p.bias) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) if (n0 + j < p.N) v[j] += __ldg(p.bias + n0 + j);
@@ -146,43 +180,56 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
         const bool full = (n0 + 32 <= p.N);
-        if (p.out_fp32 == 0) {
-          __nv_bfloat16* dst = (__nv_bfloat16*)p.C + (int64_t)m * p.ldc + n0;
-          if (full) {
+        if (p.out_fp32 == 0 && full) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 pk;
-              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]);
-              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
-              __nv_bfloat162 h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-              pk.x = *(uint32_t*)&h0; pk.y = *(uint32_t*)&h1; pk.z = *(uint32_t*)&h2; pk.w = *(uint32_t*)&h3;
-              *(uint4*)(dst + j) = pk;
-            }
-          } else {
-            for (int j = 0; j < 32 && n0 + j < p.N; ++j) dst[j] = __float2bfloat16(v[j]);
+          for (int j = 0; j < 16; ++j) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+            stage[lane * 17 + j] = *(uint32_t*)&h;
           }
-        } else {
-          float* dst = (float*)p.C + (int64_t)m * p.ldc + n0;
-          if (p.out_fp32 == 1) {
-            if (full) {
+          __syncwarp();
+          // 4 lanes cover one 64-byte row segment; 8 rows per pass
 #pragma unroll
-              for (int j = 0; j < 32; j += 4) *(float4*)(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-              for (int j = 0; j < 32 && n0 + j < p.N; ++j) dst[j] = v[j];
+          for (int pass = 0; pass < 4; ++pass) {
+            const int r = pass * 8 + (lane >> 2);
+            const int w4 = (lane & 3) * 4;
+            if (row0 + r < p.M) {
+              uint4 pk;
+              pk.x = stage[r * 17 + w4]; pk.y = stage[r * 17 + w4 + 1];
+              pk.z = stage[r * 17 + w4 + 2]; pk.w = stage[r * 17 + w4 + 3];
+              *(uint4*)((__nv_bfloat16*)p.C + (int64_t)(row0 + r) * p.ldc + n0 + w4 * 2) = pk;
             }
+          }
+          __syncwarp();
+        } else if (m < p.M) {
+          if (p.out_fp32 == 0) {
+            __nv_bfloat16* dst = (__nv_bfloat16*)p.C + (int64_t)m * p.ldc + n0;
+            for (int j = 0; j < 32 && n0 + j < p.N; ++j) dst[j] = __float2bfloat16(v[j]);
           } else {
-            for (int j = 0; j < 32 && n0 + j < p.N; ++j) red_add_f32(dst + j, v[j]);
+            float* dst = (float*)p.C + (int64_t)m * p.ldc + n0;
+            if (p.out_fp32 == 1) {
+              if (full) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) *(float4*)(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              } else {
+                for (int j = 0; j < 32 && n0 + j < p.N; ++j) dst[j] = v[j];
+              }
+            } else {
+              for (int j = 0; j < 32 && n0 + j < p.N; ++j) red_add_f32(dst + j, v[j]);
+            }
           }
         }
       }
+      // this warp is done reading accumulator `acc`
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
     }
-    tc_fence_before();
   }
+  tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<BN>(tmem_base);
+    tmem_dealloc<2 * BN>(tmem_base);
   }
 }
 
@@ -227,8 +274,12 @@ static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcPar
     CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
-  dim3 grid((unsigned)ceb_cdiv(p.M, BM), (unsigned)ceb_cdiv(p.N, BN), 1);
-  tc_tile_kernel<BN><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, p);
+  TcParams q = p;
+  q.m_tiles = (int)ceb_cdiv(p.M, BM);
+  q.n_tiles = (int)ceb_cdiv(p.N, BN);
+  const int tiles = q.m_tiles * q.n_tiles;
+  const int grid = tiles < ceb_num_sms() ? tiles : ceb_num_sms();
+  tc_tile_kernel<BN><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, q);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;

@@ -1,0 +1,222 @@
+// Weight gradient of a 3x3 / stride 1 / pad 1 convolution on tcgen05 tensor cores (sm_100a).
+//
+//   dW[co][r][s][ci] += sum over pixels p of dZ[p][co] * X[p + (r-1, s-1)][ci]      (NHWC, KRSC)
+//
+// This is a GEMM whose reduction dimension is the pixel index, i.e. BOTH operands are
+// "MN-major" (channels contiguous, pixels strided): A = dZ^T (M = co), B = shifted X (N = ci).
+// tcgen05.mma reads MN-major operands directly from 128-byte-swizzled shared memory (instruction
+// descriptor bits 15/16), so no transposed copy of the activations is ever made.  One CTA owns a
+// (co tile, kernel row r, ci tile) triple and a slice of the pixels (split-K): per 64-pixel step it
+// loads ONE dZ tile and the THREE horizontally shifted X tiles (s = 0,1,2; TMA zero fill = padding)
+// and accumulates three 128 x BN fp32 tiles in TMEM.  The epilogue adds them into the fp32 flat
+// gradient buffer (KRSC, exactly the layout of utils/flat.py "nhwc") with 16-byte vector atomics.
+// Replaces cuDNN's wgrad behind autograd of nn.Conv2d
+// (/root/reference/CommEfficient/models/resnet9.py:36-37, fed_worker.py:286 loss.backward()).
+#include "tc_common.cuh"
+
+using namespace tc;
+
+constexpr int WG_M = 128;          // output channels per tile
+constexpr int WG_KPIX = 64;        // pixels per k-step
+constexpr int WG_THREADS = 192;
+
+struct WgParams {
+  float* dW;             // [Cout][9*Cin] fp32, accumulated
+  int Cout, Cin;
+  int H, W;
+  int k_steps_total;     // ceil(Npix / 64)
+  int k_per_cta;         // k-steps handled by one CTA
+  int ci_tiles;
+  int tile_h, tile_n;    // box geometry of a 64-pixel step (tile_w == W)
+};
+
+template <int BN>
+struct WgSmem {
+  static constexpr int kChunk = WG_KPIX * 128;                   // [64 px][64 ch] bf16 = 8 KB
+  static constexpr int kABytes = 2 * kChunk;                      // 128 co
+  static constexpr int kBBytes = 3 * (BN / 64) * kChunk;          // 3 taps x BN ci
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = BN <= 64 ? 4 : 3;
+  static constexpr int kTotal = kStages * kStageBytes + 1024 + 256;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <int BN>
+__global__ void __launch_bounds__(WG_THREADS, 1)
+tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constant__ CUtensorMap tmapX, WgParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  using L = WgSmem<BN>;
+  constexpr int kStages = L::kStages;
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = (uint64_t*)(smem + kStages * L::kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full_bar = empty_bar + kStages;
+  uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  // blockIdx.x = ((co_tile * 3 + r) * ci_tiles + ci_tile), blockIdx.y = split
+  const int ci_tile = blockIdx.x % p.ci_tiles;
+  const int r = (blockIdx.x / p.ci_tiles) % 3;
+  const int co_tile = blockIdx.x / (p.ci_tiles * 3);
+  const int ks_begin = blockIdx.y * p.k_per_cta;
+  const int ks_end = min(ks_begin + p.k_per_cta, p.k_steps_total);
+  const int n_steps = ks_end - ks_begin;
+  constexpr int TMEM_COLS = (3 * BN <= 256) ? 256 : 512;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmapDZ);
+    tma_prefetch_desc(&tmapX);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (n_steps > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        const int hw = p.H * p.W;
+        for (int i = 0; i < n_steps; ++i) {
+          const int s = i % kStages;
+          const uint32_t phase = (i / kStages) & 1;
+          mbar_wait(empty_bar + s, phase ^ 1);
+          uint8_t* a_dst = smem + s * L::kStageBytes;
+          uint8_t* b_dst = a_dst + L::kABytes;
+          mbar_expect_tx(full_bar + s, L::kStageBytes);
+          const int pix0 = (ks_begin + i) * WG_KPIX;
+          // dZ: 2-D [pixels][Cout]: two 64-channel chunks
+          tma_load_2d(a_dst, &tmapDZ, full_bar + s, co_tile * WG_M, pix0);
+          tma_load_2d(a_dst + L::kChunk, &tmapDZ, full_bar + s, co_tile * WG_M + 64, pix0);
+          // X: 4-D [N][H][W][Cin], shifted by (r-1, s-1)
+          const int n0 = pix0 / hw;
+          const int h0 = (pix0 - n0 * hw) / p.W;
+#pragma unroll
+          for (int sft = 0; sft < 3; ++sft)
+#pragma unroll
+            for (int ch = 0; ch < BN / 64; ++ch)
+              tma_load_4d(b_dst + (sft * (BN / 64) + ch) * L::kChunk, &tmapX, full_bar + s,
+                          ci_tile * BN + ch * 64, sft - 1, h0 + r - 1, n0);
+        }
+      }
+    } else if (warp == 1) {
+      constexpr uint32_t idesc = idesc_bf16(WG_M, BN, 1, 1);     // both operands MN-major
+      for (int i = 0; i < n_steps; ++i) {
+        const int s = i % kStages;
+        const uint32_t phase = (i / kStages) & 1;
+        mbar_wait(full_bar + s, phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
+          const uint32_t b_addr = a_addr + L::kABytes;
+#pragma unroll
+          for (int sft = 0; sft < 3; ++sft) {
+#pragma unroll
+            for (int k = 0; k < WG_KPIX / 16; ++k) {
+              // 16 pixels = 16 rows of 128 B; MN chunks (64 channels) are L::kChunk apart
+              const uint64_t da = smem_desc_sw128(a_addr + k * 16 * 128, L::kChunk, 1024);
+              const uint64_t db = smem_desc_sw128(b_addr + sft * (BN / 64) * L::kChunk + k * 16 * 128, L::kChunk, 1024);
+              umma_bf16(tmem_base + sft * BN, da, db, idesc, (i | k) != 0);
+            }
+          }
+          umma_commit(empty_bar + s);
+          if (i == n_steps - 1) umma_commit(tmem_full_bar);
+        }
+        __syncwarp();
+      }
+    } else {
+      const int q = warp & 3;
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+      const int co = co_tile * WG_M + q * 32 + lane;
+      const int ldw = 9 * p.Cin;
+#pragma unroll 1
+      for (int sft = 0; sft < 3; ++sft) {
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          float v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + sft * BN + c * 32, v);
+          const int ci0 = ci_tile * BN + c * 32;
+          if (co < p.Cout && ci0 < p.Cin) {
+            float* dst = p.dW + (int64_t)co * ldw + (r * 3 + sft) * p.Cin + ci0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<TMEM_COLS>(tmem_base);
+  }
+}
+
+template <int BN>
+static int launch_wgrad(const CUtensorMap& tdz, const CUtensorMap& tx, WgParams p, int co_tiles, int split, cudaStream_t st) {
+  using L = WgSmem<BN>;
+  static bool configured = false;
+  if (!configured) {
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    configured = true;
+  }
+  dim3 grid((unsigned)(co_tiles * 3 * p.ci_tiles), (unsigned)split, 1);
+  tc_wgrad_kernel<BN><<<grid, WG_THREADS, L::kTotal, st>>>(tdz, tx, p);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// dW[Cout][3][3][Cin] (fp32) += wgrad(dz[N,H,W,Cout] bf16, x[N,H,W,Cin] bf16).
+// Cin % 64 == 0, Cout % 64 == 0, W in {4,8,16,32,64}, H*W a multiple of 64 or a divisor of it.
+CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin,
+                                        int Cout, void* stream) {
+  CEB_REQUIRE(dz && x && dW && Nimg > 0, "ceb_conv3x3_wgrad_bf16_nhwc: bad arguments");
+  CEB_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "ceb_conv3x3_wgrad_bf16_nhwc: Cin, Cout must be multiples of 64 (Cin=%d Cout=%d)", Cin, Cout);
+  CEB_REQUIRE(W <= WG_KPIX && WG_KPIX % W == 0, "ceb_conv3x3_wgrad_bf16_nhwc: W=%d must divide %d", W, WG_KPIX);
+  int tile_h = WG_KPIX / W, tile_n = 1;
+  if (tile_h > H) {
+    CEB_REQUIRE(tile_h % H == 0, "ceb_conv3x3_wgrad_bf16_nhwc: H=%d W=%d does not tile %d pixels", H, W, WG_KPIX);
+    tile_n = tile_h / H;
+    tile_h = H;
+  } else {
+    CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_wgrad_bf16_nhwc: H=%d not a multiple of the %d-row step", H, tile_h);
+  }
+  const int64_t npix = (int64_t)Nimg * H * W;
+  CUtensorMap tdz, tx;
+  uint64_t dd[2] = {(uint64_t)Cout, (uint64_t)npix}, sd[1] = {(uint64_t)Cout * 2};
+  uint32_t bd[2] = {64, WG_KPIX};
+  if (int e = ceb_make_tmap_bf16(&tdz, dz, 2, dd, sd, bd)) return e;
+  uint64_t dx[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
+  uint64_t sx[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
+  uint32_t bx[4] = {64, (uint32_t)W, (uint32_t)tile_h, (uint32_t)tile_n};
+  if (int e = ceb_make_tmap_bf16(&tx, x, 4, dx, sx, bx)) return e;
+
+  const int bn = (Cin % 128 == 0) ? 128 : 64;
+  WgParams p{};
+  p.dW = dW; p.Cout = Cout; p.Cin = Cin; p.H = H; p.W = W;
+  p.k_steps_total = (int)ceb_cdiv(npix, WG_KPIX);
+  p.ci_tiles = Cin / bn;
+  p.tile_h = tile_h; p.tile_n = tile_n;
+  const int co_tiles = (int)ceb_cdiv(Cout, WG_M);
+  const int base_ctas = co_tiles * 3 * p.ci_tiles;
+  int split = (int)ceb_cdiv(ceb_num_sms(), base_ctas);
+  if (split > p.k_steps_total) split = p.k_steps_total;
+  if (split < 1) split = 1;
+  p.k_per_cta = (int)ceb_cdiv(p.k_steps_total, split);
+  split = (int)ceb_cdiv(p.k_steps_total, p.k_per_cta);
+  if (bn == 128) return launch_wgrad<128>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
+  return launch_wgrad<64>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
+}

@@ -135,6 +135,12 @@ int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K,
 int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout,
                           const float* bias, int relu, int out_mode, void* stream);
 
+/* dW[Cout][3][3][Cin] (fp32) += sum_p dz[p][co] * x[p + (r-1,s-1)][ci]; dz, x bf16 NHWC.  Both GEMM
+ * operands are MN-major (pixels are the reduction dimension); split-K with vector atomics.
+ * Cin % 64 == 0, Cout % 64 == 0, W divides 64. */
+int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin,
+                                int Cout, void* stream);
+
 /* ---- peer-memory collectives over NVLink, fused with the server update ---------
  * (reference: the single NCCL reduce + host-side weight update/download,
  *  fed_worker.py:41,138, fed_aggregator.py:327-332,455).  src/dst/flags are HOST arrays of

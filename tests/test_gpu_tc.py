@@ -51,3 +51,18 @@ def test_conv3x3_matches_fp32(n, h, cin, cout, relu):
     got = tc.conv3x3_nhwc(x, w, relu=relu, out_dtype=torch.float32)
     assert got.shape == want.shape
     assert _rel_err(got, want) < 1e-4
+
+
+@pytest.mark.parametrize("n,h,cin,cout", [(4, 32, 64, 128), (2, 16, 128, 128), (6, 8, 256, 512), (16, 4, 512, 512),
+                                          (5, 16, 128, 256), (3, 4, 64, 64), (100, 32, 64, 128)])
+def test_conv3x3_wgrad_matches_fp32(n, h, cin, cout):
+    g = torch.Generator(device=DEV).manual_seed(n * h + cout)
+    x = torch.randn(n, h, h, cin, device=DEV, generator=g).bfloat16()
+    dz = torch.randn(n, h, h, cout, device=DEV, generator=g).bfloat16()
+    want = torch.nn.grad.conv2d_weight(x.float().permute(0, 3, 1, 2), (cout, cin, 3, 3),
+                                       dz.float().permute(0, 3, 1, 2), padding=1).permute(0, 2, 3, 1)
+    dw = torch.zeros(cout, 3, 3, cin, device=DEV)
+    tc.conv3x3_wgrad_nhwc(dz, x, dw)
+    assert _rel_err(dw, want) < 1e-4
+    tc.conv3x3_wgrad_nhwc(dz, x, dw)          # accumulates
+    assert _rel_err(dw, 2 * want) < 1e-4
