@@ -123,6 +123,10 @@ class ResNet9(nn.Module):
         self.kw = kw
 
     def forward(self, x):
+        if nnops.native_enabled():
+            from ..ops import tc
+            if tc.resnet9_supported(self, x):
+                return tc.resnet9_forward(self, x)
         return self.n(x)
 
     def finetune_parameters(self):

@@ -18,7 +18,15 @@ native.register_signatures({
                           native.c_ptr, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
     "ceb_conv3x3_bf16_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
                                native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
-                               native.c_ptr], native.c_i32),
+                               native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_conv_w_dgrad_layout": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_cast_f32_bf16": ([native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr], native.c_i32),
+    "ceb_maxpool_nhwc_bf16": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32, native.c_i32,
+                               native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_maxpool_bwd_nhwc_bf16": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32,
+                                   native.c_i32, native.c_i32, native.c_i32, native.c_i32, native.c_ptr],
+                                  native.c_i32),
+    "ceb_relu_bwd_bf16": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr], native.c_i32),
     "ceb_conv3x3_wgrad_bf16_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32,
                                      native.c_i32, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
 })
@@ -41,16 +49,55 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias=None, relu=False, out_dtype=t
     return out
 
 
-def conv3x3_nhwc(x: torch.Tensor, w: torch.Tensor, relu=False, out_dtype=torch.bfloat16) -> torch.Tensor:
+def conv3x3_nhwc(x: torch.Tensor, w: torch.Tensor, relu=False, out_dtype=torch.bfloat16, relu_mask=None) -> torch.Tensor:
     """3x3 / stride 1 / pad 1 convolution.  ``x``: ``[N, H, W, Cin]`` bf16 contiguous, ``w``:
-    ``[Cout, 3, 3, Cin]`` bf16 contiguous; returns ``[N, H, W, Cout]``."""
+    ``[Cout, 3, 3, Cin]`` bf16 contiguous; returns ``[N, H, W, Cout]``.  ``relu_mask`` (same shape
+    as the result): zero the result where the mask is <= 0 (ReLU backward fused into a dgrad)."""
     assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.is_contiguous() and w.is_contiguous()
     n, h, wd, cin = x.shape
     cout = w.shape[0]
     y = torch.empty((n, h, wd, cout), dtype=out_dtype, device=x.device)
     native.call("ceb_conv3x3_bf16_nhwc", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, None,
-                1 if relu else 0, _OUT[out_dtype], native.stream_ptr(x.device))
+                1 if relu else 0, _OUT[out_dtype], native.ptr(relu_mask), native.stream_ptr(x.device))
     return y
+
+
+def dgrad_weights(w_krsc_f32: torch.Tensor) -> torch.Tensor:
+    """``[Cin][3][3][Cout]`` bf16 weights of the data-gradient convolution (rotated 180 deg, in/out
+    swapped) from fp32 ``[Cout][3][3][Cin]``."""
+    cout, _, _, cin = w_krsc_f32.shape
+    out = torch.empty((cin, 3, 3, cout), dtype=torch.bfloat16, device=w_krsc_f32.device)
+    native.call("ceb_conv_w_dgrad_layout", native.ptr(w_krsc_f32), native.ptr(out), cout, cin,
+                native.stream_ptr(out.device))
+    return out
+
+
+def cast_bf16(src: torch.Tensor) -> torch.Tensor:
+    out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
+    native.call("ceb_cast_f32_bf16", native.ptr(src), native.ptr(out), src.numel(), native.stream_ptr(src.device))
+    return out
+
+
+def maxpool_nhwc(y: torch.Tensor, k: int) -> torch.Tensor:
+    n, h, w, c = y.shape
+    out = torch.empty((n, h // k, w // k, c), dtype=torch.bfloat16, device=y.device)
+    native.call("ceb_maxpool_nhwc_bf16", native.ptr(y), native.ptr(out), n, h, w, c, k, native.stream_ptr(y.device))
+    return out
+
+
+def maxpool_bwd_nhwc(y: torch.Tensor, dp: torch.Tensor, k: int, relu_mask: bool) -> torch.Tensor:
+    n, h, w, c = y.shape
+    dz = torch.empty_like(y)
+    native.call("ceb_maxpool_bwd_nhwc_bf16", native.ptr(y), native.ptr(dp), native.ptr(dz), n, h, w, c, k,
+                1 if relu_mask else 0, native.stream_ptr(y.device))
+    return dz
+
+
+def relu_bwd(y: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
+    dz = torch.empty_like(y)
+    native.call("ceb_relu_bwd_bf16", native.ptr(y), native.ptr(dy), native.ptr(dz), y.numel(),
+                native.stream_ptr(y.device))
+    return dz
 
 
 def conv3x3_wgrad_nhwc(dz: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
@@ -70,3 +117,109 @@ def conv_supported(x, weight, stride, padding) -> bool:
 
 def linear_supported(x, weight) -> bool:
     return False
+
+
+# ---------------------------------------------------------------------------- ResNet-9 on the native kernels
+def _krsc(t: torch.Tensor) -> torch.Tensor:
+    """fp32 ``[Cout,3,3,Cin]`` contiguous view of a conv weight / gradient stored NHWC in the flat buffer."""
+    v = t.permute(0, 2, 3, 1)
+    if not v.is_contiguous():
+        raise RuntimeError("native conv path needs the flat buffer in 'nhwc' layout (--flat_layout nhwc)")
+    return v
+
+
+def resnet9_supported(model, x: torch.Tensor) -> bool:
+    n = model.n
+    if not x.is_cuda or x.dim() != 4 or x.shape[2] != 32 or x.shape[3] != 32:
+        return False
+    if n.prep.do_batchnorm:
+        return False
+    ch = n.channels
+    if any(ch[k] % 64 for k in ("prep", "layer1", "layer2", "layer3")):
+        return False
+    fp = getattr(model, "_flat_params", None)
+    return fp is not None and fp.layout == "nhwc"
+
+
+class _ResNet9Fn(torch.autograd.Function):
+    """Whole-network forward/backward of ResNet-9 (no BatchNorm) on the hand-written kernels:
+    implicit-GEMM conv + fused ReLU (tcgen05), fused ReLU/max-pool backward, MN-major wgrad
+    accumulating straight into the flat fp32 gradient buffer.  The 3-channel stem and the
+    512 -> classes head are tiny and stay on library ops."""
+
+    @staticmethod
+    def forward(ctx, x, net, *weights):
+        import torch.nn.functional as F
+        convs = [net.prep.conv, net.layer1.conv, net.res1.res1.conv, net.res1.res2.conv, net.layer2.conv,
+                 net.layer3.conv, net.res3.res1.conv, net.res3.res2.conv]
+        wb = [cast_bf16(_krsc(c.weight.data)) for c in convs[1:]]
+        xb = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w0 = convs[0].weight.data.to(torch.bfloat16)
+        a0 = F.relu(F.conv2d(xb, w0, padding=1)).permute(0, 2, 3, 1).contiguous()
+        a1 = conv3x3_nhwc(a0, wb[0], relu=True)
+        p1 = maxpool_nhwc(a1, 2)
+        r1a = conv3x3_nhwc(p1, wb[1], relu=True)
+        r1b = conv3x3_nhwc(r1a, wb[2], relu=True)
+        s1 = p1 + r1b
+        a2 = conv3x3_nhwc(s1, wb[3], relu=True)
+        p2 = maxpool_nhwc(a2, 2)
+        a3 = conv3x3_nhwc(p2, wb[4], relu=True)
+        p3 = maxpool_nhwc(a3, 2)
+        r3a = conv3x3_nhwc(p3, wb[5], relu=True)
+        r3b = conv3x3_nhwc(r3a, wb[6], relu=True)
+        s3 = p3 + r3b
+        f = maxpool_nhwc(s3, 4).view(x.shape[0], -1)
+        logits = (f.float() @ net.linear.weight.data.t()) * net.out_scale
+        ctx.net = net
+        ctx.saved = (xb, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3, f)
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        net = ctx.net
+        xb, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3, f = ctx.saved
+        convs = [net.prep.conv, net.layer1.conv, net.res1.res1.conv, net.res1.res2.conv, net.layer2.conv,
+                 net.layer3.conv, net.res3.res1.conv, net.res3.res2.conv]
+        gw = [_krsc(c.weight.grad) for c in convs]                       # fp32 KRSC views of the flat gradient
+        wd = [None] + [dgrad_weights(_krsc(c.weight.data)) for c in convs[1:]]
+        n = xb.shape[0]
+
+        dl = dlogits.float() * net.out_scale
+        net.linear.weight.grad.add_(dl.t() @ f.float())
+        df = (dl @ net.linear.weight.data).to(torch.bfloat16).view(n, 1, 1, -1).contiguous()
+        ds3 = maxpool_bwd_nhwc(s3, df, 4, relu_mask=False)
+
+        dz = relu_bwd(r3b, ds3)
+        conv3x3_wgrad_nhwc(dz, r3a, gw[7])
+        dz = conv3x3_nhwc(dz, wd[7], relu_mask=r3a)
+        conv3x3_wgrad_nhwc(dz, p3, gw[6])
+        dp3 = ds3 + conv3x3_nhwc(dz, wd[6])
+
+        dz = maxpool_bwd_nhwc(a3, dp3, 2, relu_mask=True)
+        conv3x3_wgrad_nhwc(dz, p2, gw[5])
+        dp2 = conv3x3_nhwc(dz, wd[5])
+
+        dz = maxpool_bwd_nhwc(a2, dp2, 2, relu_mask=True)
+        conv3x3_wgrad_nhwc(dz, s1, gw[4])
+        ds1 = conv3x3_nhwc(dz, wd[4])
+
+        dz = relu_bwd(r1b, ds1)
+        conv3x3_wgrad_nhwc(dz, r1a, gw[3])
+        dz = conv3x3_nhwc(dz, wd[3], relu_mask=r1a)
+        conv3x3_wgrad_nhwc(dz, p1, gw[2])
+        dp1 = ds1 + conv3x3_nhwc(dz, wd[2])
+
+        dz = maxpool_bwd_nhwc(a1, dp1, 2, relu_mask=True)
+        conv3x3_wgrad_nhwc(dz, a0, gw[1])
+        da0 = conv3x3_nhwc(dz, wd[1], relu_mask=a0)
+
+        # 3-channel stem: weight gradient through the library (0.4 % of the FLOPs)
+        g0 = torch.nn.grad.conv2d_weight(xb, convs[0].weight.shape, da0.permute(0, 3, 1, 2), padding=1)
+        convs[0].weight.grad.add_(g0.float())
+        return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
+
+
+def resnet9_forward(model, x: torch.Tensor) -> torch.Tensor:
+    net = model.n
+    weights = [p for p in net.parameters() if p.requires_grad]
+    return _ResNet9Fn.apply(x, net, *weights)

@@ -1,0 +1,198 @@
+// Small bf16 NHWC helpers around the tensor-core layers (sm_100a): weight casts / re-layouts,
+// fused ReLU + 2x2 / 4x4 max-pool forward and its backward (which also applies the ReLU mask).
+// Reference ops: nn.MaxPool2d + ReLU in /root/reference/CommEfficient/models/resnet9.py:48-56,95.
+#include <cuda_bf16.h>
+#include "common.cuh"
+
+// ------------------------------------------------------------------ casts / weight layouts
+__global__ void __launch_bounds__(256)
+cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+    if (i + 3 < n) {
+      float4 v = *reinterpret_cast<const float4*>(src + i);
+      __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+      uint2 pk; pk.x = *(uint32_t*)&a; pk.y = *(uint32_t*)&b;
+      *reinterpret_cast<uint2*>(dst + i) = pk;
+    } else {
+      for (int64_t j = i; j < n; ++j) dst[j] = __float2bfloat16(src[j]);
+    }
+  }
+}
+
+// dst (bf16) = src (fp32); n elements; src 16-byte aligned.
+CEB_API int ceb_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
+  CEB_REQUIRE(src && dst && n > 0, "ceb_cast_f32_bf16: bad arguments");
+  cast_f32_bf16_kernel<<<ceb_grid_for(ceb_cdiv(n, 4), 256), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, n);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// dgrad weights: dst[ci][2-r][2-s][co] = src[co][r][s][ci]  (fp32 or bf16 source -> bf16)
+template <typename T>
+__global__ void __launch_bounds__(256)
+w_rot180_t_kernel(const T* __restrict__ src, __nv_bfloat16* __restrict__ dst, int Cout, int Cin) {
+  const int64_t total = (int64_t)Cout * 9 * Cin;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += stride) {
+    // o indexes dst: ((ci*3 + r2)*3 + s2)*Cout + co
+    const int co = (int)(o % Cout);
+    int64_t t = o / Cout;
+    const int s2 = (int)(t % 3); t /= 3;
+    const int r2 = (int)(t % 3);
+    const int ci = (int)(t / 3);
+    const int64_t si = (((int64_t)co * 3 + (2 - r2)) * 3 + (2 - s2)) * Cin + ci;
+    dst[o] = __float2bfloat16((float)src[si]);
+  }
+}
+
+CEB_API int ceb_conv_w_dgrad_layout(const float* w_krsc, void* dst_bf16, int Cout, int Cin, void* stream) {
+  CEB_REQUIRE(w_krsc && dst_bf16 && Cout > 0 && Cin > 0, "ceb_conv_w_dgrad_layout: bad arguments");
+  const int64_t total = (int64_t)Cout * 9 * Cin;
+  w_rot180_t_kernel<float><<<ceb_grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(w_krsc, (__nv_bfloat16*)dst_bf16, Cout, Cin);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ max pooling (k = 2 or 4), 8 channels per thread
+struct bf16x8 { uint4 v; };
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { float2 t = __bfloat1622float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 u;
+  __nv_bfloat162 h0 = __floats2bfloat162_rn(f[0], f[1]), h1 = __floats2bfloat162_rn(f[2], f[3]);
+  __nv_bfloat162 h2 = __floats2bfloat162_rn(f[4], f[5]), h3 = __floats2bfloat162_rn(f[6], f[7]);
+  u.x = *(uint32_t*)&h0; u.y = *(uint32_t*)&h1; u.z = *(uint32_t*)&h2; u.w = *(uint32_t*)&h3;
+  return u;
+}
+
+template <int KP>
+__global__ void __launch_bounds__(256)
+maxpool_fwd_kernel(const uint4* __restrict__ y, uint4* __restrict__ out, int N, int H, int W, int C8) {
+  const int Ho = H / KP, Wo = W / KP;
+  const int64_t total = (int64_t)N * Ho * Wo * C8;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += stride) {
+    const int c = (int)(o % C8);
+    int64_t t = o / C8;
+    const int wo = (int)(t % Wo); t /= Wo;
+    const int ho = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    float best[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) best[i] = -INFINITY;
+#pragma unroll
+    for (int dy = 0; dy < KP; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < KP; ++dx) {
+        float f[8];
+        unpack8(__ldg(y + (((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) best[i] = fmaxf(best[i], f[i]);
+      }
+    out[o] = pack8(best);
+  }
+}
+
+// dz = route dp to the first arg-max of each KPxKP window of y; with relu_mask also zero where y <= 0
+template <int KP>
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dp, uint4* __restrict__ dz,
+                   int N, int H, int W, int C8, int relu_mask) {
+  const int Ho = H / KP, Wo = W / KP;
+  const int64_t total = (int64_t)N * Ho * Wo * C8;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += stride) {
+    const int c = (int)(o % C8);
+    int64_t t = o / C8;
+    const int wo = (int)(t % Wo); t /= Wo;
+    const int ho = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    float best[8];
+    int arg[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; arg[i] = 0; }
+#pragma unroll
+    for (int dy = 0; dy < KP; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < KP; ++dx) {
+        float f[8];
+        unpack8(__ldg(y + (((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (f[i] > best[i]) { best[i] = f[i]; arg[i] = dy * KP + dx; }
+      }
+    float g[8];
+    unpack8(__ldg(dp + o), g);
+#pragma unroll
+    for (int dy = 0; dy < KP; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < KP; ++dx) {
+        float outv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          outv[i] = (arg[i] == dy * KP + dx && !(relu_mask && best[i] <= 0.f)) ? g[i] : 0.f;
+        dz[(((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c] = pack8(outv);
+      }
+  }
+}
+
+static int check_pool(const char* who, int N, int H, int W, int C, int k) {
+  CEB_REQUIRE(N > 0 && C % 8 == 0 && (k == 2 || k == 4) && H % k == 0 && W % k == 0,
+              "%s: need C %% 8 == 0, k in {2,4}, H, W multiples of k (N=%d H=%d W=%d C=%d k=%d)", who, N, H, W, C, k);
+  return 0;
+}
+
+// out[N,H/k,W/k,C] = maxpool_k(y[N,H,W,C]), bf16 NHWC
+CEB_API int ceb_maxpool_nhwc_bf16(const void* y, void* out, int N, int H, int W, int C, int k, void* stream) {
+  CEB_REQUIRE(y && out, "ceb_maxpool_nhwc_bf16: null pointer");
+  if (int e = check_pool("ceb_maxpool_nhwc_bf16", N, H, W, C, k)) return e;
+  const int64_t total = (int64_t)N * (H / k) * (W / k) * (C / 8);
+  const int grid = ceb_grid_for(total, 256);
+  if (k == 2) maxpool_fwd_kernel<2><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (uint4*)out, N, H, W, C / 8);
+  else maxpool_fwd_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (uint4*)out, N, H, W, C / 8);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// dz[N,H,W,C] = maxpool_k backward of dp[N,H/k,W/k,C] through y (and through ReLU when relu_mask)
+CEB_API int ceb_maxpool_bwd_nhwc_bf16(const void* y, const void* dp, void* dz, int N, int H, int W, int C, int k,
+                                      int relu_mask, void* stream) {
+  CEB_REQUIRE(y && dp && dz, "ceb_maxpool_bwd_nhwc_bf16: null pointer");
+  if (int e = check_pool("ceb_maxpool_bwd_nhwc_bf16", N, H, W, C, k)) return e;
+  const int64_t total = (int64_t)N * (H / k) * (W / k) * (C / 8);
+  const int grid = ceb_grid_for(total, 256);
+  if (k == 2) maxpool_bwd_kernel<2><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, C / 8, relu_mask);
+  else maxpool_bwd_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, C / 8, relu_mask);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// dz = dy where y > 0 else 0 (ReLU backward), bf16, n % 8 == 0
+__global__ void __launch_bounds__(256)
+relu_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dy, uint4* __restrict__ dz, int64_t n8) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    float a[8], g[8];
+    unpack8(__ldg(y + i), a);
+    unpack8(__ldg(dy + i), g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = a[j] > 0.f ? g[j] : 0.f;
+    dz[i] = pack8(g);
+  }
+}
+
+CEB_API int ceb_relu_bwd_bf16(const void* y, const void* dy, void* dz, int64_t n, void* stream) {
+  CEB_REQUIRE(y && dy && dz && n > 0 && n % 8 == 0, "ceb_relu_bwd_bf16: need n %% 8 == 0");
+  relu_bwd_kernel<<<ceb_grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dy, (uint4*)dz, n / 8);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}

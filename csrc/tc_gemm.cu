@@ -29,6 +29,7 @@ constexpr int kEpiStageBytes = 4 * 32 * 17 * 4;   // per epilogue warp: [32 rows
 struct TcParams {
   void* C;               // output [M][ldc]
   const float* bias;     // per output column (nullable)
+  const void* mask;      // bf16 [M][ldc] (nullable): output is zeroed where mask <= 0 (ReLU backward)
   int M, N, ldc;
   int k_steps;
   int relu;
@@ -179,6 +180,12 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
+        if (p.mask && m < p.M) {
+          const __nv_bfloat16* mk = (const __nv_bfloat16*)p.mask + (int64_t)m * p.ldc + n0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (n0 + j < p.N && !(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
+        }
         const bool full = (n0 + 32 <= p.N);
         if (p.out_fp32 == 0 && full) {
 #pragma unroll
@@ -319,7 +326,8 @@ CEB_API int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N
 // y[N,H,W,Cout] = act(conv3x3_s1_p1(x[N,H,W,Cin], w[Cout,3,3,Cin])), all bf16 NHWC / KRSC.
 // Cin % 64 == 0, Cout % 8 == 0, W <= 128 and 128 % W == 0, H % (128/W) == 0 or (128/W) % H == 0.
 CEB_API int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin,
-                                  int Cout, const float* bias, int relu, int out_mode, void* stream) {
+                                  int Cout, const float* bias, int relu, int out_mode, const void* relu_mask,
+                                  void* stream) {
   CEB_REQUIRE(x && w && y && Nimg > 0, "ceb_conv3x3_bf16_nhwc: bad arguments");
   CEB_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "ceb_conv3x3_bf16_nhwc: need Cin %% 64 == 0, Cout %% 8 == 0 (Cin=%d Cout=%d)", Cin, Cout);
   CEB_REQUIRE(W <= BM && BM % W == 0, "ceb_conv3x3_bf16_nhwc: W=%d must divide %d", W, BM);
@@ -342,7 +350,7 @@ CEB_API int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nim
   uint32_t bb[2] = {BK, (uint32_t)bn};
   if (int e = ceb_make_tmap_bf16(&tb, w, 2, db, sb, bb)) return e;
   TcParams p{};
-  p.C = y; p.bias = bias; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout; p.k_steps = 9 * (Cin / BK);
+  p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout; p.k_steps = 9 * (Cin / BK);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = H; p.W = W; p.cin_steps = Cin / BK; p.tile_h = tile_h;
   return dispatch_tile(bn, ta, tb, p, (cudaStream_t)stream);
 }

@@ -131,9 +131,21 @@ int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K,
                      int relu, int out_mode, void* stream);
 /* y[N,H,W,Cout] = act(conv3x3 stride 1 pad 1 (x[N,H,W,Cin], w[Cout,3,3,Cin]) + bias), NHWC / KRSC.
  * Implicit GEMM: the im2col tile of tap (r,s) is a shifted 4-D TMA box, padding = TMA zero fill.
- * Cin % 64 == 0, Cout % 8 == 0, W divides 128. */
+ * Cin % 64 == 0, Cout % 8 == 0, W divides 128.
+ * relu_mask (nullable, bf16, same shape as y): y is zeroed where relu_mask <= 0 -- the ReLU
+ * backward fused into a data-gradient convolution (dgrad = this kernel on dz with the weights
+ * re-laid-out by ceb_conv_w_dgrad_layout). */
 int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout,
-                          const float* bias, int relu, int out_mode, void* stream);
+                          const float* bias, int relu, int out_mode, const void* relu_mask, void* stream);
+/* dst[ci][2-r][2-s][co] (bf16) = w[co][r][s][ci] (fp32): weights of the data-gradient convolution. */
+int ceb_conv_w_dgrad_layout(const float* w_krsc, void* dst_bf16, int Cout, int Cin, void* stream);
+int ceb_cast_f32_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
+/* bf16 NHWC max pooling (k = 2 or 4) and its backward; relu_mask != 0 also applies the ReLU
+ * backward of y (reference: resnet9.py:48-56,95). */
+int ceb_maxpool_nhwc_bf16(const void* y, void* out, int N, int H, int W, int C, int k, void* stream);
+int ceb_maxpool_bwd_nhwc_bf16(const void* y, const void* dp, void* dz, int N, int H, int W, int C, int k,
+                              int relu_mask, void* stream);
+int ceb_relu_bwd_bf16(const void* y, const void* dy, void* dz, int64_t n, void* stream);
 
 /* dW[Cout][3][3][Cin] (fp32) += sum_p dz[p][co] * x[p + (r-1,s-1)][ci]; dz, x bf16 NHWC.  Both GEMM
  * operands are MN-major (pixels are the reduction dimension); split-K with vector atomics.

@@ -66,3 +66,54 @@ def test_conv3x3_wgrad_matches_fp32(n, h, cin, cout):
     assert _rel_err(dw, want) < 1e-4
     tc.conv3x3_wgrad_nhwc(dz, x, dw)          # accumulates
     assert _rel_err(dw, 2 * want) < 1e-4
+
+
+def test_pool_and_relu_bwd_kernels():
+    y = torch.relu(torch.randn(6, 8, 8, 64, device=DEV)).bfloat16()
+    for k in (2, 4):
+        want = F.max_pool2d(y.float().permute(0, 3, 1, 2), k).permute(0, 2, 3, 1)
+        got = tc.maxpool_nhwc(y, k)
+        assert torch.equal(got.float(), want)
+        dp = torch.randn_like(got)
+        yy = y.float().permute(0, 3, 1, 2).requires_grad_(True)
+        F.max_pool2d(yy, k).backward(dp.float().permute(0, 3, 1, 2))
+        want_dz = yy.grad.permute(0, 2, 3, 1) * (y.float() > 0)
+        got_dz = tc.maxpool_bwd_nhwc(y, dp, k, relu_mask=True)
+        assert _rel_err(got_dz, want_dz) < 1e-6
+    dy = torch.randn_like(y)
+    assert torch.equal(tc.relu_bwd(y, dy).float(), dy.float() * (y.float() > 0))
+    w = torch.randn(128, 3, 3, 64, device=DEV)
+    wd = tc.dgrad_weights(w)
+    assert torch.equal(wd.float(), w.flip(1, 2).permute(3, 1, 2, 0).bfloat16().float())
+
+
+def test_resnet9_native_matches_library_path():
+    from commefficient_b200 import models
+    from commefficient_b200.ops import nn as nnops
+    from commefficient_b200.utils import FlatParams
+    torch.manual_seed(0)
+    m = models.ResNet9(num_classes=10)
+    fp = FlatParams(m, DEV, layout="nhwc")
+    m._flat_params = fp
+    x = torch.randn(24, 3, 32, 32, device=DEV).contiguous(memory_format=torch.channels_last)
+    tgt = torch.randint(0, 10, (24,), device=DEV)
+
+    def run(native_on):
+        nnops.set_native(native_on)
+        try:
+            fp.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                logits = m(x).float()
+            loss = F.cross_entropy(logits, tgt, reduction="sum")
+            loss.backward()
+            return logits.detach().clone(), fp.grad.clone()
+        finally:
+            nnops.set_native(False)
+
+    l_lib, g_lib = run(False)
+    l_nat, g_nat = run(True)
+    assert _rel_err(l_nat, l_lib) < 3e-2
+    assert _rel_err(g_nat, g_lib) < 6e-2
+    # per-layer check so a wrong layer cannot hide in the norm of the others
+    for o, n_ in zip(fp.offsets, fp.sizes):
+        assert _rel_err(g_nat[o:o + n_], g_lib[o:o + n_]) < 0.12, o
