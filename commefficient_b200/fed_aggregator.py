@@ -32,6 +32,7 @@ from .ops import dense as dn
 from .ops import sketch as sk
 from .ops.topk import topk_sparse
 from .parallel.runtime import Runtime, init_runtime
+from .parallel.watchdog import RoundWatchdog, maybe_inject, parse_fault
 from .utils.flat import get_param_vec, set_param_vec  # noqa: F401  (re-exported, reference names)
 
 DEFAULT_NUM_CLIENTS = {"EMNIST": 3500, "PERSONA": 17568}
@@ -126,6 +127,8 @@ class FedModel:
         self.tracker = _DownloadTracker(self.fp.numel, self.num_clients, self.device,
                                         sparse=args.mode in ("sketch", "true_topk"))
         self.last_unique_clients = np.zeros(0, dtype=np.int64)
+        self.watchdog = RoundWatchdog(getattr(args, "watchdog_timeout", 0.0) or 0.0, self.rt.rank).start()
+        self._fault = parse_fault()
         _CURRENT = self
 
     # -- nn.Module-ish surface -------------------------------------------------------
@@ -138,6 +141,7 @@ class FedModel:
 
     def finalize(self):
         """End of training (the reference joins its worker processes here)."""
+        self.watchdog.stop()
         self.rt.barrier()
 
     def zero_grad(self):
@@ -213,7 +217,10 @@ class FedModel:
                 n = int(counts[p])
                 client_batches.append((int(cid), [t[lo:lo + n] for t in dev_cols]))
                 lo += n
+        self.watchdog.beat("clients", self.rounds + 1)
         local = self.worker.run_round(client_batches, fedavg_lr=self.fedavg_lr)
+        maybe_inject(self._fault, self.rt.rank, self.rounds + 1, self.worker.transmit)
+        self.watchdog.beat("reduce")
         if self.fused_reduce:
             self.reduce_pending = True
         else:
@@ -231,7 +238,9 @@ class FedModel:
             gathered = gathered[torch.from_numpy(perm).to(gathered.device)]
         else:
             gathered = local.float()
+        self.watchdog.beat("results")
         packed = torch.cat([gathered, dl.unsqueeze(1)], dim=1).cpu().numpy()   # the round's one D2H
+        self.watchdog.idle()
         n_res = args.num_results_train
         results = [packed[:, i].copy() for i in range(n_res)]
         download = torch.zeros(self.num_clients)

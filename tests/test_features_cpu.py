@@ -1,0 +1,174 @@
+"""CPU tests of the less-travelled features: resume sidecar, --topk_down, DP, fine-tuning,
+per-group learning rates, byte accounting, watchdog / fault injection."""
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+import pytest
+import torch
+
+from commefficient_b200 import models
+from commefficient_b200.cv_train import compute_loss_train, compute_loss_val
+from commefficient_b200.data_utils import synthetic_image_batch
+from commefficient_b200.fed_aggregator import FedModel, FedOptimizer, get_server_update
+from commefficient_b200.parallel.watchdog import RoundWatchdog, parse_fault
+from commefficient_b200.utils import make_args
+
+SMALL = {"prep": 4, "layer1": 8, "layer2": 8, "layer3": 8}
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _make(mode="sketch", model_cls=models.ResNet9, model_kw=None, **kw):
+    torch.manual_seed(0)
+    base = dict(mode=mode, num_workers=4, num_clients=16, local_batch_size=-1, k=200, num_cols=2000, num_rows=5,
+                num_blocks=4, device="cpu", dataset_name="CIFAR10", local_momentum=0.0, virtual_momentum=0.9,
+                error_type="virtual" if mode in ("sketch", "true_topk") else "none", watchdog_timeout=0.0)
+    base.update(kw)
+    args = make_args(**base)
+    model = model_cls(**(model_kw or dict(num_classes=10, channels=SMALL)))
+    fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+    opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+    for g in opt.param_groups:
+        g["lr"] = 0.05
+    return fed, opt, args
+
+
+def _round(fed, opt, step):
+    fed.train(True)
+    out = fed(synthetic_image_batch(4, 3, seed=step, first_client=(4 * step) % 12))
+    opt.step()
+    return out
+
+
+def test_resume_sidecar_reproduces_training(tmp_path):
+    fed, opt, _ = _make("sketch")
+    for s in range(2):
+        _round(fed, opt, s)
+    path = str(tmp_path / "state.fedstate.pt")
+    fed.save_fedstate(path, opt)
+    cont = [float(np.mean(_round(fed, opt, s)[0])) for s in (2, 3)]
+    w_end = fed.fp.flat.clone()
+    fed.rt.shutdown()
+
+    fed2, opt2, _ = _make("sketch")
+    fed2.load_fedstate(path, opt2)
+    again = [float(np.mean(_round(fed2, opt2, s)[0])) for s in (2, 3)]
+    assert again == pytest.approx(cont, rel=1e-6)
+    torch.testing.assert_close(fed2.fp.flat, w_end)
+
+
+def test_topk_down_keeps_stale_client_weights():
+    fed, opt, args = _make("uncompressed", do_topk_down=True, k=50)
+    _round(fed, opt, 0)
+    store = fed.worker.client_weights
+    assert sorted(store.touched()) == [0, 1, 2, 3]
+    w0 = store.get(0).clone()
+    _round(fed, opt, 3)                      # clients 0-3 again (12 % 12)
+    w1 = store.get(0)
+    changed = int((w1 != w0).sum())
+    assert 0 < changed <= 50                 # moved by at most k coordinates towards the server weights
+    assert int((w1 != fed.fp.flat).sum()) > 0
+
+
+def test_dp_worker_clip_and_noise_changes_update():
+    fed_a, opt_a, _ = _make("uncompressed")
+    fed_b, opt_b, _ = _make("uncompressed", do_dp=True, l2_norm_clip=0.01, noise_multiplier=0.0)
+    w_before = fed_a.fp.flat.clone()
+    _round(fed_a, opt_a, 0)
+    _round(fed_b, opt_b, 0)
+    step_a = (fed_a.fp.flat - w_before).norm()
+    step_b = (fed_b.fp.flat - w_before).norm()
+    # every client gradient is clipped to norm 0.01; the averaged step is far smaller than unclipped
+    assert step_b < 0.2 * step_a and step_b > 0
+
+
+def test_fixup_param_groups_lr_vector_in_flat_order():
+    torch.manual_seed(0)
+    args = make_args(mode="uncompressed", num_workers=2, num_clients=4, local_batch_size=-1, device="cpu",
+                     dataset_name="CIFAR10", local_momentum=0.0, watchdog_timeout=0.0)
+    model = models.FixupResNet18(num_classes=10)
+    named = list(model.named_parameters())
+    groups = [{"params": [p for n, p in named if "bias" in n], "lr": 0.1},
+              {"params": [p for n, p in named if "scale" in n], "lr": 0.1},
+              {"params": [p for n, p in named if "bias" not in n and "scale" not in n], "lr": 1.0}]
+    fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+    opt = FedOptimizer(torch.optim.SGD(groups, lr=1), args)
+    lr = opt.get_lr()
+    assert torch.is_tensor(lr) and lr.numel() == fed.fp.numel
+    for (name, p), off, n in zip(named, fed.fp.offsets, fed.fp.sizes):
+        want = 0.1 if ("bias" in name or "scale" in name) else 1.0
+        assert float(lr[off]) == pytest.approx(want) and float(lr[off + n - 1]) == pytest.approx(want), name
+
+
+def test_byte_accounting_sparse_and_dense():
+    fed, opt, args = _make("sketch")
+    out = _round(fed, opt, 0)
+    download, upload = out[-2], out[-1]
+    assert upload[:4].tolist() == [4.0 * 5 * 2000] * 4 and float(upload[4:].sum()) == 0
+    assert float(download.sum()) == 0                       # first round: everybody is up to date
+    out = _round(fed, opt, 1)                               # clients 4..7 never participated: need round-1 changes
+    d = out[-2]
+    assert all(0 < x <= 4.0 * args.k for x in d[4:8].tolist())
+    out = _round(fed, opt, 3)                               # clients 0..3: missed updates of rounds 1 and 2 (+their own)
+    assert all(x >= d[4] for x in out[-2][:4].tolist())
+    fed.rt.shutdown()
+    fed, opt, args = _make("uncompressed")
+    _round(fed, opt, 0)
+    out = _round(fed, opt, 1)
+    assert out[-2][4:8].tolist() == [4.0 * fed.fp.numel] * 4
+
+
+def test_get_server_update_functional_api_matches_reference_shapes():
+    args = make_args(mode="true_topk", error_type="virtual", k=3, local_momentum=0.0, virtual_momentum=0.5,
+                     device="cpu", watchdog_timeout=0.0)
+    args.grad_size = 10
+    g = torch.arange(10, dtype=torch.float32)
+    Vv, Ve = torch.zeros(10), torch.zeros(10)
+    upd, Vv2, Ve2 = get_server_update(g, Vv, Ve, args, 0.1)
+    assert upd.nonzero().view(-1).tolist() == [7, 8, 9]
+    torch.testing.assert_close(upd[7:], 0.1 * g[7:])
+    assert float(Ve2[7:].abs().sum()) == 0 and float(Vv2[7:].abs().sum()) == 0 and float(Ve2[:7].sum()) == 21
+
+
+def test_finetune_freezes_everything_but_the_new_head(tmp_path):
+    src = models.ResNet9(num_classes=100, channels=SMALL)
+    torch.save(src.state_dict(), str(tmp_path / "ResNet9.pt"))
+    m = models.ResNet9(num_classes=100, new_num_classes=10, channels=SMALL)
+    m.load_state_dict(torch.load(str(tmp_path / "ResNet9.pt")))
+    for p in m.parameters():
+        p.requires_grad = False
+    head = list(m.finetune_parameters())
+    assert len(head) == 1 and head[0].shape == (10, SMALL["layer3"])
+    assert [p.requires_grad for p in m.parameters()].count(True) == 1
+    assert m(torch.randn(2, 3, 32, 32)).shape == (2, 10)
+
+
+def test_watchdog_fires_and_parses_faults():
+    fired = []
+    wd = RoundWatchdog(0.2, rank=3, on_timeout=fired.append, poll_s=0.05).start()
+    wd.beat("clients", 7)
+    time.sleep(0.6)
+    wd.stop()
+    assert fired and "rank 3" in fired[0] and "round 7" in fired[0] and "clients" in fired[0]
+    assert parse_fault("hang:1:3") == ("hang", 1, 3) and parse_fault("") is None
+    with pytest.raises(ValueError):
+        parse_fault("boom:0:0")
+
+
+def test_hung_rank_is_detected_and_aborts_the_job(tmp_path):
+    script = tmp_path / "hang.py"
+    script.write_text(
+        "import sys; sys.path.insert(0, %r)\n"
+        "import torch\n"
+        "from tests.test_features_cpu import _make, _round\n"
+        "fed, opt, _ = _make('uncompressed', watchdog_timeout=1.0)\n"
+        "for s in range(5): _round(fed, opt, s)\n" % ROOT)
+    env = dict(os.environ, CEB_FAULT="hang:0:2")
+    t0 = time.time()
+    res = subprocess.run([sys.executable, str(script)], env=env, cwd=ROOT, stdout=subprocess.PIPE,
+                         stderr=subprocess.PIPE, text=True, timeout=120)
+    assert res.returncode == 86, res.stderr[-500:]
+    assert "no progress" in res.stderr and "round 2" in res.stderr
+    assert time.time() - t0 < 100
