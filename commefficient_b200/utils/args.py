@@ -128,6 +128,8 @@ _FLAGS = [
         _flag("flat_layout", "auto", str, choices=("auto", "reference", "nhwc"),
               help="coordinate order of conv weights in the flat buffer: reference = (out,in,kh,kw); "
                    "nhwc = (out,kh,kw,in), channels_last end to end (auto: nhwc on CUDA)"),
+        _flag("no_cuda_graphs", store_true=True,
+              help="do not capture the batched client forward/backward into a CUDA graph"),
         _flag("native_nn", store_true=True,
               help="route conv/linear through the hand-written tcgen05 kernels"),
     ]),
