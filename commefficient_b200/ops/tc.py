@@ -27,8 +27,10 @@ native.register_signatures({
                                    native.c_i32, native.c_i32, native.c_i32, native.c_i32, native.c_ptr],
                                   native.c_i32),
     "ceb_relu_bwd_bf16": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr], native.c_i32),
-    "ceb_conv3x3_wgrad_bf16_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32,
-                                     native.c_i32, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_im2col3x3_c3": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32, native.c_ptr],
+                         native.c_i32),
+    "ceb_gemm_bf16_mn_acc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
+                              native.c_i32, native.c_ptr], native.c_i32),
 })
 
 _OUT = {torch.bfloat16: 0, torch.float32: 1}
@@ -93,6 +95,34 @@ def maxpool_bwd_nhwc(y: torch.Tensor, dp: torch.Tensor, k: int, relu_mask: bool)
     return dz
 
 
+def gemm_mn_acc(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor) -> torch.Tensor:
+    """``c[M,N] (fp32) += a[K,M].T @ b[K,N]`` (bf16 row-major operands; the reduction runs over rows)."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_contiguous() and b.is_contiguous()
+    assert c.dtype == torch.float32 and c.stride(1) == 1
+    K, M = a.shape
+    N = b.shape[1]
+    native.call("ceb_gemm_bf16_mn_acc", native.ptr(a), native.ptr(b), native.ptr(c), M, N, K, c.stride(0),
+                native.stream_ptr(a.device))
+    return c
+
+
+def im2col_c3(x_nhwc_f32: torch.Tensor) -> torch.Tensor:
+    """``[N*H*W, 64]`` bf16 im2col matrix (27 valid columns) of a 3-channel NHWC fp32 batch."""
+    n, h, w, c = x_nhwc_f32.shape
+    assert c == 3 and x_nhwc_f32.is_contiguous() and x_nhwc_f32.dtype == torch.float32
+    out = torch.empty((n * h * w, 64), dtype=torch.bfloat16, device=x_nhwc_f32.device)
+    native.call("ceb_im2col3x3_c3", native.ptr(x_nhwc_f32), native.ptr(out), n, h, w, native.stream_ptr(out.device))
+    return out
+
+
+def _stem_weight_pad(w_krsc_f32: torch.Tensor) -> torch.Tensor:
+    """``[64][3][3][3]`` fp32 -> ``[64][64]`` bf16 (K-major B operand, columns 27.. zero)."""
+    cout = w_krsc_f32.shape[0]
+    pad = torch.zeros((cout, 64), dtype=torch.bfloat16, device=w_krsc_f32.device)
+    pad[:, :27] = w_krsc_f32.reshape(cout, 27)
+    return pad
+
+
 def relu_bwd(y: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
     dz = torch.empty_like(y)
     native.call("ceb_relu_bwd_bf16", native.ptr(y), native.ptr(dy), native.ptr(dz), y.numel(),
@@ -135,7 +165,7 @@ def resnet9_supported(model, x: torch.Tensor) -> bool:
     if n.prep.do_batchnorm:
         return False
     ch = n.channels
-    if any(ch[k] % 64 for k in ("prep", "layer1", "layer2", "layer3")):
+    if ch["prep"] != 64 or any(ch[k] % 64 for k in ("layer1", "layer2", "layer3")) or x.shape[1] != 3:
         return False
     fp = getattr(model, "_flat_params", None)
     return fp is not None and fp.layout == "nhwc"
@@ -144,8 +174,8 @@ def resnet9_supported(model, x: torch.Tensor) -> bool:
 class _ResNet9Fn(torch.autograd.Function):
     """Whole-network forward/backward of ResNet-9 (no BatchNorm) on the hand-written kernels:
     implicit-GEMM conv + fused ReLU (tcgen05), fused ReLU/max-pool backward, MN-major wgrad
-    accumulating straight into the flat fp32 gradient buffer.  The 3-channel stem and the
-    512 -> classes head are tiny and stay on library ops."""
+    accumulating straight into the flat fp32 gradient buffer, and the 3-channel stem lowered to
+    im2col + the same tensor-core GEMMs.  Only the 512 -> classes head (5 MFLOP) stays on library ops."""
 
     @staticmethod
     def forward(ctx, x, net, *weights):
@@ -153,9 +183,9 @@ class _ResNet9Fn(torch.autograd.Function):
         convs = [net.prep.conv, net.layer1.conv, net.res1.res1.conv, net.res1.res2.conv, net.layer2.conv,
                  net.layer3.conv, net.res3.res1.conv, net.res3.res2.conv]
         wb = [cast_bf16(_krsc(c.weight.data)) for c in convs[1:]]
-        xb = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-        w0 = convs[0].weight.data.to(torch.bfloat16)
-        a0 = F.relu(F.conv2d(xb, w0, padding=1)).permute(0, 2, 3, 1).contiguous()
+        xb = x.float().permute(0, 2, 3, 1).contiguous()           # NHWC fp32 (no copy for channels_last input)
+        col = im2col_c3(xb)                                       # [N*1024, 64] bf16
+        a0 = gemm_tn(col, _stem_weight_pad(_krsc(convs[0].weight.data)), relu=True).view(x.shape[0], 32, 32, -1)
         a1 = conv3x3_nhwc(a0, wb[0], relu=True)
         p1 = maxpool_nhwc(a1, 2)
         r1a = conv3x3_nhwc(p1, wb[1], relu=True)
@@ -171,18 +201,18 @@ class _ResNet9Fn(torch.autograd.Function):
         f = maxpool_nhwc(s3, 4).view(x.shape[0], -1)
         logits = (f.float() @ net.linear.weight.data.t()) * net.out_scale
         ctx.net = net
-        ctx.saved = (xb, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3, f)
+        ctx.saved = (col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3, f)
         return logits
 
     @staticmethod
     def backward(ctx, dlogits):
         net = ctx.net
-        xb, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3, f = ctx.saved
+        col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3, f = ctx.saved
         convs = [net.prep.conv, net.layer1.conv, net.res1.res1.conv, net.res1.res2.conv, net.layer2.conv,
                  net.layer3.conv, net.res3.res1.conv, net.res3.res2.conv]
         gw = [_krsc(c.weight.grad) for c in convs]                       # fp32 KRSC views of the flat gradient
         wd = [None] + [dgrad_weights(_krsc(c.weight.data)) for c in convs[1:]]
-        n = xb.shape[0]
+        n = a0.shape[0]
 
         dl = dlogits.float() * net.out_scale
         net.linear.weight.grad.add_(dl.t() @ f.float())
@@ -213,9 +243,9 @@ class _ResNet9Fn(torch.autograd.Function):
         conv3x3_wgrad_nhwc(dz, a0, gw[1])
         da0 = conv3x3_nhwc(dz, wd[1], relu_mask=a0)
 
-        # 3-channel stem: weight gradient through the library (0.4 % of the FLOPs)
-        g0 = torch.nn.grad.conv2d_weight(xb, convs[0].weight.shape, da0.permute(0, 3, 1, 2), padding=1)
-        convs[0].weight.grad.add_(g0.float())
+        g0 = torch.zeros((da0.shape[3], 64), dtype=torch.float32, device=da0.device)
+        gemm_mn_acc(da0.view(-1, da0.shape[3]), col, g0)
+        gw[0].view(da0.shape[3], 27).add_(g0[:, :27])
         return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 

@@ -196,3 +196,46 @@ CEB_API int ceb_relu_bwd_bf16(const void* y, const void* dy, void* dz, int64_t n
   CEB_CHECK_LAUNCH();
   return 0;
 }
+
+// ------------------------------------------------------------------ 3-channel stem (first layer)
+// K = 27 is too thin for an implicit-GEMM tile, so the stem is lowered explicitly: one pass writes
+// the im2col matrix A[pixel][64] (27 taps*channels, zero padded to one 128-byte swizzle row, fused
+// with the fp32 -> bf16 conversion of the input) and the stem then IS a tensor-core GEMM with
+// K = 64: forward  y = relu(A * W0pad^T)  (ceb_gemm_bf16_tn), weight gradient  dW0pad += dZ^T * A
+// (ceb_gemm_bf16_mn_acc).  8 threads per pixel, 8 columns each: a warp writes four full rows.
+//   x: [N,H,W,3] fp32 (channels_last view of the NCHW batch); column t = (r*3+s)*3 + ci.
+__global__ void __launch_bounds__(256)
+im2col3x3_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ A, int N, int H, int W) {
+  const int g = threadIdx.x & 7;
+  const int64_t npix = (int64_t)N * H * W;
+  const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 3);
+  for (int64_t p = (int64_t)blockIdx.x * (blockDim.x >> 3) + (threadIdx.x >> 3); p < npix; p += stride) {
+    const int wq = (int)(p % W);
+    const int hq = (int)((p / W) % H);
+    const int64_t nb = p / ((int64_t)W * H);
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int t = g * 8 + j;
+      float val = 0.f;
+      if (t < 27) {
+        const int tap = t / 3, ci = t - tap * 3;
+        const int hh = hq + tap / 3 - 1, wc = wq + tap % 3 - 1;
+        if (hh >= 0 && hh < H && wc >= 0 && wc < W) val = __ldg(x + ((nb * H + hh) * W + wc) * 3 + ci);
+      }
+      v[j] = val;
+    }
+    *reinterpret_cast<uint4*>(A + p * 64 + g * 8) = pack8(v);
+  }
+}
+
+// A[N*H*W][64] (bf16) = im2col of the 3x3 / pad 1 neighbourhoods of x[N,H,W,3] (fp32)
+CEB_API int ceb_im2col3x3_c3(const float* x_nhwc, void* A_bf16, int N, int H, int W, void* stream) {
+  CEB_REQUIRE(x_nhwc && A_bf16 && N > 0 && H > 0 && W > 0, "ceb_im2col3x3_c3: bad arguments");
+  const int64_t npix = (int64_t)N * H * W;
+  im2col3x3_c3_kernel<<<ceb_grid_for(npix * 8, 256, 8), 256, 0, (cudaStream_t)stream>>>(
+      x_nhwc, (__nv_bfloat16*)A_bf16, N, H, W);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}

@@ -28,6 +28,7 @@ struct WgParams {
   int k_per_cta;         // k-steps handled by one CTA
   int ci_tiles;
   int tile_h, tile_n;    // box geometry of a 64-pixel step (tile_w == W)
+  int ldw;               // row stride of dW (9*Cin for a convolution, ldc for a plain GEMM)
 };
 
 template <int BN>
@@ -44,7 +45,10 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-template <int BN>
+// CONV = false turns the kernel into the plain "both operands MN-major" GEMM
+//   C[M][N] (fp32) += A[K][M]^T * B[K][N]        (A, B bf16 row-major, K = reduction)
+// used for linear-layer weight gradients (dW = dY^T X) and the im2col'd stem: one tap, 2-D B.
+template <int BN, bool CONV>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constant__ CUtensorMap tmapX, WgParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -59,13 +63,14 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   // blockIdx.x = ((co_tile * 3 + r) * ci_tiles + ci_tile), blockIdx.y = split
+  constexpr int TAPS = CONV ? 3 : 1;
   const int ci_tile = blockIdx.x % p.ci_tiles;
-  const int r = (blockIdx.x / p.ci_tiles) % 3;
-  const int co_tile = blockIdx.x / (p.ci_tiles * 3);
+  const int r = CONV ? (blockIdx.x / p.ci_tiles) % 3 : 0;
+  const int co_tile = CONV ? blockIdx.x / (p.ci_tiles * 3) : blockIdx.x / p.ci_tiles;
   const int ks_begin = blockIdx.y * p.k_per_cta;
   const int ks_end = min(ks_begin + p.k_per_cta, p.k_steps_total);
   const int n_steps = ks_end - ks_begin;
-  constexpr int TMEM_COLS = (3 * BN <= 256) ? 256 : 512;
+  constexpr int TMEM_COLS = (TAPS * BN <= 128) ? 128 : ((TAPS * BN <= 256) ? 256 : 512);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmapDZ);
@@ -93,20 +98,26 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
           mbar_wait(empty_bar + s, phase ^ 1);
           uint8_t* a_dst = smem + s * L::kStageBytes;
           uint8_t* b_dst = a_dst + L::kABytes;
-          mbar_expect_tx(full_bar + s, L::kStageBytes);
+          mbar_expect_tx(full_bar + s, L::kABytes + TAPS * (BN / 64) * L::kChunk);
           const int pix0 = (ks_begin + i) * WG_KPIX;
           // dZ: 2-D [pixels][Cout]: two 64-channel chunks
           tma_load_2d(a_dst, &tmapDZ, full_bar + s, co_tile * WG_M, pix0);
           tma_load_2d(a_dst + L::kChunk, &tmapDZ, full_bar + s, co_tile * WG_M + 64, pix0);
           // X: 4-D [N][H][W][Cin], shifted by (r-1, s-1)
-          const int n0 = pix0 / hw;
-          const int h0 = (pix0 - n0 * hw) / p.W;
+          if (CONV) {
+            const int n0 = pix0 / hw;
+            const int h0 = (pix0 - n0 * hw) / p.W;
 #pragma unroll
-          for (int sft = 0; sft < 3; ++sft)
+            for (int sft = 0; sft < 3; ++sft)
+#pragma unroll
+              for (int ch = 0; ch < BN / 64; ++ch)
+                tma_load_4d(b_dst + (sft * (BN / 64) + ch) * L::kChunk, &tmapX, full_bar + s,
+                            ci_tile * BN + ch * 64, sft - 1, h0 + r - 1, n0);
+          } else {
 #pragma unroll
             for (int ch = 0; ch < BN / 64; ++ch)
-              tma_load_4d(b_dst + (sft * (BN / 64) + ch) * L::kChunk, &tmapX, full_bar + s,
-                          ci_tile * BN + ch * 64, sft - 1, h0 + r - 1, n0);
+              tma_load_2d(b_dst + ch * L::kChunk, &tmapX, full_bar + s, ci_tile * BN + ch * 64, pix0);
+          }
         }
       }
     } else if (warp == 1) {
@@ -120,7 +131,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
           const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
           const uint32_t b_addr = a_addr + L::kABytes;
 #pragma unroll
-          for (int sft = 0; sft < 3; ++sft) {
+          for (int sft = 0; sft < TAPS; ++sft) {
 #pragma unroll
             for (int k = 0; k < WG_KPIX / 16; ++k) {
               // 16 pixels = 16 rows of 128 B; MN chunks (64 channels) are L::kChunk apart
@@ -139,16 +150,16 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
       const int co = co_tile * WG_M + q * 32 + lane;
-      const int ldw = 9 * p.Cin;
+      const int ldw = p.ldw;
 #pragma unroll 1
-      for (int sft = 0; sft < 3; ++sft) {
+      for (int sft = 0; sft < TAPS; ++sft) {
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
           float v[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + sft * BN + c * 32, v);
           const int ci0 = ci_tile * BN + c * 32;
           if (co < p.Cout && ci0 < p.Cin) {
-            float* dst = p.dW + (int64_t)co * ldw + (r * 3 + sft) * p.Cin + ci0;
+            float* dst = p.dW + (int64_t)co * ldw + (CONV ? (r * 3 + sft) * p.Cin : 0) + ci0;
 #pragma unroll
             for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
           }
@@ -164,16 +175,16 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
   }
 }
 
-template <int BN>
+template <int BN, bool CONV>
 static int launch_wgrad(const CUtensorMap& tdz, const CUtensorMap& tx, WgParams p, int co_tiles, int split, cudaStream_t st) {
   using L = WgSmem<BN>;
   static bool configured = false;
   if (!configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel<BN, CONV>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
-  dim3 grid((unsigned)(co_tiles * 3 * p.ci_tiles), (unsigned)split, 1);
-  tc_wgrad_kernel<BN><<<grid, WG_THREADS, L::kTotal, st>>>(tdz, tx, p);
+  dim3 grid((unsigned)(co_tiles * (CONV ? 3 : 1) * p.ci_tiles), (unsigned)split, 1);
+  tc_wgrad_kernel<BN, CONV><<<grid, WG_THREADS, L::kTotal, st>>>(tdz, tx, p);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -209,7 +220,7 @@ CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW
   p.dW = dW; p.Cout = Cout; p.Cin = Cin; p.H = H; p.W = W;
   p.k_steps_total = (int)ceb_cdiv(npix, WG_KPIX);
   p.ci_tiles = Cin / bn;
-  p.tile_h = tile_h; p.tile_n = tile_n;
+  p.tile_h = tile_h; p.tile_n = tile_n; p.ldw = 9 * Cin;
   const int co_tiles = (int)ceb_cdiv(Cout, WG_M);
   const int base_ctas = co_tiles * 3 * p.ci_tiles;
   int split = (int)ceb_cdiv(ceb_num_sms(), base_ctas);
@@ -217,6 +228,32 @@ CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW
   if (split < 1) split = 1;
   p.k_per_cta = (int)ceb_cdiv(p.k_steps_total, split);
   split = (int)ceb_cdiv(p.k_steps_total, p.k_per_cta);
-  if (bn == 128) return launch_wgrad<128>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
-  return launch_wgrad<64>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
+  if (bn == 128) return launch_wgrad<128, true>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
+  return launch_wgrad<64, true>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
+}
+
+// C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A, B bf16 row-major.  M % 64 == N % 64 == 0.
+CEB_API int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, int N, int K, int ldc, void* stream) {
+  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_mn_acc: bad arguments");
+  CEB_REQUIRE(M % 64 == 0 && N % 64 == 0 && ldc % 4 == 0, "ceb_gemm_bf16_mn_acc: M, N must be multiples of 64 (M=%d N=%d)", M, N);
+  CUtensorMap ta, tb;
+  uint64_t da[2] = {(uint64_t)M, (uint64_t)K}, sa[1] = {(uint64_t)M * 2};
+  uint32_t ba[2] = {64, WG_KPIX};
+  if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
+  uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)N * 2};
+  if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, ba)) return e;
+  const int bn = (N % 128 == 0) ? 128 : 64;
+  WgParams p{};
+  p.dW = C; p.Cout = M; p.Cin = N; p.H = 1; p.W = 1; p.ldw = ldc;
+  p.k_steps_total = (int)ceb_cdiv(K, WG_KPIX);
+  p.ci_tiles = N / bn;
+  const int co_tiles = (int)ceb_cdiv(M, WG_M);
+  const int base_ctas = co_tiles * p.ci_tiles;
+  int split = (int)ceb_cdiv(ceb_num_sms(), base_ctas);
+  if (split > p.k_steps_total) split = p.k_steps_total;
+  if (split < 1) split = 1;
+  p.k_per_cta = (int)ceb_cdiv(p.k_steps_total, split);
+  split = (int)ceb_cdiv(p.k_steps_total, p.k_per_cta);
+  if (bn == 128) return launch_wgrad<128, false>(ta, tb, p, co_tiles, split, (cudaStream_t)stream);
+  return launch_wgrad<64, false>(ta, tb, p, co_tiles, split, (cudaStream_t)stream);
 }

@@ -146,7 +146,14 @@ int ceb_maxpool_nhwc_bf16(const void* y, void* out, int N, int H, int W, int C, 
 int ceb_maxpool_bwd_nhwc_bf16(const void* y, const void* dp, void* dz, int N, int H, int W, int C, int k,
                               int relu_mask, void* stream);
 int ceb_relu_bwd_bf16(const void* y, const void* dy, void* dz, int64_t n, void* stream);
-
+/* 3-input-channel stem (reference: the `prep` layer, models/resnet9.py:85): K = 27 is too thin for an
+ * implicit-GEMM tile, so it is lowered explicitly.  A[N*H*W][64] (bf16) = im2col of x[N,H,W,3]
+ * (fp32), column (r*3+s)*3+ci, zero padded to 64; forward = ceb_gemm_bf16_tn(A, W0pad), weight
+ * gradient = ceb_gemm_bf16_mn_acc(dZ, A). */
+int ceb_im2col3x3_c3(const float* x_nhwc, void* A_bf16, int N, int H, int W, void* stream);
+/* C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A, B bf16 row-major ("both operands
+ * MN-major": linear-layer weight gradients dW = dY^T X).  M % 64 == N % 64 == 0; split-K. */
+int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, int N, int K, int ldc, void* stream);
 /* dW[Cout][3][3][Cin] (fp32) += sum_p dz[p][co] * x[p + (r-1,s-1)][ci]; dz, x bf16 NHWC.  Both GEMM
  * operands are MN-major (pixels are the reduction dimension); split-K with vector atomics.
  * Cin % 64 == 0, Cout % 64 == 0, W divides 64. */
