@@ -180,13 +180,13 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
-        if (p.mask && m < p.M) {
+        const bool full = (n0 + 32 <= p.N);
+        if (p.mask && m < p.M && !(p.out_fp32 == 0 && full)) {   // (the bf16 fast path masks while storing)
           const __nv_bfloat16* mk = (const __nv_bfloat16*)p.mask + (int64_t)m * p.ldc + n0;
 #pragma unroll
           for (int j = 0; j < 32; ++j)
             if (n0 + j < p.N && !(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
         }
-        const bool full = (n0 + 32 <= p.N);
         if (p.out_fp32 == 0 && full) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
@@ -203,7 +203,20 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
               uint4 pk;
               pk.x = stage[r * 17 + w4]; pk.y = stage[r * 17 + w4 + 1];
               pk.z = stage[r * 17 + w4 + 2]; pk.w = stage[r * 17 + w4 + 3];
-              *(uint4*)((__nv_bfloat16*)p.C + (int64_t)(row0 + r) * p.ldc + n0 + w4 * 2) = pk;
+              const int64_t off = (int64_t)(row0 + r) * p.ldc + n0 + w4 * 2;
+              if (p.mask) {
+                // ReLU backward: keep a gradient only where the forward activation was positive
+                // (bf16 > 0  <=>  sign bit clear and magnitude bits non-zero); same coalesced
+                // 16-byte access pattern as the store
+                const uint4 mk = __ldg((const uint4*)((const __nv_bfloat16*)p.mask + off));
+                auto keep = [](uint32_t m2, uint32_t val) {
+                  const uint32_t lo = ((m2 & 0x8000u) == 0u && (m2 & 0x7fffu) != 0u) ? 0x0000ffffu : 0u;
+                  const uint32_t hi = ((m2 & 0x80000000u) == 0u && (m2 & 0x7fff0000u) != 0u) ? 0xffff0000u : 0u;
+                  return val & (lo | hi);
+                };
+                pk.x = keep(mk.x, pk.x); pk.y = keep(mk.y, pk.y); pk.z = keep(mk.z, pk.z); pk.w = keep(mk.w, pk.w);
+              }
+              *(uint4*)((__nv_bfloat16*)p.C + off) = pk;
             }
           }
           __syncwarp();
