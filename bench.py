@@ -43,7 +43,8 @@ def parse():
     ap.add_argument("--model", default="ResNet9")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--backend", default="auto")
-    ap.add_argument("--native_nn", action="store_true")
+    ap.add_argument("--no_native_nn", action="store_true",
+                    help="run conv/linear layers on cuDNN/cuBLAS instead of the hand-written tcgen05 kernels")
     ap.add_argument("--clients_per_gpu", type=int, default=CLIENTS_PER_GPU)
     ap.add_argument("--phases", action="store_true", help="also print a per-phase breakdown to stderr")
     ap.add_argument("--profile", action="store_true",
@@ -192,12 +193,11 @@ def run_ours(cfg):
     args = make_args(mode=cfg.mode, error_type="virtual" if cfg.mode in ("sketch", "true_topk") else "none",
                      local_momentum=0.0, virtual_momentum=0.9, num_workers=clients, num_clients=NUM_CLIENTS,
                      local_batch_size=-1, num_epochs=1.0, dataset_name="CIFAR10", device="cuda",
-                     precision=cfg.precision, backend=cfg.backend, model=cfg.model)
+                     precision=cfg.precision, backend=cfg.backend, model=cfg.model,
+                     no_native_nn=cfg.no_native_nn)
     rt = init_runtime(args)
     torch.manual_seed(args.seed)
     torch.backends.cudnn.benchmark = True
-    if cfg.native_nn:
-        nnops.set_native(True)
     model = getattr(models, cfg.model)(num_classes=10)
     fed = FedModel(model, compute_loss_train, args, compute_loss_val)
     opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
@@ -269,7 +269,7 @@ def run_ours(cfg):
                        "k": args.k, "global_batch": clients * IMAGES_PER_CLIENT, "clients_per_round": clients,
                        "images_per_client": IMAGES_PER_CLIENT, "seq_len": None,
                        "parallelism": "dp%d" % cfg.gpus, "backend": rt.backend,
-                       "client_batching": fed.worker.can_batch_clients(), "native_nn": bool(cfg.native_nn),
+                       "client_batching": fed.worker.can_batch_clients(), "native_nn": nnops.native_enabled(),
                        "l2": "weights+grads+sketch+activations (>300 MB/round) exceed the 126 MB L2; "
                              "%d distinct input batches rotate" % n_distinct},
             "e2e": {"value": e2e, "unit": "clients/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,

@@ -255,9 +255,6 @@ def main(argv=None):
     train_loader, test_loader = get_data_loaders(args, rt.rank)
     if args.num_clients is None:
         args.num_clients = train_loader.dataset.num_clients
-    if getattr(args, "native_nn", False):
-        from .ops import nn as nnops
-        nnops.set_native(True)
     base_opt = torch.optim.SGD(groups, lr=1)
     fed_model = FedModel(model, compute_loss_train, args, compute_loss_val)
     opt = FedOptimizer(base_opt, args)

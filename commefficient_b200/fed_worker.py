@@ -260,6 +260,9 @@ class ClientWorker:
         self._ps_copy = None
         self._graphs = {}
         self.has_bn = _has_batchnorm(model)
+        # tensor-core layers: hand-written tcgen05 kernels on CUDA unless switched off
+        from .ops import nn as nnops
+        nnops.set_native(self.device.type == "cuda" and not getattr(args, "no_native_nn", False))
         self.last_clients: List[int] = []
 
     def _prep(self, cols: Sequence[torch.Tensor]) -> List[torch.Tensor]:

@@ -130,8 +130,8 @@ _FLAGS = [
                    "nhwc = (out,kh,kw,in), channels_last end to end (auto: nhwc on CUDA)"),
         _flag("no_cuda_graphs", store_true=True,
               help="do not capture the batched client forward/backward into a CUDA graph"),
-        _flag("native_nn", store_true=True,
-              help="route conv/linear through the hand-written tcgen05 kernels"),
+        _flag("no_native_nn", store_true=True,
+              help="keep conv/linear layers on cuDNN/cuBLAS instead of the hand-written tcgen05 kernels"),
     ]),
 ]
 

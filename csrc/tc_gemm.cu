@@ -12,6 +12,7 @@
 // Replaces the cuDNN / cuBLAS calls behind the reference's nn.Conv2d / nn.Linear layers
 // (/root/reference/CommEfficient/models/resnet9.py:36-37, fixup_resnet18.py:144-154).
 #include "tc_common.cuh"
+#include <cstdlib>
 
 using namespace tc;
 
@@ -39,15 +40,26 @@ struct TcParams {
   int conv;
   int H, W, cin_steps;   // cin_steps = Cin / 64
   int tile_h;            // rows of the image covered by one M tile (tile_w == W)
+  int halo_bytes;        // MODE 1: bytes of one activation halo box
 };
 
-template <int BN>
+// MODE 0: generic tile (GEMM, or convolution with one TMA box per filter tap).
+// MODE 1: "halo" convolution for wide feature maps (W = 16 or 32, Cout tile <= 128): the CTA owns
+//   256 output pixels (two 128-row accumulators) and, per (horizontal tap s, 64-channel chunk),
+//   loads ONE activation box that is two image rows taller than the tile.  The three vertical taps
+//   r = 0,1,2 then read the same shared-memory box at row offsets r*W*128 B -- a multiple of the
+//   1024-byte swizzle atom, so the UMMA descriptor stays canonical -- and both accumulators share
+//   the three weight tiles.  Shared-memory fill per output pixel drops ~2.2x against MODE 0
+//   (which is bound by L2 -> SM operand traffic on these layers, see profiles/).
+template <int BN, int MODE>
 struct SmemLayout {
-  static constexpr int kStages = StagesFor<BN>::value;
-  static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStages = MODE == 1 ? (BN <= 64 ? 3 : 2) : StagesFor<BN>::value;
+  static constexpr int kABytes = MODE == 1 ? 40960 : BM * BK * 2;     // halo box: (256/W + 2) rows x W x 128 B <= 40 KB
+  static constexpr int kBBytes = (MODE == 1 ? 3 : 1) * BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTotal = kStages * kStageBytes + kEpiStageBytes + 1024 /* align */ + 256 /* barriers */;
+  static constexpr int kSubTiles = MODE == 1 ? 2 : 1;
+  static constexpr int kTmemCols = 2 * kSubTiles * BN;
 };
 
 // Persistent: grid = min(#tiles, #SMs).  Tiles are walked M-fastest so CTAs running at the same
@@ -55,12 +67,14 @@ struct SmemLayout {
 // columns): the epilogue warps drain tile i while the MMA thread already accumulates tile i+1,
 // and the TMA producer runs ahead across tile boundaries, so operand latency is hidden even
 // for short K loops (3x3 conv with 64 input channels has only 9 k-steps).
-template <int BN>
+template <int BN, int MODE>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, TcParams p) {
   extern __shared__ uint8_t smem_raw[];
-  using L = SmemLayout<BN>;
+  using L = SmemLayout<BN, MODE>;
   constexpr int kStages = L::kStages;
+  constexpr int SUBS = L::kSubTiles;
+  constexpr int BMT = BM * SUBS;                       // output rows per CTA tile
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B needs 1024 B
   uint8_t* epi_smem = smem + kStages * L::kStageBytes;
   uint64_t* full_bar = (uint64_t*)(epi_smem + kEpiStageBytes);
@@ -86,7 +100,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     }
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
+  if (warp == 1) tmem_alloc<L::kTmemCols>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -100,7 +114,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
         int n0 = 0, h0 = 0;
         if (p.conv) {
-          const int pix0 = m_tile * BM;
+          const int pix0 = m_tile * BMT;
           const int hw = p.H * p.W;
           n0 = pix0 / hw;
           h0 = (pix0 - n0 * hw) / p.W;
@@ -111,16 +125,28 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           mbar_wait(empty_bar + s, phase ^ 1);
           uint8_t* a_dst = smem + s * L::kStageBytes;
           uint8_t* b_dst = a_dst + L::kABytes;
-          mbar_expect_tx(full_bar + s, L::kStageBytes);
-          if (p.conv) {
-            const int tap = ks / p.cin_steps;
-            const int c0 = (ks - tap * p.cin_steps) * BK;
-            const int r = tap / 3, sft = tap - r * 3;
-            tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 + r - 1, n0);
+          if (MODE == 1) {
+            // k-step = (horizontal tap sft, channel chunk c0): one halo box + the 3 weight tiles r = 0..2
+            const int sft = ks / p.cin_steps;
+            const int c0 = (ks - sft * p.cin_steps) * BK;
+            mbar_expect_tx(full_bar + s, (uint32_t)p.halo_bytes + L::kBBytes);
+            tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 - 1, n0);
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+              tma_load_2d(b_dst + r * (BN * BK * 2), &tmapB, full_bar + s,
+                          ((r * 3 + sft) * p.cin_steps) * BK + c0, n_tile * BN);
           } else {
-            tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BK, m_tile * BM);
+            mbar_expect_tx(full_bar + s, L::kStageBytes);
+            if (p.conv) {
+              const int tap = ks / p.cin_steps;
+              const int c0 = (ks - tap * p.cin_steps) * BK;
+              const int r = tap / 3, sft = tap - r * 3;
+              tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 + r - 1, n0);
+            } else {
+              tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BK, m_tile * BM);
+            }
+            tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BK, n_tile * BN);
           }
-          tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BK, n_tile * BN);
         }
       }
     }
@@ -132,7 +158,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       const int acc = local & 1;
       mbar_wait(tmem_empty_bar + acc, ((local >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
       tc_fence_after();
-      const uint32_t tmem_d = tmem_base + acc * BN;
+      const uint32_t tmem_d = tmem_base + acc * (SUBS * BN);
       for (int ks = 0; ks < p.k_steps; ++ks, ++it) {
         const int s = it % kStages;
         const uint32_t phase = (it / kStages) & 1;
@@ -141,11 +167,26 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         if (elect_one()) {
           const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
           const uint32_t b_addr = a_addr + L::kABytes;
+          if (MODE == 1) {
+            const uint32_t row_bytes = (uint32_t)p.W * 128u;          // one image row inside the halo box
+            const uint32_t sub_rows = (uint32_t)(BM / p.W);           // image rows per 128-pixel accumulator
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t da = smem_desc_sw128(a_addr + k * UMMA_K * 2, 16, 1024);
-            const uint64_t db = smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
-            umma_bf16(tmem_d, da, db, idesc, (ks | k) != 0);
+            for (int sub = 0; sub < 2; ++sub)
+#pragma unroll
+              for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int k = 0; k < BK / UMMA_K; ++k) {
+                  const uint64_t da = smem_desc_sw128(a_addr + (sub * sub_rows + r) * row_bytes + k * UMMA_K * 2, 16, 1024);
+                  const uint64_t db = smem_desc_sw128(b_addr + r * (BN * BK * 2) + k * UMMA_K * 2, 16, 1024);
+                  umma_bf16(tmem_d + sub * BN, da, db, idesc, (ks | r | k) != 0);
+                }
+          } else {
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t da = smem_desc_sw128(a_addr + k * UMMA_K * 2, 16, 1024);
+              const uint64_t db = smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
+              umma_bf16(tmem_d, da, db, idesc, (ks | k) != 0);
+            }
           }
           umma_commit(empty_bar + s);                     // frees this smem stage when the MMAs retire
           if (ks == p.k_steps - 1) umma_commit(tmem_full_bar + acc);
@@ -163,15 +204,16 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       const int acc = local & 1;
       mbar_wait(tmem_full_bar + acc, (local >> 1) & 1);
       tc_fence_after();
-      const int row0 = m_tile * BM + q * 32;              // first output row of this warp
-      const int m = row0 + lane;
       const int n_base = n_tile * BN;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int sc = 0; sc < SUBS * (BN / 32); ++sc) {
+        const int sub = sc / (BN / 32), c = sc - sub * (BN / 32);
+        const int row0 = m_tile * BMT + sub * BM + q * 32;   // first output row of this warp
+        const int m = row0 + lane;
         float v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c * 32, v);
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * (SUBS * BN) + sub * BN + c * 32, v);
         const int n0 = n_base + c * 32;
-        if (n0 >= p.N) break;
+        if (n0 >= p.N) continue;
         if (p.bias) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) if (n0 + j < p.N) v[j] += __ldg(p.bias + n0 + j);
@@ -249,7 +291,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<2 * BN>(tmem_base);
+    tmem_dealloc<L::kTmemCols>(tmem_base);
   }
 }
 
@@ -286,20 +328,20 @@ int ceb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint6
   return 0;
 }
 
-template <int BN>
+template <int BN, int MODE>
 static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
-  using L = SmemLayout<BN>;
+  using L = SmemLayout<BN, MODE>;
   static bool configured = false;
   if (!configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
   TcParams q = p;
-  q.m_tiles = (int)ceb_cdiv(p.M, BM);
+  q.m_tiles = (int)ceb_cdiv(p.M, BM * L::kSubTiles);
   q.n_tiles = (int)ceb_cdiv(p.N, BN);
   const int tiles = q.m_tiles * q.n_tiles;
   const int grid = tiles < ceb_num_sms() ? tiles : ceb_num_sms();
-  tc_tile_kernel<BN><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, q);
+  tc_tile_kernel<BN, MODE><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, q);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -307,13 +349,18 @@ static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcPar
 
 static int pick_bn(int N) { return N <= 64 ? 64 : (N <= 128 ? 128 : 256); }
 
-static int dispatch_tile(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
-  switch (bn) {
-    case 64: return launch_tile<64>(ta, tb, p, st);
-    case 128: return launch_tile<128>(ta, tb, p, st);
-    case 256: return launch_tile<256>(ta, tb, p, st);
+static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+  if (mode == 1) {
+    if (bn == 64) return launch_tile<64, 1>(ta, tb, p, st);
+    if (bn == 128) return launch_tile<128, 1>(ta, tb, p, st);
+  } else {
+    switch (bn) {
+      case 64: return launch_tile<64, 0>(ta, tb, p, st);
+      case 128: return launch_tile<128, 0>(ta, tb, p, st);
+      case 256: return launch_tile<256, 0>(ta, tb, p, st);
+    }
   }
-  CEB_REQUIRE(false, "unsupported N tile %d", bn);
+  CEB_REQUIRE(false, "unsupported tile configuration (N tile %d, mode %d)", bn, mode);
 }
 
 // C[M,N] = act(A[M,K] * B[N,K]^T + bias).  A, B bf16 row-major (K contiguous), K % 8 == 0,
@@ -333,7 +380,7 @@ CEB_API int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N
   TcParams p{};
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = N; p.k_steps = (int)ceb_cdiv(K, BK);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 0;
-  return dispatch_tile(bn, ta, tb, p, (cudaStream_t)stream);
+  return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream);
 }
 
 // y[N,H,W,Cout] = act(conv3x3_s1_p1(x[N,H,W,Cin], w[Cout,3,3,Cin])), all bf16 NHWC / KRSC.
@@ -353,17 +400,23 @@ CEB_API int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nim
     CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_bf16_nhwc: H=%d not a multiple of the %d-row tile", H, tile_h);
   }
   const int bn = pick_bn(Cout);
+  // halo mode: 256-pixel tiles that stay inside one image, weights tile <= 128 wide
+  static const bool force_v1 = getenv("CEB_CONV_V1") != nullptr;
+  const int rows256 = (W > 0 && 256 % W == 0) ? 256 / W : 0;
+  const bool halo = !force_v1 && bn <= 128 && (W == 16 || W == 32) && rows256 > 0 && rows256 <= H && H % rows256 == 0;
   CUtensorMap ta, tb;
   uint64_t da[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
   uint64_t sa[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
-  uint32_t ba[4] = {BK, (uint32_t)W, (uint32_t)tile_h, (uint32_t)tile_n};
+  uint32_t ba[4] = {BK, (uint32_t)W, (uint32_t)(halo ? rows256 + 2 : tile_h), (uint32_t)(halo ? 1 : tile_n)};
   if (int e = ceb_make_tmap_bf16(&ta, x, 4, da, sa, ba)) return e;
   const int K = 9 * Cin;
   uint64_t db[2] = {(uint64_t)K, (uint64_t)Cout}, sb[1] = {(uint64_t)K * 2};
   uint32_t bb[2] = {BK, (uint32_t)bn};
   if (int e = ceb_make_tmap_bf16(&tb, w, 2, db, sb, bb)) return e;
   TcParams p{};
-  p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout; p.k_steps = 9 * (Cin / BK);
+  p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout;
+  p.k_steps = (halo ? 3 : 9) * (Cin / BK);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = H; p.W = W; p.cin_steps = Cin / BK; p.tile_h = tile_h;
-  return dispatch_tile(bn, ta, tb, p, (cudaStream_t)stream);
+  p.halo_bytes = halo ? (rows256 + 2) * W * 128 : 0;
+  return dispatch_tile(bn, halo ? 1 : 0, ta, tb, p, (cudaStream_t)stream);
 }
