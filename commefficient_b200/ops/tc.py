@@ -16,6 +16,8 @@ from . import native
 native.register_signatures({
     "ceb_gemm_bf16_tn": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
                           native.c_ptr, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_gemm_bf16_nn": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
+                          native.c_ptr, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
     "ceb_conv3x3_bf16_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
                                native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
                                native.c_ptr, native.c_ptr], native.c_i32),
@@ -48,6 +50,18 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias=None, relu=False, out_dtype=t
     mode = 2 if accumulate else _OUT[out.dtype]
     native.call("ceb_gemm_bf16_tn", native.ptr(a), native.ptr(b), native.ptr(out), M, N, K, native.ptr(bias),
                 1 if relu else 0, mode, native.stream_ptr(a.device))
+    return out
+
+
+def gemm_nn(a: torch.Tensor, b: torch.Tensor, bias=None, relu=False, out_dtype=torch.bfloat16) -> torch.Tensor:
+    """``act(a @ b + bias)`` with a ``[M, K]``, b ``[K, N]`` contiguous bf16 CUDA tensors."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_contiguous() and b.is_contiguous()
+    M, K = a.shape
+    K2, N = b.shape
+    assert K == K2
+    out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    native.call("ceb_gemm_bf16_nn", native.ptr(a), native.ptr(b), native.ptr(out), M, N, K, native.ptr(bias),
+                1 if relu else 0, _OUT[out_dtype], native.stream_ptr(a.device))
     return out
 
 

@@ -21,48 +21,58 @@ CEB_API void ceb_reset_launch_count() { g_ceb_launches = 0; }
 CEB_API int ceb_version() { return 1; }
 CEB_API int64_t ceb_select_scratch_bytes() { return (int64_t)sizeof(CebSelectScratch); }
 
-// Final pass: write every entry above the threshold, plus exactly k3 entries
-// equal to it (first come first served -- which ties win is unspecified, as with
-// torch.topk).
+// Final pass: write every entry above the threshold, plus exactly k3 entries equal to it (first
+// come first served -- which ties win is unspecified, as with torch.topk).  Two sweeps over the
+// block's slice: count, reserve a contiguous output range with ONE global atomic per block, then
+// write (a single output counter hammered by every warp serialises at the L2).
 __global__ void __launch_bounds__(kSelThreads)
 sel_emit_kernel(const float* __restrict__ v, int64_t n, CebSelectScratch* __restrict__ s,
                 int32_t* __restrict__ out_idx, float* __restrict__ out_val, uint32_t k) {
+  __shared__ uint32_t blk_count, blk_base, blk_fill;
   const uint32_t T = (s->b1 << 19) | (s->b2 << 8) | s->b3;
   const uint32_t need = s->k3;
   const int lane = threadIdx.x & 31;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  const int64_t start = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  // warp-uniform trip count so the ballots below are well defined
-  const int64_t warp_start = start - lane;
-  for (int64_t base = warp_start; base < n; base += stride) {
-    int64_t i = base + lane;
+  // contiguous slice per block so both sweeps hit the same (L2-resident) data
+  const int64_t per_block = ((n + gridDim.x - 1) / gridDim.x + 31) & ~(int64_t)31;
+  const int64_t begin = (int64_t)blockIdx.x * per_block;
+  const int64_t end = begin + per_block < n ? begin + per_block : n;
+  if (threadIdx.x == 0) { blk_count = 0; blk_fill = 0; }
+  __syncthreads();
+  uint32_t mine = 0;
+  for (int64_t i = begin + threadIdx.x; i < end; i += blockDim.x) mine += abs_key(__ldg(v + i)) > T;
+  mine = __reduce_add_sync(0xffffffffu, mine);
+  if (lane == 0 && mine) atomicAdd(&blk_count, mine);
+  __syncthreads();
+  if (threadIdx.x == 0) blk_base = blk_count ? atomicAdd(&s->out_count, blk_count) : 0u;
+  __syncthreads();
+  const uint32_t base = blk_base;
+  for (int64_t i0 = begin + (threadIdx.x - lane); i0 < end; i0 += blockDim.x) {
+    const int64_t i = i0 + lane;
     float val = 0.f;
     uint32_t key = 0;
-    bool valid = i < n;
+    const bool valid = i < end;
     if (valid) {
       val = __ldg(v + i);
       key = abs_key(val);
     }
-    bool gt = valid && key > T;
-    bool eq = valid && key == T;
-    if (eq && *((volatile uint32_t*)&s->tie_taken) < need) {
-      // (the plain read keeps millions of zero-magnitude ties from hammering
-      //  one address once the quota is gone)
-      uint32_t ticket = atomicAdd(&s->tie_taken, 1u);
-      if (ticket < need) gt = true;
-    }
-    unsigned m = __ballot_sync(0xffffffffu, gt);
+    const bool gt = valid && key > T;
+    const unsigned m = __ballot_sync(0xffffffffu, gt);
     if (m) {
-      uint32_t basepos = 0;
-      int leader = __ffs(m) - 1;
-      if (lane == leader) basepos = atomicAdd(&s->out_count, (uint32_t)__popc(m));
-      basepos = __shfl_sync(0xffffffffu, basepos, leader);
+      uint32_t wbase = 0;
+      const int leader = __ffs(m) - 1;
+      if (lane == leader) wbase = atomicAdd(&blk_fill, (uint32_t)__popc(m));
+      wbase = __shfl_sync(0xffffffffu, wbase, leader);
       if (gt) {
-        uint32_t pos = basepos + __popc(m & ((1u << lane) - 1u));
-        if (pos < k) {
-          out_idx[pos] = (int32_t)i;
-          out_val[pos] = (key == 0u) ? 0.f : val;  // NaN (key 0) never leaks out
-        }
+        const uint32_t pos = base + wbase + __popc(m & ((1u << lane) - 1u));
+        if (pos < k) { out_idx[pos] = (int32_t)i; out_val[pos] = val; }
+      }
+    }
+    // ties at the threshold: few (or all zeros); each takes a ticket until the quota is gone
+    if (valid && key == T && *((volatile uint32_t*)&s->tie_taken) < need) {
+      const uint32_t ticket = atomicAdd(&s->tie_taken, 1u);
+      if (ticket < need) {
+        const uint32_t pos = atomicAdd(&s->out_count, 1u);
+        if (pos < k) { out_idx[pos] = (int32_t)i; out_val[pos] = (key == 0u) ? 0.f : val; }
       }
     }
   }

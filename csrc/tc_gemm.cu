@@ -67,7 +67,10 @@ struct SmemLayout {
 // columns): the epilogue warps drain tile i while the MMA thread already accumulates tile i+1,
 // and the TMA producer runs ahead across tile boundaries, so operand latency is hidden even
 // for short K loops (3x3 conv with 64 input channels has only 9 k-steps).
-template <int BN, int MODE>
+// BMAJ = 1: the B operand is "MN-major" in memory (B[K][N] row-major, e.g. GPT-2's Conv1D weights
+// [in][out] or W itself in a data-gradient GEMM dX = dY * W): it is staged as 64-column chunks
+// [64 k][64 n] and read by tcgen05.mma through an MN-major descriptor -- no transposed copy.
+template <int BN, int MODE, int BMAJ = 0>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, TcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -145,14 +148,20 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             } else {
               tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BK, m_tile * BM);
             }
-            tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BK, n_tile * BN);
+            if (BMAJ == 1) {
+#pragma unroll
+              for (int ch = 0; ch < BN / 64; ++ch)
+                tma_load_2d(b_dst + ch * (BK * 128), &tmapB, full_bar + s, n_tile * BN + ch * 64, ks * BK);
+            } else {
+              tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BK, n_tile * BN);
+            }
           }
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one elected thread) =====
-    constexpr uint32_t idesc = idesc_bf16(BM, BN, 0, 0);
+    constexpr uint32_t idesc = idesc_bf16(BM, BN, 0, BMAJ);
     uint32_t it = 0, local = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
       const int acc = local & 1;
@@ -184,7 +193,8 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k) {
               const uint64_t da = smem_desc_sw128(a_addr + k * UMMA_K * 2, 16, 1024);
-              const uint64_t db = smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
+              const uint64_t db = BMAJ == 1 ? smem_desc_sw128(b_addr + k * UMMA_K * 128, BK * 128, 1024)
+                                            : smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
               umma_bf16(tmem_d, da, db, idesc, (ks | k) != 0);
             }
           }
@@ -328,12 +338,12 @@ int ceb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint6
   return 0;
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, int BMAJ = 0>
 static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
   using L = SmemLayout<BN, MODE>;
   static bool configured = false;
   if (!configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN, MODE, BMAJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
   TcParams q = p;
@@ -341,7 +351,7 @@ static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcPar
   q.n_tiles = (int)ceb_cdiv(p.N, BN);
   const int tiles = q.m_tiles * q.n_tiles;
   const int grid = tiles < ceb_num_sms() ? tiles : ceb_num_sms();
-  tc_tile_kernel<BN, MODE><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, q);
+  tc_tile_kernel<BN, MODE, BMAJ><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, q);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -353,6 +363,12 @@ static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensor
   if (mode == 1) {
     if (bn == 64) return launch_tile<64, 1>(ta, tb, p, st);
     if (bn == 128) return launch_tile<128, 1>(ta, tb, p, st);
+  } else if (mode == 2) {      // GEMM with MN-major B
+    switch (bn) {
+      case 64: return launch_tile<64, 0, 1>(ta, tb, p, st);
+      case 128: return launch_tile<128, 0, 1>(ta, tb, p, st);
+      case 256: return launch_tile<256, 0, 1>(ta, tb, p, st);
+    }
   } else {
     switch (bn) {
       case 64: return launch_tile<64, 0>(ta, tb, p, st);
@@ -381,6 +397,26 @@ CEB_API int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = N; p.k_steps = (int)ceb_cdiv(K, BK);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 0;
   return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream);
+}
+
+// C[M,N] = act(A[M,K] * B[K,N] + bias): like ceb_gemm_bf16_tn but B is row-major [K][N]
+// (GPT-2 Conv1D weights; data gradients dX = dY * W).  K % 8 == 0, N % 8 == 0.
+CEB_API int ceb_gemm_bf16_nn(const void* A, const void* B, void* C, int M, int N, int K, const float* bias,
+                             int relu, int out_mode, void* stream) {
+  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_nn: bad arguments");
+  CEB_REQUIRE(K % 8 == 0 && N % 8 == 0, "ceb_gemm_bf16_nn: K and N must be multiples of 8 (K=%d N=%d)", K, N);
+  const int bn = pick_bn(N);
+  CUtensorMap ta, tb;
+  uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)K * 2};
+  uint32_t ba[2] = {BK, BM};
+  if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
+  uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)N * 2};
+  uint32_t bb[2] = {64, BK};
+  if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, bb)) return e;
+  TcParams p{};
+  p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = N; p.k_steps = (int)ceb_cdiv(K, BK);
+  p.relu = relu; p.out_fp32 = out_mode; p.conv = 0;
+  return dispatch_tile(bn, 2, ta, tb, p, (cudaStream_t)stream);
 }
 
 // y[N,H,W,Cout] = act(conv3x3_s1_p1(x[N,H,W,Cin], w[Cout,3,3,Cin])), all bf16 NHWC / KRSC.

@@ -129,6 +129,9 @@ int ceb_count_changed(const float* w, float* prev, uint8_t* mask, int64_t n, uns
 /* C[M,N] = act(A[M,K] * B[N,K]^T + bias); A, B row-major with K contiguous; K % 8 == N % 8 == 0. */
 int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, const float* bias,
                      int relu, int out_mode, void* stream);
+/* C[M,N] = act(A[M,K] * B[K,N] + bias): B row-major [K][N] ("MN-major" operand, read in place). */
+int ceb_gemm_bf16_nn(const void* A, const void* B, void* C, int M, int N, int K, const float* bias,
+                     int relu, int out_mode, void* stream);
 /* y[N,H,W,Cout] = act(conv3x3 stride 1 pad 1 (x[N,H,W,Cin], w[Cout,3,3,Cin]) + bias), NHWC / KRSC.
  * Implicit GEMM: the im2col tile of tap (r,s) is a shifted 4-D TMA box, padding = TMA zero fill.
  * Cin % 64 == 0, Cout % 8 == 0, W divides 128.

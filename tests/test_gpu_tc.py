@@ -130,3 +130,13 @@ def test_mn_major_gemm_and_stem_im2col():
     want = F.unfold(x.permute(0, 3, 1, 2), 3, padding=1)     # [N, ci*9 (ci-major), L]
     want = want.view(5, 3, 9, 1024).permute(0, 3, 2, 1).reshape(5 * 1024, 27)   # -> column = tap*3 + ci
     assert torch.equal(col[:, :27].float(), want.bfloat16().float()) and float(col[:, 27:].abs().sum()) == 0
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1000, 2304, 768), (300, 768, 3072), (77, 200, 72), (512, 64, 4608)])
+def test_gemm_nn_matches_fp32(M, N, K):
+    g = torch.Generator(device=DEV).manual_seed(M * 3 + N + K)
+    a = torch.randn(M, K, device=DEV, generator=g).bfloat16()
+    b = torch.randn(K, N, device=DEV, generator=g).bfloat16()
+    bias = torch.randn(N, device=DEV, generator=g)
+    got = tc.gemm_nn(a, b, bias=bias, out_dtype=torch.float32)
+    assert _rel_err(got, a.float() @ b.float() + bias) < 1e-5
