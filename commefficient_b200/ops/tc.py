@@ -156,11 +156,75 @@ def conv3x3_wgrad_nhwc(dz: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> t
 
 
 def conv_supported(x, weight, stride, padding) -> bool:
+    # individual conv hooks are not routed natively; ResNet-9 goes through resnet9_forward as a whole
     return False
+
+
+def _weight_storage(weight: torch.Tensor):
+    """``(storage [rows, cols] contiguous, transposed?)``: an ``nn.Linear`` weight ``[N, K]`` is its own
+    storage; a GPT-2 ``Conv1D`` passes ``weight.t()`` of an ``[K, N]`` parameter."""
+    if weight.is_contiguous():
+        return weight, False
+    if weight.t().is_contiguous():
+        return weight.t(), True
+    return None, False
 
 
 def linear_supported(x, weight) -> bool:
-    return False
+    if not (x.is_cuda and weight.dim() == 2 and x.shape[-1] == weight.shape[1]):
+        return False
+    n, k = weight.shape
+    store, _ = _weight_storage(weight)
+    return store is not None and n % 64 == 0 and k % 64 == 0
+
+
+class _LinearFn(torch.autograd.Function):
+    """``y = x W^T + b`` on the tcgen05 GEMMs: forward TN (or NN for Conv1D storage), data gradient
+    NN (or TN), weight gradient by the MN-major split-K GEMM accumulating in fp32 -- directly into
+    ``weight.grad`` when that already exists (the flat gradient buffer)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        store, transposed = _weight_storage(weight)
+        xb = x.reshape(-1, x.shape[-1]).to(torch.bfloat16).contiguous()
+        wb = cast_bf16(store) if store.dtype == torch.float32 else store.to(torch.bfloat16)
+        bf = bias.float().contiguous() if bias is not None else None
+        y = gemm_nn(xb, wb, bias=bf) if transposed else gemm_tn(xb, wb, bias=bf)
+        ctx.save_for_backward(xb, wb)
+        ctx.transposed = transposed
+        ctx.weight = weight
+        ctx.has_bias = bias is not None
+        ctx.x_shape = x.shape
+        ctx.x_dtype = x.dtype
+        return y.view(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        xb, wb = ctx.saved_tensors
+        weight, transposed = ctx.weight, ctx.transposed
+        dyb = dy.reshape(-1, dy.shape[-1]).to(torch.bfloat16).contiguous()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_tn(dyb, wb) if transposed else gemm_nn(dyb, wb)
+            dx = dx.view(ctx.x_shape).to(ctx.x_dtype)
+        dw = None
+        if ctx.needs_input_grad[1]:
+            param = weight._base if (transposed and weight._base is not None) else weight
+            target = param.grad if (isinstance(param, torch.nn.Parameter) and param.grad is not None
+                                    and param.grad.is_contiguous()) else None
+            acc = target if target is not None else torch.zeros_like(_weight_storage(weight)[0], dtype=torch.float32)
+            if transposed:
+                gemm_mn_acc(xb, dyb, acc)          # dW_storage[K, N] += X^T dY
+            else:
+                gemm_mn_acc(dyb, xb, acc)          # dW[N, K] += dY^T X
+            if target is None:
+                dw = acc.t() if transposed else acc
+        db = dy.reshape(-1, dy.shape[-1]).float().sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return dx, dw, db
+
+
+def linear(x, weight, bias=None):
+    return _LinearFn.apply(x, weight, bias)
 
 
 # ---------------------------------------------------------------------------- ResNet-9 on the native kernels

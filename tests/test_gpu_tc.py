@@ -140,3 +140,34 @@ def test_gemm_nn_matches_fp32(M, N, K):
     bias = torch.randn(N, device=DEV, generator=g)
     got = tc.gemm_nn(a, b, bias=bias, out_dtype=torch.float32)
     assert _rel_err(got, a.float() @ b.float() + bias) < 1e-5
+
+
+def test_gpt2_linears_native_match_library():
+    from commefficient_b200 import models
+    from commefficient_b200.ops import nn as nnops
+    from commefficient_b200.utils import FlatParams
+    torch.manual_seed(0)
+    cfg = models.GPT2Config(vocab_size=512, n_positions=64, n_ctx=64, n_embd=128, n_layer=2, n_head=4,
+                            resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0, summary_first_dropout=0.0)
+    m = models.GPT2DoubleHeadsModel(cfg)
+    fp = FlatParams(m, DEV)
+    m._flat_params = fp
+    ids = torch.randint(0, 512, (3, 2, 48), device=DEV)
+    mc_tok = torch.full((3, 2), 47, device=DEV)
+    mc_lab = torch.tensor([0, 1, 0], device=DEV)
+
+    def run(native_on):
+        nnops.set_native(native_on)
+        try:
+            fp.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                lm_loss, mc_loss, *_ = m(ids, token_type_ids=ids, mc_token_ids=mc_tok, lm_labels=ids, mc_labels=mc_lab)
+            (lm_loss + mc_loss).backward()
+            return float(lm_loss), float(mc_loss), fp.grad.clone()
+        finally:
+            nnops.set_native(False)
+
+    l0, c0, g0 = run(False)
+    l1, c1, g1 = run(True)
+    assert abs(l0 - l1) < 2e-2 and abs(c0 - c1) < 2e-2
+    assert _rel_err(g1, g0) < 0.08
