@@ -364,7 +364,14 @@ class ClientWorker:
         for lo in range(0, total, self.MAX_BATCHED_SAMPLES):
             chunk = [t[lo:lo + self.MAX_BATCHED_SAMPLES] for t in cat]
             with _autocast(a, self.device):
-                loss_vec, *metric_vecs = self.compute_loss_train.per_sample(self.model, chunk, a)
+                if getattr(self.compute_loss_train.per_sample, "needs_segments", False):
+                    # losses that are not a plain per-sample mean (e.g. mean over a client's tokens)
+                    # get the client index of every sample and return values v_s with
+                    # sum_{s in client i} v_s = n_i * loss_i
+                    loss_vec, *metric_vecs = self.compute_loss_train.per_sample(
+                        self.model, chunk, a, seg=seg[lo:lo + self.MAX_BATCHED_SAMPLES], num_segments=len(sizes))
+                else:
+                    loss_vec, *metric_vecs = self.compute_loss_train.per_sample(self.model, chunk, a)
             loss_vec.float().sum().backward()
             per_sample_cols.append(torch.stack([loss_vec.detach().float()] +
                                                [m.detach().float() for m in metric_vecs], dim=1))

@@ -64,6 +64,29 @@ def compute_loss_train(model, batch, args):
     return lm_loss * args.lm_coef + mc_loss * args.mc_coef,
 
 
+def _per_sample_train(model, batch, args, seg, num_segments):
+    """Per-sample values ``v_s`` whose sum over a client's samples is ``n_i * loss_i`` with
+    ``loss_i = lm_coef * (mean LM loss over the client's target tokens) + mc_coef * (mean MC loss)``
+    -- exactly what ``compute_loss_train`` returns for that client alone, so the worker can run all
+    of a rank's clients in one forward/backward."""
+    input_ids, mc_token_ids, lm_labels, mc_labels, token_type_ids = batch
+    lm_logits, mc_logits, *_ = model(input_ids, token_type_ids=token_type_ids, mc_token_ids=mc_token_ids)
+    B = input_ids.shape[0]
+    logits = lm_logits[..., :-1, :].reshape(-1, lm_logits.size(-1)).float()
+    labels = lm_labels[..., 1:].reshape(-1)
+    tok_loss = F.cross_entropy(logits, labels, ignore_index=-1, reduction="none").view(B, -1)
+    tok_cnt = (labels != -1).view(B, -1).sum(1).float()
+    n_i = torch.zeros(num_segments, device=seg.device).index_add_(0, seg, torch.ones_like(tok_cnt))
+    ntok_i = torch.zeros(num_segments, device=seg.device).index_add_(0, seg, tok_cnt).clamp_min(1.0)
+    lm_part = tok_loss.sum(1) * (n_i / ntok_i)[seg]
+    mc_part = F.cross_entropy(mc_logits.float(), mc_labels, reduction="none")
+    return lm_part * args.lm_coef + mc_part * args.mc_coef,
+
+
+_per_sample_train.needs_segments = True
+compute_loss_train.per_sample = _per_sample_train
+
+
 def add_special_tokens_(model, tokenizer):
     """Add the five dialogue tokens and grow the embedding matrix accordingly."""
     base = len(tokenizer.encoder)

@@ -43,3 +43,40 @@ def test_gpt2_driver_end_to_end(tmp_path, monkeypatch):
     assert out["val_ppl"] < 512 and 0.0 <= out["val_acc"] <= 1.0
     runs = os.listdir(tmp_path / "runs")
     assert runs, "save_pretrained did not write the run directory"
+
+
+def test_gpt2_client_batching_equals_per_client_rounds():
+    """One batched forward/backward over all clients == the per-client loop (loss values, weights)."""
+    import numpy as np
+    from commefficient_b200.fed_aggregator import FedModel, FedOptimizer
+    from commefficient_b200.gpt2_train import compute_loss_train, compute_loss_val
+    from commefficient_b200.utils import make_args
+
+    def run(no_batching):
+        torch.manual_seed(0)
+        cfg = models.GPT2Config(vocab_size=64, n_positions=32, n_ctx=32, n_embd=32, n_layer=1, n_head=2,
+                                resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0, summary_first_dropout=0.0)
+        model = models.GPT2DoubleHeadsModel(cfg)
+        args = make_args(mode="uncompressed", num_workers=3, num_clients=6, local_batch_size=2, device="cpu",
+                         dataset_name="PERSONA", local_momentum=0.0, num_results_train=1, weight_decay=0.0,
+                         no_client_batching=no_batching, watchdog_timeout=0.0)
+        fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+        opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+        opt.param_groups[0]["lr"] = 0.1
+        g = torch.Generator().manual_seed(3)
+        ids = torch.randint(0, 64, (6, 2, 12), generator=g)
+        labels = ids.clone()
+        labels[:, 0] = -1
+        labels[0, 1, :8] = -1                       # clients have different numbers of target tokens
+        batch = (torch.tensor([0, 0, 1, 1, 2, 2]), ids, torch.full((6, 2), 11), labels,
+                 torch.randint(0, 2, (6,), generator=g), ids)
+        out = fed(batch)
+        opt.step()
+        w = fed.fp.flat.clone()
+        fed.rt.shutdown()
+        return out[0], w
+
+    l_b, w_b = run(False)
+    l_c, w_c = run(True)
+    np.testing.assert_allclose(l_b, l_c, rtol=1e-5)
+    torch.testing.assert_close(w_b, w_c, rtol=1e-4, atol=1e-6)
