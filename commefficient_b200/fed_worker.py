@@ -343,13 +343,19 @@ class ClientWorker:
             for dst, src in zip(entry["static_in"], cat):
                 dst.copy_(src)
             torch.cuda.synchronize(self.device)
+            from .ops import native
+            before = native.launch_count()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
                 entry["results"] = self._batched_body(entry["static_in"], sizes, entry["seg"], entry["counts"])
             entry["graph"] = graph
+            entry["native_launches"] = native.launch_count() - before   # our kernels inside the graph
         for dst, src in zip(entry["static_in"], cat):
             dst.copy_(src, non_blocking=True)
         entry["graph"].replay()
+        if entry.get("native_launches"):
+            from .ops import native
+            native.add_launch_count(entry["native_launches"])
         return entry["results"]
 
     def _batched_body(self, cat, sizes, seg, counts=None):

@@ -35,6 +35,7 @@ _SIGNATURES = {
     "ceb_version": ([], c_i32),
     "ceb_launch_count": ([], c_u64),
     "ceb_reset_launch_count": ([], None),
+    "ceb_add_launch_count": ([c_u64], None),
     "ceb_select_scratch_bytes": ([], c_i64),
     "ceb_topk_select": ([c_ptr, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr], c_i32),
     "ceb_sketch_accumulate": ([c_ptr, c_ptr, c_f32, c_f32, c_i64, c_ptr, c_i64, c_ptr, c_i32, c_ptr,
@@ -148,6 +149,10 @@ def call(name: str, *args):
 
 def launch_count() -> int:
     return int(lib().ceb_launch_count())
+
+
+def add_launch_count(n: int) -> None:
+    lib().ceb_add_launch_count(int(n))
 
 
 def reset_launch_count() -> None:

@@ -18,6 +18,9 @@ void ceb_set_error(const char* fmt, ...) {
 CEB_API const char* ceb_last_error() { return g_ceb_error.c_str(); }
 CEB_API unsigned long long ceb_launch_count() { return g_ceb_launches; }
 CEB_API void ceb_reset_launch_count() { g_ceb_launches = 0; }
+// Kernels replayed from a captured CUDA graph are not launched through this library again;
+// the caller that replays the graph credits them here (n = launches recorded at capture).
+CEB_API void ceb_add_launch_count(unsigned long long n) { g_ceb_launches += n; }
 CEB_API int ceb_version() { return 1; }
 CEB_API int64_t ceb_select_scratch_bytes() { return (int64_t)sizeof(CebSelectScratch); }
 

@@ -24,8 +24,9 @@ constexpr int UMMA_K = 16;
 // Operand ring depth: as many 16 KB + BN*128 B stages as fit beside the epilogue staging area
 // (~200 KB per SM, one persistent CTA per SM).
 template <int BN> struct StagesFor { static constexpr int value = BN <= 64 ? 8 : (BN <= 128 ? 6 : 4); };
-constexpr int kTcThreads = 192; // warp 0: TMA, warp 1: MMA + TMEM alloc, warps 2-5: epilogue
-constexpr int kEpiStageBytes = 4 * 32 * 17 * 4;   // per epilogue warp: [32 rows][16 words + 1 pad]
+constexpr int kEpiWarps = 8;     // two per TMEM lane quarter, each draining half of the tile's columns
+constexpr int kTcThreads = 64 + 32 * kEpiWarps; // warp 0: TMA, warp 1: MMA + TMEM alloc, warps 2..: epilogue
+constexpr int kEpiStageBytes = kEpiWarps * 32 * 17 * 4;   // per epilogue warp: [32 rows][16 words + 1 pad]
 
 struct TcParams {
   void* C;               // output [M][ldc]
@@ -99,7 +100,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tmem_full_bar + a, 1);
-      mbar_init(tmem_empty_bar + a, 4);               // one arrive per epilogue warp
+      mbar_init(tmem_empty_bar + a, kEpiWarps);       // one arrive per epilogue warp
     }
     mbar_fence_init();
   }
@@ -215,8 +216,10 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       mbar_wait(tmem_full_bar + acc, (local >> 1) & 1);
       tc_fence_after();
       const int n_base = n_tile * BN;
+      constexpr int kChunks = SUBS * (BN / 32);            // 32-column chunks per tile, split over the two warps of a quarter
+      const int half = (warp - 2) >> 2;
 #pragma unroll 1
-      for (int sc = 0; sc < SUBS * (BN / 32); ++sc) {
+      for (int sc = half * (kChunks / 2); sc < (half + 1) * (kChunks / 2); ++sc) {
         const int sub = sc / (BN / 32), c = sc - sub * (BN / 32);
         const int row0 = m_tile * BMT + sub * BM + q * 32;   // first output row of this warp
         const int m = row0 + lane;

@@ -30,6 +30,8 @@ int ceb_version(void);
 /* Kernel launches issued by this library since the last reset (host counter). */
 unsigned long long ceb_launch_count(void);
 void ceb_reset_launch_count(void);
+/* Credit n launches replayed from a captured CUDA graph (they bypass the library's host code). */
+void ceb_add_launch_count(unsigned long long n);
 
 /* ---- exact top-k by magnitude (reference: utils.py:232-252 `_topk`) ---------- */
 /* Bytes of zero-initialisable scratch every top-k style call needs (~26 KB). */
