@@ -6,7 +6,6 @@
 #include "select.cuh"
 #include <curand_kernel.h>
 
-constexpr int kDenseThreads = 256;
 
 // ------------------------------------------------------------------ server: momentum (+error) (+apply)
 // Vv = rho*Vv + g*inv_n (+ N(0, noise_std^2) when noise_std > 0)
