@@ -411,16 +411,57 @@ class ClientWorker:
         self.fp.flat.copy_(new)
         return stale, new
 
+    def _client_backward(self, batch, fold_weight_decay=True):
+        """zero-grad + microbatched forward/backward + per-client gradient post-processing of ONE
+        client.  On CUDA the sequence is captured into a CUDA graph per batch shape (after two
+        eager rounds) and replayed: the per-client path is launch-bound (ResNet-18 on 8 images is
+        ~400 tiny kernels), so this is where its time goes.  Returns the results tensor (a static
+        buffer when replayed: consume it before the next call)."""
+        a, fp = self.args, self.fp
+        batch = self._prep(batch)
+        use_graph = (self.device.type == "cuda" and not getattr(a, "no_cuda_graphs", False) and not a.do_dp)
+        if use_graph:
+            key = ("client", bool(fold_weight_decay)) + tuple((tuple(t.shape), t.dtype) for t in batch)
+            entry = self._graphs.setdefault(key, {"calls": 0, "graph": None})
+            entry["calls"] += 1
+            if entry["graph"] is None and entry["calls"] > 2:
+                entry["static_in"] = [torch.empty_like(t, memory_format=torch.channels_last)
+                                      if (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last)
+                                          and not t.is_contiguous()) else torch.empty_like(t) for t in batch]
+                for dst, src in zip(entry["static_in"], batch):
+                    dst.copy_(src)
+                torch.cuda.synchronize(self.device)
+                from .ops import native
+                before = native.launch_count()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    fp.zero_grad()
+                    res, iters = _run_microbatches(self.model, entry["static_in"], self.compute_loss_train, a, True)
+                    _finish_client_grad(fp, a, iters, fold_weight_decay=fold_weight_decay)
+                    entry["results"] = res
+                entry["graph"] = graph
+                entry["native_launches"] = native.launch_count() - before
+            if entry["graph"] is not None:
+                for dst, src in zip(entry["static_in"], batch):
+                    dst.copy_(src, non_blocking=True)
+                entry["graph"].replay()
+                if entry.get("native_launches"):
+                    from .ops import native
+                    native.add_launch_count(entry["native_launches"])
+                return entry["results"].clone()
+        fp.zero_grad()
+        results, num_iters = _run_microbatches(self.model, batch, self.compute_loss_train, a, True)
+        _finish_client_grad(fp, a, num_iters, fold_weight_decay=fold_weight_decay)
+        return results
+
     def _one_client(self, cid, batch):
         a, fp = self.args, self.fp
         n_i = float(batch[0].shape[0])
         stale = None
         if self.client_weights is not None:
             stale, new = self._client_weights_in(cid)
-        fp.zero_grad()
-        results, num_iters = _run_microbatches(self.model, self._prep(batch), self.compute_loss_train, a, True)
         sketch_fold = a.mode == "sketch" and not a.do_dp
-        _finish_client_grad(fp, a, num_iters, fold_weight_decay=not sketch_fold)
+        results = self._client_backward(batch, fold_weight_decay=not sketch_fold)
         if a.mode == "sketch":
             w = fp.flat if sketch_fold else None
             wd = a.weight_decay / a.num_workers if sketch_fold else 0.0
@@ -465,9 +506,7 @@ class ClientWorker:
             step, acc = 0, None
             for _epoch in range(a.num_fedavg_epochs):
                 for chunk in chunks:
-                    fp.zero_grad()
-                    res, num_iters = _run_microbatches(self.model, chunk, self.compute_loss_train, a, True)
-                    _finish_client_grad(fp, a, num_iters)
+                    res = self._client_backward(chunk)
                     fp.flat.add_(fp.grad, alpha=-float(lr) * a.fedavg_lr_decay ** step)
                     acc = res if acc is None else acc + res
                     step += 1

@@ -97,7 +97,9 @@ class BasicNet(nn.Module):
         y = self.res1(self.layer1(y))
         y = self.layer2(y)
         y = self.res3(self.layer3(y))
-        y = self.pool(y).flatten(1)
+        # MaxPool2d(4) over the final 4x4 map of a 32x32 input; for other input sizes (FEMNIST's
+        # 28x28 ends at 3x3, where the reference's fixed 4x4 window raises) pool the whole map.
+        y = (self.pool(y) if y.shape[-1] == 4 and y.shape[-2] == 4 else F.adaptive_max_pool2d(y, 1)).flatten(1)
         return nnops.linear(y, self.linear.weight, None) * self.out_scale
 
     def finetune_parameters(self):
