@@ -156,8 +156,63 @@ def conv3x3_wgrad_nhwc(dz: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> t
 
 
 def conv_supported(x, weight, stride, padding) -> bool:
-    # individual conv hooks are not routed natively; ResNet-9 goes through resnet9_forward as a whole
-    return False
+    """3x3 / stride 1 / pad 1 convolutions with 64-multiple channels on 4..32-wide maps (the
+    stride-1 layers of ResNet-18 / FixupResNet18 / ResNet-9) when the weight lives NHWC in the flat
+    buffer.  Strided and 1x1 convolutions stay on the library."""
+    if not (x.is_cuda and x.dim() == 4 and weight.dim() == 4):
+        return False
+    co, ci, kh, kw = weight.shape
+    if (kh, kw) != (3, 3) or stride != 1 or padding != 1 or ci % 64 or co % 64:
+        return False
+    h, w = x.shape[2], x.shape[3]
+    if w not in (4, 8, 16, 32) or h != w:
+        return False
+    return weight.permute(0, 2, 3, 1).is_contiguous()
+
+
+class _Conv3x3Fn(torch.autograd.Function):
+    """One 3x3 / s1 / p1 convolution (+ optional ReLU) on the tcgen05 kernels.  Activations cross
+    the boundary as channels_last NCHW tensors (= NHWC buffers)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, relu):
+        xn = x.permute(0, 2, 3, 1)
+        xb = (xn if xn.dtype == torch.bfloat16 else xn.to(torch.bfloat16)).contiguous()
+        wk = weight.permute(0, 2, 3, 1)
+        wb = cast_bf16(wk) if wk.dtype == torch.float32 else wk.to(torch.bfloat16).contiguous()
+        y = conv3x3_nhwc(xb, wb, relu=relu)
+        ctx.save_for_backward(xb, y if relu else xb)
+        ctx.weight, ctx.relu, ctx.x_dtype = weight, relu, x.dtype
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xb, y = ctx.saved_tensors
+        weight = ctx.weight
+        dz = dy.permute(0, 2, 3, 1).to(torch.bfloat16).contiguous()
+        if ctx.relu:
+            dz = relu_bwd(y, dz)
+        dx = dw = None
+        if ctx.needs_input_grad[1]:
+            target = weight.grad if (isinstance(weight, torch.nn.Parameter) and weight.grad is not None
+                                     and weight.grad.permute(0, 2, 3, 1).is_contiguous()) else None
+            acc = target.permute(0, 2, 3, 1) if target is not None else \
+                torch.zeros(weight.permute(0, 2, 3, 1).shape, dtype=torch.float32, device=dz.device)
+            conv3x3_wgrad_nhwc(dz, xb, acc)
+            if target is None:
+                dw = acc.permute(0, 3, 1, 2)
+        if ctx.needs_input_grad[0]:
+            wk = weight.data.permute(0, 2, 3, 1)
+            wd = dgrad_weights(wk if wk.dtype == torch.float32 else wk.float().contiguous())
+            dx = conv3x3_nhwc(dz, wd).permute(0, 3, 1, 2).to(ctx.x_dtype)
+        return dx, dw, None
+
+
+def conv2d(x, weight, bias, stride, padding, relu=False):
+    y = _Conv3x3Fn.apply(x, weight, relu)
+    if bias is not None:
+        y = y + bias.view(1, -1, 1, 1)
+    return y
 
 
 def _weight_storage(weight: torch.Tensor):

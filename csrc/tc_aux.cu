@@ -8,14 +8,16 @@
 __global__ void __launch_bounds__(256)
 cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+  // parameters sit at arbitrary offsets of the flat buffer: vector path only when both sides allow it
+  const bool aligned = (((uintptr_t)src & 15) == 0) && (((uintptr_t)dst & 7) == 0);
   for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
-    if (i + 3 < n) {
+    if (aligned && i + 3 < n) {
       float4 v = *reinterpret_cast<const float4*>(src + i);
       __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
       uint2 pk; pk.x = *(uint32_t*)&a; pk.y = *(uint32_t*)&b;
       *reinterpret_cast<uint2*>(dst + i) = pk;
     } else {
-      for (int64_t j = i; j < n; ++j) dst[j] = __float2bfloat16(src[j]);
+      for (int64_t j = i; j < n && j < i + 4; ++j) dst[j] = __float2bfloat16(src[j]);
     }
   }
 }

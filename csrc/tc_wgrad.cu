@@ -29,6 +29,7 @@ struct WgParams {
   int ci_tiles;
   int tile_h, tile_n;    // box geometry of a 64-pixel step (tile_w == W)
   int ldw;               // row stride of dW (9*Cin for a convolution, ldc for a plain GEMM)
+  int vec_ok;            // dW is 16-byte aligned (it is a slice of the flat gradient buffer): vector atomics allowed
 };
 
 template <int BN>
@@ -160,8 +161,13 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
           const int ci0 = ci_tile * BN + c * 32;
           if (co < p.Cout && ci0 < p.Cin) {
             float* dst = p.dW + (int64_t)co * ldw + (CONV ? (r * 3 + sft) * p.Cin : 0) + ci0;
+            if (p.vec_ok) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+              for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) red_add_f32(dst + j, v[j]);
+            }
           }
         }
       }
@@ -221,6 +227,7 @@ CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW
   p.k_steps_total = (int)ceb_cdiv(npix, WG_KPIX);
   p.ci_tiles = Cin / bn;
   p.tile_h = tile_h; p.tile_n = tile_n; p.ldw = 9 * Cin;
+  p.vec_ok = (((uintptr_t)dW & 15) == 0) ? 1 : 0;
   const int co_tiles = (int)ceb_cdiv(Cout, WG_M);
   const int base_ctas = co_tiles * 3 * p.ci_tiles;
   int split = (int)ceb_cdiv(ceb_num_sms(), base_ctas);
@@ -235,7 +242,7 @@ CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW
 // C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A, B bf16 row-major.  M % 64 == N % 64 == 0.
 CEB_API int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, int N, int K, int ldc, void* stream) {
   CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_mn_acc: bad arguments");
-  CEB_REQUIRE(M % 64 == 0 && N % 64 == 0 && ldc % 4 == 0, "ceb_gemm_bf16_mn_acc: M, N must be multiples of 64 (M=%d N=%d)", M, N);
+  CEB_REQUIRE(M % 64 == 0 && N % 64 == 0, "ceb_gemm_bf16_mn_acc: M, N must be multiples of 64 (M=%d N=%d)", M, N);
   CUtensorMap ta, tb;
   uint64_t da[2] = {(uint64_t)M, (uint64_t)K}, sa[1] = {(uint64_t)M * 2};
   uint32_t ba[2] = {64, WG_KPIX};
@@ -245,6 +252,7 @@ CEB_API int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, 
   const int bn = (N % 128 == 0) ? 128 : 64;
   WgParams p{};
   p.dW = C; p.Cout = M; p.Cin = N; p.H = 1; p.W = 1; p.ldw = ldc;
+  p.vec_ok = (((uintptr_t)C & 15) == 0 && ldc % 4 == 0) ? 1 : 0;
   p.k_steps_total = (int)ceb_cdiv(K, WG_KPIX);
   p.ci_tiles = N / bn;
   const int co_tiles = (int)ceb_cdiv(M, WG_M);

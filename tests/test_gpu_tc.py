@@ -171,3 +171,35 @@ def test_gpt2_linears_native_match_library():
     l1, c1, g1 = run(True)
     assert abs(l0 - l1) < 2e-2 and abs(c0 - c1) < 2e-2
     assert _rel_err(g1, g0) < 0.08
+
+
+def test_resnet18_stride1_convs_native_match_library():
+    from commefficient_b200 import models
+    from commefficient_b200.ops import nn as nnops
+    from commefficient_b200.utils import FlatParams
+    torch.manual_seed(0)
+    m = models.FixupResNet18(num_classes=10)
+    for p in m.parameters():                     # Fixup zero-inits half the convs; make every layer matter
+        if p.dim() == 4 and float(p.abs().sum()) == 0:
+            torch.nn.init.normal_(p, 0, 0.02)
+    torch.nn.init.normal_(m.classifier.weight, 0, 0.05)
+    fp = FlatParams(m, DEV, layout="nhwc")
+    m._flat_params = fp
+    x = torch.randn(8, 3, 32, 32, device=DEV).contiguous(memory_format=torch.channels_last)
+    tgt = torch.randint(0, 10, (8,), device=DEV)
+
+    def run(native_on):
+        nnops.set_native(native_on)
+        try:
+            fp.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = F.cross_entropy(m(x).float(), tgt)
+            loss.backward()
+            return float(loss), fp.grad.clone()
+        finally:
+            nnops.set_native(False)
+
+    l0, g0 = run(False)
+    l1, g1 = run(True)
+    assert abs(l0 - l1) < 2e-2
+    assert _rel_err(g1, g0) < 0.08
