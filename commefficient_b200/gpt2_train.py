@@ -25,7 +25,7 @@ from torch.utils.data import DataLoader
 from . import data_utils
 from .data_utils import ATTR_TO_SPECIAL_TOKEN, FedPERSONA, FedSampler, SimpleTokenizer, personachat_collate_fn
 from .fed_aggregator import FedModel, FedOptimizer
-from .models.gpt2 import GPT2Config, GPT2DoubleHeadsModel, OpenAIGPTDoubleHeadsModel
+from .models.gpt2 import GPT2Config, GPT2DoubleHeadsModel, OpenAIGPTDoubleHeadsModel, shifted_lm_rows
 from .parallel.runtime import init_runtime
 from .utils import Logger, PiecewiseLinear, TableLogger, Timer, make_logdir, parse_args, steps_per_epoch, union
 
@@ -72,10 +72,9 @@ def _per_sample_train(model, batch, args, seg, num_segments):
     input_ids, mc_token_ids, lm_labels, mc_labels, token_type_ids = batch
     lm_logits, mc_logits, *_ = model(input_ids, token_type_ids=token_type_ids, mc_token_ids=mc_token_ids)
     B = input_ids.shape[0]
-    logits = lm_logits[..., :-1, :].reshape(-1, lm_logits.size(-1)).float()
-    labels = lm_labels[..., 1:].reshape(-1)
-    tok_loss = F.cross_entropy(logits, labels, ignore_index=-1, reduction="none").view(B, -1)
-    tok_cnt = (labels != -1).view(B, -1).sum(1).float()
+    rows, mask = shifted_lm_rows(lm_logits, lm_labels)          # [B*C, T]
+    tok_loss = rows.view(B, -1)
+    tok_cnt = mask.view(B, -1).sum(1).float()
     n_i = torch.zeros(num_segments, device=seg.device).index_add_(0, seg, torch.ones_like(tok_cnt))
     ntok_i = torch.zeros(num_segments, device=seg.device).index_add_(0, seg, tok_cnt).clamp_min(1.0)
     lm_part = tok_loss.sum(1) * (n_i / ntok_i)[seg]

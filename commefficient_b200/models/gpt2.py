@@ -108,7 +108,7 @@ class MLP(nn.Module):
         self.dropout = nn.Dropout(cfg.resid_pdrop)
 
     def forward(self, x):
-        return self.dropout(self.c_proj(F.gelu(self.c_fc(x), approximate="tanh")))
+        return self.dropout(self.c_proj(nnops.gelu_tanh(self.c_fc(x))))
 
 
 class Block(nn.Module):
@@ -120,8 +120,9 @@ class Block(nn.Module):
         self.mlp = MLP(cfg)
 
     def forward(self, x):
-        x = x + self.attn(self.ln_1(x))
-        return x + self.mlp(self.ln_2(x))
+        ln1, ln2 = self.ln_1, self.ln_2
+        x = x + self.attn(nnops.layer_norm(x, ln1.weight, ln1.bias, ln1.eps))
+        return x + self.mlp(nnops.layer_norm(x, ln2.weight, ln2.bias, ln2.eps))
 
 
 class GPT2Model(nn.Module):
@@ -144,7 +145,7 @@ class GPT2Model(nn.Module):
         x = self.drop(x)
         for block in self.h:
             x = block(x)
-        return self.ln_f(x)
+        return nnops.layer_norm(x, self.ln_f.weight, self.ln_f.bias, self.ln_f.eps)
 
 
 class SequenceSummary(nn.Module):
@@ -212,6 +213,12 @@ class GPT2DoubleHeadsModel(nn.Module):
         self.config.to_json_file(os.path.join(save_directory, CONFIG_NAME))
         torch.save(self.state_dict(), os.path.join(save_directory, WEIGHTS_NAME))
 
+    @staticmethod
+    def lm_loss(lm_logits, lm_labels):
+        """Mean shifted cross-entropy over the non-ignored target tokens (ignore_index -1)."""
+        rows, mask = shifted_lm_rows(lm_logits, lm_labels)
+        return rows.sum() / mask.sum().clamp_min(1)
+
     # -- forward -------------------------------------------------------------------
     def forward(self, input_ids, token_type_ids=None, mc_token_ids=None, lm_labels=None, mc_labels=None,
                 **_ignored):
@@ -231,11 +238,20 @@ class GPT2DoubleHeadsModel(nn.Module):
             mc_loss = F.cross_entropy(mc_logits.float().view(-1, mc_logits.shape[-1]), mc_labels.view(-1))
             outputs.insert(0, mc_loss)
         if lm_labels is not None:
-            logits = lm_logits[..., :-1, :].reshape(-1, lm_logits.shape[-1])
-            labels = lm_labels[..., 1:].reshape(-1)
-            lm_loss = F.cross_entropy(logits.float(), labels, ignore_index=-1)
-            outputs.insert(0, lm_loss)
+            outputs.insert(0, self.lm_loss(lm_logits, lm_labels))
         return tuple(outputs)
+
+
+def shifted_lm_rows(lm_logits, lm_labels):
+    """Per-position LM cross-entropy ``[N, T]`` (0 at ignored positions) and the matching mask.
+    Position t is scored against label t+1; instead of slicing the logits (which would copy the
+    whole ``[N, T, V]`` tensor) the LABELS are shifted and the last position is ignored."""
+    T = lm_labels.shape[-1]
+    flat_labels = lm_labels.reshape(-1, T)
+    shifted = torch.cat([flat_labels[:, 1:], flat_labels.new_full((flat_labels.shape[0], 1), -1)], dim=1)
+    logits2d = lm_logits.reshape(-1, lm_logits.shape[-1])
+    rows = nnops.cross_entropy_rows(logits2d, shifted.reshape(-1), ignore_index=-1)
+    return rows.view(-1, T), (shifted != -1)
 
 
 class OpenAIGPTDoubleHeadsModel(GPT2DoubleHeadsModel):

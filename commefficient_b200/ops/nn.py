@@ -54,3 +54,26 @@ def linear(x, weight, bias=None):
         if tc.linear_supported(x, weight):
             return tc.linear(x, weight, bias)
     return F.linear(x, weight, bias)
+
+
+def layer_norm(x, weight, bias, eps=1e-5):
+    if _use_native(x) and weight.is_cuda:
+        from . import tfm
+        return tfm.layer_norm(x, weight, bias, eps)
+    return F.layer_norm(x, (x.shape[-1],), weight, bias, eps)
+
+
+def gelu_tanh(x):
+    if _use_native(x) and x.numel() % 2 == 0:
+        from . import tfm
+        return tfm.gelu_tanh(x)
+    return F.gelu(x, approximate="tanh")
+
+
+def cross_entropy_rows(logits, labels, ignore_index=-1):
+    """Per-row cross-entropy (0 where ``labels == ignore_index``) of ``[rows, V]`` logits."""
+    if _use_native(logits) and logits.dtype == torch.bfloat16 and logits.dim() == 2 and logits.stride(1) == 1 \
+            and logits.stride(0) % 2 == 0:
+        from . import tfm
+        return tfm.cross_entropy_rows(logits, labels, ignore_index)
+    return F.cross_entropy(logits.float(), labels, ignore_index=ignore_index, reduction="none")

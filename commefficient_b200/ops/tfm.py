@@ -1,0 +1,118 @@
+"""Transformer-side native ops (``csrc/nn_aux.cu``): fused softmax cross-entropy over bf16 logits,
+LayerNorm and tanh-GELU, each as an autograd Function.  Dispatched from ``ops/nn.py`` on CUDA when
+the native path is on; plain PyTorch otherwise.  Reference: the ATen ops inside
+pytorch_transformers' GPT-2 that /root/reference/CommEfficient/gpt2_train.py:76-99 drives."""
+from __future__ import annotations
+
+import torch
+
+from . import native
+
+native.register_signatures({
+    "ceb_softmax_ce_fwd": ([native.c_ptr, native.c_i64, native.c_i64, native.c_i32, native.c_ptr, native.c_i64,
+                            native.c_ptr, native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_softmax_ce_bwd": ([native.c_ptr, native.c_ptr, native.c_i64, native.c_i64, native.c_i32, native.c_ptr,
+                            native.c_i64, native.c_ptr, native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_layernorm_fwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                           native.c_i64, native.c_i32, native.c_f32, native.c_ptr], native.c_i32),
+    "ceb_layernorm_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                           native.c_ptr, native.c_ptr, native.c_i64, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_gelu_bf16": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr], native.c_i32),
+})
+
+
+class _CrossEntropyRows(torch.autograd.Function):
+    """Per-row cross-entropy of bf16 logits ``[rows, V]`` (0 for rows whose label is ``ignore_index``).
+    The gradient overwrites nothing the caller still owns: it is written to a fresh bf16 buffer in
+    one pass from the saved log-sum-exp (no fp32 copy of the logits is ever made)."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, ignore_index):
+        assert logits.dim() == 2 and logits.dtype == torch.bfloat16 and logits.stride(1) == 1
+        rows, V = logits.shape
+        labels = labels.contiguous()
+        loss = torch.empty(rows, dtype=torch.float32, device=logits.device)
+        lse = torch.empty(rows, dtype=torch.float32, device=logits.device)
+        native.call("ceb_softmax_ce_fwd", native.ptr(logits), logits.stride(0), rows, V, native.ptr(labels),
+                    int(ignore_index), native.ptr(loss), native.ptr(lse), native.stream_ptr(logits.device))
+        ctx.save_for_backward(logits, labels, lse)
+        ctx.ignore_index = int(ignore_index)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gloss):
+        logits, labels, lse = ctx.saved_tensors
+        rows, V = logits.shape
+        g = gloss.float().contiguous()
+        d = torch.empty_like(logits)
+        native.call("ceb_softmax_ce_bwd", native.ptr(logits), native.ptr(d), logits.stride(0), rows, V,
+                    native.ptr(labels), ctx.ignore_index, native.ptr(lse), native.ptr(g),
+                    native.stream_ptr(logits.device))
+        return d, None, None
+
+
+def cross_entropy_rows(logits: torch.Tensor, labels: torch.Tensor, ignore_index: int = -1) -> torch.Tensor:
+    return _CrossEntropyRows.apply(logits, labels, ignore_index)
+
+
+class _LayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        E = x.shape[-1]
+        x2 = x.reshape(-1, E).float().contiguous()
+        rows = x2.shape[0]
+        y = torch.empty((rows, E), dtype=torch.bfloat16, device=x.device)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        w = weight.detach().float().contiguous()
+        b = bias.detach().float().contiguous()
+        native.call("ceb_layernorm_fwd", native.ptr(x2), native.ptr(w), native.ptr(b), native.ptr(y), native.ptr(mean),
+                    native.ptr(rstd), rows, E, float(eps), native.stream_ptr(x.device))
+        ctx.save_for_backward(x2, w, mean, rstd)
+        ctx.x_shape, ctx.x_dtype = x.shape, x.dtype
+        ctx.params = (weight, bias)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w, mean, rstd = ctx.saved_tensors
+        rows, E = x2.shape
+        dyb = dy.reshape(rows, E).to(torch.bfloat16).contiguous()
+        dx = torch.empty_like(x2)
+        weight, bias = ctx.params
+        direct = (isinstance(weight, torch.nn.Parameter) and weight.grad is not None and bias.grad is not None
+                  and weight.grad.is_contiguous() and bias.grad.is_contiguous())
+        dg = weight.grad if direct else torch.zeros(E, dtype=torch.float32, device=dy.device)
+        db = bias.grad if direct else torch.zeros(E, dtype=torch.float32, device=dy.device)
+        native.call("ceb_layernorm_bwd", native.ptr(dyb), native.ptr(x2), native.ptr(w), native.ptr(mean),
+                    native.ptr(rstd), native.ptr(dx), native.ptr(dg), native.ptr(db), rows, E,
+                    native.stream_ptr(dy.device))
+        return dx.view(ctx.x_shape).to(ctx.x_dtype), (None if direct else dg), (None if direct else db), None
+
+
+def layer_norm(x, weight, bias, eps):
+    return _LayerNorm.apply(x, weight, bias, eps)
+
+
+class _Gelu(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        xb = x.to(torch.bfloat16).contiguous()
+        y = torch.empty_like(xb)
+        native.call("ceb_gelu_bf16", native.ptr(xb), None, native.ptr(y), xb.numel(), native.stream_ptr(x.device))
+        ctx.save_for_backward(xb)
+        ctx.x_dtype = x.dtype
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (xb,) = ctx.saved_tensors
+        dyb = dy.to(torch.bfloat16).contiguous()
+        dx = torch.empty_like(xb)
+        native.call("ceb_gelu_bf16", native.ptr(xb), native.ptr(dyb), native.ptr(dx), xb.numel(),
+                    native.stream_ptr(dy.device))
+        return dx.to(ctx.x_dtype)
+
+
+def gelu_tanh(x):
+    return _Gelu.apply(x)

@@ -165,6 +165,24 @@ int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, int N, i
 int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin,
                                 int Cout, void* stream);
 
+/* ---- transformer-side ops (reference: pytorch_transformers' GPT-2 behind gpt2_train.py:76-99) ----
+ * Softmax cross-entropy over bf16 logits rows (row stride ld elements, V classes, labels ==
+ * ignore_index skipped): forward writes loss[row] and lse[row]; backward writes
+ * dlogits = grad_rows[row] * (softmax - onehot) (may alias logits). */
+int ceb_softmax_ce_fwd(const void* logits_bf16, int64_t ld, int64_t rows, int V, const int64_t* labels,
+                       int64_t ignore_index, float* loss, float* lse, void* stream);
+int ceb_softmax_ce_bwd(const void* logits_bf16, void* dlogits_bf16, int64_t ld, int64_t rows, int V,
+                       const int64_t* labels, int64_t ignore_index, const float* lse, const float* grad_rows,
+                       void* stream);
+/* LayerNorm over the last dimension: x fp32 [rows][E] -> y bf16; backward gives dx fp32 and
+ * accumulates dgamma / dbeta. */
+int ceb_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* y_bf16, float* mean,
+                      float* rstd, int64_t rows, int E, float eps, void* stream);
+int ceb_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, const float* mean, const float* rstd,
+                      float* dx, float* dgamma, float* dbeta, int64_t rows, int E, void* stream);
+/* tanh-GELU on bf16: out = gelu(x) (dy NULL) or dy * gelu'(x). */
+int ceb_gelu_bf16(const void* x, const void* dy, void* out, int64_t n, void* stream);
+
 /* ---- peer-memory collectives over NVLink, fused with the server update ---------
  * (reference: the single NCCL reduce + host-side weight update/download,
  *  fed_worker.py:41,138, fed_aggregator.py:327-332,455).  src/dst/flags are HOST arrays of

@@ -203,3 +203,43 @@ def test_resnet18_stride1_convs_native_match_library():
     l1, g1 = run(True)
     assert abs(l0 - l1) < 2e-2
     assert _rel_err(g1, g0) < 0.08
+
+
+def test_ce_layernorm_gelu_kernels_match_torch():
+    from commefficient_b200.ops import tfm
+    g = torch.Generator(device=DEV).manual_seed(5)
+    logits = (torch.randn(37, 50262, device=DEV, generator=g) * 3).bfloat16().requires_grad_(True)
+    labels = torch.randint(0, 50262, (37,), device=DEV, generator=g)
+    labels[::5] = -1
+    rows = tfm.cross_entropy_rows(logits, labels, -1)
+    want = F.cross_entropy(logits.detach().float().requires_grad_(True), labels, ignore_index=-1, reduction="none")
+    torch.testing.assert_close(rows, want, rtol=1e-4, atol=1e-4)
+    w = torch.randn(37, device=DEV)
+    (rows * w).sum().backward()
+    ref_in = logits.detach().float().requires_grad_(True)
+    (F.cross_entropy(ref_in, labels, ignore_index=-1, reduction="none") * w).sum().backward()
+    assert _rel_err(logits.grad, ref_in.grad) < 1e-2
+
+    x = torch.randn(300, 768, device=DEV, requires_grad=True)
+    ln = torch.nn.LayerNorm(768).to(DEV)
+    torch.nn.init.normal_(ln.weight, 1.0, 0.1)
+    torch.nn.init.normal_(ln.bias, 0.0, 0.1)
+    y = tfm.layer_norm(x, ln.weight, ln.bias, ln.eps)
+    yr = ln(x.detach())
+    assert _rel_err(y, yr) < 5e-3
+    dy = torch.randn(300, 768, device=DEV).bfloat16()
+    y.backward(dy)
+    xr = x.detach().clone().requires_grad_(True)
+    ln2 = torch.nn.LayerNorm(768).to(DEV)
+    ln2.load_state_dict(ln.state_dict())
+    ln2(xr).backward(dy.float())
+    assert _rel_err(x.grad, xr.grad) < 1e-3
+    assert _rel_err(ln.weight.grad, ln2.weight.grad) < 1e-3 and _rel_err(ln.bias.grad, ln2.bias.grad) < 1e-3
+
+    h = torch.randn(64, 3072, device=DEV).bfloat16().requires_grad_(True)
+    out = tfm.gelu_tanh(h)
+    assert _rel_err(out, F.gelu(h.detach().float(), approximate="tanh")) < 5e-3
+    out.backward(torch.ones_like(out))
+    hr = h.detach().float().requires_grad_(True)
+    F.gelu(hr, approximate="tanh").sum().backward()
+    assert _rel_err(h.grad, hr.grad) < 1e-2
