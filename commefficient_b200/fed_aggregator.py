@@ -33,6 +33,7 @@ from .ops import sketch as sk
 from .ops.topk import topk_sparse
 from .parallel.runtime import Runtime, init_runtime
 from .parallel.watchdog import RoundWatchdog, maybe_inject, parse_fault
+from .utils.logging import PhaseTracer
 from .utils.flat import get_param_vec, set_param_vec  # noqa: F401  (re-exported, reference names)
 
 DEFAULT_NUM_CLIENTS = {"EMNIST": 3500, "PERSONA": 17568}
@@ -129,7 +130,14 @@ class FedModel:
         self.last_unique_clients = np.zeros(0, dtype=np.int64)
         self.watchdog = RoundWatchdog(getattr(args, "watchdog_timeout", 0.0) or 0.0, self.rt.rank).start()
         self._fault = parse_fault()
+        self.tracer = PhaseTracer(getattr(args, "trace_phases", "") or "", getattr(args, "trace_every", 50),
+                                  self.rt.rank, self._trace_max, self.device.type)
         _CURRENT = self
+
+    def _trace_max(self, vals):
+        if self.rt.world_size == 1:
+            return vals
+        return [self.rt.max_over_ranks(v) for v in vals]
 
     # -- nn.Module-ish surface -------------------------------------------------------
     def train(self, training=True):
@@ -142,6 +150,7 @@ class FedModel:
     def finalize(self):
         """End of training (the reference joins its worker processes here)."""
         self.watchdog.stop()
+        self.tracer.flush()
         self.rt.barrier()
 
     def zero_grad(self):
@@ -196,6 +205,9 @@ class FedModel:
         mine = self._assign(unique)[self.rt.rank]
         cols = batch[1:]
         client_batches = []
+        tr = self.tracer
+        h2d_phase = tr.phase("h2d")
+        h2d_phase.__enter__()
         if len(mine):
             order = np.argsort(inverse, kind="stable")
             counts = np.bincount(inverse, minlength=len(unique))
@@ -217,19 +229,24 @@ class FedModel:
                 n = int(counts[p])
                 client_batches.append((int(cid), [t[lo:lo + n] for t in dev_cols]))
                 lo += n
+        h2d_phase.__exit__(None, None, None)
         self.watchdog.beat("clients", self.rounds + 1)
-        local = self.worker.run_round(client_batches, fedavg_lr=self.fedavg_lr)
+        with tr.phase("clients"):
+            local = self.worker.run_round(client_batches, fedavg_lr=self.fedavg_lr)
         maybe_inject(self._fault, self.rt.rank, self.rounds + 1, self.worker.transmit)
         self.watchdog.beat("reduce")
         if self.fused_reduce:
             self.reduce_pending = True
         else:
-            self.rt.all_reduce_sum_(self.worker.transmit)
+            with tr.phase("reduce"):
+                self.rt.all_reduce_sum_(self.worker.transmit)
         self.pending_samples = int(ids.shape[0])
         self.last_unique_clients = unique
         self.rounds += 1
 
         # per-client results of every rank, in ascending client-id order
+        res_phase = tr.phase("results")
+        res_phase.__enter__()
         dl = self.tracker.download_counts(unique).to(torch.float32)
         if self.rt.world_size > 1 and self.rt.peer is not None:
             # every rank scatters its clients' rows into a zeroed [W, n_res] slab and the slabs are
@@ -248,6 +265,7 @@ class FedModel:
             gathered = local.float()
         self.watchdog.beat("results")
         packed = torch.cat([gathered, dl.unsqueeze(1)], dim=1).cpu().numpy()   # the round's one D2H
+        res_phase.__exit__(None, None, None)
         self.watchdog.idle()
         n_res = args.num_results_train
         results = [packed[:, i].copy() for i in range(n_res)]
@@ -373,6 +391,14 @@ class FedOptimizer(torch.optim.Optimizer):
     # -- the server update ---------------------------------------------------------------
     @torch.no_grad()
     def step(self, closure=None):
+        tr = self.fed_model.tracer
+        had_round = self.fed_model.pending_samples != 0
+        with tr.phase("server"):
+            self._step_impl()
+        if had_round:
+            tr.end_round()
+
+    def _step_impl(self):
         fm, args = self.fed_model, self.args
         lr = self.get_lr()
         if (not torch.is_tensor(lr)) and lr == 0:

@@ -173,3 +173,80 @@ class DeviceTimer:
         if reset:
             self._records = []
         return out
+
+
+class PhaseTracer:
+    """Per-round phase tracing (SURVEY.md section 5.1 "Ours"; the reference only has a wall-clock
+    ``Timer``).  Every phase is an NVTX range plus a CUDA-event pair on the current stream; every
+    ``every`` rounds the accumulated per-phase milliseconds are reduced to the MAX over ranks
+    (``reduce_max``: a callable taking/returning a list of floats) and rank 0 appends one JSON line
+    ``{"round": n, "rounds": m, "ms_per_round": {phase: ms}}`` to ``path``.  Disabled (zero
+    overhead beyond an attribute test) when ``path`` is empty."""
+
+    def __init__(self, path, every=50, rank=0, reduce_max=None, device="cuda"):
+        self.enabled = bool(path)
+        self.path, self.every, self.rank, self.reduce_max = path, max(1, int(every)), rank, reduce_max
+        self.timer = DeviceTimer(self.enabled, device)
+        self.rounds_open = 0
+        self.round_no = 0
+        self._nvtx = None
+        if self.enabled and self.timer.cuda:
+            import torch
+            self._nvtx = torch.cuda.nvtx
+
+    class _Range:
+        def __init__(self, owner, name):
+            self.owner, self.name = owner, name
+            self.inner = owner.timer.phase(name)
+
+        def __enter__(self):
+            if self.owner._nvtx is not None:
+                self.owner._nvtx.range_push(self.name)
+            self.inner.__enter__()
+            return self
+
+        def __exit__(self, *exc):
+            self.inner.__exit__(*exc)
+            if self.owner._nvtx is not None:
+                self.owner._nvtx.range_pop()
+            return False
+
+    class _Null:
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *exc):
+            return False
+
+    _NULL = _Null()
+
+    def phase(self, name):
+        if not self.enabled:
+            return PhaseTracer._NULL
+        return PhaseTracer._Range(self, name)
+
+    def end_round(self):
+        """Call once per federated round (after the server step)."""
+        if not self.enabled:
+            return None
+        self.round_no += 1
+        self.rounds_open += 1
+        if self.rounds_open < self.every:
+            return None
+        return self.flush()
+
+    def flush(self):
+        if not self.enabled or self.rounds_open == 0:
+            return None
+        summ = self.timer.summary()
+        names = sorted(summ)
+        vals = [summ[n] / self.rounds_open for n in names]
+        if self.reduce_max is not None:
+            vals = self.reduce_max(vals)
+        rec = {"round": self.round_no, "rounds": self.rounds_open,
+               "ms_per_round": {n: round(float(v), 4) for n, v in zip(names, vals)}}
+        self.rounds_open = 0
+        if self.rank == 0:
+            with open(self.path, "a") as f:
+                f.write(json.dumps(rec) + "\n")
+        return rec

@@ -172,3 +172,17 @@ def test_hung_rank_is_detected_and_aborts_the_job(tmp_path):
     assert res.returncode == 86, res.stderr[-500:]
     assert "no progress" in res.stderr and "round 2" in res.stderr
     assert time.time() - t0 < 100
+
+
+def test_phase_tracer_writes_max_over_ranks_records(tmp_path):
+    """--trace_phases: one JSONL record per ``trace_every`` rounds with every phase of the round."""
+    import json
+    path = str(tmp_path / "phases.jsonl")
+    fed, opt, _ = _make("sketch", trace_phases=path, trace_every=2)
+    for s in range(4):
+        _round(fed, opt, s)
+    fed.rt.shutdown()
+    recs = [json.loads(l) for l in open(path)]
+    assert len(recs) == 2 and recs[-1]["round"] == 4 and recs[0]["rounds"] == 2
+    assert {"h2d", "clients", "results", "server"} <= set(recs[0]["ms_per_round"])
+    assert all(v >= 0 for v in recs[0]["ms_per_round"].values())
