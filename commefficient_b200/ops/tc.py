@@ -33,23 +33,48 @@ native.register_signatures({
                          native.c_i32),
     "ceb_gemm_bf16_mn_acc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
                               native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_gemm_bf16_tn_ld": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i64,
+                             native.c_i32, native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
+                             native.c_ptr], native.c_i32),
+    "ceb_gemm_bf16_mn_acc_ld": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i32,
+                                 native.c_i32, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_cast_transpose_f32_bf16": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i64,
+                                     native.c_ptr], native.c_i32),
+    "ceb_colsum_bf16": ([native.c_ptr, native.c_i64, native.c_i64, native.c_i32, native.c_ptr, native.c_ptr],
+                        native.c_i32),
 })
 
 _OUT = {torch.bfloat16: 0, torch.float32: 1}
 
 
+def _rows_ok(t: torch.Tensor) -> bool:
+    """2-D bf16, unit column stride, 16-byte aligned rows (row stride a multiple of 8 elements)."""
+    return (t.dim() == 2 and t.dtype == torch.bfloat16 and t.stride(1) == 1 and t.stride(0) % 8 == 0
+            and t.stride(0) >= t.shape[1] and t.data_ptr() % 16 == 0)
+
+
+def padded_empty(rows: int, cols: int, dtype, device) -> torch.Tensor:
+    """``[rows, cols]`` view of a buffer whose row stride is ``cols`` rounded up to 8 elements, so rows
+    stay 16-byte aligned for TMA / vector access whatever ``cols`` is (e.g. the 50 262-wide logits)."""
+    ld = (cols + 7) // 8 * 8
+    return torch.empty((rows, ld), dtype=dtype, device=device)[:, :cols]
+
+
 def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias=None, relu=False, out_dtype=torch.bfloat16, out=None,
             accumulate=False) -> torch.Tensor:
-    """``act(a @ b.T + bias)`` with a ``[M, K]``, b ``[N, K]`` contiguous bf16 CUDA tensors."""
-    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_contiguous() and b.is_contiguous()
+    """``act(a @ b.T + bias)`` with a ``[M, K]``, b ``[N, K]`` bf16 CUDA tensors whose rows are 16-byte
+    aligned (row strides may exceed K).  N and K are arbitrary; when N is not a multiple of 8 the
+    result is a ``[M, N]`` view of a row-padded buffer (see ``padded_empty``)."""
+    assert _rows_ok(a) and _rows_ok(b), "gemm_tn operands must be bf16 with 16-byte aligned rows"
     M, K = a.shape
     N, K2 = b.shape
     assert K == K2
     if out is None:
-        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+        out = padded_empty(M, N, out_dtype, a.device)
+    assert out.stride(1) == 1
     mode = 2 if accumulate else _OUT[out.dtype]
-    native.call("ceb_gemm_bf16_tn", native.ptr(a), native.ptr(b), native.ptr(out), M, N, K, native.ptr(bias),
-                1 if relu else 0, mode, native.stream_ptr(a.device))
+    native.call("ceb_gemm_bf16_tn_ld", native.ptr(a), a.stride(0), native.ptr(b), b.stride(0), native.ptr(out),
+                out.stride(0), M, N, K, native.ptr(bias), 1 if relu else 0, mode, native.stream_ptr(a.device))
     return out
 
 
@@ -110,14 +135,33 @@ def maxpool_bwd_nhwc(y: torch.Tensor, dp: torch.Tensor, k: int, relu_mask: bool)
 
 
 def gemm_mn_acc(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor) -> torch.Tensor:
-    """``c[M,N] (fp32) += a[K,M].T @ b[K,N]`` (bf16 row-major operands; the reduction runs over rows)."""
-    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_contiguous() and b.is_contiguous()
+    """``c[M,N] (fp32) += a[K,M].T @ b[K,N]`` (bf16 operands with 16-byte aligned rows; the reduction
+    runs over rows).  N % 64 == 0; M arbitrary."""
+    assert _rows_ok(a) and _rows_ok(b), "gemm_mn_acc operands must be bf16 with 16-byte aligned rows"
     assert c.dtype == torch.float32 and c.stride(1) == 1
     K, M = a.shape
     N = b.shape[1]
-    native.call("ceb_gemm_bf16_mn_acc", native.ptr(a), native.ptr(b), native.ptr(c), M, N, K, c.stride(0),
-                native.stream_ptr(a.device))
+    native.call("ceb_gemm_bf16_mn_acc_ld", native.ptr(a), a.stride(0), native.ptr(b), b.stride(0), native.ptr(c),
+                M, N, K, c.stride(0), native.stream_ptr(a.device))
     return c
+
+
+def cast_transpose_bf16(src: torch.Tensor) -> torch.Tensor:
+    """bf16 ``[C, R]`` transposed copy (rows padded to 16 bytes) of a contiguous fp32 ``[R, C]`` matrix."""
+    assert src.dim() == 2 and src.dtype == torch.float32 and src.is_contiguous()
+    R, C = src.shape
+    out = padded_empty(C, R, torch.bfloat16, src.device)
+    native.call("ceb_cast_transpose_f32_bf16", native.ptr(src), native.ptr(out), R, C, out.stride(0),
+                native.stream_ptr(src.device))
+    return out
+
+
+def colsum_acc(x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """``out (fp32 [cols]) += x.sum(0)`` for bf16 ``x`` with 16-byte aligned rows and cols % 8 == 0."""
+    assert _rows_ok(x) and x.shape[1] % 8 == 0 and out.dtype == torch.float32 and out.is_contiguous()
+    native.call("ceb_colsum_bf16", native.ptr(x), x.stride(0), x.shape[0], x.shape[1], native.ptr(out),
+                native.stream_ptr(x.device))
+    return out
 
 
 def im2col_c3(x_nhwc_f32: torch.Tensor) -> torch.Tensor:
@@ -229,52 +273,79 @@ def linear_supported(x, weight) -> bool:
     if not (x.is_cuda and weight.dim() == 2 and x.shape[-1] == weight.shape[1]):
         return False
     n, k = weight.shape
-    store, _ = _weight_storage(weight)
-    return store is not None and n % 64 == 0 and k % 64 == 0
+    store, transposed = _weight_storage(weight)
+    if store is None or store.dtype != torch.float32 or k % 64 != 0 or n < 64:
+        return False
+    return n % 64 == 0 or not transposed        # Conv1D storage: N is the wgrad GEMM's 64-multiple side
+
+
+def _as_rows(t: torch.Tensor) -> torch.Tensor:
+    """bf16 2-D operand with 16-byte aligned rows, without a copy when it already is one."""
+    t2 = t.reshape(-1, t.shape[-1])
+    if t2.dtype == torch.bfloat16 and _rows_ok(t2):
+        return t2
+    out = padded_empty(t2.shape[0], t2.shape[1], torch.bfloat16, t2.device)
+    out.copy_(t2)
+    return out
 
 
 class _LinearFn(torch.autograd.Function):
-    """``y = x W^T + b`` on the tcgen05 GEMMs: forward TN (or NN for Conv1D storage), data gradient
-    NN (or TN), weight gradient by the MN-major split-K GEMM accumulating in fp32 -- directly into
-    ``weight.grad`` when that already exists (the flat gradient buffer)."""
+    """``y = x W^T + b`` on the tcgen05 GEMMs.  Both GEMMs that read the weight want it K-major, so the
+    fp32 master weight is cast to bf16 once per direction: as stored for one of them, through the
+    transposing cast for the other (``nn.Linear`` ``[N, K]``: plain forward / transposed dgrad; GPT-2
+    ``Conv1D`` ``[K, N]``: the other way round).  The weight gradient is the MN-major split-K GEMM
+    accumulating in fp32 -- directly into ``weight.grad`` when that already exists (the flat gradient
+    buffer) -- and the bias gradient a column-sum kernel over the bf16 output gradient.  N need not be
+    a multiple of 8: outputs / gradients then live in row-padded buffers (LM head, V = 50 262)."""
 
     @staticmethod
     def forward(ctx, x, weight, bias):
         store, transposed = _weight_storage(weight)
-        xb = x.reshape(-1, x.shape[-1]).to(torch.bfloat16).contiguous()
-        wb = cast_bf16(store) if store.dtype == torch.float32 else store.to(torch.bfloat16)
+        xb = _as_rows(x)
+        wb = cast_transpose_bf16(store) if transposed else cast_bf16(store)      # [N, K]
         bf = bias.float().contiguous() if bias is not None else None
-        y = gemm_nn(xb, wb, bias=bf) if transposed else gemm_tn(xb, wb, bias=bf)
-        ctx.save_for_backward(xb, wb)
+        y = gemm_tn(xb, wb, bias=bf)
+        ctx.save_for_backward(xb)
         ctx.transposed = transposed
         ctx.weight = weight
-        ctx.has_bias = bias is not None
+        ctx.bias = bias
         ctx.x_shape = x.shape
         ctx.x_dtype = x.dtype
         return y.view(*x.shape[:-1], weight.shape[0])
 
     @staticmethod
     def backward(ctx, dy):
-        xb, wb = ctx.saved_tensors
-        weight, transposed = ctx.weight, ctx.transposed
-        dyb = dy.reshape(-1, dy.shape[-1]).to(torch.bfloat16).contiguous()
+        (xb,) = ctx.saved_tensors
+        weight, transposed, bias = ctx.weight, ctx.transposed, ctx.bias
+        store, _ = _weight_storage(weight)
+        dyb = _as_rows(dy)
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = gemm_tn(dyb, wb) if transposed else gemm_nn(dyb, wb)
+            wt = cast_bf16(store) if transposed else cast_transpose_bf16(store)  # [K, N]
+            dx = gemm_tn(dyb, wt)
             dx = dx.view(ctx.x_shape).to(ctx.x_dtype)
         dw = None
         if ctx.needs_input_grad[1]:
             param = weight._base if (transposed and weight._base is not None) else weight
             target = param.grad if (isinstance(param, torch.nn.Parameter) and param.grad is not None
                                     and param.grad.is_contiguous()) else None
-            acc = target if target is not None else torch.zeros_like(_weight_storage(weight)[0], dtype=torch.float32)
+            acc = target if target is not None else torch.zeros_like(store, dtype=torch.float32)
             if transposed:
                 gemm_mn_acc(xb, dyb, acc)          # dW_storage[K, N] += X^T dY
             else:
                 gemm_mn_acc(dyb, xb, acc)          # dW[N, K] += dY^T X
             if target is None:
                 dw = acc.t() if transposed else acc
-        db = dy.reshape(-1, dy.shape[-1]).float().sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        db = None
+        if bias is not None and ctx.needs_input_grad[2]:
+            if dyb.shape[1] % 8 == 0:
+                direct = (isinstance(bias, torch.nn.Parameter) and bias.grad is not None
+                          and bias.grad.is_contiguous() and bias.grad.dtype == torch.float32)
+                acc_b = bias.grad if direct else torch.zeros(dyb.shape[1], dtype=torch.float32, device=dy.device)
+                colsum_acc(dyb, acc_b)
+                db = None if direct else acc_b
+            else:
+                db = dyb.float().sum(0)
         return dx, dw, db
 
 

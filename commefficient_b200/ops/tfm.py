@@ -44,7 +44,8 @@ class _CrossEntropyRows(torch.autograd.Function):
         logits, labels, lse = ctx.saved_tensors
         rows, V = logits.shape
         g = gloss.float().contiguous()
-        d = torch.empty_like(logits)
+        # same row stride as the logits (they may live in a row-padded buffer, V = 50 262)
+        d = torch.empty((rows, logits.stride(0)), dtype=logits.dtype, device=logits.device)[:, :V]
         native.call("ceb_softmax_ce_bwd", native.ptr(logits), native.ptr(d), logits.stride(0), rows, V,
                     native.ptr(labels), ctx.ignore_index, native.ptr(lse), native.ptr(g),
                     native.stream_ptr(logits.device))

@@ -56,7 +56,27 @@ ce_fwd_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int V, const
   const __nv_bfloat162* p2 = reinterpret_cast<const __nv_bfloat162*>(p);
   const int pairs = V >> 1;
   float m = -INFINITY, s = 0.f;          // online softmax: running max and sum of exp(x - m)
-  for (int j = threadIdx.x; j < pairs; j += blockDim.x) {
+  // 16-byte loads when every row starts 16-byte aligned (row-padded logits buffers), bf16 pairs otherwise
+  const bool vec = (ld % 8 == 0) && ((((uintptr_t)logits) & 15) == 0);
+  const int nvec = vec ? (V >> 3) : 0;
+  const uint4* p4 = reinterpret_cast<const uint4*>(p);
+  for (int j = threadIdx.x; j < nvec; j += blockDim.x) {
+    const uint4 u = p4[j];
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    float f[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 t = __bfloat1622float2(*(const __nv_bfloat162*)&w[i]);
+      f[2 * i] = t.x; f[2 * i + 1] = t.y;
+    }
+    float mx = f[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) mx = fmaxf(mx, f[i]);
+    if (mx > m) { s *= __expf(m - mx); m = mx; }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += __expf(f[i] - m);
+  }
+  for (int j = nvec * 4 + threadIdx.x; j < pairs; j += blockDim.x) {
     const float2 v = __bfloat1622float2(p2[j]);
     const float mx = fmaxf(v.x, v.y);
     if (mx > m) { s *= __expf(m - mx); m = mx; }
@@ -89,7 +109,30 @@ ce_bwd_kernel(const __nv_bfloat16* __restrict__ logits, __nv_bfloat16* __restric
   const __nv_bfloat162* p2 = reinterpret_cast<const __nv_bfloat162*>(logits + row * ld);
   __nv_bfloat162* d2 = reinterpret_cast<__nv_bfloat162*>(dlogits + row * ld);
   const int pairs = V >> 1;
-  for (int j = threadIdx.x; j < pairs; j += blockDim.x) {
+  const bool vec = (ld % 8 == 0) && (((((uintptr_t)logits) | ((uintptr_t)dlogits)) & 15) == 0);
+  const int nvec = vec ? (V >> 3) : 0;
+  const uint4* p4 = reinterpret_cast<const uint4*>(p2);
+  uint4* d4 = reinterpret_cast<uint4*>(d2);
+  for (int j = threadIdx.x; j < nvec; j += blockDim.x) {
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (!ignored) {
+      const uint4 u = p4[j];
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+      uint32_t r[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float2 t = __bfloat1622float2(*(const __nv_bfloat162*)&w[i]);
+        const int c = 8 * j + 2 * i;
+        t.x = g * (__expf(t.x - l) - (c == label ? 1.f : 0.f));
+        t.y = g * (__expf(t.y - l) - ((c + 1) == label ? 1.f : 0.f));
+        const __nv_bfloat162 h = __floats2bfloat162_rn(t.x, t.y);
+        r[i] = *(const uint32_t*)&h;
+      }
+      o = make_uint4(r[0], r[1], r[2], r[3]);
+    }
+    d4[j] = o;
+  }
+  for (int j = nvec * 4 + threadIdx.x; j < pairs; j += blockDim.x) {
     float2 v = __bfloat1622float2(p2[j]);
     v.x = ignored ? 0.f : g * (__expf(v.x - l) - ((2 * j) == label ? 1.f : 0.f));
     v.y = ignored ? 0.f : g * (__expf(v.y - l) - ((2 * j + 1) == label ? 1.f : 0.f));
@@ -190,12 +233,103 @@ CEB_API int ceb_layernorm_fwd(const float* x, const float* gamma, const float* b
   return 0;
 }
 
+// Register-accumulating variant for E = 128 * G (GPT-2: 768, 1024): one warp per row, every lane owns
+// G float4 column groups, keeps x-hat / dy in registers between the two passes and accumulates its
+// dgamma / dbeta partials in registers over all rows the warp walks; the block combines its 8 warps
+// in shared memory once and issues one global atomic per column.
+template <int G>
+__global__ void __launch_bounds__(256)
+ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
+                  const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dx,
+                  float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t rows) {
+  constexpr int E = 128 * G;
+  __shared__ float sh[2 * E];
+  for (int j = threadIdx.x; j < 2 * E; j += blockDim.x) sh[j] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  float4 gam[G], ag[G], ab[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    gam[g] = __ldg((const float4*)(gamma + g * 128 + lane * 4));
+    ag[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+    ab[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int64_t row = (int64_t)blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += (int64_t)gridDim.x * wpb) {
+    const float mu = mean[row], rs = rstd[row];
+    const float* xr = x + row * E;
+    const __nv_bfloat16* gr = dy + row * E;
+    float4 xh[G], d[G];
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const float4 xv = *(const float4*)(xr + g * 128 + lane * 4);
+      const uint2 raw = *(const uint2*)(gr + g * 128 + lane * 4);
+      const float2 d01 = __bfloat1622float2(*(const __nv_bfloat162*)&raw.x);
+      const float2 d23 = __bfloat1622float2(*(const __nv_bfloat162*)&raw.y);
+      d[g] = make_float4(d01.x, d01.y, d23.x, d23.y);
+      xh[g] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+      const float g0 = d[g].x * gam[g].x, g1 = d[g].y * gam[g].y, g2 = d[g].z * gam[g].z, g3 = d[g].w * gam[g].w;
+      a += g0 + g1 + g2 + g3;
+      b = fmaf(g0, xh[g].x, fmaf(g1, xh[g].y, fmaf(g2, xh[g].z, fmaf(g3, xh[g].w, b))));
+    }
+    a = warp_sum(a) * (1.f / E); b = warp_sum(b) * (1.f / E);
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      float4 o;
+      o.x = rs * (d[g].x * gam[g].x - a - xh[g].x * b);
+      o.y = rs * (d[g].y * gam[g].y - a - xh[g].y * b);
+      o.z = rs * (d[g].z * gam[g].z - a - xh[g].z * b);
+      o.w = rs * (d[g].w * gam[g].w - a - xh[g].w * b);
+      *(float4*)(dx + row * E + g * 128 + lane * 4) = o;
+      ag[g].x = fmaf(d[g].x, xh[g].x, ag[g].x); ag[g].y = fmaf(d[g].y, xh[g].y, ag[g].y);
+      ag[g].z = fmaf(d[g].z, xh[g].z, ag[g].z); ag[g].w = fmaf(d[g].w, xh[g].w, ag[g].w);
+      ab[g].x += d[g].x; ab[g].y += d[g].y; ab[g].z += d[g].z; ab[g].w += d[g].w;
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const int j = g * 128 + lane * 4;
+    atomicAdd(sh + j, ag[g].x); atomicAdd(sh + j + 1, ag[g].y); atomicAdd(sh + j + 2, ag[g].z); atomicAdd(sh + j + 3, ag[g].w);
+    atomicAdd(sh + E + j, ab[g].x); atomicAdd(sh + E + j + 1, ab[g].y);
+    atomicAdd(sh + E + j + 2, ab[g].z); atomicAdd(sh + E + j + 3, ab[g].w);
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < E; j += blockDim.x) {
+    atomicAdd(dgamma + j, sh[j]);
+    atomicAdd(dbeta + j, sh[E + j]);
+  }
+}
+
+template <int G>
+static void launch_ln_bwd_vec(const void* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                              float* dx, float* dgamma, float* dbeta, int64_t rows, cudaStream_t st) {
+  int blocks = ceb_num_sms() * 2;
+  if (blocks > ceb_cdiv(rows, 8)) blocks = (int)ceb_cdiv(rows, 8);
+  ln_bwd_vec_kernel<G><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows);
+}
+
 // dgamma / dbeta are accumulated (+=)
 CEB_API int ceb_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, const float* mean,
                               const float* rstd, float* dx, float* dgamma, float* dbeta, int64_t rows, int E,
                               void* stream) {
   CEB_REQUIRE(dy_bf16 && x && gamma && mean && rstd && dx && dgamma && dbeta && rows > 0, "ceb_layernorm_bwd: bad arguments");
   CEB_REQUIRE(E <= 4096, "ceb_layernorm_bwd: E=%d too wide for the shared-memory partials", E);
+  const bool aligned = ((((uintptr_t)dy_bf16 | (uintptr_t)x | (uintptr_t)dx | (uintptr_t)gamma) & 15) == 0);
+  if (aligned && (E == 768 || E == 1024 || E == 1280 || E == 512 || E == 256 || E == 128)) {
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (E / 128) {
+      case 1: launch_ln_bwd_vec<1>(dy_bf16, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, st); break;
+      case 2: launch_ln_bwd_vec<2>(dy_bf16, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, st); break;
+      case 4: launch_ln_bwd_vec<4>(dy_bf16, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, st); break;
+      case 6: launch_ln_bwd_vec<6>(dy_bf16, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, st); break;
+      case 8: launch_ln_bwd_vec<8>(dy_bf16, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, st); break;
+      default: launch_ln_bwd_vec<10>(dy_bf16, x, gamma, mean, rstd, dx, dgamma, dbeta, rows, st); break;
+    }
+    CEB_COUNT_LAUNCH(1);
+    CEB_CHECK_LAUNCH();
+    return 0;
+  }
   int blocks = ceb_num_sms() * 2;
   if (blocks > ceb_cdiv(rows, 8)) blocks = (int)ceb_cdiv(rows, 8);
   ln_bwd_kernel<<<blocks, 256, 2 * E * sizeof(float), (cudaStream_t)stream>>>(
@@ -206,38 +340,113 @@ CEB_API int ceb_layernorm_bwd(const void* dy_bf16, const float* x, const float* 
 }
 
 // ------------------------------------------------------------------ tanh-GELU (bf16)
+// tanh.approx.f32 (one MUFU op, relative error ~2^-11) is below bf16's 2^-8 output precision.
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float gelu_tanh(float x) {
   const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-  return 0.5f * x * (1.f + tanhf(u));
+  return 0.5f * x * (1.f + tanh_fast(u));
 }
 __device__ __forceinline__ float gelu_tanh_grad(float x) {
   const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-  const float t = tanhf(u);
+  const float t = tanh_fast(u);
   const float du = 0.7978845608028654f * (1.f + 3.f * 0.044715f * x * x);
   return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
 }
+__device__ __forceinline__ uint32_t gelu_pair(uint32_t xr, uint32_t gr, bool bwd) {
+  const float2 v = __bfloat1622float2(*(const __nv_bfloat162*)&xr);
+  float2 r;
+  if (bwd) {
+    const float2 g = __bfloat1622float2(*(const __nv_bfloat162*)&gr);
+    r.x = g.x * gelu_tanh_grad(v.x); r.y = g.y * gelu_tanh_grad(v.y);
+  } else {
+    r.x = gelu_tanh(v.x); r.y = gelu_tanh(v.y);
+  }
+  const __nv_bfloat162 h = __floats2bfloat162_rn(r.x, r.y);
+  return *(const uint32_t*)&h;
+}
+// VEC = 4: 16-byte accesses (8 bf16) when all pointers are 16-byte aligned; VEC = 1: bf16 pairs.
+template <int VEC>
 __global__ void __launch_bounds__(256)
-gelu_kernel(const __nv_bfloat162* __restrict__ x, const __nv_bfloat162* __restrict__ dy, __nv_bfloat162* __restrict__ out,
-            int64_t n2) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
-    const float2 v = __bfloat1622float2(x[i]);
-    float2 r;
-    if (dy) {
-      const float2 g = __bfloat1622float2(dy[i]);
-      r.x = g.x * gelu_tanh_grad(v.x); r.y = g.y * gelu_tanh_grad(v.y);
+gelu_kernel(const uint32_t* __restrict__ x, const uint32_t* __restrict__ dy, uint32_t* __restrict__ out, int64_t n2) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * VEC;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC; i < n2; i += stride) {
+    if (VEC == 4 && i + 4 <= n2) {
+      const uint4 xv = *(const uint4*)(x + i);
+      uint4 gv = make_uint4(0, 0, 0, 0);
+      if (dy) gv = *(const uint4*)(dy + i);
+      uint4 o;
+      o.x = gelu_pair(xv.x, gv.x, dy != nullptr); o.y = gelu_pair(xv.y, gv.y, dy != nullptr);
+      o.z = gelu_pair(xv.z, gv.z, dy != nullptr); o.w = gelu_pair(xv.w, gv.w, dy != nullptr);
+      *(uint4*)(out + i) = o;
     } else {
-      r.x = gelu_tanh(v.x); r.y = gelu_tanh(v.y);
+      for (int64_t j = i; j < n2 && j < i + VEC; ++j) out[j] = gelu_pair(x[j], dy ? dy[j] : 0u, dy != nullptr);
     }
-    out[i] = __floats2bfloat162_rn(r.x, r.y);
   }
 }
 
 // out = gelu(x) when dy is NULL, else out = dy * gelu'(x); bf16, n even
 CEB_API int ceb_gelu_bf16(const void* x, const void* dy, void* out, int64_t n, void* stream) {
   CEB_REQUIRE(x && out && n > 0 && n % 2 == 0, "ceb_gelu_bf16: need n even");
-  gelu_kernel<<<ceb_grid_for(n / 2, 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat162*)x, (const __nv_bfloat162*)dy,
-                                                                         (__nv_bfloat162*)out, n / 2);
+  const bool aligned = ((((uintptr_t)x | (uintptr_t)dy | (uintptr_t)out) & 15) == 0);
+  if (aligned)
+    gelu_kernel<4><<<ceb_grid_for(ceb_cdiv(n / 2, 4), 256), 256, 0, (cudaStream_t)stream>>>(
+        (const uint32_t*)x, (const uint32_t*)dy, (uint32_t*)out, n / 2);
+  else
+    gelu_kernel<1><<<ceb_grid_for(n / 2, 256), 256, 0, (cudaStream_t)stream>>>(
+        (const uint32_t*)x, (const uint32_t*)dy, (uint32_t*)out, n / 2);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ column sums (bias gradients)
+// out[c] += sum_r x[r][c] for bf16 x [rows][ld]; cols % 8 == 0, 16-byte aligned rows.  Replaces the
+// `.float().sum(0)` pair (an fp32 copy of the whole gradient plus a reduction) behind every
+// bias gradient.  Block = 32 column groups (8 columns = one 16-byte load each) x 8 row lanes.
+__global__ void __launch_bounds__(256)
+colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int64_t ld, int64_t rows, int cols, float* __restrict__ out) {
+  __shared__ float sh[8][256 + 8];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + tx) * 8;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c0 < cols) {
+    for (int64_t r = (int64_t)blockIdx.y * 8 + ty; r < rows; r += (int64_t)gridDim.y * 8) {
+      const uint4 v = *(const uint4*)(x + r * ld + c0);
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __bfloat1622float2(*(const __nv_bfloat162*)&w[j]);
+        acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sh[ty][tx * 8 + j] = acc[j];
+  __syncthreads();
+  const int c = threadIdx.x;                 // 256 columns per block
+  float s = 0.f;
+#pragma unroll
+  for (int y = 0; y < 8; ++y) s += sh[y][c];
+  const int col = blockIdx.x * 256 + c;
+  if (col < cols) atomicAdd(out + col, s);
+}
+
+CEB_API int ceb_colsum_bf16(const void* x_bf16, int64_t ld, int64_t rows, int cols, float* out, void* stream) {
+  CEB_REQUIRE(x_bf16 && out && rows > 0 && cols > 0, "ceb_colsum_bf16: bad arguments");
+  CEB_REQUIRE(cols % 8 == 0 && ld % 8 == 0 && (((uintptr_t)x_bf16) & 15) == 0,
+              "ceb_colsum_bf16: need cols %% 8 == 0, ld %% 8 == 0 and a 16-byte aligned base (cols=%d ld=%lld)", cols,
+              (long long)ld);
+  const int gx = (int)ceb_cdiv(cols, 256);
+  int gy = (int)ceb_cdiv(4 * ceb_num_sms(), gx);
+  if (gy > ceb_cdiv(rows, 8)) gy = (int)ceb_cdiv(rows, 8);
+  if (gy < 1) gy = 1;
+  colsum_bf16_kernel<<<dim3(gx, gy), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x_bf16, ld, rows, cols, out);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;

@@ -31,6 +31,47 @@ CEB_API int ceb_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stre
   return 0;
 }
 
+// dst[c][r] (bf16, row stride ldo >= R) = src[r][c] (fp32 [R][C] row-major): the K-major copy of a
+// weight that is stored MN-major for the GEMM at hand (GPT-2 Conv1D [in][out] in the forward pass,
+// the tied LM-head / embedding matrix [V][E] in its data-gradient GEMM).  64 x 64 tiles through
+// shared memory; loads are 256-byte row pieces, stores 128-byte row pieces of bf16 pairs.
+__global__ void __launch_bounds__(256)
+cast_transpose_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int R, int C, int64_t ldo) {
+  __shared__ float tile[64][65];
+  const int r0 = blockIdx.y * 64, c0 = blockIdx.x * 64;
+  const int t = threadIdx.x;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = (t >> 4) + 16 * i, c = (t & 15) * 4;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      tile[r][c + j] = (r0 + r < R && c0 + c + j < C) ? src[(int64_t)(r0 + r) * C + c0 + c + j] : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = (t >> 5) + 8 * i, r = (t & 31) * 2;
+    if (c0 + c >= C) continue;
+    __nv_bfloat16* o = dst + (int64_t)(c0 + c) * ldo + r0 + r;
+    if (r0 + r + 1 < R) {
+      *(__nv_bfloat162*)o = __floats2bfloat162_rn(tile[r][c], tile[r + 1][c]);
+    } else if (r0 + r < R) {
+      *o = __float2bfloat16(tile[r][c]);
+    }
+  }
+}
+
+CEB_API int ceb_cast_transpose_f32_bf16(const float* src, void* dst_bf16, int R, int C, int64_t ldo, void* stream) {
+  CEB_REQUIRE(src && dst_bf16 && R > 0 && C > 0, "ceb_cast_transpose_f32_bf16: bad arguments");
+  CEB_REQUIRE(ldo >= R && ldo % 2 == 0 && (((uintptr_t)dst_bf16) & 3) == 0,
+              "ceb_cast_transpose_f32_bf16: need an even ldo >= R (ldo=%lld R=%d)", (long long)ldo, R);
+  dim3 grid((unsigned)ceb_cdiv(C, 64), (unsigned)ceb_cdiv(R, 64));
+  cast_transpose_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst_bf16, R, C, ldo);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
 // dgrad weights: dst[ci][2-r][2-s][co] = src[co][r][s][ci]  (fp32 or bf16 source -> bf16)
 template <typename T>
 __global__ void __launch_bounds__(256)

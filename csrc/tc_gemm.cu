@@ -382,24 +382,41 @@ static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensor
   CEB_REQUIRE(false, "unsupported tile configuration (N tile %d, mode %d)", bn, mode);
 }
 
-// C[M,N] = act(A[M,K] * B[N,K]^T + bias).  A, B bf16 row-major (K contiguous), K % 8 == 0,
-// N % 8 == 0.  out_mode 0: bf16 C, 1: fp32 C, 2: fp32 C += (atomic).
+// C[M,N] (row stride ldc) = act(A[M,K] (row stride lda) * B[N,K]^T (row stride ldb) + bias).
+// A, B bf16, K contiguous; lda, ldb multiples of 8 elements (16-byte rows for TMA), ldc a multiple
+// of 8 (bf16 C) / 4 (fp32 C); M, N, K themselves are arbitrary: TMA zero-fills the K / N tails and
+// the epilogue bounds its stores -- this is how the 50 262-row LM head runs without padding the
+// embedding matrix (logits live in a buffer with ldc = 50 264).
+// out_mode 0: bf16 C, 1: fp32 C, 2: fp32 C += (atomic).
+CEB_API int ceb_gemm_bf16_tn_ld(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M,
+                                int N, int K, const float* bias, int relu, int out_mode, void* stream) {
+  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_tn_ld: bad arguments");
+  CEB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && lda >= K && ldb >= K,
+              "ceb_gemm_bf16_tn_ld: lda, ldb must be multiples of 8 and >= K (lda=%lld ldb=%lld K=%d)", (long long)lda,
+              (long long)ldb, K);
+  CEB_REQUIRE(ldc >= N && ldc % (out_mode == 0 ? 8 : 4) == 0 && ldc < (1ll << 31),
+              "ceb_gemm_bf16_tn_ld: ldc=%lld must be >= N=%d and a multiple of %d", (long long)ldc, N, out_mode == 0 ? 8 : 4);
+  CEB_REQUIRE((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0, "ceb_gemm_bf16_tn_ld: operands must be 16-byte aligned");
+  const int bn = pick_bn(N);
+  CUtensorMap ta, tb;
+  uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * 2};
+  uint32_t ba[2] = {BK, BM};
+  if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
+  uint64_t db[2] = {(uint64_t)K, (uint64_t)N}, sb[1] = {(uint64_t)ldb * 2};
+  uint32_t bb[2] = {BK, (uint32_t)bn};
+  if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, bb)) return e;
+  TcParams p{};
+  p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = (int)ldc; p.k_steps = (int)ceb_cdiv(K, BK);
+  p.relu = relu; p.out_fp32 = out_mode; p.conv = 0;
+  return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream);
+}
+
+// Dense form of the above (lda = ldb = K, ldc = N): K % 8 == 0, N % 8 == 0.
 CEB_API int ceb_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, const float* bias,
                              int relu, int out_mode, void* stream) {
   CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_tn: bad arguments");
   CEB_REQUIRE(K % 8 == 0 && N % 8 == 0, "ceb_gemm_bf16_tn: K and N must be multiples of 8 (K=%d N=%d)", K, N);
-  const int bn = pick_bn(N);
-  CUtensorMap ta, tb;
-  uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)K * 2};
-  uint32_t ba[2] = {BK, BM};
-  if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
-  uint64_t db[2] = {(uint64_t)K, (uint64_t)N}, sb[1] = {(uint64_t)K * 2};
-  uint32_t bb[2] = {BK, (uint32_t)bn};
-  if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, bb)) return e;
-  TcParams p{};
-  p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = N; p.k_steps = (int)ceb_cdiv(K, BK);
-  p.relu = relu; p.out_fp32 = out_mode; p.conv = 0;
-  return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream);
+  return ceb_gemm_bf16_tn_ld(A, K, B, K, C, N, M, N, K, bias, relu, out_mode, stream);
 }
 
 // C[M,N] = act(A[M,K] * B[K,N] + bias): like ceb_gemm_bf16_tn but B is row-major [K][N]

@@ -239,15 +239,22 @@ CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW
   return launch_wgrad<64, true>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
 }
 
-// C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A, B bf16 row-major.  M % 64 == N % 64 == 0.
-CEB_API int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, int N, int K, int ldc, void* stream) {
-  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_mn_acc: bad arguments");
-  CEB_REQUIRE(M % 64 == 0 && N % 64 == 0, "ceb_gemm_bf16_mn_acc: M, N must be multiples of 64 (M=%d N=%d)", M, N);
+// C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A (row stride lda), B (row stride ldb) bf16
+// with the reduction running over ROWS.  N % 64 == 0; M is arbitrary (TMA zero-fills the tail of the
+// last 128-row tile and the epilogue bounds its rows); lda, ldb multiples of 8.
+CEB_API int ceb_gemm_bf16_mn_acc_ld(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N,
+                                    int K, int ldc, void* stream) {
+  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_mn_acc_ld: bad arguments");
+  CEB_REQUIRE(N % 64 == 0, "ceb_gemm_bf16_mn_acc_ld: N must be a multiple of 64 (N=%d)", N);
+  CEB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && lda >= M && ldb >= N && ldc >= N,
+              "ceb_gemm_bf16_mn_acc_ld: need lda, ldb multiples of 8 with lda >= M, ldb >= N, ldc >= N "
+              "(lda=%lld ldb=%lld ldc=%d)", (long long)lda, (long long)ldb, ldc);
+  CEB_REQUIRE((((uintptr_t)A | (uintptr_t)B) & 15) == 0, "ceb_gemm_bf16_mn_acc_ld: operands must be 16-byte aligned");
   CUtensorMap ta, tb;
-  uint64_t da[2] = {(uint64_t)M, (uint64_t)K}, sa[1] = {(uint64_t)M * 2};
+  uint64_t da[2] = {(uint64_t)M, (uint64_t)K}, sa[1] = {(uint64_t)lda * 2};
   uint32_t ba[2] = {64, WG_KPIX};
   if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
-  uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)N * 2};
+  uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)ldb * 2};
   if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, ba)) return e;
   const int bn = (N % 128 == 0) ? 128 : 64;
   WgParams p{};
@@ -264,4 +271,11 @@ CEB_API int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, 
   split = (int)ceb_cdiv(p.k_steps_total, p.k_per_cta);
   if (bn == 128) return launch_wgrad<128, false>(ta, tb, p, co_tiles, split, (cudaStream_t)stream);
   return launch_wgrad<64, false>(ta, tb, p, co_tiles, split, (cudaStream_t)stream);
+}
+
+// Dense form (lda = M, ldb = N): M % 64 == N % 64 == 0.
+CEB_API int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, int N, int K, int ldc, void* stream) {
+  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_mn_acc: bad arguments");
+  CEB_REQUIRE(M % 64 == 0 && N % 64 == 0, "ceb_gemm_bf16_mn_acc: M, N must be multiples of 64 (M=%d N=%d)", M, N);
+  return ceb_gemm_bf16_mn_acc_ld(A, M, B, N, C, M, N, K, ldc, stream);
 }

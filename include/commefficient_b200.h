@@ -145,6 +145,14 @@ int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H
 /* dst[ci][2-r][2-s][co] (bf16) = w[co][r][s][ci] (fp32): weights of the data-gradient convolution. */
 int ceb_conv_w_dgrad_layout(const float* w_krsc, void* dst_bf16, int Cout, int Cin, void* stream);
 int ceb_cast_f32_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
+/* dst[c][r] (bf16, row stride ldo >= R, ldo even) = src[r][c] (fp32 [R][C]): the K-major bf16 copy of
+ * a weight stored the other way round (GPT-2 Conv1D [in][out]; the tied LM head in its dgrad). */
+int ceb_cast_transpose_f32_bf16(const float* src, void* dst_bf16, int R, int C, int64_t ldo, void* stream);
+/* ceb_gemm_bf16_tn with explicit row strides: lda, ldb multiples of 8 and >= K, ldc >= N and a
+ * multiple of 8 (bf16 C) or 4 (fp32 C); M, N, K arbitrary (TMA zero-fills the tails, stores are
+ * bounded).  All three bases 16-byte aligned. */
+int ceb_gemm_bf16_tn_ld(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N,
+                        int K, const float* bias, int relu, int out_mode, void* stream);
 /* bf16 NHWC max pooling (k = 2 or 4) and its backward; relu_mask != 0 also applies the ReLU
  * backward of y (reference: resnet9.py:48-56,95). */
 int ceb_maxpool_nhwc_bf16(const void* y, void* out, int N, int H, int W, int C, int k, void* stream);
@@ -159,6 +167,9 @@ int ceb_im2col3x3_c3(const float* x_nhwc, void* A_bf16, int N, int H, int W, voi
 /* C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A, B bf16 row-major ("both operands
  * MN-major": linear-layer weight gradients dW = dY^T X).  M % 64 == N % 64 == 0; split-K. */
 int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, int N, int K, int ldc, void* stream);
+/* Same with explicit operand row strides (multiples of 8, lda >= M, ldb >= N); M arbitrary, N % 64 == 0. */
+int ceb_gemm_bf16_mn_acc_ld(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N, int K,
+                            int ldc, void* stream);
 /* dW[Cout][3][3][Cin] (fp32) += sum_p dz[p][co] * x[p + (r-1,s-1)][ci]; dz, x bf16 NHWC.  Both GEMM
  * operands are MN-major (pixels are the reduction dimension); split-K with vector atomics.
  * Cin % 64 == 0, Cout % 64 == 0, W divides 64. */
@@ -182,6 +193,9 @@ int ceb_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, c
                       float* dx, float* dgamma, float* dbeta, int64_t rows, int E, void* stream);
 /* tanh-GELU on bf16: out = gelu(x) (dy NULL) or dy * gelu'(x). */
 int ceb_gelu_bf16(const void* x, const void* dy, void* out, int64_t n, void* stream);
+/* out[c] (fp32) += sum over rows of x[r][c]; x bf16 [rows][ld], cols % 8 == 0, ld % 8 == 0, 16-byte
+ * aligned base (bias gradients without an fp32 copy of the activation gradient). */
+int ceb_colsum_bf16(const void* x_bf16, int64_t ld, int64_t rows, int cols, float* out, void* stream);
 
 /* ---- peer-memory collectives over NVLink, fused with the server update ---------
  * (reference: the single NCCL reduce + host-side weight update/download,

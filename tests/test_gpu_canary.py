@@ -99,11 +99,16 @@ def test_cast_and_relu_bwd_stay_in_bounds(numel):
 def test_bad_shapes_are_rejected_not_run():
     a = torch.randn(64, 64, device=DEV).bfloat16()
     b = torch.randn(65, 64, device=DEV).bfloat16()
-    with pytest.raises(native.NativeError):
-        tc.gemm_tn(a, b)
-    with pytest.raises(native.NativeError):
-        tc.gemm_mn_acc(torch.randn(8, 10, device=DEV).bfloat16(), torch.randn(8, 64, device=DEV).bfloat16(),
-                       torch.zeros(10, 64, device=DEV))
+    c = torch.empty(64, 65, device=DEV, dtype=torch.bfloat16)
+    with pytest.raises(native.NativeError):          # dense entry point: N must be a multiple of 8
+        native.call("ceb_gemm_bf16_tn", native.ptr(a), native.ptr(b), native.ptr(c), 64, 65, 64, None, 0, 0,
+                    native.stream_ptr(a.device))
+    with pytest.raises(native.NativeError):          # strided entry point: ldc not a multiple of 8
+        native.call("ceb_gemm_bf16_tn_ld", native.ptr(a), 64, native.ptr(b), 64, native.ptr(c), 65, 64, 65, 64, None,
+                    0, 0, native.stream_ptr(a.device))
+    with pytest.raises(native.NativeError):          # N of the MN-major GEMM must be a multiple of 64
+        tc.gemm_mn_acc(torch.randn(8, 64, device=DEV).bfloat16(), torch.randn(8, 72, device=DEV).bfloat16(),
+                       torch.zeros(64, 72, device=DEV))
 
 
 @pytest.mark.parametrize("n,h,c,k", [(3, 32, 128, 2), (2, 8, 512, 2), (5, 4, 512, 4)])

@@ -243,3 +243,92 @@ def test_ce_layernorm_gelu_kernels_match_torch():
     hr = h.detach().float().requires_grad_(True)
     F.gelu(hr, approximate="tanh").sum().backward()
     assert _rel_err(h.grad, hr.grad) < 1e-2
+
+
+@pytest.mark.parametrize("M,N,K", [(300, 203, 128), (129, 50262, 64), (64, 70, 200)])
+def test_gemm_tn_row_padded_operands(M, N, K):
+    """Arbitrary N / K: operands and result live in buffers whose rows are padded to 16 bytes."""
+    g = torch.Generator(device=DEV).manual_seed(N)
+    a = tc.padded_empty(M, K, torch.bfloat16, DEV)
+    b = tc.padded_empty(N, K, torch.bfloat16, DEV)
+    a.copy_(torch.randn(M, K, device=DEV, generator=g))
+    b.copy_(torch.randn(N, K, device=DEV, generator=g))
+    want = a.float() @ b.float().t()
+    got = tc.gemm_tn(a, b)
+    assert got.shape == (M, N) and got.stride(0) % 8 == 0
+    assert _rel_err(got, want) < 5e-3
+    got32 = tc.gemm_tn(a, b, out_dtype=torch.float32)
+    assert _rel_err(got32, want) < 1e-5
+
+
+@pytest.mark.parametrize("K,M,N", [(500, 203, 128), (300, 50262, 64), (64, 1, 64)])
+def test_gemm_mn_acc_arbitrary_m(K, M, N):
+    g = torch.Generator(device=DEV).manual_seed(M)
+    a = tc.padded_empty(K, M, torch.bfloat16, DEV)
+    a.copy_(torch.randn(K, M, device=DEV, generator=g))
+    b = torch.randn(K, N, device=DEV, generator=g).bfloat16()
+    c = torch.ones(M, N, device=DEV)
+    tc.gemm_mn_acc(a, b, c)
+    assert _rel_err(c, 1 + a.float().t() @ b.float()) < 1e-5
+
+
+@pytest.mark.parametrize("R,C", [(768, 2304), (50262, 768), (65, 130), (3, 7)])
+def test_cast_transpose(R, C):
+    src = torch.randn(R, C, device=DEV)
+    out = tc.cast_transpose_bf16(src)
+    assert out.shape == (C, R) and out.stride(0) % 8 == 0
+    assert torch.equal(out, src.t().bfloat16())
+
+
+@pytest.mark.parametrize("rows,cols", [(16384, 768), (1000, 2304), (7, 8), (333, 3072)])
+def test_colsum(rows, cols):
+    x = torch.randn(rows, cols, device=DEV).bfloat16()
+    out = torch.ones(cols, device=DEV)
+    tc.colsum_acc(x, out)
+    torch.testing.assert_close(out, 1 + x.float().sum(0), rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.parametrize("n_out,conv1d", [(203, False), (50262, False), (192, True), (128, False)])
+def test_linear_autograd_any_width(n_out, conv1d):
+    """_LinearFn vs fp32 torch for nn.Linear and Conv1D storage, including widths that are not a
+    multiple of 8 (row-padded outputs and gradients, the LM-head case)."""
+    torch.manual_seed(n_out)
+    K, M = 128, 96
+    store = (torch.randn(K, n_out, device=DEV) * 0.05) if conv1d else (torch.randn(n_out, K, device=DEV) * 0.05)
+    store.requires_grad_(True)
+    weight = store.t() if conv1d else store
+    bias = torch.randn(n_out, device=DEV, requires_grad=True) if n_out % 8 == 0 else None
+    x = torch.randn(M, K, device=DEV).bfloat16().requires_grad_(True)
+    assert tc.linear_supported(x, weight)
+    y = tc.linear(x, weight, bias)
+    assert y.shape == (M, n_out)
+    dy = torch.randn(M, n_out, device=DEV)
+    (y.float() * dy).sum().backward()
+    xr = x.detach().float().requires_grad_(True)
+    sr = store.detach().clone().requires_grad_(True)
+    wr = sr.t() if conv1d else sr
+    br = bias.detach().clone().requires_grad_(True) if bias is not None else None
+    yr = F.linear(xr, wr, br)
+    (yr * dy).sum().backward()
+    assert _rel_err(y, yr) < 1e-2
+    assert _rel_err(x.grad, xr.grad) < 2e-2
+    assert _rel_err(store.grad, sr.grad) < 2e-2
+    if bias is not None:
+        assert _rel_err(bias.grad, br.grad) < 2e-2
+
+
+def test_layernorm_bwd_widths():
+    from commefficient_b200.ops import tfm
+    for E in (128, 768, 1024, 96):
+        x = torch.randn(517, E, device=DEV, requires_grad=True)
+        ln = torch.nn.LayerNorm(E).to(DEV)
+        torch.nn.init.normal_(ln.weight, 1.0, 0.1)
+        y = tfm.layer_norm(x, ln.weight, ln.bias, ln.eps)
+        dy = torch.randn(517, E, device=DEV).bfloat16()
+        y.backward(dy)
+        xr = x.detach().clone().requires_grad_(True)
+        ln2 = torch.nn.LayerNorm(E).to(DEV)
+        ln2.load_state_dict(ln.state_dict())
+        ln2(xr).backward(dy.float())
+        assert _rel_err(x.grad, xr.grad) < 1e-3, E
+        assert _rel_err(ln.weight.grad, ln2.weight.grad) < 1e-3 and _rel_err(ln.bias.grad, ln2.bias.grad) < 1e-3, E
