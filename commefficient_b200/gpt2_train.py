@@ -25,7 +25,7 @@ from torch.utils.data import DataLoader
 from . import data_utils
 from .data_utils import ATTR_TO_SPECIAL_TOKEN, FedPERSONA, FedSampler, SimpleTokenizer, personachat_collate_fn
 from .fed_aggregator import FedModel, FedOptimizer
-from .models.gpt2 import GPT2Config, GPT2DoubleHeadsModel, OpenAIGPTDoubleHeadsModel, shifted_lm_rows
+from .models.gpt2 import GPT2Config, GPT2DoubleHeadsModel, OpenAIGPTDoubleHeadsModel
 from .parallel.runtime import init_runtime
 from .utils import Logger, PiecewiseLinear, TableLogger, Timer, make_logdir, parse_args, steps_per_epoch, union
 
@@ -60,7 +60,7 @@ def compute_loss_train(model, batch, args):
     """``lm_coef * lm_loss + mc_coef * mc_loss``; no metrics (returns a 1-tuple)."""
     input_ids, mc_token_ids, lm_labels, mc_labels, token_type_ids = batch
     lm_loss, mc_loss, *_ = model(input_ids, token_type_ids=token_type_ids, mc_token_ids=mc_token_ids,
-                                 mc_labels=mc_labels, lm_labels=lm_labels)
+                                 mc_labels=mc_labels, lm_labels=lm_labels, need_logits=False)
     return lm_loss * args.lm_coef + mc_loss * args.mc_coef,
 
 
@@ -70,9 +70,10 @@ def _per_sample_train(model, batch, args, seg, num_segments):
     -- exactly what ``compute_loss_train`` returns for that client alone, so the worker can run all
     of a rank's clients in one forward/backward."""
     input_ids, mc_token_ids, lm_labels, mc_labels, token_type_ids = batch
-    lm_logits, mc_logits, *_ = model(input_ids, token_type_ids=token_type_ids, mc_token_ids=mc_token_ids)
+    _, mc_logits, hidden = model(input_ids, token_type_ids=token_type_ids, mc_token_ids=mc_token_ids,
+                                 need_logits=False, return_hidden=True)
     B = input_ids.shape[0]
-    rows, mask = shifted_lm_rows(lm_logits, lm_labels)          # [B*C, T]
+    rows, mask = model.lm_rows(hidden, lm_labels)      # [B*C, T]; LM head only where labeled
     tok_loss = rows.view(B, -1)
     tok_cnt = mask.view(B, -1).sum(1).float()
     n_i = torch.zeros(num_segments, device=seg.device).index_add_(0, seg, torch.ones_like(tok_cnt))

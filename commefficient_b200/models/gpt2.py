@@ -219,16 +219,31 @@ class GPT2DoubleHeadsModel(nn.Module):
         rows, mask = shifted_lm_rows(lm_logits, lm_labels)
         return rows.sum() / mask.sum().clamp_min(1)
 
+    def lm_rows(self, hidden, lm_labels):
+        """Per-position shifted LM cross-entropy ``[N, T]`` and its mask straight from the hidden
+        states: the LM head only runs for positions that carry a label (``ops/nn.py``)."""
+        T = lm_labels.shape[-1]
+        shifted = _shift_labels(lm_labels)
+        rows = nnops.lm_head_cross_entropy(hidden.reshape(-1, hidden.shape[-1]), self.lm_head.weight,
+                                           shifted.reshape(-1), ignore_index=-1)
+        return rows.view(-1, T), (shifted != -1)
+
     # -- forward -------------------------------------------------------------------
     def forward(self, input_ids, token_type_ids=None, mc_token_ids=None, lm_labels=None, mc_labels=None,
-                **_ignored):
+                need_logits=True, return_hidden=False, **_ignored):
+        """Outputs follow pytorch_transformers: ``([lm_loss], [mc_loss], lm_logits, mc_logits)``.
+        ``need_logits=False`` leaves ``lm_logits`` as None and computes the LM loss through
+        ``lm_rows`` (no ``[N*C*T, V]`` logits for unlabeled positions); ``return_hidden=True``
+        appends the final hidden states."""
         shape = input_ids.shape                      # (B, C, T)
         T = shape[-1]
         flat_ids = input_ids.reshape(-1, T)
         flat_types = token_type_ids.reshape(-1, T) if token_type_ids is not None else None
         hidden = self.transformer(flat_ids, flat_types)          # (B*C, T, E)
-        lm_logits = nnops.linear(hidden.reshape(-1, hidden.shape[-1]), self.lm_head.weight, None)
-        lm_logits = lm_logits.view(*shape, -1)
+        lm_logits = None
+        if need_logits:
+            lm_logits = nnops.linear(hidden.reshape(-1, hidden.shape[-1]), self.lm_head.weight, None)
+            lm_logits = lm_logits.view(*shape, -1)
         outputs = [lm_logits]
         mc_logits = None
         if mc_token_ids is not None:
@@ -238,8 +253,21 @@ class GPT2DoubleHeadsModel(nn.Module):
             mc_loss = F.cross_entropy(mc_logits.float().view(-1, mc_logits.shape[-1]), mc_labels.view(-1))
             outputs.insert(0, mc_loss)
         if lm_labels is not None:
-            outputs.insert(0, self.lm_loss(lm_logits, lm_labels))
+            if lm_logits is not None:
+                outputs.insert(0, self.lm_loss(lm_logits, lm_labels))
+            else:
+                rows, mask = self.lm_rows(hidden, lm_labels)
+                outputs.insert(0, rows.sum() / mask.sum().clamp_min(1))
+        if return_hidden:
+            outputs.append(hidden)
         return tuple(outputs)
+
+
+def _shift_labels(lm_labels):
+    """Position t is scored against label t+1; the last position is ignored."""
+    T = lm_labels.shape[-1]
+    flat = lm_labels.reshape(-1, T)
+    return torch.cat([flat[:, 1:], flat.new_full((flat.shape[0], 1), -1)], dim=1)
 
 
 def shifted_lm_rows(lm_logits, lm_labels):
@@ -247,8 +275,7 @@ def shifted_lm_rows(lm_logits, lm_labels):
     Position t is scored against label t+1; instead of slicing the logits (which would copy the
     whole ``[N, T, V]`` tensor) the LABELS are shifted and the last position is ignored."""
     T = lm_labels.shape[-1]
-    flat_labels = lm_labels.reshape(-1, T)
-    shifted = torch.cat([flat_labels[:, 1:], flat_labels.new_full((flat_labels.shape[0], 1), -1)], dim=1)
+    shifted = _shift_labels(lm_labels)
     logits2d = lm_logits.reshape(-1, lm_logits.shape[-1])
     rows = nnops.cross_entropy_rows(logits2d, shifted.reshape(-1), ignore_index=-1)
     return rows.view(-1, T), (shifted != -1)

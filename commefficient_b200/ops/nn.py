@@ -77,3 +77,13 @@ def cross_entropy_rows(logits, labels, ignore_index=-1):
         from . import tfm
         return tfm.cross_entropy_rows(logits, labels, ignore_index)
     return F.cross_entropy(logits.float(), labels, ignore_index=ignore_index, reduction="none")
+
+
+def lm_head_cross_entropy(hidden2d, weight, labels, ignore_index=-1):
+    """Per-row cross-entropy of ``hidden2d @ weight.T`` (0 where ``labels == ignore_index``).  Native
+    path: one fused function that only computes the rows with a label (``ops/tc.py:_LMHeadCE``)."""
+    if _use_native(hidden2d):
+        from . import tc
+        if tc.lm_head_supported(hidden2d, weight):
+            return tc.lm_head_ce(hidden2d, weight, labels, ignore_index)
+    return cross_entropy_rows(linear(hidden2d, weight, None), labels, ignore_index)

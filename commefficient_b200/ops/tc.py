@@ -42,6 +42,14 @@ native.register_signatures({
                                      native.c_ptr], native.c_i32),
     "ceb_colsum_bf16": ([native.c_ptr, native.c_i64, native.c_i64, native.c_i32, native.c_ptr, native.c_ptr],
                         native.c_i32),
+    "ceb_gemm_bf16_tn_rows": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i64,
+                               native.c_i32, native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
+                               native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_gemm_bf16_mn_acc_rows": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i32,
+                                   native.c_i32, native.c_i32, native.c_i32, native.c_ptr, native.c_ptr],
+                                  native.c_i32),
+    "ceb_softmax_ce_bwd_rows": ([native.c_ptr, native.c_ptr, native.c_i64, native.c_i64, native.c_i32, native.c_ptr,
+                                 native.c_i64, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr], native.c_i32),
 })
 
 _OUT = {torch.bfloat16: 0, torch.float32: 1}
@@ -351,6 +359,86 @@ class _LinearFn(torch.autograd.Function):
 
 def linear(x, weight, bias=None):
     return _LinearFn.apply(x, weight, bias)
+
+
+# ---------------------------------------------------------------------------- LM head + cross-entropy
+def lm_head_supported(hidden2d, weight) -> bool:
+    return (hidden2d.is_cuda and hidden2d.dim() == 2 and weight.dim() == 2 and weight.is_contiguous()
+            and weight.dtype == torch.float32 and weight.shape[1] == hidden2d.shape[1]
+            and weight.shape[1] % 64 == 0 and weight.shape[0] >= 64)
+
+
+class _LMHeadCE(torch.autograd.Function):
+    """Per-row cross-entropy of ``hidden @ W^T`` against ``labels`` (0 where ``labels == ignore``),
+    computing logits ONLY for the rows whose label is not ignored.  In PersonaChat-style batches
+    just the reply tokens of the gold candidate carry a label (reference:
+    /root/reference/CommEfficient/gpt2_train.py:76-99 runs the full ``[N*C*T, 50 262]`` head and lets
+    ``ignore_index=-1`` drop most of it); rows with an ignored label contribute neither loss nor
+    gradient, so skipping them is exact.  Rows are compacted on the device (valid first, stable) and
+    the three GEMMs plus the CE backward take the valid-row count from a DEVICE int, so nothing here
+    synchronises with the host and the whole thing can sit inside a CUDA graph.  The logits buffer
+    (row stride padded to 8) is overwritten in place by its own gradient."""
+
+    @staticmethod
+    def forward(ctx, hidden, weight, labels, ignore_index):
+        from . import tfm  # noqa: F401  (registers the CE signatures)
+        R, E = hidden.shape
+        V = weight.shape[0]
+        dev = hidden.device
+        labels = labels.reshape(-1)
+        valid = labels != ignore_index
+        order = torch.argsort((~valid).to(torch.uint8), stable=True)
+        nvalid = valid.sum().to(torch.int32).reshape(1)
+        h_sel = hidden.detach().to(torch.bfloat16).index_select(0, order)
+        lab_sel = labels.index_select(0, order).contiguous()
+        wb = cast_bf16(weight.detach())
+        logits = padded_empty(R, V, torch.bfloat16, dev)
+        st = native.stream_ptr(dev)
+        native.call("ceb_gemm_bf16_tn_rows", native.ptr(h_sel), h_sel.stride(0), native.ptr(wb), wb.stride(0),
+                    native.ptr(logits), logits.stride(0), R, V, E, None, 0, 0, native.ptr(nvalid), st)
+        loss_sel = torch.empty(R, dtype=torch.float32, device=dev)
+        lse = torch.empty(R, dtype=torch.float32, device=dev)
+        native.call("ceb_softmax_ce_fwd", native.ptr(logits), logits.stride(0), R, V, native.ptr(lab_sel),
+                    int(ignore_index), native.ptr(loss_sel), native.ptr(lse), st)
+        loss = torch.empty(R, dtype=torch.float32, device=dev).index_copy_(0, order, loss_sel)
+        ctx.save_for_backward(h_sel, lab_sel, lse, logits, order, nvalid)
+        ctx.weight = weight
+        ctx.ignore_index = int(ignore_index)
+        ctx.h_dtype = hidden.dtype
+        return loss
+
+    @staticmethod
+    def backward(ctx, gloss):
+        h_sel, lab_sel, lse, logits, order, nvalid = ctx.saved_tensors
+        weight = ctx.weight
+        R, E = h_sel.shape
+        V = weight.shape[0]
+        dev = h_sel.device
+        st = native.stream_ptr(dev)
+        g_sel = gloss.float().index_select(0, order).contiguous()
+        native.call("ceb_softmax_ce_bwd_rows", native.ptr(logits), native.ptr(logits), logits.stride(0), R, V,
+                    native.ptr(lab_sel), ctx.ignore_index, native.ptr(lse), native.ptr(g_sel), native.ptr(nvalid), st)
+        dlogits = logits
+        dh = None
+        if ctx.needs_input_grad[0]:
+            wt = cast_transpose_bf16(weight.detach())                       # [E, V], K-major for the dgrad
+            dh_sel = torch.zeros((R, E), dtype=torch.bfloat16, device=dev)
+            native.call("ceb_gemm_bf16_tn_rows", native.ptr(dlogits), dlogits.stride(0), native.ptr(wt), wt.stride(0),
+                        native.ptr(dh_sel), dh_sel.stride(0), R, E, V, None, 0, 0, native.ptr(nvalid), st)
+            dh = torch.empty_like(dh_sel).index_copy_(0, order, dh_sel).to(ctx.h_dtype)
+        dw = None
+        if ctx.needs_input_grad[1]:
+            target = weight.grad if (isinstance(weight, torch.nn.Parameter) and weight.grad is not None
+                                     and weight.grad.is_contiguous()) else None
+            acc = target if target is not None else torch.zeros_like(weight, dtype=torch.float32)
+            native.call("ceb_gemm_bf16_mn_acc_rows", native.ptr(dlogits), dlogits.stride(0), native.ptr(h_sel),
+                        h_sel.stride(0), native.ptr(acc), V, E, R, acc.stride(0), native.ptr(nvalid), st)
+            dw = None if target is not None else acc
+        return dh, dw, None, None
+
+
+def lm_head_ce(hidden2d, weight, labels, ignore_index=-1):
+    return _LMHeadCE.apply(hidden2d, weight, labels, ignore_index)
 
 
 # ---------------------------------------------------------------------------- ResNet-9 on the native kernels

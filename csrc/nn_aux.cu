@@ -100,8 +100,10 @@ ce_fwd_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int V, const
 __global__ void __launch_bounds__(CE_THREADS)
 ce_bwd_kernel(const __nv_bfloat16* __restrict__ logits, __nv_bfloat16* __restrict__ dlogits, int64_t ld, int V,
               const int64_t* __restrict__ labels, int64_t ignore_index, const float* __restrict__ lse,
-              const float* __restrict__ grow) {
+              const float* __restrict__ grow, const int* __restrict__ row_limit) {
   const int64_t row = blockIdx.x;
+  // compacted rows: nothing past the 128-row tile that holds the last valid row is ever read
+  if (row_limit && row >= (((int64_t)__ldg(row_limit) + 127) & ~(int64_t)127)) return;
   const int64_t label = labels[row];
   const bool ignored = label == ignore_index;
   const float g = ignored ? 0.f : grow[row];
@@ -154,15 +156,30 @@ CEB_API int ceb_softmax_ce_fwd(const void* logits_bf16, int64_t ld, int64_t rows
   return 0;
 }
 
-CEB_API int ceb_softmax_ce_bwd(const void* logits_bf16, void* dlogits_bf16, int64_t ld, int64_t rows, int V,
-                               const int64_t* labels, int64_t ignore_index, const float* lse, const float* grad_rows,
-                               void* stream) {
+static int ce_bwd_impl(const void* logits_bf16, void* dlogits_bf16, int64_t ld, int64_t rows, int V,
+                       const int64_t* labels, int64_t ignore_index, const float* lse, const float* grad_rows,
+                       const int* row_limit, void* stream) {
   CEB_REQUIRE(logits_bf16 && dlogits_bf16 && labels && lse && grad_rows && rows > 0 && ld % 2 == 0, "ceb_softmax_ce_bwd: bad arguments");
   ce_bwd_kernel<<<(unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)logits_bf16,
-      (__nv_bfloat16*)dlogits_bf16, ld, V, labels, ignore_index, lse, grad_rows);
+      (__nv_bfloat16*)dlogits_bf16, ld, V, labels, ignore_index, lse, grad_rows, row_limit);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
+}
+
+CEB_API int ceb_softmax_ce_bwd(const void* logits_bf16, void* dlogits_bf16, int64_t ld, int64_t rows, int V,
+                               const int64_t* labels, int64_t ignore_index, const float* lse, const float* grad_rows,
+                               void* stream) {
+  return ce_bwd_impl(logits_bf16, dlogits_bf16, ld, rows, V, labels, ignore_index, lse, grad_rows, nullptr, stream);
+}
+
+// Rows are compacted (valid labels first): rows past the 128-row tile containing row *row_limit_dev - 1
+// are skipped entirely (neither read nor written).  dlogits may alias logits (in place).
+CEB_API int ceb_softmax_ce_bwd_rows(const void* logits_bf16, void* dlogits_bf16, int64_t ld, int64_t rows, int V,
+                                    const int64_t* labels, int64_t ignore_index, const float* lse,
+                                    const float* grad_rows, const int* row_limit_dev, void* stream) {
+  CEB_REQUIRE(row_limit_dev != nullptr, "ceb_softmax_ce_bwd_rows: row_limit_dev is NULL");
+  return ce_bwd_impl(logits_bf16, dlogits_bf16, ld, rows, V, labels, ignore_index, lse, grad_rows, row_limit_dev, stream);
 }
 
 // ------------------------------------------------------------------ LayerNorm (one warp per row)

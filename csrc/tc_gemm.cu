@@ -42,6 +42,10 @@ struct TcParams {
   int H, W, cin_steps;   // cin_steps = Cin / 64
   int tile_h;            // rows of the image covered by one M tile (tile_w == W)
   int halo_bytes;        // MODE 1: bytes of one activation halo box
+  // optional device-side row count: only the M tiles covering rows [0, *m_limit) are computed
+  // (rows are compacted by the caller; lets a CUDA-graph-captured launch follow a data-dependent
+  // row count without a host round trip)
+  const int* m_limit;
 };
 
 // MODE 0: generic tile (GEMM, or convolution with one TMA box per filter tap).
@@ -89,7 +93,13 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.m_tiles * p.n_tiles;
+  int m_tiles_rt = p.m_tiles;
+  if (p.m_limit) {
+    const int lim = (__ldg(p.m_limit) + BMT - 1) / BMT;
+    m_tiles_rt = lim < m_tiles_rt ? lim : m_tiles_rt;
+  }
+  const int m_tiles = m_tiles_rt;
+  const int num_tiles = m_tiles * p.n_tiles;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmapA);
@@ -115,7 +125,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     if (lane == 0) {
       uint32_t it = 0;                                   // global k-step counter (ring position)
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
+        const int m_tile = t % m_tiles, n_tile = t / m_tiles;
         int n0 = 0, h0 = 0;
         if (p.conv) {
           const int pix0 = m_tile * BMT;
@@ -211,7 +221,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     uint32_t* stage = (uint32_t*)(epi_smem + (warp - 2) * (32 * 17 * 4));
     uint32_t local = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
-      const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
+      const int m_tile = t % m_tiles, n_tile = t / m_tiles;
       const int acc = local & 1;
       mbar_wait(tmem_full_bar + acc, (local >> 1) & 1);
       tc_fence_after();
@@ -388,8 +398,26 @@ static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensor
 // the epilogue bounds its stores -- this is how the 50 262-row LM head runs without padding the
 // embedding matrix (logits live in a buffer with ldc = 50 264).
 // out_mode 0: bf16 C, 1: fp32 C, 2: fp32 C += (atomic).
+static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
+                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream);
+
 CEB_API int ceb_gemm_bf16_tn_ld(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M,
                                 int N, int K, const float* bias, int relu, int out_mode, void* stream) {
+  return gemm_tn_impl(A, lda, B, ldb, C, ldc, M, N, K, bias, relu, out_mode, nullptr, stream);
+}
+
+// Same, but only rows [0, *m_limit_dev) are computed (rounded up to whole 128-row tiles, never past
+// M); rows beyond are left untouched.  m_limit_dev is a device int read by the kernel, so the launch
+// can sit in a CUDA graph while the row count changes from replay to replay.
+CEB_API int ceb_gemm_bf16_tn_rows(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M,
+                                  int N, int K, const float* bias, int relu, int out_mode, const int* m_limit_dev,
+                                  void* stream) {
+  CEB_REQUIRE(m_limit_dev != nullptr, "ceb_gemm_bf16_tn_rows: m_limit_dev is NULL");
+  return gemm_tn_impl(A, lda, B, ldb, C, ldc, M, N, K, bias, relu, out_mode, m_limit_dev, stream);
+}
+
+static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
+                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream) {
   CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_tn_ld: bad arguments");
   CEB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && lda >= K && ldb >= K,
               "ceb_gemm_bf16_tn_ld: lda, ldb must be multiples of 8 and >= K (lda=%lld ldb=%lld K=%d)", (long long)lda,
@@ -407,7 +435,7 @@ CEB_API int ceb_gemm_bf16_tn_ld(const void* A, int64_t lda, const void* B, int64
   if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, bb)) return e;
   TcParams p{};
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = (int)ldc; p.k_steps = (int)ceb_cdiv(K, BK);
-  p.relu = relu; p.out_fp32 = out_mode; p.conv = 0;
+  p.relu = relu; p.out_fp32 = out_mode; p.conv = 0; p.m_limit = m_limit;
   return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream);
 }
 

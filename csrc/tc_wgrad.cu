@@ -30,6 +30,7 @@ struct WgParams {
   int tile_h, tile_n;    // box geometry of a 64-pixel step (tile_w == W)
   int ldw;               // row stride of dW (9*Cin for a convolution, ldc for a plain GEMM)
   int vec_ok;            // dW is 16-byte aligned (it is a slice of the flat gradient buffer): vector atomics allowed
+  const int* k_limit;    // optional device-side count of reduction rows (see ceb_gemm_bf16_mn_acc_rows)
 };
 
 template <int BN>
@@ -69,7 +70,9 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
   const int r = CONV ? (blockIdx.x / p.ci_tiles) % 3 : 0;
   const int co_tile = CONV ? blockIdx.x / (p.ci_tiles * 3) : blockIdx.x / p.ci_tiles;
   const int ks_begin = blockIdx.y * p.k_per_cta;
-  const int ks_end = min(ks_begin + p.k_per_cta, p.k_steps_total);
+  int ks_total = p.k_steps_total;
+  if (p.k_limit) ks_total = min(ks_total, (__ldg(p.k_limit) + WG_KPIX - 1) / WG_KPIX);
+  const int ks_end = min(ks_begin + p.k_per_cta, ks_total);
   const int n_steps = ks_end - ks_begin;
   constexpr int TMEM_COLS = (TAPS * BN <= 128) ? 128 : ((TAPS * BN <= 256) ? 256 : 512);
 
@@ -242,8 +245,25 @@ CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW
 // C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A (row stride lda), B (row stride ldb) bf16
 // with the reduction running over ROWS.  N % 64 == 0; M is arbitrary (TMA zero-fills the tail of the
 // last 128-row tile and the epilogue bounds its rows); lda, ldb multiples of 8.
+static int mn_acc_impl(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N, int K, int ldc,
+                       const int* k_limit, void* stream);
+
 CEB_API int ceb_gemm_bf16_mn_acc_ld(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N,
                                     int K, int ldc, void* stream) {
+  return mn_acc_impl(A, lda, B, ldb, C, M, N, K, ldc, nullptr, stream);
+}
+
+// Same, reducing over rows [0, *k_limit_dev) only (rounded up to whole 64-row steps, never past K:
+// the rows between the limit and the end of its step must hold zeros or finite values the caller
+// wants included).  k_limit_dev is a device int read by the kernel (CUDA-graph friendly).
+CEB_API int ceb_gemm_bf16_mn_acc_rows(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N,
+                                      int K, int ldc, const int* k_limit_dev, void* stream) {
+  CEB_REQUIRE(k_limit_dev != nullptr, "ceb_gemm_bf16_mn_acc_rows: k_limit_dev is NULL");
+  return mn_acc_impl(A, lda, B, ldb, C, M, N, K, ldc, k_limit_dev, stream);
+}
+
+static int mn_acc_impl(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N, int K, int ldc,
+                       const int* k_limit, void* stream) {
   CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_mn_acc_ld: bad arguments");
   CEB_REQUIRE(N % 64 == 0, "ceb_gemm_bf16_mn_acc_ld: N must be a multiple of 64 (N=%d)", N);
   CEB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && lda >= M && ldb >= N && ldc >= N,
@@ -258,7 +278,7 @@ CEB_API int ceb_gemm_bf16_mn_acc_ld(const void* A, int64_t lda, const void* B, i
   if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, ba)) return e;
   const int bn = (N % 128 == 0) ? 128 : 64;
   WgParams p{};
-  p.dW = C; p.Cout = M; p.Cin = N; p.H = 1; p.W = 1; p.ldw = ldc;
+  p.dW = C; p.Cout = M; p.Cin = N; p.H = 1; p.W = 1; p.ldw = ldc; p.k_limit = k_limit;
   p.vec_ok = (((uintptr_t)C & 15) == 0 && ldc % 4 == 0) ? 1 : 0;
   p.k_steps_total = (int)ceb_cdiv(K, WG_KPIX);
   p.ci_tiles = N / bn;

@@ -153,6 +153,10 @@ int ceb_cast_transpose_f32_bf16(const float* src, void* dst_bf16, int R, int C, 
  * bounded).  All three bases 16-byte aligned. */
 int ceb_gemm_bf16_tn_ld(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N,
                         int K, const float* bias, int relu, int out_mode, void* stream);
+/* Same, computing only rows [0, *m_limit_dev) (whole 128-row tiles, never past M); m_limit_dev is a
+ * DEVICE int read by the kernel, so a captured launch follows a data-dependent row count. */
+int ceb_gemm_bf16_tn_rows(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N,
+                          int K, const float* bias, int relu, int out_mode, const int* m_limit_dev, void* stream);
 /* bf16 NHWC max pooling (k = 2 or 4) and its backward; relu_mask != 0 also applies the ReLU
  * backward of y (reference: resnet9.py:48-56,95). */
 int ceb_maxpool_nhwc_bf16(const void* y, void* out, int N, int H, int W, int C, int k, void* stream);
@@ -170,6 +174,10 @@ int ceb_gemm_bf16_mn_acc(const void* A, const void* B, float* C, int M, int N, i
 /* Same with explicit operand row strides (multiples of 8, lda >= M, ldb >= N); M arbitrary, N % 64 == 0. */
 int ceb_gemm_bf16_mn_acc_ld(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N, int K,
                             int ldc, void* stream);
+/* Same, reducing over rows [0, *k_limit_dev) only (whole 64-row steps; rows up to the end of the last
+ * step must be finite, normally zero). */
+int ceb_gemm_bf16_mn_acc_rows(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N, int K,
+                              int ldc, const int* k_limit_dev, void* stream);
 /* dW[Cout][3][3][Cin] (fp32) += sum_p dz[p][co] * x[p + (r-1,s-1)][ci]; dz, x bf16 NHWC.  Both GEMM
  * operands are MN-major (pixels are the reduction dimension); split-K with vector atomics.
  * Cin % 64 == 0, Cout % 64 == 0, W divides 64. */
@@ -185,6 +193,11 @@ int ceb_softmax_ce_fwd(const void* logits_bf16, int64_t ld, int64_t rows, int V,
 int ceb_softmax_ce_bwd(const void* logits_bf16, void* dlogits_bf16, int64_t ld, int64_t rows, int V,
                        const int64_t* labels, int64_t ignore_index, const float* lse, const float* grad_rows,
                        void* stream);
+/* Compacted rows (valid labels first): rows past the 128-row tile holding row *row_limit_dev - 1 are
+ * neither read nor written. */
+int ceb_softmax_ce_bwd_rows(const void* logits_bf16, void* dlogits_bf16, int64_t ld, int64_t rows, int V,
+                            const int64_t* labels, int64_t ignore_index, const float* lse, const float* grad_rows,
+                            const int* row_limit_dev, void* stream);
 /* LayerNorm over the last dimension: x fp32 [rows][E] -> y bf16; backward gives dx fp32 and
  * accumulates dgamma / dbeta. */
 int ceb_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* y_bf16, float* mean,

@@ -332,3 +332,31 @@ def test_layernorm_bwd_widths():
         ln2(xr).backward(dy.float())
         assert _rel_err(x.grad, xr.grad) < 1e-3, E
         assert _rel_err(ln.weight.grad, ln2.weight.grad) < 1e-3 and _rel_err(ln.bias.grad, ln2.bias.grad) < 1e-3, E
+
+
+@pytest.mark.parametrize("R,V,E,frac", [(300, 50262, 128, 0.25), (513, 1000, 64, 0.6), (256, 777, 64, 0.0),
+                                        (128, 512, 64, 1.0)])
+def test_lm_head_ce_only_labeled_rows(R, V, E, frac):
+    """Fused LM head + CE that skips unlabeled rows vs the dense fp32 computation: same per-row loss,
+    same hidden / weight gradients."""
+    g = torch.Generator(device=DEV).manual_seed(R + V)
+    hidden = (torch.randn(R, E, device=DEV, generator=g) * 0.5).bfloat16().requires_grad_(True)
+    weight = torch.nn.Parameter(torch.randn(V, E, device=DEV, generator=g) * 0.1)
+    labels = torch.randint(0, V, (R,), device=DEV, generator=g)
+    drop = torch.rand(R, device=DEV, generator=g) >= frac
+    labels[drop] = -1
+    wrow = torch.randn(R, device=DEV, generator=g)
+    loss = tc.lm_head_ce(hidden, weight, labels, -1)
+    (loss * wrow).sum().backward()
+
+    hr = hidden.detach().float().requires_grad_(True)
+    wr = weight.detach().bfloat16().float().requires_grad_(True)
+    want = F.cross_entropy(hr @ wr.t(), labels, ignore_index=-1, reduction="none")
+    (want * wrow).sum().backward()
+    torch.testing.assert_close(loss, want, rtol=2e-2, atol=2e-2)
+    assert bool((loss[labels == -1] == 0).all())
+    if frac > 0:
+        assert _rel_err(hidden.grad, hr.grad) < 3e-2
+        assert _rel_err(weight.grad, wr.grad) < 3e-2
+    else:
+        assert float(hidden.grad.abs().max()) == 0 and float(weight.grad.abs().max()) == 0
