@@ -27,7 +27,8 @@ def timed(fn, iters=20, warmup=5):
 def main():
     dev = "cuda"
     rows = []
-    for M, N, K in [(4096, 2304, 768), (4096, 768, 3072), (4096, 3072, 768), (8192, 8192, 8192), (4096, 50264, 768)]:
+    for M, N, K in [(16384, 2304, 768), (16384, 768, 768), (16384, 3072, 768), (16384, 768, 3072), (8192, 8192, 8192),
+                    (4096, 50264, 768), (16384, 768, 50264)]:
         a = torch.randn(M, K, device=dev).bfloat16()
         b = torch.randn(N, K, device=dev).bfloat16()
         t_ours = timed(lambda: tc.gemm_tn(a, b))

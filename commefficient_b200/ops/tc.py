@@ -62,9 +62,10 @@ def _rows_ok(t: torch.Tensor) -> bool:
 
 
 def padded_empty(rows: int, cols: int, dtype, device) -> torch.Tensor:
-    """``[rows, cols]`` view of a buffer whose row stride is ``cols`` rounded up to 8 elements, so rows
-    stay 16-byte aligned for TMA / vector access whatever ``cols`` is (e.g. the 50 262-wide logits)."""
-    ld = (cols + 7) // 8 * 8
+    """``[rows, cols]`` view of a buffer whose row stride is ``cols`` rounded up to 16 elements, so bf16
+    rows stay 32-byte aligned (TMA needs 16; the GEMM epilogue stores whole 32-byte sectors) whatever
+    ``cols`` is (e.g. the 50 262-wide logits)."""
+    ld = (cols + 15) // 16 * 16
     return torch.empty((rows, ld), dtype=dtype, device=device)[:, :cols]
 
 

@@ -56,11 +56,14 @@ struct TcParams {
 //   1024-byte swizzle atom, so the UMMA descriptor stays canonical -- and both accumulators share
 //   the three weight tiles.  Shared-memory fill per output pixel drops ~2.2x against MODE 0
 //   (which is bound by L2 -> SM operand traffic on these layers, see profiles/).
-template <int BN, int MODE>
+// PAIR = 2: the CTA is half of a cta_group::2 pair and stages only BN/2 rows of every B tile.
+template <int BN, int MODE, int PAIR = 1>
 struct SmemLayout {
-  static constexpr int kStages = MODE == 1 ? (BN <= 64 ? 3 : 2) : StagesFor<BN>::value;
+  static constexpr int kStages = PAIR == 2 ? (MODE == 1 ? 3 : (BN <= 128 ? 8 : 6))
+                                           : (MODE == 1 ? (BN <= 64 ? 3 : 2) : StagesFor<BN>::value);
   static constexpr int kABytes = MODE == 1 ? 40960 : BM * BK * 2;     // halo box: (256/W + 2) rows x W x 128 B <= 40 KB
-  static constexpr int kBBytes = (MODE == 1 ? 3 : 1) * BN * BK * 2;
+  static constexpr int kBTileBytes = (BN / PAIR) * BK * 2;            // one weight tile as staged by this CTA
+  static constexpr int kBBytes = (MODE == 1 ? 3 : 1) * kBTileBytes;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTotal = kStages * kStageBytes + kEpiStageBytes + 1024 /* align */ + 256 /* barriers */;
   static constexpr int kSubTiles = MODE == 1 ? 2 : 1;
@@ -75,11 +78,19 @@ struct SmemLayout {
 // BMAJ = 1: the B operand is "MN-major" in memory (B[K][N] row-major, e.g. GPT-2's Conv1D weights
 // [in][out] or W itself in a data-gradient GEMM dX = dY * W): it is staged as 64-column chunks
 // [64 k][64 n] and read by tcgen05.mma through an MN-major descriptor -- no transposed copy.
-template <int BN, int MODE, int BMAJ = 0>
+// PAIR = 2 (launched as 2-CTA clusters): two CTAs on the SMs of one TPC share every MMA --
+// tcgen05.mma.cta_group::2 with M = 256, issued by the leader (cluster rank 0) only.  Each CTA stages
+// its own 128 (or, MODE 1, 256) rows of A and HALF of each weight tile, so the shared-memory fill per
+// FLOP drops by a third to a half against two independent CTAs, which is what bounds the short-K
+// layers.  TMA completion bytes of both CTAs are counted on the leader's "full" barrier; the MMA
+// commits are multicast to the "empty" / "accumulator full" barriers of both; the peer's epilogue
+// warps release the accumulator with a remote arrive on the leader's barrier.
+template <int BN, int MODE, int BMAJ = 0, int PAIR = 1>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, TcParams p) {
+  static_assert(PAIR == 1 || BMAJ == 0, "the CTA-pair variant stages K-major B only");
   extern __shared__ uint8_t smem_raw[];
-  using L = SmemLayout<BN, MODE>;
+  using L = SmemLayout<BN, MODE, PAIR>;
   constexpr int kStages = L::kStages;
   constexpr int SUBS = L::kSubTiles;
   constexpr int BMT = BM * SUBS;                       // output rows per CTA tile
@@ -93,13 +104,18 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = PAIR == 2 ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
   int m_tiles_rt = p.m_tiles;
   if (p.m_limit) {
     const int lim = (__ldg(p.m_limit) + BMT - 1) / BMT;
     m_tiles_rt = lim < m_tiles_rt ? lim : m_tiles_rt;
   }
-  const int m_tiles = m_tiles_rt;
+  // work is handed out in units of PAIR vertically adjacent CTA tiles; a CTA of a pair owns
+  // CTA tile (unit * PAIR + rank), which may lie wholly past M (TMA zero-fills, stores are bounded)
+  const int m_tiles = (m_tiles_rt + PAIR - 1) / PAIR;
   const int num_tiles = m_tiles * p.n_tiles;
+  const int first_tile = blockIdx.x / PAIR, tile_step = gridDim.x / PAIR;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmapA);
@@ -110,13 +126,16 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tmem_full_bar + a, 1);
-      mbar_init(tmem_empty_bar + a, kEpiWarps);       // one arrive per epilogue warp
+      mbar_init(tmem_empty_bar + a, PAIR * kEpiWarps);   // one arrive per epilogue warp (of both CTAs)
     }
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc<L::kTmemCols>(tmem_slot);
+  if (warp == 1) {
+    if (PAIR == 2) tmem_alloc_pair<L::kTmemCols>(tmem_slot);
+    else tmem_alloc<L::kTmemCols>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -124,8 +143,9 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     // ===== TMA producer =====
     if (lane == 0) {
       uint32_t it = 0;                                   // global k-step counter (ring position)
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int m_tile = t % m_tiles, n_tile = t / m_tiles;
+      for (int t = first_tile; t < num_tiles; t += tile_step) {
+        const int m_tile = (t % m_tiles) * PAIR + (int)cta_rank, n_tile = t / m_tiles;
+        const int b_row0 = n_tile * BN + (int)cta_rank * (BN / PAIR);   // this CTA's share of the weight tile
         int n0 = 0, h0 = 0;
         if (p.conv) {
           const int pix0 = m_tile * BMT;
@@ -139,7 +159,30 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           mbar_wait(empty_bar + s, phase ^ 1);
           uint8_t* a_dst = smem + s * L::kStageBytes;
           uint8_t* b_dst = a_dst + L::kABytes;
-          if (MODE == 1) {
+          if (PAIR == 2) {
+            // both CTAs' bytes land on the LEADER's full barrier; only the leader arms it
+            const uint32_t fbar = mapa_u32(smem_u32(full_bar + s), 0);
+            if (MODE == 1) {
+              const int sft = ks / p.cin_steps;
+              const int c0 = (ks - sft * p.cin_steps) * BK;
+              if (leader) mbar_expect_tx(full_bar + s, 2u * ((uint32_t)p.halo_bytes + L::kBBytes));
+              tma_load_4d_pair(a_dst, &tmapA, fbar, c0, sft - 1, h0 - 1, n0);
+#pragma unroll
+              for (int r = 0; r < 3; ++r)
+                tma_load_2d_pair(b_dst + r * L::kBTileBytes, &tmapB, fbar, ((r * 3 + sft) * p.cin_steps) * BK + c0, b_row0);
+            } else {
+              if (leader) mbar_expect_tx(full_bar + s, 2u * L::kStageBytes);
+              if (p.conv) {
+                const int tap = ks / p.cin_steps;
+                const int c0 = (ks - tap * p.cin_steps) * BK;
+                const int r = tap / 3, sft = tap - r * 3;
+                tma_load_4d_pair(a_dst, &tmapA, fbar, c0, sft - 1, h0 + r - 1, n0);
+              } else {
+                tma_load_2d_pair(a_dst, &tmapA, fbar, ks * BK, m_tile * BM);
+              }
+              tma_load_2d_pair(b_dst, &tmapB, fbar, ks * BK, b_row0);
+            }
+          } else if (MODE == 1) {
             // k-step = (horizontal tap sft, channel chunk c0): one halo box + the 3 weight tiles r = 0..2
             const int sft = ks / p.cin_steps;
             const int c0 = (ks - sft * p.cin_steps) * BK;
@@ -171,10 +214,10 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one elected thread) =====
-    constexpr uint32_t idesc = idesc_bf16(BM, BN, 0, BMAJ);
+    // ===== MMA issuer (one elected thread; in a pair only the leader CTA issues) =====
+    constexpr uint32_t idesc = idesc_bf16(BM * PAIR, BN, 0, BMAJ);
     uint32_t it = 0, local = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
+    for (int t = first_tile; leader && t < num_tiles; t += tile_step, ++local) {
       const int acc = local & 1;
       mbar_wait(tmem_empty_bar + acc, ((local >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
       tc_fence_after();
@@ -197,8 +240,9 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
                 for (int k = 0; k < BK / UMMA_K; ++k) {
                   const uint64_t da = smem_desc_sw128(a_addr + (sub * sub_rows + r) * row_bytes + k * UMMA_K * 2, 16, 1024);
-                  const uint64_t db = smem_desc_sw128(b_addr + r * (BN * BK * 2) + k * UMMA_K * 2, 16, 1024);
-                  umma_bf16(tmem_d + sub * BN, da, db, idesc, (ks | r | k) != 0);
+                  const uint64_t db = smem_desc_sw128(b_addr + r * L::kBTileBytes + k * UMMA_K * 2, 16, 1024);
+                  if (PAIR == 2) umma_bf16_pair(tmem_d + sub * BN, da, db, idesc, (ks | r | k) != 0);
+                  else umma_bf16(tmem_d + sub * BN, da, db, idesc, (ks | r | k) != 0);
                 }
           } else {
 #pragma unroll
@@ -206,11 +250,17 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
               const uint64_t da = smem_desc_sw128(a_addr + k * UMMA_K * 2, 16, 1024);
               const uint64_t db = BMAJ == 1 ? smem_desc_sw128(b_addr + k * UMMA_K * 128, BK * 128, 1024)
                                             : smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
-              umma_bf16(tmem_d, da, db, idesc, (ks | k) != 0);
+              if (PAIR == 2) umma_bf16_pair(tmem_d, da, db, idesc, (ks | k) != 0);
+              else umma_bf16(tmem_d, da, db, idesc, (ks | k) != 0);
             }
           }
-          umma_commit(empty_bar + s);                     // frees this smem stage when the MMAs retire
-          if (ks == p.k_steps - 1) umma_commit(tmem_full_bar + acc);
+          if (PAIR == 2) {
+            umma_commit_pair(empty_bar + s);              // frees this stage in BOTH CTAs
+            if (ks == p.k_steps - 1) umma_commit_pair(tmem_full_bar + acc);
+          } else {
+            umma_commit(empty_bar + s);                   // frees this smem stage when the MMAs retire
+            if (ks == p.k_steps - 1) umma_commit(tmem_full_bar + acc);
+          }
         }
         __syncwarp();
       }
@@ -220,23 +270,37 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     const int q = warp & 3;                               // TMEM lane quarter this warp may access
     uint32_t* stage = (uint32_t*)(epi_smem + (warp - 2) * (32 * 17 * 4));
     uint32_t local = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
-      const int m_tile = t % m_tiles, n_tile = t / m_tiles;
+    for (int t = first_tile; t < num_tiles; t += tile_step, ++local) {
+      const int m_tile = (t % m_tiles) * PAIR + (int)cta_rank, n_tile = t / m_tiles;
       const int acc = local & 1;
       mbar_wait(tmem_full_bar + acc, (local >> 1) & 1);
       tc_fence_after();
       const int n_base = n_tile * BN;
       constexpr int kChunks = SUBS * (BN / 32);            // 32-column chunks per tile, split over the two warps of a quarter
+      constexpr int kPer = kChunks / 2;                    // chunks drained by this warp
       const int half = (warp - 2) >> 2;
-#pragma unroll 1
-      for (int sc = half * (kChunks / 2); sc < (half + 1) * (kChunks / 2); ++sc) {
+      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (SUBS * BN);
+      // direct path: bf16 output whose rows are 32-byte aligned -> every thread stores its row's 64
+      // bytes of the chunk as two full 32-byte sectors straight from registers (no shared-memory
+      // staging: the operand ring already saturates shared-memory bandwidth, see profiles/)
+      const bool direct = p.out_fp32 == 0 && (p.ldc & 15) == 0 && (((uintptr_t)p.C) & 31) == 0 &&
+                          (p.mask == nullptr || (((uintptr_t)p.mask) & 31) == 0);
+      auto chunk_addr = [&](int i) {
+        const int sc = half * kPer + i;
         const int sub = sc / (BN / 32), c = sc - sub * (BN / 32);
+        return tacc + sub * BN + c * 32;
+      };
+      auto process = [&](const uint32_t (&cur)[32], int i) {
+        const int sc = half * kPer + i;
+        const int sub = sc / (BN / 32), c = sc - sub * (BN / 32);
+        if (PAIR == 2 && m_tile >= m_tiles_rt) return;     // the peer's tile lies past the (device-side) row limit
         const int row0 = m_tile * BMT + sub * BM + q * 32;   // first output row of this warp
         const int m = row0 + lane;
         float v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * (SUBS * BN) + sub * BN + c * 32, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(cur[j]);
         const int n0 = n_base + c * 32;
-        if (n0 >= p.N) continue;
+        if (n0 >= p.N) return;
         if (p.bias) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) if (n0 + j < p.N) v[j] += __ldg(p.bias + n0 + j);
@@ -246,7 +310,35 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
         const bool full = (n0 + 32 <= p.N);
-        if (p.mask && m < p.M && !(p.out_fp32 == 0 && full)) {   // (the bf16 fast path masks while storing)
+        if (direct && full) {
+          if (m < p.M) {
+            const int64_t off = (int64_t)m * p.ldc + n0;
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2) {
+              uint32_t w[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                __nv_bfloat162 hh = __floats2bfloat162_rn(v[h2 * 16 + 2 * j], v[h2 * 16 + 2 * j + 1]);
+                w[j] = *(uint32_t*)&hh;
+              }
+              if (p.mask) {
+                // ReLU backward: keep a gradient only where the forward activation was positive
+                // (bf16 > 0  <=>  sign bit clear and magnitude bits non-zero)
+                uint32_t mk[8];
+                ld_global_nc_v8((const __nv_bfloat16*)p.mask + off + h2 * 16, mk);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const uint32_t lo = ((mk[j] & 0x8000u) == 0u && (mk[j] & 0x7fffu) != 0u) ? 0x0000ffffu : 0u;
+                  const uint32_t hi = ((mk[j] & 0x80000000u) == 0u && (mk[j] & 0x7fff0000u) != 0u) ? 0xffff0000u : 0u;
+                  w[j] &= (lo | hi);
+                }
+              }
+              st_global_v8((__nv_bfloat16*)p.C + off + h2 * 16, w);
+            }
+          }
+          return;
+        }
+        if (p.mask && m < p.M && !(p.out_fp32 == 0 && full)) {   // (the bf16 staged path masks while storing)
           const __nv_bfloat16* mk = (const __nv_bfloat16*)p.mask + (int64_t)m * p.ldc + n0;
 #pragma unroll
           for (int j = 0; j < 32; ++j)
@@ -270,9 +362,6 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
               pk.z = stage[r * 17 + w4 + 2]; pk.w = stage[r * 17 + w4 + 3];
               const int64_t off = (int64_t)(row0 + r) * p.ldc + n0 + w4 * 2;
               if (p.mask) {
-                // ReLU backward: keep a gradient only where the forward activation was positive
-                // (bf16 > 0  <=>  sign bit clear and magnitude bits non-zero); same coalesced
-                // 16-byte access pattern as the store
                 const uint4 mk = __ldg((const uint4*)((const __nv_bfloat16*)p.mask + off));
                 auto keep = [](uint32_t m2, uint32_t val) {
                   const uint32_t lo = ((m2 & 0x8000u) == 0u && (m2 & 0x7fffu) != 0u) ? 0x0000ffffu : 0u;
@@ -288,7 +377,8 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         } else if (m < p.M) {
           if (p.out_fp32 == 0) {
             __nv_bfloat16* dst = (__nv_bfloat16*)p.C + (int64_t)m * p.ldc + n0;
-            for (int j = 0; j < 32 && n0 + j < p.N; ++j) dst[j] = __float2bfloat16(v[j]);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (n0 + j < p.N) dst[j] = __float2bfloat16(v[j]);
           } else {
             float* dst = (float*)p.C + (int64_t)m * p.ldc + n0;
             if (p.out_fp32 == 1) {
@@ -296,25 +386,45 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) *(float4*)(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
               } else {
-                for (int j = 0; j < 32 && n0 + j < p.N; ++j) dst[j] = v[j];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (n0 + j < p.N) dst[j] = v[j];
               }
             } else {
-              for (int j = 0; j < 32 && n0 + j < p.N; ++j) red_add_f32(dst + j, v[j]);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) if (n0 + j < p.N) red_add_f32(dst + j, v[j]);
             }
           }
+        }
+      };
+      // software pipeline: the next chunk's TMEM read is in flight while this chunk is stored
+      uint32_t ra[32], rb[32];
+      tmem_ld_32x32_issue(chunk_addr(0), ra);
+#pragma unroll
+      for (int i = 0; i < kPer; i += 2) {
+        tmem_ld_wait(ra);
+        if (i + 1 < kPer) tmem_ld_32x32_issue(chunk_addr(i + 1), rb);
+        process(ra, i);
+        if (i + 1 < kPer) {
+          tmem_ld_wait(rb);
+          if (i + 2 < kPer) tmem_ld_32x32_issue(chunk_addr(i + 2), ra);
+          process(rb, i + 1);
         }
       }
       // this warp is done reading accumulator `acc`
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
+      if (lane == 0) {
+        if (PAIR == 2) mbar_arrive_cluster(mapa_u32(smem_u32(tmem_empty_bar + acc), 0));
+        else mbar_arrive(tmem_empty_bar + acc);
+      }
     }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<L::kTmemCols>(tmem_base);
+    if (PAIR == 2) tmem_dealloc_pair<L::kTmemCols>(tmem_base);
+    else tmem_dealloc<L::kTmemCols>(tmem_base);
   }
 }
 
@@ -370,9 +480,70 @@ static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcPar
   return 0;
 }
 
+// CTA-pair launch: 2-CTA clusters, one pair per TPC, persistent over pair tiles (2 CTA tiles tall).
+template <int BN, int MODE>
+static int launch_tile_pair(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+  using L = SmemLayout<BN, MODE, 2>;
+  static_assert(L::kTotal <= 232448, "CTA-pair stage ring exceeds the 227 KB shared-memory limit");
+  static bool configured = false;
+  if (!configured) {
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN, MODE, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    configured = true;
+  }
+  TcParams q = p;
+  q.m_tiles = (int)ceb_cdiv(p.M, BM * L::kSubTiles);
+  q.n_tiles = (int)ceb_cdiv(p.N, BN);
+  const int pair_tiles = (int)ceb_cdiv(q.m_tiles, 2) * q.n_tiles;
+  const int max_pairs = ceb_num_sms() / 2;
+  const int pairs = pair_tiles < max_pairs ? pair_tiles : max_pairs;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * pairs), 1, 1);
+  cfg.blockDim = dim3(kTcThreads, 1, 1);
+  cfg.dynamicSmemBytes = L::kTotal;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  CEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, tc_tile_kernel<BN, MODE, 0, 2>, ta, tb, q));
+  CEB_COUNT_LAUNCH(1);
+  return 0;
+}
+
+// CEB_TC_PAIR=0 disables / =1 forces the cta_group::2 variant wherever it exists.
+static int pair_env() {
+  static const int v = [] { const char* e = getenv("CEB_TC_PAIR"); return e ? atoi(e) : -1; }();
+  return v;
+}
+// Default policy (measured, profiles/bench_tc.json): CTA pairs win once there are enough 2-tile
+// units to occupy all 74 TPCs and the K loop is long enough to amortise the cluster hand-shakes;
+// the halo convolution with a single 64-channel chunk (3 k-steps per tile) stays on one CTA.
+static bool use_pair(int mode, int M, int N, int bn, int rows_per_cta_tile, int k_steps) {
+  if (pair_env() >= 0) return pair_env() != 0;
+  const int64_t pair_tiles = ceb_cdiv(ceb_cdiv(M, rows_per_cta_tile), 2) * ceb_cdiv(N, bn);
+  if (pair_tiles < ceb_num_sms() / 2) return false;
+  if (mode == 1) return k_steps >= 6;
+  return k_steps >= 4;
+}
+
 static int pick_bn(int N) { return N <= 64 ? 64 : (N <= 128 ? 128 : 256); }
 
-static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st,
+                         bool pair = false) {
+  if (pair) {
+    if (mode == 1) {
+      if (bn == 64) return launch_tile_pair<64, 1>(ta, tb, p, st);
+      if (bn == 128) return launch_tile_pair<128, 1>(ta, tb, p, st);
+    } else if (mode == 0) {
+      switch (bn) {
+        case 64: return launch_tile_pair<64, 0>(ta, tb, p, st);
+        case 128: return launch_tile_pair<128, 0>(ta, tb, p, st);
+        case 256: return launch_tile_pair<256, 0>(ta, tb, p, st);
+      }
+    }
+    CEB_REQUIRE(false, "unsupported CTA-pair tile configuration (N tile %d, mode %d)", bn, mode);
+  }
   if (mode == 1) {
     if (bn == 64) return launch_tile<64, 1>(ta, tb, p, st);
     if (bn == 128) return launch_tile<128, 1>(ta, tb, p, st);
@@ -430,13 +601,14 @@ static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, 
   uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * 2};
   uint32_t ba[2] = {BK, BM};
   if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
+  const bool pair = use_pair(0, M, N, bn, BM, (int)ceb_cdiv(K, BK));
   uint64_t db[2] = {(uint64_t)K, (uint64_t)N}, sb[1] = {(uint64_t)ldb * 2};
-  uint32_t bb[2] = {BK, (uint32_t)bn};
+  uint32_t bb[2] = {BK, (uint32_t)(pair ? bn / 2 : bn)};
   if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, bb)) return e;
   TcParams p{};
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = (int)ldc; p.k_steps = (int)ceb_cdiv(K, BK);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 0; p.m_limit = m_limit;
-  return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream);
+  return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream, pair);
 }
 
 // Dense form of the above (lda = ldb = K, ldc = N): K % 8 == 0, N % 8 == 0.
@@ -494,13 +666,14 @@ CEB_API int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nim
   uint32_t ba[4] = {BK, (uint32_t)W, (uint32_t)(halo ? rows256 + 2 : tile_h), (uint32_t)(halo ? 1 : tile_n)};
   if (int e = ceb_make_tmap_bf16(&ta, x, 4, da, sa, ba)) return e;
   const int K = 9 * Cin;
+  const bool pair = use_pair(halo ? 1 : 0, Nimg * H * W, Cout, bn, halo ? 256 : BM, (halo ? 3 : 9) * (Cin / BK));
   uint64_t db[2] = {(uint64_t)K, (uint64_t)Cout}, sb[1] = {(uint64_t)K * 2};
-  uint32_t bb[2] = {BK, (uint32_t)bn};
+  uint32_t bb[2] = {BK, (uint32_t)(pair ? bn / 2 : bn)};
   if (int e = ceb_make_tmap_bf16(&tb, w, 2, db, sb, bb)) return e;
   TcParams p{};
   p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout;
   p.k_steps = (halo ? 3 : 9) * (Cin / BK);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = H; p.W = W; p.cin_steps = Cin / BK; p.tile_h = tile_h;
   p.halo_bytes = halo ? (rows256 + 2) * W * 128 : 0;
-  return dispatch_tile(bn, halo ? 1 : 0, ta, tb, p, (cudaStream_t)stream);
+  return dispatch_tile(bn, halo ? 1 : 0, ta, tb, p, (cudaStream_t)stream, pair);
 }
