@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no_native_nn", action="store_true",
                     help="run conv/linear layers on cuDNN/cuBLAS instead of the hand-written tcgen05 kernels")
+    ap.add_argument("--no_cuda_graphs", action="store_true",
+                    help="launch the round's kernels one by one (for ncu launch lists; a graph replay hides them)")
     ap.add_argument("--clients_per_gpu", type=int, default=CLIENTS_PER_GPU)
     ap.add_argument("--phases", action="store_true", help="also print a per-phase breakdown to stderr")
     ap.add_argument("--profile", action="store_true",
@@ -194,7 +196,7 @@ def run_ours(cfg):
                      local_momentum=0.0, virtual_momentum=0.9, num_workers=clients, num_clients=NUM_CLIENTS,
                      local_batch_size=-1, num_epochs=1.0, dataset_name="CIFAR10", device="cuda",
                      precision=cfg.precision, backend=cfg.backend, model=cfg.model,
-                     no_native_nn=cfg.no_native_nn)
+                     no_native_nn=cfg.no_native_nn, no_cuda_graphs=cfg.no_cuda_graphs)
     rt = init_runtime(args)
     torch.manual_seed(args.seed)
     torch.backends.cudnn.benchmark = True

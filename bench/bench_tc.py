@@ -48,6 +48,25 @@ def main():
         fl = 2.0 * n * h * h * cout * 9 * cin
         rows.append({"op": "conv3x3+relu", "shape": [n, h, cin, cout], "ours_us": t_ours, "cudnn_us": t_lib,
                      "ours_tflops": fl / t_ours / 1e6, "cudnn_tflops": fl / t_lib / 1e6})
+    for h, cin, cout in [(32, 64, 128), (16, 128, 128), (16, 128, 256), (8, 256, 512), (4, 512, 512)]:
+        x = torch.randn(n, h, h, cin, device=dev).bfloat16()
+        dz = torch.randn(n, h, h, cout, device=dev).bfloat16()
+        dw = torch.zeros(cout, 3, 3, cin, device=dev)
+        xc, dzc = x.permute(0, 3, 1, 2), dz.permute(0, 3, 1, 2)
+        t_ours = timed(lambda: tc.conv3x3_wgrad_nhwc(dz, x, dw))
+        t_lib = timed(lambda: torch.nn.grad.conv2d_weight(xc, (cout, cin, 3, 3), dzc, padding=1))
+        fl = 2.0 * n * h * h * cout * 9 * cin
+        rows.append({"op": "conv3x3 wgrad", "shape": [n, h, cin, cout], "ours_us": t_ours, "cudnn_us": t_lib,
+                     "ours_tflops": fl / t_ours / 1e6, "cudnn_tflops": fl / t_lib / 1e6})
+    for K, M, N in [(16384, 768, 2304), (16384, 3072, 768), (16384, 768, 3072)]:
+        a = torch.randn(K, M, device=dev).bfloat16()
+        b = torch.randn(K, N, device=dev).bfloat16()
+        c = torch.zeros(M, N, device=dev)
+        t_ours = timed(lambda: tc.gemm_mn_acc(a, b, c))
+        t_lib = timed(lambda: torch.mm(a.t(), b))
+        fl = 2.0 * M * N * K
+        rows.append({"op": "gemm_mn_acc (linear wgrad)", "shape": [K, M, N], "ours_us": t_ours, "cublas_us": t_lib,
+                     "ours_tflops": fl / t_ours / 1e6, "cublas_tflops": fl / t_lib / 1e6})
     print(json.dumps(rows, indent=1))
 
 

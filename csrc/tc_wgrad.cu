@@ -13,6 +13,7 @@
 // Replaces cuDNN's wgrad behind autograd of nn.Conv2d
 // (/root/reference/CommEfficient/models/resnet9.py:36-37, fed_worker.py:286 loss.backward()).
 #include "tc_common.cuh"
+#include <cstdlib>
 
 using namespace tc;
 
@@ -33,14 +34,29 @@ struct WgParams {
   const int* k_limit;    // optional device-side count of reduction rows (see ceb_gemm_bf16_mn_acc_rows)
 };
 
-template <int BN>
+// Shared-memory ring.  TAPS weight-tap tiles per stage (3 for a convolution row, 1 for a plain GEMM);
+// a CTA of a pair (PAIR = 2) stages only its half of every tap's BN input channels.
+template <int BN, int TAPS, int PAIR>
 struct WgSmem {
-  static constexpr int kChunk = WG_KPIX * 128;                   // [64 px][64 ch] bf16 = 8 KB
-  static constexpr int kABytes = 2 * kChunk;                      // 128 co
-  static constexpr int kBBytes = 3 * (BN / 64) * kChunk;          // 3 taps x BN ci
+  static constexpr int kChunk = WG_KPIX * 128;                    // [64 px][64 ch] bf16 = 8 KB
+  static constexpr int kABytes = 2 * kChunk;                      // this CTA's 128 output channels
+  static constexpr int kCh = BN / 64 / PAIR;                      // 64-channel chunks per tap staged by this CTA
+  static constexpr int kBChunks = TAPS * kCh;
+  static constexpr int kBBytes = kBChunks * kChunk;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = BN <= 64 ? 4 : 3;
+  static constexpr int kStagesFit = (200 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesFit > 8 ? 8 : kStagesFit;
   static constexpr int kTotal = kStages * kStageBytes + 1024 + 256;
+  // One MMA instruction covers up to 256 accumulator columns: the first kC1 chunks of each CTA go
+  // into instruction 1 (N1 columns over the pair), the rest into instruction 2.
+  static constexpr int kC1 = kBChunks < 256 / (64 * PAIR) ? kBChunks : 256 / (64 * PAIR);
+  static constexpr int kC2 = kBChunks - kC1;
+  static constexpr int kN1 = kC1 * 64 * PAIR;
+  static constexpr int kN2 = kC2 * 64 * PAIR;
+  static constexpr int kNTot = kN1 + kN2;                         // accumulator columns (= TAPS * BN)
+  static constexpr int kTmemCols = kNTot <= 128 ? 128 : (kNTot <= 256 ? 256 : 512);
+  static_assert(kC2 * 64 * PAIR <= 256 && kNTot <= 512, "tile does not fit two MMA instructions / TMEM");
+  static_assert(BN % (64 * PAIR) == 0, "every CTA needs whole 64-channel chunks");
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -50,12 +66,17 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 // CONV = false turns the kernel into the plain "both operands MN-major" GEMM
 //   C[M][N] (fp32) += A[K][M]^T * B[K][N]        (A, B bf16 row-major, K = reduction)
 // used for linear-layer weight gradients (dW = dY^T X) and the im2col'd stem: one tap, 2-D B.
-template <int BN, bool CONV>
+// PAIR = 2: two CTAs of a 2-CTA cluster share every MMA (tcgen05.mma.cta_group::2, M = 256 output
+// channels): each stages its own 128 channels of dZ and half of the BN input channels of every tap,
+// so the shared-memory traffic per FLOP -- the bound of this kernel -- drops by ~40 %.
+template <int BN, bool CONV, int PAIR>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constant__ CUtensorMap tmapX, WgParams p) {
   extern __shared__ uint8_t smem_raw[];
-  using L = WgSmem<BN>;
+  constexpr int TAPS = CONV ? 3 : 1;
+  using L = WgSmem<BN, TAPS, PAIR>;
   constexpr int kStages = L::kStages;
+  constexpr int CH = L::kCh;
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = (uint64_t*)(smem + kStages * L::kStageBytes);
   uint64_t* empty_bar = full_bar + kStages;
@@ -64,17 +85,19 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  // blockIdx.x = ((co_tile * 3 + r) * ci_tiles + ci_tile), blockIdx.y = split
-  constexpr int TAPS = CONV ? 3 : 1;
-  const int ci_tile = blockIdx.x % p.ci_tiles;
-  const int r = CONV ? (blockIdx.x / p.ci_tiles) % 3 : 0;
-  const int co_tile = CONV ? blockIdx.x / (p.ci_tiles * 3) : blockIdx.x / p.ci_tiles;
+  const uint32_t cta_rank = PAIR == 2 ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
+  // unit = blockIdx.x / PAIR = ((co_unit * 3 + r) * ci_tiles + ci_tile), blockIdx.y = split
+  const int unit = blockIdx.x / PAIR;
+  const int ci_tile = unit % p.ci_tiles;
+  const int r = CONV ? (unit / p.ci_tiles) % 3 : 0;
+  const int co_tile = (CONV ? unit / (p.ci_tiles * 3) : unit / p.ci_tiles) * PAIR + (int)cta_rank;
   const int ks_begin = blockIdx.y * p.k_per_cta;
   int ks_total = p.k_steps_total;
   if (p.k_limit) ks_total = min(ks_total, (__ldg(p.k_limit) + WG_KPIX - 1) / WG_KPIX);
   const int ks_end = min(ks_begin + p.k_per_cta, ks_total);
   const int n_steps = ks_end - ks_begin;
-  constexpr int TMEM_COLS = (TAPS * BN <= 128) ? 128 : ((TAPS * BN <= 256) ? 256 : 512);
+  constexpr int TMEM_COLS = L::kTmemCols;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmapDZ);
@@ -86,9 +109,12 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
     mbar_init(tmem_full_bar, 1);
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  if (warp == 1) {
+    if (PAIR == 2) tmem_alloc_pair<TMEM_COLS>(tmem_slot);
+    else tmem_alloc<TMEM_COLS>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -96,37 +122,65 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
     if (warp == 0) {
       if (lane == 0) {
         const int hw = p.H * p.W;
+        const int ci_base = ci_tile * BN + (int)cta_rank * (BN / PAIR);   // this CTA's input channels of the tile
         for (int i = 0; i < n_steps; ++i) {
           const int s = i % kStages;
           const uint32_t phase = (i / kStages) & 1;
           mbar_wait(empty_bar + s, phase ^ 1);
           uint8_t* a_dst = smem + s * L::kStageBytes;
           uint8_t* b_dst = a_dst + L::kABytes;
-          mbar_expect_tx(full_bar + s, L::kABytes + TAPS * (BN / 64) * L::kChunk);
           const int pix0 = (ks_begin + i) * WG_KPIX;
-          // dZ: 2-D [pixels][Cout]: two 64-channel chunks
-          tma_load_2d(a_dst, &tmapDZ, full_bar + s, co_tile * WG_M, pix0);
-          tma_load_2d(a_dst + L::kChunk, &tmapDZ, full_bar + s, co_tile * WG_M + 64, pix0);
-          // X: 4-D [N][H][W][Cin], shifted by (r-1, s-1)
-          if (CONV) {
-            const int n0 = pix0 / hw;
-            const int h0 = (pix0 - n0 * hw) / p.W;
+          if (PAIR == 2) {
+            // both CTAs' bytes are counted on the leader's barrier, which only the leader arms
+            const uint32_t fbar = mapa_u32(smem_u32(full_bar + s), 0);
+            if (leader) mbar_expect_tx(full_bar + s, 2u * L::kStageBytes);
+            tma_load_2d_pair(a_dst, &tmapDZ, fbar, co_tile * WG_M, pix0);
+            tma_load_2d_pair(a_dst + L::kChunk, &tmapDZ, fbar, co_tile * WG_M + 64, pix0);
+            if (CONV) {
+              const int n0 = pix0 / hw;
+              const int h0 = (pix0 - n0 * hw) / p.W;
 #pragma unroll
-            for (int sft = 0; sft < 3; ++sft)
+              for (int sft = 0; sft < 3; ++sft)
 #pragma unroll
-              for (int ch = 0; ch < BN / 64; ++ch)
-                tma_load_4d(b_dst + (sft * (BN / 64) + ch) * L::kChunk, &tmapX, full_bar + s,
-                            ci_tile * BN + ch * 64, sft - 1, h0 + r - 1, n0);
+                for (int ch = 0; ch < CH; ++ch)
+                  tma_load_4d_pair(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, fbar, ci_base + ch * 64, sft - 1,
+                                   h0 + r - 1, n0);
+            } else {
+#pragma unroll
+              for (int ch = 0; ch < CH; ++ch)
+                tma_load_2d_pair(b_dst + ch * L::kChunk, &tmapX, fbar, ci_base + ch * 64, pix0);
+            }
           } else {
+            mbar_expect_tx(full_bar + s, L::kStageBytes);
+            // dZ: 2-D [pixels][Cout]: two 64-channel chunks
+            tma_load_2d(a_dst, &tmapDZ, full_bar + s, co_tile * WG_M, pix0);
+            tma_load_2d(a_dst + L::kChunk, &tmapDZ, full_bar + s, co_tile * WG_M + 64, pix0);
+            // X: 4-D [N][H][W][Cin], shifted by (r-1, s-1)
+            if (CONV) {
+              const int n0 = pix0 / hw;
+              const int h0 = (pix0 - n0 * hw) / p.W;
 #pragma unroll
-            for (int ch = 0; ch < BN / 64; ++ch)
-              tma_load_2d(b_dst + ch * L::kChunk, &tmapX, full_bar + s, ci_tile * BN + ch * 64, pix0);
+              for (int sft = 0; sft < 3; ++sft)
+#pragma unroll
+                for (int ch = 0; ch < CH; ++ch)
+                  tma_load_4d(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, full_bar + s, ci_base + ch * 64, sft - 1,
+                              h0 + r - 1, n0);
+            } else {
+#pragma unroll
+              for (int ch = 0; ch < CH; ++ch)
+                tma_load_2d(b_dst + ch * L::kChunk, &tmapX, full_bar + s, ci_base + ch * 64, pix0);
+            }
           }
         }
       }
     } else if (warp == 1) {
-      constexpr uint32_t idesc = idesc_bf16(WG_M, BN, 1, 1);     // both operands MN-major
-      for (int i = 0; i < n_steps; ++i) {
+      // The tap tiles of a stage are consecutive 64-channel MN-major chunks and their accumulators
+      // consecutive TMEM columns, so they are ONE wide-N operand: issue N up to 256 per instruction
+      // instead of one N = BN MMA per tap -- the dZ tile is then read from shared memory once (or
+      // twice) per k-slice instead of three times, and shared-memory bandwidth bounds this kernel.
+      constexpr uint32_t idesc1 = idesc_bf16(WG_M * PAIR, L::kN1, 1, 1);     // both operands MN-major
+      constexpr uint32_t idesc2 = idesc_bf16(WG_M * PAIR, L::kN2 > 0 ? L::kN2 : 16, 1, 1);
+      for (int i = 0; leader && i < n_steps; ++i) {
         const int s = i % kStages;
         const uint32_t phase = (i / kStages) & 1;
         mbar_wait(full_bar + s, phase);
@@ -135,17 +189,25 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
           const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
           const uint32_t b_addr = a_addr + L::kABytes;
 #pragma unroll
-          for (int sft = 0; sft < TAPS; ++sft) {
-#pragma unroll
-            for (int k = 0; k < WG_KPIX / 16; ++k) {
-              // 16 pixels = 16 rows of 128 B; MN chunks (64 channels) are L::kChunk apart
-              const uint64_t da = smem_desc_sw128(a_addr + k * 16 * 128, L::kChunk, 1024);
-              const uint64_t db = smem_desc_sw128(b_addr + sft * (BN / 64) * L::kChunk + k * 16 * 128, L::kChunk, 1024);
-              umma_bf16(tmem_base + sft * BN, da, db, idesc, (i | k) != 0);
+          for (int k = 0; k < WG_KPIX / 16; ++k) {
+            // 16 pixels = 16 rows of 128 B; MN chunks (64 channels) are L::kChunk apart
+            const uint64_t da = smem_desc_sw128(a_addr + k * 16 * 128, L::kChunk, 1024);
+            const uint64_t db = smem_desc_sw128(b_addr + k * 16 * 128, L::kChunk, 1024);
+            if (PAIR == 2) umma_bf16_pair(tmem_base, da, db, idesc1, (i | k) != 0);
+            else umma_bf16(tmem_base, da, db, idesc1, (i | k) != 0);
+            if (L::kN2 > 0) {
+              const uint64_t db2 = smem_desc_sw128(b_addr + L::kC1 * L::kChunk + k * 16 * 128, L::kChunk, 1024);
+              if (PAIR == 2) umma_bf16_pair(tmem_base + L::kN1, da, db2, idesc2, (i | k) != 0);
+              else umma_bf16(tmem_base + L::kN1, da, db2, idesc2, (i | k) != 0);
             }
           }
-          umma_commit(empty_bar + s);
-          if (i == n_steps - 1) umma_commit(tmem_full_bar);
+          if (PAIR == 2) {
+            umma_commit_pair(empty_bar + s);
+            if (i == n_steps - 1) umma_commit_pair(tmem_full_bar);
+          } else {
+            umma_commit(empty_bar + s);
+            if (i == n_steps - 1) umma_commit(tmem_full_bar);
+          }
         }
         __syncwarp();
       }
@@ -156,47 +218,92 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
       const int co = co_tile * WG_M + q * 32 + lane;
       const int ldw = p.ldw;
 #pragma unroll 1
-      for (int sft = 0; sft < TAPS; ++sft) {
-#pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          float v[32];
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + sft * BN + c * 32, v);
-          const int ci0 = ci_tile * BN + c * 32;
-          if (co < p.Cout && ci0 < p.Cin) {
-            float* dst = p.dW + (int64_t)co * ldw + (CONV ? (r * 3 + sft) * p.Cin : 0) + ci0;
-            if (p.vec_ok) {
+      for (int cc = 0; cc < L::kNTot / 32; ++cc) {
+        float v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + cc * 32, v);
+        // accumulator column -> (source CTA of the B chunk, chunk within that CTA) -> (tap, channel)
+        const int col = cc * 32;
+        const bool second = col >= L::kN1;
+        const int colm = second ? col - L::kN1 : col;
+        const int per_cta = (second ? L::kN2 : L::kN1) / PAIR;
+        const int src = colm / per_cta, local = colm - src * per_cta;
+        const int g = (second ? L::kC1 : 0) + local / 64;                  // chunk index inside the source CTA's stage
+        const int sft = g / CH, ch = g - sft * CH;
+        const int ci0 = ci_tile * BN + src * (BN / PAIR) + ch * 64 + (local & 63);
+        if (co < p.Cout && ci0 < p.Cin) {
+          float* dst = p.dW + (int64_t)co * ldw + (CONV ? (r * 3 + sft) * p.Cin : 0) + ci0;
+          if (p.vec_ok) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
+            for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) red_add_f32(dst + j, v[j]);
-            }
+            for (int j = 0; j < 32; ++j) red_add_f32(dst + j, v[j]);
           }
         }
       }
       tc_fence_before();
     }
   }
-  __syncthreads();
+  if (PAIR == 2) { tc_fence_before(); cluster_sync_all(); } else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<TMEM_COLS>(tmem_base);
+    if (PAIR == 2) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+    else tmem_dealloc<TMEM_COLS>(tmem_base);
   }
 }
 
-template <int BN, bool CONV>
-static int launch_wgrad(const CUtensorMap& tdz, const CUtensorMap& tx, WgParams p, int co_tiles, int split, cudaStream_t st) {
-  using L = WgSmem<BN>;
+// Split-K factor: minimise (number of CTA waves) x (k-steps per CTA + fixed per-CTA cost).  A grid
+// of 150 CTAs on 148 SMs takes two waves; one k-step less per CTA and 147 CTAs take one.
+static int pick_split(int base_ctas, int k_steps_total) {
+  const int sms = ceb_num_sms();
+  const int kOverheadSteps = 10;         // pipeline fill + TMEM alloc + atomic epilogue, in k-step units
+  int best = 1;
+  int64_t best_cost = -1;
+  for (int sp = 1; sp <= 128 && sp <= k_steps_total; ++sp) {
+    const int per = (int)ceb_cdiv(k_steps_total, sp);
+    const int eff = (int)ceb_cdiv(k_steps_total, per);          // CTAs along K that actually get work
+    const int64_t waves = ceb_cdiv((int64_t)base_ctas * eff, sms);
+    const int64_t cost = waves * (per + kOverheadSteps);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = eff; }
+  }
+  return best;
+}
+
+template <int BN, bool CONV, int PAIR>
+static int launch_wgrad(const CUtensorMap& tdz, const CUtensorMap& tx, WgParams p, int co_units, int split, cudaStream_t st) {
+  using L = WgSmem<BN, CONV ? 3 : 1, PAIR>;
+  static_assert(L::kTotal <= 232448, "wgrad stage ring exceeds the 227 KB shared-memory limit");
   static bool configured = false;
   if (!configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel<BN, CONV>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel<BN, CONV, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
-  dim3 grid((unsigned)(co_tiles * (CONV ? 3 : 1) * p.ci_tiles), (unsigned)split, 1);
-  tc_wgrad_kernel<BN, CONV><<<grid, WG_THREADS, L::kTotal, st>>>(tdz, tx, p);
+  dim3 grid((unsigned)(PAIR * co_units * (CONV ? 3 : 1) * p.ci_tiles), (unsigned)split, 1);
+  if (PAIR == 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(WG_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = L::kTotal;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, tc_wgrad_kernel<BN, CONV, PAIR>, tdz, tx, p));
+    CEB_COUNT_LAUNCH(1);
+    return 0;
+  }
+  tc_wgrad_kernel<BN, CONV, PAIR><<<grid, WG_THREADS, L::kTotal, st>>>(tdz, tx, p);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
+}
+
+// CEB_WG_PAIR=0 disables / =1 forces the CTA-pair weight-gradient kernels where their shape rules allow.
+static int wg_pair_env() {
+  static const int v = [] { const char* e = getenv("CEB_WG_PAIR"); return e ? atoi(e) : -1; }();
+  return v;
 }
 
 // dW[Cout][3][3][Cin] (fp32) += wgrad(dz[N,H,W,Cout] bf16, x[N,H,W,Cin] bf16).
@@ -225,21 +332,22 @@ CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW
   if (int e = ceb_make_tmap_bf16(&tx, x, 4, dx, sx, bx)) return e;
 
   const int bn = (Cin % 128 == 0) ? 128 : 64;
+  // CTA pairs: 256 output channels per pair, each CTA stages 64 of the tile's 128 input channels
+  const bool pair = bn == 128 && Cout % 256 == 0 && (wg_pair_env() >= 0 ? wg_pair_env() != 0 : true);
   WgParams p{};
   p.dW = dW; p.Cout = Cout; p.Cin = Cin; p.H = H; p.W = W;
   p.k_steps_total = (int)ceb_cdiv(npix, WG_KPIX);
   p.ci_tiles = Cin / bn;
   p.tile_h = tile_h; p.tile_n = tile_n; p.ldw = 9 * Cin;
   p.vec_ok = (((uintptr_t)dW & 15) == 0) ? 1 : 0;
-  const int co_tiles = (int)ceb_cdiv(Cout, WG_M);
-  const int base_ctas = co_tiles * 3 * p.ci_tiles;
-  int split = (int)ceb_cdiv(ceb_num_sms(), base_ctas);
-  if (split > p.k_steps_total) split = p.k_steps_total;
-  if (split < 1) split = 1;
+  const int co_units = (int)ceb_cdiv(Cout, WG_M * (pair ? 2 : 1));
+  const int base_ctas = (pair ? 2 : 1) * co_units * 3 * p.ci_tiles;
+  int split = pick_split(base_ctas, p.k_steps_total);
   p.k_per_cta = (int)ceb_cdiv(p.k_steps_total, split);
   split = (int)ceb_cdiv(p.k_steps_total, p.k_per_cta);
-  if (bn == 128) return launch_wgrad<128, true>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
-  return launch_wgrad<64, true>(tdz, tx, p, co_tiles, split, (cudaStream_t)stream);
+  if (pair) return launch_wgrad<128, true, 2>(tdz, tx, p, co_units, split, (cudaStream_t)stream);
+  if (bn == 128) return launch_wgrad<128, true, 1>(tdz, tx, p, co_units, split, (cudaStream_t)stream);
+  return launch_wgrad<64, true, 1>(tdz, tx, p, co_units, split, (cudaStream_t)stream);
 }
 
 // C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A (row stride lda), B (row stride ldb) bf16
@@ -276,21 +384,22 @@ static int mn_acc_impl(const void* A, int64_t lda, const void* B, int64_t ldb, f
   if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
   uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)ldb * 2};
   if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, ba)) return e;
-  const int bn = (N % 128 == 0) ? 128 : 64;
+  // CTA pairs: 256 x 256 output tile per pair (each CTA: 128 rows of A, 128 columns of B)
+  const bool pair = N % 256 == 0 && M >= 256 && (wg_pair_env() >= 0 ? wg_pair_env() != 0 : true);
+  const int bn = pair ? 256 : ((N % 128 == 0) ? 128 : 64);
   WgParams p{};
   p.dW = C; p.Cout = M; p.Cin = N; p.H = 1; p.W = 1; p.ldw = ldc; p.k_limit = k_limit;
   p.vec_ok = (((uintptr_t)C & 15) == 0 && ldc % 4 == 0) ? 1 : 0;
   p.k_steps_total = (int)ceb_cdiv(K, WG_KPIX);
   p.ci_tiles = N / bn;
-  const int co_tiles = (int)ceb_cdiv(M, WG_M);
-  const int base_ctas = co_tiles * p.ci_tiles;
-  int split = (int)ceb_cdiv(ceb_num_sms(), base_ctas);
-  if (split > p.k_steps_total) split = p.k_steps_total;
-  if (split < 1) split = 1;
+  const int co_units = (int)ceb_cdiv(M, WG_M * (pair ? 2 : 1));
+  const int base_ctas = (pair ? 2 : 1) * co_units * p.ci_tiles;
+  int split = pick_split(base_ctas, p.k_steps_total);
   p.k_per_cta = (int)ceb_cdiv(p.k_steps_total, split);
   split = (int)ceb_cdiv(p.k_steps_total, p.k_per_cta);
-  if (bn == 128) return launch_wgrad<128, false>(ta, tb, p, co_tiles, split, (cudaStream_t)stream);
-  return launch_wgrad<64, false>(ta, tb, p, co_tiles, split, (cudaStream_t)stream);
+  if (pair) return launch_wgrad<256, false, 2>(ta, tb, p, co_units, split, (cudaStream_t)stream);
+  if (bn == 128) return launch_wgrad<128, false, 1>(ta, tb, p, co_units, split, (cudaStream_t)stream);
+  return launch_wgrad<64, false, 1>(ta, tb, p, co_units, split, (cudaStream_t)stream);
 }
 
 // Dense form (lda = M, ldb = N): M % 64 == N % 64 == 0.
