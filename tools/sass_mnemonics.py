@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""Per-kernel counts of the Blackwell-specific / communication SASS mnemonics in the native library
+(`cuobjdump -sass`).  Usage: sass_mnemonics.py [lib.so] > profiles/sass/mnemonics.md"""
+import collections
+import re
+import subprocess
+import sys
+
+PAT = re.compile(r"\b(UTCHMMA[\w.]*|UTMALDG[\w.]*|UTMASTG[\w.]*|UTCBAR[\w.]*|UTCATOMSWS[\w.]*|LDTM[\w.]*|UCGABAR_\w+|"
+                 r"SYNCS[\w.]*|RED\.[\w.]*|ATOM[\w.]*|REDG[\w.]*|LDG\.E[\w.]*\.SYS|STG\.E[\w.]*\.SYS|"
+                 r"STG\.E\.ENL2\.256|LDG\.E\.ENL2\.256[\w.]*|MUFU\.TANH)")
+
+
+def main():
+    lib = sys.argv[1] if len(sys.argv) > 1 else "commefficient_b200/lib/libceb200.so"
+    out = subprocess.run(["cuobjdump", "-sass", lib], stdout=subprocess.PIPE, text=True).stdout
+    per = collections.OrderedDict()
+    cur = None
+    for line in out.splitlines():
+        m = re.match(r"\s*Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            per[cur] = collections.Counter()
+            continue
+        if cur is None:
+            continue
+        m = PAT.search(line)
+        if m:
+            per[cur][m.group(1).rstrip(".")] += 1
+    print("# SASS evidence (cuobjdump -sass %s, sm_100a)\n" % lib)
+    print("Counts of the Blackwell-specific / communication mnemonics per kernel.  `UTCHMMA` = tcgen05.mma "
+          "(`.2CTA` = cta_group::2), `UTMALDG` = TMA tensor load (`.2CTA` = completion on the pair leader's "
+          "barrier), `LDTM` = tcgen05.ld (TMEM), `UTCBAR` = tcgen05.commit (`.2CTA.MULTICAST` = arrive in both "
+          "CTAs), `UTCATOMSWS` = tcgen05.alloc/dealloc, `UCGABAR_*` = cluster barrier, `SYNCS` = mbarrier, "
+          "`STG.E.ENL2.256` = 256-bit global store, `RED*` = reduction atomics, `*.SYS` = system-scope (peer) "
+          "accesses, `MUFU.TANH` = tanh.approx.\n")
+    for name, cnt in per.items():
+        if not cnt:
+            continue
+        print("* `%s`\n    %s" % (name, ", ".join("%s x%d" % kv for kv in sorted(cnt.items()))))
+
+
+if __name__ == "__main__":
+    main()
