@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no_native_nn", action="store_true",
                     help="run conv/linear layers on cuDNN/cuBLAS instead of the hand-written tcgen05 kernels")
+    ap.add_argument("--sync_results", action="store_true",
+                    help="block on every round's results inside FedModel.__call__ (reference behaviour) instead "
+                         "of --defer_results")
     ap.add_argument("--no_cuda_graphs", action="store_true",
                     help="launch the round's kernels one by one (for ncu launch lists; a graph replay hides them)")
     ap.add_argument("--clients_per_gpu", type=int, default=CLIENTS_PER_GPU)
@@ -170,6 +173,7 @@ def run_reference(cfg):
 
 # ---------------------------------------------------------------------------- our arm
 def run_ours(cfg):
+    import numpy as np
     import torch
     from commefficient_b200 import models
     from commefficient_b200.cv_train import compute_loss_train, compute_loss_val
@@ -196,7 +200,8 @@ def run_ours(cfg):
                      local_momentum=0.0, virtual_momentum=0.9, num_workers=clients, num_clients=NUM_CLIENTS,
                      local_batch_size=-1, num_epochs=1.0, dataset_name="CIFAR10", device="cuda",
                      precision=cfg.precision, backend=cfg.backend, model=cfg.model,
-                     no_native_nn=cfg.no_native_nn, no_cuda_graphs=cfg.no_cuda_graphs)
+                     no_native_nn=cfg.no_native_nn, no_cuda_graphs=cfg.no_cuda_graphs,
+                     defer_results=not cfg.sync_results)
     rt = init_runtime(args)
     torch.manual_seed(args.seed)
     torch.backends.cudnn.benchmark = True
@@ -218,6 +223,9 @@ def run_ours(cfg):
     def one_round(batch):
         out = fed(batch)
         opt.step()
+        # the step's result is read on the host every round (results are deferred: the async D2H
+        # issued by fed() has been overtaken by the server step's launches, not skipped)
+        float(np.mean(out[0]))
         return out
 
     def timed(rounds, steps, warmup):

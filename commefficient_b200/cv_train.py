@@ -37,6 +37,8 @@ def compute_loss_ce(model, batch, args):
 def _per_sample_ce(model, batch, args):
     """Per-sample ``(loss, correct)`` vectors -- lets the worker batch clients together."""
     images, targets = batch
+    if hasattr(model, "ce_per_sample"):
+        return model.ce_per_sample(images, targets)
     logits = model(images).float()
     return F.cross_entropy(logits, targets, reduction="none"), (logits.argmax(dim=1) == targets).float()
 
@@ -91,13 +93,17 @@ def run_batches(model, opt, lr_scheduler, loader, training, epoch_fraction, args
         elif batch[0].numel() < args.num_workers * args.local_batch_size:
             continue            # incomplete round
         loss, acc, dl, ul = model(batch)
+        deferred = getattr(args, "defer_results", False)
+        if deferred:
+            opt.step()          # queued behind the round on the GPU before the host looks at any value
         if np.any(np.isnan(loss)):
             if is_main:
                 print("LOSS OF %s IS NAN, TERMINATING TRAINING" % np.mean(loss))
             return np.nan, np.nan, np.nan, np.nan
         download += dl
         upload += ul
-        opt.step()
+        if not deferred:
+            opt.step()
         losses.extend(loss)
         accs.extend(acc)
         if args.dataset_name == "EMNIST" and is_main:

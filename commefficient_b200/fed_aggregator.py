@@ -70,17 +70,27 @@ class _DownloadTracker:
             self.hist = new
 
     def download_counts(self, clients: np.ndarray) -> torch.Tensor:
-        """Device int64 tensor: changed-coordinate count per participating client."""
-        suffix = torch.flip(torch.cumsum(torch.flip(self.hist, [0]), 0), [0])
-        start = torch.as_tensor(np.minimum(self.seen[clients] + 1, self.hist.numel() - 1),
-                                device=self.device)
-        out = suffix[start]
+        """Device float32 tensor: changed-coordinate count per participating client."""
+        start_np = np.minimum(self.seen[clients] + 1, self.hist.numel() - 1)
         self.seen[clients] = self.round
-        return out
+        start = torch.as_tensor(start_np, device=self.device)
+        if self.hist.is_cuda:
+            from .ops import native
+            out = torch.empty(len(clients), dtype=torch.float32, device=self.device)
+            native.call("ceb_tracker_counts", native.ptr(self.hist), self.hist.numel(), native.ptr(start),
+                        len(clients), native.ptr(out), native.stream_ptr(self.device))
+            return out
+        suffix = torch.flip(torch.cumsum(torch.flip(self.hist, [0]), 0), [0])
+        return suffix[start].to(torch.float32)
 
     def record_sparse(self, idx: torch.Tensor):
         self.round += 1
         self._grow(self.round)
+        if idx.is_cuda and idx.dtype == torch.int32 and idx.is_contiguous():
+            from .ops import native
+            native.call("ceb_tracker_record", native.ptr(idx), idx.numel(), native.ptr(self.last),
+                        native.ptr(self.hist), self.round, native.stream_ptr(self.device))
+            return
         li = idx.long()
         old = self.last[li]
         self.hist.index_add_(0, old, torch.full_like(old, -1))
@@ -92,6 +102,103 @@ class _DownloadTracker:
         self._grow(self.round)
         self.hist.zero_()
         self.hist[self.round] = self.d
+
+
+class _DeferredRound:
+    """One round's packed per-client results on their way to the host (``--defer_results``): an async
+    copy into a pinned buffer plus the event that completes it.  ``get()`` blocks on the event the
+    first time anything looks at a value."""
+
+    def __init__(self, host, event, watchdog=None):
+        self.host, self.event, self.watchdog = host, event, watchdog
+        self.array = None
+
+    def get(self) -> np.ndarray:
+        if self.array is None:
+            if self.event is not None:
+                self.event.synchronize()
+            self.array = self.host.numpy().copy()
+            if self.watchdog is not None:
+                self.watchdog.idle()
+        return self.array
+
+
+class DeferredArray:
+    """numpy-like view of one result column of a ``_DeferredRound``: converts itself on first use
+    (``np.mean(x)``, ``np.isnan(x)``, iteration, indexing, arithmetic, any ndarray attribute)."""
+
+    def __init__(self, rnd: _DeferredRound, fn):
+        self._rnd, self._fn, self._val = rnd, fn, None
+
+    def materialize(self) -> np.ndarray:
+        if self._val is None:
+            self._val = self._fn(self._rnd.get())
+        return self._val
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.materialize()
+        return a.astype(dtype) if dtype is not None else a
+
+    def __len__(self):
+        return len(self.materialize())
+
+    def __iter__(self):
+        return iter(self.materialize())
+
+    def __getitem__(self, i):
+        return self.materialize()[i]
+
+    def __getattr__(self, name):
+        return getattr(self.materialize(), name)
+
+    def __repr__(self):
+        return "DeferredArray(%r)" % (self.materialize(),)
+
+
+def _binop(name):
+    def op(self, other):
+        other = other.materialize() if isinstance(other, DeferredArray) else other
+        return getattr(self.materialize(), name)(other)
+    return op
+
+
+for _n in ("__add__", "__radd__", "__sub__", "__rsub__", "__mul__", "__rmul__", "__truediv__", "__rtruediv__",
+           "__lt__", "__le__", "__gt__", "__ge__", "__eq__", "__ne__"):
+    setattr(DeferredArray, _n, _binop(_n))
+DeferredArray.__hash__ = object.__hash__
+
+
+class DeferredTensor:
+    """torch-side counterpart for the download / upload byte vectors: any torch function that
+    receives one (``total += dl``) sees the materialised CPU tensor."""
+
+    def __init__(self, rnd: _DeferredRound, fn):
+        self._rnd, self._fn, self._val = rnd, fn, None
+
+    def materialize(self) -> torch.Tensor:
+        if self._val is None:
+            self._val = self._fn(self._rnd.get())
+        return self._val
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        def conv(a):
+            if isinstance(a, DeferredTensor):
+                return a.materialize()
+            if isinstance(a, (list, tuple)):
+                return type(a)(conv(x) for x in a)
+            return a
+        return func(*conv(args), **{k: conv(v) for k, v in (kwargs or {}).items()})
+
+    def __getattr__(self, name):
+        return getattr(self.materialize(), name)
+
+    def __getitem__(self, i):
+        return self.materialize()[i]
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.materialize().numpy()
+        return a.astype(dtype) if dtype is not None else a
 
 
 class FedModel:
@@ -130,6 +237,7 @@ class FedModel:
         self.last_unique_clients = np.zeros(0, dtype=np.int64)
         self.watchdog = RoundWatchdog(getattr(args, "watchdog_timeout", 0.0) or 0.0, self.rt.rank).start()
         self._fault = parse_fault()
+        self._result_ring = {}
         self.tracer = PhaseTracer(getattr(args, "trace_phases", "") or "", getattr(args, "trace_every", 50),
                                   self.rt.rank, self._trace_max, self.device.type)
         _CURRENT = self
@@ -264,16 +372,50 @@ class FedModel:
         else:
             gathered = local.float()
         self.watchdog.beat("results")
-        packed = torch.cat([gathered, dl.unsqueeze(1)], dim=1).cpu().numpy()   # the round's one D2H
+        packed_dev = torch.cat([gathered, dl.unsqueeze(1)], dim=1)
+        n_res = args.num_results_train
+        n_cl = self.num_clients
+        up_floats = 4.0 * _upload_floats(args, self.fp.numel)
+        uniq_t = torch.from_numpy(unique)
+
+        def _download(packed):
+            out = torch.zeros(n_cl)
+            out[uniq_t] = torch.from_numpy(4.0 * packed[:, -1]).float()
+            return out
+
+        def _upload(_packed):
+            out = torch.zeros(n_cl)
+            out[uniq_t] = up_floats
+            return out
+
+        if getattr(args, "defer_results", False) and packed_dev.is_cuda:
+            # the round's one D2H is asynchronous: the caller may queue the server step (opt.step())
+            # before anything waits for the values, so the GPU never idles behind the host
+            host = self._result_buffer(packed_dev.shape)
+            host.copy_(packed_dev, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            res_phase.__exit__(None, None, None)
+            rnd = _DeferredRound(host, ev, self.watchdog)
+            results = [DeferredArray(rnd, (lambda pk, i=i: pk[:, i].copy())) for i in range(n_res)]
+            return results + [DeferredTensor(rnd, _download), DeferredTensor(rnd, _upload)]
+        packed = packed_dev.cpu().numpy()   # the round's one D2H
         res_phase.__exit__(None, None, None)
         self.watchdog.idle()
-        n_res = args.num_results_train
         results = [packed[:, i].copy() for i in range(n_res)]
-        download = torch.zeros(self.num_clients)
-        download[torch.from_numpy(unique)] = torch.from_numpy(4.0 * packed[:, -1]).float()
-        upload = torch.zeros(self.num_clients)
-        upload[torch.from_numpy(unique)] = 4.0 * _upload_floats(args, self.fp.numel)
-        return results + [download, upload]
+        return results + [_download(packed), _upload(packed)]
+
+    def _result_buffer(self, shape):
+        """Pinned host buffers for deferred results, rotated so that a round's values stay valid
+        until two further rounds have been issued."""
+        key = tuple(shape)
+        ring = self._result_ring.setdefault(key, {"bufs": [], "next": 0})
+        if len(ring["bufs"]) < 3:
+            ring["bufs"].append(torch.empty(key, dtype=torch.float32, pin_memory=True))
+            return ring["bufs"][-1]
+        buf = ring["bufs"][ring["next"]]
+        ring["next"] = (ring["next"] + 1) % 3
+        return buf
 
     # -- validation ----------------------------------------------------------------------
     def _call_val(self, batch):

@@ -132,9 +132,9 @@ def run_batches(model, opt, lr_scheduler, loader, args, timer, training, epoch=N
         elif batch[0].numel() < args.num_workers * args.local_batch_size:
             continue
         loss, dl, ul = model(batch)
+        opt.step()              # before the byte counts / loss are read: with --defer_results those are lazy
         download += dl
         upload += ul
-        opt.step()
         loss = float(np.mean(loss))
         losses.append(loss)
         train_time = timer()

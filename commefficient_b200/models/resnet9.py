@@ -131,6 +131,16 @@ class ResNet9(nn.Module):
                 return tc.resnet9_forward(self, x)
         return self.n(x)
 
+    def ce_per_sample(self, x, targets):
+        """Per-sample ``(cross-entropy, top-1 correct)``.  On the native path the classifier head and
+        the loss are fused with the trunk's autograd Function (``ops/tc.py:_ResNet9CEFn``)."""
+        if nnops.native_enabled() and torch.is_grad_enabled():
+            from ..ops import tc
+            if tc.resnet9_supported(self, x) and tc.head_supported(self.n, self.n.channels["layer3"]):
+                return tc.resnet9_ce_per_sample(self, x, targets)
+        logits = self(x).float()
+        return (F.cross_entropy(logits, targets, reduction="none"), (logits.argmax(dim=1) == targets).float())
+
     def finetune_parameters(self):
         # (the reference version dereferences an undefined ``self.iid`` -- SURVEY Q-list)
         return self.n.finetune_parameters()

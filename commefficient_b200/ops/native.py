@@ -62,6 +62,8 @@ _SIGNATURES = {
     "ceb_add_gaussian_noise": ([c_ptr, c_i64, c_f32, c_u64, c_u64, c_ptr], c_i32),
     "ceb_fedavg_delta": ([c_ptr, c_ptr, c_ptr, c_f32, c_i64, c_ptr], c_i32),
     "ceb_count_changed": ([c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr], c_i32),
+    "ceb_tracker_record": ([c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr], c_i32),
+    "ceb_tracker_counts": ([c_ptr, c_i32, c_ptr, c_i32, c_ptr, c_ptr], c_i32),
 }
 
 # Entry points added by optional translation units (peer memory, tcgen05 GEMM/conv);

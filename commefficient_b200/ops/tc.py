@@ -42,6 +42,8 @@ native.register_signatures({
                                      native.c_ptr], native.c_i32),
     "ceb_colsum_bf16": ([native.c_ptr, native.c_i64, native.c_i64, native.c_i32, native.c_ptr, native.c_ptr],
                         native.c_i32),
+    "ceb_conv_weights_prepare": ([native.c_i32, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                                  native.c_ptr], native.c_i32),
     "ceb_gemm_bf16_tn_rows": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i64,
                                native.c_i32, native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
                                native.c_ptr, native.c_ptr], native.c_i32),
@@ -120,6 +122,29 @@ def dgrad_weights(w_krsc_f32: torch.Tensor) -> torch.Tensor:
     native.call("ceb_conv_w_dgrad_layout", native.ptr(w_krsc_f32), native.ptr(out), cout, cin,
                 native.stream_ptr(out.device))
     return out
+
+
+def prepare_conv_weights(weights_krsc_f32, want_cast=True, want_rot=True):
+    """bf16 forward copies and data-gradient layouts (``dgrad_weights``) of a list of fp32
+    ``[Cout,3,3,Cin]`` conv weights in ONE launch.  Returns ``(casts, rots)`` (lists; None entries
+    where not requested)."""
+    import ctypes
+    n = len(weights_krsc_f32)
+    dev = weights_krsc_f32[0].device
+    casts = [torch.empty(w.shape, dtype=torch.bfloat16, device=dev) if want_cast else None for w in weights_krsc_f32]
+    rots = [torch.empty((w.shape[3], 3, 3, w.shape[0]), dtype=torch.bfloat16, device=dev) if want_rot else None
+            for w in weights_krsc_f32]
+    PtrArr = ctypes.c_void_p * n
+    IntArr = ctypes.c_int * n
+    src = PtrArr(*[w.data_ptr() for w in weights_krsc_f32])
+    cst = PtrArr(*[(c.data_ptr() if c is not None else None) for c in casts])
+    rot = PtrArr(*[(r.data_ptr() if r is not None else None) for r in rots])
+    cout = IntArr(*[int(w.shape[0]) for w in weights_krsc_f32])
+    cin = IntArr(*[int(w.shape[3]) for w in weights_krsc_f32])
+    native.call("ceb_conv_weights_prepare", n, ctypes.cast(src, ctypes.c_void_p), ctypes.cast(cst, ctypes.c_void_p),
+                ctypes.cast(rot, ctypes.c_void_p), ctypes.cast(cout, ctypes.c_void_p), ctypes.cast(cin, ctypes.c_void_p),
+                native.stream_ptr(dev))
+    return casts, rots
 
 
 def cast_bf16(src: torch.Tensor) -> torch.Tensor:
@@ -464,82 +489,157 @@ def resnet9_supported(model, x: torch.Tensor) -> bool:
     return fp is not None and fp.layout == "nhwc"
 
 
+def _r9_convs(net):
+    return [net.prep.conv, net.layer1.conv, net.res1.res1.conv, net.res1.res2.conv, net.layer2.conv,
+            net.layer3.conv, net.res3.res1.conv, net.res3.res2.conv]
+
+
+def _r9_features(x, net):
+    """Forward of the convolutional trunk: pooled bf16 features ``[N, C3]``, the activations the
+    backward needs, and the data-gradient weight layouts (prepared in the same launch as the bf16
+    forward copies)."""
+    convs = _r9_convs(net)
+    wb, wd = prepare_conv_weights([_krsc(c.weight.data) for c in convs[1:]])    # one launch: 7 casts + 7 dgrad layouts
+    xb = x.float().permute(0, 2, 3, 1).contiguous()           # NHWC fp32 (no copy for channels_last input)
+    col = im2col_c3(xb)                                       # [N*1024, 64] bf16
+    a0 = gemm_tn(col, _stem_weight_pad(_krsc(convs[0].weight.data)), relu=True).view(x.shape[0], 32, 32, -1)
+    a1 = conv3x3_nhwc(a0, wb[0], relu=True)
+    p1 = maxpool_nhwc(a1, 2)
+    r1a = conv3x3_nhwc(p1, wb[1], relu=True)
+    r1b = conv3x3_nhwc(r1a, wb[2], relu=True)
+    s1 = p1 + r1b
+    a2 = conv3x3_nhwc(s1, wb[3], relu=True)
+    p2 = maxpool_nhwc(a2, 2)
+    a3 = conv3x3_nhwc(p2, wb[4], relu=True)
+    p3 = maxpool_nhwc(a3, 2)
+    r3a = conv3x3_nhwc(p3, wb[5], relu=True)
+    r3b = conv3x3_nhwc(r3a, wb[6], relu=True)
+    s3 = p3 + r3b
+    f = maxpool_nhwc(s3, 4).view(x.shape[0], -1)
+    return f, (col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3), [None] + wd
+
+
+def _r9_backward(net, saved, wd, df):
+    """Backward of the trunk from ``df`` (bf16 ``[N, C3]``): weight gradients are accumulated into
+    the flat fp32 gradient buffer."""
+    col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3 = saved
+    convs = _r9_convs(net)
+    gw = [_krsc(c.weight.grad) for c in convs]                       # fp32 KRSC views of the flat gradient
+    n = a0.shape[0]
+    ds3 = maxpool_bwd_nhwc(s3, df.view(n, 1, 1, -1), 4, relu_mask=False)
+
+    dz = relu_bwd(r3b, ds3)
+    conv3x3_wgrad_nhwc(dz, r3a, gw[7])
+    dz = conv3x3_nhwc(dz, wd[7], relu_mask=r3a)
+    conv3x3_wgrad_nhwc(dz, p3, gw[6])
+    dp3 = ds3 + conv3x3_nhwc(dz, wd[6])
+
+    dz = maxpool_bwd_nhwc(a3, dp3, 2, relu_mask=True)
+    conv3x3_wgrad_nhwc(dz, p2, gw[5])
+    dp2 = conv3x3_nhwc(dz, wd[5])
+
+    dz = maxpool_bwd_nhwc(a2, dp2, 2, relu_mask=True)
+    conv3x3_wgrad_nhwc(dz, s1, gw[4])
+    ds1 = conv3x3_nhwc(dz, wd[4])
+
+    dz = relu_bwd(r1b, ds1)
+    conv3x3_wgrad_nhwc(dz, r1a, gw[3])
+    dz = conv3x3_nhwc(dz, wd[3], relu_mask=r1a)
+    conv3x3_wgrad_nhwc(dz, p1, gw[2])
+    dp1 = ds1 + conv3x3_nhwc(dz, wd[2])
+
+    dz = maxpool_bwd_nhwc(a1, dp1, 2, relu_mask=True)
+    conv3x3_wgrad_nhwc(dz, a0, gw[1])
+    da0 = conv3x3_nhwc(dz, wd[1], relu_mask=a0)
+
+    g0 = torch.zeros((da0.shape[3], 64), dtype=torch.float32, device=da0.device)
+    gemm_mn_acc(da0.view(-1, da0.shape[3]), col, g0)
+    gw[0].view(da0.shape[3], 27).add_(g0[:, :27])
+
+
 class _ResNet9Fn(torch.autograd.Function):
     """Whole-network forward/backward of ResNet-9 (no BatchNorm) on the hand-written kernels:
     implicit-GEMM conv + fused ReLU (tcgen05), fused ReLU/max-pool backward, MN-major wgrad
     accumulating straight into the flat fp32 gradient buffer, and the 3-channel stem lowered to
-    im2col + the same tensor-core GEMMs.  Only the 512 -> classes head (5 MFLOP) stays on library ops."""
+    im2col + the same tensor-core GEMMs.  Returns logits; the 512 -> classes head (5 MFLOP) runs on
+    library ops here (``_ResNet9CEFn`` fuses it with the loss)."""
 
     @staticmethod
     def forward(ctx, x, net, *weights):
-        import torch.nn.functional as F
-        convs = [net.prep.conv, net.layer1.conv, net.res1.res1.conv, net.res1.res2.conv, net.layer2.conv,
-                 net.layer3.conv, net.res3.res1.conv, net.res3.res2.conv]
-        wb = [cast_bf16(_krsc(c.weight.data)) for c in convs[1:]]
-        xb = x.float().permute(0, 2, 3, 1).contiguous()           # NHWC fp32 (no copy for channels_last input)
-        col = im2col_c3(xb)                                       # [N*1024, 64] bf16
-        a0 = gemm_tn(col, _stem_weight_pad(_krsc(convs[0].weight.data)), relu=True).view(x.shape[0], 32, 32, -1)
-        a1 = conv3x3_nhwc(a0, wb[0], relu=True)
-        p1 = maxpool_nhwc(a1, 2)
-        r1a = conv3x3_nhwc(p1, wb[1], relu=True)
-        r1b = conv3x3_nhwc(r1a, wb[2], relu=True)
-        s1 = p1 + r1b
-        a2 = conv3x3_nhwc(s1, wb[3], relu=True)
-        p2 = maxpool_nhwc(a2, 2)
-        a3 = conv3x3_nhwc(p2, wb[4], relu=True)
-        p3 = maxpool_nhwc(a3, 2)
-        r3a = conv3x3_nhwc(p3, wb[5], relu=True)
-        r3b = conv3x3_nhwc(r3a, wb[6], relu=True)
-        s3 = p3 + r3b
-        f = maxpool_nhwc(s3, 4).view(x.shape[0], -1)
+        f, saved, wd = _r9_features(x, net)
         logits = (f.float() @ net.linear.weight.data.t()) * net.out_scale
-        ctx.net = net
-        ctx.saved = (col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3, f)
+        ctx.net, ctx.wd, ctx.saved, ctx.f = net, wd, saved, f
         return logits
 
     @staticmethod
     def backward(ctx, dlogits):
-        net = ctx.net
-        col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3, f = ctx.saved
-        convs = [net.prep.conv, net.layer1.conv, net.res1.res1.conv, net.res1.res2.conv, net.layer2.conv,
-                 net.layer3.conv, net.res3.res1.conv, net.res3.res2.conv]
-        gw = [_krsc(c.weight.grad) for c in convs]                       # fp32 KRSC views of the flat gradient
-        wd = [None] + [dgrad_weights(_krsc(c.weight.data)) for c in convs[1:]]
-        n = a0.shape[0]
-
+        net, f = ctx.net, ctx.f
         dl = dlogits.float() * net.out_scale
         net.linear.weight.grad.add_(dl.t() @ f.float())
-        df = (dl @ net.linear.weight.data).to(torch.bfloat16).view(n, 1, 1, -1).contiguous()
-        ds3 = maxpool_bwd_nhwc(s3, df, 4, relu_mask=False)
-
-        dz = relu_bwd(r3b, ds3)
-        conv3x3_wgrad_nhwc(dz, r3a, gw[7])
-        dz = conv3x3_nhwc(dz, wd[7], relu_mask=r3a)
-        conv3x3_wgrad_nhwc(dz, p3, gw[6])
-        dp3 = ds3 + conv3x3_nhwc(dz, wd[6])
-
-        dz = maxpool_bwd_nhwc(a3, dp3, 2, relu_mask=True)
-        conv3x3_wgrad_nhwc(dz, p2, gw[5])
-        dp2 = conv3x3_nhwc(dz, wd[5])
-
-        dz = maxpool_bwd_nhwc(a2, dp2, 2, relu_mask=True)
-        conv3x3_wgrad_nhwc(dz, s1, gw[4])
-        ds1 = conv3x3_nhwc(dz, wd[4])
-
-        dz = relu_bwd(r1b, ds1)
-        conv3x3_wgrad_nhwc(dz, r1a, gw[3])
-        dz = conv3x3_nhwc(dz, wd[3], relu_mask=r1a)
-        conv3x3_wgrad_nhwc(dz, p1, gw[2])
-        dp1 = ds1 + conv3x3_nhwc(dz, wd[2])
-
-        dz = maxpool_bwd_nhwc(a1, dp1, 2, relu_mask=True)
-        conv3x3_wgrad_nhwc(dz, a0, gw[1])
-        da0 = conv3x3_nhwc(dz, wd[1], relu_mask=a0)
-
-        g0 = torch.zeros((da0.shape[3], 64), dtype=torch.float32, device=da0.device)
-        gemm_mn_acc(da0.view(-1, da0.shape[3]), col, g0)
-        gw[0].view(da0.shape[3], 27).add_(g0[:, :27])
+        df = (dl @ net.linear.weight.data).to(torch.bfloat16).contiguous()
+        _r9_backward(net, ctx.saved, ctx.wd, df)
         return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
+
+
+native.register_signatures({
+    "ceb_linear_ce_head": ([native.c_ptr, native.c_ptr, native.c_f32, native.c_ptr, native.c_i32, native.c_i32,
+                            native.c_i32, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                            native.c_ptr], native.c_i32),
+})
+
+
+def linear_ce_head(feat, weight, scale, labels, g=None, dW=None):
+    """Fused classifier head + cross-entropy (``ceb_linear_ce_head``).  ``g is None``: returns per-sample
+    ``(loss, correct)``; otherwise the backward for ``sum(g * loss)``: returns ``dfeat`` (bf16) and
+    accumulates into ``dW``."""
+    N, F_ = feat.shape
+    C = weight.shape[0]
+    dev = feat.device
+    labels = labels.contiguous()
+    if g is None:
+        loss = torch.empty(N, dtype=torch.float32, device=dev)
+        correct = torch.empty(N, dtype=torch.float32, device=dev)
+        native.call("ceb_linear_ce_head", native.ptr(feat), native.ptr(weight), float(scale), native.ptr(labels), N, F_,
+                    C, None, native.ptr(loss), native.ptr(correct), None, None, native.stream_ptr(dev))
+        return loss, correct
+    dfeat = torch.empty_like(feat)
+    native.call("ceb_linear_ce_head", native.ptr(feat), native.ptr(weight), float(scale), native.ptr(labels), N, F_, C,
+                native.ptr(g), None, None, native.ptr(dfeat), native.ptr(dW), native.stream_ptr(dev))
+    return dfeat
+
+
+def head_supported(net, feat_dim: int) -> bool:
+    w = net.linear.weight
+    return (w.shape[0] <= 32 and feat_dim % 64 == 0 and feat_dim <= 2048 and w.is_contiguous()
+            and w.dtype == torch.float32 and w.grad is not None and w.grad.is_contiguous())
+
+
+class _ResNet9CEFn(torch.autograd.Function):
+    """ResNet-9 trunk + classifier head + per-sample cross-entropy / top-1 correctness: the head, the
+    scale, softmax, NLL, arg-max and all of their backward are ONE kernel each way."""
+
+    @staticmethod
+    def forward(ctx, x, labels, net, *weights):
+        f, saved, wd = _r9_features(x, net)
+        f = f.contiguous()
+        loss, correct = linear_ce_head(f, net.linear.weight.data, net.out_scale, labels)
+        ctx.net, ctx.wd, ctx.saved, ctx.f, ctx.labels = net, wd, saved, f, labels
+        ctx.mark_non_differentiable(correct)
+        return loss, correct
+
+    @staticmethod
+    def backward(ctx, gloss, _gcorrect):
+        net = ctx.net
+        g = gloss.float().contiguous()
+        df = linear_ce_head(ctx.f, net.linear.weight.data, net.out_scale, ctx.labels, g=g, dW=net.linear.weight.grad)
+        _r9_backward(net, ctx.saved, ctx.wd, df)
+        return (None, None, None) + (None,) * (len(ctx.needs_input_grad) - 3)
+
+
+def resnet9_ce_per_sample(model, x: torch.Tensor, labels: torch.Tensor):
+    net = model.n
+    weights = [p for p in net.parameters() if p.requires_grad]
+    return _ResNet9CEFn.apply(x, labels, net, *weights)
 
 
 def resnet9_forward(model, x: torch.Tensor) -> torch.Tensor:

@@ -130,6 +130,9 @@ _FLAGS = [
                    "nhwc = (out,kh,kw,in), channels_last end to end (auto: nhwc on CUDA)"),
         _flag("no_cuda_graphs", store_true=True,
               help="do not capture the batched client forward/backward into a CUDA graph"),
+        _flag("defer_results", store_true=True,
+              help="return each round's losses / byte counts as lazily materialised arrays (async D2H): "
+                   "call opt.step() before reading them and the host never stalls the GPU"),
         _flag("trace_phases", "", str, help="append per-phase CUDA-event timings (max over ranks) to this "
                                             "JSONL file; phases are NVTX ranges too"),
         _flag("trace_every", 50, int, help="rounds per --trace_phases record"),

@@ -316,3 +316,59 @@ CEB_API int ceb_count_changed(const float* w, float* prev, uint8_t* mask, int64_
   CEB_CHECK_LAUNCH();
   return 0;
 }
+
+
+// ------------------------------------------------------------------ download-byte tracker
+// State (commefficient_b200/fed_aggregator.py:_DownloadTracker): last[d] = server round of every
+// coordinate's last change, hist[r] = number of coordinates whose last change was round r.
+// record: the k coordinates in idx move from their old bucket to bucket `round`.  Most of them share a
+// handful of old buckets, so decrements are aggregated per warp (match.any) before the atomic.
+__global__ void __launch_bounds__(256)
+tracker_record_kernel(const int* __restrict__ idx, int64_t k, long long* __restrict__ last,
+                      unsigned long long* __restrict__ hist, long long round) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = i < k;
+  long long old = -1;
+  if (active) {
+    const int c = idx[i];
+    old = last[c];
+    last[c] = round;
+  }
+  const unsigned peers = __match_any_sync(0xffffffffu, old);
+  const int leader = __ffs(peers) - 1;
+  if (active && (int)(threadIdx.x & 31) == leader)
+    atomicAdd(hist + old, (unsigned long long)(-(long long)__popc(peers)));
+  if (i == 0) atomicAdd(hist + round, (unsigned long long)k);
+}
+
+CEB_API int ceb_tracker_record(const int* idx, int64_t k, int64_t* last, int64_t* hist, int64_t round, void* stream) {
+  CEB_REQUIRE(idx && last && hist && k > 0 && round > 0, "ceb_tracker_record: bad arguments");
+  tracker_record_kernel<<<(unsigned)ceb_cdiv(k, 256), 256, 0, (cudaStream_t)stream>>>(
+      idx, k, (long long*)last, (unsigned long long*)hist, (long long)round);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// out[j] = sum_{r >= start[j]} hist[r]  (one warp per query; n is the number of rounds so far, small)
+__global__ void __launch_bounds__(256)
+tracker_counts_kernel(const long long* __restrict__ hist, int n, const long long* __restrict__ start, int m,
+                      float* __restrict__ out) {
+  const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (j >= m) return;
+  const int lane = threadIdx.x & 31;
+  long long s = 0;
+  for (long long r = start[j] + lane; r < n; r += 32) s += hist[r];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) out[j] = (float)s;
+}
+
+CEB_API int ceb_tracker_counts(const int64_t* hist, int n, const int64_t* start, int m, float* out, void* stream) {
+  CEB_REQUIRE(hist && start && out && n > 0 && m > 0, "ceb_tracker_counts: bad arguments");
+  tracker_counts_kernel<<<(unsigned)ceb_cdiv(m, 8), 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)hist, n, (const long long*)start, m, out);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}

@@ -468,3 +468,122 @@ CEB_API int ceb_colsum_bf16(const void* x_bf16, int64_t ld, int64_t rows, int co
   CEB_CHECK_LAUNCH();
   return 0;
 }
+
+
+// ------------------------------------------------------------------ classifier head + cross-entropy
+// logits = scale * feat @ W^T  (feat bf16 [N][F], W fp32 [C][F], C <= 32, F % 64 == 0, F <= 2048),
+// per-sample cross-entropy and top-1 correctness; with g != NULL the backward of sum_s g[s] * loss[s]:
+// dfeat (bf16) and dW (+=, fp32).  One warp per sample, lane c owns logit c, W (and the dW partials)
+// live in shared memory.  Replaces ~25 library launches of 2-7 us each (bf16 GEMM, scale, softmax,
+// nll_loss, argmax, compare, their backward, two more GEMMs) behind the reference's
+// `loss = criterion(model(x), y); acc = accuracy(...)` (cv_train.py:67-72) on a [N, 10] problem.
+__global__ void __launch_bounds__(256)
+linear_ce_head_kernel(const __nv_bfloat16* __restrict__ feat, const float* __restrict__ W, float scale,
+                      const int64_t* __restrict__ labels, int N, int F, int C, const float* __restrict__ g,
+                      float* __restrict__ loss, float* __restrict__ correct, __nv_bfloat16* __restrict__ dfeat,
+                      float* __restrict__ dW) {
+  extern __shared__ float hs[];
+  float* Ws = hs;                       // [C][F]
+  float* dWs = hs + (size_t)C * F;      // [C][F], backward only
+  const bool bwd = g != nullptr;
+  for (int i = threadIdx.x; i < C * F; i += blockDim.x) {
+    Ws[i] = W[i];
+    if (bwd) dWs[i] = 0.f;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int J = F >> 6;                 // bf16 pairs per lane
+  for (int s = blockIdx.x * wpb + warp; s < N; s += gridDim.x * wpb) {
+    float x[64];                        // F <= 2048 -> up to 32 pairs
+    const __nv_bfloat162* fr = reinterpret_cast<const __nv_bfloat162*>(feat + (size_t)s * F);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      if (j < J) {
+        const float2 v = __bfloat1622float2(fr[j * 32 + lane]);
+        x[2 * j] = v.x; x[2 * j + 1] = v.y;
+      }
+    }
+    float mylogit = -INFINITY;
+    for (int c = 0; c < C; ++c) {
+      const float* wr = Ws + (size_t)c * F;
+      float a = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < J) a = fmaf(x[2 * j], wr[j * 64 + 2 * lane], fmaf(x[2 * j + 1], wr[j * 64 + 2 * lane + 1], a));
+      a = warp_sum(a) * scale;
+      if (lane == c) mylogit = a;
+    }
+    // softmax statistics and argmax (first maximal index, like torch.argmax)
+    float mx = mylogit;
+    int am = lane < C ? lane : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, am, o);
+      if (om > mx || (om == mx && oi < am)) { mx = om; am = oi; }
+    }
+    const float e = lane < C ? __expf(mylogit - mx) : 0.f;
+    const float lse = mx + __logf(warp_sum(e));
+    const int label = (int)labels[s];
+    const float at_label = __shfl_sync(0xffffffffu, mylogit, label & 31);
+    if (!bwd) {
+      if (lane == 0) {
+        loss[s] = lse - at_label;
+        correct[s] = (am == label) ? 1.f : 0.f;
+      }
+      continue;
+    }
+    // d raw logit (before the scale) of lane c
+    const float dl = lane < C ? g[s] * (__expf(mylogit - lse) - (lane == label ? 1.f : 0.f)) * scale : 0.f;
+    float dx[64];
+#pragma unroll
+    for (int j = 0; j < 64; ++j) dx[j] = 0.f;
+    for (int c = 0; c < C; ++c) {
+      const float d = __shfl_sync(0xffffffffu, dl, c);
+      const float* wr = Ws + (size_t)c * F;
+      float* dwr = dWs + (size_t)c * F;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        if (j < J) {
+          const int f = j * 64 + 2 * lane;
+          dx[2 * j] = fmaf(d, wr[f], dx[2 * j]);
+          dx[2 * j + 1] = fmaf(d, wr[f + 1], dx[2 * j + 1]);
+          atomicAdd(dwr + f, d * x[2 * j]);
+          atomicAdd(dwr + f + 1, d * x[2 * j + 1]);
+        }
+      }
+    }
+    __nv_bfloat162* dr = reinterpret_cast<__nv_bfloat162*>(dfeat + (size_t)s * F);
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < J) dr[j * 32 + lane] = __floats2bfloat162_rn(dx[2 * j], dx[2 * j + 1]);
+  }
+  if (bwd) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < C * F; i += blockDim.x) {
+      const float v = dWs[i];
+      if (v != 0.f) atomicAdd(dW + i, v);
+    }
+  }
+}
+
+CEB_API int ceb_linear_ce_head(const void* feat_bf16, const float* W, float scale, const int64_t* labels, int N, int F,
+                               int C, const float* g, float* loss, float* correct, void* dfeat_bf16, float* dW,
+                               void* stream) {
+  CEB_REQUIRE(feat_bf16 && W && labels && N > 0, "ceb_linear_ce_head: bad arguments");
+  CEB_REQUIRE(C >= 1 && C <= 32 && F % 64 == 0 && F >= 64 && F <= 2048, "ceb_linear_ce_head: need C <= 32, F %% 64 == 0, F <= 2048 (C=%d F=%d)", C, F);
+  CEB_REQUIRE(g ? (dfeat_bf16 && dW) : (loss && correct), "ceb_linear_ce_head: missing outputs");
+  const size_t smem = (size_t)C * F * sizeof(float) * (g ? 2 : 1);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(linear_ce_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  int blocks = (int)ceb_cdiv(N, 8);
+  if (blocks > ceb_num_sms()) blocks = ceb_num_sms();
+  linear_ce_head_kernel<<<blocks, 256, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)feat_bf16, W, scale, labels, N, F,
+                                                                    C, g, loss, correct, (__nv_bfloat16*)dfeat_bf16, dW);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}

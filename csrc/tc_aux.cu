@@ -4,6 +4,8 @@
 #include <cuda_bf16.h>
 #include "common.cuh"
 
+#define CEB_WPREP_MAX 16
+
 // ------------------------------------------------------------------ casts / weight layouts
 __global__ void __launch_bounds__(256)
 cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
@@ -94,6 +96,67 @@ CEB_API int ceb_conv_w_dgrad_layout(const float* w_krsc, void* dst_bf16, int Cou
   CEB_REQUIRE(w_krsc && dst_bf16 && Cout > 0 && Cin > 0, "ceb_conv_w_dgrad_layout: bad arguments");
   const int64_t total = (int64_t)Cout * 9 * Cin;
   w_rot180_t_kernel<float><<<ceb_grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(w_krsc, (__nv_bfloat16*)dst_bf16, Cout, Cin);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ one-launch weight preparation
+// For up to CEB_WPREP_MAX 3x3 conv layers at once: the bf16 K-major copy used by the forward conv
+// and (optionally) the bf16 rotated / transposed copy used by the data-gradient conv -- what
+// ceb_cast_f32_bf16 + ceb_conv_w_dgrad_layout do per layer, in ONE launch instead of two per layer
+// (a 100-client ResNet-9 round is launch-latency bound on exactly such 3-5 us kernels).
+struct WPrepTable {
+  const float* src[CEB_WPREP_MAX];
+  __nv_bfloat16* cast[CEB_WPREP_MAX];
+  __nv_bfloat16* rot[CEB_WPREP_MAX];
+  int cout[CEB_WPREP_MAX];
+  int cin[CEB_WPREP_MAX];
+  int n;
+};
+
+__global__ void __launch_bounds__(256)
+wprep_kernel(WPrepTable t) {
+  const int layer = blockIdx.y;
+  if (layer >= t.n) return;
+  const float* __restrict__ src = t.src[layer];
+  __nv_bfloat16* __restrict__ cast = t.cast[layer];
+  __nv_bfloat16* __restrict__ rot = t.rot[layer];
+  const int Cout = t.cout[layer], Cin = t.cin[layer];
+  const int64_t total = (int64_t)Cout * 9 * Cin;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (cast) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride)
+      cast[i] = __float2bfloat16(src[i]);
+  }
+  if (rot) {
+    // o indexes rot: ((ci*3 + r2)*3 + s2)*Cout + co  (coalesced stores; the strided re-reads hit L2)
+    for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += stride) {
+      const int co = (int)(o % Cout);
+      int64_t u = o / Cout;
+      const int s2 = (int)(u % 3); u /= 3;
+      const int r2 = (int)(u % 3);
+      const int ci = (int)(u / 3);
+      rot[o] = __float2bfloat16(src[(((int64_t)co * 3 + (2 - r2)) * 3 + (2 - s2)) * Cin + ci]);
+    }
+  }
+}
+
+CEB_API int ceb_conv_weights_prepare(int n_layers, const float* const* src, void* const* cast_bf16, void* const* rot_bf16,
+                                     const int* cout, const int* cin, void* stream) {
+  CEB_REQUIRE(n_layers > 0 && n_layers <= CEB_WPREP_MAX && src && cout && cin, "ceb_conv_weights_prepare: 1..%d layers", CEB_WPREP_MAX);
+  WPrepTable t{};
+  t.n = n_layers;
+  for (int i = 0; i < n_layers; ++i) {
+    CEB_REQUIRE(src[i] && cout[i] > 0 && cin[i] > 0, "ceb_conv_weights_prepare: bad layer %d", i);
+    t.src[i] = src[i];
+    t.cast[i] = cast_bf16 ? (__nv_bfloat16*)cast_bf16[i] : nullptr;
+    t.rot[i] = rot_bf16 ? (__nv_bfloat16*)rot_bf16[i] : nullptr;
+    t.cout[i] = cout[i];
+    t.cin[i] = cin[i];
+  }
+  dim3 grid((unsigned)(2 * ceb_num_sms() / n_layers + 1), (unsigned)n_layers);
+  wprep_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(t);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;

@@ -123,6 +123,11 @@ int ceb_fedavg_delta(float* acc, const float* w0, const float* wloc, float weigh
  * (reference: fed_aggregator.py:244-250) */
 int ceb_count_changed(const float* w, float* prev, uint8_t* mask, int64_t n, unsigned long long* count,
                       void* stream);
+/* Download-byte tracker (no counterpart in the reference, which diffs full weight copies on the host):
+ * record: coordinates idx[0..k) move from bucket last[idx] to bucket `round` (last updated, hist
+ * decremented / incremented); counts: out[j] = sum of hist[r] for r >= start[j]. */
+int ceb_tracker_record(const int* idx, int64_t k, int64_t* last, int64_t* hist, int64_t round, void* stream);
+int ceb_tracker_counts(const int64_t* hist, int n, const int64_t* start, int m, float* out, void* stream);
 
 /* ---- tensor-core layers: tcgen05.mma + TMEM accumulators + TMA-staged operands --
  * (reference: the cuBLAS / cuDNN calls behind nn.Linear / nn.Conv2d, models/resnet9.py:36-37,
@@ -145,6 +150,12 @@ int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H
 /* dst[ci][2-r][2-s][co] (bf16) = w[co][r][s][ci] (fp32): weights of the data-gradient convolution. */
 int ceb_conv_w_dgrad_layout(const float* w_krsc, void* dst_bf16, int Cout, int Cin, void* stream);
 int ceb_cast_f32_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
+/* ceb_cast_f32_bf16 + ceb_conv_w_dgrad_layout for up to 16 conv layers in ONE launch: layer i has
+ * fp32 [cout][3][3][cin] weights src[i]; cast_bf16[i] (may be NULL / the array may be NULL) receives
+ * the bf16 copy, rot_bf16[i] the [cin][3][3][cout] data-gradient layout.  The pointer arrays are HOST
+ * arrays of device pointers (copied into the kernel's parameter block). */
+int ceb_conv_weights_prepare(int n_layers, const float* const* src, void* const* cast_bf16, void* const* rot_bf16,
+                             const int* cout, const int* cin, void* stream);
 /* dst[c][r] (bf16, row stride ldo >= R, ldo even) = src[r][c] (fp32 [R][C]): the K-major bf16 copy of
  * a weight stored the other way round (GPT-2 Conv1D [in][out]; the tied LM head in its dgrad). */
 int ceb_cast_transpose_f32_bf16(const float* src, void* dst_bf16, int R, int C, int64_t ldo, void* stream);
@@ -206,6 +217,12 @@ int ceb_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, c
                       float* dx, float* dgamma, float* dbeta, int64_t rows, int E, void* stream);
 /* tanh-GELU on bf16: out = gelu(x) (dy NULL) or dy * gelu'(x). */
 int ceb_gelu_bf16(const void* x, const void* dy, void* out, int64_t n, void* stream);
+/* Classifier head + cross-entropy in one kernel: logits = scale * feat (bf16 [N][F]) @ W^T (fp32 [C][F]),
+ * C <= 32, F % 64 == 0, F <= 2048.  g == NULL: forward, writes loss[N] and correct[N] (1.0 where the
+ * arg-max equals the label).  g != NULL: backward of sum_s g[s] * loss[s]: writes dfeat (bf16 [N][F]) and
+ * accumulates dW (fp32 [C][F], +=). */
+int ceb_linear_ce_head(const void* feat_bf16, const float* W, float scale, const int64_t* labels, int N, int F, int C,
+                       const float* g, float* loss, float* correct, void* dfeat_bf16, float* dW, void* stream);
 /* out[c] (fp32) += sum over rows of x[r][c]; x bf16 [rows][ld], cols % 8 == 0, ld % 8 == 0, 16-byte
  * aligned base (bias gradients without an fp32 copy of the activation gradient). */
 int ceb_colsum_bf16(const void* x_bf16, int64_t ld, int64_t rows, int cols, float* out, void* stream);

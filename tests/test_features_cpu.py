@@ -186,3 +186,43 @@ def test_phase_tracer_writes_max_over_ranks_records(tmp_path):
     assert len(recs) == 2 and recs[-1]["round"] == 4 and recs[0]["rounds"] == 2
     assert {"h2d", "clients", "results", "server"} <= set(recs[0]["ms_per_round"])
     assert all(v >= 0 for v in recs[0]["ms_per_round"].values())
+
+
+def test_deferred_result_wrappers_behave_like_arrays():
+    """--defer_results hands out lazily materialised arrays / tensors; everything the drivers do with
+    them (np.mean, np.isnan, extend, +=, .sum().item()) must work and trigger exactly one host wait."""
+    from commefficient_b200.fed_aggregator import DeferredArray, DeferredTensor, _DeferredRound
+
+    class Ev:
+        waits = 0
+
+        def synchronize(self):
+            Ev.waits += 1
+
+    host = torch.tensor([[1.0, 0.5, 3.0], [2.0, 1.0, 4.0]])
+    rnd = _DeferredRound(host, Ev())
+    loss = DeferredArray(rnd, lambda pk: pk[:, 0].copy())
+    acc = DeferredArray(rnd, lambda pk: pk[:, 1].copy())
+    dl = DeferredTensor(rnd, lambda pk: torch.from_numpy(4.0 * pk[:, -1]).float())
+    assert Ev.waits == 0
+    assert float(np.mean(loss)) == 1.5 and not np.any(np.isnan(loss))
+    assert Ev.waits == 1
+    out = []
+    out.extend(acc)
+    assert out == [0.5, 1.0] and len(loss) == 2 and float(loss[1]) == 2.0
+    assert float((loss + 1).sum()) == 5.0 and loss.shape == (2,)
+    total = torch.zeros(2)
+    total += dl
+    assert total.tolist() == [12.0, 16.0] and dl.sum().item() == 28.0
+    assert Ev.waits == 1
+
+
+def test_defer_results_flag_matches_sync_results_on_cpu():
+    """On CPU the flag is accepted and the values equal the synchronous path (nothing to defer)."""
+    fed_a, opt_a, _ = _make("sketch")
+    a = [float(np.mean(_round(fed_a, opt_a, s)[0])) for s in range(2)]
+    fed_a.rt.shutdown()
+    fed_b, opt_b, _ = _make("sketch", defer_results=True)
+    b = [float(np.mean(_round(fed_b, opt_b, s)[0])) for s in range(2)]
+    fed_b.rt.shutdown()
+    assert a == pytest.approx(b, rel=1e-6)

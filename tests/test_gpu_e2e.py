@@ -88,3 +88,17 @@ def test_nhwc_flat_layout_is_a_relabelling():
 def test_smoke_entry():
     import __graft_entry__ as g
     g.smoke()
+
+
+def test_deferred_results_equal_synchronous_results():
+    """--defer_results: same weights, losses, accuracies and byte counts as the blocking path; the
+    values may be read after opt.step() (that is the point)."""
+    w_a, loss_a, out_a = _run("cuda", "sketch", rounds=4)
+    w_b, loss_b, out_b = _run("cuda", "sketch", rounds=4, defer_results=True)
+    torch.testing.assert_close(w_a, w_b, rtol=1e-5, atol=1e-6)
+    assert loss_a == pytest.approx(loss_b, rel=1e-5)
+    np.testing.assert_allclose(np.asarray(out_a[1]), np.asarray(out_b[1]))
+    total = torch.zeros(32)
+    total += out_b[2]
+    torch.testing.assert_close(total, out_a[2])
+    assert float(out_b[3].sum()) == float(out_a[3].sum())

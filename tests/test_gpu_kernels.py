@@ -213,3 +213,23 @@ def test_launch_counter_and_errors():
     assert native.launch_count() == 4
     with pytest.raises(native.NativeError):
         native.call("ceb_topk_select", None, 10, 1, None, 0, None, None, None)
+
+
+def test_download_tracker_native_matches_torch_path():
+    """ceb_tracker_record / ceb_tracker_counts against the torch implementation on the CPU."""
+    from commefficient_b200.fed_aggregator import _DownloadTracker
+    d, n_clients = 100_003, 40
+    dev_tr = _DownloadTracker(d, n_clients, torch.device("cuda"), sparse=True)
+    cpu_tr = _DownloadTracker(d, n_clients, torch.device("cpu"), sparse=True)
+    g = torch.Generator().manual_seed(3)
+    for rnd in range(6):
+        clients = np.sort(np.random.RandomState(rnd).choice(n_clients, 7, replace=False))
+        a = dev_tr.download_counts(clients)
+        b = cpu_tr.download_counts(clients)
+        assert a.dtype == torch.float32
+        torch.testing.assert_close(a.cpu(), b)
+        idx = torch.randperm(d, generator=g)[:5000].to(torch.int32)
+        dev_tr.record_sparse(idx.cuda())
+        cpu_tr.record_sparse(idx)
+        assert torch.equal(dev_tr.hist.cpu(), cpu_tr.hist) and torch.equal(dev_tr.last.cpu(), cpu_tr.last)
+    assert int(dev_tr.hist.sum()) == d

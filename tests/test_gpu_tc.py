@@ -360,3 +360,66 @@ def test_lm_head_ce_only_labeled_rows(R, V, E, frac):
         assert _rel_err(weight.grad, wr.grad) < 3e-2
     else:
         assert float(hidden.grad.abs().max()) == 0 and float(weight.grad.abs().max()) == 0
+
+
+def test_prepare_conv_weights_one_launch():
+    ws = [torch.randn(co, 3, 3, ci, device=DEV) for co, ci in ((128, 64), (64, 64), (256, 128), (72, 8))]
+    before = __import__("commefficient_b200.ops.native", fromlist=["x"]).launch_count()
+    casts, rots = tc.prepare_conv_weights(ws)
+    assert __import__("commefficient_b200.ops.native", fromlist=["x"]).launch_count() == before + 1
+    for w, c, r in zip(ws, casts, rots):
+        assert torch.equal(c, w.bfloat16())
+        assert torch.equal(r, tc.dgrad_weights(w))
+
+
+def test_linear_ce_head_kernel_matches_torch():
+    g = torch.Generator(device=DEV).manual_seed(11)
+    for N, F_, C in ((500, 512, 10), (37, 64, 32), (9, 1024, 3)):
+        feat = torch.randn(N, F_, device=DEV, generator=g).bfloat16()
+        W = torch.randn(C, F_, device=DEV, generator=g) * 0.2
+        labels = torch.randint(0, C, (N,), device=DEV, generator=g)
+        gvec = torch.rand(N, device=DEV, generator=g) + 0.5
+        loss, correct = tc.linear_ce_head(feat, W, 0.125, labels)
+        fr = feat.float().requires_grad_(True)
+        Wr = W.clone().requires_grad_(True)
+        logits = (fr @ Wr.t()) * 0.125
+        want = F.cross_entropy(logits, labels, reduction="none")
+        torch.testing.assert_close(loss, want, rtol=1e-4, atol=1e-4)
+        assert torch.equal(correct, (logits.argmax(1) == labels).float())
+        (want * gvec).sum().backward()
+        dW = torch.ones(C, F_, device=DEV)
+        dfeat = tc.linear_ce_head(feat, W, 0.125, labels, g=gvec, dW=dW)
+        assert _rel_err(dfeat, fr.grad) < 1e-2
+        assert _rel_err(dW - 1, Wr.grad) < 1e-4
+
+
+def test_resnet9_fused_loss_matches_library_path():
+    """ce_per_sample on the native path (trunk + fused head/CE kernel) vs the library path."""
+    from commefficient_b200 import models
+    from commefficient_b200.ops import nn as nnops
+    from commefficient_b200.utils import FlatParams
+    torch.manual_seed(1)
+    m = models.ResNet9(num_classes=10)
+    fp = FlatParams(m, DEV, layout="nhwc")
+    m._flat_params = fp
+    x = torch.randn(24, 3, 32, 32, device=DEV).contiguous(memory_format=torch.channels_last)
+    tgt = torch.randint(0, 10, (24,), device=DEV)
+
+    def run(native_on):
+        nnops.set_native(native_on)
+        try:
+            fp.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss, correct = m.ce_per_sample(x, tgt)
+            loss.float().sum().backward()
+            return loss.detach().clone(), correct.detach().clone(), fp.grad.clone()
+        finally:
+            nnops.set_native(False)
+
+    l_lib, c_lib, g_lib = run(False)
+    l_nat, c_nat, g_nat = run(True)
+    assert _rel_err(l_nat, l_lib) < 3e-2
+    assert float((c_nat != c_lib).float().mean()) < 0.1      # near-ties may flip under bf16
+    assert _rel_err(g_nat, g_lib) < 0.1
+    for o, n_ in zip(fp.offsets, fp.sizes):
+        assert _rel_err(g_nat[o:o + n_], g_lib[o:o + n_]) < 0.15, o
