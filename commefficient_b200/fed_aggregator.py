@@ -312,7 +312,7 @@ class FedModel:
         unique, inverse = np.unique(ids, return_inverse=True)
         mine = self._assign(unique)[self.rt.rank]
         cols = batch[1:]
-        client_batches = []
+        client_batches = worker.ClientBatches()
         tr = self.tracer
         h2d_phase = tr.phase("h2d")
         h2d_phase.__enter__()
@@ -337,6 +337,7 @@ class FedModel:
                 n = int(counts[p])
                 client_batches.append((int(cid), [t[lo:lo + n] for t in dev_cols]))
                 lo += n
+            client_batches.cols = list(dev_cols)
         h2d_phase.__exit__(None, None, None)
         self.watchdog.beat("clients", self.rounds + 1)
         with tr.phase("clients"):

@@ -34,6 +34,12 @@ from .utils.flat import FlatParams
 
 
 # ----------------------------------------------------------------------------- client state
+class ClientBatches(list):
+    """``[(client_id, [column slices...]), ...]`` plus ``cols``: the tensors the slices were cut from, in the
+    same order (samples of consecutive clients are adjacent), so the batched path need not re-concatenate."""
+    cols = None
+
+
 class ClientStateStore:
     """Rows of per-client state (``d`` floats, or an ``(r, c)`` table), allocated on
     first touch.  Rows stay on the device while they fit in ``device_budget_bytes``;
@@ -319,8 +325,10 @@ class ClientWorker:
         and autograd dispatch costs per round that otherwise leave the GPU idle."""
         sizes = tuple(int(b[0].shape[0]) for _, b in client_batches)
         ncols = len(client_batches[0][1])
-        cat = [torch.cat([b[j] for _, b in client_batches]) if len(client_batches) > 1 else client_batches[0][1][j]
-               for j in range(ncols)]
+        cat = getattr(client_batches, "cols", None)      # FedModel hands over the undivided columns
+        if cat is None:
+            cat = [torch.cat([b[j] for _, b in client_batches]) if len(client_batches) > 1 else client_batches[0][1][j]
+                   for j in range(ncols)]
         use_graph = (self.device.type == "cuda" and not getattr(self.args, "no_cuda_graphs", False)
                      and not getattr(self.args, "p2", 0))
         if not use_graph:

@@ -21,6 +21,9 @@ native.register_signatures({
     "ceb_conv3x3_bf16_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
                                native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
                                native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_conv3x3_bf16_nhwc_res": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
+                                   native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_ptr, native.c_ptr,
+                                   native.c_ptr, native.c_ptr], native.c_i32),
     "ceb_conv_w_dgrad_layout": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
     "ceb_cast_f32_bf16": ([native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr], native.c_i32),
     "ceb_maxpool_nhwc_bf16": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32, native.c_i32,
@@ -112,6 +115,20 @@ def conv3x3_nhwc(x: torch.Tensor, w: torch.Tensor, relu=False, out_dtype=torch.b
     native.call("ceb_conv3x3_bf16_nhwc", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, None,
                 1 if relu else 0, _OUT[out_dtype], native.ptr(relu_mask), native.stream_ptr(x.device))
     return y
+
+
+def conv3x3_nhwc_res(x, w, resid, relu=False, relu_mask=None, keep_pre_add=False):
+    """``act(conv3x3(x, w)) + resid`` in one kernel (bf16).  ``keep_pre_add``: returns
+    ``(act(conv), act(conv) + resid)`` -- the first is what a later ReLU backward masks with."""
+    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.is_contiguous() and w.is_contiguous()
+    n, h, wd, cin = x.shape
+    cout = w.shape[0]
+    assert resid.shape == (n, h, wd, cout) and resid.dtype == torch.bfloat16 and resid.is_contiguous()
+    y = torch.empty((n, h, wd, cout), dtype=torch.bfloat16, device=x.device)
+    y2 = torch.empty_like(y) if keep_pre_add else None
+    native.call("ceb_conv3x3_bf16_nhwc_res", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, None,
+                1 if relu else 0, native.ptr(relu_mask), native.ptr(resid), native.ptr(y2), native.stream_ptr(x.device))
+    return (y, y2) if keep_pre_add else y
 
 
 def dgrad_weights(w_krsc_f32: torch.Tensor) -> torch.Tensor:
@@ -506,15 +523,13 @@ def _r9_features(x, net):
     a1 = conv3x3_nhwc(a0, wb[0], relu=True)
     p1 = maxpool_nhwc(a1, 2)
     r1a = conv3x3_nhwc(p1, wb[1], relu=True)
-    r1b = conv3x3_nhwc(r1a, wb[2], relu=True)
-    s1 = p1 + r1b
+    r1b, s1 = conv3x3_nhwc_res(r1a, wb[2], p1, relu=True, keep_pre_add=True)      # s1 = p1 + r1b in the epilogue
     a2 = conv3x3_nhwc(s1, wb[3], relu=True)
     p2 = maxpool_nhwc(a2, 2)
     a3 = conv3x3_nhwc(p2, wb[4], relu=True)
     p3 = maxpool_nhwc(a3, 2)
     r3a = conv3x3_nhwc(p3, wb[5], relu=True)
-    r3b = conv3x3_nhwc(r3a, wb[6], relu=True)
-    s3 = p3 + r3b
+    r3b, s3 = conv3x3_nhwc_res(r3a, wb[6], p3, relu=True, keep_pre_add=True)
     f = maxpool_nhwc(s3, 4).view(x.shape[0], -1)
     return f, (col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3), [None] + wd
 
@@ -532,7 +547,7 @@ def _r9_backward(net, saved, wd, df):
     conv3x3_wgrad_nhwc(dz, r3a, gw[7])
     dz = conv3x3_nhwc(dz, wd[7], relu_mask=r3a)
     conv3x3_wgrad_nhwc(dz, p3, gw[6])
-    dp3 = ds3 + conv3x3_nhwc(dz, wd[6])
+    dp3 = conv3x3_nhwc_res(dz, wd[6], ds3)                # ds3 + dgrad in the epilogue
 
     dz = maxpool_bwd_nhwc(a3, dp3, 2, relu_mask=True)
     conv3x3_wgrad_nhwc(dz, p2, gw[5])
@@ -546,7 +561,7 @@ def _r9_backward(net, saved, wd, df):
     conv3x3_wgrad_nhwc(dz, r1a, gw[3])
     dz = conv3x3_nhwc(dz, wd[3], relu_mask=r1a)
     conv3x3_wgrad_nhwc(dz, p1, gw[2])
-    dp1 = ds1 + conv3x3_nhwc(dz, wd[2])
+    dp1 = conv3x3_nhwc_res(dz, wd[2], ds1)
 
     dz = maxpool_bwd_nhwc(a1, dp1, 2, relu_mask=True)
     conv3x3_wgrad_nhwc(dz, a0, gw[1])

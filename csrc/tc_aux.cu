@@ -112,33 +112,47 @@ struct WPrepTable {
   __nv_bfloat16* rot[CEB_WPREP_MAX];
   int cout[CEB_WPREP_MAX];
   int cin[CEB_WPREP_MAX];
+  int blk_start[CEB_WPREP_MAX + 1];     // first block of every layer (prefix sum of its 32x32 tiles x 9 taps)
   int n;
 };
 
+// One block = one 32 (co) x 32 (ci) tile of one filter tap: read coalesced along ci, write the cast
+// copy in place and the transposed (rotated) copy coalesced along co through shared memory.
 __global__ void __launch_bounds__(256)
 wprep_kernel(WPrepTable t) {
-  const int layer = blockIdx.y;
-  if (layer >= t.n) return;
+  __shared__ float tile[32][33];
+  int layer = 0;
+  while (layer + 1 < t.n && (int)blockIdx.x >= t.blk_start[layer + 1]) ++layer;
   const float* __restrict__ src = t.src[layer];
   __nv_bfloat16* __restrict__ cast = t.cast[layer];
   __nv_bfloat16* __restrict__ rot = t.rot[layer];
   const int Cout = t.cout[layer], Cin = t.cin[layer];
-  const int64_t total = (int64_t)Cout * 9 * Cin;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  if (cast) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride)
-      cast[i] = __float2bfloat16(src[i]);
-  }
-  if (rot) {
-    // o indexes rot: ((ci*3 + r2)*3 + s2)*Cout + co  (coalesced stores; the strided re-reads hit L2)
-    for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += stride) {
-      const int co = (int)(o % Cout);
-      int64_t u = o / Cout;
-      const int s2 = (int)(u % 3); u /= 3;
-      const int r2 = (int)(u % 3);
-      const int ci = (int)(u / 3);
-      rot[o] = __float2bfloat16(src[(((int64_t)co * 3 + (2 - r2)) * 3 + (2 - s2)) * Cin + ci]);
+  const int ci_tiles = (Cin + 31) / 32, co_tiles = (Cout + 31) / 32;
+  int b = blockIdx.x - t.blk_start[layer];
+  const int ci_t = b % ci_tiles; b /= ci_tiles;
+  const int co_t = b % co_tiles;
+  const int tap = b / co_tiles;                       // r*3 + s
+  const int x = threadIdx.x & 31, y0 = threadIdx.x >> 5;
+#pragma unroll
+  for (int yy = 0; yy < 4; ++yy) {
+    const int y = y0 + 8 * yy;
+    const int co = co_t * 32 + y, ci = ci_t * 32 + x;
+    float v = 0.f;
+    if (co < Cout && ci < Cin) {
+      const int64_t i = ((int64_t)co * 9 + tap) * Cin + ci;
+      v = src[i];
+      if (cast) cast[i] = __float2bfloat16(v);
     }
+    tile[y][x] = v;
+  }
+  if (!rot) return;
+  __syncthreads();
+  const int tap_rot = 8 - tap;                        // (2-r)*3 + (2-s)
+#pragma unroll
+  for (int yy = 0; yy < 4; ++yy) {
+    const int y = y0 + 8 * yy;
+    const int ci = ci_t * 32 + y, co = co_t * 32 + x;
+    if (co < Cout && ci < Cin) rot[((int64_t)ci * 9 + tap_rot) * Cout + co] = __float2bfloat16(tile[x][y]);
   }
 }
 
@@ -147,6 +161,7 @@ CEB_API int ceb_conv_weights_prepare(int n_layers, const float* const* src, void
   CEB_REQUIRE(n_layers > 0 && n_layers <= CEB_WPREP_MAX && src && cout && cin, "ceb_conv_weights_prepare: 1..%d layers", CEB_WPREP_MAX);
   WPrepTable t{};
   t.n = n_layers;
+  int blocks = 0;
   for (int i = 0; i < n_layers; ++i) {
     CEB_REQUIRE(src[i] && cout[i] > 0 && cin[i] > 0, "ceb_conv_weights_prepare: bad layer %d", i);
     t.src[i] = src[i];
@@ -154,9 +169,11 @@ CEB_API int ceb_conv_weights_prepare(int n_layers, const float* const* src, void
     t.rot[i] = rot_bf16 ? (__nv_bfloat16*)rot_bf16[i] : nullptr;
     t.cout[i] = cout[i];
     t.cin[i] = cin[i];
+    t.blk_start[i] = blocks;
+    blocks += 9 * (int)ceb_cdiv(cout[i], 32) * (int)ceb_cdiv(cin[i], 32);
   }
-  dim3 grid((unsigned)(2 * ceb_num_sms() / n_layers + 1), (unsigned)n_layers);
-  wprep_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(t);
+  t.blk_start[n_layers] = blocks;
+  wprep_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(t);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;

@@ -46,6 +46,10 @@ struct TcParams {
   // (rows are compacted by the caller; lets a CUDA-graph-captured launch follow a data-dependent
   // row count without a host round trip)
   const int* m_limit;
+  // optional residual (bf16 [M][ldc], direct-store path only): C2 == NULL: C = out + resid;
+  // C2 != NULL: C = out (kept for the ReLU mask of the backward pass) and C2 = out + resid
+  const void* resid;
+  void* C2;
 };
 
 // MODE 0: generic tile (GEMM, or convolution with one TMA box per filter tap).
@@ -333,7 +337,19 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                   w[j] &= (lo | hi);
                 }
               }
-              st_global_v8((__nv_bfloat16*)p.C + off + h2 * 16, w);
+              if (p.resid) {
+                uint32_t rs[8];
+                ld_global_nc_v8((const __nv_bfloat16*)p.resid + off + h2 * 16, rs);
+                if (p.C2) st_global_v8((__nv_bfloat16*)p.C + off + h2 * 16, w);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const __nv_bfloat162 sum = __hadd2(*(const __nv_bfloat162*)&w[j], *(const __nv_bfloat162*)&rs[j]);
+                  w[j] = *(const uint32_t*)&sum;
+                }
+                st_global_v8((__nv_bfloat16*)(p.C2 ? p.C2 : p.C) + off + h2 * 16, w);
+              } else {
+                st_global_v8((__nv_bfloat16*)p.C + off + h2 * 16, w);
+              }
             }
           }
           return;
@@ -641,9 +657,29 @@ CEB_API int ceb_gemm_bf16_nn(const void* A, const void* B, void* C, int M, int N
 
 // y[N,H,W,Cout] = act(conv3x3_s1_p1(x[N,H,W,Cin], w[Cout,3,3,Cin])), all bf16 NHWC / KRSC.
 // Cin % 64 == 0, Cout % 8 == 0, W <= 128 and 128 % W == 0, H % (128/W) == 0 or (128/W) % H == 0.
+static int conv3x3_impl(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, const float* bias,
+                        int relu, int out_mode, const void* relu_mask, const void* resid, void* y2, void* stream);
+
 CEB_API int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin,
                                   int Cout, const float* bias, int relu, int out_mode, const void* relu_mask,
                                   void* stream) {
+  return conv3x3_impl(x, w, y, Nimg, H, W, Cin, Cout, bias, relu, out_mode, relu_mask, nullptr, nullptr, stream);
+}
+
+// Same with a fused residual add (bf16 output only; Cout % 32 == 0, 32-byte aligned tensors):
+// y2 == NULL: y = act(conv) + resid;  y2 != NULL: y = act(conv) and y2 = y + resid (the pre-add
+// activation stays available as the ReLU mask of the backward pass).
+CEB_API int ceb_conv3x3_bf16_nhwc_res(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout,
+                                      const float* bias, int relu, const void* relu_mask, const void* resid, void* y2,
+                                      void* stream) {
+  CEB_REQUIRE(resid != nullptr, "ceb_conv3x3_bf16_nhwc_res: resid is NULL");
+  CEB_REQUIRE(Cout % 32 == 0 && ((((uintptr_t)y) | ((uintptr_t)resid) | ((uintptr_t)y2) | ((uintptr_t)relu_mask)) & 31) == 0,
+              "ceb_conv3x3_bf16_nhwc_res: need Cout %% 32 == 0 and 32-byte aligned tensors (Cout=%d)", Cout);
+  return conv3x3_impl(x, w, y, Nimg, H, W, Cin, Cout, bias, relu, 0, relu_mask, resid, y2, stream);
+}
+
+static int conv3x3_impl(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, const float* bias,
+                        int relu, int out_mode, const void* relu_mask, const void* resid, void* y2, void* stream) {
   CEB_REQUIRE(x && w && y && Nimg > 0, "ceb_conv3x3_bf16_nhwc: bad arguments");
   CEB_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "ceb_conv3x3_bf16_nhwc: need Cin %% 64 == 0, Cout %% 8 == 0 (Cin=%d Cout=%d)", Cin, Cout);
   CEB_REQUIRE(W <= BM && BM % W == 0, "ceb_conv3x3_bf16_nhwc: W=%d must divide %d", W, BM);
@@ -671,7 +707,7 @@ CEB_API int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nim
   uint32_t bb[2] = {BK, (uint32_t)(pair ? bn / 2 : bn)};
   if (int e = ceb_make_tmap_bf16(&tb, w, 2, db, sb, bb)) return e;
   TcParams p{};
-  p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout;
+  p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout; p.resid = resid; p.C2 = y2;
   p.k_steps = (halo ? 3 : 9) * (Cin / BK);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = H; p.W = W; p.cin_steps = Cin / BK; p.tile_h = tile_h;
   p.halo_bytes = halo ? (rows256 + 2) * W * 128 : 0;

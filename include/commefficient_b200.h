@@ -147,6 +147,11 @@ int ceb_gemm_bf16_nn(const void* A, const void* B, void* C, int M, int N, int K,
  * re-laid-out by ceb_conv_w_dgrad_layout). */
 int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout,
                           const float* bias, int relu, int out_mode, const void* relu_mask, void* stream);
+/* Same with a fused residual add (bf16 output; Cout % 32 == 0; y, resid, y2, relu_mask 32-byte aligned):
+ * y2 == NULL: y = act(conv) + resid;  y2 != NULL: y = act(conv), y2 = y + resid. */
+int ceb_conv3x3_bf16_nhwc_res(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout,
+                              const float* bias, int relu, const void* relu_mask, const void* resid, void* y2,
+                              void* stream);
 /* dst[ci][2-r][2-s][co] (bf16) = w[co][r][s][ci] (fp32): weights of the data-gradient convolution. */
 int ceb_conv_w_dgrad_layout(const float* w_krsc, void* dst_bf16, int Cout, int Cin, void* stream);
 int ceb_cast_f32_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);

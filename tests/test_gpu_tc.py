@@ -423,3 +423,19 @@ def test_resnet9_fused_loss_matches_library_path():
     assert _rel_err(g_nat, g_lib) < 0.1
     for o, n_ in zip(fp.offsets, fp.sizes):
         assert _rel_err(g_nat[o:o + n_], g_lib[o:o + n_]) < 0.15, o
+
+
+@pytest.mark.parametrize("n,h,cin,cout", [(5, 16, 128, 128), (7, 4, 512, 512), (3, 32, 64, 64)])
+def test_conv3x3_fused_residual(n, h, cin, cout):
+    g = torch.Generator(device=DEV).manual_seed(h + cin)
+    x = torch.randn(n, h, h, cin, device=DEV, generator=g).bfloat16()
+    w = (torch.randn(cout, 3, 3, cin, device=DEV, generator=g) / (3 * cin ** 0.5)).bfloat16()
+    res = torch.randn(n, h, h, cout, device=DEV, generator=g).bfloat16()
+    plain = tc.conv3x3_nhwc(x, w, relu=True)
+    pre, post = tc.conv3x3_nhwc_res(x, w, res, relu=True, keep_pre_add=True)
+    assert torch.equal(pre, plain) and torch.equal(post, plain + res)
+    only = tc.conv3x3_nhwc_res(x, w, res, relu=False)
+    assert torch.equal(only, tc.conv3x3_nhwc(x, w) + res)
+    mask = torch.randn(n, h, h, cout, device=DEV, generator=g).bfloat16()
+    masked = tc.conv3x3_nhwc_res(x, w, res, relu_mask=mask)
+    assert torch.equal(masked, tc.conv3x3_nhwc(x, w, relu_mask=mask) + res)
