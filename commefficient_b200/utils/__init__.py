@@ -3,7 +3,7 @@ re-exported under the same names."""
 from .args import (MODES, ERROR_TYPES, DATASET_CLASSES, parse_args, make_args,
                    validate_args, build_parser, num_classes_of_dataset)
 from .logging import (Logger, TableLogger, TSVLogger, JSONLLogger, Timer,
-                      DeviceTimer, PhaseTracer, make_logdir, union)
+                      DeviceTimer, PhaseTracer, make_logdir, union, profile_helper, sm2np, shms)
 from .schedules import (PiecewiseLinear, Exp, steps_per_epoch, triangular_lr,
                         linear_decay_lr)
 from .flat import (FlatParams, get_param_vec, set_param_vec, get_grad_vec,

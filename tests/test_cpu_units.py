@@ -156,3 +156,16 @@ def test_table_logger_prints(capsys):
     t.append({"epoch": 2, "lr": 0.2, "acc": np.float32(0.75)})
     out = capsys.readouterr().out.splitlines()
     assert len(out) == 3 and "epoch" in out[0] and "0.7500" in out[2]
+
+
+def test_profile_helper_and_shm_helpers(tmp_path):
+    import pstats
+    from commefficient_b200.utils import profile_helper, shms, sm2np
+    out = profile_helper(lambda a, b: a + b, 2, 3, name="add", rank=1, directory=str(tmp_path))
+    assert out == 5
+    stats = pstats.Stats(str(tmp_path / "add.1.prof"))
+    assert stats.total_calls >= 1
+    t = torch.arange(6.0).reshape(2, 3)
+    v = sm2np(t)
+    v[0, 0] = 9.0
+    assert float(t[0, 0]) == 9.0 and isinstance(shms(), list)
