@@ -50,7 +50,18 @@ def accuracy(y_pred, y):
 
 
 def compute_loss_val(model, batch, args):
-    """``(LM negative log-likelihood over non-ignored tokens, multiple-choice accuracy)``."""
+    """``(LM negative log-likelihood over non-ignored tokens, multiple-choice accuracy)``.  Models that
+    offer ``lm_rows`` score only the labeled positions (same value: the mean over non-ignored tokens)
+    instead of materialising ``[N*C*T, V]`` logits (reference: gpt2_train.py:55-86)."""
+    if hasattr(model, "lm_rows"):
+        model.eval()
+        with torch.no_grad():
+            input_ids, mc_token_ids, lm_labels, mc_labels, token_type_ids = batch
+            _, mc_logits, hidden = model(input_ids, token_type_ids=token_type_ids, mc_token_ids=mc_token_ids,
+                                         need_logits=False, return_hidden=True)
+            rows, mask = model.lm_rows(hidden, lm_labels)
+            nll = rows.sum() / mask.sum().clamp_min(1)
+            return nll, accuracy(mc_logits, mc_labels)
     (lm_logits, mc_logits), (lm_labels, mc_labels) = inference(model, batch, args)
     nll = F.cross_entropy(lm_logits.float(), lm_labels, ignore_index=-1)
     return nll, accuracy(mc_logits, mc_labels)
