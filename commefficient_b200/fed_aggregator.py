@@ -332,12 +332,7 @@ class FedModel:
                 sel_t = torch.from_numpy(sel)
                 dev_cols = [self._to_device(t[sel_t] if t.device.type == "cpu" else t[sel_t.to(t.device)])
                             for t in cols]
-            lo = 0
-            for p, cid in zip(pos, mine):
-                n = int(counts[p])
-                client_batches.append((int(cid), [t[lo:lo + n] for t in dev_cols]))
-                lo += n
-            client_batches.cols = list(dev_cols)
+            client_batches = worker.ClientBatches(mine, counts[pos], dev_cols)
         h2d_phase.__exit__(None, None, None)
         self.watchdog.beat("clients", self.rounds + 1)
         with tr.phase("clients"):

@@ -34,10 +34,43 @@ from .utils.flat import FlatParams
 
 
 # ----------------------------------------------------------------------------- client state
-class ClientBatches(list):
-    """``[(client_id, [column slices...]), ...]`` plus ``cols``: the tensors the slices were cut from, in the
-    same order (samples of consecutive clients are adjacent), so the batched path need not re-concatenate."""
-    cols = None
+class ClientBatches:
+    """This rank's clients of one round: ``client_ids[i]`` owns the next ``sizes[i]`` samples of every
+    tensor in ``cols`` (samples of consecutive clients are adjacent).  Iterating yields the reference's
+    ``(client_id, [column slices...])`` pairs, but the slices are only cut when something iterates: the
+    batched path consumes ``cols`` whole, and 100 clients x 2 columns of eager tensor slicing cost more
+    host time per round than the server step takes on the GPU."""
+
+    def __init__(self, client_ids=(), sizes=(), cols=None):
+        self.client_ids = client_ids.tolist() if hasattr(client_ids, "tolist") else [int(c) for c in client_ids]
+        self.sizes = sizes.tolist() if hasattr(sizes, "tolist") else [int(n) for n in sizes]
+        self.cols = list(cols) if cols is not None else None
+
+    @classmethod
+    def from_pairs(cls, pairs):
+        """Build from ``[(client_id, [tensor, ...]), ...]`` (concatenates the columns)."""
+        pairs = list(pairs)
+        if not pairs:
+            return cls()
+        ncols = len(pairs[0][1])
+        cols = [torch.cat([b[j] for _, b in pairs]) if len(pairs) > 1 else pairs[0][1][j] for j in range(ncols)]
+        return cls([c for c, _ in pairs], [int(b[0].shape[0]) for _, b in pairs], cols)
+
+    def __len__(self):
+        return len(self.client_ids)
+
+    def __bool__(self):
+        return bool(self.client_ids)
+
+    def __iter__(self):
+        lo = 0
+        for cid, n in zip(self.client_ids, self.sizes):
+            yield cid, [t[lo:lo + n] for t in self.cols]
+            lo += n
+
+    def __getitem__(self, i):
+        lo = sum(self.sizes[:i])
+        return self.client_ids[i], [t[lo:lo + self.sizes[i]] for t in self.cols]
 
 
 class ClientStateStore:
@@ -294,8 +327,10 @@ class ClientWorker:
         """``client_batches``: ``[(client_id, [tensor, ...]), ...]`` for this rank (tensors
         already on the device).  Fills ``self.transmit`` with the sum over these clients
         of what each would upload and returns a ``(n_clients, n_results)`` device tensor."""
+        if not isinstance(client_batches, ClientBatches):
+            client_batches = ClientBatches.from_pairs(client_batches)
         self.transmit.zero_()
-        self.last_clients = [int(c) for c, _ in client_batches]
+        self.last_clients = list(client_batches.client_ids)
         if not client_batches:
             return torch.zeros((0, self.args.num_results_train), device=self.device)
         self.model.train()
@@ -323,12 +358,8 @@ class ClientWorker:
         (zeroing, forward, backward, per-client result reduction, sketch / accumulate) is
         captured into a CUDA graph per round shape and replayed, which removes the ~150 launch
         and autograd dispatch costs per round that otherwise leave the GPU idle."""
-        sizes = tuple(int(b[0].shape[0]) for _, b in client_batches)
-        ncols = len(client_batches[0][1])
-        cat = getattr(client_batches, "cols", None)      # FedModel hands over the undivided columns
-        if cat is None:
-            cat = [torch.cat([b[j] for _, b in client_batches]) if len(client_batches) > 1 else client_batches[0][1][j]
-                   for j in range(ncols)]
+        sizes = tuple(client_batches.sizes)
+        cat = client_batches.cols                        # the undivided columns, clients adjacent
         use_graph = (self.device.type == "cuda" and not getattr(self.args, "no_cuda_graphs", False)
                      and not getattr(self.args, "p2", 0))
         if not use_graph:
