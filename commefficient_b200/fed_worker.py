@@ -353,6 +353,11 @@ class ClientWorker:
             self.transmit.add_(ones, alpha=float(n))
         return torch.ones((n, self.args.num_results_train), device=self.device)
 
+    def _side_stream(self):
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        return self._side
+
     def _round_batched(self, client_batches):
         """One forward/backward over all of this rank's clients.  On CUDA the whole thing
         (zeroing, forward, backward, per-client result reduction, sketch / accumulate) is
@@ -406,6 +411,25 @@ class ClientWorker:
         self.transmit.zero_()
         fp.zero_grad()
         per_sample_cols = []
+        # sum_i n_i * (g_i + wd/W * w) = grad(sum of per-sample losses) + total * wd/W * w
+        wd_total = a.weight_decay / a.num_workers * total
+        # Sketch gradient ranges as soon as the backward pass reports them final (FlatParams.range_final),
+        # on a second stream: the accumulate is L2-atomic bound, the backward tensor-pipe bound.
+        early = []
+        side = None
+        single_chunk = total <= self.MAX_BATCHED_SAMPLES
+        if (a.mode == "sketch" and self.device.type == "cuda" and single_chunk
+                and not getattr(a, "p2", 0) and not getattr(a, "no_sketch_overlap", False)):
+            side = self._side_stream()
+            main = torch.cuda.current_stream(self.device)
+
+            def on_final(lo, hi):
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    sk.accumulate_range(self.plan, self.transmit, fp.grad, lo, hi, scale=1.0, weights=fp.flat,
+                                        wd=wd_total)
+                early.append((lo, hi))
+            fp.on_range_final = on_final
         for lo in range(0, total, self.MAX_BATCHED_SAMPLES):
             chunk = [t[lo:lo + self.MAX_BATCHED_SAMPLES] for t in cat]
             with _autocast(a, self.device):
@@ -426,13 +450,21 @@ class ClientWorker:
         results = torch.zeros((len(sizes), per_sample.shape[1]), device=self.device)
         results.index_add_(0, seg, per_sample)
         results /= counts
-        # sum_i n_i * (g_i + wd/W * w) = grad(sum of per-sample losses) + total * wd/W * w
-        wd_total = a.weight_decay / a.num_workers * total
+        fp.on_range_final = None
         if getattr(a, "p2", 0):
             # dense per-rank sum kept for the second-round exact fetch (FedOptimizer._second_round)
             self.dense_round_sum = fp.grad.add(fp.flat, alpha=wd_total)
         if a.mode == "sketch":
-            sk.accumulate(self.plan, self.transmit, fp.grad, scale=1.0, weights=fp.flat, wd=wd_total)
+            if early:
+                torch.cuda.current_stream(self.device).wait_stream(side)
+                lo = 0
+                for e_lo, e_hi in sorted(early) + [(fp.numel, fp.numel)]:     # the ranges nobody reported
+                    if e_lo > lo:
+                        sk.accumulate_range(self.plan, self.transmit, fp.grad, lo, e_lo, scale=1.0, weights=fp.flat,
+                                            wd=wd_total)
+                    lo = max(lo, e_hi)
+            else:
+                sk.accumulate(self.plan, self.transmit, fp.grad, scale=1.0, weights=fp.flat, wd=wd_total)
         else:
             self.transmit.add_(fp.grad)
             if wd_total != 0:

@@ -40,6 +40,8 @@ _SIGNATURES = {
     "ceb_topk_select": ([c_ptr, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr], c_i32),
     "ceb_sketch_accumulate": ([c_ptr, c_ptr, c_f32, c_f32, c_i64, c_ptr, c_i64, c_ptr, c_i32, c_ptr,
                                c_i32, c_i64, c_ptr], c_i32),
+    "ceb_sketch_accumulate_range": ([c_ptr, c_ptr, c_f32, c_f32, c_i64, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i32, c_ptr,
+                                     c_i32, c_i64, c_ptr], c_i32),
     "ceb_sketch_l2_scale": ([c_ptr, c_i32, c_i64, c_f32, c_ptr, c_ptr, c_ptr], c_i32),
     "ceb_axpy_dev": ([c_ptr, c_ptr, c_i64, c_f32, c_ptr, c_i32, c_ptr], c_i32),
     "ceb_sketch_server_update": ([c_ptr, c_ptr, c_ptr, c_f32, c_f32, c_i32, c_i64, c_ptr], c_i32),

@@ -76,6 +76,31 @@ def accumulate(plan: SketchPlan, table: torch.Tensor, vec: torch.Tensor, scale: 
                 native.ptr(table), plan.r, plan.c, native.stream_ptr(plan.device))
 
 
+def accumulate_range(plan: SketchPlan, table: torch.Tensor, vec: torch.Tensor, lo: int, hi: int, scale: float = 1.0,
+                     weights: Optional[torch.Tensor] = None, wd: float = 0.0) -> None:
+    """``table += S(scale * (vec + wd * weights))`` for coordinates ``lo <= i < hi`` only (the sum over a
+    partition of ``[0, d)`` equals ``accumulate``)."""
+    lo, hi = int(lo), int(hi)
+    if not (0 <= lo <= hi <= plan.d):
+        raise ValueError("bad coordinate range [%d, %d) for d=%d" % (lo, hi, plan.d))
+    if hi == lo:
+        return
+    if not plan.is_cuda:
+        v = vec if weights is None or wd == 0.0 else vec + wd * weights
+        part = torch.zeros_like(v)
+        part[lo:hi] = v[lo:hi]
+        ref.sketch_accum_ref(table, part, plan.hashes, scale)
+        return
+    native.require_f32_contig(vec, "vec")
+    native.require_f32_contig(table, "table")
+    w = None
+    if weights is not None and wd != 0.0:
+        w = native.require_f32_contig(weights, "weights")
+    native.call("ceb_sketch_accumulate_range", native.ptr(vec), native.ptr(w), float(wd), float(scale), plan.d, lo, hi,
+                native.ptr(plan.packed), plan.n_tokens, native.ptr(plan.blk), plan.num_blocks, native.ptr(table),
+                plan.r, plan.c, native.stream_ptr(vec.device))
+
+
 def l2_scale(plan: SketchPlan, table: torch.Tensor, clip: float = 0.0) -> torch.Tensor:
     """Device tensor ``[scale, l2]`` with ``l2 = sqrt(median_r sum_c T^2)`` and
     ``scale = clip / l2`` if ``l2 >= clip > 0`` else 1 -- no host sync."""

@@ -534,7 +534,7 @@ def _r9_features(x, net):
     return f, (col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3), [None] + wd
 
 
-def _r9_backward(net, saved, wd, df):
+def _r9_backward(net, saved, wd, df, fp=None):
     """Backward of the trunk from ``df`` (bf16 ``[N, C3]``): weight gradients are accumulated into
     the flat fp32 gradient buffer."""
     col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3 = saved
@@ -547,6 +547,11 @@ def _r9_backward(net, saved, wd, df):
     conv3x3_wgrad_nhwc(dz, r3a, gw[7])
     dz = conv3x3_nhwc(dz, wd[7], relu_mask=r3a)
     conv3x3_wgrad_nhwc(dz, p3, gw[6])
+    if fp is not None:
+        # res3 (72 % of all coordinates) and the head are final: hand them to whoever consumes the
+        # gradient (the worker sketches them on a second stream under the rest of this backward)
+        lo, hi = fp.range_of([convs[6].weight, convs[7].weight, net.linear.weight])
+        fp.range_final(lo, hi)
     dp3 = conv3x3_nhwc_res(dz, wd[6], ds3)                # ds3 + dgrad in the epilogue
 
     dz = maxpool_bwd_nhwc(a3, dp3, 2, relu_mask=True)
@@ -584,6 +589,7 @@ class _ResNet9Fn(torch.autograd.Function):
         f, saved, wd = _r9_features(x, net)
         logits = (f.float() @ net.linear.weight.data.t()) * net.out_scale
         ctx.net, ctx.wd, ctx.saved, ctx.f = net, wd, saved, f
+        ctx.fp = _FP_OF.get(id(net))
         return logits
 
     @staticmethod
@@ -592,7 +598,7 @@ class _ResNet9Fn(torch.autograd.Function):
         dl = dlogits.float() * net.out_scale
         net.linear.weight.grad.add_(dl.t() @ f.float())
         df = (dl @ net.linear.weight.data).to(torch.bfloat16).contiguous()
-        _r9_backward(net, ctx.saved, ctx.wd, df)
+        _r9_backward(net, ctx.saved, ctx.wd, df, ctx.fp)
         return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 
@@ -639,6 +645,7 @@ class _ResNet9CEFn(torch.autograd.Function):
         f = f.contiguous()
         loss, correct = linear_ce_head(f, net.linear.weight.data, net.out_scale, labels)
         ctx.net, ctx.wd, ctx.saved, ctx.f, ctx.labels = net, wd, saved, f, labels
+        ctx.fp = _FP_OF.get(id(net))
         ctx.mark_non_differentiable(correct)
         return loss, correct
 
@@ -647,17 +654,22 @@ class _ResNet9CEFn(torch.autograd.Function):
         net = ctx.net
         g = gloss.float().contiguous()
         df = linear_ce_head(ctx.f, net.linear.weight.data, net.out_scale, ctx.labels, g=g, dW=net.linear.weight.grad)
-        _r9_backward(net, ctx.saved, ctx.wd, df)
+        _r9_backward(net, ctx.saved, ctx.wd, df, ctx.fp)
         return (None, None, None) + (None,) * (len(ctx.needs_input_grad) - 3)
 
 
 def resnet9_ce_per_sample(model, x: torch.Tensor, labels: torch.Tensor):
     net = model.n
+    _FP_OF[id(net)] = getattr(model, "_flat_params", None)
     weights = [p for p in net.parameters() if p.requires_grad]
     return _ResNet9CEFn.apply(x, labels, net, *weights)
 
 
+_FP_OF = {}          # id(inner net) -> FlatParams of the model it belongs to (set on every call)
+
+
 def resnet9_forward(model, x: torch.Tensor) -> torch.Tensor:
     net = model.n
+    _FP_OF[id(net)] = getattr(model, "_flat_params", None)
     weights = [p for p in net.parameters() if p.requires_grad]
     return _ResNet9Fn.apply(x, net, *weights)

@@ -130,6 +130,9 @@ _FLAGS = [
                    "nhwc = (out,kh,kw,in), channels_last end to end (auto: nhwc on CUDA)"),
         _flag("no_cuda_graphs", store_true=True,
               help="do not capture the batched client forward/backward into a CUDA graph"),
+        _flag("no_sketch_overlap", store_true=True,
+              help="sketch the whole gradient after the backward pass instead of sketching finished ranges "
+                   "on a second stream while the backward is still running"),
         _flag("defer_results", store_true=True,
               help="return each round's losses / byte counts as lazily materialised arrays (async D2H): "
                    "call opt.step() before reading them and the host never stalls the GPU"),

@@ -16,7 +16,7 @@ written against ``utils.get_param_vec`` & co.
 """
 from __future__ import annotations
 
-from typing import List
+from typing import Tuple, List
 
 import torch
 
@@ -86,6 +86,29 @@ class FlatParams:
                 if p.data.data_ptr() != self.flat[o:o + n].data_ptr():
                     self._view(self.flat, o, n, shp).copy_(p.data)
         self._bind()
+
+    # -- early hand-off of finished gradient ranges -------------------------------------
+    # A consumer (the sketching worker) may set ``on_range_final`` to a callable ``(lo, hi)``; code that
+    # knows a contiguous coordinate range of ``grad`` will not change any more during the current
+    # backward pass calls ``range_final`` so the range can be consumed (sketched on a second stream)
+    # while the rest of the backward is still running.
+    on_range_final = None
+
+    def range_of(self, params) -> Tuple[int, int]:
+        """``(lo, hi)`` of the coordinates covered by ``params`` (which must be adjacent in the buffer)."""
+        ids = {id(p) for p in params}
+        idx = [i for i, p in enumerate(self.params) if id(p) in ids]
+        if not idx:
+            return 0, 0
+        lo_i, hi_i = min(idx), max(idx)
+        if hi_i - lo_i + 1 != len(idx):
+            raise ValueError("parameters are not adjacent in the flat buffer")
+        return self.offsets[lo_i], self.offsets[hi_i] + self.sizes[hi_i]
+
+    def range_final(self, lo: int, hi: int) -> None:
+        cb = self.on_range_final
+        if cb is not None and hi > lo:
+            cb(int(lo), int(hi))
 
     def zero_grad(self):
         self.grad.zero_()

@@ -103,6 +103,55 @@ CEB_API int ceb_sketch_accumulate(const float* g, const float* w, float wd, floa
   return 0;
 }
 
+// Coordinates [lo, hi) only, one thread per coordinate (the hash words of its token are loaded per
+// coordinate instead of once per 20 hash blocks): lets a caller sketch the part of the gradient that is
+// already final on a second stream while the rest of the backward pass is still running -- the
+// accumulate is bound by L2 atomics, the backward by the tensor pipe, so they overlap well.
+template <int R>
+__global__ void __launch_bounds__(kSketchThreads)
+sketch_accum_range_kernel(const float* __restrict__ g, const float* __restrict__ w, float wd, float scale,
+                          int64_t lo, int64_t hi, const int32_t* __restrict__ packed, int64_t n,
+                          const int32_t* __restrict__ blk, float* __restrict__ table, uint32_t c) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    float v = __ldg(g + i);
+    if (w != nullptr) v = fmaf(wd, __ldg(w + i), v);
+    v *= scale;
+    if (v == 0.f) continue;
+    const int b = (int)(i / n);
+    const int64_t t = i - (int64_t)b * n;
+    const uint32_t bp = (uint32_t)__ldg(blk + b);
+    const uint32_t off = bp & 0x7fffffffu;
+    const uint32_t vb = __float_as_uint(v) ^ (bp & 0x80000000u);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t hp = (uint32_t)__ldg(packed + (int64_t)r * n + t);
+      uint32_t col = (hp & 0x7fffffffu) + off;
+      if (col >= c) col -= c;
+      red_add_f32(table + (int64_t)r * c + col, __uint_as_float(vb ^ (hp & 0x80000000u)));
+    }
+  }
+}
+
+// table += S(scale * (g + wd * w)) restricted to coordinates lo <= i < hi (g, w indexed by the GLOBAL i).
+CEB_API int ceb_sketch_accumulate_range(const float* g, const float* w, float wd, float scale, int64_t d, int64_t lo,
+                                        int64_t hi, const int32_t* packed, int64_t n_tokens, const int32_t* blk,
+                                        int num_blocks, float* table, int r, int64_t c, void* stream) {
+  CEB_REQUIRE(g && packed && blk && table, "ceb_sketch_accumulate_range: null pointer");
+  CEB_REQUIRE(0 <= lo && lo <= hi && hi <= d, "ceb_sketch_accumulate_range: bad range [%lld, %lld) for d=%lld", (long long)lo,
+              (long long)hi, (long long)d);
+  if (int e = check_sketch_dims("ceb_sketch_accumulate_range", r, c, d, n_tokens, num_blocks)) return e;
+  if (hi == lo) return 0;
+  int64_t gx = ceb_cdiv(hi - lo, kSketchThreads);
+  const int64_t cap = (int64_t)ceb_num_sms() * 16;
+  if (gx > cap) gx = cap;
+  CEB_DISPATCH_ROWS(r, (sketch_accum_range_kernel<R><<<(unsigned)gx, kSketchThreads, 0, (cudaStream_t)stream>>>(
+                           g, w, wd, scale, lo, hi, packed, n_tokens, blk, table, (uint32_t)c)));
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
 // ------------------------------------------------------------------ l2 estimate / clip
 __global__ void __launch_bounds__(256)
 rowsumsq_kernel(const float* __restrict__ table, int64_t c, float* __restrict__ out) {

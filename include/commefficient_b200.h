@@ -47,6 +47,11 @@ int ceb_topk_select(const float* vec, int64_t n, int64_t k, void* scratch, int64
 int ceb_sketch_accumulate(const float* g, const float* w, float wd, float scale, int64_t d,
                           const int32_t* packed, int64_t n_tokens, const int32_t* blk, int num_blocks,
                           float* table, int r, int64_t c, void* stream);
+/* Same restricted to coordinates lo <= i < hi (g and w are indexed by the global coordinate): sketch the
+ * part of a gradient that is already final while the rest is still being computed (second stream). */
+int ceb_sketch_accumulate_range(const float* g, const float* w, float wd, float scale, int64_t d, int64_t lo, int64_t hi,
+                                const int32_t* packed, int64_t n_tokens, const int32_t* blk, int num_blocks,
+                                float* table, int r, int64_t c, void* stream);
 /* out2[1] = l2 estimate sqrt(median_r sum_c T^2); out2[0] = clip/l2 if l2 >= clip > 0 else 1.
  * rowsq_tmp: r floats of scratch.  (reference: utils.py:305-313 on a CSVec) */
 int ceb_sketch_l2_scale(const float* table, int r, int64_t c, float clip, float* rowsq_tmp, float* out2,

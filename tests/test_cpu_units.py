@@ -169,3 +169,15 @@ def test_profile_helper_and_shm_helpers(tmp_path):
     v = sm2np(t)
     v[0, 0] = 9.0
     assert float(t[0, 0]) == 9.0 and isinstance(shms(), list)
+
+
+def test_accumulate_range_cpu_oracle():
+    from commefficient_b200.ops import sketch as sk
+    plan = sk.SketchPlan.get(1000, 97, 3, 4, "cpu")
+    g = torch.randn(1000)
+    full = plan.new_table()
+    sk.accumulate(plan, full, g)
+    parts = plan.new_table()
+    for lo, hi in ((0, 10), (10, 600), (600, 1000)):
+        sk.accumulate_range(plan, parts, g, lo, hi)
+    torch.testing.assert_close(parts, full)

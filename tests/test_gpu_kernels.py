@@ -233,3 +233,18 @@ def test_download_tracker_native_matches_torch_path():
         cpu_tr.record_sparse(idx)
         assert torch.equal(dev_tr.hist.cpu(), cpu_tr.hist) and torch.equal(dev_tr.last.cpu(), cpu_tr.last)
     assert int(dev_tr.hist.sum()) == d
+
+
+def test_sketch_accumulate_range_partitions_sum_to_full():
+    from commefficient_b200.ops import sketch as sk
+    d, c, r = 1_000_003, 50_000, 5
+    plan = sk.SketchPlan.get(d, c, r, 20, "cuda")
+    g = torch.randn(d, device="cuda")
+    w = torch.randn(d, device="cuda")
+    full = plan.new_table()
+    sk.accumulate(plan, full, g, scale=0.5, weights=w, wd=0.01)
+    parts = plan.new_table()
+    cuts = [0, 17, 300_000, 300_001, 777_777, d]
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        sk.accumulate_range(plan, parts, g, lo, hi, scale=0.5, weights=w, wd=0.01)
+    torch.testing.assert_close(parts, full, rtol=1e-4, atol=1e-4)
