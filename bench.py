@@ -265,8 +265,8 @@ def run_ours(cfg):
     clocks = sampler.stop() if rt.rank == 0 else None
     last_loss = float(out[0].mean())
 
-    if cfg.phases and rt.rank == 0:
-        _phase_breakdown(fed, opt, dev_rounds, torch)
+    if cfg.phases:      # every rank runs the rounds (they contain collectives); rank 0 prints
+        _phase_breakdown(fed, opt, dev_rounds, torch, rt.rank == 0)
 
     if rt.rank == 0:
         value = clients / (ms_dev / 1e3)
@@ -290,7 +290,7 @@ def run_ours(cfg):
     return 0
 
 
-def _phase_breakdown(fed, opt, rounds, torch):
+def _phase_breakdown(fed, opt, rounds, torch, report=True):
     """Per-phase device times of one round (stderr; not part of the JSON contract)."""
     import numpy as np
     ev = lambda: torch.cuda.Event(enable_timing=True)
@@ -305,7 +305,8 @@ def _phase_breakdown(fed, opt, rounds, torch):
         torch.cuda.synchronize()
         acc.setdefault("clients+sketch+reduce", []).append(e[0].elapsed_time(e[1]))
         acc.setdefault("server_step", []).append(e[1].elapsed_time(e[2]))
-    print("phase ms: " + ", ".join("%s=%.3f" % (k, float(np.median(v))) for k, v in acc.items()), file=sys.stderr)
+    if report:
+        print("phase ms: " + ", ".join("%s=%.3f" % (k, float(np.median(v))) for k, v in acc.items()), file=sys.stderr)
 
 
 def main():
