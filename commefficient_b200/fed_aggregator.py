@@ -58,7 +58,12 @@ class _DownloadTracker:
     def __init__(self, d: int, num_clients: int, device, sparse: bool):
         self.d, self.device, self.sparse = d, device, sparse
         self.round = 0                      # number of server updates applied so far
-        self.hist = torch.zeros(1024, dtype=torch.int64, device=device)
+        # (on CUDA the histogram is sized so that growing it -- which moves it and invalidates the server
+        # step's CUDA graph -- practically never happens)
+        self.hist = torch.zeros(65536 if torch.device(device).type == "cuda" else 1024, dtype=torch.int64,
+                                device=device)
+        self.generation = 0                 # bumped whenever hist / last are re-allocated
+        self.round_dev = None               # device copy of `round` for graph-replayed updates
         self.last = torch.zeros(d, dtype=torch.int64, device=device) if sparse else None
         self.hist[0] = d                    # bucket 0 = never changed; never inside a suffix sum
         self.seen = np.zeros(num_clients, dtype=np.int64)   # server round each client last saw
@@ -68,6 +73,7 @@ class _DownloadTracker:
             new = torch.zeros(max(need + 1, 2 * self.hist.numel()), dtype=torch.int64, device=self.device)
             new[: self.hist.numel()] = self.hist
             self.hist = new
+            self.generation += 1
 
     def download_counts(self, clients: np.ndarray) -> torch.Tensor:
         """Device float32 tensor: changed-coordinate count per participating client."""
@@ -96,6 +102,24 @@ class _DownloadTracker:
         self.hist.index_add_(0, old, torch.full_like(old, -1))
         self.hist[self.round] += li.numel()
         self.last[li] = self.round
+
+    # -- CUDA-graph friendly variant: the round number lives on the device -----------------
+    def sync_round_dev(self):
+        if self.round_dev is None:
+            self.round_dev = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.round_dev.fill_(self.round)
+
+    def host_advance(self):
+        """Host half of ``record_sparse_graph``: advance the round and make room in the histogram."""
+        self.round += 1
+        self._grow(self.round)
+
+    def record_sparse_graph(self, idx: torch.Tensor):
+        """Device half (capturable): ``round_dev += 1`` then move ``idx`` into that round's bucket."""
+        from .ops import native
+        self.round_dev.add_(1)
+        native.call("ceb_tracker_record_dev", native.ptr(idx), idx.numel(), native.ptr(self.last),
+                    native.ptr(self.hist), native.ptr(self.round_dev), native.stream_ptr(self.device))
 
     def record_dense(self):
         self.round += 1
@@ -463,6 +487,7 @@ class FedModel:
         self.tracker.hist = tr["hist"].to(self.device)
         if tr["last"] is not None:
             self.tracker.last = tr["last"].to(self.device)
+        self.tracker.generation += 1          # re-allocated: any captured server-step graph is stale
         w = self.worker
         for store, key in ((w.velocities, "client_velocities"), (w.errors, "client_errors"),
                            (w.client_weights, "client_weights")):
@@ -503,6 +528,7 @@ class FedOptimizer(torch.optim.Optimizer):
         self._lr_vec_key = None
         self._noise_calls = 0
         self.last_update = None           # (idx, val) of the last sparse update, for inspection
+        self._tail = {"calls": 0, "graph": None, "gen": -1, "src": 0, "lr": None, "out": None, "native": 0}
 
     # -- learning rate -----------------------------------------------------------------
     def get_lr(self):
@@ -563,6 +589,10 @@ class FedOptimizer(torch.optim.Optimizer):
             if self.verror_buf is None:
                 sk.server_update(self.Vvelocity, self.Verror, g, inv_n, rho, args.error_type)
             src = self.Verror if args.error_type != "none" else self.Vvelocity
+            if (w.is_cuda and not torch.is_tensor(lr) and not (getattr(args, "p2", 0) and args.p2 > 0)
+                    and not getattr(args, "no_cuda_graphs", False)):
+                self._sketch_tail_graphed(plan, src, float(lr))
+                return
             if getattr(args, "p2", 0) and args.p2 > 0:
                 idx, val = self._second_round(plan, src, g, inv_n)
             else:
@@ -587,6 +617,47 @@ class FedOptimizer(torch.optim.Optimizer):
             dn.dense_server_update(self.Vvelocity, g, inv_n, rho, w, 1.0 if args.mode == "fedavg" else lr,
                                    noise_std=noise, seed=args.seed + 7, noise_offset=self._noise_calls << 20)
             fm.tracker.record_dense()
+
+    def _sketch_tail(self, plan, src, lr, record):
+        """Heavy-hitter recovery, bucket zeroing + weight update, byte accounting (sketch mode)."""
+        fm, args = self.fed_model, self.args
+        idx, val = sk.unsketch_topk(plan, src, args.k)
+        sk.apply_zero(plan, idx, val, self.Vvelocity,
+                      self.Verror if args.error_type == "virtual" else None, fm.fp.flat, lr)
+        if args.error_type == "local":
+            self.Verror.copy_(self.Vvelocity)
+        record(idx)
+        return idx, val
+
+    def _sketch_tail_graphed(self, plan, src, lr: float):
+        """The tail of the sketch-mode server step as ONE CUDA-graph replay (after two eager rounds):
+        the learning rate and the round number are read from device memory by the kernels
+        (``ceb_sketch_apply_zero_dev`` / ``ceb_tracker_record_dev``), everything else is static."""
+        fm = self.fed_model
+        tr = fm.tracker
+        st = self._tail
+        st["calls"] += 1
+        if st["graph"] is None and st["calls"] <= 2:
+            self.last_update = self._sketch_tail(plan, src, lr, tr.record_sparse)
+            return
+        from .ops import native
+        if st["lr"] is None:
+            st["lr"] = torch.zeros(1, dtype=torch.float32, device=fm.device)
+        tr.host_advance()                              # may re-allocate the histogram (generation changes)
+        if st["graph"] is None or st["gen"] != tr.generation or st["src"] != src.data_ptr():
+            tr.round -= 1
+            tr.sync_round_dev()                        # device round = rounds applied so far
+            tr.round += 1
+            torch.cuda.synchronize(fm.device)
+            before = native.launch_count()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                st["out"] = self._sketch_tail(plan, src, st["lr"], tr.record_sparse_graph)
+            st.update(graph=graph, gen=tr.generation, src=src.data_ptr(), native=native.launch_count() - before)
+        st["lr"].fill_(lr)
+        st["graph"].replay()
+        native.add_launch_count(st["native"])
+        self.last_update = st["out"]
 
     def _step_fused(self, inv_n, rho, lr) -> bool:
         """Peer-memory path: the cross-rank reduce-scatter, the momentum/error (or momentum +

@@ -65,6 +65,9 @@ _SIGNATURES = {
     "ceb_fedavg_delta": ([c_ptr, c_ptr, c_ptr, c_f32, c_i64, c_ptr], c_i32),
     "ceb_count_changed": ([c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr], c_i32),
     "ceb_tracker_record": ([c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr], c_i32),
+    "ceb_tracker_record_dev": ([c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr], c_i32),
+    "ceb_sketch_apply_zero_dev": ([c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_i32, c_i64, c_ptr, c_ptr, c_ptr, c_ptr,
+                                   c_ptr, c_ptr], c_i32),
     "ceb_tracker_counts": ([c_ptr, c_i32, c_ptr, c_i32, c_ptr, c_ptr], c_i32),
 }
 

@@ -179,6 +179,13 @@ def apply_zero(plan: SketchPlan, idx: torch.Tensor, val: torch.Tensor, Vv: Optio
                changed: Optional[torch.Tensor] = None) -> None:
     """Zero the buckets of the selected coordinates in ``Vv``/``Ve`` and apply
     ``weights[idx] -= lr * val`` (``lr`` float or length-d tensor)."""
+    lr_dev = lr if (torch.is_tensor(lr) and lr.numel() == 1 and plan.is_cuda) else None   # device scalar
+    if lr_dev is not None:
+        native.call("ceb_sketch_apply_zero_dev", native.ptr(idx), native.ptr(val), idx.numel(),
+                    native.ptr(plan.packed), plan.n_tokens, native.ptr(plan.blk), plan.r, plan.c,
+                    native.ptr(Vv), native.ptr(Ve), native.ptr(weights), native.ptr(lr_dev), native.ptr(changed),
+                    native.stream_ptr(plan.device))
+        return
     lr_vec = lr if torch.is_tensor(lr) else None
     if not plan.is_cuda:
         ref.sketch_zero_buckets_ref([Vv, Ve], idx, val, plan.hashes)

@@ -325,7 +325,9 @@ CEB_API int ceb_count_changed(const float* w, float* prev, uint8_t* mask, int64_
 // handful of old buckets, so decrements are aggregated per warp (match.any) before the atomic.
 __global__ void __launch_bounds__(256)
 tracker_record_kernel(const int* __restrict__ idx, int64_t k, long long* __restrict__ last,
-                      unsigned long long* __restrict__ hist, long long round) {
+                      unsigned long long* __restrict__ hist, long long round,
+                      const long long* __restrict__ round_dev) {
+  if (round_dev) round = *round_dev;       // round number kept on the device (CUDA-graph replays)
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool active = i < k;
   long long old = -1;
@@ -344,7 +346,18 @@ tracker_record_kernel(const int* __restrict__ idx, int64_t k, long long* __restr
 CEB_API int ceb_tracker_record(const int* idx, int64_t k, int64_t* last, int64_t* hist, int64_t round, void* stream) {
   CEB_REQUIRE(idx && last && hist && k > 0 && round > 0, "ceb_tracker_record: bad arguments");
   tracker_record_kernel<<<(unsigned)ceb_cdiv(k, 256), 256, 0, (cudaStream_t)stream>>>(
-      idx, k, (long long*)last, (unsigned long long*)hist, (long long)round);
+      idx, k, (long long*)last, (unsigned long long*)hist, (long long)round, nullptr);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Same with the round number read from device memory (*round_dev > 0 and < the length of hist).
+CEB_API int ceb_tracker_record_dev(const int* idx, int64_t k, int64_t* last, int64_t* hist, const int64_t* round_dev,
+                                   void* stream) {
+  CEB_REQUIRE(idx && last && hist && round_dev && k > 0, "ceb_tracker_record_dev: bad arguments");
+  tracker_record_kernel<<<(unsigned)ceb_cdiv(k, 256), 256, 0, (cudaStream_t)stream>>>(
+      idx, k, (long long*)last, (unsigned long long*)hist, 0, (const long long*)round_dev);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;

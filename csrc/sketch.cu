@@ -374,9 +374,10 @@ sketch_apply_zero_kernel(const int32_t* __restrict__ idx, const float* __restric
                          const int32_t* __restrict__ packed, int64_t n, const int32_t* __restrict__ blk,
                          int r, uint32_t c, float* __restrict__ Vv, float* __restrict__ Ve,
                          float* __restrict__ w, float lr, const float* __restrict__ lr_vec,
-                         uint8_t* __restrict__ changed) {
+                         uint8_t* __restrict__ changed, const float* __restrict__ lr_dev) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= k) return;
+  if (lr_dev) lr = __ldg(lr_dev);          // learning rate read from device memory (CUDA-graph replays)
   const float v = __ldg(val + j);
   if (v == 0.f) return;
   const int64_t i = __ldg(idx + j);
@@ -395,18 +396,33 @@ sketch_apply_zero_kernel(const int32_t* __restrict__ idx, const float* __restric
   }
 }
 
-CEB_API int ceb_sketch_apply_zero(const int32_t* idx, const float* val, int64_t k, const int32_t* packed,
-                                  int64_t n_tokens, const int32_t* blk, int r, int64_t c, float* Vv,
-                                  float* Ve, float* w, float lr, const float* lr_vec, uint8_t* changed,
-                                  void* stream) {
+static int apply_zero_impl(const int32_t* idx, const float* val, int64_t k, const int32_t* packed, int64_t n_tokens,
+                           const int32_t* blk, int r, int64_t c, float* Vv, float* Ve, float* w, float lr,
+                           const float* lr_vec, uint8_t* changed, const float* lr_dev, void* stream) {
   CEB_REQUIRE(idx && val && packed && blk, "ceb_sketch_apply_zero: null pointer");
   CEB_REQUIRE(r >= 1 && r <= kMaxRows, "ceb_sketch_apply_zero: num_rows=%d", r);
   if (k <= 0) return 0;
   sketch_apply_zero_kernel<<<(unsigned)ceb_cdiv(k, 256), 256, 0, (cudaStream_t)stream>>>(
-      idx, val, k, packed, n_tokens, blk, r, (uint32_t)c, Vv, Ve, w, lr, lr_vec, changed);
+      idx, val, k, packed, n_tokens, blk, r, (uint32_t)c, Vv, Ve, w, lr, lr_vec, changed, lr_dev);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
+}
+
+CEB_API int ceb_sketch_apply_zero(const int32_t* idx, const float* val, int64_t k, const int32_t* packed,
+                                  int64_t n_tokens, const int32_t* blk, int r, int64_t c, float* Vv,
+                                  float* Ve, float* w, float lr, const float* lr_vec, uint8_t* changed,
+                                  void* stream) {
+  return apply_zero_impl(idx, val, k, packed, n_tokens, blk, r, c, Vv, Ve, w, lr, lr_vec, changed, nullptr, stream);
+}
+
+// Same with the scalar learning rate read from device memory at run time, so the launch can be
+// replayed from a CUDA graph while the schedule changes the rate every round.
+CEB_API int ceb_sketch_apply_zero_dev(const int32_t* idx, const float* val, int64_t k, const int32_t* packed,
+                                      int64_t n_tokens, const int32_t* blk, int r, int64_t c, float* Vv, float* Ve,
+                                      float* w, const float* lr_dev, uint8_t* changed, void* stream) {
+  CEB_REQUIRE(lr_dev != nullptr, "ceb_sketch_apply_zero_dev: lr_dev is NULL");
+  return apply_zero_impl(idx, val, k, packed, n_tokens, blk, r, c, Vv, Ve, w, 0.f, nullptr, changed, lr_dev, stream);
 }
 
 // ------------------------------------------------------------------ heavy-hitter recovery without any allocation

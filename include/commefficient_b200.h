@@ -91,6 +91,10 @@ int ceb_sketch_query(const float* table, const int32_t* packed, int64_t n_tokens
 int ceb_sketch_apply_zero(const int32_t* idx, const float* val, int64_t k, const int32_t* packed,
                           int64_t n_tokens, const int32_t* blk, int r, int64_t c, float* Vv, float* Ve,
                           float* w, float lr, const float* lr_vec, uint8_t* changed, void* stream);
+/* Same with the scalar learning rate read from device memory at run time (CUDA-graph replays). */
+int ceb_sketch_apply_zero_dev(const int32_t* idx, const float* val, int64_t k, const int32_t* packed, int64_t n_tokens,
+                              const int32_t* blk, int r, int64_t c, float* Vv, float* Ve, float* w, const float* lr_dev,
+                              uint8_t* changed, void* stream);
 
 /* ---- dense modes (reference: fed_aggregator.py:483-566) ---------------------- */
 /* Vv = rho*Vv + g*inv_n (+ N(0,noise_std^2)); w -= lr*Vv.  uncompressed / local_topk / fedavg. */
@@ -132,6 +136,8 @@ int ceb_count_changed(const float* w, float* prev, uint8_t* mask, int64_t n, uns
  * record: coordinates idx[0..k) move from bucket last[idx] to bucket `round` (last updated, hist
  * decremented / incremented); counts: out[j] = sum of hist[r] for r >= start[j]. */
 int ceb_tracker_record(const int* idx, int64_t k, int64_t* last, int64_t* hist, int64_t round, void* stream);
+int ceb_tracker_record_dev(const int* idx, int64_t k, int64_t* last, int64_t* hist, const int64_t* round_dev,
+                           void* stream);
 int ceb_tracker_counts(const int64_t* hist, int n, const int64_t* start, int m, float* out, void* stream);
 
 /* ---- tensor-core layers: tcgen05.mma + TMEM accumulators + TMA-staged operands --

@@ -163,7 +163,7 @@ def test_hung_rank_is_detected_and_aborts_the_job(tmp_path):
         "import sys; sys.path.insert(0, %r)\n"
         "import torch\n"
         "from tests.test_features_cpu import _make, _round\n"
-        "fed, opt, _ = _make('uncompressed', watchdog_timeout=1.0)\n"
+        "fed, opt, _ = _make('uncompressed', watchdog_timeout=5.0)\n"
         "for s in range(5): _round(fed, opt, s)\n" % ROOT)
     env = dict(os.environ, CEB_FAULT="hang:0:2")
     t0 = time.time()
