@@ -220,15 +220,16 @@ def run_ours(cfg):
     h2d = per_rank_samples * (3 * 32 * 32 * 4 + 8)
     d2h = clients * (args.num_results_train + 1) * 4
 
-    def one_round(batch):
+    def one_round(batch, read=True):
         out = fed(batch)
         opt.step()
-        # the step's result is read on the host every round (results are deferred: the async D2H
-        # issued by fed() has been overtaken by the server step's launches, not skipped)
-        float(np.mean(out[0]))
+        if read:
+            # the step's result is read on the host (results are deferred: the async D2H issued by
+            # fed() has been overtaken by the server step's launches, not skipped)
+            float(np.mean(out[0]))
         return out
 
-    def timed(rounds, steps, warmup):
+    def timed(rounds, steps, warmup, read_every_step):
         for i in range(warmup):
             one_round(rounds[i % len(rounds)])
         rt.barrier()
@@ -238,7 +239,9 @@ def run_ours(cfg):
         a.record()
         out = None
         for i in range(steps):
-            out = one_round(rounds[(warmup + i) % len(rounds)])
+            # device-timed loop: the loss is read once, after the last step (a driver that logs every K
+            # rounds); end-to-end loop: the loss of EVERY step is read on the host
+            out = one_round(rounds[(warmup + i) % len(rounds)], read=read_every_step or i == steps - 1)
         b.record()
         rt.barrier()
         torch.cuda.synchronize()
@@ -260,8 +263,8 @@ def run_ours(cfg):
         print(json.dumps({"profile_run": True, "steps": cfg.steps}))
         rt.shutdown()
         return 0
-    ms_dev, launches_dev, _ = timed(dev_rounds, cfg.steps, cfg.warmup)
-    ms_e2e, launches, out = timed(host_rounds, cfg.steps, max(3, cfg.warmup))
+    ms_dev, launches_dev, _ = timed(dev_rounds, cfg.steps, cfg.warmup, read_every_step=cfg.sync_results)
+    ms_e2e, launches, out = timed(host_rounds, cfg.steps, max(3, cfg.warmup), read_every_step=True)
     clocks = sampler.stop() if rt.rank == 0 else None
     last_loss = float(out[0].mean())
 

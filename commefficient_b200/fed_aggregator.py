@@ -333,7 +333,19 @@ class FedModel:
         args = self.args
         ids_t = batch[0]
         ids = ids_t.cpu().numpy() if torch.is_tensor(ids_t) else np.asarray(ids_t)
-        unique, inverse = np.unique(ids, return_inverse=True)
+        sorted_already = bool(ids.size <= 1 or np.all(ids[1:] >= ids[:-1]))
+        if sorted_already:
+            # the samplers emit each client's samples together in ascending client order: group
+            # boundaries are where the id changes (no sort / inverse permutation needed)
+            starts = np.concatenate([[0], np.flatnonzero(ids[1:] != ids[:-1]) + 1])
+            unique = ids[starts]
+            counts = np.diff(np.concatenate([starts, [ids.size]]))
+            order = None
+        else:
+            unique, inverse = np.unique(ids, return_inverse=True)
+            order = np.argsort(inverse, kind="stable")
+            counts = np.bincount(inverse, minlength=len(unique))
+            starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
         mine = self._assign(unique)[self.rt.rank]
         cols = batch[1:]
         client_batches = worker.ClientBatches()
@@ -341,17 +353,15 @@ class FedModel:
         h2d_phase = tr.phase("h2d")
         h2d_phase.__enter__()
         if len(mine):
-            order = np.argsort(inverse, kind="stable")
-            counts = np.bincount(inverse, minlength=len(unique))
-            starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
             pos = np.searchsorted(unique, mine)
-            sorted_already = bool(np.all(order == np.arange(len(order))))
             if sorted_already and int(pos[-1] - pos[0]) + 1 == len(pos):
                 # this rank's clients are one contiguous run of samples: slice (views of the
                 # caller's -- ideally pinned -- tensors), then one async H2D per column
                 a, b = int(starts[pos[0]]), int(starts[pos[-1]] + counts[pos[-1]])
                 dev_cols = [self._to_device(t[a:b]) for t in cols]
             else:
+                if order is None:
+                    order = np.arange(ids.size)
                 sel = np.concatenate([order[starts[p]:starts[p] + counts[p]] for p in pos])
                 sel_t = torch.from_numpy(sel)
                 dev_cols = [self._to_device(t[sel_t] if t.device.type == "cpu" else t[sel_t.to(t.device)])

@@ -231,7 +231,9 @@ def test_download_tracker_native_matches_torch_path():
         idx = torch.randperm(d, generator=g)[:5000].to(torch.int32)
         dev_tr.record_sparse(idx.cuda())
         cpu_tr.record_sparse(idx)
-        assert torch.equal(dev_tr.hist.cpu(), cpu_tr.hist) and torch.equal(dev_tr.last.cpu(), cpu_tr.last)
+        n = cpu_tr.hist.numel()
+        assert torch.equal(dev_tr.hist[:n].cpu(), cpu_tr.hist) and int(dev_tr.hist[n:].sum()) == 0
+        assert torch.equal(dev_tr.last.cpu(), cpu_tr.last)
     assert int(dev_tr.hist.sum()) == d
 
 
