@@ -48,6 +48,39 @@ def _upload_floats(args, d: int) -> int:
             "sketch": args.num_rows * args.num_cols, "fedavg": d}[args.mode]
 
 
+class _SmallH2D:
+    """Asynchronous host->device copies of small per-round index arrays.  ``torch.as_tensor(np_array,
+    device="cuda")`` copies from pageable memory, which blocks the host until everything queued on the
+    stream before it -- i.e. the whole client round -- has finished; staging through a ring of pinned
+    buffers (each guarded by the event of its last copy) keeps the host ahead of the GPU."""
+
+    def __init__(self, device, slots: int = 8):
+        self.device = torch.device(device)
+        self.slots, self.next = slots, 0
+        self.ring = {}
+
+    def __call__(self, arr: np.ndarray) -> torch.Tensor:
+        arr = np.ascontiguousarray(arr)
+        if self.device.type != "cuda":
+            return torch.as_tensor(arr, device=self.device)
+        key = (arr.dtype.str, arr.size)
+        ring = self.ring.setdefault(key, [])
+        if len(ring) < self.slots:
+            ring.append([torch.empty(arr.shape, dtype=torch.from_numpy(arr).dtype).pin_memory(), None])
+            slot = ring[-1]
+        else:
+            slot = ring[self.next % self.slots]
+            self.next += 1
+            if slot[1] is not None:
+                slot[1].synchronize()           # the copy that last used this buffer has long finished
+        slot[0].numpy()[...] = arr.reshape(slot[0].shape)
+        dev = slot[0].to(self.device, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        slot[1] = ev
+        return dev
+
+
 class _DownloadTracker:
     """Bytes a client must download = 4 x (coordinates changed since it last took part).
     Kept on the device as ``last_changed[d]`` (round of each coordinate's last update)
@@ -62,6 +95,7 @@ class _DownloadTracker:
         # step's CUDA graph -- practically never happens)
         self.hist = torch.zeros(65536 if torch.device(device).type == "cuda" else 1024, dtype=torch.int64,
                                 device=device)
+        self.h2d = _SmallH2D(device)
         self.generation = 0                 # bumped whenever hist / last are re-allocated
         self.round_dev = None               # device copy of `round` for graph-replayed updates
         self.last = torch.zeros(d, dtype=torch.int64, device=device) if sparse else None
@@ -79,7 +113,7 @@ class _DownloadTracker:
         """Device float32 tensor: changed-coordinate count per participating client."""
         start_np = np.minimum(self.seen[clients] + 1, self.hist.numel() - 1)
         self.seen[clients] = self.round
-        start = torch.as_tensor(start_np, device=self.device)
+        start = self.h2d(start_np.astype(np.int64))
         if self.hist.is_cuda:
             from .ops import native
             out = torch.empty(len(clients), dtype=torch.float32, device=self.device)
@@ -392,7 +426,7 @@ class FedModel:
             slab = torch.zeros((len(unique), local.shape[1] if local.dim() == 2 else args.num_results_train),
                                dtype=torch.float32, device=self.device)
             if len(mine):
-                slab[torch.from_numpy(np.searchsorted(unique, mine)).to(self.device)] = local.float()
+                slab[self.tracker.h2d(np.searchsorted(unique, mine).astype(np.int64))] = local.float()
             gathered = self.rt.peer.all_reduce_sum_(slab)
         elif self.rt.world_size > 1:
             sizes = [len(c) for c in self._assign(unique)]
