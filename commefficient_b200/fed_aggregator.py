@@ -296,6 +296,7 @@ class FedModel:
         self.watchdog = RoundWatchdog(getattr(args, "watchdog_timeout", 0.0) or 0.0, self.rt.rank).start()
         self._fault = parse_fault()
         self._result_ring = {}
+        self._copy_stream = None
         self.tracer = PhaseTracer(getattr(args, "trace_phases", "") or "", getattr(args, "trace_every", 50),
                                   self.rt.rank, self._trace_max, self.device.type)
         _CURRENT = self
@@ -361,7 +362,21 @@ class FedModel:
         return [np.asarray(c, dtype=np.int64) for c in np.array_split(unique, ws)]
 
     def _to_device(self, t: torch.Tensor) -> torch.Tensor:
-        return t.to(self.device, non_blocking=True) if t.device != self.device else t
+        """Inputs from pinned host memory are copied on a dedicated stream, so the transfer of round t+1
+        starts as soon as the driver calls the model -- under round t's server step -- instead of queueing
+        behind it; the compute stream waits on the copy's event."""
+        if t.device == self.device:
+            return t
+        if self.device.type != "cuda" or not t.is_pinned():
+            return t.to(self.device, non_blocking=True)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        main = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self._copy_stream):
+            dev = t.to(self.device, non_blocking=True)
+        main.wait_stream(self._copy_stream)
+        dev.record_stream(main)
+        return dev
 
     def _call_train(self, batch):
         args = self.args
