@@ -153,6 +153,14 @@ def _has_batchnorm(model: torch.nn.Module) -> bool:
     return any(isinstance(m, torch.nn.modules.batchnorm._BatchNorm) for m in model.modules())
 
 
+def _bn_segmentable(model: torch.nn.Module) -> bool:
+    """Every BatchNorm layer can keep per-client statistics inside a batched forward
+    (``ops/nn.py:BatchNorm2d`` under ``bn_segments``)."""
+    from .ops import nn as nnops
+    bns = [m for m in model.modules() if isinstance(m, torch.nn.modules.batchnorm._BatchNorm)]
+    return all(isinstance(m, nnops.BatchNorm2d) and m.affine for m in bns)
+
+
 def _autocast(args, device):
     if device.type == "cuda" and getattr(args, "precision", "bf16") == "bf16":
         return torch.autocast("cuda", dtype=torch.bfloat16)
@@ -299,6 +307,7 @@ class ClientWorker:
         self._ps_copy = None
         self._graphs = {}
         self.has_bn = _has_batchnorm(model)
+        self.bn_segmentable = self.has_bn and _bn_segmentable(model)
         # tensor-core layers: hand-written tcgen05 kernels on CUDA unless switched off
         from .ops import nn as nnops
         nnops.set_native(self.device.type == "cuda" and not getattr(args, "no_native_nn", False))
@@ -313,13 +322,20 @@ class ClientWorker:
                 if (t.dim() == 4 and t.is_floating_point()) else t for t in cols]
 
     # -- which path ----------------------------------------------------------------
-    def can_batch_clients(self) -> bool:
+    def can_batch_clients(self, sizes=None) -> bool:
+        """Whether a round can run as ONE forward/backward over all of this rank's clients.  BatchNorm
+        models qualify when their BN layers can keep per-client statistics (segment-wise BN), which
+        needs equal client batch sizes (``sizes``) that fit one chunk."""
         a = self.args
+        if self.has_bn:
+            if not self.bn_segmentable:
+                return False
+            if sizes is not None and (len(set(sizes)) != 1 or sum(sizes) > self.MAX_BATCHED_SAMPLES):
+                return False
         return (not getattr(a, "no_client_batching", False)
                 and a.mode in ("sketch", "uncompressed", "true_topk")
                 and a.max_grad_norm is None and not a.do_dp and not a.do_topk_down
                 and self.velocities is None and self.errors is None
-                and not self.has_bn
                 and hasattr(self.compute_loss_train, "per_sample"))
 
     # -- training round --------------------------------------------------------------
@@ -338,7 +354,7 @@ class ClientWorker:
             return self._round_test(client_batches)
         if self.args.mode == "fedavg":
             return self._round_fedavg(client_batches, fedavg_lr)
-        if self.can_batch_clients():
+        if self.can_batch_clients(client_batches.sizes):
             return self._round_batched(client_batches)
         return torch.stack([self._one_client(cid, batch) for cid, batch in client_batches])
 
@@ -432,7 +448,8 @@ class ClientWorker:
             fp.on_range_final = on_final
         for lo in range(0, total, self.MAX_BATCHED_SAMPLES):
             chunk = [t[lo:lo + self.MAX_BATCHED_SAMPLES] for t in cat]
-            with _autocast(a, self.device):
+            from .ops import nn as nnops
+            with _autocast(a, self.device), nnops.bn_segments(len(sizes) if self.has_bn else 0):
                 if getattr(self.compute_loss_train.per_sample, "needs_segments", False):
                     # losses that are not a plain per-sample mean (e.g. mean over a client's tokens)
                     # get the client index of every sample and return values v_s with

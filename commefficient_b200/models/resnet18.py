@@ -80,9 +80,9 @@ class PreActBlock(nn.Module):
 
     def __init__(self, in_channels, out_channels, stride=1):
         super().__init__()
-        self.bn1 = nn.BatchNorm2d(out_channels)
+        self.bn1 = nnops.BatchNorm2d(out_channels)
         self.conv1 = _conv3x3(in_channels, out_channels, stride)
-        self.bn2 = nn.BatchNorm2d(out_channels)
+        self.bn2 = nnops.BatchNorm2d(out_channels)
         self.conv2 = _conv3x3(out_channels, out_channels, 1)
         if _needs_projection(in_channels, out_channels, stride):
             self.shortcut = nn.Sequential(

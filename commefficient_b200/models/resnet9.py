@@ -33,7 +33,7 @@ DEFAULT_CHANNELS = {"prep": 64, "layer1": 128, "layer2": 256, "layer3": 512}
 
 def _make_bn(channels, bn_bias_init=None, bn_bias_freeze=False, bn_weight_init=None,
              bn_weight_freeze=False):
-    bn = nn.BatchNorm2d(channels)
+    bn = nnops.BatchNorm2d(channels)
     if bn_bias_init is not None:
         nn.init.constant_(bn.bias, bn_bias_init)
     if bn_weight_init is not None:

@@ -19,6 +19,8 @@ from typing import List, Optional, Sequence, Type
 import torch
 import torch.nn as nn
 
+from ..ops import nn as nnops
+
 __all__ = ["ResNet", "BasicBlock", "Bottleneck", "resnet18", "resnet34", "resnet50", "resnet101",
            "resnet152", "resnext50_32x4d", "resnext101_32x8d", "wide_resnet50_2", "wide_resnet101_2"]
 
@@ -40,7 +42,7 @@ class BasicBlock(nn.Module):
     expansion = 1
 
     def __init__(self, inplanes, planes, hw, stride=1, downsample=None, groups=1, base_width=64,
-                 dilation=1, norm_layer=nn.BatchNorm2d):
+                 dilation=1, norm_layer=nnops.BatchNorm2d):
         super().__init__()
         if groups != 1 or base_width != 64 or dilation != 1:
             raise ValueError("BasicBlock supports only groups=1, base_width=64, dilation=1")
@@ -64,7 +66,7 @@ class Bottleneck(nn.Module):
     expansion = 4
 
     def __init__(self, inplanes, planes, hw, stride=1, downsample=None, groups=1, base_width=64,
-                 dilation=1, norm_layer=nn.BatchNorm2d):
+                 dilation=1, norm_layer=nnops.BatchNorm2d):
         super().__init__()
         width = int(planes * (base_width / 64.0)) * groups
         out_hw = math.ceil(hw / stride)
@@ -96,7 +98,7 @@ class ResNet(nn.Module):
                  replace_stride_with_dilation: Optional[Sequence[bool]] = None, norm_layer=None,
                  in_channels=1):
         super().__init__()
-        norm_layer = norm_layer or nn.BatchNorm2d
+        norm_layer = norm_layer or nnops.BatchNorm2d
         self._norm_layer = norm_layer
         dilate = list(replace_stride_with_dilation or (False, False, False))
         if len(dilate) != 3:

@@ -87,3 +87,90 @@ def lm_head_cross_entropy(hidden2d, weight, labels, ignore_index=-1):
         if tc.lm_head_supported(hidden2d, weight):
             return tc.lm_head_ce(hidden2d, weight, labels, ignore_index)
     return cross_entropy_rows(linear(hidden2d, weight, None), labels, ignore_index)
+
+
+# ---------------------------------------------------------------------------- segment-wise BatchNorm
+# The reference runs every client's batch through the model separately, so BatchNorm statistics are
+# per CLIENT batch (resnet9.py:17-29, fixup_resnet18.py:143-146).  To batch a rank's clients into one
+# forward/backward (fed_worker._round_batched) BatchNorm must keep that semantics: statistics per
+# (client, channel) over that client's samples only.  ``bn_segments(n)`` announces that the leading
+# dimension of every activation is n equal-sized client segments; ``BatchNorm2d`` (a drop-in
+# ``nn.BatchNorm2d``: same parameters, buffers and state_dict keys) then normalises per segment.
+_bn_segments = 0
+
+
+class bn_segments:
+    def __init__(self, n: int):
+        self.n = int(n)
+
+    def __enter__(self):
+        global _bn_segments
+        self.prev, _bn_segments = _bn_segments, self.n
+        return self
+
+    def __exit__(self, *exc):
+        global _bn_segments
+        _bn_segments = self.prev
+        return False
+
+
+class _SegmentBN(torch.autograd.Function):
+    """y = (x - mean_seg) * rstd_seg * gamma + beta with statistics per (segment, channel).
+    x: ``[S*n, C, H, W]`` (any memory format); fp32 statistics; two passes forward, two backward."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, segments, eps):
+        N, C = x.shape[0], x.shape[1]
+        n = N // segments
+        x5 = x.reshape(segments, n, C, -1)                               # [S, n, C, HW] (view when possible)
+        xf = x5.float()
+        var, mean = torch.var_mean(xf, dim=(1, 3), unbiased=False, keepdim=True)     # [S, 1, C, 1]
+        rstd = torch.rsqrt(var + eps)
+        xhat = (xf - mean) * rstd
+        y = xhat * weight.float().view(1, 1, C, 1) + bias.float().view(1, 1, C, 1)
+        ctx.save_for_backward(xhat.to(x.dtype), rstd, weight)
+        ctx.shape = x.shape
+        out = y.to(x.dtype).reshape(x.shape)
+        if x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last):
+            out = out.contiguous(memory_format=torch.channels_last)
+        mean, var = mean.reshape(segments, C), var.reshape(segments, C)
+        ctx.mark_non_differentiable(mean, var)
+        return out, mean, var
+
+    @staticmethod
+    def backward(ctx, dy, _dmean, _dvar):
+        xhat, rstd, weight = ctx.saved_tensors
+        S, n, C, L = xhat.shape
+        dyf = dy.reshape(S, n, C, L).float()
+        xh = xhat.float()
+        dbeta = dyf.sum(dim=(0, 1, 3))
+        dgamma = (dyf * xh).sum(dim=(0, 1, 3))
+        g = dyf * weight.float().view(1, 1, C, 1)
+        m1 = g.mean(dim=(1, 3), keepdim=True)
+        m2 = (g * xh).mean(dim=(1, 3), keepdim=True)
+        dx = (g - m1 - xh * m2) * rstd
+        dx = dx.to(dy.dtype).reshape(ctx.shape)
+        if dy.dim() == 4 and dy.is_contiguous(memory_format=torch.channels_last):
+            dx = dx.contiguous(memory_format=torch.channels_last)
+        return dx, dgamma.to(weight.dtype), dbeta.to(weight.dtype), None, None
+
+
+class BatchNorm2d(torch.nn.BatchNorm2d):
+    """``nn.BatchNorm2d`` that, inside ``bn_segments(n)`` and in training mode, normalises each of the n
+    equal client segments of the batch with its own statistics.  Running statistics are advanced once
+    per call with the mean over the segments (the reference never federates them: SURVEY Q12)."""
+
+    def forward(self, x):
+        S = _bn_segments
+        if not (self.training and S > 1 and x.shape[0] % S == 0 and self.affine):
+            return super().forward(x)
+        y, mean, var = _SegmentBN.apply(x, self.weight, self.bias, S, self.eps)
+        if self.track_running_stats and self.running_mean is not None:
+            with torch.no_grad():
+                n = x.shape[0] // S * (x.numel() // (x.shape[0] * x.shape[1]))     # samples x pixels per segment
+                m = self.momentum if self.momentum is not None else 0.1
+                self.running_mean.mul_(1 - m).add_(mean.mean(0).to(self.running_mean.dtype), alpha=m)
+                unbiased = var.mean(0) * (n / max(n - 1, 1))
+                self.running_var.mul_(1 - m).add_(unbiased.to(self.running_var.dtype), alpha=m)
+                self.num_batches_tracked += 1
+        return y
