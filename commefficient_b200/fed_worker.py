@@ -324,13 +324,13 @@ class ClientWorker:
     # -- which path ----------------------------------------------------------------
     def can_batch_clients(self, sizes=None) -> bool:
         """Whether a round can run as ONE forward/backward over all of this rank's clients.  BatchNorm
-        models qualify when their BN layers can keep per-client statistics (segment-wise BN), which
-        needs equal client batch sizes (``sizes``) that fit one chunk."""
+        models qualify when their BN layers can keep per-client statistics (segment-wise BN) and the
+        round fits one chunk."""
         a = self.args
         if self.has_bn:
             if not self.bn_segmentable:
                 return False
-            if sizes is not None and (len(set(sizes)) != 1 or sum(sizes) > self.MAX_BATCHED_SAMPLES):
+            if sizes is not None and sum(sizes) > self.MAX_BATCHED_SAMPLES:
                 return False
         return (not getattr(a, "no_client_batching", False)
                 and a.mode in ("sketch", "uncompressed", "true_topk")
@@ -449,7 +449,12 @@ class ClientWorker:
         for lo in range(0, total, self.MAX_BATCHED_SAMPLES):
             chunk = [t[lo:lo + self.MAX_BATCHED_SAMPLES] for t in cat]
             from .ops import nn as nnops
-            with _autocast(a, self.device), nnops.bn_segments(len(sizes) if self.has_bn else 0):
+            equal = len(set(sizes)) == 1
+            bn_ctx = (nnops.bn_segments(0) if not self.has_bn else
+                      nnops.bn_segments(len(sizes)) if equal else
+                      nnops.bn_segments(len(sizes), seg=seg, counts=counts if counts is not None else
+                                        torch.tensor(sizes, device=self.device, dtype=torch.float32)))
+            with _autocast(a, self.device), bn_ctx:
                 if getattr(self.compute_loss_train.per_sample, "needs_segments", False):
                     # losses that are not a plain per-sample mean (e.g. mean over a client's tokens)
                     # get the client index of every sample and return values v_s with

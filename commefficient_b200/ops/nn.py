@@ -96,22 +96,73 @@ def lm_head_cross_entropy(hidden2d, weight, labels, ignore_index=-1):
 # (client, channel) over that client's samples only.  ``bn_segments(n)`` announces that the leading
 # dimension of every activation is n equal-sized client segments; ``BatchNorm2d`` (a drop-in
 # ``nn.BatchNorm2d``: same parameters, buffers and state_dict keys) then normalises per segment.
-_bn_segments = 0
+_bn_segments = 0            # number of client segments in the current batch (0: plain BatchNorm)
+_bn_seg_ids = None          # [N] long: segment of every sample (None: equal-sized consecutive segments)
+_bn_seg_counts = None       # [S] float: samples per segment
 
 
 class bn_segments:
-    def __init__(self, n: int):
-        self.n = int(n)
+    """``with bn_segments(n):`` -- the batch is n equal-sized consecutive client segments;
+    ``with bn_segments(n, seg=ids, counts=c):`` -- arbitrary sizes: ``ids[i]`` is the segment of sample i
+    and ``c[s]`` the number of samples of segment s (device tensors, built once outside any graph capture)."""
+
+    def __init__(self, n: int, seg=None, counts=None):
+        self.n, self.seg = int(n), seg
+        self.counts = counts.reshape(-1).float() if counts is not None else None
 
     def __enter__(self):
-        global _bn_segments
-        self.prev, _bn_segments = _bn_segments, self.n
+        global _bn_segments, _bn_seg_ids, _bn_seg_counts
+        self.prev = (_bn_segments, _bn_seg_ids, _bn_seg_counts)
+        _bn_segments, _bn_seg_ids, _bn_seg_counts = self.n, self.seg, self.counts
         return self
 
     def __exit__(self, *exc):
-        global _bn_segments
-        _bn_segments = self.prev
+        global _bn_segments, _bn_seg_ids, _bn_seg_counts
+        _bn_segments, _bn_seg_ids, _bn_seg_counts = self.prev
         return False
+
+
+class _SegmentBNGeneral(torch.autograd.Function):
+    """Segment-wise BatchNorm for segments of different sizes: per-sample partial sums are combined per
+    segment with ``index_add_`` and the statistics gathered back per sample."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, seg, counts, segments, eps):
+        N, C = x.shape[0], x.shape[1]
+        xf = x.reshape(N, C, -1).float()
+        L = xf.shape[2]
+        denom = (counts * L).clamp_min(1.0).view(segments, 1)
+        mean = torch.zeros(segments, C, dtype=torch.float32, device=x.device).index_add_(0, seg, xf.sum(2)) / denom
+        xc = xf - mean[seg].unsqueeze(2)
+        var = torch.zeros(segments, C, dtype=torch.float32, device=x.device).index_add_(0, seg, (xc * xc).sum(2)) / denom
+        rstd = torch.rsqrt(var + eps)
+        xhat = xc * rstd[seg].unsqueeze(2)
+        y = xhat * weight.float().view(1, C, 1) + bias.float().view(1, C, 1)
+        ctx.save_for_backward(xhat.to(x.dtype), rstd, weight, seg, denom)
+        ctx.shape, ctx.segments = x.shape, segments
+        out = y.to(x.dtype).reshape(x.shape)
+        if x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last):
+            out = out.contiguous(memory_format=torch.channels_last)
+        ctx.mark_non_differentiable(mean, var)
+        return out, mean, var
+
+    @staticmethod
+    def backward(ctx, dy, _dmean, _dvar):
+        xhat, rstd, weight, seg, denom = ctx.saved_tensors
+        N, C, L = xhat.shape
+        S = ctx.segments
+        dyf = dy.reshape(N, C, L).float()
+        xh = xhat.float()
+        dbeta = dyf.sum(dim=(0, 2))
+        dgamma = (dyf * xh).sum(dim=(0, 2))
+        g = dyf * weight.float().view(1, C, 1)
+        m1 = torch.zeros(S, C, dtype=torch.float32, device=dy.device).index_add_(0, seg, g.sum(2)) / denom
+        m2 = torch.zeros(S, C, dtype=torch.float32, device=dy.device).index_add_(0, seg, (g * xh).sum(2)) / denom
+        dx = (g - m1[seg].unsqueeze(2) - xh * m2[seg].unsqueeze(2)) * rstd[seg].unsqueeze(2)
+        dx = dx.to(dy.dtype).reshape(ctx.shape)
+        if dy.dim() == 4 and dy.is_contiguous(memory_format=torch.channels_last):
+            dx = dx.contiguous(memory_format=torch.channels_last)
+        return dx, dgamma.to(weight.dtype), dbeta.to(weight.dtype), None, None, None, None
 
 
 class _SegmentBN(torch.autograd.Function):
@@ -162,12 +213,16 @@ class BatchNorm2d(torch.nn.BatchNorm2d):
 
     def forward(self, x):
         S = _bn_segments
-        if not (self.training and S > 1 and x.shape[0] % S == 0 and self.affine):
+        general = _bn_seg_ids is not None and _bn_seg_ids.shape[0] == x.shape[0]
+        if not (self.training and S > 1 and self.affine and (general or x.shape[0] % S == 0)):
             return super().forward(x)
-        y, mean, var = _SegmentBN.apply(x, self.weight, self.bias, S, self.eps)
+        if general:
+            y, mean, var = _SegmentBNGeneral.apply(x, self.weight, self.bias, _bn_seg_ids, _bn_seg_counts, S, self.eps)
+        else:
+            y, mean, var = _SegmentBN.apply(x, self.weight, self.bias, S, self.eps)
         if self.track_running_stats and self.running_mean is not None:
             with torch.no_grad():
-                n = x.shape[0] // S * (x.numel() // (x.shape[0] * x.shape[1]))     # samples x pixels per segment
+                n = max(x.shape[0] // S, 1) * (x.numel() // (x.shape[0] * x.shape[1]))   # ~samples x pixels per segment
                 m = self.momentum if self.momentum is not None else 0.1
                 self.running_mean.mul_(1 - m).add_(mean.mean(0).to(self.running_mean.dtype), alpha=m)
                 unbiased = var.mean(0) * (n / max(n - 1, 1))

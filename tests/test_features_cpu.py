@@ -267,12 +267,15 @@ def test_batchnorm_model_batched_round_equals_per_client_round():
         losses = []
         for s in range(2):          # 16x16 images keep the CPU run short (the head pools globally)
             fed.train(True)
-            out = fed(synthetic_image_batch(4, 3, shape=(3, 16, 16), seed=s, first_client=4 * s))
+            batch = synthetic_image_batch(4, 3, shape=(3, 16, 16), seed=s, first_client=4 * s)
+            if s == 1:              # unequal client batch sizes: 3, 2, 3, 2 (general segment path)
+                keep = torch.tensor([0, 1, 2, 3, 4, 6, 7, 8, 9, 10])
+                batch = tuple(t[keep] for t in batch)
+            out = fed(batch)
             opt.step()
             losses.append(float(np.mean(out[0])))
         w = fed.fp.flat.clone()
-        batched = fed.worker.can_batch_clients([3, 3, 3, 3])
-        assert not fed.worker.can_batch_clients([3, 2, 3, 3]) or not fed.worker.has_bn
+        batched = fed.worker.can_batch_clients([3, 3, 3, 3]) and fed.worker.can_batch_clients([3, 2, 3, 3])
         fed.rt.shutdown()
         return w, losses, batched
 
@@ -283,3 +286,26 @@ def test_batchnorm_model_batched_round_equals_per_client_round():
     # top-k picks may differ where two candidates tie to rounding: all but a handful of the 2 x 500 updated
     # coordinates must agree
     assert int(((w_b - w_c).abs() > 1e-5).sum()) < 150
+
+
+def test_segment_batchnorm_unequal_segments():
+    from commefficient_b200.ops import nn as nnops
+    torch.manual_seed(1)
+    sizes = [2, 5, 3, 4]
+    C = 4
+    x = torch.randn(sum(sizes), C, 3, 3, requires_grad=True)
+    bn, ref = nnops.BatchNorm2d(C), torch.nn.BatchNorm2d(C)
+    torch.nn.init.normal_(bn.weight, 1, 0.2)
+    ref.load_state_dict(bn.state_dict())
+    seg = torch.repeat_interleave(torch.arange(len(sizes)), torch.tensor(sizes))
+    with nnops.bn_segments(len(sizes), seg=seg, counts=torch.tensor(sizes, dtype=torch.float32)):
+        y = bn(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xs = x.detach().clone().requires_grad_(True)
+    bounds = np.cumsum([0] + sizes)
+    ys = torch.cat([ref(xs[a:b]) for a, b in zip(bounds[:-1], bounds[1:])])
+    ys.backward(dy)
+    torch.testing.assert_close(y, ys, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(x.grad, xs.grad, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=1e-4, atol=1e-4)
