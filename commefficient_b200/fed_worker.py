@@ -449,7 +449,7 @@ class ClientWorker:
         for lo in range(0, total, self.MAX_BATCHED_SAMPLES):
             chunk = [t[lo:lo + self.MAX_BATCHED_SAMPLES] for t in cat]
             from .ops import nn as nnops
-            equal = len(set(sizes)) == 1
+            equal = len(set(sizes)) == 1 and self.device.type != "cuda"   # (CUDA: seg ids feed the native kernels)
             bn_ctx = (nnops.bn_segments(0) if not self.has_bn else
                       nnops.bn_segments(len(sizes)) if equal else
                       nnops.bn_segments(len(sizes), seg=seg, counts=counts if counts is not None else

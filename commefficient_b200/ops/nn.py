@@ -216,7 +216,13 @@ class BatchNorm2d(torch.nn.BatchNorm2d):
         general = _bn_seg_ids is not None and _bn_seg_ids.shape[0] == x.shape[0]
         if not (self.training and S > 1 and self.affine and (general or x.shape[0] % S == 0)):
             return super().forward(x)
-        if general:
+        native_ok = False
+        if general and _use_native(x):
+            from . import tfm
+            native_ok = tfm.segment_bn_supported(x, _bn_seg_ids, _bn_seg_counts)
+        if native_ok:
+            y, mean, var = tfm.segment_batch_norm(x, self.weight, self.bias, _bn_seg_ids, _bn_seg_counts, S, self.eps)
+        elif general:
             y, mean, var = _SegmentBNGeneral.apply(x, self.weight, self.bias, _bn_seg_ids, _bn_seg_counts, S, self.eps)
         else:
             y, mean, var = _SegmentBN.apply(x, self.weight, self.bias, S, self.eps)

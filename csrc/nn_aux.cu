@@ -587,3 +587,177 @@ CEB_API int ceb_linear_ce_head(const void* feat_bf16, const float* W, float scal
   CEB_CHECK_LAUNCH();
   return 0;
 }
+
+// ------------------------------------------------------------------ segment-wise BatchNorm (NHWC bf16)
+// BatchNorm whose statistics are per (client segment, channel): sample n belongs to segment seg[n], and
+// every segment is normalised with the mean / variance of its own samples only -- the semantics of the
+// reference's one-forward-per-client loop (models/resnet9.py:17-29, fixup_resnet18.py:143-146) inside ONE
+// batched forward.  x, y, dy, dx: [N][L][C] bf16 (channels_last), C % 8 == 0; statistics fp32 [S][C].
+// Thread = 8 channels of one pixel (16-byte accesses); block = 32 pixel lanes x 8 channel groups
+// (64 channels); a block stays inside one sample, so its partial sums go to one segment.
+constexpr int SEGBN_PIX = 256;          // pixels of one sample handled by a block
+
+__device__ __forceinline__ void segbn_unpack(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 t = __bfloat1622float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ uint4 segbn_pack(const float (&f)[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return u;
+}
+
+// MODE 0: a[s][c] += sum x, b[s][c] += sum x^2.   MODE 1 (backward): a += sum dy, b += sum dy * xhat.
+template <int MODE>
+__global__ void __launch_bounds__(256)
+segbn_sums_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                  const int64_t* __restrict__ seg, int L, int C, int chunks, const float* __restrict__ mean,
+                  const float* __restrict__ rstd, float* __restrict__ a, float* __restrict__ b) {
+  __shared__ float sa[32][65], sb[32][65];
+  const int n = blockIdx.x / chunks, chunk = blockIdx.x - n * chunks;
+  const int cg = threadIdx.x & 7, pl = threadIdx.x >> 3;
+  const int c0 = blockIdx.y * 64 + cg * 8;
+  const int s = (int)seg[n];
+  float acc_a[8], acc_b[8], mu[8], rs[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { acc_a[j] = 0.f; acc_b[j] = 0.f; mu[j] = 0.f; rs[j] = 1.f; }
+  if (c0 < C) {
+    if (MODE == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { mu[j] = mean[(size_t)s * C + c0 + j]; rs[j] = rstd[(size_t)s * C + c0 + j]; }
+    }
+    const int p_end = min(L, (chunk + 1) * SEGBN_PIX);
+    for (int p = chunk * SEGBN_PIX + pl; p < p_end; p += 32) {
+      const size_t off = ((size_t)n * L + p) * C + c0;
+      float xv[8];
+      segbn_unpack(*reinterpret_cast<const uint4*>(x + off), xv);
+      if (MODE == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { acc_a[j] += xv[j]; acc_b[j] = fmaf(xv[j], xv[j], acc_b[j]); }
+      } else {
+        float dv[8];
+        segbn_unpack(*reinterpret_cast<const uint4*>(dy + off), dv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { acc_a[j] += dv[j]; acc_b[j] = fmaf(dv[j], (xv[j] - mu[j]) * rs[j], acc_b[j]); }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { sa[pl][cg * 8 + j] = acc_a[j]; sb[pl][cg * 8 + j] = acc_b[j]; }
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int c = threadIdx.x & 63;
+    const bool second = threadIdx.x >= 64;
+    float t = 0.f;
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) t += second ? sb[r][c] : sa[r][c];
+    const int cc = blockIdx.y * 64 + c;
+    if (cc < C) atomicAdd((second ? b : a) + (size_t)s * C + cc, t);
+  }
+}
+
+// mean = a / cnt, rstd = 1 / sqrt(b / cnt - mean^2 + eps); var (biased) also returned; cnt = samples[s] * L
+__global__ void segbn_finalize_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                      const float* __restrict__ samples, int L, int S, int C, float eps,
+                                      float* __restrict__ mean, float* __restrict__ var, float* __restrict__ rstd) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= S * C) return;
+  const float cnt = fmaxf(samples[i / C] * (float)L, 1.f);
+  const float m = a[i] / cnt;
+  const float v = fmaxf(b[i] / cnt - m * m, 0.f);
+  mean[i] = m; var[i] = v; rstd[i] = rsqrtf(v + eps);
+}
+
+// MODE 0: y = (x - mean) * rstd * gamma + beta.
+// MODE 1: dx = gamma * rstd * (dy - A/cnt - xhat * B/cnt)   (A, B from segbn_sums_kernel<1>)
+template <int MODE>
+__global__ void __launch_bounds__(256)
+segbn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                   const int64_t* __restrict__ seg, int L, int C, int64_t total8, const float* __restrict__ mean,
+                   const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
+                   const float* __restrict__ A, const float* __restrict__ B, const float* __restrict__ samples,
+                   __nv_bfloat16* __restrict__ out) {
+  const int c8 = C >> 3;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total8; i += stride) {
+    const int c0 = (int)(i % c8) * 8;
+    const int64_t pix = i / c8;
+    const int n = (int)(pix / L);
+    const int s = (int)seg[n];
+    const size_t off = (size_t)pix * C + c0, so = (size_t)s * C + c0;
+    float xv[8], o[8];
+    segbn_unpack(*reinterpret_cast<const uint4*>(x + off), xv);
+    if (MODE == 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        o[j] = fmaf((xv[j] - mean[so + j]) * rstd[so + j], __ldg(gamma + c0 + j), __ldg(beta + c0 + j));
+    } else {
+      float dv[8];
+      segbn_unpack(*reinterpret_cast<const uint4*>(dy + off), dv);
+      const float inv = 1.f / fmaxf(samples[s] * (float)L, 1.f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float rs = rstd[so + j];
+        const float xh = (xv[j] - mean[so + j]) * rs;
+        o[j] = __ldg(gamma + c0 + j) * rs * (dv[j] - A[so + j] * inv - xh * B[so + j] * inv);
+      }
+    }
+    *reinterpret_cast<uint4*>(out + off) = segbn_pack(o);
+  }
+}
+
+static int segbn_check(const char* who, const void* x, int64_t N, int L, int C, int S) {
+  CEB_REQUIRE(x && N > 0 && L > 0 && S > 0, "%s: bad arguments", who);
+  CEB_REQUIRE(C % 8 == 0 && (((uintptr_t)x) & 15) == 0, "%s: need C %% 8 == 0 and 16-byte aligned tensors (C=%d)", who, C);
+  return 0;
+}
+
+// Forward.  sums: [2][S][C] fp32 scratch (zeroed here); mean / var / rstd: [S][C] outputs; samples: [S]
+// fp32 samples per segment; seg: [N] int64 segment of every sample.
+CEB_API int ceb_segment_bn_fwd(const void* x_bf16, const int64_t* seg, const float* samples, int64_t N, int L, int C,
+                               int S, const float* gamma, const float* beta, float eps, float* sums, float* mean,
+                               float* var, float* rstd, void* y_bf16, void* stream) {
+  if (int e = segbn_check("ceb_segment_bn_fwd", x_bf16, N, L, C, S)) return e;
+  CEB_REQUIRE(seg && samples && gamma && beta && sums && mean && var && rstd && y_bf16, "ceb_segment_bn_fwd: null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int chunks = (int)ceb_cdiv(L, SEGBN_PIX);
+  CEB_CHECK_CUDA(cudaMemsetAsync(sums, 0, (size_t)2 * S * C * sizeof(float), st));
+  dim3 grid((unsigned)(N * chunks), (unsigned)ceb_cdiv(C, 64));
+  segbn_sums_kernel<0><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x_bf16, nullptr, seg, L, C, chunks, nullptr, nullptr,
+                                             sums, sums + (size_t)S * C);
+  segbn_finalize_kernel<<<(unsigned)ceb_cdiv((int64_t)S * C, 256), 256, 0, st>>>(sums, sums + (size_t)S * C, samples, L, S,
+                                                                               C, eps, mean, var, rstd);
+  const int64_t total8 = N * L * (C / 8);
+  segbn_apply_kernel<0><<<ceb_grid_for(total8, 256), 256, 0, st>>>((const __nv_bfloat16*)x_bf16, nullptr, seg, L, C, total8,
+                                                                  mean, rstd, gamma, beta, nullptr, nullptr, samples,
+                                                                  (__nv_bfloat16*)y_bf16);
+  CEB_COUNT_LAUNCH(3);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Backward.  sums: [2][S][C] scratch; on return sums[0] = per-segment sum of dy (dbeta = its sum over
+// segments), sums[1] = per-segment sum of dy * xhat (dgamma likewise).
+CEB_API int ceb_segment_bn_bwd(const void* dy_bf16, const void* x_bf16, const int64_t* seg, const float* samples,
+                               int64_t N, int L, int C, int S, const float* gamma, const float* mean, const float* rstd,
+                               float* sums, void* dx_bf16, void* stream) {
+  if (int e = segbn_check("ceb_segment_bn_bwd", x_bf16, N, L, C, S)) return e;
+  CEB_REQUIRE(dy_bf16 && seg && samples && gamma && mean && rstd && sums && dx_bf16 && (((uintptr_t)dy_bf16) & 15) == 0,
+              "ceb_segment_bn_bwd: null or misaligned pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int chunks = (int)ceb_cdiv(L, SEGBN_PIX);
+  CEB_CHECK_CUDA(cudaMemsetAsync(sums, 0, (size_t)2 * S * C * sizeof(float), st));
+  dim3 grid((unsigned)(N * chunks), (unsigned)ceb_cdiv(C, 64));
+  segbn_sums_kernel<1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x_bf16, (const __nv_bfloat16*)dy_bf16, seg, L, C, chunks,
+                                             mean, rstd, sums, sums + (size_t)S * C);
+  const int64_t total8 = N * L * (C / 8);
+  segbn_apply_kernel<1><<<ceb_grid_for(total8, 256), 256, 0, st>>>((const __nv_bfloat16*)x_bf16, (const __nv_bfloat16*)dy_bf16,
+                                                                  seg, L, C, total8, mean, rstd, gamma, nullptr, sums,
+                                                                  sums + (size_t)S * C, samples, (__nv_bfloat16*)dx_bf16);
+  CEB_COUNT_LAUNCH(2);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}

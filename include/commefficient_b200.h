@@ -233,6 +233,18 @@ int ceb_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, c
                       float* dx, float* dgamma, float* dbeta, int64_t rows, int E, void* stream);
 /* tanh-GELU on bf16: out = gelu(x) (dy NULL) or dy * gelu'(x). */
 int ceb_gelu_bf16(const void* x, const void* dy, void* out, int64_t n, void* stream);
+/* Segment-wise BatchNorm (training mode) over NHWC bf16 activations x [N][L][C], C % 8 == 0: sample n
+ * belongs to segment seg[n] (int64) and is normalised with the statistics of its own segment only
+ * (per-client statistics inside a batched forward; no counterpart in the reference, which runs clients
+ * one by one).  samples[s] = number of samples of segment s (fp32); sums = [2][S][C] fp32 scratch.
+ * fwd writes y and mean / var (biased) / rstd [S][C]; bwd writes dx and leaves the per-segment sums of dy
+ * and dy * xhat in sums[0] / sums[1] (dbeta / dgamma are their sums over segments). */
+int ceb_segment_bn_fwd(const void* x_bf16, const int64_t* seg, const float* samples, int64_t N, int L, int C, int S,
+                       const float* gamma, const float* beta, float eps, float* sums, float* mean, float* var,
+                       float* rstd, void* y_bf16, void* stream);
+int ceb_segment_bn_bwd(const void* dy_bf16, const void* x_bf16, const int64_t* seg, const float* samples, int64_t N,
+                       int L, int C, int S, const float* gamma, const float* mean, const float* rstd, float* sums,
+                       void* dx_bf16, void* stream);
 /* Classifier head + cross-entropy in one kernel: logits = scale * feat (bf16 [N][F]) @ W^T (fp32 [C][F]),
  * C <= 32, F % 64 == 0, F <= 2048.  g == NULL: forward, writes loss[N] and correct[N] (1.0 where the
  * arg-max equals the label).  g != NULL: backward of sum_s g[s] * loss[s]: writes dfeat (bf16 [N][F]) and

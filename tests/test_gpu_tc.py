@@ -439,3 +439,38 @@ def test_conv3x3_fused_residual(n, h, cin, cout):
     mask = torch.randn(n, h, h, cout, device=DEV, generator=g).bfloat16()
     masked = tc.conv3x3_nhwc_res(x, w, res, relu_mask=mask)
     assert torch.equal(masked, tc.conv3x3_nhwc(x, w, relu_mask=mask) + res)
+
+
+@pytest.mark.parametrize("sizes,C,H", [([8] * 16, 64, 32), ([3, 5, 1, 7], 128, 8), ([2, 2, 2], 72, 5), ([6] * 4, 256, 4)])
+def test_segment_batchnorm_native_matches_reference(sizes, C, H):
+    """ceb_segment_bn_fwd / bwd vs per-client nn.BatchNorm2d in fp32."""
+    from commefficient_b200.ops import tfm
+    torch.manual_seed(C + H)
+    N, S = sum(sizes), len(sizes)
+    x = (torch.randn(N, C, H, H, device=DEV) * 1.5 + 0.3).bfloat16().contiguous(memory_format=torch.channels_last)
+    x.requires_grad_(True)
+    w = torch.nn.Parameter(torch.randn(C, device=DEV) * 0.2 + 1.0)
+    b = torch.nn.Parameter(torch.randn(C, device=DEV) * 0.2)
+    seg = torch.repeat_interleave(torch.arange(S, device=DEV), torch.tensor(sizes, device=DEV))
+    samples = torch.tensor(sizes, device=DEV, dtype=torch.float32)
+    assert tfm.segment_bn_supported(x, seg, samples)
+    y, mean, var = tfm.segment_batch_norm(x, w, b, seg, samples, S, 1e-5)
+    assert y.is_contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(N, C, H, H, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+    y.backward(dy)
+
+    xr = x.detach().float().requires_grad_(True)
+    ref = torch.nn.BatchNorm2d(C).to(DEV)
+    with torch.no_grad():
+        ref.weight.copy_(w)
+        ref.bias.copy_(b)
+    bounds = [0]
+    for n_ in sizes:
+        bounds.append(bounds[-1] + n_)
+    yr = torch.cat([ref(xr[a:c]) for a, c in zip(bounds[:-1], bounds[1:])])
+    yr.backward(dy.float())
+    assert _rel_err(y, yr) < 1e-2
+    mr = torch.stack([xr[a:c].mean(dim=(0, 2, 3)) for a, c in zip(bounds[:-1], bounds[1:])])
+    torch.testing.assert_close(mean, mr.detach(), rtol=1e-3, atol=1e-3)
+    assert _rel_err(x.grad, xr.grad) < 2e-2
+    assert _rel_err(w.grad, ref.weight.grad) < 1e-2 and _rel_err(b.grad, ref.bias.grad) < 1e-2
