@@ -309,3 +309,27 @@ def test_segment_batchnorm_unequal_segments():
     torch.testing.assert_close(y, ys, rtol=1e-5, atol=1e-5)
     torch.testing.assert_close(x.grad, xs.grad, rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=1e-4, atol=1e-4)
+
+
+def test_round_is_invariant_to_sample_order_in_the_batch():
+    """FedModel groups samples by client id itself: a batch whose samples arrive interleaved gives the same
+    per-client results and the same update as the sorted batch (sorted fast path vs general path)."""
+    batch = synthetic_image_batch(4, 3, seed=5, first_client=4)
+    perm = torch.randperm(batch[0].numel(), generator=torch.Generator().manual_seed(0))
+    shuffled = tuple(t[perm] for t in batch)
+
+    def run(b):
+        fed, opt, _ = _make("sketch")
+        fed.train(True)
+        out = fed(b)
+        opt.step()
+        w = fed.fp.flat.clone()
+        fed.rt.shutdown()
+        return out, w
+
+    (loss_a, acc_a, dl_a, ul_a), w_a = run(batch)
+    (loss_b, acc_b, dl_b, ul_b), w_b = run(shuffled)
+    np.testing.assert_allclose(np.asarray(loss_a), np.asarray(loss_b), rtol=1e-5)
+    np.testing.assert_allclose(np.asarray(acc_a), np.asarray(acc_b))
+    torch.testing.assert_close(w_a, w_b, rtol=1e-5, atol=1e-6)
+    assert torch.equal(torch.as_tensor(ul_a), torch.as_tensor(ul_b))
