@@ -143,9 +143,18 @@ class GPT2Model(nn.Module):
         if token_type_ids is not None:
             x = x + self.wte(token_type_ids)
         x = self.drop(x)
-        for block in self.h:
-            x = block(x)
-        return nnops.layer_norm(x, self.ln_f.weight, self.ln_f.bias, self.ln_f.eps)
+        # Same math as ``for block in self.h: x = block(x)`` followed by ln_f, regrouped so that every
+        # residual add is fused with the LayerNorm that consumes its result (ops/nn.py:add_layer_norm):
+        # x + attn(ln_1(x)) feeds ln_2 of the same block, x + mlp(ln_2(x)) feeds ln_1 of the next block
+        # (or ln_f after the last one).
+        blocks = list(self.h)
+        first = blocks[0].ln_1 if blocks else self.ln_f
+        h = nnops.layer_norm(x, first.weight, first.bias, first.eps)
+        for i, block in enumerate(blocks):
+            x, h = nnops.add_layer_norm(x, block.attn(h), block.ln_2.weight, block.ln_2.bias, block.ln_2.eps)
+            nxt = blocks[i + 1].ln_1 if i + 1 < len(blocks) else self.ln_f
+            x, h = nnops.add_layer_norm(x, block.mlp(h), nxt.weight, nxt.bias, nxt.eps)
+        return h
 
 
 class SequenceSummary(nn.Module):

@@ -63,6 +63,17 @@ def layer_norm(x, weight, bias, eps=1e-5):
     return F.layer_norm(x, (x.shape[-1],), weight, bias, eps)
 
 
+def add_layer_norm(resid, branch, weight, bias, eps=1e-5):
+    """``(resid + branch, LayerNorm(resid + branch))`` -- the residual add fused into the LayerNorm that
+    follows it (native path: one kernel each way, ``ops/tfm.py:_AddLayerNorm``)."""
+    if (_use_native(resid) and weight.is_cuda and resid.dtype == torch.float32
+            and resid.shape[-1] in (128, 256, 512, 768, 1024, 1280)):
+        from . import tfm
+        return tfm.add_layer_norm(resid, branch, weight, bias, eps)
+    new_resid = resid + branch
+    return new_resid, layer_norm(new_resid, weight, bias, eps)
+
+
 def gelu_tanh(x):
     if _use_native(x) and x.numel() % 2 == 0:
         from . import tfm

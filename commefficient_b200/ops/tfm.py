@@ -18,6 +18,12 @@ native.register_signatures({
     "ceb_layernorm_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
                            native.c_ptr, native.c_ptr, native.c_i64, native.c_i32, native.c_ptr], native.c_i32),
     "ceb_gelu_bf16": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr], native.c_i32),
+    "ceb_add_layernorm_fwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                               native.c_ptr, native.c_ptr, native.c_i64, native.c_i32, native.c_f32, native.c_ptr],
+                              native.c_i32),
+    "ceb_add_layernorm_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                               native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32,
+                               native.c_ptr], native.c_i32),
     "ceb_segment_bn_fwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32, native.c_i32,
                             native.c_i32, native.c_ptr, native.c_ptr, native.c_f32, native.c_ptr, native.c_ptr,
                             native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr], native.c_i32),
@@ -171,3 +177,58 @@ def segment_bn_supported(x, seg, samples) -> bool:
 
 def segment_batch_norm(x, weight, bias, seg, samples, segments, eps):
     return _SegmentBNNative.apply(x, weight, bias, seg.contiguous(), samples.contiguous(), segments, eps)
+
+
+ADD_LN_WIDTHS = (128, 256, 512, 768, 1024, 1280)
+
+
+class _AddLayerNorm(torch.autograd.Function):
+    """``new_resid = resid + branch`` (fp32 stream + bf16 branch) and ``y = LayerNorm(new_resid)`` in one
+    kernel; the backward folds the gradient arriving through the residual stream into the LayerNorm
+    backward and emits it once in fp32 (for the stream) and once in bf16 (for the branch)."""
+
+    @staticmethod
+    def forward(ctx, resid, branch, weight, bias, eps):
+        E = resid.shape[-1]
+        r2 = resid.reshape(-1, E).float().contiguous()
+        b2 = branch.reshape(-1, E).to(torch.bfloat16).contiguous()
+        rows = r2.shape[0]
+        dev = resid.device
+        new_resid = torch.empty_like(r2)
+        y = torch.empty((rows, E), dtype=torch.bfloat16, device=dev)
+        mean = torch.empty(rows, dtype=torch.float32, device=dev)
+        rstd = torch.empty(rows, dtype=torch.float32, device=dev)
+        w = weight.detach().float().contiguous()
+        b = bias.detach().float().contiguous()
+        native.call("ceb_add_layernorm_fwd", native.ptr(r2), native.ptr(b2), native.ptr(w), native.ptr(b),
+                    native.ptr(new_resid), native.ptr(y), native.ptr(mean), native.ptr(rstd), rows, E, float(eps),
+                    native.stream_ptr(dev))
+        ctx.save_for_backward(new_resid, w, mean, rstd)
+        ctx.shape, ctx.branch_dtype, ctx.params = resid.shape, branch.dtype, (weight, bias)
+        return new_resid.view(resid.shape), y.view(resid.shape)
+
+    @staticmethod
+    def backward(ctx, d_resid, dy):
+        new_resid, w, mean, rstd = ctx.saved_tensors
+        rows, E = new_resid.shape
+        dev = new_resid.device
+        weight, bias = ctx.params
+        if dy is None:
+            dy = torch.zeros((rows, E), dtype=torch.bfloat16, device=dev)
+        dyb = dy.reshape(rows, E).to(torch.bfloat16).contiguous()
+        dres = d_resid.reshape(rows, E).float().contiguous() if d_resid is not None else None
+        dx = torch.empty_like(new_resid)
+        dxb = torch.empty((rows, E), dtype=torch.bfloat16, device=dev)
+        direct = (isinstance(weight, torch.nn.Parameter) and weight.grad is not None and bias.grad is not None
+                  and weight.grad.is_contiguous() and bias.grad.is_contiguous())
+        dg = weight.grad if direct else torch.zeros(E, dtype=torch.float32, device=dev)
+        db = bias.grad if direct else torch.zeros(E, dtype=torch.float32, device=dev)
+        native.call("ceb_add_layernorm_bwd", native.ptr(dyb), native.ptr(new_resid), native.ptr(w), native.ptr(mean),
+                    native.ptr(rstd), native.ptr(dres), native.ptr(dx), native.ptr(dxb), native.ptr(dg), native.ptr(db),
+                    rows, E, native.stream_ptr(dev))
+        return (dx.view(ctx.shape), dxb.view(ctx.shape).to(ctx.branch_dtype), (None if direct else dg),
+                (None if direct else db), None)
+
+
+def add_layer_norm(resid, branch, weight, bias, eps):
+    return _AddLayerNorm.apply(resid, branch, weight, bias, eps)

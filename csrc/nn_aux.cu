@@ -187,11 +187,19 @@ CEB_API int ceb_softmax_ce_bwd_rows(const void* logits_bf16, void* dlogits_bf16,
 __global__ void __launch_bounds__(256)
 ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
               __nv_bfloat16* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd, int64_t rows,
-              int E, float eps) {
+              int E, float eps, const __nv_bfloat16* __restrict__ branch, float* __restrict__ resid_out) {
   const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
   const float* xr = x + row * E;
+  if (branch) {
+    // fused residual add: resid_out = x + branch (the new fp32 residual stream), normalised below
+    const __nv_bfloat16* br = branch + row * E;
+    float* ro = resid_out + row * E;
+    for (int j = lane; j < E; j += 32) ro[j] = xr[j] + __bfloat162float(br[j]);
+    __syncwarp();
+    xr = ro;
+  }
   float s = 0.f, ss = 0.f;
   for (int j = lane; j < E; j += 32) { const float v = xr[j]; s += v; ss = fmaf(v, v, ss); }
   s = warp_sum(s); ss = warp_sum(ss);
@@ -244,7 +252,21 @@ CEB_API int ceb_layernorm_fwd(const float* x, const float* gamma, const float* b
                               float* rstd, int64_t rows, int E, float eps, void* stream) {
   CEB_REQUIRE(x && gamma && beta && y_bf16 && mean && rstd && rows > 0 && E > 0, "ceb_layernorm_fwd: bad arguments");
   ln_fwd_kernel<<<(unsigned)ceb_cdiv(rows, 8), 256, 0, (cudaStream_t)stream>>>(x, gamma, beta, (__nv_bfloat16*)y_bf16,
-                                                                                mean, rstd, rows, E, eps);
+                                                                                mean, rstd, rows, E, eps, nullptr, nullptr);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Residual add fused into the LayerNorm that follows it: resid_out (fp32) = x (fp32) + branch (bf16),
+// y (bf16) = LayerNorm(resid_out).  One pass instead of an add kernel plus a LayerNorm kernel.
+CEB_API int ceb_add_layernorm_fwd(const float* x, const void* branch_bf16, const float* gamma, const float* beta,
+                                  float* resid_out, void* y_bf16, float* mean, float* rstd, int64_t rows, int E,
+                                  float eps, void* stream) {
+  CEB_REQUIRE(x && branch_bf16 && gamma && beta && resid_out && y_bf16 && mean && rstd && rows > 0 && E > 0,
+              "ceb_add_layernorm_fwd: bad arguments");
+  ln_fwd_kernel<<<(unsigned)ceb_cdiv(rows, 8), 256, 0, (cudaStream_t)stream>>>(
+      x, gamma, beta, (__nv_bfloat16*)y_bf16, mean, rstd, rows, E, eps, (const __nv_bfloat16*)branch_bf16, resid_out);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -258,7 +280,8 @@ template <int G>
 __global__ void __launch_bounds__(256)
 ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
                   const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dx,
-                  float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t rows) {
+                  float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t rows,
+                  const float* __restrict__ dres, __nv_bfloat16* __restrict__ dx_bf16) {
   constexpr int E = 128 * G;
   __shared__ float sh[2 * E];
   for (int j = threadIdx.x; j < 2 * E; j += blockDim.x) sh[j] = 0.f;
@@ -298,7 +321,16 @@ ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict_
       o.y = rs * (d[g].y * gam[g].y - a - xh[g].y * b);
       o.z = rs * (d[g].z * gam[g].z - a - xh[g].z * b);
       o.w = rs * (d[g].w * gam[g].w - a - xh[g].w * b);
+      if (dres) {      // gradient arriving through the residual stream joins here (fused add)
+        const float4 r4 = *(const float4*)(dres + row * E + g * 128 + lane * 4);
+        o.x += r4.x; o.y += r4.y; o.z += r4.z; o.w += r4.w;
+      }
       *(float4*)(dx + row * E + g * 128 + lane * 4) = o;
+      if (dx_bf16) {   // the same gradient for the bf16 branch that was added to the stream
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+        uint2 pk; pk.x = *(const uint32_t*)&lo; pk.y = *(const uint32_t*)&hi;
+        *(uint2*)(dx_bf16 + row * E + g * 128 + lane * 4) = pk;
+      }
       ag[g].x = fmaf(d[g].x, xh[g].x, ag[g].x); ag[g].y = fmaf(d[g].y, xh[g].y, ag[g].y);
       ag[g].z = fmaf(d[g].z, xh[g].z, ag[g].z); ag[g].w = fmaf(d[g].w, xh[g].w, ag[g].w);
       ab[g].x += d[g].x; ab[g].y += d[g].y; ab[g].z += d[g].z; ab[g].w += d[g].w;
@@ -320,10 +352,42 @@ ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict_
 
 template <int G>
 static void launch_ln_bwd_vec(const void* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
-                              float* dx, float* dgamma, float* dbeta, int64_t rows, cudaStream_t st) {
+                              float* dx, float* dgamma, float* dbeta, int64_t rows, cudaStream_t st,
+                              const float* dres = nullptr, void* dx_bf16 = nullptr) {
   int blocks = ceb_num_sms() * 2;
   if (blocks > ceb_cdiv(rows, 8)) blocks = (int)ceb_cdiv(rows, 8);
-  ln_bwd_vec_kernel<G><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows);
+  ln_bwd_vec_kernel<G><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows,
+                                              dres, (__nv_bfloat16*)dx_bf16);
+}
+
+static bool ln_vec_width(int E) { return E == 128 || E == 256 || E == 512 || E == 768 || E == 1024 || E == 1280; }
+
+template <typename... A>
+static void dispatch_ln_bwd_vec(int E, A... args) {
+  switch (E / 128) {
+    case 1: launch_ln_bwd_vec<1>(args...); break;
+    case 2: launch_ln_bwd_vec<2>(args...); break;
+    case 4: launch_ln_bwd_vec<4>(args...); break;
+    case 6: launch_ln_bwd_vec<6>(args...); break;
+    case 8: launch_ln_bwd_vec<8>(args...); break;
+    default: launch_ln_bwd_vec<10>(args...); break;
+  }
+}
+
+// Backward of ceb_add_layernorm_fwd: dx (fp32) = LayerNorm-backward(dy) + dres (the gradient that reaches the
+// residual stream from later layers; may be NULL), dx_bf16 = the same values in bf16 (gradient of the added
+// branch); dgamma / dbeta accumulated.  E must be one of 128, 256, 512, 768, 1024, 1280.
+CEB_API int ceb_add_layernorm_bwd(const void* dy_bf16, const float* resid, const float* gamma, const float* mean,
+                                  const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
+                                  float* dbeta, int64_t rows, int E, void* stream) {
+  CEB_REQUIRE(dy_bf16 && resid && gamma && mean && rstd && dx && dgamma && dbeta && rows > 0, "ceb_add_layernorm_bwd: bad arguments");
+  CEB_REQUIRE(ln_vec_width(E), "ceb_add_layernorm_bwd: unsupported width E=%d", E);
+  CEB_REQUIRE(((((uintptr_t)dy_bf16) | ((uintptr_t)resid) | ((uintptr_t)dx) | ((uintptr_t)gamma) | ((uintptr_t)dres) |
+                ((uintptr_t)dx_bf16)) & 15) == 0, "ceb_add_layernorm_bwd: tensors must be 16-byte aligned");
+  dispatch_ln_bwd_vec(E, dy_bf16, resid, gamma, mean, rstd, dx, dgamma, dbeta, rows, (cudaStream_t)stream, dres, dx_bf16);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
 }
 
 // dgamma / dbeta are accumulated (+=)

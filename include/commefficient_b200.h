@@ -231,6 +231,16 @@ int ceb_layernorm_fwd(const float* x, const float* gamma, const float* beta, voi
                       float* rstd, int64_t rows, int E, float eps, void* stream);
 int ceb_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, const float* mean, const float* rstd,
                       float* dx, float* dgamma, float* dbeta, int64_t rows, int E, void* stream);
+/* Residual add fused with the LayerNorm that follows it: resid_out (fp32) = x (fp32) + branch (bf16),
+ * y = LayerNorm(resid_out); the backward adds the gradient arriving through the residual stream (dres,
+ * may be NULL) and also emits the total in bf16 for the branch (dx_bf16, may be NULL).
+ * bwd: E in {128, 256, 512, 768, 1024, 1280}, 16-byte aligned tensors. */
+int ceb_add_layernorm_fwd(const float* x, const void* branch_bf16, const float* gamma, const float* beta,
+                          float* resid_out, void* y_bf16, float* mean, float* rstd, int64_t rows, int E, float eps,
+                          void* stream);
+int ceb_add_layernorm_bwd(const void* dy_bf16, const float* resid, const float* gamma, const float* mean,
+                          const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma, float* dbeta,
+                          int64_t rows, int E, void* stream);
 /* tanh-GELU on bf16: out = gelu(x) (dy NULL) or dy * gelu'(x). */
 int ceb_gelu_bf16(const void* x, const void* dy, void* out, int64_t n, void* stream);
 /* Segment-wise BatchNorm (training mode) over NHWC bf16 activations x [N][L][C], C % 8 == 0: sample n

@@ -181,3 +181,22 @@ def test_accumulate_range_cpu_oracle():
     for lo, hi in ((0, 10), (10, 600), (600, 1000)):
         sk.accumulate_range(plan, parts, g, lo, hi)
     torch.testing.assert_close(parts, full)
+
+
+def test_gpt2_regrouped_forward_equals_blockwise_forward():
+    """GPT2Model.forward fuses every residual add with the following LayerNorm; it must equal the textbook
+    ``for block: x = block(x)`` + ln_f formulation."""
+    from commefficient_b200 import models
+    import torch.nn.functional as F
+    torch.manual_seed(0)
+    cfg = models.GPT2Config(vocab_size=97, n_positions=32, n_ctx=32, n_embd=32, n_layer=3, n_head=4,
+                            resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0, summary_first_dropout=0.0)
+    m = models.GPT2DoubleHeadsModel(cfg).eval()
+    tr = m.transformer
+    ids = torch.randint(0, 97, (3, 20))
+    got = tr(ids, ids)
+    x = tr.wte(ids) + tr.wpe(torch.arange(20)) + tr.wte(ids)
+    for block in tr.h:
+        x = block(x)
+    want = F.layer_norm(x, (32,), tr.ln_f.weight, tr.ln_f.bias, tr.ln_f.eps)
+    torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-5)

@@ -474,3 +474,39 @@ def test_segment_batchnorm_native_matches_reference(sizes, C, H):
     torch.testing.assert_close(mean, mr.detach(), rtol=1e-3, atol=1e-3)
     assert _rel_err(x.grad, xr.grad) < 2e-2
     assert _rel_err(w.grad, ref.weight.grad) < 1e-2 and _rel_err(b.grad, ref.bias.grad) < 1e-2
+
+
+@pytest.mark.parametrize("E", [128, 768, 1024])
+def test_add_layer_norm_fused_matches_torch(E):
+    from commefficient_b200.ops import tfm
+    torch.manual_seed(E)
+    rows = 333
+    resid = torch.randn(rows, E, device=DEV, requires_grad=True)
+    branch = torch.randn(rows, E, device=DEV).bfloat16().requires_grad_(True)
+    ln = torch.nn.LayerNorm(E).to(DEV)
+    torch.nn.init.normal_(ln.weight, 1.0, 0.1)
+    torch.nn.init.normal_(ln.bias, 0.0, 0.1)
+    new_resid, y = tfm.add_layer_norm(resid, branch, ln.weight, ln.bias, ln.eps)
+    d_res = torch.randn(rows, E, device=DEV)
+    dy = torch.randn(rows, E, device=DEV).bfloat16()
+    torch.autograd.backward([new_resid, y], [d_res, dy])
+
+    r2 = resid.detach().clone().requires_grad_(True)
+    b2 = branch.detach().float().requires_grad_(True)
+    ln2 = torch.nn.LayerNorm(E).to(DEV)
+    ln2.load_state_dict(ln.state_dict())
+    nr = r2 + b2
+    y2 = ln2(nr)
+    torch.autograd.backward([nr, y2], [d_res, dy.float()])
+    torch.testing.assert_close(new_resid, nr.detach(), rtol=1e-6, atol=1e-6)
+    assert _rel_err(y, y2) < 5e-3
+    assert _rel_err(resid.grad, r2.grad) < 1e-3
+    assert _rel_err(branch.grad, b2.grad) < 5e-3
+    assert _rel_err(ln.weight.grad, ln2.weight.grad) < 1e-3 and _rel_err(ln.bias.grad, ln2.bias.grad) < 1e-3
+    # no gradient through the residual output (the last add of the network)
+    resid.grad = None
+    nr3, y3 = tfm.add_layer_norm(resid, branch, ln.weight, ln.bias, ln.eps)
+    y3.backward(dy)
+    r2.grad = None
+    ln2(r2 + b2.detach()).backward(dy.float())
+    assert _rel_err(resid.grad, r2.grad) < 1e-3
