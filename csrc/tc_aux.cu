@@ -327,37 +327,51 @@ CEB_API int ceb_relu_bwd_bf16(const void* y, const void* dy, void* dz, int64_t n
 // K = 64: forward  y = relu(A * W0pad^T)  (ceb_gemm_bf16_tn), weight gradient  dW0pad += dZ^T * A
 // (ceb_gemm_bf16_mn_acc).  8 threads per pixel, 8 columns each: a warp writes four full rows.
 //   x: [N,H,W,3] fp32 (channels_last view of the NCHW batch); column t = (r*3+s)*3 + ci.
+// Block = 32 consecutive pixels of one image row x 8 column groups.  The three input rows the pixels'
+// windows touch (with a one-pixel halo, zero outside the image) are staged in shared memory with
+// coalesced loads; every thread then assembles its 8 output columns from there.
 __global__ void __launch_bounds__(256)
 im2col3x3_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ A, int N, int H, int W) {
-  const int g = threadIdx.x & 7;
-  const int64_t npix = (int64_t)N * H * W;
-  const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 3);
-  for (int64_t p = (int64_t)blockIdx.x * (blockDim.x >> 3) + (threadIdx.x >> 3); p < npix; p += stride) {
-    const int wq = (int)(p % W);
-    const int hq = (int)((p / W) % H);
-    const int64_t nb = p / ((int64_t)W * H);
-    float v[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int t = g * 8 + j;
-      float val = 0.f;
-      if (t < 27) {
-        const int tap = t / 3, ci = t - tap * 3;
-        const int hh = hq + tap / 3 - 1, wc = wq + tap % 3 - 1;
-        if (hh >= 0 && hh < H && wc >= 0 && wc < W) val = __ldg(x + ((nb * H + hh) * W + wc) * 3 + ci);
-      }
-      v[j] = val;
-    }
-    *reinterpret_cast<uint4*>(A + p * 64 + g * 8) = pack8(v);
+  __shared__ float rows[3][(32 + 2) * 3];
+  const int segs = (W + 31) / 32;                          // 32-pixel segments per image row
+  const int64_t blk = blockIdx.x;
+  const int seg = (int)(blk % segs);
+  const int hq = (int)((blk / segs) % H);
+  const int64_t nb = blk / ((int64_t)segs * H);
+  const int w0 = seg * 32;
+  for (int i = threadIdx.x; i < 3 * 34 * 3; i += blockDim.x) {
+    const int r = i / (34 * 3), rem = i - r * (34 * 3);
+    const int px = rem / 3, ci = rem - px * 3;
+    const int hh = hq + r - 1, wc = w0 + px - 1;
+    float v = 0.f;
+    if (hh >= 0 && hh < H && wc >= 0 && wc < W) v = __ldg(x + ((nb * H + hh) * W + wc) * 3 + ci);
+    rows[r][rem] = v;
   }
+  __syncthreads();
+  const int g = threadIdx.x & 7, pl = threadIdx.x >> 3;
+  const int wq = w0 + pl;
+  if (wq >= W) return;
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int t = g * 8 + j;                               // column (r*3 + s)*3 + ci
+    float val = 0.f;
+    if (t < 27) {
+      const int r = t / 9, rem = t - r * 9;                // rem = s*3 + ci: 9 consecutive floats of the row
+      val = rows[r][pl * 3 + rem];
+    }
+    v[j] = val;
+  }
+  const int64_t p = (nb * H + hq) * W + wq;
+  *reinterpret_cast<uint4*>(A + p * 64 + g * 8) = pack8(v);
 }
 
 // A[N*H*W][64] (bf16) = im2col of the 3x3 / pad 1 neighbourhoods of x[N,H,W,3] (fp32)
 CEB_API int ceb_im2col3x3_c3(const float* x_nhwc, void* A_bf16, int N, int H, int W, void* stream) {
   CEB_REQUIRE(x_nhwc && A_bf16 && N > 0 && H > 0 && W > 0, "ceb_im2col3x3_c3: bad arguments");
-  const int64_t npix = (int64_t)N * H * W;
-  im2col3x3_c3_kernel<<<ceb_grid_for(npix * 8, 256, 8), 256, 0, (cudaStream_t)stream>>>(
-      x_nhwc, (__nv_bfloat16*)A_bf16, N, H, W);
+  const int64_t blocks = (int64_t)N * H * ((W + 31) / 32);
+  CEB_REQUIRE(blocks < (1ll << 31), "ceb_im2col3x3_c3: batch too large");
+  im2col3x3_c3_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x_nhwc, (__nv_bfloat16*)A_bf16, N, H, W);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
