@@ -30,3 +30,19 @@ def _fresh_runtime():
     rt = runtime.get_runtime()
     if rt is not None:
         rt.shutdown()
+
+
+@pytest.fixture(autouse=True)
+def _deterministic_cpu_tests(request):
+    """CPU tests draw their random inputs from a per-test seed, so a rare unlucky draw (e.g. a heavy
+    hitter that lands next to zero) cannot fail a run that stops at the first failure.  GPU tests keep
+    their own generators / seeds."""
+    if "gpu" not in request.keywords:
+        import zlib
+
+        import numpy as np
+        import torch
+        seed = zlib.crc32(request.node.nodeid.encode()) & 0x7FFFFFFF
+        torch.manual_seed(seed)
+        np.random.seed(seed % (2 ** 32))
+    yield
