@@ -24,8 +24,9 @@ def _fed_run(device, mode, backend, rounds=3, **kw):
                 local_momentum=0.0, virtual_momentum=0.9, flat_layout="reference", backend=backend,
                 error_type="virtual" if mode in ("sketch", "true_topk") else "none")
     base.update(kw)
+    bn = base.pop("bn", False)
     args = make_args(**base)
-    model = models.ResNet9(num_classes=10, channels=SMALL)
+    model = models.ResNet9(num_classes=10, channels=SMALL, do_batchnorm=bn)
     fed = FedModel(model, compute_loss_train, args, compute_loss_val)
     opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
     opt.param_groups[0]["lr"] = 0.05
@@ -66,6 +67,18 @@ def test_gloo_two_ranks_match_single_rank(mode, kw):
     fed.rt.shutdown()
     np.testing.assert_allclose(ranks[0]["losses"], l1, rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(ranks[0]["val"], v1, rtol=1e-4, atol=1e-5)
+    assert (ranks[0]["w"] - w1).norm() / w1.norm() < 1e-3
+
+
+def test_gloo_two_ranks_batchnorm_model_matches_single_rank():
+    """A BatchNorm model on two ranks: every rank batches its own clients with segment-wise BN statistics;
+    the result equals the single-rank run (which batches all six clients) and the replicas stay identical."""
+    ranks = _spawn(2, "cpu", "uncompressed", "gloo", bn=True)
+    torch.testing.assert_close(ranks[0]["w"], ranks[1]["w"], rtol=0, atol=0)
+    w1, l1, _v1, fed = _fed_run("cpu", "uncompressed", "auto", bn=True)
+    assert fed.worker.has_bn and fed.worker.can_batch_clients([4] * 6)
+    fed.rt.shutdown()
+    np.testing.assert_allclose(ranks[0]["losses"], l1, rtol=1e-4, atol=1e-5)
     assert (ranks[0]["w"] - w1).norm() / w1.norm() < 1e-3
 
 
