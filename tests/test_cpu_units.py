@@ -200,3 +200,26 @@ def test_gpt2_regrouped_forward_equals_blockwise_forward():
         x = block(x)
     want = F.layer_norm(x, (32,), tr.ln_f.weight, tr.ln_f.bias, tr.ln_f.eps)
     torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-5)
+
+
+def test_gpt2_label_sparse_loss_equals_full_logits_loss():
+    """need_logits=False scores only through lm_rows; on any device it must equal the loss computed
+    from the full logits (and the MC loss is untouched)."""
+    from commefficient_b200 import models
+    cfg = models.GPT2Config(vocab_size=101, n_positions=32, n_ctx=32, n_embd=32, n_layer=2, n_head=4,
+                            resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0, summary_first_dropout=0.0)
+    m = models.GPT2DoubleHeadsModel(cfg).eval()
+    ids = torch.randint(0, 101, (3, 2, 16))
+    labels = ids.clone()
+    labels[:, 0] = -1
+    labels[:, 1, :9] = -1
+    mc_tok = torch.full((3, 2), 15)
+    mc_lab = torch.tensor([1, 0, 1])
+    full = m(ids, token_type_ids=ids, mc_token_ids=mc_tok, lm_labels=labels, mc_labels=mc_lab)
+    sparse = m(ids, token_type_ids=ids, mc_token_ids=mc_tok, lm_labels=labels, mc_labels=mc_lab, need_logits=False,
+               return_hidden=True)
+    assert sparse[2] is None and sparse[-1].shape == (6, 16, 32)
+    torch.testing.assert_close(sparse[0], full[0], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(sparse[1], full[1])
+    rows, mask = m.lm_rows(sparse[-1], labels)
+    assert int(mask.sum()) == 3 * 7 and bool((rows[~mask] == 0).all())      # labels 9..15 -> 7 scored positions
