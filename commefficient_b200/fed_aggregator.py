@@ -33,6 +33,7 @@ from .ops import sketch as sk
 from .ops.topk import topk_sparse
 from .parallel.runtime import Runtime, init_runtime
 from .parallel.watchdog import RoundWatchdog, maybe_inject, parse_fault
+from .utils import graphs
 from .utils.logging import PhaseTracer
 from .utils.flat import get_param_vec, set_param_vec  # noqa: F401  (re-exported, reference names)
 
@@ -696,10 +697,9 @@ class FedOptimizer(torch.optim.Optimizer):
         tr = fm.tracker
         st = self._tail
         st["calls"] += 1
-        if st["graph"] is None and st["calls"] <= 2:
+        if st.get("eager_only") or (st["graph"] is None and st["calls"] <= 2):
             self.last_update = self._sketch_tail(plan, src, lr, tr.record_sparse)
             return
-        from .ops import native
         if st["lr"] is None:
             st["lr"] = torch.zeros(1, dtype=torch.float32, device=fm.device)
         tr.host_advance()                              # may re-allocate the histogram (generation changes)
@@ -707,16 +707,20 @@ class FedOptimizer(torch.optim.Optimizer):
             tr.round -= 1
             tr.sync_round_dev()                        # device round = rounds applied so far
             tr.round += 1
-            torch.cuda.synchronize(fm.device)
-            before = native.launch_count()
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                st["out"] = self._sketch_tail(plan, src, st["lr"], tr.record_sparse_graph)
-            st.update(graph=graph, gen=tr.generation, src=src.data_ptr(), native=native.launch_count() - before)
+            # (no eager warm-up on the capture stream: the tail mutates the server state, and it is
+            # native kernels only -- nothing in it creates stream-keyed library handles)
+            cap = graphs.try_capture(
+                fm.device, lambda: self._sketch_tail(plan, src, st["lr"], tr.record_sparse_graph),
+                what="sketch server tail", warmup=False)
+            if cap is None:
+                st["eager_only"] = True
+                st["graph"] = None
+                tr.round -= 1                          # record_sparse advances the round itself
+                self.last_update = self._sketch_tail(plan, src, lr, tr.record_sparse)
+                return
+            st.update(graph=cap, gen=tr.generation, src=src.data_ptr())
         st["lr"].fill_(lr)
-        st["graph"].replay()
-        native.add_launch_count(st["native"])
-        self.last_update = st["out"]
+        self.last_update = st["graph"].replay()
 
     def _step_fused(self, inv_n, rho, lr) -> bool:
         """Peer-memory path: the cross-rank reduce-scatter, the momentum/error (or momentum +

@@ -30,6 +30,7 @@ import torch
 from .ops import dense as dn
 from .ops import sketch as sk
 from .ops.topk import topk_sparse
+from .utils import graphs
 from .utils.flat import FlatParams
 
 
@@ -305,7 +306,7 @@ class ClientWorker:
         if args.do_topk_down:
             self.client_weights = ClientStateStore((self.d,), self.device, init=self.fp.flat.clone())
         self._ps_copy = None
-        self._graphs = {}
+        self._graphs = graphs.GraphCache()
         self.has_bn = _has_batchnorm(model)
         self.bn_segmentable = self.has_bn and _bn_segmentable(model)
         # tensor-core layers: hand-written tcgen05 kernels on CUDA unless switched off
@@ -387,11 +388,8 @@ class ClientWorker:
             return self._batched_body(self._prep(cat), sizes, None)
         key = (sizes,) + tuple((tuple(t.shape), t.dtype) for t in cat)
         entry = self._graphs.get(key)
-        if entry is None:
-            entry = {"calls": 0, "graph": None}
-            self._graphs[key] = entry
         entry["calls"] += 1
-        if entry["graph"] is None and entry["calls"] <= 2:
+        if entry["eager_only"] or (entry["graph"] is None and entry["calls"] <= 2):
             return self._batched_body(self._prep(cat), sizes, None)          # eager warm-up rounds
         if entry["graph"] is None:
             entry["static_in"] = [torch.empty_like(t, memory_format=torch.channels_last)
@@ -402,21 +400,19 @@ class ClientWorker:
             entry["counts"] = torch.tensor(sizes, device=self.device, dtype=torch.float32).unsqueeze(1)
             for dst, src in zip(entry["static_in"], cat):
                 dst.copy_(src)
-            torch.cuda.synchronize(self.device)
-            from .ops import native
-            before = native.launch_count()
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                entry["results"] = self._batched_body(entry["static_in"], sizes, entry["seg"], entry["counts"])
-            entry["graph"] = graph
-            entry["native_launches"] = native.launch_count() - before   # our kernels inside the graph
+            entry["graph"] = graphs.try_capture(
+                self.device, lambda: self._batched_body(entry["static_in"], sizes, entry["seg"], entry["counts"]),
+                what="batched client round")
+            if entry["graph"] is None:
+                # capture is an optimisation: this shape stays eager (the reference always is)
+                entry["eager_only"] = True
+                self.fp.on_range_final = None
+                for k in ("static_in", "seg", "counts"):
+                    entry.pop(k, None)
+                return self._batched_body(self._prep(cat), sizes, None)
         for dst, src in zip(entry["static_in"], cat):
             dst.copy_(src, non_blocking=True)
-        entry["graph"].replay()
-        if entry.get("native_launches"):
-            from .ops import native
-            native.add_launch_count(entry["native_launches"])
-        return entry["results"]
+        return entry["graph"].replay()
 
     def _batched_body(self, cat, sizes, seg, counts=None):
         a, fp = self.args, self.fp
@@ -515,33 +511,28 @@ class ClientWorker:
         use_graph = (self.device.type == "cuda" and not getattr(a, "no_cuda_graphs", False) and not a.do_dp)
         if use_graph:
             key = ("client", bool(fold_weight_decay)) + tuple((tuple(t.shape), t.dtype) for t in batch)
-            entry = self._graphs.setdefault(key, {"calls": 0, "graph": None})
+            entry = self._graphs.get(key)
             entry["calls"] += 1
-            if entry["graph"] is None and entry["calls"] > 2:
+            if entry["graph"] is None and entry["calls"] > 2 and not entry["eager_only"]:
                 entry["static_in"] = [torch.empty_like(t, memory_format=torch.channels_last)
                                       if (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last)
                                           and not t.is_contiguous()) else torch.empty_like(t) for t in batch]
                 for dst, src in zip(entry["static_in"], batch):
                     dst.copy_(src)
-                torch.cuda.synchronize(self.device)
-                from .ops import native
-                before = native.launch_count()
-                graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph):
+
+                def body():
                     fp.zero_grad()
                     res, iters = _run_microbatches(self.model, entry["static_in"], self.compute_loss_train, a, True)
                     _finish_client_grad(fp, a, iters, fold_weight_decay=fold_weight_decay)
-                    entry["results"] = res
-                entry["graph"] = graph
-                entry["native_launches"] = native.launch_count() - before
+                    return res
+                entry["graph"] = graphs.try_capture(self.device, body, what="per-client backward")
+                if entry["graph"] is None:
+                    entry["eager_only"] = True
+                    entry.pop("static_in", None)
             if entry["graph"] is not None:
                 for dst, src in zip(entry["static_in"], batch):
                     dst.copy_(src, non_blocking=True)
-                entry["graph"].replay()
-                if entry.get("native_launches"):
-                    from .ops import native
-                    native.add_launch_count(entry["native_launches"])
-                return entry["results"].clone()
+                return entry["graph"].replay().clone()
         fp.zero_grad()
         results, num_iters = _run_microbatches(self.model, batch, self.compute_loss_train, a, True)
         _finish_client_grad(fp, a, num_iters, fold_weight_decay=fold_weight_decay)

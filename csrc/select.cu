@@ -24,66 +24,142 @@ CEB_API void ceb_add_launch_count(unsigned long long n) { g_ceb_launches += n; }
 CEB_API int ceb_version() { return 1; }
 CEB_API int64_t ceb_select_scratch_bytes() { return (int64_t)sizeof(CebSelectScratch); }
 
-// Final pass: write every entry above the threshold, plus exactly k3 entries equal to it (first
-// come first served -- which ties win is unspecified, as with torch.topk).  Two sweeps over the
-// block's slice: count, reserve a contiguous output range with ONE global atomic per block, then
-// write (a single output counter hammered by every warp serialises at the L2).
+// Final pass, deterministic: the output is the k selected entries in ASCENDING INDEX ORDER -- first
+// every entry above the threshold (k - k3 of them), then the k3 LOWEST-INDEX entries equal to it.
+// Which of several equal-magnitude entries at the threshold win is therefore a function of the data
+// alone, never of thread timing: replicas that run the same select on the same vector pick the same
+// set (the multi-GPU design relies on that; torch.topk leaves it unspecified).
+// Two kernels over identical contiguous per-block slices: (1) count entries above / equal to the
+// threshold per block, (2) every block sums the counts of the blocks before it and writes its entries
+// at their exact ranks.  Loads are 16-byte vectors; in-block ranks come from a warp scan + a 16-entry
+// warp-total table per iteration.
+struct SelSlice { int64_t begin, end; };
+__device__ __forceinline__ SelSlice sel_slice(int64_t n) {
+  const int64_t per_block = ((n + gridDim.x - 1) / gridDim.x + 3) & ~(int64_t)3;
+  SelSlice s;
+  s.begin = (int64_t)blockIdx.x * per_block;
+  s.end = s.begin + per_block < n ? s.begin + per_block : n;
+  if (s.begin > n) s.begin = n;
+  return s;
+}
+__device__ __forceinline__ void sel_load4(const float* __restrict__ v, int64_t i, int64_t end, bool vec, float (&x)[4]) {
+  if (vec && i + 3 < end) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(v + i));
+    x[0] = t.x; x[1] = t.y; x[2] = t.z; x[3] = t.w;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) x[j] = (i + j < end) ? __ldg(v + i + j) : 0.f;
+  }
+}
+
+__global__ void __launch_bounds__(kSelThreads)
+sel_count_kernel(const float* __restrict__ v, int64_t n, CebSelectScratch* __restrict__ s) {
+  __shared__ uint32_t sh_gt, sh_eq;
+  const uint32_t T = (s->b1 << 19) | (s->b2 << 8) | s->b3;
+  const SelSlice sl = sel_slice(n);
+  const bool vec = (((uintptr_t)v) & 15) == 0;
+  if (threadIdx.x == 0) { sh_gt = 0; sh_eq = 0; }
+  __syncthreads();
+  uint32_t gt = 0, eq = 0;
+  for (int64_t i = sl.begin + (int64_t)threadIdx.x * 4; i < sl.end; i += (int64_t)blockDim.x * 4) {
+    float x[4];
+    sel_load4(v, i, sl.end, vec, x);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (i + j < sl.end) {
+        const uint32_t key = abs_key(x[j]);
+        gt += key > T;
+        eq += key == T;
+      }
+    }
+  }
+  gt = __reduce_add_sync(0xffffffffu, gt);
+  eq = __reduce_add_sync(0xffffffffu, eq);
+  if ((threadIdx.x & 31) == 0) {
+    if (gt) atomicAdd(&sh_gt, gt);
+    if (eq) atomicAdd(&sh_eq, eq);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) { s->blk_gt[blockIdx.x] = sh_gt; s->blk_eq[blockIdx.x] = sh_eq; }
+}
+
 __global__ void __launch_bounds__(kSelThreads)
 sel_emit_kernel(const float* __restrict__ v, int64_t n, CebSelectScratch* __restrict__ s,
-                int32_t* __restrict__ out_idx, float* __restrict__ out_val, uint32_t k) {
-  __shared__ uint32_t blk_count, blk_base, blk_fill;
+                int32_t* __restrict__ out_idx, float* __restrict__ out_val, uint32_t k, int64_t idx_offset) {
+  __shared__ uint32_t base_sh[2];
+  __shared__ uint32_t wtot[2][kSelThreads / 32];      // per-warp (gt | eq << 16) totals, double buffered
   const uint32_t T = (s->b1 << 19) | (s->b2 << 8) | s->b3;
   const uint32_t need = s->k3;
-  const int lane = threadIdx.x & 31;
-  // contiguous slice per block so both sweeps hit the same (L2-resident) data
-  const int64_t per_block = ((n + gridDim.x - 1) / gridDim.x + 31) & ~(int64_t)31;
-  const int64_t begin = (int64_t)blockIdx.x * per_block;
-  const int64_t end = begin + per_block < n ? begin + per_block : n;
-  if (threadIdx.x == 0) { blk_count = 0; blk_fill = 0; }
+  const uint32_t first_tie_pos = k - need;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const SelSlice sl = sel_slice(n);
+  const bool vec = (((uintptr_t)v) & 15) == 0;
+  if (warp == 0) {
+    uint32_t g = 0, e = 0;
+    for (int b = lane; b < (int)blockIdx.x; b += 32) { g += s->blk_gt[b]; e += s->blk_eq[b]; }
+    g = __reduce_add_sync(0xffffffffu, g);
+    e = __reduce_add_sync(0xffffffffu, e);
+    if (lane == 0) { base_sh[0] = g; base_sh[1] = e; }
+  }
   __syncthreads();
-  uint32_t mine = 0;
-  for (int64_t i = begin + threadIdx.x; i < end; i += blockDim.x) mine += abs_key(__ldg(v + i)) > T;
-  mine = __reduce_add_sync(0xffffffffu, mine);
-  if (lane == 0 && mine) atomicAdd(&blk_count, mine);
-  __syncthreads();
-  if (threadIdx.x == 0) blk_base = blk_count ? atomicAdd(&s->out_count, blk_count) : 0u;
-  __syncthreads();
-  const uint32_t base = blk_base;
-  for (int64_t i0 = begin + (threadIdx.x - lane); i0 < end; i0 += blockDim.x) {
-    const int64_t i = i0 + lane;
-    float val = 0.f;
-    uint32_t key = 0;
-    const bool valid = i < end;
-    if (valid) {
-      val = __ldg(v + i);
-      key = abs_key(val);
-    }
-    const bool gt = valid && key > T;
-    const unsigned m = __ballot_sync(0xffffffffu, gt);
-    if (m) {
-      uint32_t wbase = 0;
-      const int leader = __ffs(m) - 1;
-      if (lane == leader) wbase = atomicAdd(&blk_fill, (uint32_t)__popc(m));
-      wbase = __shfl_sync(0xffffffffu, wbase, leader);
-      if (gt) {
-        const uint32_t pos = base + wbase + __popc(m & ((1u << lane) - 1u));
-        if (pos < k) { out_idx[pos] = (int32_t)i; out_val[pos] = val; }
+  uint32_t run_gt = base_sh[0], run_eq = base_sh[1];
+  int buf = 0;
+  // uniform trip count: every thread of the block takes part in every iteration's barrier
+  for (int64_t i0 = sl.begin; i0 < sl.end; i0 += (int64_t)blockDim.x * 4, buf ^= 1) {
+    const int64_t i = i0 + (int64_t)threadIdx.x * 4;
+    float x[4] = {0.f, 0.f, 0.f, 0.f};
+    uint32_t fg = 0, fe = 0;                           // 4-bit flags
+    if (i < sl.end) {
+      sel_load4(v, i, sl.end, vec, x);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (i + j < sl.end) {
+          const uint32_t key = abs_key(x[j]);
+          fg |= (uint32_t)(key > T) << j;
+          fe |= (uint32_t)(key == T) << j;
+        }
       }
     }
-    // ties at the threshold: few (or all zeros); each takes a ticket until the quota is gone
-    if (valid && key == T && *((volatile uint32_t*)&s->tie_taken) < need) {
-      const uint32_t ticket = atomicAdd(&s->tie_taken, 1u);
-      if (ticket < need) {
-        const uint32_t pos = atomicAdd(&s->out_count, 1u);
-        if (pos < k) { out_idx[pos] = (int32_t)i; out_val[pos] = (key == 0u) ? 0.f : val; }
+    const uint32_t mine = (uint32_t)__popc(fg) | ((uint32_t)__popc(fe) << 16);
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += up;
+    }
+    if (lane == 31) wtot[buf][warp] = incl;
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w2 = 0; w2 < kSelThreads / 32; ++w2) {
+      const uint32_t t = wtot[buf][w2];
+      total += t;
+      if (w2 < warp) before += t;
+    }
+    uint32_t excl = before + incl - mine;
+    uint32_t pg = run_gt + (excl & 0xffffu), pe = run_eq + (excl >> 16);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (fg & (1u << j)) {
+        if (pg < k) { out_idx[pg] = (int32_t)(i + j + idx_offset); out_val[pg] = x[j]; }
+        ++pg;
+      } else if (fe & (1u << j)) {
+        if (pe < need) {
+          const uint32_t pos = first_tie_pos + pe;
+          if (pos < k) { out_idx[pos] = (int32_t)(i + j + idx_offset); out_val[pos] = (T == 0u) ? 0.f : x[j]; }
+        }
+        ++pe;
       }
     }
+    run_gt += total & 0xffffu;
+    run_eq += total >> 16;
   }
 }
 
 int ceb_select_run(const float* v, int64_t n, int64_t k, CebSelectScratch* s, int32_t* out_idx,
                    float* out_val, bool pass1_done, cudaStream_t stream) {
-  const int grid = ceb_grid_for(n, kSelThreads, 4);
+  int grid = ceb_grid_for(n, kSelThreads, 4);
+  if (grid > kSelMaxBlocks) grid = kSelMaxBlocks;
   if (!pass1_done) {
     CEB_CHECK_CUDA(cudaMemsetAsync(s, 0, sizeof(CebSelectScratch), stream));
     sel_hist_kernel<1><<<grid, kSelThreads, 0, stream>>>(v, n, s, (uint32_t)k);
@@ -91,8 +167,10 @@ int ceb_select_run(const float* v, int64_t n, int64_t k, CebSelectScratch* s, in
   }
   sel_hist_kernel<2><<<grid, kSelThreads, 0, stream>>>(v, n, s, (uint32_t)k);
   sel_hist_kernel<3><<<grid, kSelThreads, 0, stream>>>(v, n, s, (uint32_t)k);
-  sel_emit_kernel<<<grid, kSelThreads, 0, stream>>>(v, n, s, out_idx, out_val, (uint32_t)k);
-  CEB_COUNT_LAUNCH(3);
+  const int egrid = (int)(ceb_cdiv(n, kSelThreads * 4) < grid ? ceb_cdiv(n, kSelThreads * 4) : grid);
+  sel_count_kernel<<<egrid, kSelThreads, 0, stream>>>(v, n, s);
+  sel_emit_kernel<<<egrid, kSelThreads, 0, stream>>>(v, n, s, out_idx, out_val, (uint32_t)k, 0);
+  CEB_COUNT_LAUNCH(4);
   CEB_CHECK_LAUNCH();
   return 0;
 }

@@ -8,6 +8,8 @@
 #pragma once
 #include "common.cuh"
 
+constexpr int kSelMaxBlocks = 1024;
+
 struct CebSelectScratch {
   uint32_t hist1[4096];   // digit 1: key >> 19
   uint32_t hist2[2048];   // digit 2: (key >> 8) & 0x7ff, only keys whose digit 1 == b1
@@ -16,9 +18,12 @@ struct CebSelectScratch {
   uint32_t b1, k1;        // chosen bin of pass 1, how many still to find inside it
   uint32_t b2, k2;
   uint32_t b3, k3;        // k3 = number of keys equal to the threshold to take
-  uint32_t out_count;     // entries written so far
-  uint32_t tie_taken;     // tickets handed out to keys == threshold
+  uint32_t out_count;     // (unused by the ordered emit; kept for layout stability)
+  uint32_t tie_taken;
   uint32_t pad[4];
+  // ordered emit: entries above / equal to the threshold in every block's slice of the vector
+  uint32_t blk_gt[kSelMaxBlocks];
+  uint32_t blk_eq[kSelMaxBlocks];
 };
 
 static_assert(sizeof(CebSelectScratch) % 16 == 0, "scratch must stay 16B aligned");

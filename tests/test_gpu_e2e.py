@@ -169,3 +169,27 @@ def test_batchnorm_model_batched_graph_round_on_gpu():
     # (TF32 convolutions pick different algorithms for the two batch shapes and 6-sample BatchNorm amplifies
     # the rounding; the exact equivalence is asserted in fp32 on the CPU, tests/test_features_cpu.py)
     assert float((w_b - w_c).norm() / w_c.norm()) < 1e-2
+
+
+@pytest.mark.parametrize("mode,kw", [("sketch", {}), ("local_topk", {"error_type": "local", "local_momentum": 0.9})])
+def test_capture_failure_falls_back_to_eager(mode, kw):
+    """A CUDA-graph capture that fails (forced here) must not take the round down: the shape is marked
+    eager-only and training gives the same result as with graphs switched off."""
+    import warnings
+
+    from commefficient_b200.utils import graphs
+    w_ref, l_ref, _ = _run("cuda", mode, rounds=5, no_cuda_graphs=True, **kw)
+    graphs.FORCE_FAIL = True
+    graphs._WARNED.clear()
+    try:
+        with warnings.catch_warnings(record=True) as caught:
+            warnings.simplefilter("always")
+            w_f, l_f, _ = _run("cuda", mode, rounds=5, **kw)
+    finally:
+        graphs.FORCE_FAIL = False
+    assert any("capture" in str(c.message) for c in caught), "the fallback must say so once"
+    np.testing.assert_allclose(l_f, l_ref, rtol=1e-4, atol=1e-4)
+    assert float((w_f - w_ref).norm() / w_ref.norm()) < (5e-2 if mode == "sketch" else 1e-4)
+    # and graphs still work afterwards
+    w_g, l_g, _ = _run("cuda", mode, rounds=5, **kw)
+    np.testing.assert_allclose(l_g, l_ref, rtol=1e-3, atol=1e-3)
