@@ -270,6 +270,8 @@ def main(argv=None):
     schedule = PiecewiseLinear([0, args.pivot_epoch, args.num_epochs], [0, args.lr_scale, 0])
     spe = steps_per_epoch(args.local_batch_size, train_loader.dataset, args.num_workers)
     lr_scheduler = LambdaLR(opt, lr_lambda=lambda step: schedule(step / spe))
+    if args.resume:
+        fed_model.restore_scheduler(lr_scheduler)
 
     writer = None
     if args.use_tensorboard and is_main:
@@ -281,10 +283,12 @@ def main(argv=None):
     summary = train(fed_model, opt, lr_scheduler, train_loader, test_loader, args, writer,
                     loggers=(TableLogger(),), timer=timer, is_main=is_main)
     fed_model.finalize()
-    if args.do_checkpoint and is_main:
+    if args.do_checkpoint:
         os.makedirs(args.checkpoint_path, exist_ok=True)
-        torch.save(fed_model.state_dict(), os.path.join(args.checkpoint_path, args.model + ".pt"))
-        fed_model.save_fedstate(os.path.join(args.checkpoint_path, args.model + ".fedstate.pt"), opt)
+        if is_main:
+            torch.save(fed_model.state_dict(), os.path.join(args.checkpoint_path, args.model + ".pt"))
+        # every rank writes its own sidecar (server-state shard + the client rows it owns)
+        fed_model.save_fedstate(os.path.join(args.checkpoint_path, args.model + ".fedstate.pt"), opt, lr_scheduler)
     rt.shutdown()
     return summary
 

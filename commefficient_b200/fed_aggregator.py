@@ -516,7 +516,7 @@ class FedModel:
         return [out[:, i].copy() for i in range(args.num_results_val)]
 
     # -- resume sidecar ----------------------------------------------------
-    def fedstate(self, opt: "FedOptimizer"):
+    def fedstate(self, opt: "FedOptimizer", scheduler=None):
         w = self.worker
         return {
             "weights": self.fp.flat.detach().cpu(),
@@ -529,19 +529,34 @@ class FedModel:
             "client_errors": None if w.errors is None else w.errors.state_dict(),
             "client_weights": None if w.client_weights is None else w.client_weights.state_dict(),
             "torch_rng": torch.random.get_rng_state(), "numpy_rng": np.random.get_state(),
+            # what the flat vectors mean: a state saved under one layout / world size / sharding must not be
+            # loaded under another (conv weights would be silently permuted, shards misplaced)
+            "flat_layout": self.fp.layout, "numel": int(self.fp.numel), "world_size": self.rt.world_size,
+            "rank": self.rt.rank, "shard": (int(opt.shard_lo), int(opt.shard_hi)), "mode": self.args.mode,
+            "sched_step": None if scheduler is None else int(scheduler.last_epoch),
         }
 
-    def save_fedstate(self, path, opt: "FedOptimizer"):
-        path = "%s.rank%d" % (path, self.rt.rank) if self.rt.world_size > 1 else path
-        torch.save(self.fedstate(opt), path)
+    def _fedstate_path(self, path):
+        return "%s.rank%d" % (path, self.rt.rank) if self.rt.world_size > 1 else path
 
-    def load_fedstate(self, path, opt: "FedOptimizer"):
-        path = "%s.rank%d" % (path, self.rt.rank) if self.rt.world_size > 1 else path
-        st = torch.load(path, map_location="cpu", weights_only=False)
+    def save_fedstate(self, path, opt: "FedOptimizer", scheduler=None):
+        """Resume sidecar.  EVERY rank must call this: with more than one rank each writes
+        ``<path>.rank<r>`` (its Vvelocity shard and the per-client rows it owns live nowhere else)."""
+        torch.save(self.fedstate(opt, scheduler), self._fedstate_path(path))
+        self.rt.barrier()
+
+    def load_fedstate(self, path, opt: "FedOptimizer", scheduler=None):
+        st = torch.load(self._fedstate_path(path), map_location="cpu", weights_only=False)
+        for key, have in (("flat_layout", self.fp.layout), ("numel", int(self.fp.numel)),
+                          ("world_size", self.rt.world_size), ("mode", self.args.mode)):
+            if key in st and st[key] != have:
+                raise ValueError("resume state %s was saved with %s=%r, this run has %r"
+                                 % (path, key, st[key], have))
         self.fp.flat.copy_(st["weights"].to(self.device))
         opt.Vvelocity.copy_(st["Vvelocity"].to(self.device))
         opt.Verror.copy_(st["Verror"].to(self.device))
         self.rounds, self.fedavg_lr = st["rounds"], st["fedavg_lr"]
+        self.worker.round_no = int(st["rounds"])
         tr = st["tracker"]
         self.tracker.round, self.tracker.seen = tr["round"], tr["seen"]
         self.tracker.hist = tr["hist"].to(self.device)
@@ -555,6 +570,22 @@ class FedModel:
                 store.load_state_dict(st[key])
         torch.random.set_rng_state(st["torch_rng"])
         np.random.set_state(st["numpy_rng"])
+        self.resumed_sched_step = st.get("sched_step")
+        if scheduler is not None:
+            self.restore_scheduler(scheduler)
+
+    def restore_scheduler(self, scheduler):
+        """Put a ``LambdaLR`` back at the step the sidecar was saved at (the drivers build the
+        scheduler after loading the state); without this the learning rate would restart at 0."""
+        step = getattr(self, "resumed_sched_step", None)
+        if step is None:
+            return
+        scheduler.last_epoch = int(step)
+        lrs = []
+        for group, base, lmbda in zip(scheduler.optimizer.param_groups, scheduler.base_lrs, scheduler.lr_lambdas):
+            group["lr"] = base * lmbda(int(step))
+            lrs.append(group["lr"])
+        scheduler._last_lr = lrs
 
 
 class FedOptimizer(torch.optim.Optimizer):

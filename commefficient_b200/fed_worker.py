@@ -231,9 +231,22 @@ def forward_grad(model, batch, compute_loss, args, compute_grad=True):
     return fp.grad, results
 
 
-def _finish_client_grad(fp: FlatParams, args, num_iters: int, fold_weight_decay: bool = True):
+def noise_seed(seed: int, client_id: int, round_no: int) -> int:
+    """Philox seed of one client's DP noise in one round: a 63-bit mix (splitmix64 finaliser) of the run
+    seed, the client id and the round.  Every (client, round) pair gets its own stream whatever rank it
+    runs on; the reference draws independent noise in each worker process (fed_worker.py:304-309)."""
+    z = (int(seed) * 0x9E3779B97F4A7C15 + (int(client_id) + 1) * 0xBF58476D1CE4E5B9
+         + (int(round_no) + 1) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+    return (z ^ (z >> 31)) & 0x7FFFFFFFFFFFFFFF
+
+
+def _finish_client_grad(fp: FlatParams, args, num_iters: int, fold_weight_decay: bool = True, noise_key=None):
     """Per-client post-processing of the flat gradient, in the reference's order:
-    norm clip (non-sketch modes), weight decay / W (quirk Q7), DP clip + noise."""
+    norm clip (non-sketch modes), weight decay / W (quirk Q7), DP clip + noise.  ``noise_key`` =
+    ``(client_id, round)`` selects the noise stream; callers without one (the reference-shaped
+    ``forward_grad``) get a per-process, per-rank call counter instead."""
     g = fp.grad
     if args.max_grad_norm is not None and args.mode != "sketch":
         factor = num_iters if getattr(args, "compat_microbatch_sum", False) else 1
@@ -243,9 +256,13 @@ def _finish_client_grad(fp: FlatParams, args, num_iters: int, fold_weight_decay:
     if args.do_dp:
         dn.clip_by_norm(g, args.l2_norm_clip, eps=0.0)
         if args.dp_mode == "worker" and args.noise_multiplier > 0:
-            _finish_client_grad.noise_calls += 1
+            if noise_key is None:
+                from .parallel import runtime as _rt
+                rt = _rt.get_runtime()
+                _finish_client_grad.noise_calls += 1
+                noise_key = (-2 - (rt.rank if rt is not None else 0), _finish_client_grad.noise_calls)
             dn.add_gaussian_noise(g, args.noise_multiplier * math.sqrt(args.num_workers),
-                                  seed=args.seed, offset=_finish_client_grad.noise_calls * (1 << 20))
+                                  seed=noise_seed(args.seed, noise_key[0], noise_key[1]), offset=0)
 
 
 _finish_client_grad.noise_calls = 0
@@ -313,6 +330,7 @@ class ClientWorker:
         from .ops import nn as nnops
         nnops.set_native(self.device.type == "cuda" and not getattr(args, "no_native_nn", False))
         self.last_clients: List[int] = []
+        self.round_no = 0                 # training rounds run so far (part of the DP noise stream id)
 
     def _prep(self, cols: Sequence[torch.Tensor]) -> List[torch.Tensor]:
         """Image batches go channels_last when the weights are stored NHWC, so cuDNN / the
@@ -347,6 +365,7 @@ class ClientWorker:
         if not isinstance(client_batches, ClientBatches):
             client_batches = ClientBatches.from_pairs(client_batches)
         self.transmit.zero_()
+        self.round_no += 1
         self.last_clients = list(client_batches.client_ids)
         if not client_batches:
             return torch.zeros((0, self.args.num_results_train), device=self.device)
@@ -500,7 +519,7 @@ class ClientWorker:
         self.fp.flat.copy_(new)
         return stale, new
 
-    def _client_backward(self, batch, fold_weight_decay=True):
+    def _client_backward(self, batch, fold_weight_decay=True, noise_key=None):
         """zero-grad + microbatched forward/backward + per-client gradient post-processing of ONE
         client.  On CUDA the sequence is captured into a CUDA graph per batch shape (after two
         eager rounds) and replayed: the per-client path is launch-bound (ResNet-18 on 8 images is
@@ -535,7 +554,7 @@ class ClientWorker:
                 return entry["graph"].replay().clone()
         fp.zero_grad()
         results, num_iters = _run_microbatches(self.model, batch, self.compute_loss_train, a, True)
-        _finish_client_grad(fp, a, num_iters, fold_weight_decay=fold_weight_decay)
+        _finish_client_grad(fp, a, num_iters, fold_weight_decay=fold_weight_decay, noise_key=noise_key)
         return results
 
     def _one_client(self, cid, batch):
@@ -545,7 +564,7 @@ class ClientWorker:
         if self.client_weights is not None:
             stale, new = self._client_weights_in(cid)
         sketch_fold = a.mode == "sketch" and not a.do_dp
-        results = self._client_backward(batch, fold_weight_decay=not sketch_fold)
+        results = self._client_backward(batch, fold_weight_decay=not sketch_fold, noise_key=(cid, self.round_no))
         if a.mode == "sketch":
             w = fp.flat if sketch_fold else None
             wd = a.weight_decay / a.num_workers if sketch_fold else 0.0
@@ -590,7 +609,7 @@ class ClientWorker:
             step, acc = 0, None
             for _epoch in range(a.num_fedavg_epochs):
                 for chunk in chunks:
-                    res = self._client_backward(chunk)
+                    res = self._client_backward(chunk, noise_key=(cid, self.round_no * 4096 + step))
                     fp.flat.add_(fp.grad, alpha=-float(lr) * a.fedavg_lr_decay ** step)
                     acc = res if acc is None else acc + res
                     step += 1

@@ -272,6 +272,8 @@ def train(argv=None):
     spe = steps_per_epoch(args.local_batch_size, train_loader.dataset, args.num_workers)
     schedule = PiecewiseLinear([0, args.num_epochs * spe], [args.lr_scale, 0.0])
     scheduler = LambdaLR(fed_opt, lr_lambda=lambda step: schedule(step))
+    if args.resume:
+        fed_model.restore_scheduler(scheduler)
     if is_main:
         print("Steps per epoch", spe)
     if args.do_finetune:
@@ -280,9 +282,9 @@ def train(argv=None):
         out = train_gpt2(fed_model, fed_opt, scheduler, train_loader, val_loader, args, log_dir, writer,
                          logger=TableLogger(), timer=timer, is_main=is_main)
     fed_model.finalize()
-    if args.do_checkpoint and is_main:
+    if args.do_checkpoint:
         os.makedirs(args.checkpoint_path, exist_ok=True)
-        fed_model.save_fedstate(os.path.join(args.checkpoint_path, "gpt2.fedstate.pt"), fed_opt)
+        fed_model.save_fedstate(os.path.join(args.checkpoint_path, "gpt2.fedstate.pt"), fed_opt, scheduler)
     rt.shutdown()
     return out
 

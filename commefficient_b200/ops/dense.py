@@ -157,7 +157,7 @@ def add_gaussian_noise(x: torch.Tensor, std: float, seed: int, offset: int = 0) 
     if std == 0:
         return
     if not x.is_cuda:
-        gen = torch.Generator().manual_seed(int(seed) * 1000003 + int(offset))
+        gen = torch.Generator().manual_seed((int(seed) * 1000003 + int(offset)) & 0x7FFFFFFFFFFFFFFF)
         x.add_(torch.normal(0.0, std, x.shape, generator=gen))
         return
     native.call("ceb_add_gaussian_noise", native.ptr(x), x.numel(), float(std), int(seed), int(offset),

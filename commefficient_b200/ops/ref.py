@@ -26,8 +26,18 @@ def topk_sparse_ref(vec: torch.Tensor, k: int) -> Tuple[torch.Tensor, torch.Tens
     k = min(int(k), vec.numel())
     mag = vec.detach().float().abs()
     mag = torch.where(torch.isnan(mag), torch.zeros_like(mag), mag)
-    _, idx = torch.topk(mag, k, sorted=False)
-    return idx, vec[idx]
+    if k == 0:
+        return torch.zeros(0, dtype=torch.long, device=vec.device), vec[:0]
+    # Deterministic rule shared with csrc/select.cu: everything above the k-th largest magnitude, then
+    # the LOWEST-INDEX entries equal to it; output in (above: ascending index, ties: ascending index).
+    thresh = torch.topk(mag, k, sorted=True).values[-1]
+    above = torch.nonzero(mag > thresh).flatten()
+    ties = torch.nonzero(mag == thresh).flatten()[: k - above.numel()]
+    idx = torch.cat([above, ties])
+    val = vec[idx]
+    if float(thresh) == 0.0:
+        val = torch.where(mag[idx] == 0, torch.zeros_like(val), val)     # NaN at magnitude 0 reads as 0
+    return idx, val
 
 
 def topk_dense_ref(vec: torch.Tensor, k: int) -> torch.Tensor:

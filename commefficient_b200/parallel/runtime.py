@@ -149,9 +149,12 @@ def init_runtime(args=None, rank: Optional[int] = None, world_size: Optional[int
             from .symm import PeerGroup
             rt.peer = PeerGroup(rt)
         except Exception as exc:  # fall back to NCCL but say so loudly
+            # (PeerGroup raises on EVERY rank when any rank fails -- its set-up exchanges a status with
+            # each step -- so all ranks take this branch together)
             import warnings
             warnings.warn("peer-memory backend unavailable (%s); using NCCL collectives" % (exc,))
             rt.backend = "nccl"
+            rt.peer = None
     _RUNTIME = rt
     return rt
 

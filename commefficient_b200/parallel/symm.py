@@ -47,22 +47,46 @@ class SymmBuffer:
         self.group = group
         self.numel = int(numel)
         itemsize = torch.empty((), dtype=dtype).element_size()
-        nbytes = max(256, self.numel * itemsize)
+        # the kernels work on whole 16-byte vectors: the allocation covers padded(numel) elements
+        nbytes = max(256, PeerGroup.padded(self.numel) * itemsize)
         hb = int(lib.ceb_peer_handle_bytes())
         handle = ctypes.create_string_buffer(hb)
         local = ctypes.c_void_p()
-        native.check(lib.ceb_peer_alloc(nbytes, ctypes.byref(local), handle), "ceb_peer_alloc")
-        self.local_ptr = int(local.value)
-        handles: List[Optional[bytes]] = [None] * group.world
-        dist.all_gather_object(handles, bytes(handle.raw))
+        # Failures must be COLLECTIVE: a rank that raised on its own would leave the others waiting in the
+        # exchange below (or, later, spinning on its flags).  Every step's status travels with the data.
+        err = None
+        try:
+            native.check(lib.ceb_peer_alloc(nbytes, ctypes.byref(local), handle), "ceb_peer_alloc")
+        except Exception as exc:      # noqa: BLE001
+            err = "rank %d: %s" % (group.rank, exc)
+        self.local_ptr = int(local.value or 0)
+        gathered: List[Optional[tuple]] = [None] * group.world
+        dist.all_gather_object(gathered, (err, bytes(handle.raw)))
+        errs = [e for e, _ in gathered if e]
+        if errs:
+            if err is None:
+                lib.ceb_peer_release(ctypes.c_void_p(self.local_ptr), 1)
+            raise RuntimeError("symmetric allocation failed: " + "; ".join(errs))
         self.ptrs: List[int] = []
-        for q, h in enumerate(handles):
+        for q, (_e, h) in enumerate(gathered):
             if q == group.rank:
                 self.ptrs.append(self.local_ptr)
                 continue
             p = ctypes.c_void_p()
-            native.check(lib.ceb_peer_open(ctypes.create_string_buffer(h, hb), ctypes.byref(p)), "ceb_peer_open")
-            self.ptrs.append(int(p.value))
+            try:
+                native.check(lib.ceb_peer_open(ctypes.create_string_buffer(h, hb), ctypes.byref(p)), "ceb_peer_open")
+            except Exception as exc:  # noqa: BLE001
+                err = "rank %d opening rank %d: %s" % (group.rank, q, exc)
+            self.ptrs.append(int(p.value or 0))
+        oks: List[Optional[str]] = [None] * group.world
+        dist.all_gather_object(oks, err)
+        errs = [e for e in oks if e]
+        if errs:
+            for q, p in enumerate(self.ptrs):
+                if q != group.rank and p:
+                    lib.ceb_peer_release(ctypes.c_void_p(p), 0)
+            lib.ceb_peer_release(ctypes.c_void_p(self.local_ptr), 1)
+            raise RuntimeError("mapping peer memory failed: " + "; ".join(errs))
         typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
         self.tensor = torch.as_tensor(_RawCuda(self.local_ptr, self.numel, typestr), device=group.device)
         self.ptr_array = (ctypes.c_void_p * group.world)(*self.ptrs)
@@ -92,9 +116,20 @@ class PeerGroup:
             raise RuntimeError("peer-memory collectives support at most %d ranks" % self.MAX_WORLD)
         self.rt = rt
         self.rank, self.world, self.device = rt.rank, rt.world_size, rt.device
-        for q in range(torch.cuda.device_count()):
-            if q != self.device.index and q < self.world and not torch.cuda.can_device_access_peer(self.device.index, q):
-                raise RuntimeError("GPU %d cannot access GPU %d over P2P" % (self.device.index, q))
+        err = None
+        try:
+            native.lib()
+            for q in range(torch.cuda.device_count()):
+                if q != self.device.index and q < self.world and \
+                        not torch.cuda.can_device_access_peer(self.device.index, q):
+                    err = "GPU %d cannot access GPU %d over P2P" % (self.device.index, q)
+        except Exception as exc:      # noqa: BLE001
+            err = "rank %d: %s" % (self.rank, exc)
+        errs: List[Optional[str]] = [None] * self.world
+        dist.all_gather_object(errs, err)             # every rank learns of any rank's failure
+        errs = [e for e in errs if e]
+        if errs:
+            raise RuntimeError("; ".join(errs))
         self.buffers: List[SymmBuffer] = []
         self.flags = self.symm_empty(64, torch.int32)
         self.ticket = torch.zeros(4, dtype=torch.int32, device=self.device)
@@ -141,6 +176,13 @@ class PeerGroup:
                 return self.all_reduce_buffer_(buf)
         n = t.numel()
         if self._staging is None or self._staging.numel < self.padded(n):
+            if self._staging is not None:
+                # every rank regrows at the same call (same sizes everywhere): nobody may still be reading
+                # the old mapping when it goes away
+                torch.cuda.synchronize(self.device)
+                dist.barrier(device_ids=[self.device.index])
+                self.buffers.remove(self._staging)
+                self._staging.close()
             self._staging = self.symm_empty(self.padded(n))
         stage = self._staging.tensor[:n]
         stage.copy_(t.reshape(-1))

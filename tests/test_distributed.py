@@ -165,3 +165,99 @@ def test_peer_backend_matches_nccl_backend(mode):
     torch.testing.assert_close(a[0]["w"], a[1]["w"], rtol=0, atol=0)            # replicas identical
     np.testing.assert_allclose(a[0]["losses"], b[0]["losses"], rtol=2e-3, atol=2e-3)
     assert (a[0]["w"] - b[0]["w"]).norm() / b[0]["w"].norm() < (5e-2 if mode != "uncompressed" else 1e-3)
+
+
+# --------------------------------------------------------------------------- resume sidecar on two ranks
+def _resume_main(rank, world, out_dir, phase):
+    from torch.optim.lr_scheduler import LambdaLR
+
+    from commefficient_b200 import models
+    from commefficient_b200.cv_train import compute_loss_train, compute_loss_val
+    from commefficient_b200.data_utils import synthetic_image_batch
+    from commefficient_b200.fed_aggregator import FedModel, FedOptimizer
+    from commefficient_b200.utils import make_args
+    rt = runtime.init_runtime(rank=rank, world_size=world, device="cpu", backend="gloo")
+    torch.manual_seed(0)
+    args = make_args(mode="local_topk", num_workers=4, num_clients=8, local_batch_size=-1, k=300, device="cpu",
+                     dataset_name="CIFAR10", precision="fp32", weight_decay=5e-4, local_momentum=0.9,
+                     virtual_momentum=0.9, flat_layout="reference", backend="gloo", error_type="local")
+    model = models.ResNet9(num_classes=10, channels=SMALL)
+    fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+    opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+    path = os.path.join(out_dir, "state.fedstate.pt")
+    if phase == "resume":
+        fed.load_fedstate(path, opt)
+    sched = LambdaLR(opt, lr_lambda=lambda step: 0.01 * (step + 1))
+    if phase == "resume":
+        fed.restore_scheduler(sched)
+
+    def rnd(step):
+        sched.step()
+        fed.train(True)
+        out = fed(synthetic_image_batch(4, 3, seed=step, first_client=(4 * step) % 8))
+        opt.step()
+        return float(np.mean(out[0]))
+
+    losses = []
+    if phase == "straight":
+        for s in range(2):
+            rnd(s)
+        fed.save_fedstate(path, opt, sched)           # every rank writes <path>.rank<r>
+        losses = [rnd(s) for s in (2, 3)]
+    else:
+        losses = [rnd(s) for s in (2, 3)]
+    torch.save({"losses": losses, "w": fed.fp.flat.clone(), "lr": opt.param_groups[0]["lr"]},
+               os.path.join(out_dir, "%s_r%d.pt" % (phase, rank)))
+    rt.shutdown()
+
+
+def test_resume_sidecar_two_ranks_roundtrip():
+    """Every rank saves and loads its own sidecar (client-state rows owned by client id mod world size, the
+    scheduler step, the flat layout): the resumed two-rank run continues exactly like the uninterrupted one."""
+    out_dir = tempfile.mkdtemp()
+    runtime.spawn(_resume_main, 2, args=(out_dir, "straight"), device="cpu")
+    assert all(os.path.exists(os.path.join(out_dir, "state.fedstate.pt.rank%d" % r)) for r in range(2))
+    runtime.spawn(_resume_main, 2, args=(out_dir, "resume"), device="cpu")
+    for r in range(2):
+        a = torch.load(os.path.join(out_dir, "straight_r%d.pt" % r))
+        b = torch.load(os.path.join(out_dir, "resume_r%d.pt" % r))
+        assert a["losses"] == pytest.approx(b["losses"], rel=1e-6)
+        torch.testing.assert_close(a["w"], b["w"])
+        assert a["lr"] == pytest.approx(b["lr"]) and a["lr"] == pytest.approx(0.01 * 5)
+
+
+def test_resume_sidecar_rejects_other_layout(tmp_path):
+    from tests.test_features_cpu import _make, _round
+    fed, opt, _ = _make("sketch")
+    _round(fed, opt, 0)
+    path = str(tmp_path / "s.pt")
+    fed.save_fedstate(path, opt)
+    st = torch.load(path, weights_only=False)
+    st["flat_layout"] = "nhwc"
+    torch.save(st, path)
+    with pytest.raises(ValueError, match="flat_layout"):
+        fed.load_fedstate(path, opt)
+    fed.rt.shutdown()
+
+
+# --------------------------------------------------------------------------- DP noise is independent per client
+def _dp_main(rank, world, out_dir):
+    from commefficient_b200 import fed_worker
+    from commefficient_b200.ops import dense as dn
+    rt = runtime.init_runtime(rank=rank, world_size=world, device="cpu", backend="gloo")
+    # the j-th client of every rank: same position in the rank's loop, different client id
+    x = torch.zeros(4096)
+    dn.add_gaussian_noise(x, 1.0, seed=fed_worker.noise_seed(5, client_id=10 + rank, round_no=3))
+    torch.save(x, os.path.join(out_dir, "n%d.pt" % rank))
+    rt.shutdown()
+
+
+def test_dp_noise_differs_across_ranks_and_rounds():
+    from commefficient_b200 import fed_worker
+    out_dir = tempfile.mkdtemp()
+    runtime.spawn(_dp_main, 2, args=(out_dir,), device="cpu")
+    a, b = (torch.load(os.path.join(out_dir, "n%d.pt" % r)) for r in range(2))
+    assert float((a - b).abs().max()) > 0.1 and abs(float(torch.corrcoef(torch.stack([a, b]))[0, 1])) < 0.1
+    assert float((a - b).std()) == pytest.approx(2 ** 0.5, rel=0.1)      # the difference does not cancel
+    seeds = {fed_worker.noise_seed(5, c, r) for c in range(50) for r in range(50)}
+    assert len(seeds) == 2500

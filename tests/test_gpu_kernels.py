@@ -47,6 +47,33 @@ def test_topk_select_ties_zeros_nan():
     assert idx.unique().numel() == 17 and bool((val == 1).all())
 
 
+@pytest.mark.parametrize("n,k,nties", [(5000, 40, 100), (1 << 20, 50000, 4000), (300007, 1000, 2500)])
+def test_topk_select_ties_are_lowest_index_and_output_is_ordered(n, k, nties):
+    """Entries equal to the threshold are taken in ascending index order (deterministic: replicas that
+    select on the same vector agree), the output lists the entries above the threshold and then the
+    ties, each in ascending index order -- and the CPU oracle follows the same rule."""
+    from commefficient_b200.ops.ref import topk_sparse_ref
+    g = torch.Generator(device=DEV).manual_seed(n)
+    v = torch.rand(n, device=DEV, generator=g) * 0.5
+    big = torch.randperm(n, device=DEV, generator=g)[: k - nties // 4]       # strictly above the ties
+    v[big] = 2.0 + torch.rand(big.numel(), device=DEV, generator=g)
+    tie_pos = torch.randperm(n, device=DEV, generator=g)[:nties]
+    tie_pos = tie_pos[~torch.isin(tie_pos, big)]
+    v[tie_pos] = 1.0
+    v[tie_pos[::2]] = -1.0
+    idx, val = topk_sparse(v, k)
+    n_above = big.numel()
+    want_ties = tie_pos.sort().values[: k - n_above]
+    assert torch.equal(idx[:n_above].long(), big.sort().values)
+    assert torch.equal(idx[n_above:].long(), want_ties)
+    assert torch.equal(val, v[idx.long()])
+    for _ in range(3):                                   # and the same answer every time
+        idx2, _ = topk_sparse(v, k)
+        assert torch.equal(idx, idx2)
+    ci, cv = topk_sparse_ref(v.cpu(), k)
+    assert torch.equal(ci, idx.cpu().long()) and torch.equal(cv, val.cpu())
+
+
 @pytest.mark.parametrize("d,c,r,nb", [(1000, 50, 3, 1), (1003, 97, 5, 20), (70001, 5000, 5, 20),
                                        (4096, 16, 1, 4), (50000, 1000, 8, 7), (30000, 999, 16, 3)])
 def test_sketch_accumulate_and_query(d, c, r, nb):
