@@ -329,6 +329,7 @@ class ClientWorker:
         # tensor-core layers: hand-written tcgen05 kernels on CUDA unless switched off
         from .ops import nn as nnops
         nnops.set_native(self.device.type == "cuda" and not getattr(args, "no_native_nn", False))
+        nnops.set_precision(getattr(args, "precision", "bf16"))
         self.last_clients: List[int] = []
         self.round_no = 0                 # training rounds run so far (part of the DP noise stream id)
 

@@ -17,6 +17,7 @@ import torch
 import torch.nn.functional as F
 
 _native = False
+_precision = "bf16"
 
 
 def set_native(flag: bool) -> None:
@@ -24,12 +25,43 @@ def set_native(flag: bool) -> None:
     _native = bool(flag)
 
 
+def set_precision(precision: str) -> None:
+    """``--precision``, honestly:
+      * ``bf16``: bf16 activations, tcgen05 ``kind::f16`` MMAs, fp32 accumulation (the fast path);
+      * ``tf32``: fp32 activations whose GEMM / convolution inputs the tensor cores read as TF32
+        (``kind::tf32``) -- the arithmetic the reference's fp32 convolutions get from cuDNN, whose
+        ``allow_tf32`` defaults to True; library fallbacks run with TF32 enabled as well;
+      * ``fp32``: IEEE fp32 everywhere: no tensor-core layer runs (there is no fp32 MMA), the library path
+        is used with TF32 switched OFF.
+    The bf16-I/O transformer kernels (LayerNorm, GELU, cross-entropy, segment BatchNorm) only run under
+    ``bf16``."""
+    global _precision
+    if precision not in ("bf16", "tf32", "fp32"):
+        raise ValueError("unknown precision %r" % (precision,))
+    _precision = precision
+    if precision != "fp32":
+        from . import tc
+        tc.set_precision(precision)
+    if torch.cuda.is_available():
+        tf = precision != "fp32"
+        torch.backends.cudnn.allow_tf32 = tf
+        torch.backends.cuda.matmul.allow_tf32 = tf
+
+
+def precision() -> str:
+    return _precision
+
+
 def native_enabled() -> bool:
-    return _native
+    return _native and _precision != "fp32"
 
 
 def _use_native(x: torch.Tensor) -> bool:
-    return _native and x.is_cuda
+    return _native and x.is_cuda and _precision != "fp32"
+
+
+def _use_native_bf16(x: torch.Tensor) -> bool:
+    return _use_native(x) and _precision == "bf16"
 
 
 def conv2d(x, weight, bias=None, stride=1, padding=0):
@@ -57,7 +89,7 @@ def linear(x, weight, bias=None):
 
 
 def layer_norm(x, weight, bias, eps=1e-5):
-    if _use_native(x) and weight.is_cuda:
+    if _use_native_bf16(x) and weight.is_cuda:
         from . import tfm
         return tfm.layer_norm(x, weight, bias, eps)
     return F.layer_norm(x, (x.shape[-1],), weight, bias, eps)
@@ -66,7 +98,7 @@ def layer_norm(x, weight, bias, eps=1e-5):
 def add_layer_norm(resid, branch, weight, bias, eps=1e-5):
     """``(resid + branch, LayerNorm(resid + branch))`` -- the residual add fused into the LayerNorm that
     follows it (native path: one kernel each way, ``ops/tfm.py:_AddLayerNorm``)."""
-    if (_use_native(resid) and weight.is_cuda and resid.dtype == torch.float32
+    if (_use_native_bf16(resid) and weight.is_cuda and resid.dtype == torch.float32
             and resid.shape[-1] in (128, 256, 512, 768, 1024, 1280)):
         from . import tfm
         return tfm.add_layer_norm(resid, branch, weight, bias, eps)
@@ -75,7 +107,7 @@ def add_layer_norm(resid, branch, weight, bias, eps=1e-5):
 
 
 def gelu_tanh(x):
-    if _use_native(x) and x.numel() % 2 == 0:
+    if _use_native_bf16(x) and x.numel() % 2 == 0:
         from . import tfm
         return tfm.gelu_tanh(x)
     return F.gelu(x, approximate="tanh")
@@ -83,7 +115,7 @@ def gelu_tanh(x):
 
 def cross_entropy_rows(logits, labels, ignore_index=-1):
     """Per-row cross-entropy (0 where ``labels == ignore_index``) of ``[rows, V]`` logits."""
-    if _use_native(logits) and logits.dtype == torch.bfloat16 and logits.dim() == 2 and logits.stride(1) == 1 \
+    if _use_native_bf16(logits) and logits.dtype == torch.bfloat16 and logits.dim() == 2 and logits.stride(1) == 1 \
             and logits.stride(0) % 2 == 0:
         from . import tfm
         return tfm.cross_entropy_rows(logits, labels, ignore_index)
@@ -93,7 +125,7 @@ def cross_entropy_rows(logits, labels, ignore_index=-1):
 def lm_head_cross_entropy(hidden2d, weight, labels, ignore_index=-1):
     """Per-row cross-entropy of ``hidden2d @ weight.T`` (0 where ``labels == ignore_index``).  Native
     path: one fused function that only computes the rows with a label (``ops/tc.py:_LMHeadCE``)."""
-    if _use_native(hidden2d):
+    if _use_native_bf16(hidden2d):
         from . import tc
         if tc.lm_head_supported(hidden2d, weight):
             return tc.lm_head_ce(hidden2d, weight, labels, ignore_index)
@@ -228,7 +260,7 @@ class BatchNorm2d(torch.nn.BatchNorm2d):
         if not (self.training and S > 1 and self.affine and (general or x.shape[0] % S == 0)):
             return super().forward(x)
         native_ok = False
-        if general and _use_native(x):
+        if general and _use_native_bf16(x):
             from . import tfm
             native_ok = tfm.segment_bn_supported(x, _bn_seg_ids, _bn_seg_counts)
         if native_ok:

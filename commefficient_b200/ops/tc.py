@@ -57,13 +57,60 @@ native.register_signatures({
                                  native.c_i64, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr], native.c_i32),
 })
 
+native.register_signatures({
+    "ceb_gemm_tf32_tn_ld": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i64,
+                             native.c_i32, native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
+                             native.c_ptr], native.c_i32),
+    "ceb_conv3x3_tf32_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
+                               native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_ptr, native.c_ptr,
+                               native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_conv3x3_wgrad_tf32_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
+                                     native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_gemm_tf32_mn_acc_ld": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i32,
+                                 native.c_i32, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_conv_weights_prepare_f32": ([native.c_i32, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                                      native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_maxpool_nhwc_f32": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32, native.c_i32,
+                              native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_maxpool_bwd_nhwc_f32": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
+                                  native.c_i32, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_relu_bwd_f32": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr], native.c_i32),
+    "ceb_im2col3x3": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32, native.c_i32,
+                       native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_linear_ce_head_f32": ([native.c_ptr, native.c_ptr, native.c_f32, native.c_ptr, native.c_i32, native.c_i32,
+                                native.c_i32, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                                native.c_ptr], native.c_i32),
+})
+
 _OUT = {torch.bfloat16: 0, torch.float32: 1}
+
+# Operand precision of the tensor-core layers (``--precision``): "bf16" -> bf16 activations and
+# tcgen05.mma.kind::f16; "tf32" -> fp32 activations read by the tensor cores as TF32 (kind::tf32), which is
+# what the reference's fp32 convolutions do inside cuDNN (torch.backends.cudnn.allow_tf32 defaults to True).
+# "fp32" never reaches this module: ops/nn.py keeps those runs on the library with TF32 switched off.
+_PRECISION = "bf16"
+
+
+def set_precision(p: str) -> None:
+    global _PRECISION
+    if p not in ("bf16", "tf32"):
+        raise ValueError("tensor-core layers run bf16 or tf32 operands, not %r" % (p,))
+    _PRECISION = p
+
+
+def act_dtype() -> torch.dtype:
+    return torch.float32 if _PRECISION == "tf32" else torch.bfloat16
+
+
+def _al(dtype) -> int:
+    """Elements per 16 bytes."""
+    return 4 if dtype == torch.float32 else 8
 
 
 def _rows_ok(t: torch.Tensor) -> bool:
-    """2-D bf16, unit column stride, 16-byte aligned rows (row stride a multiple of 8 elements)."""
-    return (t.dim() == 2 and t.dtype == torch.bfloat16 and t.stride(1) == 1 and t.stride(0) % 8 == 0
-            and t.stride(0) >= t.shape[1] and t.data_ptr() % 16 == 0)
+    """2-D bf16 / fp32, unit column stride, 16-byte aligned rows."""
+    return (t.dim() == 2 and t.dtype in (torch.bfloat16, torch.float32) and t.stride(1) == 1
+            and t.stride(0) % _al(t.dtype) == 0 and t.stride(0) >= t.shape[1] and t.data_ptr() % 16 == 0)
 
 
 def padded_empty(rows: int, cols: int, dtype, device) -> torch.Tensor:
@@ -79,16 +126,18 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias=None, relu=False, out_dtype=t
     """``act(a @ b.T + bias)`` with a ``[M, K]``, b ``[N, K]`` bf16 CUDA tensors whose rows are 16-byte
     aligned (row strides may exceed K).  N and K are arbitrary; when N is not a multiple of 8 the
     result is a ``[M, N]`` view of a row-padded buffer (see ``padded_empty``)."""
-    assert _rows_ok(a) and _rows_ok(b), "gemm_tn operands must be bf16 with 16-byte aligned rows"
+    assert _rows_ok(a) and _rows_ok(b) and a.dtype == b.dtype, "gemm_tn operands need 16-byte aligned rows"
     M, K = a.shape
     N, K2 = b.shape
     assert K == K2
+    tf = a.dtype == torch.float32
     if out is None:
-        out = padded_empty(M, N, out_dtype, a.device)
+        out = padded_empty(M, N, torch.float32 if tf else out_dtype, a.device)
     assert out.stride(1) == 1
     mode = 2 if accumulate else _OUT[out.dtype]
-    native.call("ceb_gemm_bf16_tn_ld", native.ptr(a), a.stride(0), native.ptr(b), b.stride(0), native.ptr(out),
-                out.stride(0), M, N, K, native.ptr(bias), 1 if relu else 0, mode, native.stream_ptr(a.device))
+    native.call("ceb_gemm_tf32_tn_ld" if tf else "ceb_gemm_bf16_tn_ld", native.ptr(a), a.stride(0), native.ptr(b),
+                b.stride(0), native.ptr(out), out.stride(0), M, N, K, native.ptr(bias), 1 if relu else 0, mode,
+                native.stream_ptr(a.device))
     return out
 
 
@@ -108,9 +157,15 @@ def conv3x3_nhwc(x: torch.Tensor, w: torch.Tensor, relu=False, out_dtype=torch.b
     """3x3 / stride 1 / pad 1 convolution.  ``x``: ``[N, H, W, Cin]`` bf16 contiguous, ``w``:
     ``[Cout, 3, 3, Cin]`` bf16 contiguous; returns ``[N, H, W, Cout]``.  ``relu_mask`` (same shape
     as the result): zero the result where the mask is <= 0 (ReLU backward fused into a dgrad)."""
-    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.is_contiguous() and w.is_contiguous()
+    assert x.dtype == w.dtype and x.is_contiguous() and w.is_contiguous()
     n, h, wd, cin = x.shape
     cout = w.shape[0]
+    if x.dtype == torch.float32:
+        y = torch.empty((n, h, wd, cout), dtype=torch.float32, device=x.device)
+        native.call("ceb_conv3x3_tf32_nhwc", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, None,
+                    1 if relu else 0, native.ptr(relu_mask), None, None, native.stream_ptr(x.device))
+        return y
+    assert x.dtype == torch.bfloat16
     y = torch.empty((n, h, wd, cout), dtype=out_dtype, device=x.device)
     native.call("ceb_conv3x3_bf16_nhwc", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, None,
                 1 if relu else 0, _OUT[out_dtype], native.ptr(relu_mask), native.stream_ptr(x.device))
@@ -120,20 +175,27 @@ def conv3x3_nhwc(x: torch.Tensor, w: torch.Tensor, relu=False, out_dtype=torch.b
 def conv3x3_nhwc_res(x, w, resid, relu=False, relu_mask=None, keep_pre_add=False):
     """``act(conv3x3(x, w)) + resid`` in one kernel (bf16).  ``keep_pre_add``: returns
     ``(act(conv), act(conv) + resid)`` -- the first is what a later ReLU backward masks with."""
-    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.is_contiguous() and w.is_contiguous()
+    assert x.dtype == w.dtype and x.is_contiguous() and w.is_contiguous()
     n, h, wd, cin = x.shape
     cout = w.shape[0]
-    assert resid.shape == (n, h, wd, cout) and resid.dtype == torch.bfloat16 and resid.is_contiguous()
-    y = torch.empty((n, h, wd, cout), dtype=torch.bfloat16, device=x.device)
+    assert resid.shape == (n, h, wd, cout) and resid.dtype == x.dtype and resid.is_contiguous()
+    y = torch.empty((n, h, wd, cout), dtype=x.dtype, device=x.device)
     y2 = torch.empty_like(y) if keep_pre_add else None
+    if x.dtype == torch.float32:
+        native.call("ceb_conv3x3_tf32_nhwc", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, None,
+                    1 if relu else 0, native.ptr(relu_mask), native.ptr(resid), native.ptr(y2),
+                    native.stream_ptr(x.device))
+        return (y, y2) if keep_pre_add else y
     native.call("ceb_conv3x3_bf16_nhwc_res", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, None,
                 1 if relu else 0, native.ptr(relu_mask), native.ptr(resid), native.ptr(y2), native.stream_ptr(x.device))
     return (y, y2) if keep_pre_add else y
 
 
-def dgrad_weights(w_krsc_f32: torch.Tensor) -> torch.Tensor:
-    """``[Cin][3][3][Cout]`` bf16 weights of the data-gradient convolution (rotated 180 deg, in/out
+def dgrad_weights(w_krsc_f32: torch.Tensor, dtype=torch.bfloat16) -> torch.Tensor:
+    """``[Cin][3][3][Cout]`` weights of the data-gradient convolution (rotated 180 deg, in/out
     swapped) from fp32 ``[Cout][3][3][Cin]``."""
+    if dtype == torch.float32:
+        return prepare_conv_weights([w_krsc_f32], want_cast=False, want_rot=True, dtype=torch.float32)[1][0]
     cout, _, _, cin = w_krsc_f32.shape
     out = torch.empty((cin, 3, 3, cout), dtype=torch.bfloat16, device=w_krsc_f32.device)
     native.call("ceb_conv_w_dgrad_layout", native.ptr(w_krsc_f32), native.ptr(out), cout, cin,
@@ -141,15 +203,21 @@ def dgrad_weights(w_krsc_f32: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def prepare_conv_weights(weights_krsc_f32, want_cast=True, want_rot=True):
-    """bf16 forward copies and data-gradient layouts (``dgrad_weights``) of a list of fp32
-    ``[Cout,3,3,Cin]`` conv weights in ONE launch.  Returns ``(casts, rots)`` (lists; None entries
-    where not requested)."""
+def prepare_conv_weights(weights_krsc_f32, want_cast=True, want_rot=True, dtype=torch.bfloat16):
+    """Forward copies (bf16 casts; with ``dtype=float32`` the fp32 weights are used IN PLACE when they are
+    16-byte aligned in the flat buffer, else copied) and data-gradient layouts (``dgrad_weights``) of a
+    list of fp32 ``[Cout,3,3,Cin]`` conv weights in ONE launch.  Returns ``(casts, rots)`` (lists; None
+    entries where not requested)."""
     import ctypes
     n = len(weights_krsc_f32)
     dev = weights_krsc_f32[0].device
-    casts = [torch.empty(w.shape, dtype=torch.bfloat16, device=dev) if want_cast else None for w in weights_krsc_f32]
-    rots = [torch.empty((w.shape[3], 3, 3, w.shape[0]), dtype=torch.bfloat16, device=dev) if want_rot else None
+    if dtype == torch.float32:
+        inplace = [w.data_ptr() % 16 == 0 for w in weights_krsc_f32]
+        casts = [None if (not want_cast or ok) else torch.empty(w.shape, dtype=dtype, device=dev)
+                 for w, ok in zip(weights_krsc_f32, inplace)]
+    else:
+        casts = [torch.empty(w.shape, dtype=dtype, device=dev) if want_cast else None for w in weights_krsc_f32]
+    rots = [torch.empty((w.shape[3], 3, 3, w.shape[0]), dtype=dtype, device=dev) if want_rot else None
             for w in weights_krsc_f32]
     PtrArr = ctypes.c_void_p * n
     IntArr = ctypes.c_int * n
@@ -158,9 +226,14 @@ def prepare_conv_weights(weights_krsc_f32, want_cast=True, want_rot=True):
     rot = PtrArr(*[(r.data_ptr() if r is not None else None) for r in rots])
     cout = IntArr(*[int(w.shape[0]) for w in weights_krsc_f32])
     cin = IntArr(*[int(w.shape[3]) for w in weights_krsc_f32])
-    native.call("ceb_conv_weights_prepare", n, ctypes.cast(src, ctypes.c_void_p), ctypes.cast(cst, ctypes.c_void_p),
+    if dtype == torch.float32 and not want_rot and all(c is None for c in casts):
+        return list(weights_krsc_f32) if want_cast else casts, rots          # nothing to launch
+    native.call("ceb_conv_weights_prepare_f32" if dtype == torch.float32 else "ceb_conv_weights_prepare", n,
+                ctypes.cast(src, ctypes.c_void_p), ctypes.cast(cst, ctypes.c_void_p),
                 ctypes.cast(rot, ctypes.c_void_p), ctypes.cast(cout, ctypes.c_void_p), ctypes.cast(cin, ctypes.c_void_p),
                 native.stream_ptr(dev))
+    if dtype == torch.float32 and want_cast:
+        casts = [c if c is not None else w for c, w in zip(casts, weights_krsc_f32)]
     return casts, rots
 
 
@@ -172,15 +245,17 @@ def cast_bf16(src: torch.Tensor) -> torch.Tensor:
 
 def maxpool_nhwc(y: torch.Tensor, k: int) -> torch.Tensor:
     n, h, w, c = y.shape
-    out = torch.empty((n, h // k, w // k, c), dtype=torch.bfloat16, device=y.device)
-    native.call("ceb_maxpool_nhwc_bf16", native.ptr(y), native.ptr(out), n, h, w, c, k, native.stream_ptr(y.device))
+    out = torch.empty((n, h // k, w // k, c), dtype=y.dtype, device=y.device)
+    native.call("ceb_maxpool_nhwc_f32" if y.dtype == torch.float32 else "ceb_maxpool_nhwc_bf16", native.ptr(y), native.ptr(out), n, h, w, c, k, native.stream_ptr(y.device))
     return out
 
 
 def maxpool_bwd_nhwc(y: torch.Tensor, dp: torch.Tensor, k: int, relu_mask: bool) -> torch.Tensor:
     n, h, w, c = y.shape
     dz = torch.empty_like(y)
-    native.call("ceb_maxpool_bwd_nhwc_bf16", native.ptr(y), native.ptr(dp), native.ptr(dz), n, h, w, c, k,
+    assert dp.dtype == y.dtype and dp.is_contiguous()
+    native.call("ceb_maxpool_bwd_nhwc_f32" if y.dtype == torch.float32 else "ceb_maxpool_bwd_nhwc_bf16",
+                native.ptr(y), native.ptr(dp), native.ptr(dz), n, h, w, c, k,
                 1 if relu_mask else 0, native.stream_ptr(y.device))
     return dz
 
@@ -188,11 +263,11 @@ def maxpool_bwd_nhwc(y: torch.Tensor, dp: torch.Tensor, k: int, relu_mask: bool)
 def gemm_mn_acc(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor) -> torch.Tensor:
     """``c[M,N] (fp32) += a[K,M].T @ b[K,N]`` (bf16 operands with 16-byte aligned rows; the reduction
     runs over rows).  N % 64 == 0; M arbitrary."""
-    assert _rows_ok(a) and _rows_ok(b), "gemm_mn_acc operands must be bf16 with 16-byte aligned rows"
+    assert _rows_ok(a) and _rows_ok(b) and a.dtype == b.dtype, "gemm_mn_acc operands need 16-byte aligned rows"
     assert c.dtype == torch.float32 and c.stride(1) == 1
     K, M = a.shape
     N = b.shape[1]
-    native.call("ceb_gemm_bf16_mn_acc_ld", native.ptr(a), a.stride(0), native.ptr(b), b.stride(0), native.ptr(c),
+    native.call("ceb_gemm_tf32_mn_acc_ld" if a.dtype == torch.float32 else "ceb_gemm_bf16_mn_acc_ld", native.ptr(a), a.stride(0), native.ptr(b), b.stride(0), native.ptr(c),
                 M, N, K, c.stride(0), native.stream_ptr(a.device))
     return c
 
@@ -215,37 +290,43 @@ def colsum_acc(x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def im2col_c3(x_nhwc_f32: torch.Tensor) -> torch.Tensor:
-    """``[N*H*W, 64]`` bf16 im2col matrix (27 valid columns) of a 3-channel NHWC fp32 batch."""
+def im2col_c3(x_nhwc_f32: torch.Tensor, dtype=torch.bfloat16) -> torch.Tensor:
+    """im2col matrix of the 3x3 / pad 1 windows of a 1- or 3-channel NHWC fp32 batch: ``[N*H*W, 64]`` bf16 or
+    ``[N*H*W, 32]`` fp32 (9*Cin valid columns, zero padded to one 128-byte row)."""
     n, h, w, c = x_nhwc_f32.shape
-    assert c == 3 and x_nhwc_f32.is_contiguous() and x_nhwc_f32.dtype == torch.float32
-    out = torch.empty((n * h * w, 64), dtype=torch.bfloat16, device=x_nhwc_f32.device)
-    native.call("ceb_im2col3x3_c3", native.ptr(x_nhwc_f32), native.ptr(out), n, h, w, native.stream_ptr(out.device))
+    assert c in (1, 3) and x_nhwc_f32.is_contiguous() and x_nhwc_f32.dtype == torch.float32
+    f32 = dtype == torch.float32
+    out = torch.empty((n * h * w, 32 if f32 else 64), dtype=dtype, device=x_nhwc_f32.device)
+    native.call("ceb_im2col3x3", native.ptr(x_nhwc_f32), native.ptr(out), n, h, w, c, 1 if f32 else 0,
+                native.stream_ptr(out.device))
     return out
 
 
-def _stem_weight_pad(w_krsc_f32: torch.Tensor) -> torch.Tensor:
-    """``[64][3][3][3]`` fp32 -> ``[64][64]`` bf16 (K-major B operand, columns 27.. zero)."""
+def _stem_weight_pad(w_krsc_f32: torch.Tensor, dtype=torch.bfloat16) -> torch.Tensor:
+    """``[Cout][3][3][Cin]`` fp32 -> ``[Cout][64]`` bf16 / ``[Cout][32]`` fp32 (K-major B operand, zero padded)."""
     cout = w_krsc_f32.shape[0]
-    pad = torch.zeros((cout, 64), dtype=torch.bfloat16, device=w_krsc_f32.device)
-    pad[:, :27] = w_krsc_f32.reshape(cout, 27)
+    k = w_krsc_f32[0].numel()
+    pad = torch.zeros((cout, 32 if dtype == torch.float32 else 64), dtype=dtype, device=w_krsc_f32.device)
+    pad[:, :k] = w_krsc_f32.reshape(cout, k)
     return pad
 
 
 def relu_bwd(y: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
     dz = torch.empty_like(y)
-    native.call("ceb_relu_bwd_bf16", native.ptr(y), native.ptr(dy), native.ptr(dz), y.numel(),
+    assert dy.dtype == y.dtype
+    native.call("ceb_relu_bwd_f32" if y.dtype == torch.float32 else "ceb_relu_bwd_bf16", native.ptr(y),
+                native.ptr(dy), native.ptr(dz), y.numel(),
                 native.stream_ptr(y.device))
     return dz
 
 
 def conv3x3_wgrad_nhwc(dz: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
     """``dw[Cout,3,3,Cin] (fp32, contiguous) += wgrad(dz[N,H,W,Cout], x[N,H,W,Cin])`` (bf16 inputs)."""
-    assert dz.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and dz.is_contiguous() and x.is_contiguous()
+    assert dz.dtype == x.dtype and dz.is_contiguous() and x.is_contiguous()
     assert dw.dtype == torch.float32 and dw.is_contiguous()
     n, h, wd, cin = x.shape
     cout = dz.shape[3]
-    native.call("ceb_conv3x3_wgrad_bf16_nhwc", native.ptr(dz), native.ptr(x), native.ptr(dw), n, h, wd, cin, cout,
+    native.call("ceb_conv3x3_wgrad_tf32_nhwc" if x.dtype == torch.float32 else "ceb_conv3x3_wgrad_bf16_nhwc", native.ptr(dz), native.ptr(x), native.ptr(dw), n, h, wd, cin, cout,
                 native.stream_ptr(x.device))
     return dw
 
@@ -271,10 +352,16 @@ class _Conv3x3Fn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, relu):
+        dt = act_dtype()
         xn = x.permute(0, 2, 3, 1)
-        xb = (xn if xn.dtype == torch.bfloat16 else xn.to(torch.bfloat16)).contiguous()
+        xb = (xn if xn.dtype == dt else xn.to(dt)).contiguous()
         wk = weight.permute(0, 2, 3, 1)
-        wb = cast_bf16(wk) if wk.dtype == torch.float32 else wk.to(torch.bfloat16).contiguous()
+        if dt == torch.float32:
+            wb = wk.float().contiguous()
+            if wb.data_ptr() % 16:
+                wb = wb.clone()
+        else:
+            wb = cast_bf16(wk) if wk.dtype == torch.float32 else wk.to(torch.bfloat16).contiguous()
         y = conv3x3_nhwc(xb, wb, relu=relu)
         ctx.save_for_backward(xb, y if relu else xb)
         ctx.weight, ctx.relu, ctx.x_dtype = weight, relu, x.dtype
@@ -284,7 +371,7 @@ class _Conv3x3Fn(torch.autograd.Function):
     def backward(ctx, dy):
         xb, y = ctx.saved_tensors
         weight = ctx.weight
-        dz = dy.permute(0, 2, 3, 1).to(torch.bfloat16).contiguous()
+        dz = dy.permute(0, 2, 3, 1).to(xb.dtype).contiguous()
         if ctx.relu:
             dz = relu_bwd(y, dz)
         dx = dw = None
@@ -298,7 +385,7 @@ class _Conv3x3Fn(torch.autograd.Function):
                 dw = acc.permute(0, 3, 1, 2)
         if ctx.needs_input_grad[0]:
             wk = weight.data.permute(0, 2, 3, 1)
-            wd = dgrad_weights(wk if wk.dtype == torch.float32 else wk.float().contiguous())
+            wd = dgrad_weights(wk if wk.dtype == torch.float32 else wk.float().contiguous(), dtype=xb.dtype)
             dx = conv3x3_nhwc(dz, wd).permute(0, 3, 1, 2).to(ctx.x_dtype)
         return dx, dw, None
 
@@ -330,14 +417,29 @@ def linear_supported(x, weight) -> bool:
     return n % 64 == 0 or not transposed        # Conv1D storage: N is the wgrad GEMM's 64-multiple side
 
 
-def _as_rows(t: torch.Tensor) -> torch.Tensor:
-    """bf16 2-D operand with 16-byte aligned rows, without a copy when it already is one."""
+def _as_rows(t: torch.Tensor, dtype=None) -> torch.Tensor:
+    """2-D operand (``dtype``, default: the active precision's) with 16-byte aligned rows, without a copy
+    when it already is one."""
+    dtype = dtype or act_dtype()
     t2 = t.reshape(-1, t.shape[-1])
-    if t2.dtype == torch.bfloat16 and _rows_ok(t2):
+    if t2.dtype == dtype and _rows_ok(t2):
         return t2
-    out = padded_empty(t2.shape[0], t2.shape[1], torch.bfloat16, t2.device)
+    out = padded_empty(t2.shape[0], t2.shape[1], dtype, t2.device)
     out.copy_(t2)
     return out
+
+
+def _w_rows(store: torch.Tensor, transpose: bool, dtype) -> torch.Tensor:
+    """K-major GEMM operand made from an fp32 weight ``store`` (optionally transposed): a bf16 cast, or for
+    the TF32 path the fp32 weight itself (no copy unless it must be transposed or re-aligned)."""
+    if dtype == torch.bfloat16:
+        return cast_transpose_bf16(store) if transpose else cast_bf16(store)
+    if transpose:
+        R, C = store.shape
+        out = padded_empty(C, R, torch.float32, store.device)
+        out.copy_(store.t())
+        return out
+    return store if _rows_ok(store) else _as_rows(store, torch.float32)
 
 
 class _LinearFn(torch.autograd.Function):
@@ -353,7 +455,7 @@ class _LinearFn(torch.autograd.Function):
     def forward(ctx, x, weight, bias):
         store, transposed = _weight_storage(weight)
         xb = _as_rows(x)
-        wb = cast_transpose_bf16(store) if transposed else cast_bf16(store)      # [N, K]
+        wb = _w_rows(store, transposed, xb.dtype)                                 # [N, K]
         bf = bias.float().contiguous() if bias is not None else None
         y = gemm_tn(xb, wb, bias=bf)
         ctx.save_for_backward(xb)
@@ -369,10 +471,10 @@ class _LinearFn(torch.autograd.Function):
         (xb,) = ctx.saved_tensors
         weight, transposed, bias = ctx.weight, ctx.transposed, ctx.bias
         store, _ = _weight_storage(weight)
-        dyb = _as_rows(dy)
+        dyb = _as_rows(dy, xb.dtype)
         dx = None
         if ctx.needs_input_grad[0]:
-            wt = cast_bf16(store) if transposed else cast_transpose_bf16(store)  # [K, N]
+            wt = _w_rows(store, not transposed, xb.dtype)                        # [K, N]
             dx = gemm_tn(dyb, wt)
             dx = dx.view(ctx.x_shape).to(ctx.x_dtype)
         dw = None
@@ -389,7 +491,7 @@ class _LinearFn(torch.autograd.Function):
                 dw = acc.t() if transposed else acc
         db = None
         if bias is not None and ctx.needs_input_grad[2]:
-            if dyb.shape[1] % 8 == 0:
+            if dyb.shape[1] % 8 == 0 and dyb.dtype == torch.bfloat16:
                 direct = (isinstance(bias, torch.nn.Parameter) and bias.grad is not None
                           and bias.grad.is_contiguous() and bias.grad.dtype == torch.float32)
                 acc_b = bias.grad if direct else torch.zeros(dyb.shape[1], dtype=torch.float32, device=dy.device)
@@ -516,10 +618,12 @@ def _r9_features(x, net):
     backward needs, and the data-gradient weight layouts (prepared in the same launch as the bf16
     forward copies)."""
     convs = _r9_convs(net)
-    wb, wd = prepare_conv_weights([_krsc(c.weight.data) for c in convs[1:]])    # one launch: 7 casts + 7 dgrad layouts
+    dt = act_dtype()
+    # one launch: 7 casts + 7 dgrad layouts (TF32 path: the fp32 weights are read in place, 7 dgrad layouts)
+    wb, wd = prepare_conv_weights([_krsc(c.weight.data) for c in convs[1:]], dtype=dt)
     xb = x.float().permute(0, 2, 3, 1).contiguous()           # NHWC fp32 (no copy for channels_last input)
-    col = im2col_c3(xb)                                       # [N*1024, 64] bf16
-    a0 = gemm_tn(col, _stem_weight_pad(_krsc(convs[0].weight.data)), relu=True).view(x.shape[0], 32, 32, -1)
+    col = im2col_c3(xb, dt)                                   # [N*1024, 64] bf16 / [N*1024, 32] fp32
+    a0 = gemm_tn(col, _stem_weight_pad(_krsc(convs[0].weight.data), dt), relu=True).view(x.shape[0], 32, 32, -1)
     a1 = conv3x3_nhwc(a0, wb[0], relu=True)
     p1 = maxpool_nhwc(a1, 2)
     r1a = conv3x3_nhwc(p1, wb[1], relu=True)
@@ -573,7 +677,7 @@ def _r9_backward(net, saved, wd, df, fp=None):
     da0 = conv3x3_nhwc(dz, wd[1], relu_mask=a0)
 
     g0 = torch.zeros((da0.shape[3], 64), dtype=torch.float32, device=da0.device)
-    gemm_mn_acc(da0.view(-1, da0.shape[3]), col, g0)
+    gemm_mn_acc(da0.view(-1, da0.shape[3]), col, g0[:, :col.shape[1]])
     gw[0].view(da0.shape[3], 27).add_(g0[:, :27])
 
 
@@ -597,7 +701,7 @@ class _ResNet9Fn(torch.autograd.Function):
         net, f = ctx.net, ctx.f
         dl = dlogits.float() * net.out_scale
         net.linear.weight.grad.add_(dl.t() @ f.float())
-        df = (dl @ net.linear.weight.data).to(torch.bfloat16).contiguous()
+        df = (dl @ net.linear.weight.data).to(f.dtype).contiguous()
         _r9_backward(net, ctx.saved, ctx.wd, df, ctx.fp)
         return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
@@ -617,14 +721,15 @@ def linear_ce_head(feat, weight, scale, labels, g=None, dW=None):
     C = weight.shape[0]
     dev = feat.device
     labels = labels.contiguous()
+    fn = "ceb_linear_ce_head_f32" if feat.dtype == torch.float32 else "ceb_linear_ce_head"
     if g is None:
         loss = torch.empty(N, dtype=torch.float32, device=dev)
         correct = torch.empty(N, dtype=torch.float32, device=dev)
-        native.call("ceb_linear_ce_head", native.ptr(feat), native.ptr(weight), float(scale), native.ptr(labels), N, F_,
+        native.call(fn, native.ptr(feat), native.ptr(weight), float(scale), native.ptr(labels), N, F_,
                     C, None, native.ptr(loss), native.ptr(correct), None, None, native.stream_ptr(dev))
         return loss, correct
     dfeat = torch.empty_like(feat)
-    native.call("ceb_linear_ce_head", native.ptr(feat), native.ptr(weight), float(scale), native.ptr(labels), N, F_, C,
+    native.call(fn, native.ptr(feat), native.ptr(weight), float(scale), native.ptr(labels), N, F_, C,
                 native.ptr(g), None, None, native.ptr(dfeat), native.ptr(dW), native.stream_ptr(dev))
     return dfeat
 

@@ -541,10 +541,18 @@ CEB_API int ceb_colsum_bf16(const void* x_bf16, int64_t ld, int64_t rows, int co
 // live in shared memory.  Replaces ~25 library launches of 2-7 us each (bf16 GEMM, scale, softmax,
 // nll_loss, argmax, compare, their backward, two more GEMMs) behind the reference's
 // `loss = criterion(model(x), y); acc = accuracy(...)` (cv_train.py:67-72) on a [N, 10] problem.
+__device__ __forceinline__ float2 head_ld2(const __nv_bfloat16* p) { return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p)); }
+__device__ __forceinline__ float2 head_ld2(const float* p) { return *reinterpret_cast<const float2*>(p); }
+__device__ __forceinline__ void head_st2(__nv_bfloat16* p, float a, float b) { *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b); }
+__device__ __forceinline__ void head_st2(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
+
+// FT = feature / feature-gradient element type: bf16 (fast path) or float (TF32 / matched-precision path; the
+// head itself is fp32 FMA either way, like the reference's cuBLAS SGEMM for this 512 -> C layer).
+template <typename FT>
 __global__ void __launch_bounds__(256)
-linear_ce_head_kernel(const __nv_bfloat16* __restrict__ feat, const float* __restrict__ W, float scale,
+linear_ce_head_kernel(const FT* __restrict__ feat, const float* __restrict__ W, float scale,
                       const int64_t* __restrict__ labels, int N, int F, int C, const float* __restrict__ g,
-                      float* __restrict__ loss, float* __restrict__ correct, __nv_bfloat16* __restrict__ dfeat,
+                      float* __restrict__ loss, float* __restrict__ correct, FT* __restrict__ dfeat,
                       float* __restrict__ dW) {
   extern __shared__ float hs[];
   float* Ws = hs;                       // [C][F]
@@ -559,11 +567,11 @@ linear_ce_head_kernel(const __nv_bfloat16* __restrict__ feat, const float* __res
   const int J = F >> 6;                 // bf16 pairs per lane
   for (int s = blockIdx.x * wpb + warp; s < N; s += gridDim.x * wpb) {
     float x[64];                        // F <= 2048 -> up to 32 pairs
-    const __nv_bfloat162* fr = reinterpret_cast<const __nv_bfloat162*>(feat + (size_t)s * F);
+    const FT* fr = feat + (size_t)s * F;
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       if (j < J) {
-        const float2 v = __bfloat1622float2(fr[j * 32 + lane]);
+        const float2 v = head_ld2(fr + (j * 32 + lane) * 2);
         x[2 * j] = v.x; x[2 * j + 1] = v.y;
       }
     }
@@ -617,10 +625,10 @@ linear_ce_head_kernel(const __nv_bfloat16* __restrict__ feat, const float* __res
         }
       }
     }
-    __nv_bfloat162* dr = reinterpret_cast<__nv_bfloat162*>(dfeat + (size_t)s * F);
+    FT* dr = dfeat + (size_t)s * F;
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-      if (j < J) dr[j * 32 + lane] = __floats2bfloat162_rn(dx[2 * j], dx[2 * j + 1]);
+      if (j < J) head_st2(dr + (j * 32 + lane) * 2, dx[2 * j], dx[2 * j + 1]);
   }
   if (bwd) {
     __syncthreads();
@@ -631,25 +639,37 @@ linear_ce_head_kernel(const __nv_bfloat16* __restrict__ feat, const float* __res
   }
 }
 
-CEB_API int ceb_linear_ce_head(const void* feat_bf16, const float* W, float scale, const int64_t* labels, int N, int F,
-                               int C, const float* g, float* loss, float* correct, void* dfeat_bf16, float* dW,
-                               void* stream) {
-  CEB_REQUIRE(feat_bf16 && W && labels && N > 0, "ceb_linear_ce_head: bad arguments");
+template <typename FT>
+static int linear_ce_head_impl(const FT* feat, const float* W, float scale, const int64_t* labels, int N, int F,
+                               int C, const float* g, float* loss, float* correct, FT* dfeat, float* dW, void* stream) {
+  CEB_REQUIRE(feat && W && labels && N > 0, "ceb_linear_ce_head: bad arguments");
   CEB_REQUIRE(C >= 1 && C <= 32 && F % 64 == 0 && F >= 64 && F <= 2048, "ceb_linear_ce_head: need C <= 32, F %% 64 == 0, F <= 2048 (C=%d F=%d)", C, F);
-  CEB_REQUIRE(g ? (dfeat_bf16 && dW) : (loss && correct), "ceb_linear_ce_head: missing outputs");
+  CEB_REQUIRE(g ? (dfeat && dW) : (loss && correct), "ceb_linear_ce_head: missing outputs");
   const size_t smem = (size_t)C * F * sizeof(float) * (g ? 2 : 1);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(linear_ce_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(linear_ce_head_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
   int blocks = (int)ceb_cdiv(N, 8);
   if (blocks > ceb_num_sms()) blocks = ceb_num_sms();
-  linear_ce_head_kernel<<<blocks, 256, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)feat_bf16, W, scale, labels, N, F,
-                                                                    C, g, loss, correct, (__nv_bfloat16*)dfeat_bf16, dW);
+  linear_ce_head_kernel<FT><<<blocks, 256, smem, (cudaStream_t)stream>>>(feat, W, scale, labels, N, F, C, g, loss, correct, dfeat, dW);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
+}
+
+CEB_API int ceb_linear_ce_head(const void* feat_bf16, const float* W, float scale, const int64_t* labels, int N, int F,
+                               int C, const float* g, float* loss, float* correct, void* dfeat_bf16, float* dW,
+                               void* stream) {
+  return linear_ce_head_impl<__nv_bfloat16>((const __nv_bfloat16*)feat_bf16, W, scale, labels, N, F, C, g, loss, correct,
+                                            (__nv_bfloat16*)dfeat_bf16, dW, stream);
+}
+
+CEB_API int ceb_linear_ce_head_f32(const float* feat, const float* W, float scale, const int64_t* labels, int N, int F,
+                                   int C, const float* g, float* loss, float* correct, float* dfeat, float* dW,
+                                   void* stream) {
+  return linear_ce_head_impl<float>(feat, W, scale, labels, N, F, C, g, loss, correct, dfeat, dW, stream);
 }
 
 // ------------------------------------------------------------------ segment-wise BatchNorm (NHWC bf16)

@@ -106,10 +106,13 @@ CEB_API int ceb_conv_w_dgrad_layout(const float* w_krsc, void* dst_bf16, int Cou
 // and (optionally) the bf16 rotated / transposed copy used by the data-gradient conv -- what
 // ceb_cast_f32_bf16 + ceb_conv_w_dgrad_layout do per layer, in ONE launch instead of two per layer
 // (a 100-client ResNet-9 round is launch-latency bound on exactly such 3-5 us kernels).
+__device__ __forceinline__ void store_cvt(__nv_bfloat16* p, float v) { *p = __float2bfloat16(v); }
+__device__ __forceinline__ void store_cvt(float* p, float v) { *p = v; }
+
 struct WPrepTable {
   const float* src[CEB_WPREP_MAX];
-  __nv_bfloat16* cast[CEB_WPREP_MAX];
-  __nv_bfloat16* rot[CEB_WPREP_MAX];
+  void* cast[CEB_WPREP_MAX];
+  void* rot[CEB_WPREP_MAX];
   int cout[CEB_WPREP_MAX];
   int cin[CEB_WPREP_MAX];
   int blk_start[CEB_WPREP_MAX + 1];     // first block of every layer (prefix sum of its 32x32 tiles x 9 taps)
@@ -118,14 +121,15 @@ struct WPrepTable {
 
 // One block = one 32 (co) x 32 (ci) tile of one filter tap: read coalesced along ci, write the cast
 // copy in place and the transposed (rotated) copy coalesced along co through shared memory.
+template <typename OutT>
 __global__ void __launch_bounds__(256)
 wprep_kernel(WPrepTable t) {
   __shared__ float tile[32][33];
   int layer = 0;
   while (layer + 1 < t.n && (int)blockIdx.x >= t.blk_start[layer + 1]) ++layer;
   const float* __restrict__ src = t.src[layer];
-  __nv_bfloat16* __restrict__ cast = t.cast[layer];
-  __nv_bfloat16* __restrict__ rot = t.rot[layer];
+  OutT* __restrict__ cast = (OutT*)t.cast[layer];
+  OutT* __restrict__ rot = (OutT*)t.rot[layer];
   const int Cout = t.cout[layer], Cin = t.cin[layer];
   const int ci_tiles = (Cin + 31) / 32, co_tiles = (Cout + 31) / 32;
   int b = blockIdx.x - t.blk_start[layer];
@@ -141,7 +145,7 @@ wprep_kernel(WPrepTable t) {
     if (co < Cout && ci < Cin) {
       const int64_t i = ((int64_t)co * 9 + tap) * Cin + ci;
       v = src[i];
-      if (cast) cast[i] = __float2bfloat16(v);
+      if (cast) store_cvt(cast + i, v);
     }
     tile[y][x] = v;
   }
@@ -152,12 +156,12 @@ wprep_kernel(WPrepTable t) {
   for (int yy = 0; yy < 4; ++yy) {
     const int y = y0 + 8 * yy;
     const int ci = ci_t * 32 + y, co = co_t * 32 + x;
-    if (co < Cout && ci < Cin) rot[((int64_t)ci * 9 + tap_rot) * Cout + co] = __float2bfloat16(tile[x][y]);
+    if (co < Cout && ci < Cin) store_cvt(rot + ((int64_t)ci * 9 + tap_rot) * Cout + co, tile[x][y]);
   }
 }
 
-CEB_API int ceb_conv_weights_prepare(int n_layers, const float* const* src, void* const* cast_bf16, void* const* rot_bf16,
-                                     const int* cout, const int* cin, void* stream) {
+static int wprep_impl(int n_layers, const float* const* src, void* const* cast_bf16, void* const* rot_bf16,
+                      const int* cout, const int* cin, void* stream, int f32) {
   CEB_REQUIRE(n_layers > 0 && n_layers <= CEB_WPREP_MAX && src && cout && cin, "ceb_conv_weights_prepare: 1..%d layers", CEB_WPREP_MAX);
   WPrepTable t{};
   t.n = n_layers;
@@ -165,18 +169,30 @@ CEB_API int ceb_conv_weights_prepare(int n_layers, const float* const* src, void
   for (int i = 0; i < n_layers; ++i) {
     CEB_REQUIRE(src[i] && cout[i] > 0 && cin[i] > 0, "ceb_conv_weights_prepare: bad layer %d", i);
     t.src[i] = src[i];
-    t.cast[i] = cast_bf16 ? (__nv_bfloat16*)cast_bf16[i] : nullptr;
-    t.rot[i] = rot_bf16 ? (__nv_bfloat16*)rot_bf16[i] : nullptr;
+    t.cast[i] = cast_bf16 ? cast_bf16[i] : nullptr;
+    t.rot[i] = rot_bf16 ? rot_bf16[i] : nullptr;
     t.cout[i] = cout[i];
     t.cin[i] = cin[i];
     t.blk_start[i] = blocks;
     blocks += 9 * (int)ceb_cdiv(cout[i], 32) * (int)ceb_cdiv(cin[i], 32);
   }
   t.blk_start[n_layers] = blocks;
-  wprep_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(t);
+  if (f32) wprep_kernel<float><<<blocks, 256, 0, (cudaStream_t)stream>>>(t);
+  else wprep_kernel<__nv_bfloat16><<<blocks, 256, 0, (cudaStream_t)stream>>>(t);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
+}
+
+CEB_API int ceb_conv_weights_prepare(int n_layers, const float* const* src, void* const* cast_bf16, void* const* rot_bf16,
+                                     const int* cout, const int* cin, void* stream) {
+  return wprep_impl(n_layers, src, cast_bf16, rot_bf16, cout, cin, stream, 0);
+}
+
+// fp32 outputs (TF32 path): `copy` (nullable per layer) = plain copies, `rot` = data-gradient layouts.
+CEB_API int ceb_conv_weights_prepare_f32(int n_layers, const float* const* src, void* const* copy_f32, void* const* rot_f32,
+                                         const int* cout, const int* cin, void* stream) {
+  return wprep_impl(n_layers, src, copy_f32, rot_f32, cout, cin, stream, 1);
 }
 
 // ------------------------------------------------------------------ max pooling (k = 2 or 4), 8 channels per thread
@@ -194,9 +210,28 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   return u;
 }
 
-template <int KP>
+// Vector traits: one 16-byte access = 8 bf16 channels or 4 fp32 channels.
+struct VecBF {
+  static constexpr int kN = 8;
+  __device__ static void load(const uint4* p, float (&f)[8]) { unpack8(__ldg(p), f); }
+  __device__ static void store(uint4* p, const float (&f)[8]) { *p = pack8(f); }
+};
+struct VecF {
+  static constexpr int kN = 4;
+  __device__ static void load(const uint4* p, float (&f)[4]) {
+    const uint4 u = __ldg(p);
+    f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+  }
+  __device__ static void store(uint4* p, const float (&f)[4]) {
+    uint4 u; u.x = __float_as_uint(f[0]); u.y = __float_as_uint(f[1]); u.z = __float_as_uint(f[2]); u.w = __float_as_uint(f[3]);
+    *p = u;
+  }
+};
+
+template <int KP, typename V = VecBF>
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const uint4* __restrict__ y, uint4* __restrict__ out, int N, int H, int W, int C8) {
+  constexpr int VN = V::kN;
   const int Ho = H / KP, Wo = W / KP;
   const int64_t total = (int64_t)N * Ho * Wo * C8;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -206,27 +241,28 @@ maxpool_fwd_kernel(const uint4* __restrict__ y, uint4* __restrict__ out, int N, 
     const int wo = (int)(t % Wo); t /= Wo;
     const int ho = (int)(t % Ho);
     const int n = (int)(t / Ho);
-    float best[8];
+    float best[VN];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) best[i] = -INFINITY;
+    for (int i = 0; i < VN; ++i) best[i] = -INFINITY;
 #pragma unroll
     for (int dy = 0; dy < KP; ++dy)
 #pragma unroll
       for (int dx = 0; dx < KP; ++dx) {
-        float f[8];
-        unpack8(__ldg(y + (((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c), f);
+        float f[VN];
+        V::load(y + (((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c, f);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) best[i] = fmaxf(best[i], f[i]);
+        for (int i = 0; i < VN; ++i) best[i] = fmaxf(best[i], f[i]);
       }
-    out[o] = pack8(best);
+    V::store(out + o, best);
   }
 }
 
 // dz = route dp to the first arg-max of each KPxKP window of y; with relu_mask also zero where y <= 0
-template <int KP>
+template <int KP, typename V = VecBF>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dp, uint4* __restrict__ dz,
                    int N, int H, int W, int C8, int relu_mask) {
+  constexpr int VN = V::kN;
   const int Ho = H / KP, Wo = W / KP;
   const int64_t total = (int64_t)N * Ho * Wo * C8;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -236,31 +272,31 @@ maxpool_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dp, ui
     const int wo = (int)(t % Wo); t /= Wo;
     const int ho = (int)(t % Ho);
     const int n = (int)(t / Ho);
-    float best[8];
-    int arg[8];
+    float best[VN];
+    int arg[VN];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; arg[i] = 0; }
+    for (int i = 0; i < VN; ++i) { best[i] = -INFINITY; arg[i] = 0; }
 #pragma unroll
     for (int dy = 0; dy < KP; ++dy)
 #pragma unroll
       for (int dx = 0; dx < KP; ++dx) {
-        float f[8];
-        unpack8(__ldg(y + (((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c), f);
+        float f[VN];
+        V::load(y + (((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c, f);
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < VN; ++i)
           if (f[i] > best[i]) { best[i] = f[i]; arg[i] = dy * KP + dx; }
       }
-    float g[8];
-    unpack8(__ldg(dp + o), g);
+    float g[VN];
+    V::load(dp + o, g);
 #pragma unroll
     for (int dy = 0; dy < KP; ++dy)
 #pragma unroll
       for (int dx = 0; dx < KP; ++dx) {
-        float outv[8];
+        float outv[VN];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < VN; ++i)
           outv[i] = (arg[i] == dy * KP + dx && !(relu_mask && best[i] <= 0.f)) ? g[i] : 0.f;
-        dz[(((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c] = pack8(outv);
+        V::store(dz + (((int64_t)n * H + ho * KP + dy) * W + wo * KP + dx) * C8 + c, outv);
       }
   }
 }
@@ -298,23 +334,59 @@ CEB_API int ceb_maxpool_bwd_nhwc_bf16(const void* y, const void* dp, void* dz, i
   return 0;
 }
 
+// fp32 NHWC variants (TF32 path): C % 4 == 0
+CEB_API int ceb_maxpool_nhwc_f32(const float* y, float* out, int N, int H, int W, int C, int k, void* stream) {
+  CEB_REQUIRE(y && out, "ceb_maxpool_nhwc_f32: null pointer");
+  CEB_REQUIRE(N > 0 && C % 4 == 0 && (k == 2 || k == 4) && H % k == 0 && W % k == 0, "ceb_maxpool_nhwc_f32: bad shape");
+  const int64_t total = (int64_t)N * (H / k) * (W / k) * (C / 4);
+  const int grid = ceb_grid_for(total, 256);
+  if (k == 2) maxpool_fwd_kernel<2, VecF><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (uint4*)out, N, H, W, C / 4);
+  else maxpool_fwd_kernel<4, VecF><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (uint4*)out, N, H, W, C / 4);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+CEB_API int ceb_maxpool_bwd_nhwc_f32(const float* y, const float* dp, float* dz, int N, int H, int W, int C, int k,
+                                     int relu_mask, void* stream) {
+  CEB_REQUIRE(y && dp && dz, "ceb_maxpool_bwd_nhwc_f32: null pointer");
+  CEB_REQUIRE(N > 0 && C % 4 == 0 && (k == 2 || k == 4) && H % k == 0 && W % k == 0, "ceb_maxpool_bwd_nhwc_f32: bad shape");
+  const int64_t total = (int64_t)N * (H / k) * (W / k) * (C / 4);
+  const int grid = ceb_grid_for(total, 256);
+  if (k == 2) maxpool_bwd_kernel<2, VecF><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, C / 4, relu_mask);
+  else maxpool_bwd_kernel<4, VecF><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, C / 4, relu_mask);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
 // dz = dy where y > 0 else 0 (ReLU backward), bf16, n % 8 == 0
+template <typename V = VecBF>
 __global__ void __launch_bounds__(256)
 relu_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dy, uint4* __restrict__ dz, int64_t n8) {
+  constexpr int VN = V::kN;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
-    float a[8], g[8];
-    unpack8(__ldg(y + i), a);
-    unpack8(__ldg(dy + i), g);
+    float a[VN], g[VN];
+    V::load(y + i, a);
+    V::load(dy + i, g);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) g[j] = a[j] > 0.f ? g[j] : 0.f;
-    dz[i] = pack8(g);
+    for (int j = 0; j < VN; ++j) g[j] = a[j] > 0.f ? g[j] : 0.f;
+    V::store(dz + i, g);
   }
+}
+
+CEB_API int ceb_relu_bwd_f32(const float* y, const float* dy, float* dz, int64_t n, void* stream) {
+  CEB_REQUIRE(y && dy && dz && n > 0 && n % 4 == 0, "ceb_relu_bwd_f32: need n %% 4 == 0");
+  relu_bwd_kernel<VecF><<<ceb_grid_for(n / 4, 256), 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dy, (uint4*)dz, n / 4);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
 }
 
 CEB_API int ceb_relu_bwd_bf16(const void* y, const void* dy, void* dz, int64_t n, void* stream) {
   CEB_REQUIRE(y && dy && dz && n > 0 && n % 8 == 0, "ceb_relu_bwd_bf16: need n %% 8 == 0");
-  relu_bwd_kernel<<<ceb_grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dy, (uint4*)dz, n / 8);
+  relu_bwd_kernel<VecBF><<<ceb_grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dy, (uint4*)dz, n / 8);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -330,40 +402,47 @@ CEB_API int ceb_relu_bwd_bf16(const void* y, const void* dy, void* dz, int64_t n
 // Block = 32 consecutive pixels of one image row x 8 column groups.  The three input rows the pixels'
 // windows touch (with a one-pixel halo, zero outside the image) are staged in shared memory with
 // coalesced loads; every thread then assembles its 8 output columns from there.
+template <int CIN, typename OutT>
 __global__ void __launch_bounds__(256)
-im2col3x3_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ A, int N, int H, int W) {
-  __shared__ float rows[3][(32 + 2) * 3];
+im2col3x3_kernel(const float* __restrict__ x, OutT* __restrict__ A, int N, int H, int W) {
+  constexpr int KPAD = sizeof(OutT) == 2 ? 64 : 32;        // one 128-byte swizzle row
+  constexpr int PER = KPAD / 8;                            // columns per thread (16 bytes)
+  __shared__ float rows[3][(32 + 2) * CIN];
   const int segs = (W + 31) / 32;                          // 32-pixel segments per image row
   const int64_t blk = blockIdx.x;
   const int seg = (int)(blk % segs);
   const int hq = (int)((blk / segs) % H);
   const int64_t nb = blk / ((int64_t)segs * H);
   const int w0 = seg * 32;
-  for (int i = threadIdx.x; i < 3 * 34 * 3; i += blockDim.x) {
-    const int r = i / (34 * 3), rem = i - r * (34 * 3);
-    const int px = rem / 3, ci = rem - px * 3;
+  for (int i = threadIdx.x; i < 3 * 34 * CIN; i += blockDim.x) {
+    const int r = i / (34 * CIN), rem = i - r * (34 * CIN);
+    const int px = rem / CIN, ci = rem - px * CIN;
     const int hh = hq + r - 1, wc = w0 + px - 1;
     float v = 0.f;
-    if (hh >= 0 && hh < H && wc >= 0 && wc < W) v = __ldg(x + ((nb * H + hh) * W + wc) * 3 + ci);
+    if (hh >= 0 && hh < H && wc >= 0 && wc < W) v = __ldg(x + ((nb * H + hh) * W + wc) * CIN + ci);
     rows[r][rem] = v;
   }
   __syncthreads();
   const int g = threadIdx.x & 7, pl = threadIdx.x >> 3;
   const int wq = w0 + pl;
   if (wq >= W) return;
-  float v[8];
+  float v[PER];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int t = g * 8 + j;                               // column (r*3 + s)*3 + ci
+  for (int j = 0; j < PER; ++j) {
+    const int t = g * PER + j;                             // column (r*3 + s)*CIN + ci
     float val = 0.f;
-    if (t < 27) {
-      const int r = t / 9, rem = t - r * 9;                // rem = s*3 + ci: 9 consecutive floats of the row
-      val = rows[r][pl * 3 + rem];
+    if (t < 9 * CIN) {
+      const int r = t / (3 * CIN), rem = t - r * (3 * CIN);   // rem = s*CIN + ci: consecutive floats of the row
+      val = rows[r][pl * CIN + rem];
     }
     v[j] = val;
   }
   const int64_t p = (nb * H + hq) * W + wq;
-  *reinterpret_cast<uint4*>(A + p * 64 + g * 8) = pack8(v);
+  if constexpr (sizeof(OutT) == 2) {
+    *reinterpret_cast<uint4*>(A + p * KPAD + g * PER) = pack8(v);
+  } else {
+    *reinterpret_cast<float4*>(A + p * KPAD + g * PER) = make_float4(v[0], v[1], v[2], v[3]);
+  }
 }
 
 // A[N*H*W][64] (bf16) = im2col of the 3x3 / pad 1 neighbourhoods of x[N,H,W,3] (fp32)
@@ -371,7 +450,24 @@ CEB_API int ceb_im2col3x3_c3(const float* x_nhwc, void* A_bf16, int N, int H, in
   CEB_REQUIRE(x_nhwc && A_bf16 && N > 0 && H > 0 && W > 0, "ceb_im2col3x3_c3: bad arguments");
   const int64_t blocks = (int64_t)N * H * ((W + 31) / 32);
   CEB_REQUIRE(blocks < (1ll << 31), "ceb_im2col3x3_c3: batch too large");
-  im2col3x3_c3_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x_nhwc, (__nv_bfloat16*)A_bf16, N, H, W);
+  im2col3x3_kernel<3, __nv_bfloat16><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x_nhwc, (__nv_bfloat16*)A_bf16, N, H, W);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// General stem lowering: x[N,H,W,Cin] fp32 with Cin in {1, 3}; out_f32 = 0: A[N*H*W][64] bf16, 1: A[N*H*W][32] fp32
+// (9*Cin valid columns, zero padded to one 128-byte row either way).
+CEB_API int ceb_im2col3x3(const float* x_nhwc, void* A, int N, int H, int W, int Cin, int out_f32, void* stream) {
+  CEB_REQUIRE(x_nhwc && A && N > 0 && H > 0 && W > 0, "ceb_im2col3x3: bad arguments");
+  CEB_REQUIRE(Cin == 1 || Cin == 3, "ceb_im2col3x3: Cin must be 1 or 3 (got %d)", Cin);
+  const int64_t blocks = (int64_t)N * H * ((W + 31) / 32);
+  CEB_REQUIRE(blocks < (1ll << 31), "ceb_im2col3x3: batch too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (Cin == 3 && out_f32) im2col3x3_kernel<3, float><<<(unsigned)blocks, 256, 0, st>>>(x_nhwc, (float*)A, N, H, W);
+  else if (Cin == 3) im2col3x3_kernel<3, __nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(x_nhwc, (__nv_bfloat16*)A, N, H, W);
+  else if (out_f32) im2col3x3_kernel<1, float><<<(unsigned)blocks, 256, 0, st>>>(x_nhwc, (float*)A, N, H, W);
+  else im2col3x3_kernel<1, __nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(x_nhwc, (__nv_bfloat16*)A, N, H, W);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;

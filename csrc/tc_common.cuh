@@ -68,6 +68,14 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
+// Same with fp32 operands read as TF32 (kind::tf32: 8 elements of K per instruction, fp32 accumulate).
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
 // arrive on an mbarrier once every MMA issued so far by this thread has completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -170,6 +178,19 @@ __device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t desc_a,
       "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// element-type dispatch: TF = 0 bf16 operands (kind::f16), TF = 1 fp32 operands read as TF32 (kind::tf32)
+template <int TF, int PAIR>
+__device__ __forceinline__ void umma_any(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  if (TF) { if (PAIR == 2) umma_tf32_pair(tmem_d, da, db, idesc, accumulate); else umma_tf32(tmem_d, da, db, idesc, accumulate); }
+  else { if (PAIR == 2) umma_bf16_pair(tmem_d, da, db, idesc, accumulate); else umma_bf16(tmem_d, da, db, idesc, accumulate); }
+}
 // arrive on the barrier at the same shared-memory offset in BOTH CTAs once the MMAs issued so far retire
 __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
   const uint16_t mask = 3;
@@ -193,11 +214,39 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo
   d |= (uint64_t)2 << 61;
   return d;
 }
+// MN-major operands of 32-bit (TF32) elements have ONE legal swizzled layout: 128-byte rows whose 32-byte
+// units are permuted with a period of 4 rows (layout type 1, "128B with 32-byte atoms"; what TMA writes under
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B).  LBO = bytes between 128-byte-wide MN chunks, SBO = bytes between
+// 4-row K groups (512 when the rows of a chunk are contiguous).
+__device__ __forceinline__ uint64_t smem_desc_sw128_base32(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)1 << 61;
+  return d;
+}
+// MN-major operand descriptor for either element size
+template <int TF>
+__device__ __forceinline__ uint64_t smem_desc_mn(uint32_t saddr, uint32_t lbo_bytes) {
+  return TF ? smem_desc_sw128_base32(saddr, lbo_bytes, 512) : smem_desc_sw128(saddr, lbo_bytes, 1024);
+}
 // Instruction descriptor, .kind::f16: [4,6) D format (1 = f32), [7,10) A format (1 = bf16),
 // [10,13) B format, [15] A major (0 = K, 1 = MN), [16] B major, [17,23) N>>3, [24,29) M>>4.
 __host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// .kind::tf32: A / B format 2 (TF32); everything else as above.
+__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+template <int TF>
+__host__ __device__ constexpr uint32_t idesc_any(int M, int N, int a_mn_major, int b_mn_major) {
+  return TF ? idesc_tf32(M, N, a_mn_major, b_mn_major) : idesc_bf16(M, N, a_mn_major, b_mn_major);
 }
 
 __device__ __forceinline__ bool elect_one() {
@@ -214,3 +263,10 @@ __device__ __forceinline__ bool elect_one() {
 // Host: encode a tiled tensor map (bf16, 128-byte swizzle, zero fill out of bounds).
 int ceb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                        const uint64_t* strides_bytes /* rank-1 entries */, const uint32_t* box);
+// Same for fp32 elements (32 per 128-byte swizzle row) and, generally, elem_bytes in {2, 4} with
+// optional element strides (estr[i] > 1 samples every estr[i]-th element of dimension i: strided
+// convolutions read their input pixels this way).
+// atom32 = true: the 32-byte-atom variant of the 128-byte swizzle (MN-major TF32 operands, see above).
+int ceb_make_tmap(CUtensorMap* out, int elem_bytes, const void* base, int rank, const uint64_t* dims,
+                  const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr /* nullable */,
+                  bool atom32 = false);

@@ -18,7 +18,6 @@ using namespace tc;
 
 constexpr int BM = 128;
 constexpr int BK = 64;          // bf16 elements per k-step = one 128-byte swizzle row
-constexpr int UMMA_K = 16;
 // 3 stages of (16 KB + BN*128 B): two CTAs fit in one SM's 227 KB for BN <= 128, so one CTA's
 // epilogue overlaps the other's main loop without a persistent scheduler.
 // Operand ring depth: as many 16 KB + BN*128 B stages as fit beside the epilogue staging area
@@ -89,10 +88,17 @@ struct SmemLayout {
 // layers.  TMA completion bytes of both CTAs are counted on the leader's "full" barrier; the MMA
 // commits are multicast to the "empty" / "accumulator full" barriers of both; the peer's epilogue
 // warps release the accumulator with a remote arrive on the leader's barrier.
-template <int BN, int MODE, int BMAJ = 0, int PAIR = 1>
+// TF = 1: fp32 operands read by the tensor cores as TF32 (tcgen05.mma.kind::tf32), fp32 output / mask /
+// residual -- the matched-precision path (the reference's fp32 convolutions run TF32 inside cuDNN).  In
+// BYTES nothing changes (a k-step is still one 128-byte swizzle row per operand row, an instruction still
+// consumes 32 bytes of K), so the ring, the descriptors' advance and the TMEM layout are shared; only the
+// element counts (32 per row, 8 per instruction), the instruction kind and the epilogue's element size differ.
+template <int BN, int MODE, int BMAJ = 0, int PAIR = 1, int TF = 0>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB, TcParams p) {
   static_assert(PAIR == 1 || BMAJ == 0, "the CTA-pair variant stages K-major B only");
+  constexpr int BKE = TF ? 32 : 64;                    // elements per 128-byte operand row
+  constexpr int UKE = TF ? 8 : 16;                     // K elements per MMA instruction (32 bytes)
   extern __shared__ uint8_t smem_raw[];
   using L = SmemLayout<BN, MODE, PAIR>;
   constexpr int kStages = L::kStages;
@@ -168,50 +174,50 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             const uint32_t fbar = mapa_u32(smem_u32(full_bar + s), 0);
             if (MODE == 1) {
               const int sft = ks / p.cin_steps;
-              const int c0 = (ks - sft * p.cin_steps) * BK;
+              const int c0 = (ks - sft * p.cin_steps) * BKE;
               if (leader) mbar_expect_tx(full_bar + s, 2u * ((uint32_t)p.halo_bytes + L::kBBytes));
               tma_load_4d_pair(a_dst, &tmapA, fbar, c0, sft - 1, h0 - 1, n0);
 #pragma unroll
               for (int r = 0; r < 3; ++r)
-                tma_load_2d_pair(b_dst + r * L::kBTileBytes, &tmapB, fbar, ((r * 3 + sft) * p.cin_steps) * BK + c0, b_row0);
+                tma_load_2d_pair(b_dst + r * L::kBTileBytes, &tmapB, fbar, ((r * 3 + sft) * p.cin_steps) * BKE + c0, b_row0);
             } else {
               if (leader) mbar_expect_tx(full_bar + s, 2u * L::kStageBytes);
               if (p.conv) {
                 const int tap = ks / p.cin_steps;
-                const int c0 = (ks - tap * p.cin_steps) * BK;
+                const int c0 = (ks - tap * p.cin_steps) * BKE;
                 const int r = tap / 3, sft = tap - r * 3;
                 tma_load_4d_pair(a_dst, &tmapA, fbar, c0, sft - 1, h0 + r - 1, n0);
               } else {
-                tma_load_2d_pair(a_dst, &tmapA, fbar, ks * BK, m_tile * BM);
+                tma_load_2d_pair(a_dst, &tmapA, fbar, ks * BKE, m_tile * BM);
               }
-              tma_load_2d_pair(b_dst, &tmapB, fbar, ks * BK, b_row0);
+              tma_load_2d_pair(b_dst, &tmapB, fbar, ks * BKE, b_row0);
             }
           } else if (MODE == 1) {
             // k-step = (horizontal tap sft, channel chunk c0): one halo box + the 3 weight tiles r = 0..2
             const int sft = ks / p.cin_steps;
-            const int c0 = (ks - sft * p.cin_steps) * BK;
+            const int c0 = (ks - sft * p.cin_steps) * BKE;
             mbar_expect_tx(full_bar + s, (uint32_t)p.halo_bytes + L::kBBytes);
             tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 - 1, n0);
 #pragma unroll
             for (int r = 0; r < 3; ++r)
               tma_load_2d(b_dst + r * (BN * BK * 2), &tmapB, full_bar + s,
-                          ((r * 3 + sft) * p.cin_steps) * BK + c0, n_tile * BN);
+                          ((r * 3 + sft) * p.cin_steps) * BKE + c0, n_tile * BN);
           } else {
             mbar_expect_tx(full_bar + s, L::kStageBytes);
             if (p.conv) {
               const int tap = ks / p.cin_steps;
-              const int c0 = (ks - tap * p.cin_steps) * BK;
+              const int c0 = (ks - tap * p.cin_steps) * BKE;
               const int r = tap / 3, sft = tap - r * 3;
               tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 + r - 1, n0);
             } else {
-              tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BK, m_tile * BM);
+              tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BKE, m_tile * BM);
             }
             if (BMAJ == 1) {
 #pragma unroll
-              for (int ch = 0; ch < BN / 64; ++ch)
-                tma_load_2d(b_dst + ch * (BK * 128), &tmapB, full_bar + s, n_tile * BN + ch * 64, ks * BK);
+              for (int ch = 0; ch < BN / BKE; ++ch)
+                tma_load_2d(b_dst + ch * (BKE * 128), &tmapB, full_bar + s, n_tile * BN + ch * BKE, ks * BKE);
             } else {
-              tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BK, n_tile * BN);
+              tma_load_2d(b_dst, &tmapB, full_bar + s, ks * BKE, n_tile * BN);
             }
           }
         }
@@ -219,7 +225,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one elected thread; in a pair only the leader CTA issues) =====
-    constexpr uint32_t idesc = idesc_bf16(BM * PAIR, BN, 0, BMAJ);
+    constexpr uint32_t idesc = idesc_any<TF>(BM * PAIR, BN, 0, BMAJ);
     uint32_t it = 0, local = 0;
     for (int t = first_tile; leader && t < num_tiles; t += tile_step, ++local) {
       const int acc = local & 1;
@@ -242,20 +248,18 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
               for (int r = 0; r < 3; ++r)
 #pragma unroll
-                for (int k = 0; k < BK / UMMA_K; ++k) {
-                  const uint64_t da = smem_desc_sw128(a_addr + (sub * sub_rows + r) * row_bytes + k * UMMA_K * 2, 16, 1024);
-                  const uint64_t db = smem_desc_sw128(b_addr + r * L::kBTileBytes + k * UMMA_K * 2, 16, 1024);
-                  if (PAIR == 2) umma_bf16_pair(tmem_d + sub * BN, da, db, idesc, (ks | r | k) != 0);
-                  else umma_bf16(tmem_d + sub * BN, da, db, idesc, (ks | r | k) != 0);
+                for (int k = 0; k < 4; ++k) {
+                  const uint64_t da = smem_desc_sw128(a_addr + (sub * sub_rows + r) * row_bytes + k * 32, 16, 1024);
+                  const uint64_t db = smem_desc_sw128(b_addr + r * L::kBTileBytes + k * 32, 16, 1024);
+                  umma_any<TF, PAIR>(tmem_d + sub * BN, da, db, idesc, (ks | r | k) != 0);
                 }
           } else {
 #pragma unroll
-            for (int k = 0; k < BK / UMMA_K; ++k) {
-              const uint64_t da = smem_desc_sw128(a_addr + k * UMMA_K * 2, 16, 1024);
-              const uint64_t db = BMAJ == 1 ? smem_desc_sw128(b_addr + k * UMMA_K * 128, BK * 128, 1024)
-                                            : smem_desc_sw128(b_addr + k * UMMA_K * 2, 16, 1024);
-              if (PAIR == 2) umma_bf16_pair(tmem_d, da, db, idesc, (ks | k) != 0);
-              else umma_bf16(tmem_d, da, db, idesc, (ks | k) != 0);
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t da = smem_desc_sw128(a_addr + k * 32, 16, 1024);
+              const uint64_t db = BMAJ == 1 ? smem_desc_mn<TF>(b_addr + k * UKE * 128, BKE * 128)
+                                            : smem_desc_sw128(b_addr + k * 32, 16, 1024);
+              umma_any<TF, PAIR>(tmem_d, da, db, idesc, (ks | k) != 0);
             }
           }
           if (PAIR == 2) {
@@ -314,6 +318,54 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
         const bool full = (n0 + 32 <= p.N);
+        if (TF && p.out_fp32 == 1) {
+          // fp32 activations: the thread's 32 columns are 128 contiguous bytes of its output row
+          if (m >= p.M) return;
+          const int64_t off = (int64_t)m * p.ldc + n0;
+          float* crow = (float*)p.C + off;
+          const float* mrow = p.mask ? (const float*)p.mask + off : nullptr;
+          const float* rrow = p.resid ? (const float*)p.resid + off : nullptr;
+          float* c2row = p.C2 ? (float*)p.C2 + off : nullptr;
+          const bool vec = full && (p.ldc & 7) == 0 && ((((uintptr_t)p.C) | ((uintptr_t)p.mask) | ((uintptr_t)p.resid) |
+                                                          ((uintptr_t)p.C2)) & 31) == 0;
+          if (vec) {
+#pragma unroll
+            for (int g8 = 0; g8 < 4; ++g8) {
+              uint32_t w[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) w[j] = __float_as_uint(v[g8 * 8 + j]);
+              if (mrow) {
+                uint32_t mk[8];
+                ld_global_nc_v8(mrow + g8 * 8, mk);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) if (!(__uint_as_float(mk[j]) > 0.f)) w[j] = 0u;
+              }
+              if (rrow) {
+                uint32_t rs[8];
+                ld_global_nc_v8(rrow + g8 * 8, rs);
+                if (c2row) st_global_v8(crow + g8 * 8, w);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) w[j] = __float_as_uint(__uint_as_float(w[j]) + __uint_as_float(rs[j]));
+                st_global_v8((c2row ? c2row : crow) + g8 * 8, w);
+              } else {
+                st_global_v8(crow + g8 * 8, w);
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (n0 + j >= p.N) break;
+              float o = v[j];
+              if (mrow && !(mrow[j] > 0.f)) o = 0.f;
+              if (rrow) {
+                if (c2row) { crow[j] = o; c2row[j] = o + rrow[j]; } else crow[j] = o + rrow[j];
+              } else {
+                crow[j] = o;
+              }
+            }
+          }
+          return;
+        }
         if (direct && full) {
           if (m < p.M) {
             const int64_t off = (int64_t)m * p.ldc + n0;
@@ -477,12 +529,30 @@ int ceb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint6
   return 0;
 }
 
-template <int BN, int MODE, int BMAJ = 0>
+int ceb_make_tmap(CUtensorMap* out, int elem_bytes, const void* base, int rank, const uint64_t* dims,
+                  const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr_in, bool atom32) {
+  PFN_encodeTiled enc = get_encode_fn();
+  CEB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  CEB_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "ceb_make_tmap: element size %d", elem_bytes);
+  cuuint64_t gdims[5], gstr[5];
+  cuuint32_t gbox[5], estr[5];
+  for (int i = 0; i < rank; ++i) { gdims[i] = dims[i]; gbox[i] = box[i]; estr[i] = estr_in ? estr_in[i] : 1; }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
+  CUresult r = enc(out, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank,
+                   (void*)base, gdims, gstr, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CEB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rank %d, elem %d B, dims %llu/%llu, box %u/%u)",
+              (int)r, rank, elem_bytes, (unsigned long long)dims[0], (unsigned long long)dims[1], box[0], box[1]);
+  return 0;
+}
+
+template <int BN, int MODE, int BMAJ = 0, int TF = 0>
 static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
   using L = SmemLayout<BN, MODE>;
   static bool configured = false;
   if (!configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN, MODE, BMAJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN, MODE, BMAJ, 1, TF>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
   TcParams q = p;
@@ -490,20 +560,20 @@ static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcPar
   q.n_tiles = (int)ceb_cdiv(p.N, BN);
   const int tiles = q.m_tiles * q.n_tiles;
   const int grid = tiles < ceb_num_sms() ? tiles : ceb_num_sms();
-  tc_tile_kernel<BN, MODE, BMAJ><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, q);
+  tc_tile_kernel<BN, MODE, BMAJ, 1, TF><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, q);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
 }
 
 // CTA-pair launch: 2-CTA clusters, one pair per TPC, persistent over pair tiles (2 CTA tiles tall).
-template <int BN, int MODE>
+template <int BN, int MODE, int TF = 0>
 static int launch_tile_pair(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
   using L = SmemLayout<BN, MODE, 2>;
   static_assert(L::kTotal <= 232448, "CTA-pair stage ring exceeds the 227 KB shared-memory limit");
   static bool configured = false;
   if (!configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN, MODE, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_tile_kernel<BN, MODE, 0, 2, TF>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
   TcParams q = p;
@@ -522,7 +592,7 @@ static int launch_tile_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  CEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, tc_tile_kernel<BN, MODE, 0, 2>, ta, tb, q));
+  CEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, tc_tile_kernel<BN, MODE, 0, 2, TF>, ta, tb, q));
   CEB_COUNT_LAUNCH(1);
   return 0;
 }
@@ -545,38 +615,44 @@ static bool use_pair(int mode, int M, int N, int bn, int rows_per_cta_tile, int 
 
 static int pick_bn(int N) { return N <= 64 ? 64 : (N <= 128 ? 128 : 256); }
 
-static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st,
-                         bool pair = false) {
+template <int TF>
+static int dispatch_tile_t(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st,
+                           bool pair) {
   if (pair) {
     if (mode == 1) {
-      if (bn == 64) return launch_tile_pair<64, 1>(ta, tb, p, st);
-      if (bn == 128) return launch_tile_pair<128, 1>(ta, tb, p, st);
+      if (bn == 64) return launch_tile_pair<64, 1, TF>(ta, tb, p, st);
+      if (bn == 128) return launch_tile_pair<128, 1, TF>(ta, tb, p, st);
     } else if (mode == 0) {
       switch (bn) {
-        case 64: return launch_tile_pair<64, 0>(ta, tb, p, st);
-        case 128: return launch_tile_pair<128, 0>(ta, tb, p, st);
-        case 256: return launch_tile_pair<256, 0>(ta, tb, p, st);
+        case 64: return launch_tile_pair<64, 0, TF>(ta, tb, p, st);
+        case 128: return launch_tile_pair<128, 0, TF>(ta, tb, p, st);
+        case 256: return launch_tile_pair<256, 0, TF>(ta, tb, p, st);
       }
     }
     CEB_REQUIRE(false, "unsupported CTA-pair tile configuration (N tile %d, mode %d)", bn, mode);
   }
   if (mode == 1) {
-    if (bn == 64) return launch_tile<64, 1>(ta, tb, p, st);
-    if (bn == 128) return launch_tile<128, 1>(ta, tb, p, st);
+    if (bn == 64) return launch_tile<64, 1, 0, TF>(ta, tb, p, st);
+    if (bn == 128) return launch_tile<128, 1, 0, TF>(ta, tb, p, st);
   } else if (mode == 2) {      // GEMM with MN-major B
     switch (bn) {
-      case 64: return launch_tile<64, 0, 1>(ta, tb, p, st);
-      case 128: return launch_tile<128, 0, 1>(ta, tb, p, st);
-      case 256: return launch_tile<256, 0, 1>(ta, tb, p, st);
+      case 64: return launch_tile<64, 0, 1, TF>(ta, tb, p, st);
+      case 128: return launch_tile<128, 0, 1, TF>(ta, tb, p, st);
+      case 256: return launch_tile<256, 0, 1, TF>(ta, tb, p, st);
     }
   } else {
     switch (bn) {
-      case 64: return launch_tile<64, 0>(ta, tb, p, st);
-      case 128: return launch_tile<128, 0>(ta, tb, p, st);
-      case 256: return launch_tile<256, 0>(ta, tb, p, st);
+      case 64: return launch_tile<64, 0, 0, TF>(ta, tb, p, st);
+      case 128: return launch_tile<128, 0, 0, TF>(ta, tb, p, st);
+      case 256: return launch_tile<256, 0, 0, TF>(ta, tb, p, st);
     }
   }
   CEB_REQUIRE(false, "unsupported tile configuration (N tile %d, mode %d)", bn, mode);
+}
+
+static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st,
+                         bool pair = false, int tf = 0) {
+  return tf ? dispatch_tile_t<1>(bn, mode, ta, tb, p, st, pair) : dispatch_tile_t<0>(bn, mode, ta, tb, p, st, pair);
 }
 
 // C[M,N] (row stride ldc) = act(A[M,K] (row stride lda) * B[N,K]^T (row stride ldb) + bias).
@@ -586,7 +662,7 @@ static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensor
 // embedding matrix (logits live in a buffer with ldc = 50 264).
 // out_mode 0: bf16 C, 1: fp32 C, 2: fp32 C += (atomic).
 static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
-                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream);
+                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream, int tf = 0);
 
 CEB_API int ceb_gemm_bf16_tn_ld(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M,
                                 int N, int K, const float* bias, int relu, int out_mode, void* stream) {
@@ -604,27 +680,36 @@ CEB_API int ceb_gemm_bf16_tn_rows(const void* A, int64_t lda, const void* B, int
 }
 
 static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
-                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream) {
-  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_tn_ld: bad arguments");
-  CEB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && lda >= K && ldb >= K,
-              "ceb_gemm_bf16_tn_ld: lda, ldb must be multiples of 8 and >= K (lda=%lld ldb=%lld K=%d)", (long long)lda,
+                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream, int tf) {
+  const int esz = tf ? 4 : 2, bke = 128 / esz, al = 16 / esz;     // element bytes, elements per k-step, 16-byte granule
+  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_tn: bad arguments");
+  CEB_REQUIRE(lda % al == 0 && ldb % al == 0 && lda >= K && ldb >= K,
+              "ceb_gemm_tn: lda, ldb must be multiples of %d and >= K (lda=%lld ldb=%lld K=%d)", al, (long long)lda,
               (long long)ldb, K);
+  CEB_REQUIRE(!tf || out_mode != 0, "ceb_gemm_tf32_tn: the output is fp32 (out_mode 1 or 2)");
   CEB_REQUIRE(ldc >= N && ldc % (out_mode == 0 ? 8 : 4) == 0 && ldc < (1ll << 31),
-              "ceb_gemm_bf16_tn_ld: ldc=%lld must be >= N=%d and a multiple of %d", (long long)ldc, N, out_mode == 0 ? 8 : 4);
-  CEB_REQUIRE((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0, "ceb_gemm_bf16_tn_ld: operands must be 16-byte aligned");
+              "ceb_gemm_tn: ldc=%lld must be >= N=%d and a multiple of %d", (long long)ldc, N, out_mode == 0 ? 8 : 4);
+  CEB_REQUIRE((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0, "ceb_gemm_tn: operands must be 16-byte aligned");
   const int bn = pick_bn(N);
   CUtensorMap ta, tb;
-  uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * 2};
-  uint32_t ba[2] = {BK, BM};
-  if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
-  const bool pair = use_pair(0, M, N, bn, BM, (int)ceb_cdiv(K, BK));
-  uint64_t db[2] = {(uint64_t)K, (uint64_t)N}, sb[1] = {(uint64_t)ldb * 2};
-  uint32_t bb[2] = {BK, (uint32_t)(pair ? bn / 2 : bn)};
-  if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, bb)) return e;
+  uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * esz};
+  uint32_t ba[2] = {(uint32_t)bke, BM};
+  if (int e = ceb_make_tmap(&ta, esz, A, 2, da, sa, ba, nullptr)) return e;
+  const bool pair = use_pair(0, M, N, bn, BM, (int)ceb_cdiv(K, bke));
+  uint64_t db[2] = {(uint64_t)K, (uint64_t)N}, sb[1] = {(uint64_t)ldb * esz};
+  uint32_t bb[2] = {(uint32_t)bke, (uint32_t)(pair ? bn / 2 : bn)};
+  if (int e = ceb_make_tmap(&tb, esz, B, 2, db, sb, bb, nullptr)) return e;
   TcParams p{};
-  p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = (int)ldc; p.k_steps = (int)ceb_cdiv(K, BK);
+  p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = (int)ldc; p.k_steps = (int)ceb_cdiv(K, bke);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 0; p.m_limit = m_limit;
-  return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream, pair);
+  return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream, pair, tf);
+}
+
+// fp32 operands on the TF32 tensor-core path: C[M,N] (fp32) = act(A[M,K] * B[N,K]^T + bias).  lda, ldb
+// multiples of 4 elements; out_mode 1: store, 2: atomic add.
+CEB_API int ceb_gemm_tf32_tn_ld(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int M,
+                                int N, int K, const float* bias, int relu, int out_mode, void* stream) {
+  return gemm_tn_impl(A, lda, B, ldb, C, ldc, M, N, K, bias, relu, out_mode, nullptr, stream, 1);
 }
 
 // Dense form of the above (lda = ldb = K, ldc = N): K % 8 == 0, N % 8 == 0.
@@ -658,7 +743,15 @@ CEB_API int ceb_gemm_bf16_nn(const void* A, const void* B, void* C, int M, int N
 // y[N,H,W,Cout] = act(conv3x3_s1_p1(x[N,H,W,Cin], w[Cout,3,3,Cin])), all bf16 NHWC / KRSC.
 // Cin % 64 == 0, Cout % 8 == 0, W <= 128 and 128 % W == 0, H % (128/W) == 0 or (128/W) % H == 0.
 static int conv3x3_impl(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, const float* bias,
-                        int relu, int out_mode, const void* relu_mask, const void* resid, void* y2, void* stream);
+                        int relu, int out_mode, const void* relu_mask, const void* resid, void* y2, void* stream, int tf = 0);
+
+// fp32 NHWC activations / KRSC weights on the TF32 tensor-core path (fp32 output, mask, residual).
+// Cin % 32 == 0; resid (nullable) / y2 (nullable) as in ceb_conv3x3_bf16_nhwc_res.
+CEB_API int ceb_conv3x3_tf32_nhwc(const float* x, const float* w, float* y, int Nimg, int H, int W, int Cin, int Cout,
+                                  const float* bias, int relu, const float* relu_mask, const float* resid, float* y2,
+                                  void* stream) {
+  return conv3x3_impl(x, w, y, Nimg, H, W, Cin, Cout, bias, relu, 1, relu_mask, resid, y2, stream, 1);
+}
 
 CEB_API int ceb_conv3x3_bf16_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin,
                                   int Cout, const float* bias, int relu, int out_mode, const void* relu_mask,
@@ -679,17 +772,18 @@ CEB_API int ceb_conv3x3_bf16_nhwc_res(const void* x, const void* w, void* y, int
 }
 
 static int conv3x3_impl(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, const float* bias,
-                        int relu, int out_mode, const void* relu_mask, const void* resid, void* y2, void* stream) {
-  CEB_REQUIRE(x && w && y && Nimg > 0, "ceb_conv3x3_bf16_nhwc: bad arguments");
-  CEB_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "ceb_conv3x3_bf16_nhwc: need Cin %% 64 == 0, Cout %% 8 == 0 (Cin=%d Cout=%d)", Cin, Cout);
-  CEB_REQUIRE(W <= BM && BM % W == 0, "ceb_conv3x3_bf16_nhwc: W=%d must divide %d", W, BM);
+                        int relu, int out_mode, const void* relu_mask, const void* resid, void* y2, void* stream, int tf) {
+  const int esz = tf ? 4 : 2, bke = 128 / esz;
+  CEB_REQUIRE(x && w && y && Nimg > 0, "ceb_conv3x3_nhwc: bad arguments");
+  CEB_REQUIRE(Cin % bke == 0 && Cout % 8 == 0, "ceb_conv3x3_nhwc: need Cin %% %d == 0, Cout %% 8 == 0 (Cin=%d Cout=%d)", bke, Cin, Cout);
+  CEB_REQUIRE(W <= BM && BM % W == 0, "ceb_conv3x3_nhwc: W=%d must divide %d", W, BM);
   int tile_h = BM / W, tile_n = 1;
   if (tile_h > H) {
-    CEB_REQUIRE(tile_h % H == 0, "ceb_conv3x3_bf16_nhwc: H=%d W=%d does not tile %d pixels", H, W, BM);
+    CEB_REQUIRE(tile_h % H == 0, "ceb_conv3x3_nhwc: H=%d W=%d does not tile %d pixels", H, W, BM);
     tile_n = tile_h / H;
     tile_h = H;
   } else {
-    CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_bf16_nhwc: H=%d not a multiple of the %d-row tile", H, tile_h);
+    CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_nhwc: H=%d not a multiple of the %d-row tile", H, tile_h);
   }
   const int bn = pick_bn(Cout);
   // halo mode: 256-pixel tiles that stay inside one image, weights tile <= 128 wide
@@ -698,18 +792,18 @@ static int conv3x3_impl(const void* x, const void* w, void* y, int Nimg, int H, 
   const bool halo = !force_v1 && bn <= 128 && (W == 16 || W == 32) && rows256 > 0 && rows256 <= H && H % rows256 == 0;
   CUtensorMap ta, tb;
   uint64_t da[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
-  uint64_t sa[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
-  uint32_t ba[4] = {BK, (uint32_t)W, (uint32_t)(halo ? rows256 + 2 : tile_h), (uint32_t)(halo ? 1 : tile_n)};
-  if (int e = ceb_make_tmap_bf16(&ta, x, 4, da, sa, ba)) return e;
+  uint64_t sa[3] = {(uint64_t)Cin * esz, (uint64_t)W * Cin * esz, (uint64_t)H * W * Cin * esz};
+  uint32_t ba[4] = {(uint32_t)bke, (uint32_t)W, (uint32_t)(halo ? rows256 + 2 : tile_h), (uint32_t)(halo ? 1 : tile_n)};
+  if (int e = ceb_make_tmap(&ta, esz, x, 4, da, sa, ba, nullptr)) return e;
   const int K = 9 * Cin;
-  const bool pair = use_pair(halo ? 1 : 0, Nimg * H * W, Cout, bn, halo ? 256 : BM, (halo ? 3 : 9) * (Cin / BK));
-  uint64_t db[2] = {(uint64_t)K, (uint64_t)Cout}, sb[1] = {(uint64_t)K * 2};
-  uint32_t bb[2] = {BK, (uint32_t)(pair ? bn / 2 : bn)};
-  if (int e = ceb_make_tmap_bf16(&tb, w, 2, db, sb, bb)) return e;
+  const bool pair = use_pair(halo ? 1 : 0, Nimg * H * W, Cout, bn, halo ? 256 : BM, (halo ? 3 : 9) * (Cin / bke));
+  uint64_t db[2] = {(uint64_t)K, (uint64_t)Cout}, sb[1] = {(uint64_t)K * esz};
+  uint32_t bb[2] = {(uint32_t)bke, (uint32_t)(pair ? bn / 2 : bn)};
+  if (int e = ceb_make_tmap(&tb, esz, w, 2, db, sb, bb, nullptr)) return e;
   TcParams p{};
   p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout; p.resid = resid; p.C2 = y2;
-  p.k_steps = (halo ? 3 : 9) * (Cin / BK);
-  p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = H; p.W = W; p.cin_steps = Cin / BK; p.tile_h = tile_h;
+  p.k_steps = (halo ? 3 : 9) * (Cin / bke);
+  p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = H; p.W = W; p.cin_steps = Cin / bke; p.tile_h = tile_h;
   p.halo_bytes = halo ? (rows256 + 2) * W * 128 : 0;
-  return dispatch_tile(bn, halo ? 1 : 0, ta, tb, p, (cudaStream_t)stream, pair);
+  return dispatch_tile(bn, halo ? 1 : 0, ta, tb, p, (cudaStream_t)stream, pair, tf);
 }

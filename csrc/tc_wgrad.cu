@@ -18,8 +18,16 @@
 using namespace tc;
 
 constexpr int WG_M = 128;          // output channels per tile
-constexpr int WG_KPIX = 64;        // pixels per k-step
 constexpr int WG_THREADS = 192;
+// TF = 0: bf16 operands, 64 pixels per k-step, 64-channel (128-byte) MN chunks, 16 pixels per MMA.
+// TF = 1: fp32 operands read as TF32 (kind::tf32): 32-channel chunks and 8 pixels per MMA; the k-step
+//         is halved to 32 pixels so a stage keeps its size in bytes.
+template <int TF> struct WgGeom {
+  static constexpr int kPix = TF ? 32 : 64;          // pixels per k-step
+  static constexpr int kChE = TF ? 32 : 64;          // channels per 128-byte chunk row
+  static constexpr int kUk = TF ? 8 : 16;            // pixels per MMA instruction
+  static constexpr int kEsz = TF ? 4 : 2;
+};
 
 struct WgParams {
   float* dW;             // [Cout][9*Cin] fp32, accumulated
@@ -36,11 +44,13 @@ struct WgParams {
 
 // Shared-memory ring.  TAPS weight-tap tiles per stage (3 for a convolution row, 1 for a plain GEMM);
 // a CTA of a pair (PAIR = 2) stages only its half of every tap's BN input channels.
-template <int BN, int TAPS, int PAIR>
+template <int BN, int TAPS, int PAIR, int TF = 0>
 struct WgSmem {
-  static constexpr int kChunk = WG_KPIX * 128;                    // [64 px][64 ch] bf16 = 8 KB
-  static constexpr int kABytes = 2 * kChunk;                      // this CTA's 128 output channels
-  static constexpr int kCh = BN / 64 / PAIR;                      // 64-channel chunks per tap staged by this CTA
+  using G = WgGeom<TF>;
+  static constexpr int kChunk = G::kPix * 128;                    // [pixels][one 128-byte channel row]
+  static constexpr int kAChunks = WG_M / G::kChE;
+  static constexpr int kABytes = kAChunks * kChunk;               // this CTA's 128 output channels
+  static constexpr int kCh = BN / G::kChE / PAIR;                 // channel chunks per tap staged by this CTA
   static constexpr int kBChunks = TAPS * kCh;
   static constexpr int kBBytes = kBChunks * kChunk;
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -49,14 +59,14 @@ struct WgSmem {
   static constexpr int kTotal = kStages * kStageBytes + 1024 + 256;
   // One MMA instruction covers up to 256 accumulator columns: the first kC1 chunks of each CTA go
   // into instruction 1 (N1 columns over the pair), the rest into instruction 2.
-  static constexpr int kC1 = kBChunks < 256 / (64 * PAIR) ? kBChunks : 256 / (64 * PAIR);
+  static constexpr int kC1 = kBChunks < 256 / (G::kChE * PAIR) ? kBChunks : 256 / (G::kChE * PAIR);
   static constexpr int kC2 = kBChunks - kC1;
-  static constexpr int kN1 = kC1 * 64 * PAIR;
-  static constexpr int kN2 = kC2 * 64 * PAIR;
+  static constexpr int kN1 = kC1 * G::kChE * PAIR;
+  static constexpr int kN2 = kC2 * G::kChE * PAIR;
   static constexpr int kNTot = kN1 + kN2;                         // accumulator columns (= TAPS * BN)
   static constexpr int kTmemCols = kNTot <= 128 ? 128 : (kNTot <= 256 ? 256 : 512);
-  static_assert(kC2 * 64 * PAIR <= 256 && kNTot <= 512, "tile does not fit two MMA instructions / TMEM");
-  static_assert(BN % (64 * PAIR) == 0, "every CTA needs whole 64-channel chunks");
+  static_assert(kC2 * G::kChE * PAIR <= 256 && kNTot <= 512, "tile does not fit two MMA instructions / TMEM");
+  static_assert(BN % (G::kChE * PAIR) == 0, "every CTA needs whole channel chunks");
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -69,12 +79,15 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 // PAIR = 2: two CTAs of a 2-CTA cluster share every MMA (tcgen05.mma.cta_group::2, M = 256 output
 // channels): each stages its own 128 channels of dZ and half of the BN input channels of every tap,
 // so the shared-memory traffic per FLOP -- the bound of this kernel -- drops by ~40 %.
-template <int BN, bool CONV, int PAIR>
+template <int BN, bool CONV, int PAIR, int TF = 0>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constant__ CUtensorMap tmapX, WgParams p) {
   extern __shared__ uint8_t smem_raw[];
   constexpr int TAPS = CONV ? 3 : 1;
-  using L = WgSmem<BN, TAPS, PAIR>;
+  using L = WgSmem<BN, TAPS, PAIR, TF>;
+  using G = WgGeom<TF>;
+  constexpr int WG_KPIX = G::kPix;
+  constexpr int CHE = G::kChE;
   constexpr int kStages = L::kStages;
   constexpr int CH = L::kCh;
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -134,8 +147,9 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
             // both CTAs' bytes are counted on the leader's barrier, which only the leader arms
             const uint32_t fbar = mapa_u32(smem_u32(full_bar + s), 0);
             if (leader) mbar_expect_tx(full_bar + s, 2u * L::kStageBytes);
-            tma_load_2d_pair(a_dst, &tmapDZ, fbar, co_tile * WG_M, pix0);
-            tma_load_2d_pair(a_dst + L::kChunk, &tmapDZ, fbar, co_tile * WG_M + 64, pix0);
+#pragma unroll
+            for (int ac = 0; ac < L::kAChunks; ++ac)
+              tma_load_2d_pair(a_dst + ac * L::kChunk, &tmapDZ, fbar, co_tile * WG_M + ac * CHE, pix0);
             if (CONV) {
               const int n0 = pix0 / hw;
               const int h0 = (pix0 - n0 * hw) / p.W;
@@ -143,18 +157,19 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
               for (int sft = 0; sft < 3; ++sft)
 #pragma unroll
                 for (int ch = 0; ch < CH; ++ch)
-                  tma_load_4d_pair(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, fbar, ci_base + ch * 64, sft - 1,
+                  tma_load_4d_pair(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, fbar, ci_base + ch * CHE, sft - 1,
                                    h0 + r - 1, n0);
             } else {
 #pragma unroll
               for (int ch = 0; ch < CH; ++ch)
-                tma_load_2d_pair(b_dst + ch * L::kChunk, &tmapX, fbar, ci_base + ch * 64, pix0);
+                tma_load_2d_pair(b_dst + ch * L::kChunk, &tmapX, fbar, ci_base + ch * CHE, pix0);
             }
           } else {
             mbar_expect_tx(full_bar + s, L::kStageBytes);
             // dZ: 2-D [pixels][Cout]: two 64-channel chunks
-            tma_load_2d(a_dst, &tmapDZ, full_bar + s, co_tile * WG_M, pix0);
-            tma_load_2d(a_dst + L::kChunk, &tmapDZ, full_bar + s, co_tile * WG_M + 64, pix0);
+#pragma unroll
+            for (int ac = 0; ac < L::kAChunks; ++ac)
+              tma_load_2d(a_dst + ac * L::kChunk, &tmapDZ, full_bar + s, co_tile * WG_M + ac * CHE, pix0);
             // X: 4-D [N][H][W][Cin], shifted by (r-1, s-1)
             if (CONV) {
               const int n0 = pix0 / hw;
@@ -163,12 +178,12 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
               for (int sft = 0; sft < 3; ++sft)
 #pragma unroll
                 for (int ch = 0; ch < CH; ++ch)
-                  tma_load_4d(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, full_bar + s, ci_base + ch * 64, sft - 1,
+                  tma_load_4d(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, full_bar + s, ci_base + ch * CHE, sft - 1,
                               h0 + r - 1, n0);
             } else {
 #pragma unroll
               for (int ch = 0; ch < CH; ++ch)
-                tma_load_2d(b_dst + ch * L::kChunk, &tmapX, full_bar + s, ci_base + ch * 64, pix0);
+                tma_load_2d(b_dst + ch * L::kChunk, &tmapX, full_bar + s, ci_base + ch * CHE, pix0);
             }
           }
         }
@@ -178,8 +193,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
       // consecutive TMEM columns, so they are ONE wide-N operand: issue N up to 256 per instruction
       // instead of one N = BN MMA per tap -- the dZ tile is then read from shared memory once (or
       // twice) per k-slice instead of three times, and shared-memory bandwidth bounds this kernel.
-      constexpr uint32_t idesc1 = idesc_bf16(WG_M * PAIR, L::kN1, 1, 1);     // both operands MN-major
-      constexpr uint32_t idesc2 = idesc_bf16(WG_M * PAIR, L::kN2 > 0 ? L::kN2 : 16, 1, 1);
+      constexpr uint32_t idesc1 = idesc_any<TF>(WG_M * PAIR, L::kN1, 1, 1);     // both operands MN-major
+      constexpr uint32_t idesc2 = idesc_any<TF>(WG_M * PAIR, L::kN2 > 0 ? L::kN2 : 16, 1, 1);
       for (int i = 0; leader && i < n_steps; ++i) {
         const int s = i % kStages;
         const uint32_t phase = (i / kStages) & 1;
@@ -189,16 +204,15 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
           const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
           const uint32_t b_addr = a_addr + L::kABytes;
 #pragma unroll
-          for (int k = 0; k < WG_KPIX / 16; ++k) {
-            // 16 pixels = 16 rows of 128 B; MN chunks (64 channels) are L::kChunk apart
-            const uint64_t da = smem_desc_sw128(a_addr + k * 16 * 128, L::kChunk, 1024);
-            const uint64_t db = smem_desc_sw128(b_addr + k * 16 * 128, L::kChunk, 1024);
-            if (PAIR == 2) umma_bf16_pair(tmem_base, da, db, idesc1, (i | k) != 0);
-            else umma_bf16(tmem_base, da, db, idesc1, (i | k) != 0);
+          for (int k = 0; k < WG_KPIX / G::kUk; ++k) {
+            // one instruction = kUk pixels = kUk rows of 128 B; MN chunks (one 128-byte channel row wide) are
+            // L::kChunk apart
+            const uint64_t da = smem_desc_mn<TF>(a_addr + k * G::kUk * 128, L::kChunk);
+            const uint64_t db = smem_desc_mn<TF>(b_addr + k * G::kUk * 128, L::kChunk);
+            umma_any<TF, PAIR>(tmem_base, da, db, idesc1, (i | k) != 0);
             if (L::kN2 > 0) {
-              const uint64_t db2 = smem_desc_sw128(b_addr + L::kC1 * L::kChunk + k * 16 * 128, L::kChunk, 1024);
-              if (PAIR == 2) umma_bf16_pair(tmem_base + L::kN1, da, db2, idesc2, (i | k) != 0);
-              else umma_bf16(tmem_base + L::kN1, da, db2, idesc2, (i | k) != 0);
+              const uint64_t db2 = smem_desc_mn<TF>(b_addr + L::kC1 * L::kChunk + k * G::kUk * 128, L::kChunk);
+              umma_any<TF, PAIR>(tmem_base + L::kN1, da, db2, idesc2, (i | k) != 0);
             }
           }
           if (PAIR == 2) {
@@ -227,9 +241,9 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
         const int colm = second ? col - L::kN1 : col;
         const int per_cta = (second ? L::kN2 : L::kN1) / PAIR;
         const int src = colm / per_cta, local = colm - src * per_cta;
-        const int g = (second ? L::kC1 : 0) + local / 64;                  // chunk index inside the source CTA's stage
+        const int g = (second ? L::kC1 : 0) + local / CHE;                 // chunk index inside the source CTA's stage
         const int sft = g / CH, ch = g - sft * CH;
-        const int ci0 = ci_tile * BN + src * (BN / PAIR) + ch * 64 + (local & 63);
+        const int ci0 = ci_tile * BN + src * (BN / PAIR) + ch * CHE + (local % CHE);
         if (co < p.Cout && ci0 < p.Cin) {
           float* dst = p.dW + (int64_t)co * ldw + (CONV ? (r * 3 + sft) * p.Cin : 0) + ci0;
           if (p.vec_ok) {
@@ -269,13 +283,13 @@ static int pick_split(int base_ctas, int k_steps_total) {
   return best;
 }
 
-template <int BN, bool CONV, int PAIR>
+template <int BN, bool CONV, int PAIR, int TF = 0>
 static int launch_wgrad(const CUtensorMap& tdz, const CUtensorMap& tx, WgParams p, int co_units, int split, cudaStream_t st) {
-  using L = WgSmem<BN, CONV ? 3 : 1, PAIR>;
+  using L = WgSmem<BN, CONV ? 3 : 1, PAIR, TF>;
   static_assert(L::kTotal <= 232448, "wgrad stage ring exceeds the 227 KB shared-memory limit");
   static bool configured = false;
   if (!configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel<BN, CONV, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel<BN, CONV, PAIR, TF>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
   dim3 grid((unsigned)(PAIR * co_units * (CONV ? 3 : 1) * p.ci_tiles), (unsigned)split, 1);
@@ -290,11 +304,11 @@ static int launch_wgrad(const CUtensorMap& tdz, const CUtensorMap& tx, WgParams 
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    CEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, tc_wgrad_kernel<BN, CONV, PAIR>, tdz, tx, p));
+    CEB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, tc_wgrad_kernel<BN, CONV, PAIR, TF>, tdz, tx, p));
     CEB_COUNT_LAUNCH(1);
     return 0;
   }
-  tc_wgrad_kernel<BN, CONV, PAIR><<<grid, WG_THREADS, L::kTotal, st>>>(tdz, tx, p);
+  tc_wgrad_kernel<BN, CONV, PAIR, TF><<<grid, WG_THREADS, L::kTotal, st>>>(tdz, tx, p);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -306,37 +320,39 @@ static int wg_pair_env() {
   return v;
 }
 
-// dW[Cout][3][3][Cin] (fp32) += wgrad(dz[N,H,W,Cout] bf16, x[N,H,W,Cin] bf16).
-// Cin % 64 == 0, Cout % 64 == 0, W in {4,8,16,32,64}, H*W a multiple of 64 or a divisor of it.
-CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin,
-                                        int Cout, void* stream) {
-  CEB_REQUIRE(dz && x && dW && Nimg > 0, "ceb_conv3x3_wgrad_bf16_nhwc: bad arguments");
-  CEB_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "ceb_conv3x3_wgrad_bf16_nhwc: Cin, Cout must be multiples of 64 (Cin=%d Cout=%d)", Cin, Cout);
-  CEB_REQUIRE(W <= WG_KPIX && WG_KPIX % W == 0, "ceb_conv3x3_wgrad_bf16_nhwc: W=%d must divide %d", W, WG_KPIX);
-  int tile_h = WG_KPIX / W, tile_n = 1;
+// dW[Cout][3][3][Cin] (fp32) += wgrad(dz[N,H,W,Cout], x[N,H,W,Cin]); operands bf16 (tf = 0) or fp32 read as
+// TF32 (tf = 1).  Cin, Cout multiples of 64, W in {4,8,16,32(,64 bf16)}, H*W a multiple of the k-step or a
+// divisor of it.
+static int conv_wgrad_impl(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin, int Cout,
+                           void* stream, int tf) {
+  const int esz = tf ? 4 : 2, che = 128 / esz, kpix = tf ? 32 : 64;
+  CEB_REQUIRE(dz && x && dW && Nimg > 0, "ceb_conv3x3_wgrad_nhwc: bad arguments");
+  CEB_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "ceb_conv3x3_wgrad_nhwc: Cin, Cout must be multiples of 64 (Cin=%d Cout=%d)", Cin, Cout);
+  CEB_REQUIRE(W <= kpix && kpix % W == 0, "ceb_conv3x3_wgrad_nhwc: W=%d must divide %d", W, kpix);
+  int tile_h = kpix / W, tile_n = 1;
   if (tile_h > H) {
-    CEB_REQUIRE(tile_h % H == 0, "ceb_conv3x3_wgrad_bf16_nhwc: H=%d W=%d does not tile %d pixels", H, W, WG_KPIX);
+    CEB_REQUIRE(tile_h % H == 0, "ceb_conv3x3_wgrad_nhwc: H=%d W=%d does not tile %d pixels", H, W, kpix);
     tile_n = tile_h / H;
     tile_h = H;
   } else {
-    CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_wgrad_bf16_nhwc: H=%d not a multiple of the %d-row step", H, tile_h);
+    CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_wgrad_nhwc: H=%d not a multiple of the %d-row step", H, tile_h);
   }
   const int64_t npix = (int64_t)Nimg * H * W;
   CUtensorMap tdz, tx;
-  uint64_t dd[2] = {(uint64_t)Cout, (uint64_t)npix}, sd[1] = {(uint64_t)Cout * 2};
-  uint32_t bd[2] = {64, WG_KPIX};
-  if (int e = ceb_make_tmap_bf16(&tdz, dz, 2, dd, sd, bd)) return e;
+  uint64_t dd[2] = {(uint64_t)Cout, (uint64_t)npix}, sd[1] = {(uint64_t)Cout * esz};
+  uint32_t bd[2] = {(uint32_t)che, (uint32_t)kpix};
+  if (int e = ceb_make_tmap(&tdz, esz, dz, 2, dd, sd, bd, nullptr, tf != 0)) return e;
   uint64_t dx[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
-  uint64_t sx[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
-  uint32_t bx[4] = {64, (uint32_t)W, (uint32_t)tile_h, (uint32_t)tile_n};
-  if (int e = ceb_make_tmap_bf16(&tx, x, 4, dx, sx, bx)) return e;
+  uint64_t sx[3] = {(uint64_t)Cin * esz, (uint64_t)W * Cin * esz, (uint64_t)H * W * Cin * esz};
+  uint32_t bx[4] = {(uint32_t)che, (uint32_t)W, (uint32_t)tile_h, (uint32_t)tile_n};
+  if (int e = ceb_make_tmap(&tx, esz, x, 4, dx, sx, bx, nullptr, tf != 0)) return e;
 
   const int bn = (Cin % 128 == 0) ? 128 : 64;
   // CTA pairs: 256 output channels per pair, each CTA stages 64 of the tile's 128 input channels
   const bool pair = bn == 128 && Cout % 256 == 0 && (wg_pair_env() >= 0 ? wg_pair_env() != 0 : true);
   WgParams p{};
   p.dW = dW; p.Cout = Cout; p.Cin = Cin; p.H = H; p.W = W;
-  p.k_steps_total = (int)ceb_cdiv(npix, WG_KPIX);
+  p.k_steps_total = (int)ceb_cdiv(npix, kpix);
   p.ci_tiles = Cin / bn;
   p.tile_h = tile_h; p.tile_n = tile_n; p.ldw = 9 * Cin;
   p.vec_ok = (((uintptr_t)dW & 15) == 0) ? 1 : 0;
@@ -345,20 +361,41 @@ CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW
   int split = pick_split(base_ctas, p.k_steps_total);
   p.k_per_cta = (int)ceb_cdiv(p.k_steps_total, split);
   split = (int)ceb_cdiv(p.k_steps_total, p.k_per_cta);
-  if (pair) return launch_wgrad<128, true, 2>(tdz, tx, p, co_units, split, (cudaStream_t)stream);
-  if (bn == 128) return launch_wgrad<128, true, 1>(tdz, tx, p, co_units, split, (cudaStream_t)stream);
-  return launch_wgrad<64, true, 1>(tdz, tx, p, co_units, split, (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (tf) {
+    if (pair) return launch_wgrad<128, true, 2, 1>(tdz, tx, p, co_units, split, st);
+    if (bn == 128) return launch_wgrad<128, true, 1, 1>(tdz, tx, p, co_units, split, st);
+    return launch_wgrad<64, true, 1, 1>(tdz, tx, p, co_units, split, st);
+  }
+  if (pair) return launch_wgrad<128, true, 2>(tdz, tx, p, co_units, split, st);
+  if (bn == 128) return launch_wgrad<128, true, 1>(tdz, tx, p, co_units, split, st);
+  return launch_wgrad<64, true, 1>(tdz, tx, p, co_units, split, st);
 }
 
-// C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A (row stride lda), B (row stride ldb) bf16
-// with the reduction running over ROWS.  N % 64 == 0; M is arbitrary (TMA zero-fills the tail of the
-// last 128-row tile and the epilogue bounds its rows); lda, ldb multiples of 8.
+CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin,
+                                        int Cout, void* stream) {
+  return conv_wgrad_impl(dz, x, dW, Nimg, H, W, Cin, Cout, stream, 0);
+}
+
+CEB_API int ceb_conv3x3_wgrad_tf32_nhwc(const float* dz, const float* x, float* dW, int Nimg, int H, int W, int Cin,
+                                        int Cout, void* stream) {
+  return conv_wgrad_impl(dz, x, dW, Nimg, H, W, Cin, Cout, stream, 1);
+}
+
+// C[M][N] (fp32, row stride ldc) += A[K][M]^T * B[K][N]; A (row stride lda), B (row stride ldb) bf16 (or fp32
+// read as TF32) with the reduction running over ROWS.  N % 64 == 0; M is arbitrary (TMA zero-fills the tail
+// of the last 128-row tile and the epilogue bounds its rows); lda, ldb multiples of 16 bytes.
 static int mn_acc_impl(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N, int K, int ldc,
-                       const int* k_limit, void* stream);
+                       const int* k_limit, void* stream, int tf = 0);
 
 CEB_API int ceb_gemm_bf16_mn_acc_ld(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N,
                                     int K, int ldc, void* stream) {
   return mn_acc_impl(A, lda, B, ldb, C, M, N, K, ldc, nullptr, stream);
+}
+
+CEB_API int ceb_gemm_tf32_mn_acc_ld(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int M, int N,
+                                    int K, int ldc, void* stream) {
+  return mn_acc_impl(A, lda, B, ldb, C, M, N, K, ldc, nullptr, stream, 1);
 }
 
 // Same, reducing over rows [0, *k_limit_dev) only (rounded up to whole 64-row steps, never past K:
@@ -371,35 +408,42 @@ CEB_API int ceb_gemm_bf16_mn_acc_rows(const void* A, int64_t lda, const void* B,
 }
 
 static int mn_acc_impl(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int M, int N, int K, int ldc,
-                       const int* k_limit, void* stream) {
-  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_bf16_mn_acc_ld: bad arguments");
-  CEB_REQUIRE(N % 64 == 0, "ceb_gemm_bf16_mn_acc_ld: N must be a multiple of 64 (N=%d)", N);
-  CEB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && lda >= M && ldb >= N && ldc >= N,
-              "ceb_gemm_bf16_mn_acc_ld: need lda, ldb multiples of 8 with lda >= M, ldb >= N, ldc >= N "
-              "(lda=%lld ldb=%lld ldc=%d)", (long long)lda, (long long)ldb, ldc);
-  CEB_REQUIRE((((uintptr_t)A | (uintptr_t)B) & 15) == 0, "ceb_gemm_bf16_mn_acc_ld: operands must be 16-byte aligned");
+                       const int* k_limit, void* stream, int tf) {
+  const int esz = tf ? 4 : 2, che = 128 / esz, kpix = tf ? 32 : 64, al = 16 / esz;
+  CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_mn_acc_ld: bad arguments");
+  CEB_REQUIRE(N % che == 0, "ceb_gemm_mn_acc_ld: N must be a multiple of %d (N=%d)", che, N);
+  CEB_REQUIRE(lda % al == 0 && ldb % al == 0 && lda >= M && ldb >= N && ldc >= N,
+              "ceb_gemm_mn_acc_ld: need lda, ldb multiples of %d with lda >= M, ldb >= N, ldc >= N "
+              "(lda=%lld ldb=%lld ldc=%d)", al, (long long)lda, (long long)ldb, ldc);
+  CEB_REQUIRE((((uintptr_t)A | (uintptr_t)B) & 15) == 0, "ceb_gemm_mn_acc_ld: operands must be 16-byte aligned");
   CUtensorMap ta, tb;
-  uint64_t da[2] = {(uint64_t)M, (uint64_t)K}, sa[1] = {(uint64_t)lda * 2};
-  uint32_t ba[2] = {64, WG_KPIX};
-  if (int e = ceb_make_tmap_bf16(&ta, A, 2, da, sa, ba)) return e;
-  uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)ldb * 2};
-  if (int e = ceb_make_tmap_bf16(&tb, B, 2, db, sb, ba)) return e;
+  uint64_t da[2] = {(uint64_t)M, (uint64_t)K}, sa[1] = {(uint64_t)lda * esz};
+  uint32_t ba[2] = {(uint32_t)che, (uint32_t)kpix};
+  if (int e = ceb_make_tmap(&ta, esz, A, 2, da, sa, ba, nullptr, tf != 0)) return e;
+  uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)ldb * esz};
+  if (int e = ceb_make_tmap(&tb, esz, B, 2, db, sb, ba, nullptr, tf != 0)) return e;
   // CTA pairs: 256 x 256 output tile per pair (each CTA: 128 rows of A, 128 columns of B)
   const bool pair = N % 256 == 0 && M >= 256 && (wg_pair_env() >= 0 ? wg_pair_env() != 0 : true);
   const int bn = pair ? 256 : ((N % 128 == 0) ? 128 : 64);
   WgParams p{};
   p.dW = C; p.Cout = M; p.Cin = N; p.H = 1; p.W = 1; p.ldw = ldc; p.k_limit = k_limit;
   p.vec_ok = (((uintptr_t)C & 15) == 0 && ldc % 4 == 0) ? 1 : 0;
-  p.k_steps_total = (int)ceb_cdiv(K, WG_KPIX);
-  p.ci_tiles = N / bn;
+  p.k_steps_total = (int)ceb_cdiv(K, kpix);
+  p.ci_tiles = (int)ceb_cdiv(N, bn);                  // (a last partial tile is zero-filled by TMA and bounded by the epilogue)
   const int co_units = (int)ceb_cdiv(M, WG_M * (pair ? 2 : 1));
   const int base_ctas = (pair ? 2 : 1) * co_units * p.ci_tiles;
   int split = pick_split(base_ctas, p.k_steps_total);
   p.k_per_cta = (int)ceb_cdiv(p.k_steps_total, split);
   split = (int)ceb_cdiv(p.k_steps_total, p.k_per_cta);
-  if (pair) return launch_wgrad<256, false, 2>(ta, tb, p, co_units, split, (cudaStream_t)stream);
-  if (bn == 128) return launch_wgrad<128, false, 1>(ta, tb, p, co_units, split, (cudaStream_t)stream);
-  return launch_wgrad<64, false, 1>(ta, tb, p, co_units, split, (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (tf) {
+    if (pair) return launch_wgrad<256, false, 2, 1>(ta, tb, p, co_units, split, st);
+    if (bn == 128) return launch_wgrad<128, false, 1, 1>(ta, tb, p, co_units, split, st);
+    return launch_wgrad<64, false, 1, 1>(ta, tb, p, co_units, split, st);
+  }
+  if (pair) return launch_wgrad<256, false, 2>(ta, tb, p, co_units, split, st);
+  if (bn == 128) return launch_wgrad<128, false, 1>(ta, tb, p, co_units, split, st);
+  return launch_wgrad<64, false, 1>(ta, tb, p, co_units, split, st);
 }
 
 // Dense form (lda = M, ldb = N): M % 64 == N % 64 == 0.
