@@ -41,7 +41,10 @@ def parse():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--mode", default="sketch")
     ap.add_argument("--model", default="ResNet9")
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16", "fp32"],
+                    help="tf32 (headline): fp32 activations, tcgen05 kind::tf32 -- the precision the reference's fp32 "
+                         "convolutions get from cuDNN; bf16: the fast path (reported as the extra key \"bf16\")")
+    ap.add_argument("--no_extra", action="store_true", help="skip the extra bf16 measurement")
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no_native_nn", action="store_true",
                     help="run conv/linear layers on cuDNN/cuBLAS instead of the hand-written tcgen05 kernels")
@@ -196,99 +199,124 @@ def run_ours(cfg):
             return subprocess.call(cmd)
         raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (cfg.gpus, world))
     clients = cfg.clients_per_gpu * cfg.gpus
-    args = make_args(mode=cfg.mode, error_type="virtual" if cfg.mode in ("sketch", "true_topk") else "none",
-                     local_momentum=0.0, virtual_momentum=0.9, num_workers=clients, num_clients=NUM_CLIENTS,
-                     local_batch_size=-1, num_epochs=1.0, dataset_name="CIFAR10", device="cuda",
-                     precision=cfg.precision, backend=cfg.backend, model=cfg.model,
-                     no_native_nn=cfg.no_native_nn, no_cuda_graphs=cfg.no_cuda_graphs,
-                     defer_results=not cfg.sync_results)
-    rt = init_runtime(args)
-    torch.manual_seed(args.seed)
-    torch.backends.cudnn.benchmark = True
-    model = getattr(models, cfg.model)(num_classes=10)
-    fed = FedModel(model, compute_loss_train, args, compute_loss_val)
-    opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
-    opt.param_groups[0]["lr"] = 0.05
-    fed.train(True)
-
     n_distinct = 4
     host_rounds = [synthetic_image_batch(clients, IMAGES_PER_CLIENT, seed=s, first_client=(s * clients) % (NUM_CLIENTS - clients),
                                          pin=True) for s in range(n_distinct)]
-    dev = rt.device
-    dev_rounds = [(ids, img.to(dev), lab.to(dev)) for ids, img, lab in host_rounds]
     per_rank_samples = cfg.clients_per_gpu * IMAGES_PER_CLIENT
     h2d = per_rank_samples * (3 * 32 * 32 * 4 + 8)
-    d2h = clients * (args.num_results_train + 1) * 4
+    state = {}
 
-    def one_round(batch, read=True):
-        out = fed(batch)
-        opt.step()
-        if read:
-            # the step's result is read on the host (results are deferred: the async D2H issued by
-            # fed() has been overtaken by the server step's launches, not skipped)
-            float(np.mean(out[0]))
-        return out
+    def measure(precision, steps, warmup, e2e=True, profile=False):
+        args = make_args(mode=cfg.mode, error_type="virtual" if cfg.mode in ("sketch", "true_topk") else "none",
+                         local_momentum=0.0, virtual_momentum=0.9, num_workers=clients, num_clients=NUM_CLIENTS,
+                         local_batch_size=-1, num_epochs=1.0, dataset_name="CIFAR10", device="cuda",
+                         precision=precision, backend=cfg.backend, model=cfg.model,
+                         no_native_nn=cfg.no_native_nn, no_cuda_graphs=cfg.no_cuda_graphs,
+                         defer_results=not cfg.sync_results)
+        rt = init_runtime(args)
+        torch.manual_seed(args.seed)
+        torch.backends.cudnn.benchmark = True
+        model = getattr(models, cfg.model)(num_classes=10)
+        fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+        opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+        opt.param_groups[0]["lr"] = 0.05
+        fed.train(True)
+        dev = rt.device
+        dev_rounds = [(ids, img.to(dev), lab.to(dev)) for ids, img, lab in host_rounds]
+        d2h = clients * (args.num_results_train + 1) * 4
 
-    def timed(rounds, steps, warmup, read_every_step):
-        for i in range(warmup):
-            one_round(rounds[i % len(rounds)])
-        rt.barrier()
-        torch.cuda.synchronize()
-        native.reset_launch_count()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        out = None
-        for i in range(steps):
-            # device-timed loop: the loss is read once, after the last step (a driver that logs every K
-            # rounds); end-to-end loop: the loss of EVERY step is read on the host
-            out = one_round(rounds[(warmup + i) % len(rounds)], read=read_every_step or i == steps - 1)
-        b.record()
-        rt.barrier()
-        torch.cuda.synchronize()
-        ms = rt.max_over_ranks(a.elapsed_time(b))
-        return ms / steps, native.launch_count(), out
+        def one_round(batch, read=True):
+            out = fed(batch)
+            opt.step()
+            if read:
+                # the step's result is read on the host (results are deferred: the async D2H issued by
+                # fed() has been overtaken by the server step's launches, not skipped)
+                float(np.mean(out[0]))
+            return out
 
-    sampler = ClockSampler(dev.index or 0)
-    if rt.rank == 0 and not cfg.profile:
-        sampler.start()
+        def timed(rounds, steps, warmup, read_every_step):
+            for i in range(warmup):
+                one_round(rounds[i % len(rounds)])
+            rt.barrier()
+            torch.cuda.synchronize()
+            native.reset_launch_count()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            out = None
+            for i in range(steps):
+                # device-timed loop: the loss is read once, after the last step (a driver that logs every K
+                # rounds); end-to-end loop: the loss of EVERY step is read on the host
+                out = one_round(rounds[(warmup + i) % len(rounds)], read=read_every_step or i == steps - 1)
+            b.record()
+            rt.barrier()
+            torch.cuda.synchronize()
+            ms = rt.max_over_ranks(a.elapsed_time(b))
+            return ms / steps, native.launch_count(), out
+
+        if profile:
+            for i in range(warmup):
+                one_round(dev_rounds[i % n_distinct])
+            torch.cuda.synchronize()
+            torch.cuda.profiler.start()
+            for i in range(steps):
+                one_round(dev_rounds[i % n_distinct])
+            torch.cuda.synchronize()
+            torch.cuda.profiler.stop()
+            return None
+        ms_dev, launches_dev, out = timed(dev_rounds, steps, warmup, read_every_step=cfg.sync_results)
+        res = {"ms_dev": ms_dev, "launches": launches_dev, "args": args, "rt": rt, "d2h": d2h,
+               "client_batching": fed.worker.can_batch_clients(), "native_nn": nnops.native_enabled(),
+               "backend": rt.backend}
+        if e2e:
+            ms_e2e, launches, out = timed(host_rounds, steps, max(3, warmup), read_every_step=True)
+            res.update(ms_e2e=ms_e2e, launches=launches)
+        res["last_loss"] = float(out[0].mean())
+        if cfg.phases:      # every rank runs the rounds (they contain collectives); rank 0 prints
+            _phase_breakdown(fed, opt, dev_rounds, torch, rt.rank == 0)
+        state["fed"] = fed
+        return res
+
+    rank0 = int(os.environ.get("RANK", "0")) == 0
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
     if cfg.profile:
-        for i in range(cfg.warmup):
-            one_round(dev_rounds[i % n_distinct])
-        torch.cuda.synchronize()
-        torch.cuda.profiler.start()
-        for i in range(cfg.steps):
-            one_round(dev_rounds[i % n_distinct])
-        torch.cuda.synchronize()
-        torch.cuda.profiler.stop()
+        measure(cfg.precision, cfg.steps, cfg.warmup, profile=True)
         print(json.dumps({"profile_run": True, "steps": cfg.steps}))
-        rt.shutdown()
         return 0
-    ms_dev, launches_dev, _ = timed(dev_rounds, cfg.steps, cfg.warmup, read_every_step=cfg.sync_results)
-    ms_e2e, launches, out = timed(host_rounds, cfg.steps, max(3, cfg.warmup), read_every_step=True)
-    clocks = sampler.stop() if rt.rank == 0 else None
-    last_loss = float(out[0].mean())
-
-    if cfg.phases:      # every rank runs the rounds (they contain collectives); rank 0 prints
-        _phase_breakdown(fed, opt, dev_rounds, torch, rt.rank == 0)
-
+    if rank0:
+        sampler.start()
+    main = measure(cfg.precision, cfg.steps, cfg.warmup)
+    clocks = sampler.stop() if rank0 else None
+    extra = None
+    if cfg.precision == "tf32" and not cfg.no_extra:
+        # the fast path, same config and timing rules (device-timed + end to end), reported beside the headline
+        extra = measure("bf16", cfg.steps, cfg.warmup)
+    rt, args = main["rt"], main["args"]
     if rt.rank == 0:
-        value = clients / (ms_dev / 1e3)
-        e2e = clients / (ms_e2e / 1e3)
-        print(json.dumps({
+        value = clients / (main["ms_dev"] / 1e3)
+        e2e = clients / (main["ms_e2e"] / 1e3)
+        line = {
             "metric": METRIC, "value": value, "unit": "clients/s", "n_gpus": cfg.gpus, "steps": cfg.steps,
-            "warmup": cfg.warmup, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
+            "warmup": cfg.warmup, "ms_per_step": main["ms_dev"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": cfg.precision, "data": "synthetic",
             "config": {"model": cfg.model, "mode": cfg.mode, "num_rows": args.num_rows, "num_cols": args.num_cols,
                        "k": args.k, "global_batch": clients * IMAGES_PER_CLIENT, "clients_per_round": clients,
                        "images_per_client": IMAGES_PER_CLIENT, "seq_len": None,
-                       "parallelism": "dp%d" % cfg.gpus, "backend": rt.backend,
-                       "client_batching": fed.worker.can_batch_clients(), "native_nn": nnops.native_enabled(),
+                       "parallelism": "dp%d" % cfg.gpus, "backend": main["backend"],
+                       "client_batching": main["client_batching"], "native_nn": main["native_nn"],
+                       "precision_note": "tf32 = fp32 activations / weights, tcgen05 kind::tf32 MMAs with fp32 "
+                                         "accumulation, fp32 head: what the reference's fp32 model gets from cuDNN "
+                                         "(allow_tf32 defaults to True)",
                        "l2": "weights+grads+sketch+activations (>300 MB/round) exceed the 126 MB L2; "
                              "%d distinct input batches rotate" % n_distinct},
-            "e2e": {"value": e2e, "unit": "clients/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h},
-            "gpu_launches": int(launches), "clocks": clocks, "last_loss": last_loss,
-        }))
+            "e2e": {"value": e2e, "unit": "clients/s", "ms_per_step": main["ms_e2e"], "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": main["d2h"]},
+            "gpu_launches": int(main["launches"]), "clocks": clocks, "last_loss": main["last_loss"],
+        }
+        if extra is not None:
+            line["bf16"] = {"value": clients / (extra["ms_dev"] / 1e3), "ms_per_step": extra["ms_dev"],
+                            "e2e_value": clients / (extra["ms_e2e"] / 1e3), "e2e_ms_per_step": extra["ms_e2e"],
+                            "gpu_launches": int(extra["launches"]), "last_loss": extra["last_loss"]}
+        print(json.dumps(line))
     rt.shutdown()
     return 0
 

@@ -163,7 +163,7 @@ def _bn_segmentable(model: torch.nn.Module) -> bool:
 
 
 def _autocast(args, device):
-    if device.type == "cuda" and getattr(args, "precision", "bf16") == "bf16":
+    if device.type == "cuda" and getattr(args, "precision", "tf32") == "bf16":
         return torch.autocast("cuda", dtype=torch.bfloat16)
     return torch.autocast(device.type, enabled=False)
 
@@ -329,7 +329,7 @@ class ClientWorker:
         # tensor-core layers: hand-written tcgen05 kernels on CUDA unless switched off
         from .ops import nn as nnops
         nnops.set_native(self.device.type == "cuda" and not getattr(args, "no_native_nn", False))
-        nnops.set_precision(getattr(args, "precision", "bf16"))
+        nnops.set_precision(getattr(args, "precision", "tf32"))
         self.last_clients: List[int] = []
         self.round_no = 0                 # training rounds run so far (part of the DP noise stream id)
 

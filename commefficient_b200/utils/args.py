@@ -112,8 +112,9 @@ _FLAGS = [
     ("b200", [
         _flag("backend", "auto", str, choices=("auto", "b200", "nccl", "gloo"),
               help="collective backend: b200 = peer-memory kernels over NVLink"),
-        _flag("precision", "bf16", str, choices=("fp32", "tf32", "bf16"),
-              help="conv/GEMM input precision (fp32 master weights always)"),
+        _flag("precision", "tf32", str, choices=("fp32", "tf32", "bf16"),
+              help="tf32 (default): fp32 activations, TF32 tensor-core inputs, as the reference under cuDNN; "
+                   "bf16: fast path; fp32: IEEE fp32 on the library, no tensor cores"),
         _flag("p2", 0, int,
               help="FetchSGD second round: re-rank p2*k sketch candidates by exact value"),
         _flag("synthetic", store_true=True, help="generate data of the dataset's shape"),
