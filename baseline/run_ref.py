@@ -33,12 +33,12 @@ def _prepare_paths():
     os.environ["PYTHONPATH"] = extra + os.pathsep + os.environ.get("PYTHONPATH", "")
 
 
-def make_round(num_clients_round, per_client, num_total_clients, seed, torch):
+def make_round(num_clients_round, per_client, num_total_clients, seed, torch, noise=0.5):
     g = torch.Generator().manual_seed(seed)
     protos = torch.randn((10, 3, 32, 32), generator=torch.Generator().manual_seed(1234))
     n = num_clients_round * per_client
     labels = torch.randint(0, 10, (n,), generator=g)
-    images = protos[labels] + 0.5 * torch.randn((n, 3, 32, 32), generator=g)
+    images = protos[labels] + noise * torch.randn((n, 3, 32, 32), generator=g)
     first = (seed * num_clients_round) % max(1, num_total_clients - num_clients_round)
     ids = (torch.arange(num_clients_round).repeat_interleave(per_client) + first).long()
     return ids, images, labels
@@ -54,6 +54,16 @@ def main():
     ap.add_argument("--per_client", type=int, default=5)
     ap.add_argument("--num_clients", type=int, default=10000)
     ap.add_argument("--port", type=int, default=5315)
+    # accuracy-vs-round curve mode (bench/curves.py): same data, initial weights and LR schedule as our arm
+    ap.add_argument("--curve_out", default="")
+    ap.add_argument("--curve_init", default="", help="state_dict file with the initial weights")
+    ap.add_argument("--noise", type=float, default=0.5)
+    ap.add_argument("--lr_peak", type=float, default=0.1)
+    ap.add_argument("--pivot", type=int, default=0)
+    ap.add_argument("--val_every", type=int, default=25)
+    ap.add_argument("--val_images", type=int, default=1000)
+    ap.add_argument("--k", type=int, default=50000)
+    ap.add_argument("--num_cols", type=int, default=500000)
     cfg = ap.parse_args()
 
     _prepare_paths()
@@ -68,7 +78,8 @@ def main():
                 "--local_momentum", "0", "--virtual_momentum", "0.9", "--num_workers", str(cfg.clients_per_round),
                 "--num_clients", str(cfg.num_clients), "--local_batch_size", "-1", "--num_epochs", "1",
                 "--num_devices", str(cfg.gpus), "--device", "cuda", "--port", str(cfg.port),
-                "--lr_scale", "0.4"]
+                "--lr_scale", "0.4", "--k", str(cfg.k), "--num_cols", str(cfg.num_cols),
+                "--valid_batch_size", "500"]
     if cfg.gpus == 1:
         ref_argv.append("--share_ps_gpu")
     sys.argv = ["cv_train.py"] + ref_argv
@@ -83,6 +94,8 @@ def main():
     model = ref_models.ResNet9(do_batchnorm=False, num_classes=10, new_num_classes=None,
                                bn_bias_freeze=False, bn_weight_freeze=False,
                                channels={"prep": 64, "layer1": 128, "layer2": 256, "layer3": 512})
+    if cfg.curve_init:
+        model.load_state_dict(torch.load(cfg.curve_init, map_location="cpu"))
     opt = torch.optim.SGD(model.parameters(), lr=1)
     fed_model = FedModel(model, ref_cv.compute_loss_train, args, ref_cv.compute_loss_val)
     fed_opt = FedOptimizer(opt, args)
@@ -90,6 +103,9 @@ def main():
         group["lr"] = 0.05
     n_procs = len(fed_model.update_forward_grad_ps)
     processed = (cfg.clients_per_round // n_procs) * n_procs      # reference drops the remainder (Q1)
+
+    if cfg.curve_out:
+        return run_curve(cfg, fed_model, fed_opt, torch)
 
     fed_model.train(True)
     rounds = [make_round(cfg.clients_per_round, cfg.per_client, cfg.num_clients, s, torch)
@@ -122,6 +138,41 @@ def main():
         "h2d_bytes_per_step": h2d + 4 * model_numel(model) * n_procs,
         "d2h_bytes_per_step": 4 * model_numel(model),
         "last_loss": loss, "one_gpu_transport": os.environ.get("CEB_REF_ONE_GPU") == "1"}), flush=True)
+
+
+def curve_lr(t, rounds, pivot, peak):
+    """Triangular schedule of the reference's cv_train (0 -> peak at `pivot` -> 0 at `rounds`), at round t >= 1."""
+    import numpy as np
+    return float(np.interp(t, [0, pivot, rounds], [0.0, peak, 0.0]))
+
+
+def run_curve(cfg, fed_model, fed_opt, torch):
+    """Train for cfg.steps rounds on the shared synthetic task and record the per-round mean client loss /
+    accuracy and the validation loss / accuracy every cfg.val_every rounds."""
+    import numpy as np
+    pivot = cfg.pivot or max(1, cfg.steps // 5)
+    val = make_round(cfg.val_images // 5, 5, 10 ** 9, 999983, torch, cfg.noise)
+    val = (torch.full_like(val[0], -1), val[1], val[2])
+    rec = {"round": [], "train_loss": [], "train_acc": [], "val_round": [], "val_loss": [], "val_acc": []}
+    for t in range(1, cfg.steps + 1):
+        for group in fed_opt.param_groups:
+            group["lr"] = curve_lr(t, cfg.steps, pivot, cfg.lr_peak)
+        fed_model.train(True)
+        out = fed_model(make_round(cfg.clients_per_round, cfg.per_client, cfg.num_clients, t, torch, cfg.noise))
+        fed_opt.step()
+        rec["round"].append(t)
+        rec["train_loss"].append(float(np.mean(out[0])))
+        rec["train_acc"].append(float(np.mean(out[1])))
+        if t % cfg.val_every == 0 or t == cfg.steps:
+            fed_model.train(False)
+            vout = fed_model(val)
+            rec["val_round"].append(t)
+            rec["val_loss"].append(float(np.mean(vout[0])))
+            rec["val_acc"].append(float(np.mean(vout[1])))
+    fed_model.finalize()
+    with open(cfg.curve_out, "w") as f:
+        json.dump(rec, f)
+    print("REF_CURVE " + cfg.curve_out, flush=True)
 
 
 def model_numel(model):

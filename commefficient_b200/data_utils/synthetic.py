@@ -129,7 +129,7 @@ def write_synthetic_persona(dataset_dir, num_clients=64, dialogs_per_client=2, u
 
 
 def synthetic_image_batch(num_clients, per_client, num_classes=10, shape=(3, 32, 32), seed=0,
-                          first_client=0, dtype=torch.float32, pin=False):
+                          first_client=0, dtype=torch.float32, pin=False, noise=0.5):
     """One round's batch ``(client_ids, images, labels)`` generated directly as tensors
     (normalised class-prototype + noise images) -- used by benchmarks and smoke tests
     where the on-disk pipeline is not the object of measurement."""
@@ -137,7 +137,7 @@ def synthetic_image_batch(num_clients, per_client, num_classes=10, shape=(3, 32,
     protos = torch.randn((num_classes,) + tuple(shape), generator=torch.Generator().manual_seed(1234))
     n = num_clients * per_client
     labels = torch.randint(0, num_classes, (n,), generator=g)
-    images = (protos[labels] + 0.5 * torch.randn((n,) + tuple(shape), generator=g)).to(dtype)
+    images = (protos[labels] + noise * torch.randn((n,) + tuple(shape), generator=g)).to(dtype)
     client_ids = (torch.arange(num_clients).repeat_interleave(per_client) + first_client).long()
     if pin and torch.cuda.is_available():
         images, labels, client_ids = images.pin_memory(), labels.pin_memory(), client_ids.pin_memory()

@@ -87,17 +87,14 @@ class Attention(nn.Module):
         self.attn_pdrop = cfg.attn_pdrop
         self.resid_dropout = nn.Dropout(cfg.resid_pdrop)
 
-    def forward(self, x):
+    def forward(self, x, salt=0, fuse_resid_dropout=False):
+        """``fuse_resid_dropout``: the caller applies the residual dropout inside the add + LayerNorm kernel
+        that consumes this branch, so it is skipped here."""
         B, T, E = x.shape
-        q, k, v = self.c_attn(x).split(E, dim=2)
-        hd = E // self.n_head
-        q = q.view(B, T, self.n_head, hd).transpose(1, 2)
-        k = k.view(B, T, self.n_head, hd).transpose(1, 2)
-        v = v.view(B, T, self.n_head, hd).transpose(1, 2)
-        y = F.scaled_dot_product_attention(q, k, v, is_causal=True,
-                                           dropout_p=self.attn_pdrop if self.training else 0.0)
-        y = y.transpose(1, 2).reshape(B, T, E)
-        return self.resid_dropout(self.c_proj(y))
+        y = nnops.attention(self.c_attn(x), B, T, self.n_head,
+                            p_drop=self.attn_pdrop if self.training else 0.0, salt=salt)
+        y = self.c_proj(y)
+        return y if fuse_resid_dropout else self.resid_dropout(y)
 
 
 class MLP(nn.Module):
@@ -107,8 +104,9 @@ class MLP(nn.Module):
         self.c_proj = Conv1D(cfg.n_embd, 4 * cfg.n_embd, cfg.initializer_range)
         self.dropout = nn.Dropout(cfg.resid_pdrop)
 
-    def forward(self, x):
-        return self.dropout(self.c_proj(nnops.gelu_tanh(self.c_fc(x))))
+    def forward(self, x, fuse_resid_dropout=False):
+        y = self.c_proj(nnops.gelu_tanh(self.c_fc(x)))
+        return y if fuse_resid_dropout else self.dropout(y)
 
 
 class Block(nn.Module):
@@ -137,12 +135,14 @@ class GPT2Model(nn.Module):
         nn.init.normal_(self.wpe.weight, 0.0, cfg.initializer_range)
 
     def forward(self, input_ids, token_type_ids=None):
-        T = input_ids.shape[-1]
-        pos = torch.arange(T, device=input_ids.device)
-        x = self.wte(input_ids) + self.wpe(pos)
-        if token_type_ids is not None:
-            x = x + self.wte(token_type_ids)
-        x = self.drop(x)
+        # native path: every dropout of the trunk is applied INSIDE the kernel that produces / consumes the
+        # tensor (embedding gather, attention probabilities, the residual add + LayerNorm); masks come from a
+        # counter hash of (device seed, site salt, position) and are regenerated in the backward
+        fused = self.training and nnops.fused_dropout_available(self.wte.weight)
+        if fused:
+            nnops.advance_dropout(input_ids.device)
+        x = nnops.embed(self.wte.weight, self.wpe.weight, input_ids, token_type_ids,
+                        p_drop=self.drop.p if self.training else 0.0, salt=1)
         # Same math as ``for block in self.h: x = block(x)`` followed by ln_f, regrouped so that every
         # residual add is fused with the LayerNorm that consumes its result (ops/nn.py:add_layer_norm):
         # x + attn(ln_1(x)) feeds ln_2 of the same block, x + mlp(ln_2(x)) feeds ln_1 of the next block
@@ -151,9 +151,13 @@ class GPT2Model(nn.Module):
         first = blocks[0].ln_1 if blocks else self.ln_f
         h = nnops.layer_norm(x, first.weight, first.bias, first.eps)
         for i, block in enumerate(blocks):
-            x, h = nnops.add_layer_norm(x, block.attn(h), block.ln_2.weight, block.ln_2.bias, block.ln_2.eps)
+            pr = block.attn.resid_dropout.p if fused else 0.0
+            x, h = nnops.add_layer_norm(x, block.attn(h, salt=16 * i + 2, fuse_resid_dropout=fused), block.ln_2.weight,
+                                        block.ln_2.bias, block.ln_2.eps, p_drop=pr, salt=16 * i + 3)
             nxt = blocks[i + 1].ln_1 if i + 1 < len(blocks) else self.ln_f
-            x, h = nnops.add_layer_norm(x, block.mlp(h), nxt.weight, nxt.bias, nxt.eps)
+            pr = block.mlp.dropout.p if fused else 0.0
+            x, h = nnops.add_layer_norm(x, block.mlp(h, fuse_resid_dropout=fused), nxt.weight, nxt.bias, nxt.eps,
+                                        p_drop=pr, salt=16 * i + 4)
         return h
 
 

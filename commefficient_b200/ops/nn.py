@@ -95,15 +95,64 @@ def layer_norm(x, weight, bias, eps=1e-5):
     return F.layer_norm(x, (x.shape[-1],), weight, bias, eps)
 
 
-def add_layer_norm(resid, branch, weight, bias, eps=1e-5):
-    """``(resid + branch, LayerNorm(resid + branch))`` -- the residual add fused into the LayerNorm that
-    follows it (native path: one kernel each way, ``ops/tfm.py:_AddLayerNorm``)."""
+def add_layer_norm(resid, branch, weight, bias, eps=1e-5, p_drop=0.0, salt=0):
+    """``(resid + dropout(branch), LayerNorm(of that))`` -- the residual add (and the dropout in front of it)
+    fused into the LayerNorm that follows (native path: one kernel each way, ``ops/tfm.py:_AddLayerNorm``;
+    the mask is a counter hash of the position, regenerated in the backward)."""
     if (_use_native_bf16(resid) and weight.is_cuda and resid.dtype == torch.float32
             and resid.shape[-1] in (128, 256, 512, 768, 1024, 1280)):
         from . import tfm
-        return tfm.add_layer_norm(resid, branch, weight, bias, eps)
+        return tfm.add_layer_norm(resid, branch, weight, bias, eps, p_drop, salt,
+                                  tfm.dropout_state(resid.device) if p_drop > 0 else None)
+    if p_drop > 0:
+        branch = F.dropout(branch, p_drop, training=True)
     new_resid = resid + branch
     return new_resid, layer_norm(new_resid, weight, bias, eps)
+
+
+def fused_dropout_available(x: torch.Tensor) -> bool:
+    """Whether the hooks below apply dropout inside their kernels (so the model must not apply it again)."""
+    return _use_native_bf16(x)
+
+
+def attention(qkv, B, T, n_head, p_drop=0.0, salt=0):
+    """Causal multi-head self-attention over the fused projection ``qkv [B, T, 3E]`` -> ``[B, T, E]``
+    (head dim 64).  Native path: tcgen05 flash-style kernels (``csrc/attn.cu``); library path: SDPA."""
+    E = qkv.shape[-1] // 3
+    if _use_native_bf16(qkv):
+        from . import tfm
+        if tfm.attention_supported(qkv, T, n_head):
+            y = tfm.attention(qkv, B, T, n_head, p_drop, salt, tfm.dropout_state(qkv.device) if p_drop > 0 else None)
+            return y.view(B, T, E)
+    hd = E // n_head
+    q, k, v = qkv.view(B, T, 3 * E).split(E, dim=2)
+    q = q.view(B, T, n_head, hd).transpose(1, 2)
+    k = k.view(B, T, n_head, hd).transpose(1, 2)
+    v = v.view(B, T, n_head, hd).transpose(1, 2)
+    y = F.scaled_dot_product_attention(q, k, v, is_causal=True, dropout_p=p_drop)
+    return y.transpose(1, 2).reshape(B, T, E)
+
+
+def embed(wte, wpe, input_ids, token_type_ids, p_drop=0.0, salt=0):
+    """``dropout(wte[ids] + wpe[pos] + wte[token_types])`` -> fp32 ``[..., T, E]``."""
+    T = input_ids.shape[-1]
+    if _use_native_bf16(wte):
+        from . import tfm
+        if tfm.embed_supported(wte, wpe):
+            return tfm.embed(wte, wpe, input_ids, token_type_ids, T, p_drop, salt,
+                             tfm.dropout_state(wte.device) if p_drop > 0 else None)
+    pos = torch.arange(T, device=input_ids.device)
+    x = F.embedding(input_ids, wte) + F.embedding(pos, wpe)
+    if token_type_ids is not None:
+        x = x + F.embedding(token_type_ids, wte)
+    return F.dropout(x, p_drop, training=True) if p_drop > 0 else x
+
+
+def advance_dropout(device) -> None:
+    """Once per training forward pass: move every native dropout site to a fresh mask."""
+    if _native and _precision == "bf16" and torch.device(device).type == "cuda":
+        from . import tfm
+        tfm.dropout_state(device).advance()
 
 
 def gelu_tanh(x):

@@ -4,9 +4,13 @@ the native path is on; plain PyTorch otherwise.  Reference: the ATen ops inside
 pytorch_transformers' GPT-2 that /root/reference/CommEfficient/gpt2_train.py:76-99 drives."""
 from __future__ import annotations
 
+import ctypes as _ctypes
+
 import torch
 
 from . import native
+
+_c_u32 = _ctypes.c_uint32
 
 native.register_signatures({
     "ceb_softmax_ce_fwd": ([native.c_ptr, native.c_i64, native.c_i64, native.c_i32, native.c_ptr, native.c_i64,
@@ -24,6 +28,16 @@ native.register_signatures({
     "ceb_add_layernorm_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
                                native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32,
                                native.c_ptr], native.c_i32),
+    "ceb_add_layernorm_drop_fwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                                    native.c_ptr, native.c_ptr, native.c_i64, native.c_i32, native.c_f32, native.c_f32,
+                                    native.c_ptr, _c_u32, native.c_ptr], native.c_i32),
+    "ceb_add_layernorm_drop_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                                    native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32,
+                                    native.c_f32, native.c_ptr, _c_u32, native.c_ptr], native.c_i32),
+    "ceb_embed_fwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32,
+                       native.c_i32, native.c_f32, native.c_ptr, _c_u32, native.c_ptr], native.c_i32),
+    "ceb_embed_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32,
+                       native.c_i32, native.c_f32, native.c_ptr, _c_u32, native.c_ptr], native.c_i32),
     "ceb_segment_bn_fwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32, native.c_i32,
                             native.c_i32, native.c_ptr, native.c_ptr, native.c_f32, native.c_ptr, native.c_ptr,
                             native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr], native.c_i32),
@@ -188,7 +202,7 @@ class _AddLayerNorm(torch.autograd.Function):
     backward and emits it once in fp32 (for the stream) and once in bf16 (for the branch)."""
 
     @staticmethod
-    def forward(ctx, resid, branch, weight, bias, eps):
+    def forward(ctx, resid, branch, weight, bias, eps, p_drop=0.0, salt=0, state=None):
         E = resid.shape[-1]
         r2 = resid.reshape(-1, E).float().contiguous()
         b2 = branch.reshape(-1, E).to(torch.bfloat16).contiguous()
@@ -200,11 +214,13 @@ class _AddLayerNorm(torch.autograd.Function):
         rstd = torch.empty(rows, dtype=torch.float32, device=dev)
         w = weight.detach().float().contiguous()
         b = bias.detach().float().contiguous()
-        native.call("ceb_add_layernorm_fwd", native.ptr(r2), native.ptr(b2), native.ptr(w), native.ptr(b),
+        seed = state.seed if (state is not None and p_drop > 0) else None
+        native.call("ceb_add_layernorm_drop_fwd", native.ptr(r2), native.ptr(b2), native.ptr(w), native.ptr(b),
                     native.ptr(new_resid), native.ptr(y), native.ptr(mean), native.ptr(rstd), rows, E, float(eps),
-                    native.stream_ptr(dev))
+                    float(p_drop), native.ptr(seed), int(salt), native.stream_ptr(dev))
         ctx.save_for_backward(new_resid, w, mean, rstd)
         ctx.shape, ctx.branch_dtype, ctx.params = resid.shape, branch.dtype, (weight, bias)
+        ctx.drop = (float(p_drop), int(salt), seed)
         return new_resid.view(resid.shape), y.view(resid.shape)
 
     @staticmethod
@@ -223,12 +239,166 @@ class _AddLayerNorm(torch.autograd.Function):
                   and weight.grad.is_contiguous() and bias.grad.is_contiguous())
         dg = weight.grad if direct else torch.zeros(E, dtype=torch.float32, device=dev)
         db = bias.grad if direct else torch.zeros(E, dtype=torch.float32, device=dev)
-        native.call("ceb_add_layernorm_bwd", native.ptr(dyb), native.ptr(new_resid), native.ptr(w), native.ptr(mean),
-                    native.ptr(rstd), native.ptr(dres), native.ptr(dx), native.ptr(dxb), native.ptr(dg), native.ptr(db),
-                    rows, E, native.stream_ptr(dev))
+        p_drop, salt, seed = ctx.drop
+        native.call("ceb_add_layernorm_drop_bwd", native.ptr(dyb), native.ptr(new_resid), native.ptr(w),
+                    native.ptr(mean), native.ptr(rstd), native.ptr(dres), native.ptr(dx), native.ptr(dxb),
+                    native.ptr(dg), native.ptr(db), rows, E, p_drop, native.ptr(seed), salt, native.stream_ptr(dev))
         return (dx.view(ctx.shape), dxb.view(ctx.shape).to(ctx.branch_dtype), (None if direct else dg),
-                (None if direct else db), None)
+                (None if direct else db), None, None, None, None)
 
 
-def add_layer_norm(resid, branch, weight, bias, eps):
-    return _AddLayerNorm.apply(resid, branch, weight, bias, eps)
+def add_layer_norm(resid, branch, weight, bias, eps, p_drop=0.0, salt=0, state=None):
+    """``(resid + dropout_p(branch), LayerNorm(of that))``; the dropout mask is regenerated in the backward."""
+    return _AddLayerNorm.apply(resid, branch, weight, bias, eps, p_drop, salt, state)
+
+
+# ---------------------------------------------------------------------------- attention (csrc/attn.cu)
+native.register_signatures({
+    "ceb_attention_fwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
+                           native.c_i32, native.c_f32, native.c_ptr, _c_u32,
+                           native.c_ptr], native.c_i32),
+    "ceb_attention_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                           native.c_i32, native.c_i32, native.c_i32, native.c_i32, native.c_f32, native.c_ptr,
+                           _c_u32, native.c_ptr], native.c_i32),
+})
+
+
+class DropoutState:
+    """Device-resident seed shared by every native dropout site of one model.  ``advance()`` (one tiny
+    in-place add, capturable in a CUDA graph) is called once per forward pass; the kernels read the value
+    from device memory, so a replayed graph draws fresh masks every round and the backward of the same
+    round regenerates exactly the masks of its forward.  Each site passes its own ``salt``."""
+
+    def __init__(self, device, seed: int = 0):
+        self.seed = torch.full((1,), int(seed) * 0x9E3779B1 & 0x7FFFFFFFFFFFFFFF, dtype=torch.int64, device=device)
+
+    def advance(self):
+        self.seed.add_(0x632BE59BD9B4E019 & 0x7FFFFFFFFFFFFFFF)
+
+
+_DROPOUT_STATES = {}
+
+
+def dropout_state(device, seed: int = 0) -> DropoutState:
+    key = torch.device(device).index or 0
+    st = _DROPOUT_STATES.get(key)
+    if st is None:
+        st = DropoutState(device, seed)
+        _DROPOUT_STATES[key] = st
+    return st
+
+
+def attention_supported(qkv: torch.Tensor, T: int, n_head: int) -> bool:
+    E3 = qkv.shape[-1]
+    return (qkv.is_cuda and E3 % 3 == 0 and E3 // 3 == n_head * 64 and T <= 1024)
+
+
+class _Attention(torch.autograd.Function):
+    """Causal self-attention over the fused projection output ``qkv [B*T, 3E]`` -> ``[B*T, E]`` on the tcgen05
+    kernels (``ceb_attention_fwd / _bwd``): no head transposes, no materialised scores, dropout regenerated
+    in the backward from (seed, salt, position)."""
+
+    @staticmethod
+    def forward(ctx, qkv, B, T, H, p_drop, salt, state):
+        E = qkv.shape[-1] // 3
+        q2 = qkv.reshape(B * T, 3 * E)
+        q2 = (q2 if q2.dtype == torch.bfloat16 else q2.to(torch.bfloat16)).contiguous()
+        dev = qkv.device
+        out = torch.empty((B * T, E), dtype=torch.bfloat16, device=dev)
+        lse = torch.empty((B * H, T), dtype=torch.float32, device=dev)
+        seed = state.seed if (state is not None and p_drop > 0) else None
+        native.call("ceb_attention_fwd", native.ptr(q2), native.ptr(out), native.ptr(lse), B, T, H, E, float(p_drop),
+                    native.ptr(seed), int(salt), native.stream_ptr(dev))
+        ctx.save_for_backward(q2, out, lse)
+        ctx.cfg = (B, T, H, E, float(p_drop), int(salt), seed, qkv.dtype, qkv.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q2, out, lse = ctx.saved_tensors
+        B, T, H, E, p_drop, salt, seed, in_dtype, in_shape = ctx.cfg
+        dev = q2.device
+        do = dout.reshape(B * T, E)
+        do = (do if do.dtype == torch.bfloat16 else do.to(torch.bfloat16)).contiguous()
+        dqkv = torch.empty_like(q2)
+        scratch = torch.empty((B * T, E), dtype=torch.float32, device=dev) if T > 128 else None
+        native.call("ceb_attention_bwd", native.ptr(q2), native.ptr(out), native.ptr(do), native.ptr(lse),
+                    native.ptr(dqkv), native.ptr(scratch), B, T, H, E, p_drop, native.ptr(seed), salt,
+                    native.stream_ptr(dev))
+        return dqkv.view(in_shape).to(in_dtype), None, None, None, None, None, None
+
+
+def attention(qkv, B, T, n_head, p_drop=0.0, salt=0, state=None):
+    return _Attention.apply(qkv, B, T, n_head, p_drop, salt, state)
+
+
+def attention_keep_mask(seed: int, salt: int, B: int, H: int, T: int, p_drop: float, device="cpu") -> torch.Tensor:
+    """The dropout keep-mask ``[B, H, T, T]`` the attention kernels generate (pure function of seed / salt /
+    position) -- the test oracle re-implements the hash with torch integer ops."""
+    M32 = 0xFFFFFFFF
+
+    def h(x):
+        x = x & M32
+        x = x ^ (x >> 16); x = (x * 0x7feb352d) & M32
+        x = x ^ (x >> 15); x = (x * 0x846ca68b) & M32
+        return x ^ (x >> 16)
+    seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    lo, hi = seed & M32, seed >> 32
+    bh = torch.arange(B * H, dtype=torch.int64, device=device).view(B * H, 1)
+    q = torch.arange(T, dtype=torch.int64, device=device).view(1, T)
+    rowkey = h(lo ^ h(hi ^ (int(salt) & M32) ^ h(bh * T + q)))                       # [BH, T]
+    kv = torch.arange(T, dtype=torch.int64, device=device).view(1, 1, T)
+    hv = h(rowkey.unsqueeze(-1) + kv)
+    th = min(int(p_drop * 4294967296.0), M32)
+    th = max(th, 1)
+    return (hv >= th).view(B, H, T, T)
+
+
+# ---------------------------------------------------------------------------- input embedding
+class _Embed(torch.autograd.Function):
+    """``dropout(wte[ids] + wpe[position] + wte[token_type])`` as ONE gather kernel producing the fp32 residual
+    stream, and its backward as vector reductions straight into the (flat) fp32 gradients of the two tables."""
+
+    @staticmethod
+    def forward(ctx, wte, wpe, ids, token_types, T, p_drop, salt, state):
+        E = wte.shape[1]
+        ids2 = ids.reshape(-1).contiguous()
+        tt2 = token_types.reshape(-1).contiguous() if token_types is not None else None
+        rows = ids2.numel()
+        dev = wte.device
+        x = torch.empty((rows, E), dtype=torch.float32, device=dev)
+        seed = state.seed if (state is not None and p_drop > 0) else None
+        native.call("ceb_embed_fwd", native.ptr(ids2), native.ptr(tt2), native.ptr(wte.detach()), native.ptr(wpe.detach()),
+                    native.ptr(x), rows, int(T), E, float(p_drop), native.ptr(seed), int(salt), native.stream_ptr(dev))
+        ctx.save_for_backward(ids2, tt2) if tt2 is not None else ctx.save_for_backward(ids2)
+        ctx.has_tt = tt2 is not None
+        ctx.cfg = (int(T), float(p_drop), int(salt), seed, wte, wpe)
+        return x.view(*ids.shape, E)
+
+    @staticmethod
+    def backward(ctx, dx):
+        saved = ctx.saved_tensors
+        ids2, tt2 = saved[0], (saved[1] if ctx.has_tt else None)
+        T, p_drop, salt, seed, wte, wpe = ctx.cfg
+        E = wte.shape[1]
+        dev = dx.device
+        d2 = dx.reshape(-1, E).float().contiguous()
+
+        def target(p):
+            ok = isinstance(p, torch.nn.Parameter) and p.grad is not None and p.grad.is_contiguous() \
+                and p.grad.dtype == torch.float32 and p.grad.data_ptr() % 16 == 0
+            return (p.grad, True) if ok else (torch.zeros_like(p, dtype=torch.float32), False)
+        gte, d1 = target(wte)
+        gpe, d2_ = target(wpe)
+        native.call("ceb_embed_bwd", native.ptr(ids2), native.ptr(tt2), native.ptr(d2), native.ptr(gte), native.ptr(gpe),
+                    ids2.numel(), T, E, p_drop, native.ptr(seed), salt, native.stream_ptr(dev))
+        return (None if d1 else gte), (None if d2_ else gpe), None, None, None, None, None, None
+
+
+def embed_supported(wte, wpe) -> bool:
+    return (wte.is_cuda and wte.dtype == torch.float32 and wpe.dtype == torch.float32 and wte.shape[1] % 4 == 0
+            and wte.is_contiguous() and wpe.is_contiguous() and wte.data_ptr() % 16 == 0 and wpe.data_ptr() % 16 == 0)
+
+
+def embed(wte, wpe, ids, token_types, T, p_drop=0.0, salt=0, state=None):
+    return _Embed.apply(wte, wpe, ids, token_types, T, p_drop, salt, state)

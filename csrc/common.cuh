@@ -71,6 +71,25 @@ __device__ __forceinline__ void red_add_f32(float* addr, float v) {
   asm volatile("red.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
 }
 
+// ---- counter-hash dropout shared by the attention, embedding and add+LayerNorm kernels ----------------
+// An element keeps its value iff ceb_hash32(rowkey + column) >= thresh, thresh = p * 2^32; rowkey mixes the
+// device-resident seed, the call site's salt and the row.  Pure function of its inputs: the backward pass
+// regenerates the mask instead of storing it.
+__device__ __forceinline__ uint32_t ceb_hash32(uint32_t x) {        // "lowbias32" integer finaliser
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+__device__ __forceinline__ uint32_t ceb_drop_rowkey(const unsigned long long* seed_dev, uint32_t salt, uint32_t row) {
+  const unsigned long long seed = seed_dev ? __ldg(seed_dev) : 0ull;
+  return ceb_hash32((uint32_t)seed ^ ceb_hash32((uint32_t)(seed >> 32) ^ salt ^ ceb_hash32(row)));
+}
+static inline uint32_t ceb_drop_thresh(float p_drop) {
+  if (!(p_drop > 0.f)) return 0u;
+  const double th = (double)p_drop * 4294967296.0;
+  const uint32_t t = th >= 4294967295.0 ? 0xffffffffu : (uint32_t)th;
+  return t == 0 ? 1u : t;
+}
+
 __device__ __forceinline__ uint32_t abs_key(float v) {
   // Monotone key of |v|; NaN maps to 0 so it is never preferred by top-k.
   uint32_t b = __float_as_uint(v) & 0x7fffffffu;

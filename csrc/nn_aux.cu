@@ -5,6 +5,14 @@
 #include <cuda_bf16.h>
 #include "common.cuh"
 
+CEB_API int ceb_add_layernorm_drop_fwd(const float* x, const void* branch_bf16, const float* gamma, const float* beta,
+                                       float* resid_out, void* y_bf16, float* mean, float* rstd, int64_t rows, int E,
+                                       float eps, float p_drop, const uint64_t* seed_dev, uint32_t salt, void* stream);
+CEB_API int ceb_add_layernorm_drop_bwd(const void* dy_bf16, const float* resid, const float* gamma, const float* mean,
+                                       const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
+                                       float* dbeta, int64_t rows, int E, float p_drop, const uint64_t* seed_dev,
+                                       uint32_t salt, void* stream);
+
 // ------------------------------------------------------------------ softmax cross-entropy
 // One block per row.  Forward: loss[row] = logsumexp(row) - row[label] (0 when label == ignore),
 // lse[row] saved.  Backward (in place allowed): d[row][j] = g[row] * (exp(l[j] - lse) - [j == label]).
@@ -187,16 +195,26 @@ CEB_API int ceb_softmax_ce_bwd_rows(const void* logits_bf16, void* dlogits_bf16,
 __global__ void __launch_bounds__(256)
 ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
               __nv_bfloat16* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd, int64_t rows,
-              int E, float eps, const __nv_bfloat16* __restrict__ branch, float* __restrict__ resid_out) {
+              int E, float eps, const __nv_bfloat16* __restrict__ branch, float* __restrict__ resid_out,
+              uint32_t drop_thresh = 0, float inv_keep = 1.f, const unsigned long long* __restrict__ seed_dev = nullptr,
+              uint32_t salt = 0) {
   const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
   const float* xr = x + row * E;
   if (branch) {
-    // fused residual add: resid_out = x + branch (the new fp32 residual stream), normalised below
+    // fused residual add: resid_out = x + dropout(branch) (the new fp32 residual stream), normalised below
     const __nv_bfloat16* br = branch + row * E;
     float* ro = resid_out + row * E;
-    for (int j = lane; j < E; j += 32) ro[j] = xr[j] + __bfloat162float(br[j]);
+    if (drop_thresh) {
+      const uint32_t rowkey = ceb_drop_rowkey(seed_dev, salt, (uint32_t)row);
+      for (int j = lane; j < E; j += 32) {
+        const float keep = ceb_hash32(rowkey + (uint32_t)j) >= drop_thresh ? inv_keep : 0.f;
+        ro[j] = fmaf(__bfloat162float(br[j]), keep, xr[j]);
+      }
+    } else {
+      for (int j = lane; j < E; j += 32) ro[j] = xr[j] + __bfloat162float(br[j]);
+    }
     __syncwarp();
     xr = ro;
   }
@@ -263,10 +281,22 @@ CEB_API int ceb_layernorm_fwd(const float* x, const float* gamma, const float* b
 CEB_API int ceb_add_layernorm_fwd(const float* x, const void* branch_bf16, const float* gamma, const float* beta,
                                   float* resid_out, void* y_bf16, float* mean, float* rstd, int64_t rows, int E,
                                   float eps, void* stream) {
+  return ceb_add_layernorm_drop_fwd(x, branch_bf16, gamma, beta, resid_out, y_bf16, mean, rstd, rows, E, eps, 0.f,
+                                    nullptr, 0, stream);
+}
+
+// Same with dropout on the branch before the add: resid_out = x + dropout_p(branch).  The mask is a pure
+// function of (*seed_dev, salt, row, column) -- see common.cuh -- so nothing is stored for the backward.
+CEB_API int ceb_add_layernorm_drop_fwd(const float* x, const void* branch_bf16, const float* gamma, const float* beta,
+                                       float* resid_out, void* y_bf16, float* mean, float* rstd, int64_t rows, int E,
+                                       float eps, float p_drop, const uint64_t* seed_dev, uint32_t salt, void* stream) {
   CEB_REQUIRE(x && branch_bf16 && gamma && beta && resid_out && y_bf16 && mean && rstd && rows > 0 && E > 0,
               "ceb_add_layernorm_fwd: bad arguments");
+  CEB_REQUIRE(p_drop >= 0.f && p_drop < 1.f && rows < (1ll << 32), "ceb_add_layernorm_fwd: p_drop=%f rows=%lld", p_drop, (long long)rows);
+  const uint32_t th = ceb_drop_thresh(p_drop);
   ln_fwd_kernel<<<(unsigned)ceb_cdiv(rows, 8), 256, 0, (cudaStream_t)stream>>>(
-      x, gamma, beta, (__nv_bfloat16*)y_bf16, mean, rstd, rows, E, eps, (const __nv_bfloat16*)branch_bf16, resid_out);
+      x, gamma, beta, (__nv_bfloat16*)y_bf16, mean, rstd, rows, E, eps, (const __nv_bfloat16*)branch_bf16, resid_out,
+      th, th ? 1.f / (1.f - p_drop) : 1.f, (const unsigned long long*)seed_dev, salt);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -281,7 +311,8 @@ __global__ void __launch_bounds__(256)
 ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
                   const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dx,
                   float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t rows,
-                  const float* __restrict__ dres, __nv_bfloat16* __restrict__ dx_bf16) {
+                  const float* __restrict__ dres, __nv_bfloat16* __restrict__ dx_bf16, uint32_t drop_thresh = 0,
+                  float inv_keep = 1.f, const unsigned long long* __restrict__ seed_dev = nullptr, uint32_t salt = 0) {
   constexpr int E = 128 * G;
   __shared__ float sh[2 * E];
   for (int j = threadIdx.x; j < 2 * E; j += blockDim.x) sh[j] = 0.f;
@@ -326,7 +357,14 @@ ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict_
         o.x += r4.x; o.y += r4.y; o.z += r4.z; o.w += r4.w;
       }
       *(float4*)(dx + row * E + g * 128 + lane * 4) = o;
-      if (dx_bf16) {   // the same gradient for the bf16 branch that was added to the stream
+      if (dx_bf16) {   // the same gradient for the bf16 branch that was added to the stream (through its dropout mask)
+        if (drop_thresh) {
+          const uint32_t key = ceb_drop_rowkey(seed_dev, salt, (uint32_t)row) + (uint32_t)(g * 128 + lane * 4);
+          o.x *= ceb_hash32(key) >= drop_thresh ? inv_keep : 0.f;
+          o.y *= ceb_hash32(key + 1) >= drop_thresh ? inv_keep : 0.f;
+          o.z *= ceb_hash32(key + 2) >= drop_thresh ? inv_keep : 0.f;
+          o.w *= ceb_hash32(key + 3) >= drop_thresh ? inv_keep : 0.f;
+        }
         const __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
         uint2 pk; pk.x = *(const uint32_t*)&lo; pk.y = *(const uint32_t*)&hi;
         *(uint2*)(dx_bf16 + row * E + g * 128 + lane * 4) = pk;
@@ -353,11 +391,12 @@ ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict_
 template <int G>
 static void launch_ln_bwd_vec(const void* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                               float* dx, float* dgamma, float* dbeta, int64_t rows, cudaStream_t st,
-                              const float* dres = nullptr, void* dx_bf16 = nullptr) {
+                              const float* dres = nullptr, void* dx_bf16 = nullptr, uint32_t drop_thresh = 0,
+                              float inv_keep = 1.f, const unsigned long long* seed_dev = nullptr, uint32_t salt = 0) {
   int blocks = ceb_num_sms() * 2;
   if (blocks > ceb_cdiv(rows, 8)) blocks = (int)ceb_cdiv(rows, 8);
   ln_bwd_vec_kernel<G><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows,
-                                              dres, (__nv_bfloat16*)dx_bf16);
+                                              dres, (__nv_bfloat16*)dx_bf16, drop_thresh, inv_keep, seed_dev, salt);
 }
 
 static bool ln_vec_width(int E) { return E == 128 || E == 256 || E == 512 || E == 768 || E == 1024 || E == 1280; }
@@ -380,11 +419,24 @@ static void dispatch_ln_bwd_vec(int E, A... args) {
 CEB_API int ceb_add_layernorm_bwd(const void* dy_bf16, const float* resid, const float* gamma, const float* mean,
                                   const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
                                   float* dbeta, int64_t rows, int E, void* stream) {
+  return ceb_add_layernorm_drop_bwd(dy_bf16, resid, gamma, mean, rstd, dres, dx, dx_bf16, dgamma, dbeta, rows, E, 0.f,
+                                    nullptr, 0, stream);
+}
+
+// Backward of ceb_add_layernorm_drop_fwd: dx_bf16 (the branch's gradient) additionally passes through the
+// regenerated dropout mask; dx (the stream's gradient) does not.
+CEB_API int ceb_add_layernorm_drop_bwd(const void* dy_bf16, const float* resid, const float* gamma, const float* mean,
+                                       const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
+                                       float* dbeta, int64_t rows, int E, float p_drop, const uint64_t* seed_dev,
+                                       uint32_t salt, void* stream) {
   CEB_REQUIRE(dy_bf16 && resid && gamma && mean && rstd && dx && dgamma && dbeta && rows > 0, "ceb_add_layernorm_bwd: bad arguments");
   CEB_REQUIRE(ln_vec_width(E), "ceb_add_layernorm_bwd: unsupported width E=%d", E);
   CEB_REQUIRE(((((uintptr_t)dy_bf16) | ((uintptr_t)resid) | ((uintptr_t)dx) | ((uintptr_t)gamma) | ((uintptr_t)dres) |
                 ((uintptr_t)dx_bf16)) & 15) == 0, "ceb_add_layernorm_bwd: tensors must be 16-byte aligned");
-  dispatch_ln_bwd_vec(E, dy_bf16, resid, gamma, mean, rstd, dx, dgamma, dbeta, rows, (cudaStream_t)stream, dres, dx_bf16);
+  CEB_REQUIRE(p_drop >= 0.f && p_drop < 1.f, "ceb_add_layernorm_bwd: p_drop=%f", p_drop);
+  const uint32_t th = ceb_drop_thresh(p_drop);
+  dispatch_ln_bwd_vec(E, dy_bf16, resid, gamma, mean, rstd, dx, dgamma, dbeta, rows, (cudaStream_t)stream, dres, dx_bf16,
+                      th, th ? 1.f / (1.f - p_drop) : 1.f, (const unsigned long long*)seed_dev, salt);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -670,6 +722,97 @@ CEB_API int ceb_linear_ce_head_f32(const float* feat, const float* W, float scal
                                    int C, const float* g, float* loss, float* correct, float* dfeat, float* dW,
                                    void* stream) {
   return linear_ce_head_impl<float>(feat, W, scale, labels, N, F, C, g, loss, correct, dfeat, dW, stream);
+}
+
+// ------------------------------------------------------------------ GPT-2 input embedding (gather + add + dropout)
+// x[row][E] (fp32) = dropout_p( wte[ids[row]] + wpe[row % T] + (tt ? wte[tt[row]] : 0) ), one warp per row.
+// Replaces nn.Embedding x3, two adds and nn.Dropout of the reference model's GPT2Model.forward
+// (pytorch_transformers, driven from /root/reference/CommEfficient/gpt2_train.py:88-99).
+__global__ void __launch_bounds__(256)
+embed_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__ tt, const float* __restrict__ wte,
+                 const float* __restrict__ wpe, float* __restrict__ x, int64_t rows, int T, int E, uint32_t drop_thresh,
+                 float inv_keep, const unsigned long long* __restrict__ seed_dev, uint32_t salt) {
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const float4* a = reinterpret_cast<const float4*>(wte + ids[row] * E);
+  const float4* b = reinterpret_cast<const float4*>(wpe + (row % T) * E);
+  const float4* c = tt ? reinterpret_cast<const float4*>(wte + tt[row] * E) : nullptr;
+  float4* o = reinterpret_cast<float4*>(x + row * E);
+  const uint32_t rowkey = drop_thresh ? ceb_drop_rowkey(seed_dev, salt, (uint32_t)row) : 0u;
+  for (int j = lane; j < E / 4; j += 32) {
+    float4 v = __ldg(a + j);
+    const float4 pb = __ldg(b + j);
+    v.x += pb.x; v.y += pb.y; v.z += pb.z; v.w += pb.w;
+    if (c) { const float4 pc = __ldg(c + j); v.x += pc.x; v.y += pc.y; v.z += pc.z; v.w += pc.w; }
+    if (drop_thresh) {
+      const uint32_t key = rowkey + (uint32_t)(j * 4);
+      v.x *= ceb_hash32(key) >= drop_thresh ? inv_keep : 0.f;
+      v.y *= ceb_hash32(key + 1) >= drop_thresh ? inv_keep : 0.f;
+      v.z *= ceb_hash32(key + 2) >= drop_thresh ? inv_keep : 0.f;
+      v.w *= ceb_hash32(key + 3) >= drop_thresh ? inv_keep : 0.f;
+    }
+    o[j] = v;
+  }
+}
+
+// dwte[ids[row]] += g, dwpe[row % T] += g, dwte[tt[row]] += g with g = dx[row] through the regenerated mask:
+// 16-byte vector reductions straight into the flat fp32 gradient (no sort, no dense [rows][E] temporaries).
+__global__ void __launch_bounds__(256)
+embed_bwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__ tt, const float* __restrict__ dx,
+                 float* __restrict__ dwte, float* __restrict__ dwpe, int64_t rows, int T, int E, uint32_t drop_thresh,
+                 float inv_keep, const unsigned long long* __restrict__ seed_dev, uint32_t salt) {
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float* a = dwte + ids[row] * E;
+  float* b = dwpe + (row % T) * E;
+  float* c = tt ? dwte + tt[row] * E : nullptr;
+  const float4* g4 = reinterpret_cast<const float4*>(dx + row * E);
+  const uint32_t rowkey = drop_thresh ? ceb_drop_rowkey(seed_dev, salt, (uint32_t)row) : 0u;
+  for (int j = lane; j < E / 4; j += 32) {
+    float4 v = __ldg(g4 + j);
+    if (drop_thresh) {
+      const uint32_t key = rowkey + (uint32_t)(j * 4);
+      v.x *= ceb_hash32(key) >= drop_thresh ? inv_keep : 0.f;
+      v.y *= ceb_hash32(key + 1) >= drop_thresh ? inv_keep : 0.f;
+      v.z *= ceb_hash32(key + 2) >= drop_thresh ? inv_keep : 0.f;
+      v.w *= ceb_hash32(key + 3) >= drop_thresh ? inv_keep : 0.f;
+    }
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a + j * 4), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(b + j * 4), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    if (c) asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(c + j * 4), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+  }
+}
+
+static int embed_check(const char* who, const void* ids, const void* w1, const void* w2, const void* x, int64_t rows, int T, int E) {
+  CEB_REQUIRE(ids && w1 && w2 && x && rows > 0 && T > 0 && rows < (1ll << 32), "%s: bad arguments", who);
+  CEB_REQUIRE(E % 4 == 0 && ((((uintptr_t)w1) | ((uintptr_t)w2) | ((uintptr_t)x)) & 15) == 0,
+              "%s: E %% 4 == 0 and 16-byte aligned tables needed (E=%d)", who, E);
+  return 0;
+}
+
+CEB_API int ceb_embed_fwd(const int64_t* ids, const int64_t* token_types, const float* wte, const float* wpe, float* x,
+                          int64_t rows, int T, int E, float p_drop, const uint64_t* seed_dev, uint32_t salt, void* stream) {
+  if (int e = embed_check("ceb_embed_fwd", ids, wte, wpe, x, rows, T, E)) return e;
+  const uint32_t th = ceb_drop_thresh(p_drop);
+  embed_fwd_kernel<<<(unsigned)ceb_cdiv(rows, 8), 256, 0, (cudaStream_t)stream>>>(
+      ids, token_types, wte, wpe, x, rows, T, E, th, th ? 1.f / (1.f - p_drop) : 1.f, (const unsigned long long*)seed_dev, salt);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+// dwte / dwpe are accumulated (+=): pass the flat gradient views.
+CEB_API int ceb_embed_bwd(const int64_t* ids, const int64_t* token_types, const float* dx, float* dwte, float* dwpe,
+                          int64_t rows, int T, int E, float p_drop, const uint64_t* seed_dev, uint32_t salt, void* stream) {
+  if (int e = embed_check("ceb_embed_bwd", ids, dwte, dwpe, dx, rows, T, E)) return e;
+  const uint32_t th = ceb_drop_thresh(p_drop);
+  embed_bwd_kernel<<<(unsigned)ceb_cdiv(rows, 8), 256, 0, (cudaStream_t)stream>>>(
+      ids, token_types, dx, dwte, dwpe, rows, T, E, th, th ? 1.f / (1.f - p_drop) : 1.f, (const unsigned long long*)seed_dev, salt);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
 }
 
 // ------------------------------------------------------------------ segment-wise BatchNorm (NHWC bf16)

@@ -45,3 +45,18 @@ def _deterministic_inputs(request):
     torch.manual_seed(seed)             # seeds the CUDA generators too
     np.random.seed(seed % (2 ** 32))
     yield
+
+
+@pytest.fixture(autouse=True)
+def _default_nn_state():
+    """The tensor-core switch and the precision are process-wide: start every test from the same state
+    (native layers off, bf16 operands) so that no test's result depends on which test ran before it."""
+    from commefficient_b200.ops import nn as nnops
+    nnops.set_native(False)
+    nnops._precision = "bf16"
+    try:
+        from commefficient_b200.ops import tc
+        tc._PRECISION = "bf16"
+    except Exception:
+        pass
+    yield
