@@ -31,13 +31,16 @@ def main():
     ap.add_argument("--no_native_nn", action="store_true")
     ap.add_argument("--no_client_batching", action="store_true")
     ap.add_argument("--no_cuda_graphs", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "tf32", "fp32"])
+    ap.add_argument("--no_sketch_overlap", action="store_true")
+    ap.add_argument("--mode", default="sketch")
     cfg = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     W = cfg.clients_per_gpu * world
-    args = make_args(mode="sketch", error_type="virtual", local_momentum=0.0, virtual_momentum=0.9, num_workers=W,
+    args = make_args(mode=cfg.mode, error_type="virtual" if cfg.mode == "sketch" else "none", no_sketch_overlap=cfg.no_sketch_overlap, local_momentum=0.0, virtual_momentum=0.9, num_workers=W,
                      num_clients=17568, local_batch_size=cfg.local_batch, dataset_name="PERSONA", device="cuda",
                      num_results_train=1, no_native_nn=cfg.no_native_nn, no_client_batching=cfg.no_client_batching, no_cuda_graphs=cfg.no_cuda_graphs,
-                     weight_decay=0.0)
+                     weight_decay=0.0, precision=cfg.precision)
     rt = init_runtime(args)
     torch.manual_seed(0)
     model = models.GPT2DoubleHeadsModel()
@@ -81,7 +84,7 @@ def main():
         print(json.dumps({"model": "GPT2DoubleHeads small", "d": fed.fp.numel, "mode": "sketch", "n_gpus": world,
                           "clients_per_round": W, "sequences_per_client": cfg.local_batch * 2, "seq_len": cfg.seq,
                           "ms_per_round": ms, "clients_per_sec": W / (ms / 1e3),
-                          "tokens_per_sec": n * 2 * cfg.seq / (ms / 1e3), "native_nn": not cfg.no_native_nn, "cuda_graphs": not cfg.no_cuda_graphs,
+                          "tokens_per_sec": n * 2 * cfg.seq / (ms / 1e3), "native_nn": not cfg.no_native_nn, "dtype": cfg.precision, "cuda_graphs": not cfg.no_cuda_graphs,
                           "client_batching": fed.worker.can_batch_clients(), "native_launches": native.launch_count(),
                           "last_loss": float(out[0].mean())}))
     rt.shutdown()

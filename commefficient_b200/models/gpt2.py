@@ -134,7 +134,7 @@ class GPT2Model(nn.Module):
         nn.init.normal_(self.wte.weight, 0.0, cfg.initializer_range)
         nn.init.normal_(self.wpe.weight, 0.0, cfg.initializer_range)
 
-    def forward(self, input_ids, token_type_ids=None):
+    def forward(self, input_ids, token_type_ids=None, flat_params=None):
         # native path: every dropout of the trunk is applied INSIDE the kernel that produces / consumes the
         # tensor (embedding gather, attention probabilities, the residual add + LayerNorm); masks come from a
         # counter hash of (device seed, site salt, position) and are regenerated in the backward
@@ -150,7 +150,23 @@ class GPT2Model(nn.Module):
         blocks = list(self.h)
         first = blocks[0].ln_1 if blocks else self.ln_f
         h = nnops.layer_norm(x, first.weight, first.bias, first.eps)
+        report = (flat_params is not None and flat_params.on_range_final is not None and torch.is_grad_enabled()
+                  and x.requires_grad)
         for i, block in enumerate(blocks):
+            if report:
+                # The gradient of the stream entering block i is complete only after the whole backward of block i
+                # (and of the LayerNorm that follows it) has run: everything from this block's attention weights
+                # (from its ln_1 for block 0) up to and including the next block's ln_1 / ln_f is final then, and
+                # the consumer may start sketching it while blocks i-1 .. 0 are still in their backward pass.
+                first = block.ln_1.weight if i == 0 else block.attn.c_attn.weight
+                nxt_ln = blocks[i + 1].ln_1 if i + 1 < len(blocks) else self.ln_f
+                params = [p for p in flat_params.params]
+                ids = {id(p): k for k, p in enumerate(params)}
+                lo_k, hi_k = ids.get(id(first)), ids.get(id(nxt_ln.bias))
+                if lo_k is not None and hi_k is not None and hi_k > lo_k:
+                    lo = flat_params.offsets[lo_k]
+                    hi = flat_params.offsets[hi_k] + flat_params.sizes[hi_k]
+                    x.register_hook(lambda g, lo=lo, hi=hi: flat_params.range_final(lo, hi))
             pr = block.attn.resid_dropout.p if fused else 0.0
             x, h = nnops.add_layer_norm(x, block.attn(h, salt=16 * i + 2, fuse_resid_dropout=fused), block.ln_2.weight,
                                         block.ln_2.bias, block.ln_2.eps, p_drop=pr, salt=16 * i + 3)
@@ -252,7 +268,7 @@ class GPT2DoubleHeadsModel(nn.Module):
         T = shape[-1]
         flat_ids = input_ids.reshape(-1, T)
         flat_types = token_type_ids.reshape(-1, T) if token_type_ids is not None else None
-        hidden = self.transformer(flat_ids, flat_types)          # (B*C, T, E)
+        hidden = self.transformer(flat_ids, flat_types, flat_params=getattr(self, "_flat_params", None))   # (B*C, T, E)
         lm_logits = None
         if need_logits:
             lm_logits = nnops.linear(hidden.reshape(-1, hidden.shape[-1]), self.lm_head.weight, None)

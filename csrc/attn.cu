@@ -72,15 +72,17 @@ __device__ __forceinline__ uint64_t desc_mn(uint32_t base, int k, uint32_t lbo) 
 }
 
 // ------------------------------------------------------------------------------------------------ forward
-__global__ void __launch_bounds__(AT_THREADS)
+__global__ void __launch_bounds__(AT_THREADS, 3)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  // [Q 16K][K 16K][pad 16K][V 16K]; the bf16 probability tile P (32 KB) overwrites K + pad once S = Q K^T has
+  // retired (K is dead by then), which keeps a CTA at 64 KB so three fit on an SM
   uint8_t* sQ = smem;
   uint8_t* sK = smem + AT_TILE_BYTES;
-  uint8_t* sV = smem + 2 * AT_TILE_BYTES;
-  uint8_t* sP = smem + 3 * AT_TILE_BYTES;
-  uint64_t* bar_q = (uint64_t*)(sP + AT_P_BYTES);
+  uint8_t* sP = sK;
+  uint8_t* sV = smem + 3 * AT_TILE_BYTES;
+  uint64_t* bar_q = (uint64_t*)(smem + 4 * AT_TILE_BYTES);
   uint64_t* bar_kv = bar_q + 1;
   uint64_t* bar_s = bar_q + 2;
   uint64_t* bar_p = bar_q + 3;
@@ -98,12 +100,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     mbar_init(bar_q, 1); mbar_init(bar_kv, 1); mbar_init(bar_s, 1); mbar_init(bar_p, AT_TILE); mbar_init(bar_o, 1);
     mbar_fence_init();
   }
-  if (warp == 4) tmem_alloc<256>(tmem_slot);
+  if (warp == 4) tmem_alloc<128>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_S = tmem_base, tmem_O = tmem_base + 128;
+  // the P V product lands on the first 64 columns of S: every thread has consumed its S row before P V is issued
+  const uint32_t tmem_S = tmem_base, tmem_O = tmem_base;
 
   if (warp == 4) {
     if (lane == 0) {
@@ -214,25 +217,32 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
   __syncthreads();
   if (warp == 4) {
     tc_fence_after();
-    tmem_dealloc<256>(tmem_base);
+    tmem_dealloc<128>(tmem_base);
   }
 }
 
 // ------------------------------------------------------------------------------------------------ backward
 // One CTA per (batch, head).  Outer loop: key block j; inner loop: query blocks i >= j.
-//   TMEM columns: S [0,128)  dP [128,256)  dV [256,320)  dK [320,384)  dQ tile [384,448)
-__global__ void __launch_bounds__(AT_THREADS)
+//   MULTI (T > 128): TMEM columns S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ tile [384,448); dV / dK
+//     accumulate over the inner loop; 128 KB of shared memory, one CTA per SM.
+//   single tile (T <= 128): nothing accumulates across steps, so dV / dK / dQ reuse the S / dP columns (256
+//     TMEM columns) and dS overwrites V (+16 KB) once dP = dO V^T has retired: 112 KB, two CTAs per SM -- the
+//     kernel is a chain of short dependent phases (TMA, MMA, softmax math, MMA, stores), which only a second
+//     resident CTA can overlap.
+template <bool MULTI>
+__global__ void __launch_bounds__(AT_THREADS, MULTI ? 1 : 2)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, AttnParams p) {
-  extern __shared__ uint8_t smem_raw[];
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  if (!MULTI && smem != smem_raw) __trap();             // the single-tile variant is sized without alignment slack
   uint8_t* sQ = smem;
   uint8_t* sDO = smem + AT_TILE_BYTES;
   uint8_t* sK = smem + 2 * AT_TILE_BYTES;
   uint8_t* sV = smem + 3 * AT_TILE_BYTES;
-  uint8_t* sAd = smem + 4 * AT_TILE_BYTES;                     // dropped probabilities   [q][kv]
-  uint8_t* sDS = sAd + AT_P_BYTES;                             // dS * scale              [q][kv]
-  float* sDelta = (float*)(sDS + AT_P_BYTES);                  // [<= 1024]
-  uint64_t* bar_kv = (uint64_t*)(sDelta + 1024);
+  uint8_t* sDS = MULTI ? smem + 4 * AT_TILE_BYTES + AT_P_BYTES : sV;                 // dS * scale   [q][kv]
+  uint8_t* sAd = MULTI ? smem + 4 * AT_TILE_BYTES : smem + 5 * AT_TILE_BYTES;        // dropped probabilities [q][kv]
+  uint64_t* bar_kv = (uint64_t*)(smem + (MULTI ? 4 * AT_TILE_BYTES + 2 * AT_P_BYTES : 5 * AT_TILE_BYTES + AT_P_BYTES));
+  constexpr int kTmemCols = MULTI ? 512 : 256;
   uint64_t* bar_qd = bar_kv + 1;
   uint64_t* bar_s = bar_kv + 2;
   uint64_t* bar_p = bar_kv + 3;
@@ -252,33 +262,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     mbar_init(bar_kv, 1); mbar_init(bar_qd, 1); mbar_init(bar_s, 1); mbar_init(bar_p, AT_TILE); mbar_init(bar_o, 1);
     mbar_fence_init();
   }
-  if (warp == 4) tmem_alloc<512>(tmem_slot);
-  if (warp < 4) {
-    // delta[q] = sum_d dO[q][d] * O[q][d]  (= row sum of dP * P after dropout)
-    for (int q = threadIdx.x; q < T; q += AT_TILE) {
-      const uint4* po = reinterpret_cast<const uint4*>(p.o + (size_t)(row0 + q) * E + h * AT_D);
-      const uint4* pd = reinterpret_cast<const uint4*>(p.dout + (size_t)(row0 + q) * E + h * AT_D);
-      float acc = 0.f;
-#pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        const uint4 a = __ldg(po + g), d = __ldg(pd + g);
-        const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
-        const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&d);
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          const float2 fa = __bfloat1622float2(ha[t]), fd = __bfloat1622float2(hd[t]);
-          acc = fmaf(fa.x, fd.x, fmaf(fa.y, fd.y, acc));
-        }
-      }
-      sDelta[q] = acc;
-    }
-  }
+  if (warp == 4) tmem_alloc<kTmemCols>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_S = tmem_base, tmem_dP = tmem_base + 128, tmem_dV = tmem_base + 256, tmem_dK = tmem_base + 320,
-                 tmem_dQ = tmem_base + 384;
+  const uint32_t tmem_S = tmem_base, tmem_dP = tmem_base + 128, tmem_dV = tmem_base + (MULTI ? 256 : 0),
+                 tmem_dK = tmem_base + (MULTI ? 320 : 64), tmem_dQ = tmem_base + (MULTI ? 384 : 128);
 
   if (warp == 4) {
     if (lane == 0) {
@@ -333,7 +323,23 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         const int q_abs = i * AT_TILE + r;
         const bool q_ok = q_abs < T;
         const float L = q_ok ? __ldg(p.lse + (size_t)bh * T + q_abs) : 0.f;
-        const float delta = q_ok ? sDelta[q_abs] : 0.f;
+        // delta = sum_d dO[q][d] * O[q][d]  (= row sum of dP * P after dropout); overlaps the TMA / MMA latency
+        float delta = 0.f;
+        if (q_ok) {
+          const uint4* po = reinterpret_cast<const uint4*>(p.o + (size_t)(row0 + q_abs) * E + h * AT_D);
+          const uint4* pd = reinterpret_cast<const uint4*>(p.dout + (size_t)(row0 + q_abs) * E + h * AT_D);
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const uint4 a = __ldg(po + g), d = __ldg(pd + g);
+            const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
+            const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&d);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const float2 fa = __bfloat1622float2(ha[t]), fd = __bfloat1622float2(hd[t]);
+              delta = fmaf(fa.x, fd.x, fmaf(fa.y, fd.y, delta));
+            }
+          }
+        }
         const uint32_t rowkey = p.drop_thresh ? at_rowkey(p, bh, q_abs) : 0u;
         mbar_wait(bar_s, step & 1);
         tc_fence_after();
@@ -431,13 +437,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   __syncthreads();
   if (warp == 4) {
     tc_fence_after();
-    tmem_dealloc<512>(tmem_base);
+    tmem_dealloc<kTmemCols>(tmem_base);
   }
 }
 
 // ------------------------------------------------------------------------------------------------ host
-constexpr int kFwdSmem = 3 * AT_TILE_BYTES + AT_P_BYTES + 1024 + 128;
-constexpr int kBwdSmem = 4 * AT_TILE_BYTES + 2 * AT_P_BYTES + 4096 + 1024 + 128;
+constexpr int kFwdSmem = 4 * AT_TILE_BYTES + 1024 + 128;
+constexpr int kBwdSmemMulti = 4 * AT_TILE_BYTES + 2 * AT_P_BYTES + 1024 + 128;
+// no alignment slack: two CTAs (2 x (112 KB + 128 B) + 2 x 1 KB reserved) must fit the SM's 228 KB; the dynamic
+// window of a kernel without static shared memory starts 1 KB-aligned (checked in the kernel)
+constexpr int kBwdSmemSingle = 5 * AT_TILE_BYTES + AT_P_BYTES + 128;
 
 static int attn_check(const char* who, int B, int T, int H, int E) {
   CEB_REQUIRE(B > 0 && T > 0 && H > 0 && E == H * AT_D, "%s: need E == H * 64 (B=%d T=%d H=%d E=%d)", who, B, T, H, E);
@@ -505,10 +514,12 @@ CEB_API int ceb_attention_bwd(const void* qkv, const void* out, const void* dout
   p.lse = (float*)lse; p.dq_acc = T > AT_TILE ? dq_scratch : nullptr;
   static bool configured = false;
   if (!configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemMulti));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemSingle));
     configured = true;
   }
-  attn_bwd_kernel<<<(unsigned)(B * H), AT_THREADS, kBwdSmem, (cudaStream_t)stream>>>(tm, tmdo, p);
+  if (T > AT_TILE) attn_bwd_kernel<true><<<(unsigned)(B * H), AT_THREADS, kBwdSmemMulti, (cudaStream_t)stream>>>(tm, tmdo, p);
+  else attn_bwd_kernel<false><<<(unsigned)(B * H), AT_THREADS, kBwdSmemSingle, (cudaStream_t)stream>>>(tm, tmdo, p);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
