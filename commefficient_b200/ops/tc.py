@@ -82,6 +82,18 @@ native.register_signatures({
                                 native.c_ptr], native.c_i32),
 })
 
+native.register_signatures({
+    "ceb_conv2d_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32, native.c_i32,
+                         native.c_i32, native.c_i32, native.c_i32, native.c_i32, native.c_i32, native.c_i32, native.c_ptr,
+                         native.c_ptr, native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_conv3x3_wgrad_nhwc": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32,
+                                native.c_i32, native.c_i32, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_subsample2_nhwc": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32, native.c_i32,
+                             native.c_ptr], native.c_i32),
+    "ceb_upsample2_zero_nhwc": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i32, native.c_i32,
+                                 native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
+})
+
 _OUT = {torch.bfloat16: 0, torch.float32: 1}
 
 # Operand precision of the tensor-core layers (``--precision``): "bf16" -> bf16 activations and
@@ -331,28 +343,81 @@ def conv3x3_wgrad_nhwc(dz: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> t
     return dw
 
 
+def conv2d_nhwc(x, w, ks=3, stride=1, pad=1, relu=False, relu_mask=None, resid=None, keep_pre_add=False):
+    """General NHWC convolution on the tile kernel: ``x [N,H,W,Cin]``, ``w [Cout,ks,ks,Cin]`` (both bf16, or both
+    fp32 for the TF32 path), ks in {1, 3}, stride in {1, 2}, pad in {0, 1}; any map whose OUTPUT width is <= 128.
+    Optional fused ReLU, ReLU-backward mask and residual add as in ``conv3x3_nhwc(_res)``."""
+    assert x.dtype == w.dtype and x.is_contiguous() and w.is_contiguous()
+    n, h, wd, cin = x.shape
+    cout = w.shape[0]
+    ho, wo = (h + 2 * pad - ks) // stride + 1, (wd + 2 * pad - ks) // stride + 1
+    y = torch.empty((n, ho, wo, cout), dtype=x.dtype, device=x.device)
+    y2 = torch.empty_like(y) if (resid is not None and keep_pre_add) else None
+    native.call("ceb_conv2d_nhwc", native.ptr(x), native.ptr(w), native.ptr(y), n, h, wd, cin, cout, ks, stride, pad,
+                1 if relu else 0, 1 if x.dtype == torch.float32 else 0, native.ptr(relu_mask), native.ptr(resid),
+                native.ptr(y2), native.stream_ptr(x.device))
+    return (y, y2) if y2 is not None else y
+
+
+def conv3x3_wgrad_strided(dz, x, dw, stride):
+    """``dw[Cout,3,3,Cin] (fp32) +=`` weight gradient of a 3x3 / pad 1 / stride 1|2 convolution: ``x`` is the INPUT
+    ``[N,H,W,Cin]``, ``dz`` the output gradient ``[N,Ho,Wo,Cout]`` (any map size with Wo <= 64 bf16 / 32 fp32)."""
+    assert dz.dtype == x.dtype and dz.is_contiguous() and x.is_contiguous() and dw.dtype == torch.float32 and dw.is_contiguous()
+    n, h, wd, cin = x.shape
+    native.call("ceb_conv3x3_wgrad_nhwc", native.ptr(dz), native.ptr(x), native.ptr(dw), n, h, wd, cin, dz.shape[3],
+                stride, 1 if x.dtype == torch.float32 else 0, native.stream_ptr(x.device))
+    return dw
+
+
+def subsample2(x):
+    """``x[:, ::2, ::2, :]`` of an NHWC tensor as a dense tensor."""
+    n, h, w, c = x.shape
+    out = torch.empty((n, (h + 1) // 2, (w + 1) // 2, c), dtype=x.dtype, device=x.device)
+    native.call("ceb_subsample2_nhwc", native.ptr(x), native.ptr(out), n, h, w, c * x.element_size(),
+                native.stream_ptr(x.device))
+    return out
+
+
+def upsample2_zero(g, h, w):
+    """``up[:, ::2, ::2, :] = g``, zero elsewhere, on an ``h x w`` grid."""
+    n, ho, wo, c = g.shape
+    up = torch.empty((n, h, w, c), dtype=g.dtype, device=g.device)
+    native.call("ceb_upsample2_zero_nhwc", native.ptr(g), native.ptr(up), n, h, w, ho, wo, c * g.element_size(),
+                native.stream_ptr(g.device))
+    return up
+
+
 def conv_supported(x, weight, stride, padding) -> bool:
-    """3x3 / stride 1 / pad 1 convolutions with 64-multiple channels on 4..32-wide maps (the
-    stride-1 layers of ResNet-18 / FixupResNet18 / ResNet-9) when the weight lives NHWC in the flat
-    buffer.  Strided and 1x1 convolutions stay on the library."""
+    """3x3 / pad 1 and 1x1 / pad 0 convolutions with stride 1 or 2 and 64-multiple channels on maps up to 64
+    pixels wide (every layer of ResNet-9 / ResNet-18 / FixupResNet18 except the 3- or 1-channel stems, which
+    are lowered to im2col + GEMM by the whole-network paths), when the weight lives NHWC in the flat buffer."""
     if not (x.is_cuda and x.dim() == 4 and weight.dim() == 4):
         return False
     co, ci, kh, kw = weight.shape
-    if (kh, kw) != (3, 3) or stride != 1 or padding != 1 or ci % 64 or co % 64:
+    if (kh, kw, padding) not in ((3, 3, 1), (1, 1, 0)) or stride not in (1, 2) or ci % 64 or co % 64:
         return False
     h, w = x.shape[2], x.shape[3]
-    if w not in (4, 8, 16, 32) or h != w:
+    wo = (w + 2 * padding - kw) // stride + 1
+    kmax = 32 if act_dtype() == torch.float32 else 64
+    if wo < 1 or wo > kmax or w > 128:
         return False
     return weight.permute(0, 2, 3, 1).is_contiguous()
 
 
-class _Conv3x3Fn(torch.autograd.Function):
-    """One 3x3 / s1 / p1 convolution (+ optional ReLU) on the tcgen05 kernels.  Activations cross
-    the boundary as channels_last NCHW tensors (= NHWC buffers)."""
+class _ConvFn(torch.autograd.Function):
+    """One convolution (3x3 / pad 1 or 1x1 / pad 0, stride 1 or 2, + optional ReLU) on the tcgen05 kernels.
+    Activations cross the boundary as channels_last NCHW tensors (= NHWC buffers).  Backward:
+      * data gradient: stride 1 -> the transposed-weight convolution; stride 2 -> the output gradient is spread
+        onto the input grid with zeros (``upsample2_zero``) and then convolved at stride 1 (3x3), or is a GEMM
+        followed by that spreading (1x1);
+      * weight gradient: the MN-major wgrad kernel, whose TMA box steps through the input with the stride
+        (3x3), or the plain MN-major GEMM over the sub-sampled input (1x1)."""
 
     @staticmethod
-    def forward(ctx, x, weight, relu):
+    def forward(ctx, x, weight, relu, stride):
         dt = act_dtype()
+        ks = weight.shape[2]
+        pad = 1 if ks == 3 else 0
         xn = x.permute(0, 2, 3, 1)
         xb = (xn if xn.dtype == dt else xn.to(dt)).contiguous()
         wk = weight.permute(0, 2, 3, 1)
@@ -362,36 +427,51 @@ class _Conv3x3Fn(torch.autograd.Function):
                 wb = wb.clone()
         else:
             wb = cast_bf16(wk) if wk.dtype == torch.float32 else wk.to(torch.bfloat16).contiguous()
-        y = conv3x3_nhwc(xb, wb, relu=relu)
+        y = conv2d_nhwc(xb, wb, ks, stride, pad, relu=relu)
         ctx.save_for_backward(xb, y if relu else xb)
-        ctx.weight, ctx.relu, ctx.x_dtype = weight, relu, x.dtype
+        ctx.weight, ctx.relu, ctx.x_dtype, ctx.geom = weight, relu, x.dtype, (ks, stride, pad)
         return y.permute(0, 3, 1, 2)
 
     @staticmethod
     def backward(ctx, dy):
         xb, y = ctx.saved_tensors
         weight = ctx.weight
+        ks, stride, pad = ctx.geom
+        n, h, w, cin = xb.shape
         dz = dy.permute(0, 2, 3, 1).to(xb.dtype).contiguous()
         if ctx.relu:
             dz = relu_bwd(y, dz)
+        cout = dz.shape[3]
         dx = dw = None
         if ctx.needs_input_grad[1]:
             target = weight.grad if (isinstance(weight, torch.nn.Parameter) and weight.grad is not None
                                      and weight.grad.permute(0, 2, 3, 1).is_contiguous()) else None
             acc = target.permute(0, 2, 3, 1) if target is not None else \
                 torch.zeros(weight.permute(0, 2, 3, 1).shape, dtype=torch.float32, device=dz.device)
-            conv3x3_wgrad_nhwc(dz, xb, acc)
+            if ks == 3:
+                conv3x3_wgrad_strided(dz, xb, acc, stride)
+            else:
+                xs = subsample2(xb) if stride == 2 else xb
+                gemm_mn_acc(dz.view(-1, cout), xs.view(-1, cin), acc.view(cout, cin))
             if target is None:
                 dw = acc.permute(0, 3, 1, 2)
         if ctx.needs_input_grad[0]:
             wk = weight.data.permute(0, 2, 3, 1)
-            wd = dgrad_weights(wk if wk.dtype == torch.float32 else wk.float().contiguous(), dtype=xb.dtype)
-            dx = conv3x3_nhwc(dz, wd).permute(0, 3, 1, 2).to(ctx.x_dtype)
-        return dx, dw, None
+            wk = wk if wk.dtype == torch.float32 else wk.float().contiguous()
+            if ks == 3:
+                wd = dgrad_weights(wk, dtype=xb.dtype)
+                g = upsample2_zero(dz, h, w) if stride == 2 else dz
+                dxn = conv2d_nhwc(g, wd, 3, 1, 1)
+            else:
+                wt = _w_rows(wk.reshape(cout, cin), True, xb.dtype)                 # [Cin, Cout], K-major
+                g = gemm_tn(dz.view(-1, cout), wt).view(n, dz.shape[1], dz.shape[2], cin)
+                dxn = upsample2_zero(g.contiguous(), h, w) if stride == 2 else g
+            dx = dxn.permute(0, 3, 1, 2).to(ctx.x_dtype)
+        return dx, dw, None, None
 
 
 def conv2d(x, weight, bias, stride, padding, relu=False):
-    y = _Conv3x3Fn.apply(x, weight, relu)
+    y = _ConvFn.apply(x, weight, relu, stride)
     if bias is not None:
         y = y + bias.view(1, -1, 1, 1)
     return y
@@ -597,12 +677,13 @@ def _krsc(t: torch.Tensor) -> torch.Tensor:
 
 def resnet9_supported(model, x: torch.Tensor) -> bool:
     n = model.n
-    if not x.is_cuda or x.dim() != 4 or x.shape[2] != 32 or x.shape[3] != 32:
+    # CIFAR (3 x 32 x 32) and FEMNIST (1 x 28 x 28: maps 28 -> 14 -> 7 -> 3, final 3 x 3 max-pool)
+    if not x.is_cuda or x.dim() != 4 or x.shape[2] != x.shape[3] or x.shape[2] not in (32, 28):
         return False
     if n.prep.do_batchnorm:
         return False
     ch = n.channels
-    if ch["prep"] != 64 or any(ch[k] % 64 for k in ("layer1", "layer2", "layer3")) or x.shape[1] != 3:
+    if ch["prep"] != 64 or any(ch[k] % 64 for k in ("layer1", "layer2", "layer3")) or x.shape[1] not in (1, 3):
         return False
     fp = getattr(model, "_flat_params", None)
     return fp is not None and fp.layout == "nhwc"
@@ -622,8 +703,9 @@ def _r9_features(x, net):
     # one launch: 7 casts + 7 dgrad layouts (TF32 path: the fp32 weights are read in place, 7 dgrad layouts)
     wb, wd = prepare_conv_weights([_krsc(c.weight.data) for c in convs[1:]], dtype=dt)
     xb = x.float().permute(0, 2, 3, 1).contiguous()           # NHWC fp32 (no copy for channels_last input)
-    col = im2col_c3(xb, dt)                                   # [N*1024, 64] bf16 / [N*1024, 32] fp32
-    a0 = gemm_tn(col, _stem_weight_pad(_krsc(convs[0].weight.data), dt), relu=True).view(x.shape[0], 32, 32, -1)
+    col = im2col_c3(xb, dt)                                   # [N*H*W, 64] bf16 / [N*H*W, 32] fp32
+    a0 = gemm_tn(col, _stem_weight_pad(_krsc(convs[0].weight.data), dt), relu=True).view(x.shape[0], x.shape[2],
+                                                                                         x.shape[3], -1)
     a1 = conv3x3_nhwc(a0, wb[0], relu=True)
     p1 = maxpool_nhwc(a1, 2)
     r1a = conv3x3_nhwc(p1, wb[1], relu=True)
@@ -634,7 +716,7 @@ def _r9_features(x, net):
     p3 = maxpool_nhwc(a3, 2)
     r3a = conv3x3_nhwc(p3, wb[5], relu=True)
     r3b, s3 = conv3x3_nhwc_res(r3a, wb[6], p3, relu=True, keep_pre_add=True)
-    f = maxpool_nhwc(s3, 4).view(x.shape[0], -1)
+    f = maxpool_nhwc(s3, s3.shape[1]).view(x.shape[0], -1)     # 4 x 4 (CIFAR) or 3 x 3 (FEMNIST) -> 1 x 1
     return f, (col, a0, a1, p1, r1a, r1b, s1, a2, p2, a3, p3, r3a, r3b, s3), [None] + wd
 
 
@@ -645,7 +727,7 @@ def _r9_backward(net, saved, wd, df, fp=None):
     convs = _r9_convs(net)
     gw = [_krsc(c.weight.grad) for c in convs]                       # fp32 KRSC views of the flat gradient
     n = a0.shape[0]
-    ds3 = maxpool_bwd_nhwc(s3, df.view(n, 1, 1, -1), 4, relu_mask=False)
+    ds3 = maxpool_bwd_nhwc(s3, df.view(n, 1, 1, -1), s3.shape[1], relu_mask=False)
 
     dz = relu_bwd(r3b, ds3)
     conv3x3_wgrad_nhwc(dz, r3a, gw[7])
@@ -678,7 +760,8 @@ def _r9_backward(net, saved, wd, df, fp=None):
 
     g0 = torch.zeros((da0.shape[3], 64), dtype=torch.float32, device=da0.device)
     gemm_mn_acc(da0.view(-1, da0.shape[3]), col, g0[:, :col.shape[1]])
-    gw[0].view(da0.shape[3], 27).add_(g0[:, :27])
+    k0 = gw[0][0].numel()                                          # 27 (RGB) or 9 (grey) stem taps
+    gw[0].view(da0.shape[3], k0).add_(g0[:, :k0])
 
 
 class _ResNet9Fn(torch.autograd.Function):
@@ -736,7 +819,8 @@ def linear_ce_head(feat, weight, scale, labels, g=None, dW=None):
 
 def head_supported(net, feat_dim: int) -> bool:
     w = net.linear.weight
-    return (w.shape[0] <= 32 and feat_dim % 64 == 0 and feat_dim <= 2048 and w.is_contiguous()
+    return (w.shape[0] <= 128 and w.shape[0] * feat_dim * 4 <= 224 * 1024 and feat_dim % 64 == 0 and feat_dim <= 2048
+            and w.is_contiguous()
             and w.dtype == torch.float32 and w.grad is not None and w.grad.is_contiguous())
 
 

@@ -600,23 +600,27 @@ __device__ __forceinline__ void head_st2(float* p, float a, float b) { *reinterp
 
 // FT = feature / feature-gradient element type: bf16 (fast path) or float (TF32 / matched-precision path; the
 // head itself is fp32 FMA either way, like the reference's cuBLAS SGEMM for this 512 -> C layer).
-template <typename FT>
+// Classes are distributed over lanes: lane l owns classes l, l + 32, ... (CL = ceil(C / 32) <= 4 per lane).
+// dW_in_smem: the block accumulates its weight gradient in shared memory and adds it to the global gradient
+// once (small heads); otherwise (the two [C][F] fp32 tables exceed shared memory) every lane reduces straight
+// into global memory.
+template <typename FT, int CL>
 __global__ void __launch_bounds__(256)
 linear_ce_head_kernel(const FT* __restrict__ feat, const float* __restrict__ W, float scale,
                       const int64_t* __restrict__ labels, int N, int F, int C, const float* __restrict__ g,
                       float* __restrict__ loss, float* __restrict__ correct, FT* __restrict__ dfeat,
-                      float* __restrict__ dW) {
+                      float* __restrict__ dW, int dW_in_smem) {
   extern __shared__ float hs[];
   float* Ws = hs;                       // [C][F]
-  float* dWs = hs + (size_t)C * F;      // [C][F], backward only
+  float* dWs = hs + (size_t)C * F;      // [C][F], backward with dW_in_smem only
   const bool bwd = g != nullptr;
   for (int i = threadIdx.x; i < C * F; i += blockDim.x) {
     Ws[i] = W[i];
-    if (bwd) dWs[i] = 0.f;
+    if (bwd && dW_in_smem) dWs[i] = 0.f;
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  const int J = F >> 6;                 // bf16 pairs per lane
+  const int J = F >> 6;                 // element pairs per lane
   for (int s = blockIdx.x * wpb + warp; s < N; s += gridDim.x * wpb) {
     float x[64];                        // F <= 2048 -> up to 32 pairs
     const FT* fr = feat + (size_t)s * F;
@@ -627,7 +631,9 @@ linear_ce_head_kernel(const FT* __restrict__ feat, const float* __restrict__ W, 
         x[2 * j] = v.x; x[2 * j + 1] = v.y;
       }
     }
-    float mylogit = -INFINITY;
+    float mylogit[CL];
+#pragma unroll
+    for (int q = 0; q < CL; ++q) mylogit[q] = -INFINITY;
     for (int c = 0; c < C; ++c) {
       const float* wr = Ws + (size_t)c * F;
       float a = 0.f;
@@ -635,21 +641,36 @@ linear_ce_head_kernel(const FT* __restrict__ feat, const float* __restrict__ W, 
       for (int j = 0; j < 32; ++j)
         if (j < J) a = fmaf(x[2 * j], wr[j * 64 + 2 * lane], fmaf(x[2 * j + 1], wr[j * 64 + 2 * lane + 1], a));
       a = warp_sum(a) * scale;
-      if (lane == c) mylogit = a;
+#pragma unroll
+      for (int q = 0; q < CL; ++q)
+        if (c == q * 32 + lane) mylogit[q] = a;
     }
     // softmax statistics and argmax (first maximal index, like torch.argmax)
-    float mx = mylogit;
-    int am = lane < C ? lane : 0x7fffffff;
+    float mx = -INFINITY;
+    int am = 0x7fffffff;
+#pragma unroll
+    for (int q = 0; q < CL; ++q) {
+      const int c = q * 32 + lane;
+      if (c < C && (mylogit[q] > mx || (mylogit[q] == mx && c < am))) { mx = mylogit[q]; am = c; }
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const float om = __shfl_xor_sync(0xffffffffu, mx, o);
       const int oi = __shfl_xor_sync(0xffffffffu, am, o);
       if (om > mx || (om == mx && oi < am)) { mx = om; am = oi; }
     }
-    const float e = lane < C ? __expf(mylogit - mx) : 0.f;
+    float e = 0.f;
+#pragma unroll
+    for (int q = 0; q < CL; ++q)
+      if (q * 32 + lane < C) e += __expf(mylogit[q] - mx);
     const float lse = mx + __logf(warp_sum(e));
     const int label = (int)labels[s];
-    const float at_label = __shfl_sync(0xffffffffu, mylogit, label & 31);
+    float at_label = 0.f;
+#pragma unroll
+    for (int q = 0; q < CL; ++q) {
+      const float v = __shfl_sync(0xffffffffu, mylogit[q], label & 31);
+      if ((label >> 5) == q) at_label = v;
+    }
     if (!bwd) {
       if (lane == 0) {
         loss[s] = lse - at_label;
@@ -657,15 +678,25 @@ linear_ce_head_kernel(const FT* __restrict__ feat, const float* __restrict__ W, 
       }
       continue;
     }
-    // d raw logit (before the scale) of lane c
-    const float dl = lane < C ? g[s] * (__expf(mylogit - lse) - (lane == label ? 1.f : 0.f)) * scale : 0.f;
+    // d raw logit (before the scale) of this lane's classes
+    float dl[CL];
+#pragma unroll
+    for (int q = 0; q < CL; ++q) {
+      const int c = q * 32 + lane;
+      dl[q] = c < C ? g[s] * (__expf(mylogit[q] - lse) - (c == label ? 1.f : 0.f)) * scale : 0.f;
+    }
     float dx[64];
 #pragma unroll
     for (int j = 0; j < 64; ++j) dx[j] = 0.f;
     for (int c = 0; c < C; ++c) {
-      const float d = __shfl_sync(0xffffffffu, dl, c);
+      float d = 0.f;
+#pragma unroll
+      for (int q = 0; q < CL; ++q) {
+        const float v = __shfl_sync(0xffffffffu, dl[q], c & 31);
+        if ((c >> 5) == q) d = v;
+      }
       const float* wr = Ws + (size_t)c * F;
-      float* dwr = dWs + (size_t)c * F;
+      float* dwr = (dW_in_smem ? dWs : dW) + (size_t)c * F;
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         if (j < J) {
@@ -682,7 +713,7 @@ linear_ce_head_kernel(const FT* __restrict__ feat, const float* __restrict__ W, 
     for (int j = 0; j < 32; ++j)
       if (j < J) head_st2(dr + (j * 32 + lane) * 2, dx[2 * j], dx[2 * j + 1]);
   }
-  if (bwd) {
+  if (bwd && dW_in_smem) {
     __syncthreads();
     for (int i = threadIdx.x; i < C * F; i += blockDim.x) {
       const float v = dWs[i];
@@ -691,24 +722,39 @@ linear_ce_head_kernel(const FT* __restrict__ feat, const float* __restrict__ W, 
   }
 }
 
-template <typename FT>
-static int linear_ce_head_impl(const FT* feat, const float* W, float scale, const int64_t* labels, int N, int F,
-                               int C, const float* g, float* loss, float* correct, FT* dfeat, float* dW, void* stream) {
-  CEB_REQUIRE(feat && W && labels && N > 0, "ceb_linear_ce_head: bad arguments");
-  CEB_REQUIRE(C >= 1 && C <= 32 && F % 64 == 0 && F >= 64 && F <= 2048, "ceb_linear_ce_head: need C <= 32, F %% 64 == 0, F <= 2048 (C=%d F=%d)", C, F);
-  CEB_REQUIRE(g ? (dfeat && dW) : (loss && correct), "ceb_linear_ce_head: missing outputs");
-  const size_t smem = (size_t)C * F * sizeof(float) * (g ? 2 : 1);
+template <typename FT, int CL>
+static int linear_ce_head_launch(const FT* feat, const float* W, float scale, const int64_t* labels, int N, int F,
+                                 int C, const float* g, float* loss, float* correct, FT* dfeat, float* dW, void* stream) {
+  const size_t one = (size_t)C * F * sizeof(float);
+  const int dW_in_smem = (g && 2 * one <= 200 * 1024) ? 1 : 0;
+  const size_t smem = one * ((g && dW_in_smem) ? 2 : 1);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
-    CEB_CHECK_CUDA(cudaFuncSetAttribute(linear_ce_head_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CEB_CHECK_CUDA(cudaFuncSetAttribute(linear_ce_head_kernel<FT, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
   int blocks = (int)ceb_cdiv(N, 8);
   if (blocks > ceb_num_sms()) blocks = ceb_num_sms();
-  linear_ce_head_kernel<FT><<<blocks, 256, smem, (cudaStream_t)stream>>>(feat, W, scale, labels, N, F, C, g, loss, correct, dfeat, dW);
+  linear_ce_head_kernel<FT, CL><<<blocks, 256, smem, (cudaStream_t)stream>>>(feat, W, scale, labels, N, F, C, g, loss, correct,
+                                                                          dfeat, dW, dW_in_smem);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
+}
+
+template <typename FT>
+static int linear_ce_head_impl(const FT* feat, const float* W, float scale, const int64_t* labels, int N, int F,
+                               int C, const float* g, float* loss, float* correct, FT* dfeat, float* dW, void* stream) {
+  CEB_REQUIRE(feat && W && labels && N > 0, "ceb_linear_ce_head: bad arguments");
+  CEB_REQUIRE(C >= 1 && C <= 128 && F % 64 == 0 && F >= 64 && F <= 2048 && (size_t)C * F * 4 <= 224 * 1024,
+              "ceb_linear_ce_head: need C <= 128, F %% 64 == 0, F <= 2048, C * F * 4 <= 224 KB (C=%d F=%d)", C, F);
+  CEB_REQUIRE(g ? (dfeat && dW) : (loss && correct), "ceb_linear_ce_head: missing outputs");
+  switch ((C + 31) / 32) {
+    case 1: return linear_ce_head_launch<FT, 1>(feat, W, scale, labels, N, F, C, g, loss, correct, dfeat, dW, stream);
+    case 2: return linear_ce_head_launch<FT, 2>(feat, W, scale, labels, N, F, C, g, loss, correct, dfeat, dW, stream);
+    case 3: return linear_ce_head_launch<FT, 3>(feat, W, scale, labels, N, F, C, g, loss, correct, dfeat, dW, stream);
+    default: return linear_ce_head_launch<FT, 4>(feat, W, scale, labels, N, F, C, g, loss, correct, dfeat, dW, stream);
+  }
 }
 
 CEB_API int ceb_linear_ce_head(const void* feat_bf16, const float* W, float scale, const int64_t* labels, int N, int F,

@@ -301,9 +301,32 @@ maxpool_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dp, ui
   }
 }
 
+// Windows tile the map from the top-left corner; rows / columns beyond the last whole window are ignored
+// (torch.nn.MaxPool2d's floor mode): Ho = H / k, Wo = W / k.
 static int check_pool(const char* who, int N, int H, int W, int C, int k) {
-  CEB_REQUIRE(N > 0 && C % 8 == 0 && (k == 2 || k == 4) && H % k == 0 && W % k == 0,
-              "%s: need C %% 8 == 0, k in {2,4}, H, W multiples of k (N=%d H=%d W=%d C=%d k=%d)", who, N, H, W, C, k);
+  CEB_REQUIRE(N > 0 && C % 8 == 0 && (k == 2 || k == 3 || k == 4) && H >= k && W >= k,
+              "%s: need C %% 8 == 0, k in {2,3,4}, H, W >= k (N=%d H=%d W=%d C=%d k=%d)", who, N, H, W, C, k);
+  return 0;
+}
+
+template <typename V>
+static void launch_pool_fwd(const void* y, void* out, int N, int H, int W, int Cv, int k, cudaStream_t st) {
+  const int64_t total = (int64_t)N * (H / k) * (W / k) * Cv;
+  const int grid = ceb_grid_for(total, 256);
+  if (k == 2) maxpool_fwd_kernel<2, V><<<grid, 256, 0, st>>>((const uint4*)y, (uint4*)out, N, H, W, Cv);
+  else if (k == 3) maxpool_fwd_kernel<3, V><<<grid, 256, 0, st>>>((const uint4*)y, (uint4*)out, N, H, W, Cv);
+  else maxpool_fwd_kernel<4, V><<<grid, 256, 0, st>>>((const uint4*)y, (uint4*)out, N, H, W, Cv);
+}
+template <typename V>
+static int launch_pool_bwd(const void* y, const void* dp, void* dz, int N, int H, int W, int Cv, int k, int relu_mask,
+                           size_t elem_bytes_per_vec, cudaStream_t st) {
+  if (H % k != 0 || W % k != 0)      // pixels outside every window get no gradient
+    CEB_CHECK_CUDA(cudaMemsetAsync(dz, 0, (size_t)N * H * W * Cv * elem_bytes_per_vec, st));
+  const int64_t total = (int64_t)N * (H / k) * (W / k) * Cv;
+  const int grid = ceb_grid_for(total, 256);
+  if (k == 2) maxpool_bwd_kernel<2, V><<<grid, 256, 0, st>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, Cv, relu_mask);
+  else if (k == 3) maxpool_bwd_kernel<3, V><<<grid, 256, 0, st>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, Cv, relu_mask);
+  else maxpool_bwd_kernel<4, V><<<grid, 256, 0, st>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, Cv, relu_mask);
   return 0;
 }
 
@@ -311,10 +334,7 @@ static int check_pool(const char* who, int N, int H, int W, int C, int k) {
 CEB_API int ceb_maxpool_nhwc_bf16(const void* y, void* out, int N, int H, int W, int C, int k, void* stream) {
   CEB_REQUIRE(y && out, "ceb_maxpool_nhwc_bf16: null pointer");
   if (int e = check_pool("ceb_maxpool_nhwc_bf16", N, H, W, C, k)) return e;
-  const int64_t total = (int64_t)N * (H / k) * (W / k) * (C / 8);
-  const int grid = ceb_grid_for(total, 256);
-  if (k == 2) maxpool_fwd_kernel<2><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (uint4*)out, N, H, W, C / 8);
-  else maxpool_fwd_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (uint4*)out, N, H, W, C / 8);
+  launch_pool_fwd<VecBF>(y, out, N, H, W, C / 8, k, (cudaStream_t)stream);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -325,10 +345,7 @@ CEB_API int ceb_maxpool_bwd_nhwc_bf16(const void* y, const void* dp, void* dz, i
                                       int relu_mask, void* stream) {
   CEB_REQUIRE(y && dp && dz, "ceb_maxpool_bwd_nhwc_bf16: null pointer");
   if (int e = check_pool("ceb_maxpool_bwd_nhwc_bf16", N, H, W, C, k)) return e;
-  const int64_t total = (int64_t)N * (H / k) * (W / k) * (C / 8);
-  const int grid = ceb_grid_for(total, 256);
-  if (k == 2) maxpool_bwd_kernel<2><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, C / 8, relu_mask);
-  else maxpool_bwd_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, C / 8, relu_mask);
+  if (int e = launch_pool_bwd<VecBF>(y, dp, dz, N, H, W, C / 8, k, relu_mask, 16, (cudaStream_t)stream)) return e;
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -337,11 +354,8 @@ CEB_API int ceb_maxpool_bwd_nhwc_bf16(const void* y, const void* dp, void* dz, i
 // fp32 NHWC variants (TF32 path): C % 4 == 0
 CEB_API int ceb_maxpool_nhwc_f32(const float* y, float* out, int N, int H, int W, int C, int k, void* stream) {
   CEB_REQUIRE(y && out, "ceb_maxpool_nhwc_f32: null pointer");
-  CEB_REQUIRE(N > 0 && C % 4 == 0 && (k == 2 || k == 4) && H % k == 0 && W % k == 0, "ceb_maxpool_nhwc_f32: bad shape");
-  const int64_t total = (int64_t)N * (H / k) * (W / k) * (C / 4);
-  const int grid = ceb_grid_for(total, 256);
-  if (k == 2) maxpool_fwd_kernel<2, VecF><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (uint4*)out, N, H, W, C / 4);
-  else maxpool_fwd_kernel<4, VecF><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (uint4*)out, N, H, W, C / 4);
+  CEB_REQUIRE(N > 0 && C % 4 == 0 && (k == 2 || k == 3 || k == 4) && H >= k && W >= k, "ceb_maxpool_nhwc_f32: bad shape");
+  launch_pool_fwd<VecF>(y, out, N, H, W, C / 4, k, (cudaStream_t)stream);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -350,11 +364,8 @@ CEB_API int ceb_maxpool_nhwc_f32(const float* y, float* out, int N, int H, int W
 CEB_API int ceb_maxpool_bwd_nhwc_f32(const float* y, const float* dp, float* dz, int N, int H, int W, int C, int k,
                                      int relu_mask, void* stream) {
   CEB_REQUIRE(y && dp && dz, "ceb_maxpool_bwd_nhwc_f32: null pointer");
-  CEB_REQUIRE(N > 0 && C % 4 == 0 && (k == 2 || k == 4) && H % k == 0 && W % k == 0, "ceb_maxpool_bwd_nhwc_f32: bad shape");
-  const int64_t total = (int64_t)N * (H / k) * (W / k) * (C / 4);
-  const int grid = ceb_grid_for(total, 256);
-  if (k == 2) maxpool_bwd_kernel<2, VecF><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, C / 4, relu_mask);
-  else maxpool_bwd_kernel<4, VecF><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)y, (const uint4*)dp, (uint4*)dz, N, H, W, C / 4, relu_mask);
+  CEB_REQUIRE(N > 0 && C % 4 == 0 && (k == 2 || k == 3 || k == 4) && H >= k && W >= k, "ceb_maxpool_bwd_nhwc_f32: bad shape");
+  if (int e = launch_pool_bwd<VecF>(y, dp, dz, N, H, W, C / 4, k, relu_mask, 16, (cudaStream_t)stream)) return e;
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -468,6 +479,62 @@ CEB_API int ceb_im2col3x3(const float* x_nhwc, void* A, int N, int H, int W, int
   else if (Cin == 3) im2col3x3_kernel<3, __nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(x_nhwc, (__nv_bfloat16*)A, N, H, W);
   else if (out_f32) im2col3x3_kernel<1, float><<<(unsigned)blocks, 256, 0, st>>>(x_nhwc, (float*)A, N, H, W);
   else im2col3x3_kernel<1, __nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(x_nhwc, (__nv_bfloat16*)A, N, H, W);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+
+// ------------------------------------------------------------------ stride-2 helpers (any 16-byte-vector dtype)
+// sub[n][ho][wo][:] = x[n][2 ho][2 wo][:]  (input of a 1x1 / stride-2 shortcut as a dense matrix)
+__global__ void __launch_bounds__(256)
+subsample2_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int N, int H, int W, int Ho, int Wo, int Cv) {
+  const int64_t total = (int64_t)N * Ho * Wo * Cv;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += stride) {
+    const int c = (int)(o % Cv);
+    int64_t t = o / Cv;
+    const int wo = (int)(t % Wo); t /= Wo;
+    const int ho = (int)(t % Ho);
+    const int64_t n = t / Ho;
+    out[o] = __ldg(x + ((n * H + 2 * ho) * W + 2 * wo) * Cv + c);
+  }
+}
+// up[n][h][w][:] = g[n][h/2][w/2][:] where h, w are both even (and inside g), 0 elsewhere: the gradient of a
+// stride-2 layer spread back onto the input grid, after which its data gradient is a stride-1 convolution
+__global__ void __launch_bounds__(256)
+upsample2_zero_kernel(const uint4* __restrict__ g, uint4* __restrict__ up, int N, int H, int W, int Ho, int Wo, int Cv) {
+  const int64_t total = (int64_t)N * H * W * Cv;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += stride) {
+    const int c = (int)(o % Cv);
+    int64_t t = o / Cv;
+    const int w = (int)(t % W); t /= W;
+    const int h = (int)(t % H);
+    const int64_t n = t / H;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (!(h & 1) && !(w & 1) && (h >> 1) < Ho && (w >> 1) < Wo) v = __ldg(g + ((n * Ho + (h >> 1)) * Wo + (w >> 1)) * Cv + c);
+    up[o] = v;
+  }
+}
+
+// row_bytes = C * sizeof(element), a multiple of 16
+CEB_API int ceb_subsample2_nhwc(const void* x, void* out, int N, int H, int W, int row_bytes, void* stream) {
+  CEB_REQUIRE(x && out && N > 0 && H > 0 && W > 0 && row_bytes % 16 == 0, "ceb_subsample2_nhwc: bad arguments");
+  const int Ho = (H + 1) / 2, Wo = (W + 1) / 2, Cv = row_bytes / 16;
+  subsample2_kernel<<<ceb_grid_for((int64_t)N * Ho * Wo * Cv, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)x, (uint4*)out, N, H, W, Ho, Wo, Cv);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
+CEB_API int ceb_upsample2_zero_nhwc(const void* g, void* up, int N, int H, int W, int Ho, int Wo, int row_bytes, void* stream) {
+  CEB_REQUIRE(g && up && N > 0 && H > 0 && W > 0 && row_bytes % 16 == 0, "ceb_upsample2_zero_nhwc: bad arguments");
+  CEB_REQUIRE(2 * (Ho - 1) < H && 2 * (Wo - 1) < W, "ceb_upsample2_zero_nhwc: %dx%d does not fit %dx%d", Ho, Wo, H, W);
+  const int Cv = row_bytes / 16;
+  upsample2_zero_kernel<<<ceb_grid_for((int64_t)N * H * W * Cv, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)g, (uint4*)up, N, H, W, Ho, Wo, Cv);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;

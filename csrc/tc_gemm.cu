@@ -38,9 +38,13 @@ struct TcParams {
   int m_tiles, n_tiles;
   // convolution geometry
   int conv;
-  int H, W, cin_steps;   // cin_steps = Cin / 64
-  int tile_h;            // rows of the image covered by one M tile (tile_w == W)
+  int H, W, cin_steps;   // OUTPUT map height / width; cin_steps = Cin / (elements per 128-byte row)
+  int tile_h;            // rows of the output map covered by one M tile (tile_w == W)
   int halo_bytes;        // MODE 1: bytes of one activation halo box
+  // general convolution geometry (MODE 0): filter size 1 or 3, stride, padding; an M tile covers tile_pix
+  // (<= 128) output pixels -- whole rows of the output map, so maps whose width does not divide 128 (28, 14,
+  // 7, 3) leave the last rows of the 128-row MMA tile unused -- and its activation box holds a_bytes
+  int ks, stride, pad, tile_pix, a_bytes;
   // optional device-side row count: only the M tiles covering rows [0, *m_limit) are computed
   // (rows are compacted by the caller; lets a CUDA-graph-captured launch follow a data-dependent
   // row count without a host round trip)
@@ -118,7 +122,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   const bool leader = cta_rank == 0;
   int m_tiles_rt = p.m_tiles;
   if (p.m_limit) {
-    const int lim = (__ldg(p.m_limit) + BMT - 1) / BMT;
+    const int lim = (__ldg(p.m_limit) + p.tile_pix - 1) / p.tile_pix;
     m_tiles_rt = lim < m_tiles_rt ? lim : m_tiles_rt;
   }
   // work is handed out in units of PAIR vertically adjacent CTA tiles; a CTA of a pair owns
@@ -158,7 +162,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         const int b_row0 = n_tile * BN + (int)cta_rank * (BN / PAIR);   // this CTA's share of the weight tile
         int n0 = 0, h0 = 0;
         if (p.conv) {
-          const int pix0 = m_tile * BMT;
+          const int pix0 = m_tile * p.tile_pix;
           const int hw = p.H * p.W;
           n0 = pix0 / hw;
           h0 = (pix0 - n0 * hw) / p.W;
@@ -181,12 +185,12 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
               for (int r = 0; r < 3; ++r)
                 tma_load_2d_pair(b_dst + r * L::kBTileBytes, &tmapB, fbar, ((r * 3 + sft) * p.cin_steps) * BKE + c0, b_row0);
             } else {
-              if (leader) mbar_expect_tx(full_bar + s, 2u * L::kStageBytes);
+              if (leader) mbar_expect_tx(full_bar + s, 2u * ((uint32_t)p.a_bytes + L::kBBytes));
               if (p.conv) {
                 const int tap = ks / p.cin_steps;
                 const int c0 = (ks - tap * p.cin_steps) * BKE;
-                const int r = tap / 3, sft = tap - r * 3;
-                tma_load_4d_pair(a_dst, &tmapA, fbar, c0, sft - 1, h0 + r - 1, n0);
+                const int r = tap / p.ks, sft = tap - r * p.ks;
+                tma_load_4d_pair(a_dst, &tmapA, fbar, c0, sft - p.pad, h0 * p.stride + r - p.pad, n0);
               } else {
                 tma_load_2d_pair(a_dst, &tmapA, fbar, ks * BKE, m_tile * BM);
               }
@@ -203,12 +207,12 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
               tma_load_2d(b_dst + r * (BN * BK * 2), &tmapB, full_bar + s,
                           ((r * 3 + sft) * p.cin_steps) * BKE + c0, n_tile * BN);
           } else {
-            mbar_expect_tx(full_bar + s, L::kStageBytes);
+            mbar_expect_tx(full_bar + s, (uint32_t)p.a_bytes + L::kBBytes);
             if (p.conv) {
               const int tap = ks / p.cin_steps;
               const int c0 = (ks - tap * p.cin_steps) * BKE;
-              const int r = tap / 3, sft = tap - r * 3;
-              tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - 1, h0 + r - 1, n0);
+              const int r = tap / p.ks, sft = tap - r * p.ks;
+              tma_load_4d(a_dst, &tmapA, full_bar + s, c0, sft - p.pad, h0 * p.stride + r - p.pad, n0);
             } else {
               tma_load_2d(a_dst, &tmapA, full_bar + s, ks * BKE, m_tile * BM);
             }
@@ -302,8 +306,11 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         const int sc = half * kPer + i;
         const int sub = sc / (BN / 32), c = sc - sub * (BN / 32);
         if (PAIR == 2 && m_tile >= m_tiles_rt) return;     // the peer's tile lies past the (device-side) row limit
-        const int row0 = m_tile * BMT + sub * BM + q * 32;   // first output row of this warp
+        const int row0 = m_tile * p.tile_pix + sub * BM + q * 32;   // first output row of this warp
         const int m = row0 + lane;
+        // rows of this tile that exist: inside the matrix and inside the tile's tile_pix valid pixels
+        const int m_end_tile = m_tile * p.tile_pix + p.tile_pix;
+        const int M_lim = m_end_tile < p.M ? m_end_tile : p.M;
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(cur[j]);
@@ -320,7 +327,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         const bool full = (n0 + 32 <= p.N);
         if (TF && p.out_fp32 == 1) {
           // fp32 activations: the thread's 32 columns are 128 contiguous bytes of its output row
-          if (m >= p.M) return;
+          if (m >= M_lim) return;
           const int64_t off = (int64_t)m * p.ldc + n0;
           float* crow = (float*)p.C + off;
           const float* mrow = p.mask ? (const float*)p.mask + off : nullptr;
@@ -367,7 +374,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           return;
         }
         if (direct && full) {
-          if (m < p.M) {
+          if (m < M_lim) {
             const int64_t off = (int64_t)m * p.ldc + n0;
 #pragma unroll
             for (int h2 = 0; h2 < 2; ++h2) {
@@ -406,7 +413,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           }
           return;
         }
-        if (p.mask && m < p.M && !(p.out_fp32 == 0 && full)) {   // (the bf16 staged path masks while storing)
+        if (p.mask && m < M_lim && !(p.out_fp32 == 0 && full)) {   // (the bf16 staged path masks while storing)
           const __nv_bfloat16* mk = (const __nv_bfloat16*)p.mask + (int64_t)m * p.ldc + n0;
 #pragma unroll
           for (int j = 0; j < 32; ++j)
@@ -424,7 +431,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           for (int pass = 0; pass < 4; ++pass) {
             const int r = pass * 8 + (lane >> 2);
             const int w4 = (lane & 3) * 4;
-            if (row0 + r < p.M) {
+            if (row0 + r < M_lim) {
               uint4 pk;
               pk.x = stage[r * 17 + w4]; pk.y = stage[r * 17 + w4 + 1];
               pk.z = stage[r * 17 + w4 + 2]; pk.w = stage[r * 17 + w4 + 3];
@@ -442,7 +449,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             }
           }
           __syncwarp();
-        } else if (m < p.M) {
+        } else if (m < M_lim) {
           if (p.out_fp32 == 0) {
             __nv_bfloat16* dst = (__nv_bfloat16*)p.C + (int64_t)m * p.ldc + n0;
 #pragma unroll
@@ -568,7 +575,10 @@ static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcPar
     configured = true;
   }
   TcParams q = p;
-  q.m_tiles = (int)ceb_cdiv(p.M, BM * L::kSubTiles);
+  if (q.tile_pix == 0) q.tile_pix = BM * L::kSubTiles;
+  if (q.a_bytes == 0) q.a_bytes = BM * 128;
+  if (q.ks == 0) { q.ks = 3; q.stride = 1; q.pad = 1; }
+  q.m_tiles = (int)ceb_cdiv(p.M, q.tile_pix);
   q.n_tiles = (int)ceb_cdiv(p.N, BN);
   const int tiles = q.m_tiles * q.n_tiles;
   const int grid = tiles < ceb_num_sms() ? tiles : ceb_num_sms();
@@ -589,7 +599,10 @@ static int launch_tile_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
     configured = true;
   }
   TcParams q = p;
-  q.m_tiles = (int)ceb_cdiv(p.M, BM * L::kSubTiles);
+  if (q.tile_pix == 0) q.tile_pix = BM * L::kSubTiles;
+  if (q.a_bytes == 0) q.a_bytes = BM * 128;
+  if (q.ks == 0) { q.ks = 3; q.stride = 1; q.pad = 1; }
+  q.m_tiles = (int)ceb_cdiv(p.M, q.tile_pix);
   q.n_tiles = (int)ceb_cdiv(p.N, BN);
   const int pair_tiles = (int)ceb_cdiv(q.m_tiles, 2) * q.n_tiles;
   const int max_pairs = ceb_num_sms() / 2;
@@ -783,39 +796,68 @@ CEB_API int ceb_conv3x3_bf16_nhwc_res(const void* x, const void* w, void* y, int
   return conv3x3_impl(x, w, y, Nimg, H, W, Cin, Cout, bias, relu, 0, relu_mask, resid, y2, stream);
 }
 
-static int conv3x3_impl(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, const float* bias,
-                        int relu, int out_mode, const void* relu_mask, const void* resid, void* y2, void* stream, int tf) {
+// General NHWC convolution: filter ks x ks (1 or 3), stride 1 or 2, padding pad; H, W are the INPUT map dims.
+static int conv_impl(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, int ks, int stride,
+                     int pad, const float* bias, int relu, int out_mode, const void* relu_mask, const void* resid, void* y2,
+                     void* stream, int tf) {
   const int esz = tf ? 4 : 2, bke = 128 / esz;
-  CEB_REQUIRE(x && w && y && Nimg > 0, "ceb_conv3x3_nhwc: bad arguments");
-  CEB_REQUIRE(Cin % bke == 0 && Cout % 8 == 0, "ceb_conv3x3_nhwc: need Cin %% %d == 0, Cout %% 8 == 0 (Cin=%d Cout=%d)", bke, Cin, Cout);
-  CEB_REQUIRE(W <= BM && BM % W == 0, "ceb_conv3x3_nhwc: W=%d must divide %d", W, BM);
-  int tile_h = BM / W, tile_n = 1;
-  if (tile_h > H) {
-    CEB_REQUIRE(tile_h % H == 0, "ceb_conv3x3_nhwc: H=%d W=%d does not tile %d pixels", H, W, BM);
-    tile_n = tile_h / H;
-    tile_h = H;
-  } else {
-    CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_nhwc: H=%d not a multiple of the %d-row tile", H, tile_h);
-  }
+  CEB_REQUIRE(x && w && y && Nimg > 0, "ceb_conv_nhwc: bad arguments");
+  CEB_REQUIRE((ks == 1 || ks == 3) && (stride == 1 || stride == 2) && pad >= 0 && pad <= 1,
+              "ceb_conv_nhwc: filter %d stride %d pad %d not supported", ks, stride, pad);
+  CEB_REQUIRE(Cin % bke == 0 && Cout % 8 == 0, "ceb_conv_nhwc: need Cin %% %d == 0, Cout %% 8 == 0 (Cin=%d Cout=%d)", bke, Cin, Cout);
+  const int Ho = (H + 2 * pad - ks) / stride + 1, Wo = (W + 2 * pad - ks) / stride + 1;
+  CEB_REQUIRE(Ho > 0 && Wo > 0 && Wo <= BM, "ceb_conv_nhwc: output map %d x %d", Ho, Wo);
+  // An M tile = whole rows of the OUTPUT map: tile_h rows of one image, or tile_n whole images.
+  int tile_h = 1, tile_n = 1;
+  for (int th = 1; th <= Ho; ++th)
+    if (Ho % th == 0 && th * Wo <= BM) tile_h = th;
+  if (tile_h == Ho) tile_n = BM / (Ho * Wo);
+  if (tile_n < 1) tile_n = 1;
+  if (tile_n > Nimg) tile_n = Nimg;
+  const int tile_pix = tile_h * Wo * tile_n;
   const int bn = pick_bn(Cout);
-  // halo mode: 256-pixel tiles that stay inside one image, weights tile <= 128 wide
+  // halo mode: 3x3 / stride 1, 256-pixel tiles that stay inside one image, weights tile <= 128 wide
   static const bool force_v1 = getenv("CEB_CONV_V1") != nullptr;
-  const int rows256 = (W > 0 && 256 % W == 0) ? 256 / W : 0;
-  const bool halo = !force_v1 && bn <= 128 && (W == 16 || W == 32) && rows256 > 0 && rows256 <= H && H % rows256 == 0;
+  const int rows256 = (Wo > 0 && 256 % Wo == 0) ? 256 / Wo : 0;
+  const bool halo = !force_v1 && ks == 3 && stride == 1 && pad == 1 && bn <= 128 && (Wo == 16 || Wo == 32) && rows256 > 0 &&
+                    rows256 <= Ho && Ho % rows256 == 0;
   CUtensorMap ta, tb;
   uint64_t da[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
   uint64_t sa[3] = {(uint64_t)Cin * esz, (uint64_t)W * Cin * esz, (uint64_t)H * W * Cin * esz};
-  uint32_t ba[4] = {(uint32_t)bke, (uint32_t)W, (uint32_t)(halo ? rows256 + 2 : tile_h), (uint32_t)(halo ? 1 : tile_n)};
-  if (int e = ceb_make_tmap(&ta, esz, x, 4, da, sa, ba, nullptr)) return e;
-  const int K = 9 * Cin;
-  const bool pair = use_pair(halo ? 1 : 0, Nimg * H * W, Cout, bn, halo ? 256 : BM, (halo ? 3 : 9) * (Cin / bke));
+  // with a traversal stride the box spans count * stride input elements (TMA keeps every stride-th one)
+  uint32_t ba[4] = {(uint32_t)bke, (uint32_t)(Wo * stride), (uint32_t)((halo ? rows256 + 2 : tile_h) * stride),
+                    (uint32_t)(halo ? 1 : tile_n)};
+  uint32_t es[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
+  if (int e = ceb_make_tmap(&ta, esz, x, 4, da, sa, ba, es)) return e;
+  const int K = ks * ks * Cin;
+  const int k_steps = (halo ? 3 : ks * ks) * (Cin / bke);
+  const bool pair = use_pair(halo ? 1 : 0, Nimg * Ho * Wo, Cout, bn, halo ? 256 : tile_pix, k_steps);
   uint64_t db[2] = {(uint64_t)K, (uint64_t)Cout}, sb[1] = {(uint64_t)K * esz};
   uint32_t bb[2] = {(uint32_t)bke, (uint32_t)(pair ? bn / 2 : bn)};
   if (int e = ceb_make_tmap(&tb, esz, w, 2, db, sb, bb, nullptr)) return e;
   TcParams p{};
-  p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * H * W; p.N = Cout; p.ldc = Cout; p.resid = resid; p.C2 = y2;
-  p.k_steps = (halo ? 3 : 9) * (Cin / bke);
-  p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = H; p.W = W; p.cin_steps = Cin / bke; p.tile_h = tile_h;
-  p.halo_bytes = halo ? (rows256 + 2) * W * 128 : 0;
+  p.C = y; p.bias = bias; p.mask = relu_mask; p.M = Nimg * Ho * Wo; p.N = Cout; p.ldc = Cout; p.resid = resid; p.C2 = y2;
+  p.k_steps = k_steps;
+  p.relu = relu; p.out_fp32 = out_mode; p.conv = 1; p.H = Ho; p.W = Wo; p.cin_steps = Cin / bke; p.tile_h = tile_h;
+  p.halo_bytes = halo ? (rows256 + 2) * Wo * 128 : 0;
+  p.ks = ks; p.stride = stride; p.pad = pad;
+  p.tile_pix = halo ? 256 : tile_pix;
+  p.a_bytes = tile_pix * 128;
   return dispatch_tile(bn, halo ? 1 : 0, ta, tb, p, (cudaStream_t)stream, pair, tf);
+}
+
+static int conv3x3_impl(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, const float* bias,
+                        int relu, int out_mode, const void* relu_mask, const void* resid, void* y2, void* stream, int tf) {
+  return conv_impl(x, w, y, Nimg, H, W, Cin, Cout, 3, 1, 1, bias, relu, out_mode, relu_mask, resid, y2, stream, tf);
+}
+
+// y[N,Ho,Wo,Cout] = act(conv_{ks x ks, stride, pad}(x[N,H,W,Cin], w[Cout,ks,ks,Cin])) (+ mask / residual as in
+// ceb_conv3x3_*): ks in {1, 3}, stride in {1, 2}, any map size whose output width is <= 128 (rows of the
+// output map are tiled whole, so widths such as 28, 14, 7, 3 work).  f32 = 0: bf16 tensors (out_mode as in
+// ceb_conv3x3_bf16_nhwc, mask / resid / y2 bf16); f32 = 1: fp32 tensors on the TF32 path.
+CEB_API int ceb_conv2d_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, int ks,
+                            int stride, int pad, int relu, int f32, const void* relu_mask, const void* resid, void* y2,
+                            void* stream) {
+  return conv_impl(x, w, y, Nimg, H, W, Cin, Cout, ks, stride, pad, nullptr, relu, f32 ? 1 : 0, relu_mask, resid, y2,
+                   stream, f32);
 }

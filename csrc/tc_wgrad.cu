@@ -40,6 +40,10 @@ struct WgParams {
   int ldw;               // row stride of dW (9*Cin for a convolution, ldc for a plain GEMM)
   int vec_ok;            // dW is 16-byte aligned (it is a slice of the flat gradient buffer): vector atomics allowed
   const int* k_limit;    // optional device-side count of reduction rows (see ceb_gemm_bf16_mn_acc_rows)
+  // general convolution geometry: H, W above are the OUTPUT map; a k-step covers kpix (<= the template's k-step)
+  // output pixels -- whole rows of the output map -- and transfers stage_bytes; the rows of a stage beyond kpix
+  // are never written by TMA and are zeroed once at kernel start (zero pixels add nothing to the reduction)
+  int stride, pad, kpix, stage_bytes;
 };
 
 // Shared-memory ring.  TAPS weight-tap tiles per stage (3 for a convolution row, 1 for a plain GEMM);
@@ -107,7 +111,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
   const int co_tile = (CONV ? unit / (p.ci_tiles * 3) : unit / p.ci_tiles) * PAIR + (int)cta_rank;
   const int ks_begin = blockIdx.y * p.k_per_cta;
   int ks_total = p.k_steps_total;
-  if (p.k_limit) ks_total = min(ks_total, (__ldg(p.k_limit) + WG_KPIX - 1) / WG_KPIX);
+  if (p.k_limit) ks_total = min(ks_total, (__ldg(p.k_limit) + p.kpix - 1) / p.kpix);
   const int ks_end = min(ks_begin + p.k_per_cta, ks_total);
   const int n_steps = ks_end - ks_begin;
   constexpr int TMEM_COLS = L::kTmemCols;
@@ -121,6 +125,12 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
     }
     mbar_init(tmem_full_bar, 1);
     mbar_fence_init();
+  }
+  if (p.kpix < WG_KPIX) {
+    // partial k-steps: rows [kpix, k-step) of every chunk stay untouched by TMA -- make them zero
+    uint4* z = reinterpret_cast<uint4*>(smem);
+    for (int i = threadIdx.x; i < kStages * L::kStageBytes / 16; i += blockDim.x) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   if (warp == 1) {
     if (PAIR == 2) tmem_alloc_pair<TMEM_COLS>(tmem_slot);
@@ -142,11 +152,11 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
           mbar_wait(empty_bar + s, phase ^ 1);
           uint8_t* a_dst = smem + s * L::kStageBytes;
           uint8_t* b_dst = a_dst + L::kABytes;
-          const int pix0 = (ks_begin + i) * WG_KPIX;
+          const int pix0 = (ks_begin + i) * p.kpix;
           if (PAIR == 2) {
             // both CTAs' bytes are counted on the leader's barrier, which only the leader arms
             const uint32_t fbar = mapa_u32(smem_u32(full_bar + s), 0);
-            if (leader) mbar_expect_tx(full_bar + s, 2u * L::kStageBytes);
+            if (leader) mbar_expect_tx(full_bar + s, 2u * (uint32_t)p.stage_bytes);
 #pragma unroll
             for (int ac = 0; ac < L::kAChunks; ++ac)
               tma_load_2d_pair(a_dst + ac * L::kChunk, &tmapDZ, fbar, co_tile * WG_M + ac * CHE, pix0);
@@ -157,15 +167,15 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
               for (int sft = 0; sft < 3; ++sft)
 #pragma unroll
                 for (int ch = 0; ch < CH; ++ch)
-                  tma_load_4d_pair(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, fbar, ci_base + ch * CHE, sft - 1,
-                                   h0 + r - 1, n0);
+                  tma_load_4d_pair(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, fbar, ci_base + ch * CHE, sft - p.pad,
+                                   h0 * p.stride + r - p.pad, n0);
             } else {
 #pragma unroll
               for (int ch = 0; ch < CH; ++ch)
                 tma_load_2d_pair(b_dst + ch * L::kChunk, &tmapX, fbar, ci_base + ch * CHE, pix0);
             }
           } else {
-            mbar_expect_tx(full_bar + s, L::kStageBytes);
+            mbar_expect_tx(full_bar + s, (uint32_t)p.stage_bytes);
             // dZ: 2-D [pixels][Cout]: two 64-channel chunks
 #pragma unroll
             for (int ac = 0; ac < L::kAChunks; ++ac)
@@ -178,8 +188,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDZ, const __grid_constan
               for (int sft = 0; sft < 3; ++sft)
 #pragma unroll
                 for (int ch = 0; ch < CH; ++ch)
-                  tma_load_4d(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, full_bar + s, ci_base + ch * CHE, sft - 1,
-                              h0 + r - 1, n0);
+                  tma_load_4d(b_dst + (sft * CH + ch) * L::kChunk, &tmapX, full_bar + s, ci_base + ch * CHE, sft - p.pad,
+                              h0 * p.stride + r - p.pad, n0);
             } else {
 #pragma unroll
               for (int ch = 0; ch < CH; ++ch)
@@ -292,6 +302,8 @@ static int launch_wgrad(const CUtensorMap& tdz, const CUtensorMap& tx, WgParams 
     CEB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel<BN, CONV, PAIR, TF>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
     configured = true;
   }
+  if (p.kpix == 0) { p.kpix = WgGeom<TF>::kPix; p.stride = 1; p.pad = 1; }
+  if (p.stage_bytes == 0) p.stage_bytes = L::kStageBytes;
   dim3 grid((unsigned)(PAIR * co_units * (CONV ? 3 : 1) * p.ci_tiles), (unsigned)split, 1);
   if (PAIR == 2) {
     cudaLaunchConfig_t cfg = {};
@@ -324,38 +336,47 @@ static int wg_pair_env() {
 // TF32 (tf = 1).  Cin, Cout multiples of 64, W in {4,8,16,32(,64 bf16)}, H*W a multiple of the k-step or a
 // divisor of it.
 static int conv_wgrad_impl(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin, int Cout,
-                           void* stream, int tf) {
-  const int esz = tf ? 4 : 2, che = 128 / esz, kpix = tf ? 32 : 64;
+                           void* stream, int tf, int stride = 1) {
+  const int esz = tf ? 4 : 2, che = 128 / esz, kmax = tf ? 32 : 64;
   CEB_REQUIRE(dz && x && dW && Nimg > 0, "ceb_conv3x3_wgrad_nhwc: bad arguments");
   CEB_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "ceb_conv3x3_wgrad_nhwc: Cin, Cout must be multiples of 64 (Cin=%d Cout=%d)", Cin, Cout);
-  CEB_REQUIRE(W <= kpix && kpix % W == 0, "ceb_conv3x3_wgrad_nhwc: W=%d must divide %d", W, kpix);
-  int tile_h = kpix / W, tile_n = 1;
-  if (tile_h > H) {
-    CEB_REQUIRE(tile_h % H == 0, "ceb_conv3x3_wgrad_nhwc: H=%d W=%d does not tile %d pixels", H, W, kpix);
-    tile_n = tile_h / H;
-    tile_h = H;
-  } else {
-    CEB_REQUIRE(H % tile_h == 0, "ceb_conv3x3_wgrad_nhwc: H=%d not a multiple of the %d-row step", H, tile_h);
-  }
-  const int64_t npix = (int64_t)Nimg * H * W;
+  CEB_REQUIRE(stride == 1 || stride == 2, "ceb_conv3x3_wgrad_nhwc: stride %d", stride);
+  // H, W: INPUT map; the reduction runs over the pixels of the OUTPUT map (3x3, pad 1)
+  const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+  CEB_REQUIRE(Wo >= 1 && Wo <= kmax, "ceb_conv3x3_wgrad_nhwc: output width %d exceeds the %d-pixel k-step", Wo, kmax);
+  // a k-step = whole rows of the output map (or whole images)
+  int tile_h = 1, tile_n = 1;
+  for (int th = 1; th <= Ho; ++th)
+    if (Ho % th == 0 && th * Wo <= kmax) tile_h = th;
+  if (tile_h == Ho) tile_n = kmax / (Ho * Wo);
+  if (tile_n < 1) tile_n = 1;
+  if (tile_n > Nimg) tile_n = Nimg;
+  const int kpix = tile_h * Wo * tile_n;
+  const int64_t npix = (int64_t)Nimg * Ho * Wo;
   CUtensorMap tdz, tx;
   uint64_t dd[2] = {(uint64_t)Cout, (uint64_t)npix}, sd[1] = {(uint64_t)Cout * esz};
   uint32_t bd[2] = {(uint32_t)che, (uint32_t)kpix};
   if (int e = ceb_make_tmap(&tdz, esz, dz, 2, dd, sd, bd, nullptr, tf != 0)) return e;
   uint64_t dx[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
   uint64_t sx[3] = {(uint64_t)Cin * esz, (uint64_t)W * Cin * esz, (uint64_t)H * W * Cin * esz};
-  uint32_t bx[4] = {(uint32_t)che, (uint32_t)W, (uint32_t)tile_h, (uint32_t)tile_n};
-  if (int e = ceb_make_tmap(&tx, esz, x, 4, dx, sx, bx, nullptr, tf != 0)) return e;
+  uint32_t bx[4] = {(uint32_t)che, (uint32_t)(Wo * stride), (uint32_t)(tile_h * stride), (uint32_t)tile_n};
+  uint32_t es[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
+  if (int e = ceb_make_tmap(&tx, esz, x, 4, dx, sx, bx, es, tf != 0)) return e;
 
   const int bn = (Cin % 128 == 0) ? 128 : 64;
   // CTA pairs: 256 output channels per pair, each CTA stages 64 of the tile's 128 input channels
   const bool pair = bn == 128 && Cout % 256 == 0 && (wg_pair_env() >= 0 ? wg_pair_env() != 0 : true);
   WgParams p{};
-  p.dW = dW; p.Cout = Cout; p.Cin = Cin; p.H = H; p.W = W;
+  p.dW = dW; p.Cout = Cout; p.Cin = Cin; p.H = Ho; p.W = Wo;
   p.k_steps_total = (int)ceb_cdiv(npix, kpix);
   p.ci_tiles = Cin / bn;
   p.tile_h = tile_h; p.tile_n = tile_n; p.ldw = 9 * Cin;
   p.vec_ok = (((uintptr_t)dW & 15) == 0) ? 1 : 0;
+  p.stride = stride; p.pad = 1; p.kpix = kpix;
+  {
+    const int a_chunks = WG_M / che, b_chunks = 3 * (bn / che) / (pair ? 2 : 1);
+    p.stage_bytes = (a_chunks + b_chunks) * kpix * 128;
+  }
   const int co_units = (int)ceb_cdiv(Cout, WG_M * (pair ? 2 : 1));
   const int base_ctas = (pair ? 2 : 1) * co_units * 3 * p.ci_tiles;
   int split = pick_split(base_ctas, p.k_steps_total);
@@ -370,6 +391,13 @@ static int conv_wgrad_impl(const void* dz, const void* x, float* dW, int Nimg, i
   if (pair) return launch_wgrad<128, true, 2>(tdz, tx, p, co_units, split, st);
   if (bn == 128) return launch_wgrad<128, true, 1>(tdz, tx, p, co_units, split, st);
   return launch_wgrad<64, true, 1>(tdz, tx, p, co_units, split, st);
+}
+
+// General form: 3x3 / pad 1 convolution with stride 1 or 2 over an INPUT map H x W (any size whose output
+// width fits a k-step: <= 64 pixels bf16, <= 32 TF32); dz is [N, Ho, Wo, Cout].  f32 = 1: fp32 operands (TF32).
+CEB_API int ceb_conv3x3_wgrad_nhwc(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin, int Cout,
+                                   int stride, int f32, void* stream) {
+  return conv_wgrad_impl(dz, x, dW, Nimg, H, W, Cin, Cout, stream, f32, stride);
 }
 
 CEB_API int ceb_conv3x3_wgrad_bf16_nhwc(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin,
