@@ -279,7 +279,8 @@ class FedModel:
                                           self.device, self.num_clients, peer=self.rt.peer)
         # With the peer-memory backend the cross-rank sum is fused into the server kernel
         # (FedOptimizer.step); otherwise it happens here, right after the clients ran.
-        self.fused_reduce = (self.rt.peer is not None and args.mode in ("sketch", "uncompressed", "local_topk", "fedavg")
+        self.fused_reduce = (self.rt.peer is not None
+                             and args.mode in ("sketch", "uncompressed", "local_topk", "fedavg", "true_topk")
                              and not (args.mode == "uncompressed" and args.do_dp and args.dp_mode == "server")
                              and not getattr(args, "p2", 0))
         self.reduce_pending = False
@@ -620,6 +621,16 @@ class FedOptimizer(torch.optim.Optimizer):
         self._noise_calls = 0
         self.last_update = None           # (idx, val) of the last sparse update, for inspection
         self._tail = {"calls": 0, "graph": None, "gen": -1, "src": 0, "lr": None, "out": None, "native": 0}
+        # multi-GPU sparse modes: the server tail is sharded -- every rank estimates / owns 1/W of the coordinates
+        # and the exact top-k is found by the distributed select (parallel/symm.py:DistSelect)
+        self.dsel = None
+        self._est_slice = None
+        if fm.fused_reduce and args.mode in ("sketch", "true_topk") and not getattr(args, "replicated_tail", False):
+            from .parallel.symm import DistSelect
+            self.dsel = DistSelect(peer, min(int(args.k), fm.fp.numel))
+            if args.mode == "sketch":
+                lo_c, hi_c = DistSelect.coord_range(fm.fp.numel, peer.rank, peer.world)
+                self._est_slice = torch.empty(max(hi_c - lo_c, 1), dtype=torch.float32, device=device)
 
     # -- learning rate -----------------------------------------------------------------
     def get_lr(self):
@@ -712,13 +723,32 @@ class FedOptimizer(torch.optim.Optimizer):
     def _sketch_tail(self, plan, src, lr, record):
         """Heavy-hitter recovery, bucket zeroing + weight update, byte accounting (sketch mode)."""
         fm, args = self.fed_model, self.args
-        idx, val = sk.unsketch_topk(plan, src, args.k)
+        if self.dsel is not None:
+            idx, val = self._unsketch_topk_sharded(plan, src)
+        else:
+            idx, val = sk.unsketch_topk(plan, src, args.k)
         sk.apply_zero(plan, idx, val, self.Vvelocity,
                       self.Verror if args.error_type == "virtual" else None, fm.fp.flat, lr)
         if args.error_type == "local":
             self.Verror.copy_(self.Vvelocity)
         record(idx)
         return idx, val
+
+    def _unsketch_topk_sharded(self, plan, table):
+        """Heavy-hitter recovery with the work divided over the ranks: this rank computes the median estimates of
+        its d/W coordinates only (``ceb_sketch_unsketch_est_range``), the exact global top-k comes out of the
+        distributed select, and every rank ends up with the same ``(idx, val)`` list."""
+        from .ops import native
+        from .parallel.symm import DistSelect
+        fm = self.fed_model
+        peer = fm.rt.peer
+        d = fm.fp.numel
+        lo, hi = DistSelect.coord_range(d, peer.rank, peer.world)
+        scratch = native.select_scratch(fm.device)
+        native.call("ceb_sketch_unsketch_est_range", native.ptr(table), native.ptr(plan.packed), plan.n_tokens,
+                    native.ptr(plan.blk), plan.num_blocks, plan.r, plan.c, plan.d, lo, hi, native.ptr(self._est_slice),
+                    native.ptr(scratch), scratch.numel(), native.stream_ptr(fm.device))
+        return self.dsel.run(self._est_slice[:hi - lo], lo, scratch, pass1_done=True)
 
     def _sketch_tail_graphed(self, plan, src, lr: float):
         """The tail of the sketch-mode server step as ONE CUDA-graph replay (after two eager rounds):
@@ -761,6 +791,27 @@ class FedOptimizer(torch.optim.Optimizer):
         peer, w = fm.rt.peer, fm.worker
         lo = self.shard_lo
         vv_shard = self.Vvelocity.view(-1)[lo:]
+        if args.mode == "true_topk":
+            if self.dsel is None:
+                # replicated tail (--replicated_tail): plain all-reduce, then the single-GPU rule on every rank
+                peer.all_reduce_buffer_(w.transmit_buf)
+                return False
+            from .ops import native
+            d = fm.fp.numel
+            hi = min(self.shard_hi, d)
+            ve_shard = self.Verror.view(-1)[lo:]
+            peer.fused_topk_state(w.transmit_buf, vv_shard, ve_shard, inv_n, rho)
+            scratch = native.select_scratch(fm.device)
+            idx, val = self.dsel.run(ve_shard[:max(hi - lo, 0)], lo, scratch, pass1_done=False)
+            lr_vec = lr if torch.is_tensor(lr) else None
+            native.call("ceb_dense_apply_zero_shard", native.ptr(idx), native.ptr(val), idx.numel(), native.ptr(vv_shard),
+                        native.ptr(ve_shard), lo, hi, native.ptr(fm.fp.flat), 0.0 if lr_vec is not None else float(lr),
+                        native.ptr(lr_vec), native.stream_ptr(fm.device))
+            if args.local_momentum > 0:
+                w.mask_velocities(idx, val)
+            fm.tracker.record_sparse(idx)
+            self.last_update = (idx, val)
+            return True
         if args.mode == "sketch":
             ve_shard = self.Verror.view(-1)[lo:]
             peer.fused_sketch(w.transmit_buf, self.verror_buf, vv_shard, ve_shard, inv_n, rho, args.error_type)

@@ -67,7 +67,7 @@ def _use_native_bf16(x: torch.Tensor) -> bool:
 def conv2d(x, weight, bias=None, stride=1, padding=0):
     if _use_native(x):
         from . import tc
-        if tc.conv_supported(x, weight, stride, padding):
+        if tc.conv_supported(x, weight, stride, padding) or tc.stem_supported(x, weight, stride, padding):
             return tc.conv2d(x, weight, bias, stride, padding, relu=False)
     return F.conv2d(x, weight, bias, stride=stride, padding=padding)
 
@@ -75,7 +75,7 @@ def conv2d(x, weight, bias=None, stride=1, padding=0):
 def conv2d_relu(x, weight, bias=None, stride=1, padding=0):
     if _use_native(x):
         from . import tc
-        if tc.conv_supported(x, weight, stride, padding):
+        if tc.conv_supported(x, weight, stride, padding) or tc.stem_supported(x, weight, stride, padding):
             return tc.conv2d(x, weight, bias, stride, padding, relu=True)
     return F.relu(F.conv2d(x, weight, bias, stride=stride, padding=padding))
 

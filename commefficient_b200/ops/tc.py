@@ -470,7 +470,55 @@ class _ConvFn(torch.autograd.Function):
         return dx, dw, None, None
 
 
+def stem_supported(x, weight, stride, padding) -> bool:
+    """The 1- or 3-channel first layer (3x3 / s1 / p1): lowered to im2col + the tensor-core GEMMs."""
+    if not (x.is_cuda and x.dim() == 4 and weight.dim() == 4) or x.requires_grad:
+        return False
+    co, ci, kh, kw = weight.shape
+    return ((kh, kw, stride, padding) == (3, 3, 1, 1) and ci in (1, 3) and co % 64 == 0 and x.shape[1] == ci
+            and weight.permute(0, 2, 3, 1).is_contiguous())
+
+
+class _StemFn(torch.autograd.Function):
+    """First convolution of an image model (K = 9 or 27 is too thin for an implicit-GEMM tile): one pass writes
+    the im2col matrix (zero padded to one 128-byte row), the layer then IS a K = 64 / 32 GEMM; the weight
+    gradient is the MN-major GEMM over the same matrix.  The input needs no gradient."""
+
+    @staticmethod
+    def forward(ctx, x, weight, relu):
+        dt = act_dtype()
+        xb = x.float().permute(0, 2, 3, 1).contiguous()
+        col = im2col_c3(xb, dt)
+        wk = weight.permute(0, 2, 3, 1)
+        y = gemm_tn(col, _stem_weight_pad(wk.float(), dt), relu=relu)
+        n, _, h, w = x.shape
+        ctx.save_for_backward(col, y if relu else col)
+        ctx.weight, ctx.relu = weight, relu
+        return y.view(n, h, w, -1).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        col, y = ctx.saved_tensors
+        weight = ctx.weight
+        co = weight.shape[0]
+        dz = dy.permute(0, 2, 3, 1).to(col.dtype).contiguous().view(-1, co)
+        if ctx.relu:
+            dz = relu_bwd(y, dz)
+        k = weight[0].numel()
+        g0 = torch.zeros((co, 64), dtype=torch.float32, device=dz.device)
+        gemm_mn_acc(dz, col, g0[:, :col.shape[1]])
+        target = weight.grad if (isinstance(weight, torch.nn.Parameter) and weight.grad is not None
+                                 and weight.grad.permute(0, 2, 3, 1).is_contiguous()) else None
+        if target is not None:
+            target.permute(0, 2, 3, 1).reshape(co, k).add_(g0[:, :k])
+            return None, None, None
+        return None, g0[:, :k].reshape(co, weight.shape[2], weight.shape[3], weight.shape[1]).permute(0, 3, 1, 2), None
+
+
 def conv2d(x, weight, bias, stride, padding, relu=False):
+    if weight.shape[1] in (1, 3):
+        y = _StemFn.apply(x, weight, relu)
+        return y if bias is None else y + bias.view(1, -1, 1, 1)
     y = _ConvFn.apply(x, weight, relu, stride)
     if bias is not None:
         y = y + bias.view(1, -1, 1, 1)

@@ -28,6 +28,16 @@ native.register_signatures({
     "ceb_peer_alloc": ([native.c_i64, ctypes.POINTER(ctypes.c_void_p), native.c_ptr], native.c_i32),
     "ceb_peer_open": ([native.c_ptr, ctypes.POINTER(ctypes.c_void_p)], native.c_i32),
     "ceb_peer_release": ([native.c_ptr, native.c_i32], native.c_i32),
+    "ceb_dsel_exch_bytes": ([], native.c_i64),
+    "ceb_dsel_flag_words": ([], native.c_i32),
+    "ceb_dsel_run": ([native.c_ptr, native.c_i64, native.c_i64, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr,
+                      native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_ptr,
+                      native.c_i32, native.c_ptr], native.c_i32),
+    "ceb_sketch_unsketch_est_range": ([native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr, native.c_i32, native.c_i32,
+                                       native.c_i64, native.c_i64, native.c_i64, native.c_i64, native.c_ptr, native.c_ptr,
+                                       native.c_i64, native.c_ptr], native.c_i32),
+    "ceb_dense_apply_zero_shard": ([native.c_ptr, native.c_ptr, native.c_i64, native.c_ptr, native.c_ptr, native.c_i64,
+                                    native.c_i64, native.c_ptr, native.c_f32, native.c_ptr, native.c_ptr], native.c_i32),
 })
 
 
@@ -204,6 +214,18 @@ class PeerGroup:
         self._launch(2, transmit, weights, self.padded(transmit.numel), Vv_shard, None, inv_n, rho, 0,
                      0.0 if lr_vec is not None else lr, lr_vec)
 
+    def fused_topk_state(self, transmit: SymmBuffer, Vv_shard, Ve_shard, inv_n, rho):
+        """true_topk: reduce-scatter(transmit) -> ``Vv = rho Vv + s/N; Ve += Vv`` on this rank's coordinate shard.
+        Nothing is gathered: the distributed select (``DistSelect``) works on the shards in place."""
+        self._launch(3, transmit, transmit, self.padded(transmit.numel), Vv_shard, Ve_shard, inv_n, rho)
+
+    def check(self):
+        """Raise if a device-side barrier wait ran out of its spin budget (a peer never arrived)."""
+        word = int(self.ticket[2].item())
+        if word:
+            raise RuntimeError("peer-memory barrier timed out on rank %d (phase %d, waiting for rank %d): a peer did "
+                               "not reach the collective" % (self.rank, (word >> 8) & 0xFF, word & 0xFF))
+
     def close(self):
         torch.cuda.synchronize(self.device)
         try:
@@ -213,3 +235,35 @@ class PeerGroup:
         for buf in self.buffers:
             buf.close()
         self.buffers = []
+
+
+class DistSelect:
+    """Exact top-k of a vector that is spread over the ranks (``csrc/dselect.cu``): per-pass histograms are
+    merged through peer memory, winners are written straight into every rank's ``(idx, val)`` lists.  One
+    instance per (group, k); ``run`` is CUDA-graph capturable (its barrier epoch lives on the device)."""
+
+    def __init__(self, group: PeerGroup, k: int):
+        lib = native.lib()
+        self.group, self.k = group, int(k)
+        self.exch = group.symm_empty(int(lib.ceb_dsel_exch_bytes()), torch.uint8)
+        self.flags = group.symm_empty(int(lib.ceb_dsel_flag_words()), torch.int32)
+        self.out_idx = group.symm_empty(self.k, torch.int32)
+        self.out_val = group.symm_empty(self.k, torch.float32)
+        self.epoch = torch.zeros(4, dtype=torch.int32, device=group.device)
+        dist.barrier(device_ids=[group.device.index])
+
+    def run(self, v_slice: torch.Tensor, idx_offset: int, scratch: torch.Tensor, pass1_done: bool):
+        """``v_slice``: this rank's contiguous fp32 slice (may be empty); returns this rank's copies of the
+        global ``(idx int32[k], val float32[k])`` -- identical on every rank."""
+        g = self.group
+        n = int(v_slice.numel())
+        native.call("ceb_dsel_run", native.ptr(v_slice) if n else None, n, int(idx_offset), self.k, native.ptr(scratch),
+                    scratch.numel(), self.exch.ptr_array, self.flags.ptr_array, self.out_idx.ptr_array,
+                    self.out_val.ptr_array, ctypes.c_void_p(g.ticket.data_ptr() + 8), g.rank, g.world,
+                    native.ptr(self.epoch), 1 if pass1_done else 0, native.stream_ptr(g.device))
+        return self.out_idx.tensor, self.out_val.tensor
+
+    @staticmethod
+    def coord_range(d: int, rank: int, world: int):
+        per = (-(-d // world) + 3) // 4 * 4
+        return min(per * rank, d), min(per * (rank + 1), d)

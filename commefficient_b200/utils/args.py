@@ -115,6 +115,9 @@ _FLAGS = [
         _flag("precision", "tf32", str, choices=("fp32", "tf32", "bf16"),
               help="tf32 (default): fp32 activations, TF32 tensor-core inputs, as the reference under cuDNN; "
                    "bf16: fast path; fp32: IEEE fp32 on the library, no tensor cores"),
+        _flag("replicated_tail", store_true=True,
+              help="multi-GPU sketch / true_topk: every rank recomputes the whole server tail (unsketch + top-k) "
+                   "instead of the sharded tail with the distributed select"),
         _flag("p2", 0, int,
               help="FetchSGD second round: re-rank p2*k sketch candidates by exact value"),
         _flag("synthetic", store_true=True, help="generate data of the dataset's shape"),

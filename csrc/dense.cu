@@ -98,6 +98,32 @@ CEB_API int ceb_dense_apply_zero(const int32_t* idx, const float* val, int64_t k
   return 0;
 }
 
+// Sharded form (multi-GPU true_topk): Vv / Ve are this rank's coordinate shard [lo, hi) (indexed from lo); every
+// rank applies the whole update to its weight replica, only the owner of a coordinate zeroes its state.
+__global__ void __launch_bounds__(256)
+dense_apply_zero_shard_kernel(const int32_t* __restrict__ idx, const float* __restrict__ val, int64_t k,
+                              float* __restrict__ Vv, float* __restrict__ Ve, int64_t lo, int64_t hi,
+                              float* __restrict__ w, float lr, const float* __restrict__ lr_vec) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= k) return;
+  const float v = __ldg(val + j);
+  if (v == 0.f) return;
+  const int64_t i = __ldg(idx + j);
+  if (i >= lo && i < hi) { Ve[i - lo] = 0.f; Vv[i - lo] = 0.f; }
+  w[i] -= (lr_vec ? __ldg(lr_vec + i) : lr) * v;
+}
+
+CEB_API int ceb_dense_apply_zero_shard(const int32_t* idx, const float* val, int64_t k, float* Vv_shard, float* Ve_shard,
+                                       int64_t lo, int64_t hi, float* w, float lr, const float* lr_vec, void* stream) {
+  CEB_REQUIRE(idx && val && Vv_shard && Ve_shard && w && lo <= hi, "ceb_dense_apply_zero_shard: bad arguments");
+  if (k <= 0) return 0;
+  dense_apply_zero_shard_kernel<<<(unsigned)ceb_cdiv(k, 256), 256, 0, (cudaStream_t)stream>>>(
+      idx, val, k, Vv_shard, Ve_shard, lo, hi, w, lr, lr_vec);
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
 // true_topk in one call: momentum + error + exact top-k of the error vector + zeroing + apply.
 CEB_API int ceb_true_topk_step(float* Vv, float* Ve, const float* g, float inv_n, float rho, int64_t n,
                                int64_t k, float* w, float lr, const float* lr_vec, uint8_t* changed,

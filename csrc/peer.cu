@@ -15,55 +15,7 @@
 //      (all-gather), and
 //   5. signals completion and waits for the other ranks' pushes to land.
 // No NCCL call is involved.  Buffers are cudaMalloc'd once and exchanged as CUDA IPC handles.
-#include "common.cuh"
-
-constexpr int kMaxPeers = 8;
-constexpr int kPeerThreads = 256;
-constexpr int kFlagStride = 32;   // uint32 slots per phase (>= kMaxPeers, keeps phases on separate lines)
-
-struct CebPeerCtx {
-  float* src[kMaxPeers];        // every rank's transmit (staging) buffer, peer-mapped
-  float* dst[kMaxPeers];        // every rank's destination buffer, peer-mapped
-  uint32_t* flags[kMaxPeers];   // every rank's flag block: [2 phases][kFlagStride]
-  uint32_t* ticket;             // local: finished-block counter
-  int rank, world;
-  uint32_t epoch;
-};
-
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
-  float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
-  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
-               ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-}
-
-// serial-number comparison so the 32-bit epoch may wrap
-__device__ __forceinline__ bool epoch_reached(uint32_t seen, uint32_t want) { return (int32_t)(seen - want) >= 0; }
-
-__device__ __forceinline__ void peer_wait_all(const CebPeerCtx& c, int phase) {
-  if ((int)threadIdx.x < c.world) {
-    const uint32_t* slot = c.flags[c.rank] + phase * kFlagStride + threadIdx.x;
-    while (!epoch_reached(ld_acquire_sys(slot), c.epoch)) __nanosleep(20);
-  }
-  __syncthreads();
-}
-
-__device__ __forceinline__ void peer_signal_all(const CebPeerCtx& c, int phase) {
-  if ((int)threadIdx.x < c.world)
-    st_release_sys(c.flags[threadIdx.x] + phase * kFlagStride + c.rank, c.epoch);
-}
+#include "peer.cuh"
 
 struct OpSum {
   __device__ __forceinline__ float4 operator()(int64_t, float4 s) const { return s; }
@@ -103,7 +55,23 @@ struct OpDense {    // Vv is a shard; w is read from this rank's own replica (ds
 // (compile time, so the per-peer loads unroll), U = float4s per thread per step chosen so
 // that U*W ~ 8 sixteen-byte peer loads are in flight per thread: NVLink needs ~2-3 us x
 // 770 GB/s ~ 2 MB outstanding per GPU to run at link speed.
-template <class Op, int W, int U>
+struct OpTopkState {   // true_topk: Vv = rho*Vv + s/N ; Ve += Vv on this rank's coordinate shard; nothing is gathered
+  float* Vv; float* Ve; float inv_n, rho; int64_t lo;
+  __device__ __forceinline__ float4 operator()(int64_t i, float4 s) const {
+    float4 v = *reinterpret_cast<float4*>(Vv + (i - lo));
+    v.x = fmaf(rho, v.x, s.x * inv_n); v.y = fmaf(rho, v.y, s.y * inv_n);
+    v.z = fmaf(rho, v.z, s.z * inv_n); v.w = fmaf(rho, v.w, s.w * inv_n);
+    *reinterpret_cast<float4*>(Vv + (i - lo)) = v;
+    float4 e = *reinterpret_cast<float4*>(Ve + (i - lo));
+    e.x += v.x; e.y += v.y; e.z += v.z; e.w += v.w;
+    *reinterpret_cast<float4*>(Ve + (i - lo)) = e;
+    return e;
+  }
+};
+
+// GATHER = false: reduce-scatter + update only (the shard's result stays with its owner; the second barrier
+// then only means "every rank has finished reading every transmit buffer").
+template <class Op, int W, int U, bool GATHER = true>
 __global__ void __launch_bounds__(kPeerThreads)
 peer_rs_op_ag_kernel(CebPeerCtx c, int64_t lo, int64_t hi, Op op) {
   __shared__ bool is_last;
@@ -131,8 +99,10 @@ peer_rs_op_ag_kernel(CebPeerCtx c, int64_t lo, int64_t hi, Op op) {
         s.x += part[q][u].x; s.y += part[q][u].y; s.z += part[q][u].z; s.w += part[q][u].w;
       }
       const float4 out = op(i, s);
+      if (GATHER) {
 #pragma unroll
-      for (int q = 0; q < W; ++q) st_peer_f4(c.dst[q] + i, out);
+        for (int q = 0; q < W; ++q) st_peer_f4(c.dst[q] + i, out);
+      }
     }
   }
   __threadfence_system();
@@ -150,7 +120,7 @@ peer_rs_op_ag_kernel(CebPeerCtx c, int64_t lo, int64_t hi, Op op) {
   }
 }
 
-template <class Op>
+template <class Op, bool GATHER = true>
 static void launch_peer(const CebPeerCtx& c, int64_t lo, int64_t hi, Op op, cudaStream_t st) {
   auto grid_for = [&](int U) {
     int64_t need = ceb_cdiv((hi - lo) / 4 + 1, (int64_t)kPeerThreads * U);
@@ -160,7 +130,7 @@ static void launch_peer(const CebPeerCtx& c, int64_t lo, int64_t hi, Op op, cuda
   };
   switch (c.world) {
 #define CEB_PEER_CASE(W_, U_) \
-    case W_: peer_rs_op_ag_kernel<Op, W_, U_><<<grid_for(U_), kPeerThreads, 0, st>>>(c, lo, hi, op); break;
+    case W_: peer_rs_op_ag_kernel<Op, W_, U_, GATHER><<<grid_for(U_), kPeerThreads, 0, st>>>(c, lo, hi, op); break;
     CEB_PEER_CASE(1, 4) CEB_PEER_CASE(2, 4) CEB_PEER_CASE(3, 2) CEB_PEER_CASE(4, 2)
     CEB_PEER_CASE(5, 1) CEB_PEER_CASE(6, 1) CEB_PEER_CASE(7, 1) CEB_PEER_CASE(8, 1)
 #undef CEB_PEER_CASE
@@ -199,6 +169,7 @@ CEB_API int64_t ceb_peer_shard_elems(int64_t n, int world) {
 // mode 0: dst = sum(src)                                      (all-reduce; dst may equal src)
 // mode 1: sketch -- Vv,Ve shards updated, dst = Ve             (error_mode 0: dst = Vv)
 // mode 2: dense  -- Vv shard updated, dst (= weights) -= lr*Vv
+// mode 3: true_topk state -- Vv, Ve shards updated (Ve += Vv), nothing gathered (dst unused; pass src)
 CEB_API int ceb_peer_fused_reduce(int mode, const void* const* src, const void* const* dst,
                                   const void* const* flags, void* ticket, int rank, int world,
                                   unsigned int epoch, int64_t n, float* Vv_shard, float* Ve_shard,
@@ -218,6 +189,9 @@ CEB_API int ceb_peer_fused_reduce(int mode, const void* const* src, const void* 
   } else if (mode == 2) {
     CEB_REQUIRE(Vv_shard, "ceb_peer_fused_reduce: dense mode needs the momentum shard");
     launch_peer(c, lo, hi, OpDense{Vv_shard, (const float*)dst[rank], lr_vec, inv_n, rho, lr, lo}, st);
+  } else if (mode == 3) {
+    CEB_REQUIRE(Vv_shard && Ve_shard, "ceb_peer_fused_reduce: true_topk mode needs both state shards");
+    launch_peer<OpTopkState, false>(c, lo, hi, OpTopkState{Vv_shard, Ve_shard, inv_n, rho, lo}, st);
   } else {
     CEB_REQUIRE(false, "ceb_peer_fused_reduce: unknown mode %d", mode);
   }

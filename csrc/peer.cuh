@@ -1,0 +1,64 @@
+// Device helpers shared by the peer-memory kernels (peer.cu, dselect.cu): system-scope flag barriers over
+// CUDA-IPC-mapped memory with a BOUNDED wait -- a rank that died before signalling must not leave the other
+// GPUs spinning until the host watchdog fires: after kPeerSpinBudget polls (a few seconds) the waiter records
+// the phase in an error word and gives up, which the host reports (parallel/symm.py:PeerGroup.check).
+#pragma once
+#include "common.cuh"
+
+constexpr int kMaxPeers = 8;
+constexpr int kPeerThreads = 256;
+constexpr int kFlagStride = 32;   // uint32 slots per phase (>= kMaxPeers, keeps phases on separate lines)
+
+constexpr unsigned long long kPeerSpinBudget = 1ull << 27;     // x ~40 ns per poll: about five seconds
+
+struct CebPeerCtx {
+  float* src[kMaxPeers];        // every rank's transmit (staging) buffer, peer-mapped
+  float* dst[kMaxPeers];        // every rank's destination buffer, peer-mapped
+  uint32_t* flags[kMaxPeers];   // every rank's flag block: [phases][kFlagStride]
+  uint32_t* ticket;             // local: finished-block counter; ticket[2] = error word (0 = fine)
+  int rank, world;
+  uint32_t epoch;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// serial-number comparison so the 32-bit epoch may wrap
+__device__ __forceinline__ bool epoch_reached(uint32_t seen, uint32_t want) { return (int32_t)(seen - want) >= 0; }
+
+__device__ __forceinline__ void peer_wait_all(const CebPeerCtx& c, int phase) {
+  if ((int)threadIdx.x < c.world) {
+    const uint32_t* slot = c.flags[c.rank] + phase * kFlagStride + threadIdx.x;
+    unsigned long long polls = 0;
+    while (!epoch_reached(ld_acquire_sys(slot), c.epoch)) {
+      __nanosleep(20);
+      if (++polls > kPeerSpinBudget) {          // the peer never arrived: say so and stop waiting
+        atomicExch(c.ticket + 2, 0x80000000u | ((uint32_t)phase << 8) | (uint32_t)threadIdx.x);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void peer_signal_all(const CebPeerCtx& c, int phase) {
+  if ((int)threadIdx.x < c.world)
+    st_release_sys(c.flags[threadIdx.x] + phase * kFlagStride + c.rank, c.epoch);
+}
+

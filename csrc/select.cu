@@ -33,25 +33,6 @@ CEB_API int64_t ceb_select_scratch_bytes() { return (int64_t)sizeof(CebSelectScr
 // threshold per block, (2) every block sums the counts of the blocks before it and writes its entries
 // at their exact ranks.  Loads are 16-byte vectors; in-block ranks come from a warp scan + a 16-entry
 // warp-total table per iteration.
-struct SelSlice { int64_t begin, end; };
-__device__ __forceinline__ SelSlice sel_slice(int64_t n) {
-  const int64_t per_block = ((n + gridDim.x - 1) / gridDim.x + 3) & ~(int64_t)3;
-  SelSlice s;
-  s.begin = (int64_t)blockIdx.x * per_block;
-  s.end = s.begin + per_block < n ? s.begin + per_block : n;
-  if (s.begin > n) s.begin = n;
-  return s;
-}
-__device__ __forceinline__ void sel_load4(const float* __restrict__ v, int64_t i, int64_t end, bool vec, float (&x)[4]) {
-  if (vec && i + 3 < end) {
-    const float4 t = __ldg(reinterpret_cast<const float4*>(v + i));
-    x[0] = t.x; x[1] = t.y; x[2] = t.z; x[3] = t.w;
-  } else {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) x[j] = (i + j < end) ? __ldg(v + i + j) : 0.f;
-  }
-}
-
 __global__ void __launch_bounds__(kSelThreads)
 sel_count_kernel(const float* __restrict__ v, int64_t n, CebSelectScratch* __restrict__ s) {
   __shared__ uint32_t sh_gt, sh_eq;

@@ -143,6 +143,26 @@ sel_hist_kernel(const float* __restrict__ v, int64_t n, CebSelectScratch* __rest
   sel_merge_and_scan<PASS>(sh, s, k);
 }
 
+// Contiguous per-block slices of the vector (the ordered emit and its counting pass must agree on them).
+struct SelSlice { int64_t begin, end; };
+__device__ __forceinline__ SelSlice sel_slice(int64_t n) {
+  const int64_t per_block = ((n + gridDim.x - 1) / gridDim.x + 3) & ~(int64_t)3;
+  SelSlice s;
+  s.begin = (int64_t)blockIdx.x * per_block;
+  s.end = s.begin + per_block < n ? s.begin + per_block : n;
+  if (s.begin > n) s.begin = n;
+  return s;
+}
+__device__ __forceinline__ void sel_load4(const float* __restrict__ v, int64_t i, int64_t end, bool vec, float (&x)[4]) {
+  if (vec && i + 3 < end) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(v + i));
+    x[0] = t.x; x[1] = t.y; x[2] = t.z; x[3] = t.w;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) x[j] = (i + j < end) ? __ldg(v + i + j) : 0.f;
+  }
+}
+
 // Host-side driver shared by ceb_topk_select and the unsketch path.  When
 // `first_pass_done` the caller already accumulated hist1 (fused producer) and ran
 // the pass-1 scan itself; otherwise all passes run here.

@@ -327,6 +327,62 @@ CEB_API int ceb_sketch_unsketch_topk(const float* table, const int32_t* packed, 
   return ceb_select_run(est, d, k, s, out_idx, out_val, true, st);
 }
 
+// Range variant for the sharded server tail: one thread per coordinate i in [lo, hi) (consecutive threads read
+// consecutive packed hash words), estimates written compactly to est[i - lo]; digit-1 histogram of this
+// range accumulated into the scratch (the cross-rank merge is ceb_dsel_run's first step).
+template <int R>
+__global__ void __launch_bounds__(kSelThreads)
+unsketch_est_range_kernel(const float* __restrict__ table, uint32_t c, const int32_t* __restrict__ packed,
+                          int64_t n, const int32_t* __restrict__ blk, int64_t lo, int64_t hi,
+                          float* __restrict__ est, CebSelectScratch* __restrict__ s, uint32_t k) {
+  __shared__ uint32_t sh[4096];
+  for (int j = threadIdx.x; j < 4096; j += blockDim.x) sh[j] = 0;
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    const int64_t b = i / n, t = i - b * n;
+    const uint32_t bp = (uint32_t)__ldg(blk + b);
+    const uint32_t off = bp & 0x7fffffffu;
+    const uint32_t bs = bp & 0x80000000u;
+    float vals[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t hp = (uint32_t)__ldg(packed + (int64_t)r * n + t);
+      uint32_t col = (hp & 0x7fffffffu) + off;
+      if (col >= c) col -= c;
+      const float x = __ldg(table + (int64_t)r * c + col);
+      vals[r] = __uint_as_float(__float_as_uint(x) ^ ((hp & 0x80000000u) ^ bs));
+    }
+    const float m = lower_median<R>(vals);
+    est[i - lo] = m;
+    atomicAdd(&sh[sel_d1(abs_key(m))], 1u);
+  }
+  __syncthreads();
+  sel_merge_and_scan<1>(sh, s, k);
+}
+
+// est (hi - lo floats) receives the median estimates of coordinates [lo, hi); the scratch is zeroed and left
+// with this range's digit-1 histogram (pass1_done = 1 for ceb_dsel_run).
+CEB_API int ceb_sketch_unsketch_est_range(const float* table, const int32_t* packed, int64_t n_tokens,
+                                          const int32_t* blk, int num_blocks, int r, int64_t c, int64_t d,
+                                          int64_t lo, int64_t hi, float* est, void* scratch, int64_t scratch_bytes,
+                                          void* stream) {
+  CEB_REQUIRE(table && packed && blk && scratch, "ceb_sketch_unsketch_est_range: null pointer");
+  if (int e = check_sketch_dims("ceb_sketch_unsketch_est_range", r, c, d, n_tokens, num_blocks)) return e;
+  CEB_REQUIRE(lo >= 0 && lo <= hi && hi <= d && (hi == lo || est), "ceb_sketch_unsketch_est_range: bad range [%lld, %lld) of %lld",
+              (long long)lo, (long long)hi, (long long)d);
+  CEB_REQUIRE(scratch_bytes >= (int64_t)sizeof(CebSelectScratch), "ceb_sketch_unsketch_est_range: scratch too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  CebSelectScratch* s = (CebSelectScratch*)scratch;
+  CEB_CHECK_CUDA(cudaMemsetAsync(s, 0, sizeof(CebSelectScratch), st));
+  const int grid = ceb_grid_for(hi - lo > 0 ? hi - lo : 1, kSelThreads, 4);
+  CEB_DISPATCH_ROWS(r, (unsketch_est_range_kernel<R><<<grid, kSelThreads, 0, st>>>(
+                           table, (uint32_t)c, packed, n_tokens, blk, lo, hi, est, s, 1u)));
+  CEB_COUNT_LAUNCH(1);
+  CEB_CHECK_LAUNCH();
+  return 0;
+}
+
 // Estimates only (CSVec.unSketch over all coordinates / tests).
 template <int R>
 __global__ void __launch_bounds__(256)

@@ -140,6 +140,31 @@ def _peer_kernel_main(rank, world, out_dir):
     peer.fused_dense(tr2, wb, Vv[lo:], 0.5, 0.9, 0.1)
     torch.cuda.synchronize()
     ok["dense_w"] = float((wb.tensor[:n] - w_ref).abs().max())
+    # distributed exact top-k over per-rank slices (with ties at the threshold) against the single-GPU select
+    from commefficient_b200.ops import native
+    from commefficient_b200.ops.topk import topk_sparse
+    from commefficient_b200.parallel.symm import DistSelect
+    for n_total, k, nties in ((100_003, 1000, 0), (1_000_000, 50_000, 3000), (5000, 4999, 0)):
+        g3 = torch.Generator(device=dev).manual_seed(n_total)              # the same full vector on every rank
+        full = torch.randn(n_total, device=dev, generator=g3)
+        if nties:
+            thr = full.abs().topk(k).values[-1]
+            pos = torch.randperm(n_total, device=dev, generator=g3)[:nties]
+            full[pos] = thr * torch.where(torch.rand(nties, device=dev, generator=g3) < 0.5, -1.0, 1.0)
+        lo, hi = DistSelect.coord_range(n_total, rank, world)
+        ds = DistSelect(peer, k)
+        for rep in range(2):                                               # second call: fresh epoch, reused buffers
+            idx, val = ds.run(full[lo:hi].contiguous(), lo, native.select_scratch(dev), pass1_done=False)
+            torch.cuda.synchronize()
+            torch.distributed.barrier()
+            want_idx, want_val = topk_sparse(full, k)
+            same = torch.equal(idx.long().sort().values, want_idx.long().sort().values)
+            ok["dsel_%d_%d_set" % (n_total, rep)] = 0.0 if same else 1.0
+            ok["dsel_%d_%d_val" % (n_total, rep)] = float((full[idx.long()] - val).abs().max())
+            gathered = [torch.empty_like(idx) for _ in range(world)]
+            torch.distributed.all_gather(gathered, idx.contiguous())
+            ok["dsel_%d_%d_replicas" % (n_total, rep)] = 0.0 if all(torch.equal(gathered[0], t) for t in gathered) else 1.0
+    peer.check()
     torch.save(ok, os.path.join(out_dir, "r%d.pt" % rank))
     rt.shutdown()
 
@@ -153,6 +178,22 @@ def test_peer_kernels_two_gpus():
         res = torch.load(os.path.join(out_dir, "r%d.pt" % r))
         for name, err in res.items():
             assert err < 1e-4, (r, name, err)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["sketch", "true_topk"])
+def test_sharded_server_tail_equals_replicated_tail(mode):
+    """The sharded tail (each rank estimates / owns half the coordinates, distributed select) picks the
+    coordinates the replicated tail picks: replicas identical bit for bit within a run, and the two runs agree to
+    the run-to-run noise of the (library, small-model) convolutions -- one differently chosen coordinate would
+    move the weights by three orders of magnitude more."""
+    _need_gpus(2)
+    a = _spawn(2, "cuda", mode, "b200", rounds=4)
+    b = _spawn(2, "cuda", mode, "b200", rounds=4, replicated_tail=True)
+    torch.testing.assert_close(a[0]["w"], a[1]["w"], rtol=0, atol=0)
+    torch.testing.assert_close(b[0]["w"], b[1]["w"], rtol=0, atol=0)
+    np.testing.assert_allclose(a[0]["losses"], b[0]["losses"], rtol=1e-5, atol=1e-5)
+    assert float((a[0]["w"] - b[0]["w"]).norm() / b[0]["w"].norm()) < 1e-5
 
 
 @pytest.mark.gpu
