@@ -54,6 +54,7 @@ def main():
     ap.add_argument("--per_client", type=int, default=5)
     ap.add_argument("--num_clients", type=int, default=10000)
     ap.add_argument("--port", type=int, default=5315)
+    ap.add_argument("--config", default="resnet9_sketch", help="a key of baseline/bench_configs.py:CONFIGS")
     # accuracy-vs-round curve mode (bench/curves.py): same data, initial weights and LR schedule as our arm
     ap.add_argument("--curve_out", default="")
     ap.add_argument("--curve_init", default="", help="state_dict file with the initial weights")
@@ -67,6 +68,10 @@ def main():
     cfg = ap.parse_args()
 
     _prepare_paths()
+    sys.path.insert(0, HERE)
+    import bench_configs
+    if bench_configs.CONFIGS[cfg.config]["family"] == "gpt2":
+        os.environ["CEB_REF_GPT2"] = "1"          # the pytorch_transformers stand-in builds its GPT-2 adapter classes
     if cfg.gpus == 1:
         os.environ["CEB_REF_ONE_GPU"] = "1"
     import _ref_compat  # noqa: F401
@@ -74,33 +79,66 @@ def main():
     import torch.multiprocessing as multiprocessing
     multiprocessing.set_start_method("spawn")
 
-    ref_argv = ["--dataset_name", "CIFAR10", "--mode", "sketch", "--error_type", "virtual",
-                "--local_momentum", "0", "--virtual_momentum", "0.9", "--num_workers", str(cfg.clients_per_round),
-                "--num_clients", str(cfg.num_clients), "--local_batch_size", "-1", "--num_epochs", "1",
-                "--num_devices", str(cfg.gpus), "--device", "cuda", "--port", str(cfg.port),
-                "--lr_scale", "0.4", "--k", str(cfg.k), "--num_cols", str(cfg.num_cols),
-                "--valid_batch_size", "500"]
+    bc = bench_configs.CONFIGS[cfg.config]
+    gpt2 = bc["family"] == "gpt2"
+    if bc["family"] == "cv" and bc["model"] == "ResNet9" and tuple(bc["shape"])[1] != 32:
+        # the reference's ResNet-9 ends in MaxPool2d(4) (models/resnet9.py:95): on 28 x 28 input the map is 3 x 3 by
+        # then and the layer raises ("Output size is too small") -- its worker dies and the server waits 600 s
+        print("REF_UNAVAILABLE the reference's ResNet9 raises on %dx%d input (MaxPool2d(4) over a 3x3 map); see the "
+              "femnist32_* configurations for the same task on 32x32-padded images" % tuple(bc["shape"])[1:], flush=True)
+        return
+    flags = dict(bc["flags"])
+    ref_argv = ["--dataset_name", bc["dataset"], "--mode", flags["mode"], "--error_type", flags.get("error_type", "none"),
+                "--local_momentum", str(flags.get("local_momentum", 0.0)),
+                "--virtual_momentum", str(flags.get("virtual_momentum", 0.0)), "--num_workers", str(cfg.clients_per_round),
+                "--num_clients", str(cfg.num_clients), "--local_batch_size", str(bc["per_client"] if gpt2 else -1),
+                "--num_epochs", "1", "--num_devices", str(cfg.gpus), "--device", "cuda", "--port", str(cfg.port),
+                "--lr_scale", "0.4", "--k", str(flags.get("k", cfg.k)), "--num_cols", str(cfg.num_cols),
+                "--valid_batch_size", "500", "--weight_decay", str(flags.get("weight_decay", 5e-4))]
+    if flags["mode"] == "fedavg":
+        ref_argv += ["--num_fedavg_epochs", str(flags["num_fedavg_epochs"]), "--fedavg_batch_size",
+                     str(flags["fedavg_batch_size"])]
+    if gpt2:
+        ref_argv += ["--num_results_train", "1", "--num_candidates", str(bc["candidates"])]
+    else:
+        ref_argv += ["--model", bc["model"]]
     if cfg.gpus == 1:
         ref_argv.append("--share_ps_gpu")
     sys.argv = ["cv_train.py"] + ref_argv
 
     import utils as ref_utils                 # reference modules (bare names, as the reference does)
     import models as ref_models
-    import cv_train as ref_cv
     from fed_aggregator import FedModel, FedOptimizer
 
-    args = ref_utils.parse_args()
+    args = ref_utils.parse_args(default_lr=4e-2) if gpt2 else ref_utils.parse_args()
     torch.manual_seed(args.seed)
-    model = ref_models.ResNet9(do_batchnorm=False, num_classes=10, new_num_classes=None,
-                               bn_bias_freeze=False, bn_weight_freeze=False,
-                               channels={"prep": 64, "layer1": 128, "layer2": 256, "layer3": 512})
+    if gpt2:
+        import gpt2_train as ref_train
+        from pytorch_transformers import GPT2DoubleHeadsModel
+        model = GPT2DoubleHeadsModel.from_pretrained("gpt2")          # random init (no network), HF transformers
+        model.resize_token_embeddings(50257 + 5)
+        args.len_tokenizer = 50257 + 5
+        loss_train, loss_val = ref_train.compute_loss_train, ref_train.compute_loss_val
+    else:
+        import cv_train as ref_train
+        if bc["model"] == "ResNet9":
+            kw = dict(bc["model_kw"])
+            model = ref_models.ResNet9(do_batchnorm=False, num_classes=kw.get("num_classes", 10), new_num_classes=None,
+                                       bn_bias_freeze=False, bn_weight_freeze=False,
+                                       initial_channels=kw.get("initial_channels", 3),
+                                       channels={"prep": 64, "layer1": 128, "layer2": 256, "layer3": 512})
+        else:
+            model = getattr(ref_models, bc["model"])(**bc["model_kw"])
+        loss_train, loss_val = ref_train.compute_loss_train, ref_train.compute_loss_val
     if cfg.curve_init:
         model.load_state_dict(torch.load(cfg.curve_init, map_location="cpu"))
     opt = torch.optim.SGD(model.parameters(), lr=1)
-    fed_model = FedModel(model, ref_cv.compute_loss_train, args, ref_cv.compute_loss_val)
+    fed_model = FedModel(model, loss_train, args, loss_val)
     fed_opt = FedOptimizer(opt, args)
     for group in fed_opt.param_groups:
-        group["lr"] = 0.05
+        group["lr"] = 0.01 if gpt2 else 0.05
+    if flags["mode"] == "fedavg":
+        fed_opt.step()                        # publishes the learning rate to the workers (fed_aggregator.py:441-444)
     n_procs = len(fed_model.update_forward_grad_ps)
     processed = (cfg.clients_per_round // n_procs) * n_procs      # reference drops the remainder (Q1)
 
@@ -108,8 +146,8 @@ def main():
         return run_curve(cfg, fed_model, fed_opt, torch)
 
     fed_model.train(True)
-    rounds = [make_round(cfg.clients_per_round, cfg.per_client, cfg.num_clients, s, torch)
-              for s in range(cfg.warmup + cfg.steps)]
+    make = bench_configs.gpt2_round if gpt2 else bench_configs.cv_round
+    rounds = [make(bc, cfg.clients_per_round, s, torch) for s in range(cfg.warmup + cfg.steps)]
     h2d = sum(t.numel() * t.element_size() for t in rounds[0][1:])
     for r in rounds[:cfg.warmup]:
         fed_model(r)

@@ -27,10 +27,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+sys.path.insert(0, os.path.join(ROOT, "baseline"))
+import bench_configs  # noqa: E402  (plain data shared with the reference harness)
+
 METRIC = "clients/sec per FL round (device-timed, max over ranks)"
-CLIENTS_PER_GPU = 100
-IMAGES_PER_CLIENT = 5
-NUM_CLIENTS = 10000
 
 
 def parse():
@@ -39,12 +39,15 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--mode", default="sketch")
-    ap.add_argument("--model", default="ResNet9")
+    ap.add_argument("--config", default="resnet9_sketch", choices=sorted(bench_configs.CONFIGS),
+                    help="which BASELINE.json configuration (default: the headline ResNet-9 FetchSGD sketch)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: clients_per_gpu x N clients per round; strong: a fixed round for every N")
     ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16", "fp32"],
                     help="tf32 (headline): fp32 activations, tcgen05 kind::tf32 -- the precision the reference's fp32 "
                          "convolutions get from cuDNN; bf16: the fast path (reported as the extra key \"bf16\")")
     ap.add_argument("--no_extra", action="store_true", help="skip the extra bf16 measurement")
+    ap.add_argument("--ref_timeout", type=int, default=1500, help="seconds before the reference arm is abandoned")
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no_native_nn", action="store_true",
                     help="run conv/linear layers on cuDNN/cuBLAS instead of the hand-written tcgen05 kernels")
@@ -53,7 +56,7 @@ def parse():
                          "of --defer_results")
     ap.add_argument("--no_cuda_graphs", action="store_true",
                     help="launch the round's kernels one by one (for ncu launch lists; a graph replay hides them)")
-    ap.add_argument("--clients_per_gpu", type=int, default=CLIENTS_PER_GPU)
+    ap.add_argument("--clients_per_gpu", type=int, default=0, help="override the configuration's clients per GPU")
     ap.add_argument("--phases", action="store_true", help="also print a per-phase breakdown to stderr")
     ap.add_argument("--profile", action="store_true",
                     help="profiling aid: device-resident phase only, wrapped in cudaProfilerStart/Stop "
@@ -133,21 +136,28 @@ def run_reference(cfg):
                  "GROUP_RANK", "ROLE_RANK", "ROLE_NAME", "GROUP_WORLD_SIZE", "ROLE_WORLD_SIZE",
                  "OMP_NUM_THREADS", "NCCL_ASYNC_ERROR_HANDLING") or k.startswith(("TORCHELASTIC", "TORCH_NCCL")):
             env.pop(k, None)
-    clients = cfg.clients_per_gpu * cfg.gpus
+    bc = dict(bench_configs.CONFIGS[cfg.config])
+    if cfg.clients_per_gpu:
+        bc["clients_per_gpu"] = cfg.clients_per_gpu
+    clients = bench_configs.clients_per_round(bc, cfg.gpus, cfg.scaling)
     cmd = [sys.executable, os.path.join(ROOT, "baseline", "run_ref.py"), "--gpus", str(cfg.gpus),
            "--steps", str(cfg.steps), "--warmup", str(cfg.warmup), "--clients_per_round", str(clients),
-           "--per_client", str(IMAGES_PER_CLIENT), "--num_clients", str(NUM_CLIENTS),
+           "--per_client", str(bc["per_client"]), "--num_clients", str(bc["num_clients"]), "--config", cfg.config,
            "--port", str(5315 + os.getpid() % 500)]
     sampler = ClockSampler(0)
     sampler.start()
     try:
         res = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
-                             timeout=3000)
+                             timeout=cfg.ref_timeout)
     except subprocess.TimeoutExpired:
         sampler.stop()
-        print(json.dumps({"impl": "reference", "unavailable": "reference run exceeded 3000 s"}))
+        print(json.dumps({"impl": "reference", "unavailable": "reference run exceeded %d s" % cfg.ref_timeout}))
         return 0
     clocks = sampler.stop()
+    unavailable = [l for l in res.stdout.splitlines() if l.startswith("REF_UNAVAILABLE ")]
+    if unavailable:
+        print(json.dumps({"impl": "reference", "config": cfg.config, "unavailable": unavailable[-1][len("REF_UNAVAILABLE "):]}))
+        return 0
     line = [l for l in res.stdout.splitlines() if l.startswith("REF_RESULT ")]
     if res.returncode != 0 or not line:
         tail = (res.stderr or res.stdout).strip().splitlines()[-3:]
@@ -158,11 +168,14 @@ def run_reference(cfg):
     out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "clients/s", "n_gpus": cfg.gpus,
         "steps": cfg.steps, "warmup": cfg.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-        "config": {"model": "ResNet9", "mode": "sketch", "num_rows": 5, "num_cols": 500000, "k": 50000,
-                   "global_batch": clients * IMAGES_PER_CLIENT, "clients_per_round": clients,
+        "scaling": cfg.scaling, "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+        "config": {"name": cfg.config, "model": bc["model"], "mode": bc["flags"]["mode"], "num_rows": 5,
+                   "num_cols": 500000, "k": bc["flags"].get("k", 50000),
+                   "global_batch": clients * bc["per_client"], "clients_per_round": clients,
                    "clients_processed_per_round": r["clients_processed_per_round"],
-                   "images_per_client": IMAGES_PER_CLIENT,
+                   "images_per_client": bc["per_client"], "seq_len": bc.get("seq"),
+                   "precision_note": "the reference's only mode: fp32 tensors, TF32 convolutions inside cuDNN "
+                                     "(torch.backends.cudnn.allow_tf32 defaults to True), fp32 matmuls",
                    "parallelism": "ps+%dworkers" % r["worker_procs"],
                    "l2": "inputs + activations exceed L2; fresh inputs every round",
                    "one_gpu_transport_gloo": r["one_gpu_transport"]},
@@ -198,31 +211,45 @@ def run_ours(cfg):
                    "--master-addr", "127.0.0.1", "--master-port", str(29400 + os.getpid() % 500)] + sys.argv
             return subprocess.call(cmd)
         raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (cfg.gpus, world))
-    clients = cfg.clients_per_gpu * cfg.gpus
-    n_distinct = 4
-    host_rounds = [synthetic_image_batch(clients, IMAGES_PER_CLIENT, seed=s, first_client=(s * clients) % (NUM_CLIENTS - clients),
-                                         pin=True) for s in range(n_distinct)]
-    per_rank_samples = cfg.clients_per_gpu * IMAGES_PER_CLIENT
-    h2d = per_rank_samples * (3 * 32 * 32 * 4 + 8)
+    bc = dict(bench_configs.CONFIGS[cfg.config])
+    if cfg.clients_per_gpu:
+        bc["clients_per_gpu"] = cfg.clients_per_gpu
+    clients = bench_configs.clients_per_round(bc, cfg.gpus, cfg.scaling)
+    gpt2 = bc["family"] == "gpt2"
+    n_distinct = 3 if gpt2 else 4
+
+    def pin(t):
+        return t.pin_memory() if torch.cuda.is_available() else t
+    if gpt2:
+        from commefficient_b200.gpt2_train import compute_loss_train as loss_train, compute_loss_val as loss_val
+        host_rounds = [tuple(pin(t) for t in bench_configs.gpt2_round(bc, clients, s, torch)) for s in range(n_distinct)]
+    else:
+        loss_train, loss_val = compute_loss_train, compute_loss_val
+        host_rounds = [tuple(pin(t) for t in bench_configs.cv_round(bc, clients, s, torch)) for s in range(n_distinct)]
+    per_rank = clients // cfg.gpus if clients % cfg.gpus == 0 else -(-clients // cfg.gpus)
+    h2d = sum(t[0:1].numel() * t.element_size() * per_rank * bc["per_client"] for t in host_rounds[0][1:])
     state = {}
 
     def measure(precision, steps, warmup, e2e=True, profile=False):
-        args = make_args(mode=cfg.mode, error_type="virtual" if cfg.mode in ("sketch", "true_topk") else "none",
-                         local_momentum=0.0, virtual_momentum=0.9, num_workers=clients, num_clients=NUM_CLIENTS,
-                         local_batch_size=-1, num_epochs=1.0, dataset_name="CIFAR10", device="cuda",
-                         precision=precision, backend=cfg.backend, model=cfg.model,
+        flags = dict(bc["flags"])
+        args = make_args(num_workers=clients, num_clients=bc["num_clients"],
+                         local_batch_size=bc["per_client"] if gpt2 else -1, num_epochs=1.0, dataset_name=bc["dataset"],
+                         device="cuda", precision=precision, backend=cfg.backend, model=bc["model"],
                          no_native_nn=cfg.no_native_nn, no_cuda_graphs=cfg.no_cuda_graphs,
-                         defer_results=not cfg.sync_results)
+                         defer_results=not cfg.sync_results, num_results_train=1 if gpt2 else 2, **flags)
         rt = init_runtime(args)
         torch.manual_seed(args.seed)
         torch.backends.cudnn.benchmark = True
-        model = getattr(models, cfg.model)(num_classes=10)
-        fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+        model = getattr(models, bc["model"])(**bc["model_kw"])
+        if gpt2:
+            model.resize_token_embeddings(50257 + 5)
+        fed = FedModel(model, loss_train, args, loss_val)
         opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
-        opt.param_groups[0]["lr"] = 0.05
+        opt.param_groups[0]["lr"] = 0.01 if gpt2 else 0.05
+        opt.step()                                 # publishes the learning rate (fedavg clients read it)
         fed.train(True)
         dev = rt.device
-        dev_rounds = [(ids, img.to(dev), lab.to(dev)) for ids, img, lab in host_rounds]
+        dev_rounds = [(r[0],) + tuple(t.to(dev) for t in r[1:]) for r in host_rounds]
         d2h = clients * (args.num_results_train + 1) * 4
 
         def one_round(batch, read=True):
@@ -287,7 +314,7 @@ def run_ours(cfg):
     main = measure(cfg.precision, cfg.steps, cfg.warmup)
     clocks = sampler.stop() if rank0 else None
     extra = None
-    if cfg.precision == "tf32" and not cfg.no_extra:
+    if cfg.precision == "tf32" and not cfg.no_extra and cfg.config == "resnet9_sketch":
         # the fast path, same config and timing rules (device-timed + end to end), reported beside the headline
         extra = measure("bf16", cfg.steps, cfg.warmup)
     rt, args = main["rt"], main["args"]
@@ -296,11 +323,12 @@ def run_ours(cfg):
         e2e = clients / (main["ms_e2e"] / 1e3)
         line = {
             "metric": METRIC, "value": value, "unit": "clients/s", "n_gpus": cfg.gpus, "steps": cfg.steps,
-            "warmup": cfg.warmup, "ms_per_step": main["ms_dev"], "higher_is_better": True, "scaling": "weak",
+            "warmup": cfg.warmup, "ms_per_step": main["ms_dev"], "higher_is_better": True, "scaling": cfg.scaling,
             "vs_baseline": None, "dtype": cfg.precision, "data": "synthetic",
-            "config": {"model": cfg.model, "mode": cfg.mode, "num_rows": args.num_rows, "num_cols": args.num_cols,
-                       "k": args.k, "global_batch": clients * IMAGES_PER_CLIENT, "clients_per_round": clients,
-                       "images_per_client": IMAGES_PER_CLIENT, "seq_len": None,
+            "config": {"name": cfg.config, "model": bc["model"], "mode": args.mode, "num_rows": args.num_rows,
+                       "num_cols": args.num_cols,
+                       "k": args.k, "global_batch": clients * bc["per_client"], "clients_per_round": clients,
+                       "images_per_client": bc["per_client"], "seq_len": bc.get("seq"),
                        "parallelism": "dp%d" % cfg.gpus, "backend": main["backend"],
                        "client_batching": main["client_batching"], "native_nn": main["native_nn"],
                        "precision_note": "tf32 = fp32 activations / weights, tcgen05 kind::tf32 MMAs with fp32 "
