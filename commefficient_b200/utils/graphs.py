@@ -11,8 +11,13 @@ captured and replayed.  Capture is an optimisation, never a requirement:
     watchdog) cannot poison it;
   * any exception during capture is swallowed: the caller gets ``None``, marks the shape "eager only"
     and carries on with the eager result;
-  * one memory pool is shared by all graphs of a device and the cache is a small LRU, so varying
-    client sizes (non-iid EMNIST / PERSONA) cannot accumulate hundreds of private pools.
+  * the per-shape cache is a small LRU, so varying client sizes (non-iid EMNIST / PERSONA) cannot accumulate
+    hundreds of graphs with their private memory pools (a pool handle shared across graphs is NOT used: PyTorch
+    drops a shared pool when its last graph dies, and the next capture into that handle trips an allocator
+    assertion);
+  * if a capture does fail after random-number kernels were recorded, the device generator is left with a
+    non-zero in-graph offset and every later ``torch.randn`` on the device would raise: the handler rebuilds
+    the generator state.
 """
 from __future__ import annotations
 
@@ -38,13 +43,20 @@ def capture_stream(device) -> "torch.cuda.Stream":
     return s
 
 
-def shared_pool(device):
-    key = torch.device(device).index or 0
-    p = _POOLS.get(key)
-    if p is None:
-        p = torch.cuda.graph_pool_handle()
-        _POOLS[key] = p
-    return p
+def _repair_generator(device) -> None:
+    """After a failed capture: give the device's default generator a fresh state object (same seed and offset)
+    so that its in-graph bookkeeping is back to "not capturing"."""
+    try:
+        idx = torch.device(device).index or 0
+        gen = torch.cuda.default_generators[idx]
+        fresh = torch.Generator(device=torch.device("cuda", idx))
+        try:
+            fresh.set_state(gen.get_state())
+        except Exception:             # noqa: BLE001
+            fresh.manual_seed(gen.initial_seed())
+        gen.graphsafe_set_state(fresh.graphsafe_get_state())
+    except Exception:                 # noqa: BLE001
+        pass
 
 
 class Captured:
@@ -79,7 +91,7 @@ def try_capture(device, body: Callable[[], object], what: str = "graph", warmup:
         torch.cuda.synchronize(device)
         before = native.launch_count() if native.available() else 0
         graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph, pool=shared_pool(device), stream=stream, capture_error_mode="thread_local"):
+        with torch.cuda.graph(graph, stream=stream, capture_error_mode="thread_local"):
             if FORCE_FAIL:
                 raise RuntimeError("forced capture failure (test hook)")
             out = body()
@@ -90,6 +102,7 @@ def try_capture(device, body: Callable[[], object], what: str = "graph", warmup:
             torch.cuda.synchronize(device)
         except Exception:             # noqa: BLE001
             pass
+        _repair_generator(device)
         if what not in _WARNED:
             _WARNED.add(what)
             warnings.warn("CUDA-graph capture of the %s failed (%s: %s); running it eagerly from now on"

@@ -193,3 +193,20 @@ def test_capture_failure_falls_back_to_eager(mode, kw):
     # and graphs still work afterwards
     w_g, l_g, _ = _run("cuda", mode, rounds=5, **kw)
     np.testing.assert_allclose(l_g, l_ref, rtol=1e-3, atol=1e-3)
+
+
+def test_failed_capture_with_rng_ops_leaves_the_generator_usable():
+    """A capture that dies after random-number kernels were recorded must not poison torch's CUDA generator."""
+    from commefficient_b200.utils import graphs
+
+    def body():
+        x = torch.randn(1000, device="cuda")          # advances the generator's in-graph offset
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("simulated failure in the middle of a capture")
+        return x
+
+    assert graphs.try_capture("cuda", body, what="rng test") is None
+    y = torch.randn(1000, device="cuda")              # would raise "Offset increment outside graph capture ..."
+    assert torch.isfinite(y).all()
+    cap = graphs.try_capture("cuda", lambda: torch.randn(1000, device="cuda"), what="rng test 2")
+    assert cap is not None and torch.isfinite(cap.replay()).all()

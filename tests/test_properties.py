@@ -1,0 +1,98 @@
+"""Property-based tests (hypothesis) of the compression primitives: the algebraic facts the federated rules rely
+on, checked on the torch oracles (CPU tier) and -- marked gpu -- on the native kernels against those oracles.
+Reference semantics: ``_topk`` (/root/reference/CommEfficient/utils.py:232-252) and the CSVec calls of
+fed_worker.py:312-320 / fed_aggregator.py:584-611."""
+import numpy as np
+import pytest
+import torch
+from hypothesis import given, settings, strategies as st
+
+from commefficient_b200.ops import ref
+from commefficient_b200.ops.hashing import make_hashes
+
+vec = st.integers(min_value=1, max_value=400).flatmap(
+    lambda n: st.lists(st.floats(min_value=-100, max_value=100, allow_nan=False, width=32), min_size=n, max_size=n))
+
+
+@settings(max_examples=60, deadline=None)
+@given(vec, st.integers(min_value=1, max_value=500))
+def test_topk_oracle_properties(values, k):
+    v = torch.tensor(values, dtype=torch.float32)
+    k = min(k, v.numel())
+    idx, val = ref.topk_sparse_ref(v, k)
+    assert idx.numel() == k and idx.unique().numel() == k              # exactly k distinct coordinates
+    assert torch.equal(val, v[idx])
+    kept = torch.zeros(v.numel(), dtype=torch.bool)
+    kept[idx] = True
+    if k < v.numel():                                                   # nothing dropped beats anything kept
+        assert float(v[~kept].abs().max()) <= float(v[kept].abs().min())
+    thresh = v[kept].abs().min()
+    ties = torch.nonzero(v.abs() == thresh).flatten()                   # ties are taken in ascending index order
+    taken = ties[kept[ties]]
+    assert torch.equal(taken, ties[: taken.numel()])
+    dense = ref.topk_dense_ref(v, k)
+    assert int((dense != 0).sum()) <= k and torch.equal(dense[idx], v[idx])
+
+
+@settings(max_examples=25, deadline=None)
+@given(st.integers(min_value=20, max_value=600), st.integers(min_value=8, max_value=64), st.integers(min_value=1, max_value=5),
+       st.integers(min_value=1, max_value=7), st.integers(min_value=0, max_value=2 ** 16))
+def test_sketch_is_linear_and_recovers_isolated_heavy_hitters(d, c, r, nb, seed):
+    g = torch.Generator().manual_seed(seed)
+    h = make_hashes(d, c, r, nb)
+    a, b = torch.randn(d, generator=g), torch.randn(d, generator=g)
+    ta, tb, tab = (torch.zeros(r, c) for _ in range(3))
+    ref.sketch_accum_ref(ta, a, h)
+    ref.sketch_accum_ref(tb, b, h)
+    ref.sketch_accum_ref(tab, 2.0 * a - 3.0 * b, h)
+    torch.testing.assert_close(tab, 2.0 * ta - 3.0 * tb, rtol=1e-4, atol=1e-4)      # S(2a - 3b) = 2 S(a) - 3 S(b)
+    # a vector with a single non-zero is estimated exactly, whatever the geometry
+    e = torch.zeros(d)
+    i = int(torch.randint(0, d, (1,), generator=g))
+    e[i] = 7.5
+    te = torch.zeros(r, c)
+    ref.sketch_accum_ref(te, e, h)
+    est = ref.sketch_estimate_ref(te, h)
+    assert float(est[i]) == pytest.approx(7.5)
+    # heavy-hitter recovery returns it -- or, in a tiny table, a coordinate that collides with it in a majority of
+    # the rows and is therefore indistinguishable (same magnitude; the lowest index wins the tie)
+    idx, val = ref.unsketch_ref(te, h, 1)
+    assert abs(float(val[0])) == pytest.approx(7.5) and int(idx[0]) <= i
+
+
+@pytest.mark.gpu
+@settings(max_examples=30, deadline=None)
+@given(st.integers(min_value=1, max_value=70000), st.integers(min_value=1, max_value=5000), st.integers(min_value=0, max_value=2 ** 16),
+       st.sampled_from([0, 1, 8, 200]))
+def test_native_topk_equals_oracle(n, k, seed, quantise):
+    from commefficient_b200.ops.topk import topk_sparse
+    g = torch.Generator().manual_seed(seed)
+    v = torch.randn(n, generator=g)
+    if quantise:
+        v = (v * quantise).round() / quantise            # forces ties, including at the threshold and at zero
+    k = min(k, n)
+    idx, val = topk_sparse(v.cuda(), k)
+    ci, cv = ref.topk_sparse_ref(v, k)
+    assert torch.equal(idx.cpu().long(), ci) and torch.equal(val.cpu(), cv)
+
+
+@pytest.mark.gpu
+@settings(max_examples=15, deadline=None)
+@given(st.integers(min_value=50, max_value=40000), st.integers(min_value=16, max_value=3000), st.integers(min_value=1, max_value=5),
+       st.integers(min_value=1, max_value=20), st.integers(min_value=0, max_value=2 ** 16))
+def test_native_sketch_equals_oracle(d, c, r, nb, seed):
+    from commefficient_b200.ops import sketch as sk
+    g = torch.Generator().manual_seed(seed)
+    v = torch.randn(d, generator=g)
+    plan = sk.SketchPlan.get(d, c, r, nb, "cuda")
+    table = plan.new_table()
+    sk.accumulate(plan, table, v.cuda())
+    want = torch.zeros(r, c)
+    ref.sketch_accum_ref(want, v, plan.hashes)
+    torch.testing.assert_close(table.cpu(), want, rtol=1e-4, atol=1e-4)
+    k = max(1, min(d // 10, 500))
+    idx, val = sk.unsketch_topk(plan, table, k)
+    est = ref.sketch_estimate_ref(table.cpu(), plan.hashes)
+    torch.testing.assert_close(val.cpu(), est[idx.cpu().long()], rtol=1e-5, atol=1e-6)
+    thresh = est.abs().topk(k).values[-1]
+    assert float(val.abs().min()) >= float(thresh) - 1e-6

@@ -14,10 +14,14 @@ PAT = re.compile(r"\b(UTCHMMA[\w.]*|UTMALDG[\w.]*|UTMASTG[\w.]*|UTCBAR[\w.]*|UTC
 def main():
     lib = sys.argv[1] if len(sys.argv) > 1 else "commefficient_b200/lib/libceb200.so"
     out = subprocess.run(["cuobjdump", "-sass", lib], stdout=subprocess.PIPE, text=True).stdout
+    try:        # readable kernel names
+        out = subprocess.run(["c++filt"], input=out, stdout=subprocess.PIPE, text=True).stdout
+    except Exception:
+        pass
     per = collections.OrderedDict()
     cur = None
     for line in out.splitlines():
-        m = re.match(r"\s*Function : (\S+)", line)
+        m = re.match(r"\s*Function : (.+)$", line)
         if m:
             cur = m.group(1)
             per[cur] = collections.Counter()
@@ -33,7 +37,9 @@ def main():
           "barrier), `LDTM` = tcgen05.ld (TMEM), `UTCBAR` = tcgen05.commit (`.2CTA.MULTICAST` = arrive in both "
           "CTAs), `UTCATOMSWS` = tcgen05.alloc/dealloc, `UCGABAR_*` = cluster barrier, `SYNCS` = mbarrier, "
           "`STG.E.ENL2.256` = 256-bit global store, `RED*` = reduction atomics, `*.SYS` = system-scope (peer) "
-          "accesses, `MUFU.TANH` = tanh.approx.\n")
+          "accesses, `MUFU.TANH` = tanh.approx.  `tcgen05.mma.kind::tf32` assembles to the same `UTCHMMA` mnemonic as "
+          "`kind::f16` (the operand kind travels in the instruction descriptor): the TF32 kernels are the "
+          "instantiations whose last template argument is 1 (`tc_tile_kernel<..., 1>`, `tc_wgrad_kernel<..., 1>`).\n")
     for name, cnt in per.items():
         if not cnt:
             continue
