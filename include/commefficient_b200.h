@@ -9,8 +9,9 @@
  *     buffer, including scratch (sizes via the *_bytes() queries), so the library can be
  *     driven from PyTorch's caching allocator without fragmenting it (the ceb_peer_alloc
  *     family, which creates IPC-exportable buffers, is the exception);
- *   - top-k results are unordered; which of several equal-magnitude entries at
- *     the threshold are kept is unspecified (as with torch.topk).
+ *   - top-k results are deterministic: the entries above the k-th largest magnitude in ascending
+ *     index order, then the lowest-index entries equal to it (replicas that select on the same
+ *     vector pick the same set; torch.topk leaves this unspecified).
  *
  * "Reference" below is pursueorigin/CommEfficient (paths relative to
  * CommEfficient/ in that repository).
@@ -34,7 +35,7 @@ void ceb_reset_launch_count(void);
 void ceb_add_launch_count(unsigned long long n);
 
 /* ---- exact top-k by magnitude (reference: utils.py:232-252 `_topk`) ---------- */
-/* Bytes of zero-initialisable scratch every top-k style call needs (~26 KB). */
+/* Bytes of zero-initialisable scratch every top-k style call needs (~34 KB). */
 int64_t ceb_select_scratch_bytes(void);
 /* out_idx/out_val receive the k largest-|v| entries of vec[0..n). 0 < k <= n < 2^31. */
 int ceb_topk_select(const float* vec, int64_t n, int64_t k, void* scratch, int64_t scratch_bytes,
@@ -73,7 +74,7 @@ int ceb_sketch_unsketch_topk(const float* table, const int32_t* packed, int64_t 
  * it exists for hosts of this library that may not allocate device memory -- a service whose
  * GPU memory was partitioned once at start-up, a plug-in inside another framework's pool, a
  * latency-critical loop that must avoid cudaMalloc's device-wide synchronisation).  Scratch
- * lives in a device array built into the library: CEB_STATIC_UNSKETCH_MAX_D floats + ~26 KB
+ * lives in a device array built into the library: CEB_STATIC_UNSKETCH_MAX_D floats + ~34 KB
  * on every GPU that loads the library, held until exit.  d above the maximum is an error.
  * All calls on a device share that array (overlapping calls race; serialise them), and the
  * first call on a device looks up its address -- do that call outside stream capture. */
@@ -275,6 +276,8 @@ int ceb_colsum_bf16(const void* x_bf16, int64_t ld, int64_t rows, int cols, floa
  *    mode 0  dst = sum_q src[q]                              (all-reduce)
  *    mode 1  Vv = rho*Vv + sum/N; Ve += Vv (error_mode 2) or Ve = Vv (1); dst = Ve (or Vv)
  *    mode 2  Vv = rho*Vv + sum/N; dst (= every replica's weights) -= lr * Vv
+ *    mode 3  true_topk state: Vv = rho*Vv + sum/N; Ve += Vv on the shard, nothing gathered (pass dst = src)
+ *  Barrier waits are bounded: after ~5 s without a peer the waiter writes a code into ticket[2] and goes on.
  *  Vv_shard / Ve_shard hold this rank's ceb_peer_shard_elems(n, world) entries. */
 int64_t ceb_peer_shard_elems(int64_t n, int world);
 int ceb_peer_fused_reduce(int mode, const void* const* src, const void* const* dst,
@@ -287,6 +290,98 @@ int ceb_peer_handle_bytes(void);
 int ceb_peer_alloc(int64_t bytes, void** ptr_out, void* handle_out);
 int ceb_peer_open(const void* handle, void** ptr_out);
 int ceb_peer_release(void* ptr, int is_owner);
+
+/* ---- TF32 tensor-core path (--precision tf32): fp32 operands read by tcgen05.mma.kind::tf32, fp32
+ *      accumulation and fp32 outputs -- the arithmetic the reference's fp32 convolutions get from cuDNN
+ *      (torch.backends.cudnn.allow_tf32 defaults to True; reference: fed_worker.py:20, no autocast) ------ */
+/* C[M,N] (fp32) = act(A[M,K] * B[N,K]^T + bias); lda, ldb multiples of 4; out_mode 1: store, 2: atomic add. */
+int ceb_gemm_tf32_tn_ld(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int M, int N,
+                        int K, const float* bias, int relu, int out_mode, void* stream);
+/* 3x3 / s1 / p1 convolution over fp32 NHWC / KRSC tensors, Cin % 32 == 0.  relu_mask (nullable): zero where
+ * mask <= 0; resid (nullable): y = act(conv) + resid, or with y2 != NULL: y = act(conv), y2 = y + resid. */
+int ceb_conv3x3_tf32_nhwc(const float* x, const float* w, float* y, int Nimg, int H, int W, int Cin, int Cout,
+                          const float* bias, int relu, const float* relu_mask, const float* resid, float* y2,
+                          void* stream);
+int ceb_conv3x3_wgrad_tf32_nhwc(const float* dz, const float* x, float* dW, int Nimg, int H, int W, int Cin, int Cout,
+                                void* stream);
+/* C[M][N] (fp32) += A[K][M]^T * B[K][N], fp32 operands (MN-major, 32-byte-atom swizzle); N % 32 == 0. */
+int ceb_gemm_tf32_mn_acc_ld(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int M, int N, int K,
+                            int ldc, void* stream);
+/* fp32 counterparts of the NHWC helpers: pooling windows k in {2,3,4} tile the map from the top-left corner
+ * (floor mode), C % 4 == 0. */
+int ceb_conv_weights_prepare_f32(int n_layers, const float* const* src, void* const* copy_f32, void* const* rot_f32,
+                                 const int* cout, const int* cin, void* stream);
+int ceb_maxpool_nhwc_f32(const float* y, float* out, int N, int H, int W, int C, int k, void* stream);
+int ceb_maxpool_bwd_nhwc_f32(const float* y, const float* dp, float* dz, int N, int H, int W, int C, int k,
+                             int relu_mask, void* stream);
+int ceb_relu_bwd_f32(const float* y, const float* dy, float* dz, int64_t n, void* stream);
+int ceb_linear_ce_head_f32(const float* feat, const float* W, float scale, const int64_t* labels, int N, int F, int C,
+                           const float* g, float* loss, float* correct, float* dfeat, float* dW, void* stream);
+
+/* ---- general convolutions (reference: models/fixup_resnet18.py:144-154 3x3 s2 / 1x1 s2; models/resnet9.py on
+ *      the 28 x 28 FEMNIST input of cv_train.py:353-354) ------------------------------------------------- */
+/* ks in {1,3}, stride in {1,2}, pad in {0,1}; any map whose OUTPUT width is <= 128 (whole output rows per tile:
+ * widths 28 / 14 / 7 / 3 work).  f32 = 0: bf16 tensors, 1: fp32 tensors on the TF32 path. */
+int ceb_conv2d_nhwc(const void* x, const void* w, void* y, int Nimg, int H, int W, int Cin, int Cout, int ks,
+                    int stride, int pad, int relu, int f32, const void* relu_mask, const void* resid, void* y2,
+                    void* stream);
+/* 3x3 / pad 1 weight gradient with stride 1 or 2 over an INPUT map H x W; dz is [N, Ho, Wo, Cout]. */
+int ceb_conv3x3_wgrad_nhwc(const void* dz, const void* x, float* dW, int Nimg, int H, int W, int Cin, int Cout,
+                           int stride, int f32, void* stream);
+/* x[N,H,W,Cin] fp32, Cin in {1,3} -> im2col rows of 9*Cin taps zero-padded to one 128-byte row
+ * (out_f32 = 0: [N*H*W][64] bf16, 1: [N*H*W][32] fp32). */
+int ceb_im2col3x3(const float* x_nhwc, void* A, int N, int H, int W, int Cin, int out_f32, void* stream);
+/* sub = x[:, ::2, ::2, :];  up[:, ::2, ::2, :] = g, zero elsewhere.  row_bytes = C * sizeof(element) % 16 == 0. */
+int ceb_subsample2_nhwc(const void* x, void* out, int N, int H, int W, int row_bytes, void* stream);
+int ceb_upsample2_zero_nhwc(const void* g, void* up, int N, int H, int W, int Ho, int Wo, int row_bytes, void* stream);
+
+/* ---- transformer kernels (reference: the GPT-2 block of pytorch_transformers that gpt2_train.py:88-99,262-273
+ *      trains: matmul-softmax-dropout-matmul attention, nn.Embedding x3 + dropout, dropout + residual add) ---- */
+/* out[B*T][E] (bf16) = dropout_p(softmax(Q K^T / 8 + causal)) V over the fused projection qkv[B*T][3E] (bf16),
+ * head dim 64, T <= 1024; lse[B*H][T] (fp32) is kept for the backward.  The dropout mask is a pure function of
+ * (*seed_dev, salt, batch, head, query, key): nothing is stored, the backward regenerates it. */
+int ceb_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int E, float p_drop,
+                      const uint64_t* seed_dev, uint32_t salt, void* stream);
+/* dqkv[B*T][3E] (bf16) from dout[B*T][E]; dq_scratch: fp32 [B*T][E], needed only when T > 128. */
+int ceb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                      float* dq_scratch, int B, int T, int H, int E, float p_drop, const uint64_t* seed_dev,
+                      uint32_t salt, void* stream);
+/* x[row][E] (fp32) = dropout_p(wte[ids[row]] + wpe[row % T] + (token_types ? wte[token_types[row]] : 0)). */
+int ceb_embed_fwd(const int64_t* ids, const int64_t* token_types, const float* wte, const float* wpe, float* x,
+                  int64_t rows, int T, int E, float p_drop, const uint64_t* seed_dev, uint32_t salt, void* stream);
+/* dwte / dwpe += scatter of dx (through the regenerated mask): 16-byte vector reductions. */
+int ceb_embed_bwd(const int64_t* ids, const int64_t* token_types, const float* dx, float* dwte, float* dwpe,
+                  int64_t rows, int T, int E, float p_drop, const uint64_t* seed_dev, uint32_t salt, void* stream);
+/* resid_out = x + dropout_p(branch); y = LayerNorm(resid_out) -- and the backward, in which only the branch's
+ * gradient passes through the mask. */
+int ceb_add_layernorm_drop_fwd(const float* x, const void* branch_bf16, const float* gamma, const float* beta,
+                               float* resid_out, void* y_bf16, float* mean, float* rstd, int64_t rows, int E,
+                               float eps, float p_drop, const uint64_t* seed_dev, uint32_t salt, void* stream);
+int ceb_add_layernorm_drop_bwd(const void* dy_bf16, const float* resid, const float* gamma, const float* mean,
+                               const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
+                               float* dbeta, int64_t rows, int E, float p_drop, const uint64_t* seed_dev,
+                               uint32_t salt, void* stream);
+
+/* ---- sharded server tail (reference: fed_aggregator.py:511-542 true_topk, :584-611 sketch -- there on one
+ *      GPU over the full vector) ------------------------------------------------------------------------- */
+/* Median estimates of coordinates [lo, hi) only (est[i - lo]); leaves the range's digit-1 histogram in scratch. */
+int ceb_sketch_unsketch_est_range(const float* table, const int32_t* packed, int64_t n_tokens, const int32_t* blk,
+                                  int num_blocks, int r, int64_t c, int64_t d, int64_t lo, int64_t hi, float* est,
+                                  void* scratch, int64_t scratch_bytes, void* stream);
+/* Exact top-k of a vector spread over `world` ranks (this rank: v[0..n_local), global index of v[0] =
+ * idx_offset): per-pass histograms merged through peer memory, winners written into EVERY rank's lists.
+ * exch / flags / out_idx / out_val: host arrays of `world` peer-mapped pointers (ceb_dsel_exch_bytes() bytes,
+ * ceb_dsel_flag_words() uint32, k int32, k float each); err, epoch_dev: local device uint32 words (zero at
+ * start; the epoch is advanced on the device, so a call captured in a CUDA graph stays valid on replay). */
+int64_t ceb_dsel_exch_bytes(void);
+int ceb_dsel_flag_words(void);
+int ceb_dsel_run(const float* v, int64_t n_local, int64_t idx_offset, int64_t k, void* scratch, int64_t scratch_bytes,
+                 const void* const* exch, const void* const* flags, const void* const* out_idx,
+                 const void* const* out_val, void* err, int rank, int world, void* epoch_dev, int pass1_done,
+                 void* stream);
+/* Sharded true_topk apply: Vv / Ve are the shard [lo, hi) (indexed from lo); every rank updates its weights. */
+int ceb_dense_apply_zero_shard(const int32_t* idx, const float* val, int64_t k, float* Vv_shard, float* Ve_shard,
+                               int64_t lo, int64_t hi, float* w, float lr, const float* lr_vec, void* stream);
 
 #ifdef __cplusplus
 }
