@@ -16,6 +16,7 @@
 //   5. signals completion and waits for the other ranks' pushes to land.
 // No NCCL call is involved.  Buffers are cudaMalloc'd once and exchanged as CUDA IPC handles.
 #include "peer.cuh"
+#include <cstdlib>
 
 struct OpSum {
   __device__ __forceinline__ float4 operator()(int64_t, float4 s) const { return s; }
@@ -128,11 +129,22 @@ static void launch_peer(const CebPeerCtx& c, int64_t lo, int64_t hi, Op op, cuda
     if (need < 1) need = 1;
     return (int)(need < cap ? need : cap);
   };
+  // CEB_PEER_U=1|2|4 overrides the float4s in flight per thread and peer for the 8-rank kernels (A/B timing)
+  int u8 = 1;
+  if (c.world == 8) {
+    const char* e = getenv("CEB_PEER_U");
+    if (e) u8 = atoi(e);
+  }
   switch (c.world) {
 #define CEB_PEER_CASE(W_, U_) \
     case W_: peer_rs_op_ag_kernel<Op, W_, U_, GATHER><<<grid_for(U_), kPeerThreads, 0, st>>>(c, lo, hi, op); break;
     CEB_PEER_CASE(1, 4) CEB_PEER_CASE(2, 4) CEB_PEER_CASE(3, 2) CEB_PEER_CASE(4, 2)
-    CEB_PEER_CASE(5, 1) CEB_PEER_CASE(6, 1) CEB_PEER_CASE(7, 1) CEB_PEER_CASE(8, 1)
+    CEB_PEER_CASE(5, 1) CEB_PEER_CASE(6, 1) CEB_PEER_CASE(7, 1)
+    case 8:
+      if (u8 == 4) peer_rs_op_ag_kernel<Op, 8, 4, GATHER><<<grid_for(4), kPeerThreads, 0, st>>>(c, lo, hi, op);
+      else if (u8 == 2) peer_rs_op_ag_kernel<Op, 8, 2, GATHER><<<grid_for(2), kPeerThreads, 0, st>>>(c, lo, hi, op);
+      else peer_rs_op_ag_kernel<Op, 8, 1, GATHER><<<grid_for(1), kPeerThreads, 0, st>>>(c, lo, hi, op);
+      break;
 #undef CEB_PEER_CASE
     default: break;
   }
