@@ -695,9 +695,12 @@ class _LMHeadCE(torch.autograd.Function):
         dh = None
         if ctx.needs_input_grad[0]:
             wt = cast_transpose_bf16(weight.detach())                       # [E, V], K-major for the dgrad
-            dh_sel = torch.zeros((R, E), dtype=torch.bfloat16, device=dev)
+            # K = V = 50 262 with only (rows / 128) x (E / 256) output tiles: accumulate into fp32 so the kernel may
+            # split the reduction over the idle SMs (out_mode 2), then round once
+            dh32 = torch.zeros((R, E), dtype=torch.float32, device=dev)
             native.call("ceb_gemm_bf16_tn_rows", native.ptr(dlogits), dlogits.stride(0), native.ptr(wt), wt.stride(0),
-                        native.ptr(dh_sel), dh_sel.stride(0), R, E, V, None, 0, 0, native.ptr(nvalid), st)
+                        native.ptr(dh32), dh32.stride(0), R, E, V, None, 0, 2, native.ptr(nvalid), st)
+            dh_sel = cast_bf16(dh32)
             dh = torch.empty_like(dh_sel).index_copy_(0, order, dh_sel).to(ctx.h_dtype)
         dw = None
         if ctx.needs_input_grad[1]:

@@ -492,7 +492,7 @@ CEB_API int ceb_sketch_apply_zero_dev(const int32_t* idx, const float* val, int6
 //
 // Cost and limits, stated plainly:
 //   * the array is CEB_STATIC_UNSKETCH_MAX_D floats (8 Mi coordinates = 32 MiB) plus the
-//     ~26 KB select block; every GPU on which this library is loaded holds it until the
+//     ~34 KB select block; every GPU on which this library is loaded holds it until the
 //     process exits, whether or not this entry point is ever called;
 //   * d above that maximum is refused with an error (use ceb_sketch_unsketch_topk);
 //   * all calls on a device share the one array: it still holds the previous call's

@@ -45,6 +45,11 @@ struct TcParams {
   // (<= 128) output pixels -- whole rows of the output map, so maps whose width does not divide 128 (28, 14,
   // 7, 3) leave the last rows of the 128-row MMA tile unused -- and its activation box holds a_bytes
   int ks, stride, pad, tile_pix, a_bytes;
+  // split-K (atomic-accumulate outputs only): the k-steps are divided into k_split ranges of k_steps each
+  // (k_total in all); a work item is (split, n tile, m tile).  Fills the machine when M x N alone gives fewer
+  // tiles than SMs and K is long (the LM-head data gradient: 96 tiles, 785 k-steps).
+  int k_split, k_total;
+  int auto_split;        // the row count is only known on the device (m_limit): choose the split there
   // optional device-side row count: only the M tiles covering rows [0, *m_limit) are computed
   // (rows are compacted by the caller; lets a CUDA-graph-captured launch follow a data-dependent
   // row count without a host round trip)
@@ -128,7 +133,23 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   // work is handed out in units of PAIR vertically adjacent CTA tiles; a CTA of a pair owns
   // CTA tile (unit * PAIR + rank), which may lie wholly past M (TMA zero-fills, stores are bounded)
   const int m_tiles = (m_tiles_rt + PAIR - 1) / PAIR;
-  const int num_tiles = m_tiles * p.n_tiles;
+  const int mn_tiles = m_tiles * p.n_tiles;
+  if (p.auto_split && p.m_limit) {
+    // same cost model as the host's (waves x (k-steps per item + fixed cost)), evaluated with the real tile count
+    const int slots = (int)gridDim.x / PAIR;
+    const int kt = p.k_total;
+    int best_steps = kt;
+    long long best_cost = (long long)((mn_tiles + slots - 1) / slots) * (kt + 8);
+    for (int sp = 2; sp <= 16 && sp * 16 <= kt; ++sp) {
+      const int per = (kt + sp - 1) / sp;
+      const int eff = (kt + per - 1) / per;
+      const long long cost = (long long)((mn_tiles * eff + slots - 1) / slots) * (per + 8);
+      if (cost < best_cost) { best_cost = cost; best_steps = per; }
+    }
+    p.k_steps = best_steps;
+    p.k_split = (kt + best_steps - 1) / best_steps;
+  }
+  const int num_tiles = mn_tiles * p.k_split;
   const int first_tile = blockIdx.x / PAIR, tile_step = gridDim.x / PAIR;
 
   if (warp == 0 && lane == 0) {
@@ -158,7 +179,9 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     if (lane == 0) {
       uint32_t it = 0;                                   // global k-step counter (ring position)
       for (int t = first_tile; t < num_tiles; t += tile_step) {
-        const int m_tile = (t % m_tiles) * PAIR + (int)cta_rank, n_tile = t / m_tiles;
+        const int split = t / mn_tiles, tt = t - split * mn_tiles;
+        const int m_tile = (tt % m_tiles) * PAIR + (int)cta_rank, n_tile = tt / m_tiles;
+        const int ks0 = split * p.k_steps, ks1 = min(ks0 + p.k_steps, p.k_total);
         const int b_row0 = n_tile * BN + (int)cta_rank * (BN / PAIR);   // this CTA's share of the weight tile
         int n0 = 0, h0 = 0;
         if (p.conv) {
@@ -167,7 +190,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           n0 = pix0 / hw;
           h0 = (pix0 - n0 * hw) / p.W;
         }
-        for (int ks = 0; ks < p.k_steps; ++ks, ++it) {
+        for (int ks = ks0; ks < ks1; ++ks, ++it) {
           const int s = it % kStages;
           const uint32_t phase = (it / kStages) & 1;
           mbar_wait(empty_bar + s, phase ^ 1);
@@ -236,7 +259,9 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       mbar_wait(tmem_empty_bar + acc, ((local >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * (SUBS * BN);
-      for (int ks = 0; ks < p.k_steps; ++ks, ++it) {
+      const int split = t / mn_tiles;
+      const int ks0 = split * p.k_steps, ks1 = min(ks0 + p.k_steps, p.k_total);
+      for (int ks = ks0; ks < ks1; ++ks, ++it) {
         const int s = it % kStages;
         const uint32_t phase = (it / kStages) & 1;
         mbar_wait(full_bar + s, phase);
@@ -255,7 +280,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 for (int k = 0; k < 4; ++k) {
                   const uint64_t da = smem_desc_sw128(a_addr + (sub * sub_rows + r) * row_bytes + k * 32, 16, 1024);
                   const uint64_t db = smem_desc_sw128(b_addr + r * L::kBTileBytes + k * 32, 16, 1024);
-                  umma_any<TF, PAIR>(tmem_d + sub * BN, da, db, idesc, (ks | r | k) != 0);
+                  umma_any<TF, PAIR>(tmem_d + sub * BN, da, db, idesc, ((ks - ks0) | r | k) != 0);
                 }
           } else {
 #pragma unroll
@@ -263,15 +288,15 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
               const uint64_t da = smem_desc_sw128(a_addr + k * 32, 16, 1024);
               const uint64_t db = BMAJ == 1 ? smem_desc_mn<TF>(b_addr + k * UKE * 128, BKE * 128)
                                             : smem_desc_sw128(b_addr + k * 32, 16, 1024);
-              umma_any<TF, PAIR>(tmem_d, da, db, idesc, (ks | k) != 0);
+              umma_any<TF, PAIR>(tmem_d, da, db, idesc, ((ks - ks0) | k) != 0);
             }
           }
           if (PAIR == 2) {
             umma_commit_pair(empty_bar + s);              // frees this stage in BOTH CTAs
-            if (ks == p.k_steps - 1) umma_commit_pair(tmem_full_bar + acc);
+            if (ks == ks1 - 1) umma_commit_pair(tmem_full_bar + acc);
           } else {
             umma_commit(empty_bar + s);                   // frees this smem stage when the MMAs retire
-            if (ks == p.k_steps - 1) umma_commit(tmem_full_bar + acc);
+            if (ks == ks1 - 1) umma_commit(tmem_full_bar + acc);
           }
         }
         __syncwarp();
@@ -283,7 +308,8 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     uint32_t* stage = (uint32_t*)(epi_smem + (warp - 2) * (32 * 17 * 4));
     uint32_t local = 0;
     for (int t = first_tile; t < num_tiles; t += tile_step, ++local) {
-      const int m_tile = (t % m_tiles) * PAIR + (int)cta_rank, n_tile = t / m_tiles;
+      const int split = t / mn_tiles, tt = t - split * mn_tiles;
+      const int m_tile = (tt % m_tiles) * PAIR + (int)cta_rank, n_tile = tt / m_tiles;
       const int acc = local & 1;
       mbar_wait(tmem_full_bar + acc, (local >> 1) & 1);
       tc_fence_after();
@@ -316,7 +342,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(cur[j]);
         const int n0 = n_base + c * 32;
         if (n0 >= p.N) return;
-        if (p.bias) {
+        if (p.bias && split == 0) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) if (n0 + j < p.N) v[j] += __ldg(p.bias + n0 + j);
         }
@@ -580,7 +606,8 @@ static int launch_tile(const CUtensorMap& ta, const CUtensorMap& tb, const TcPar
   if (q.ks == 0) { q.ks = 3; q.stride = 1; q.pad = 1; }
   q.m_tiles = (int)ceb_cdiv(p.M, q.tile_pix);
   q.n_tiles = (int)ceb_cdiv(p.N, BN);
-  const int tiles = q.m_tiles * q.n_tiles;
+  if (q.k_split < 1) { q.k_split = 1; q.k_total = q.k_steps; }
+  const int tiles = q.m_tiles * q.n_tiles * q.k_split;
   const int grid = tiles < ceb_num_sms() ? tiles : ceb_num_sms();
   tc_tile_kernel<BN, MODE, BMAJ, 1, TF><<<grid, kTcThreads, L::kTotal, st>>>(ta, tb, q);
   CEB_COUNT_LAUNCH(1);
@@ -604,7 +631,8 @@ static int launch_tile_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
   if (q.ks == 0) { q.ks = 3; q.stride = 1; q.pad = 1; }
   q.m_tiles = (int)ceb_cdiv(p.M, q.tile_pix);
   q.n_tiles = (int)ceb_cdiv(p.N, BN);
-  const int pair_tiles = (int)ceb_cdiv(q.m_tiles, 2) * q.n_tiles;
+  if (q.k_split < 1) { q.k_split = 1; q.k_total = q.k_steps; }
+  const int pair_tiles = (int)ceb_cdiv(q.m_tiles, 2) * q.n_tiles * q.k_split;
   const int max_pairs = ceb_num_sms() / 2;
   const int pairs = pair_tiles < max_pairs ? pair_tiles : max_pairs;
   cudaLaunchConfig_t cfg = {};
@@ -727,6 +755,26 @@ static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, 
   TcParams p{};
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = (int)ldc; p.k_steps = (int)ceb_cdiv(K, bke);
   p.relu = relu; p.out_fp32 = out_mode; p.conv = 0; p.m_limit = m_limit;
+  if (out_mode == 2 && !relu) {
+    // accumulate semantics allow split-K: pick the split that minimises (waves) x (k-steps per item + fixed cost)
+    const int64_t units = pair ? ceb_cdiv(ceb_cdiv(M, BM), 2) * ceb_cdiv(N, bn) : ceb_cdiv(M, BM) * ceb_cdiv(N, bn);
+    const int slots = pair ? ceb_num_sms() / 2 : ceb_num_sms();
+    const int kt = p.k_steps;
+    int best = 1;
+    int64_t best_cost = ceb_cdiv(units, slots) * (kt + 8);
+    for (int sp = 2; sp <= 16 && sp * 16 <= kt; ++sp) {
+      const int per = (int)ceb_cdiv(kt, sp);
+      const int eff = (int)ceb_cdiv(kt, per);
+      const int64_t cost = ceb_cdiv(units * eff, slots) * (per + 8);
+      if (cost < best_cost) { best_cost = cost; best = eff; }
+    }
+    if (best > 1) {
+      p.k_total = kt;
+      p.k_steps = (int)ceb_cdiv(kt, best);
+      p.k_split = (int)ceb_cdiv(kt, p.k_steps);
+    }
+    if (m_limit) { p.auto_split = 1; p.k_total = kt; if (p.k_split < 1) p.k_split = 1; }
+  }
   return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream, pair, tf);
 }
 

@@ -510,3 +510,15 @@ def test_add_layer_norm_fused_matches_torch(E):
     r2.grad = None
     ln2(r2 + b2.detach()).backward(dy.float())
     assert _rel_err(resid.grad, r2.grad) < 1e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(4096, 768, 50264), (300, 256, 8000), (128, 64, 4096), (1000, 768, 768)])
+def test_gemm_accumulate_split_k_matches_fp32(M, N, K):
+    """fp32-accumulate outputs may split the reduction over CTAs (few output tiles, long K: the LM-head data
+    gradient); the result is the plain product added to what was there."""
+    g = torch.Generator(device=DEV).manual_seed(M + K)
+    a = (torch.randn(M, K, device=DEV, generator=g) * 0.1).bfloat16()
+    b = (torch.randn(N, K, device=DEV, generator=g) * 0.1).bfloat16()
+    acc = torch.ones(M, N, device=DEV)
+    tc.gemm_tn(a, b, out=acc, accumulate=True)
+    assert _rel_err(acc, 1 + a.float() @ b.float().t()) < 2e-5
