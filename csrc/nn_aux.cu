@@ -307,51 +307,60 @@ CEB_API int ceb_add_layernorm_drop_fwd(const float* x, const void* branch_bf16, 
 // dgamma / dbeta partials in registers over all rows the warp walks; the block combines its 8 warps
 // in shared memory once and issues one global atomic per column.
 template <int G>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
                   const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dx,
                   float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t rows,
                   const float* __restrict__ dres, __nv_bfloat16* __restrict__ dx_bf16, uint32_t drop_thresh = 0,
                   float inv_keep = 1.f, const unsigned long long* __restrict__ seed_dev = nullptr, uint32_t salt = 0) {
+  // Two passes over the row: the first only accumulates the two row sums, the second RELOADS x / dy (they are
+  // still in L1: a row is 4.5 KB) instead of keeping them in registers -- 212 registers and one block per SM
+  // (12 % of the warp slots, latency-bound at a quarter of the DRAM bandwidth) became ~100 and two blocks.
   constexpr int E = 128 * G;
   __shared__ float sh[2 * E];
   for (int j = threadIdx.x; j < 2 * E; j += blockDim.x) sh[j] = 0.f;
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
-  float4 gam[G], ag[G], ab[G];
+  float4 ag[G], ab[G];
 #pragma unroll
   for (int g = 0; g < G; ++g) {
-    gam[g] = __ldg((const float4*)(gamma + g * 128 + lane * 4));
     ag[g] = make_float4(0.f, 0.f, 0.f, 0.f);
     ab[g] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
+  auto load_d = [&](const __nv_bfloat16* gr, int g) {
+    const uint2 raw = *(const uint2*)(gr + g * 128 + lane * 4);
+    const float2 d01 = __bfloat1622float2(*(const __nv_bfloat162*)&raw.x);
+    const float2 d23 = __bfloat1622float2(*(const __nv_bfloat162*)&raw.y);
+    return make_float4(d01.x, d01.y, d23.x, d23.y);
+  };
   for (int64_t row = (int64_t)blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += (int64_t)gridDim.x * wpb) {
     const float mu = mean[row], rs = rstd[row];
     const float* xr = x + row * E;
     const __nv_bfloat16* gr = dy + row * E;
-    float4 xh[G], d[G];
     float a = 0.f, b = 0.f;
 #pragma unroll
     for (int g = 0; g < G; ++g) {
       const float4 xv = *(const float4*)(xr + g * 128 + lane * 4);
-      const uint2 raw = *(const uint2*)(gr + g * 128 + lane * 4);
-      const float2 d01 = __bfloat1622float2(*(const __nv_bfloat162*)&raw.x);
-      const float2 d23 = __bfloat1622float2(*(const __nv_bfloat162*)&raw.y);
-      d[g] = make_float4(d01.x, d01.y, d23.x, d23.y);
-      xh[g] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
-      const float g0 = d[g].x * gam[g].x, g1 = d[g].y * gam[g].y, g2 = d[g].z * gam[g].z, g3 = d[g].w * gam[g].w;
+      const float4 d = load_d(gr, g);
+      const float4 gm = __ldg((const float4*)(gamma + g * 128 + lane * 4));
+      const float g0 = d.x * gm.x, g1 = d.y * gm.y, g2 = d.z * gm.z, g3 = d.w * gm.w;
       a += g0 + g1 + g2 + g3;
-      b = fmaf(g0, xh[g].x, fmaf(g1, xh[g].y, fmaf(g2, xh[g].z, fmaf(g3, xh[g].w, b))));
+      b = fmaf(g0, (xv.x - mu) * rs, fmaf(g1, (xv.y - mu) * rs, fmaf(g2, (xv.z - mu) * rs, fmaf(g3, (xv.w - mu) * rs, b))));
     }
     a = warp_sum(a) * (1.f / E); b = warp_sum(b) * (1.f / E);
+    const uint32_t rowkey = drop_thresh ? ceb_drop_rowkey(seed_dev, salt, (uint32_t)row) : 0u;
 #pragma unroll
     for (int g = 0; g < G; ++g) {
+      const float4 xv = *(const float4*)(xr + g * 128 + lane * 4);
+      const float4 d = load_d(gr, g);
+      const float4 gm = __ldg((const float4*)(gamma + g * 128 + lane * 4));
+      const float4 xh = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
       float4 o;
-      o.x = rs * (d[g].x * gam[g].x - a - xh[g].x * b);
-      o.y = rs * (d[g].y * gam[g].y - a - xh[g].y * b);
-      o.z = rs * (d[g].z * gam[g].z - a - xh[g].z * b);
-      o.w = rs * (d[g].w * gam[g].w - a - xh[g].w * b);
+      o.x = rs * (d.x * gm.x - a - xh.x * b);
+      o.y = rs * (d.y * gm.y - a - xh.y * b);
+      o.z = rs * (d.z * gm.z - a - xh.z * b);
+      o.w = rs * (d.w * gm.w - a - xh.w * b);
       if (dres) {      // gradient arriving through the residual stream joins here (fused add)
         const float4 r4 = *(const float4*)(dres + row * E + g * 128 + lane * 4);
         o.x += r4.x; o.y += r4.y; o.z += r4.z; o.w += r4.w;
@@ -359,7 +368,7 @@ ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict_
       *(float4*)(dx + row * E + g * 128 + lane * 4) = o;
       if (dx_bf16) {   // the same gradient for the bf16 branch that was added to the stream (through its dropout mask)
         if (drop_thresh) {
-          const uint32_t key = ceb_drop_rowkey(seed_dev, salt, (uint32_t)row) + (uint32_t)(g * 128 + lane * 4);
+          const uint32_t key = rowkey + (uint32_t)(g * 128 + lane * 4);
           o.x *= ceb_hash32(key) >= drop_thresh ? inv_keep : 0.f;
           o.y *= ceb_hash32(key + 1) >= drop_thresh ? inv_keep : 0.f;
           o.z *= ceb_hash32(key + 2) >= drop_thresh ? inv_keep : 0.f;
@@ -369,9 +378,9 @@ ln_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict_
         uint2 pk; pk.x = *(const uint32_t*)&lo; pk.y = *(const uint32_t*)&hi;
         *(uint2*)(dx_bf16 + row * E + g * 128 + lane * 4) = pk;
       }
-      ag[g].x = fmaf(d[g].x, xh[g].x, ag[g].x); ag[g].y = fmaf(d[g].y, xh[g].y, ag[g].y);
-      ag[g].z = fmaf(d[g].z, xh[g].z, ag[g].z); ag[g].w = fmaf(d[g].w, xh[g].w, ag[g].w);
-      ab[g].x += d[g].x; ab[g].y += d[g].y; ab[g].z += d[g].z; ab[g].w += d[g].w;
+      ag[g].x = fmaf(d.x, xh.x, ag[g].x); ag[g].y = fmaf(d.y, xh.y, ag[g].y);
+      ag[g].z = fmaf(d.z, xh.z, ag[g].z); ag[g].w = fmaf(d.w, xh.w, ag[g].w);
+      ab[g].x += d.x; ab[g].y += d.y; ab[g].z += d.z; ab[g].w += d.w;
     }
   }
 #pragma unroll
@@ -393,7 +402,7 @@ static void launch_ln_bwd_vec(const void* dy, const float* x, const float* gamma
                               float* dx, float* dgamma, float* dbeta, int64_t rows, cudaStream_t st,
                               const float* dres = nullptr, void* dx_bf16 = nullptr, uint32_t drop_thresh = 0,
                               float inv_keep = 1.f, const unsigned long long* seed_dev = nullptr, uint32_t salt = 0) {
-  int blocks = ceb_num_sms() * 2;
+  int blocks = ceb_num_sms() * 4;
   if (blocks > ceb_cdiv(rows, 8)) blocks = (int)ceb_cdiv(rows, 8);
   ln_bwd_vec_kernel<G><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)dy, x, gamma, mean, rstd, dx, dgamma, dbeta, rows,
                                               dres, (__nv_bfloat16*)dx_bf16, drop_thresh, inv_keep, seed_dev, salt);
