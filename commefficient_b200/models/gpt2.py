@@ -105,7 +105,9 @@ class MLP(nn.Module):
         self.dropout = nn.Dropout(cfg.resid_pdrop)
 
     def forward(self, x, fuse_resid_dropout=False):
-        y = self.c_proj(nnops.gelu_tanh(self.c_fc(x)))
+        fc, pr = self.c_fc, self.c_proj
+        y = nnops.mlp_gelu(x.reshape(-1, x.shape[-1]), fc.weight.t(), fc.bias, pr.weight.t(), pr.bias)
+        y = y.view(x.shape[:-1] + (pr.nf,))
         return y if fuse_resid_dropout else self.dropout(y)
 
 

@@ -13,6 +13,8 @@ a checkpoint.  Reference layers: /root/reference/CommEfficient/models/resnet9.py
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn.functional as F
 
@@ -153,6 +155,19 @@ def advance_dropout(device) -> None:
     if _native and _precision == "bf16" and torch.device(device).type == "cuda":
         from . import tfm
         tfm.dropout_state(device).advance()
+
+
+_FUSE_MLP = os.environ.get("CEB_FUSE_MLP", "1") != "0"      # A/B switch for bench/ (the unfused chain is the fallback)
+
+
+def mlp_gelu(x, w_fc, b_fc, w_proj, b_proj):
+    """``proj(gelu_tanh(fc(x)))`` (weights in ``F.linear`` orientation ``[out, in]``).  Native bf16 path: the GELU and
+    its backward live in the GEMM epilogues (``ops/tc.py:_MLPGeluFn``)."""
+    if _use_native_bf16(x) and _FUSE_MLP:
+        from . import tc
+        if tc.mlp_gelu_supported(x, w_fc, w_proj):
+            return tc.mlp_gelu(x, w_fc, b_fc, w_proj, b_proj)
+    return linear(gelu_tanh(linear(x, w_fc, b_fc)), w_proj, b_proj)
 
 
 def gelu_tanh(x):
@@ -309,7 +324,7 @@ class BatchNorm2d(torch.nn.BatchNorm2d):
         if not (self.training and S > 1 and self.affine and (general or x.shape[0] % S == 0)):
             return super().forward(x)
         native_ok = False
-        if general and _use_native_bf16(x):
+        if general and _use_native(x) and _precision in ("bf16", "tf32"):
             from . import tfm
             native_ok = tfm.segment_bn_supported(x, _bn_seg_ids, _bn_seg_counts)
         if native_ok:

@@ -39,6 +39,9 @@ native.register_signatures({
     "ceb_gemm_bf16_tn_ld": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i64,
                              native.c_i32, native.c_i32, native.c_i32, native.c_ptr, native.c_i32, native.c_i32,
                              native.c_ptr], native.c_i32),
+    "ceb_gemm_bf16_tn_gelu": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_ptr,
+                               native.c_ptr, native.c_i64, native.c_i32, native.c_i32, native.c_i32, native.c_ptr,
+                               native.c_i32, native.c_ptr], native.c_i32),
     "ceb_gemm_bf16_mn_acc_ld": ([native.c_ptr, native.c_i64, native.c_ptr, native.c_i64, native.c_ptr, native.c_i32,
                                  native.c_i32, native.c_i32, native.c_i32, native.c_ptr], native.c_i32),
     "ceb_cast_transpose_f32_bf16": ([native.c_ptr, native.c_ptr, native.c_i32, native.c_i32, native.c_i64,
@@ -150,6 +153,32 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias=None, relu=False, out_dtype=t
     native.call("ceb_gemm_tf32_tn_ld" if tf else "ceb_gemm_bf16_tn_ld", native.ptr(a), a.stride(0), native.ptr(b),
                 b.stride(0), native.ptr(out), out.stride(0), M, N, K, native.ptr(bias), 1 if relu else 0, mode,
                 native.stream_ptr(a.device))
+    return out
+
+
+def gemm_tn_gelu(a: torch.Tensor, b: torch.Tensor, bias=None):
+    """``pre = a @ b.T + bias`` and ``act = gelu_tanh(pre)`` from one GEMM (bf16, N % 32 == 0): returns
+    ``(pre, act)``; the pre-activation is what the backward needs."""
+    assert _rows_ok(a) and _rows_ok(b) and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    M, K = a.shape
+    N = b.shape[0]
+    assert b.shape[1] == K and N % 32 == 0
+    pre = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    act = torch.empty_like(pre)
+    native.call("ceb_gemm_bf16_tn_gelu", native.ptr(a), a.stride(0), native.ptr(b), b.stride(0), native.ptr(pre),
+                native.ptr(act), None, N, M, N, K, native.ptr(bias), 2, native.stream_ptr(a.device))
+    return pre, act
+
+
+def gemm_tn_gelu_grad(a: torch.Tensor, b: torch.Tensor, pre: torch.Tensor) -> torch.Tensor:
+    """``(a @ b.T) * gelu_tanh'(pre)``: the GELU backward applied in the epilogue of the data-gradient GEMM."""
+    assert _rows_ok(a) and _rows_ok(b) and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    M, K = a.shape
+    N = b.shape[0]
+    assert b.shape[1] == K and N % 32 == 0 and pre.shape == (M, N) and pre.is_contiguous() and pre.dtype == torch.bfloat16
+    out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    native.call("ceb_gemm_bf16_tn_gelu", native.ptr(a), a.stride(0), native.ptr(b), b.stride(0), native.ptr(out), None,
+                native.ptr(pre), N, M, N, K, None, 3, native.stream_ptr(a.device))
     return out
 
 
@@ -570,6 +599,34 @@ def _w_rows(store: torch.Tensor, transpose: bool, dtype) -> torch.Tensor:
     return store if _rows_ok(store) else _as_rows(store, torch.float32)
 
 
+def _weight_grad(xb, dyb, weight, transposed):
+    """``dW += dY^T X`` (split-K MN-major GEMM, fp32 accumulate) -- straight into ``weight.grad`` when that exists
+    (the flat gradient buffer), in which case ``None`` is returned."""
+    store, _ = _weight_storage(weight)
+    param = weight._base if (transposed and weight._base is not None) else weight
+    target = param.grad if (isinstance(param, torch.nn.Parameter) and param.grad is not None
+                            and param.grad.is_contiguous()) else None
+    acc = target if target is not None else torch.zeros_like(store, dtype=torch.float32)
+    if transposed:
+        gemm_mn_acc(xb, dyb, acc)          # dW_storage[K, N] += X^T dY
+    else:
+        gemm_mn_acc(dyb, xb, acc)          # dW[N, K] += dY^T X
+    if target is not None:
+        return None
+    return acc.t() if transposed else acc
+
+
+def _bias_grad(dyb, bias):
+    """Column sums of the output gradient, accumulated straight into ``bias.grad`` when that exists."""
+    if dyb.shape[1] % 8 == 0 and dyb.dtype == torch.bfloat16:
+        direct = (isinstance(bias, torch.nn.Parameter) and bias.grad is not None
+                  and bias.grad.is_contiguous() and bias.grad.dtype == torch.float32)
+        acc_b = bias.grad if direct else torch.zeros(dyb.shape[1], dtype=torch.float32, device=dyb.device)
+        colsum_acc(dyb, acc_b)
+        return None if direct else acc_b
+    return dyb.float().sum(0)
+
+
 class _LinearFn(torch.autograd.Function):
     """``y = x W^T + b`` on the tcgen05 GEMMs.  Both GEMMs that read the weight want it K-major, so the
     fp32 master weight is cast to bf16 once per direction: as stored for one of them, through the
@@ -605,33 +662,61 @@ class _LinearFn(torch.autograd.Function):
             wt = _w_rows(store, not transposed, xb.dtype)                        # [K, N]
             dx = gemm_tn(dyb, wt)
             dx = dx.view(ctx.x_shape).to(ctx.x_dtype)
-        dw = None
-        if ctx.needs_input_grad[1]:
-            param = weight._base if (transposed and weight._base is not None) else weight
-            target = param.grad if (isinstance(param, torch.nn.Parameter) and param.grad is not None
-                                    and param.grad.is_contiguous()) else None
-            acc = target if target is not None else torch.zeros_like(store, dtype=torch.float32)
-            if transposed:
-                gemm_mn_acc(xb, dyb, acc)          # dW_storage[K, N] += X^T dY
-            else:
-                gemm_mn_acc(dyb, xb, acc)          # dW[N, K] += dY^T X
-            if target is None:
-                dw = acc.t() if transposed else acc
-        db = None
-        if bias is not None and ctx.needs_input_grad[2]:
-            if dyb.shape[1] % 8 == 0 and dyb.dtype == torch.bfloat16:
-                direct = (isinstance(bias, torch.nn.Parameter) and bias.grad is not None
-                          and bias.grad.is_contiguous() and bias.grad.dtype == torch.float32)
-                acc_b = bias.grad if direct else torch.zeros(dyb.shape[1], dtype=torch.float32, device=dy.device)
-                colsum_acc(dyb, acc_b)
-                db = None if direct else acc_b
-            else:
-                db = dyb.float().sum(0)
+        dw = _weight_grad(xb, dyb, weight, transposed) if ctx.needs_input_grad[1] else None
+        db = _bias_grad(dyb, bias) if (bias is not None and ctx.needs_input_grad[2]) else None
         return dx, dw, db
 
 
 def linear(x, weight, bias=None):
     return _LinearFn.apply(x, weight, bias)
+
+
+class _MLPGeluFn(torch.autograd.Function):
+    """The transformer MLP ``proj(gelu_tanh(fc(x)))`` with the activation inside the GEMM epilogues: the fc GEMM
+    writes the pre-activation and its GELU in one pass, and the data-gradient GEMM of proj multiplies by
+    ``GELU'(pre)`` while storing -- the ``[rows, 4E]`` tensors are touched by no element-wise kernel at all
+    (reference: pytorch_transformers' MLP called from /root/reference/CommEfficient/gpt2_train.py:259-262)."""
+
+    @staticmethod
+    def forward(ctx, x, w_fc, b_fc, w_proj, b_proj):
+        s_fc, t_fc = _weight_storage(w_fc)
+        s_pr, t_pr = _weight_storage(w_proj)
+        xb = _as_rows(x, torch.bfloat16)
+        pre, act = gemm_tn_gelu(xb, _w_rows(s_fc, t_fc, torch.bfloat16),
+                                bias=b_fc.float().contiguous() if b_fc is not None else None)
+        y = gemm_tn(act, _w_rows(s_pr, t_pr, torch.bfloat16), bias=b_proj.float().contiguous() if b_proj is not None else None)
+        ctx.save_for_backward(xb, pre, act)
+        ctx.params = (w_fc, b_fc, w_proj, b_proj, t_fc, t_pr)
+        ctx.x_shape, ctx.x_dtype = x.shape, x.dtype
+        return y.view(*x.shape[:-1], w_proj.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        xb, pre, act = ctx.saved_tensors
+        w_fc, b_fc, w_proj, b_proj, t_fc, t_pr = ctx.params
+        s_fc, _ = _weight_storage(w_fc)
+        s_pr, _ = _weight_storage(w_proj)
+        dyb = _as_rows(dy, torch.bfloat16)
+        need = ctx.needs_input_grad
+        d_pre = gemm_tn_gelu_grad(dyb, _w_rows(s_pr, not t_pr, torch.bfloat16), pre)
+        dw_pr = _weight_grad(act, dyb, w_proj, t_pr) if need[3] else None
+        db_pr = _bias_grad(dyb, b_proj) if (b_proj is not None and need[4]) else None
+        dx = None
+        if need[0]:
+            dx = gemm_tn(d_pre, _w_rows(s_fc, not t_fc, torch.bfloat16)).view(ctx.x_shape).to(ctx.x_dtype)
+        dw_fc = _weight_grad(xb, d_pre, w_fc, t_fc) if need[1] else None
+        db_fc = _bias_grad(d_pre, b_fc) if (b_fc is not None and need[2]) else None
+        return dx, dw_fc, db_fc, dw_pr, db_pr
+
+
+def mlp_gelu_supported(x, w_fc, w_proj) -> bool:
+    return (linear_supported(x, w_fc) and w_fc.shape[0] % 64 == 0 and w_proj.dim() == 2
+            and w_proj.shape[1] == w_fc.shape[0] and _weight_storage(w_proj)[0] is not None
+            and w_proj.dtype == torch.float32 and w_proj.shape[0] % 64 == 0)
+
+
+def mlp_gelu(x, w_fc, b_fc, w_proj, b_proj):
+    return _MLPGeluFn.apply(x, w_fc, b_fc, w_proj, b_proj)
 
 
 # ---------------------------------------------------------------------------- LM head + cross-entropy

@@ -44,6 +44,12 @@ native.register_signatures({
     "ceb_segment_bn_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32,
                             native.c_i32, native.c_i32, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
                             native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_segment_bn_f32_fwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32, native.c_i32,
+                                native.c_i32, native.c_ptr, native.c_ptr, native.c_f32, native.c_ptr, native.c_ptr,
+                                native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr], native.c_i32),
+    "ceb_segment_bn_f32_bwd": ([native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr, native.c_i64, native.c_i32,
+                                native.c_i32, native.c_i32, native.c_ptr, native.c_ptr, native.c_ptr, native.c_ptr,
+                                native.c_ptr, native.c_ptr], native.c_i32),
 })
 
 
@@ -146,8 +152,9 @@ def gelu_tanh(x):
 
 
 class _SegmentBNNative(torch.autograd.Function):
-    """Segment-wise BatchNorm on the native kernels (``csrc/nn_aux.cu``): channels_last bf16 activations,
-    fp32 statistics per (client segment, channel); 3 launches forward, 2 backward, no fp32 copies."""
+    """Segment-wise BatchNorm on the native kernels (``csrc/nn_aux.cu``): channels_last bf16 (or, in the
+    tf32 / fp32 precision modes, fp32) activations, fp32 statistics per (client segment, channel); 3 launches
+    forward, 2 backward, no copies."""
 
     @staticmethod
     def forward(ctx, x, weight, bias, seg, samples, segments, eps):
@@ -161,7 +168,7 @@ class _SegmentBNNative(torch.autograd.Function):
         var = torch.empty_like(mean)
         rstd = torch.empty_like(mean)
         y = torch.empty_like(x)                      # keeps channels_last strides
-        native.call("ceb_segment_bn_fwd", native.ptr(x), native.ptr(seg), native.ptr(samples), N, L, C, segments,
+        native.call("ceb_segment_bn_f32_fwd" if x.dtype == torch.float32 else "ceb_segment_bn_fwd", native.ptr(x), native.ptr(seg), native.ptr(samples), N, L, C, segments,
                     native.ptr(g), native.ptr(b), float(eps), native.ptr(sums), native.ptr(mean), native.ptr(var),
                     native.ptr(rstd), native.ptr(y), native.stream_ptr(dev))
         ctx.save_for_backward(x, g, mean, rstd, seg, samples)
@@ -174,17 +181,17 @@ class _SegmentBNNative(torch.autograd.Function):
         x, g, mean, rstd, seg, samples = ctx.saved_tensors
         N, C, H, W = x.shape
         dev = x.device
-        dyc = dy.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        dyc = dy.to(x.dtype).contiguous(memory_format=torch.channels_last)
         sums = torch.empty((2, ctx.segments, C), dtype=torch.float32, device=dev)
         dx = torch.empty_like(x)
-        native.call("ceb_segment_bn_bwd", native.ptr(dyc), native.ptr(x), native.ptr(seg), native.ptr(samples), N, H * W,
+        native.call("ceb_segment_bn_f32_bwd" if x.dtype == torch.float32 else "ceb_segment_bn_bwd", native.ptr(dyc), native.ptr(x), native.ptr(seg), native.ptr(samples), N, H * W,
                     C, ctx.segments, native.ptr(g), native.ptr(mean), native.ptr(rstd), native.ptr(sums), native.ptr(dx),
                     native.stream_ptr(dev))
         return dx, sums[1].sum(0), sums[0].sum(0), None, None, None, None
 
 
 def segment_bn_supported(x, seg, samples) -> bool:
-    return (x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and x.shape[1] % 8 == 0
+    return (x.is_cuda and x.dim() == 4 and x.dtype in (torch.bfloat16, torch.float32) and x.shape[1] % 8 == 0
             and x.is_contiguous(memory_format=torch.channels_last) and seg is not None and samples is not None
             and seg.dtype == torch.int64 and seg.is_cuda)
 

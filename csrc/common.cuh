@@ -90,6 +90,24 @@ static inline uint32_t ceb_drop_thresh(float p_drop) {
   return t == 0 ? 1u : t;
 }
 
+// tanh-GELU (GPT-2's activation).  tanh.approx.f32 is one MUFU op with relative error ~2^-11, below bf16's
+// 2^-8 output precision.
+__device__ __forceinline__ float ceb_tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float ceb_gelu_tanh(float x) {
+  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  return 0.5f * x * (1.f + ceb_tanh_fast(u));
+}
+__device__ __forceinline__ float ceb_gelu_tanh_grad(float x) {
+  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  const float t = ceb_tanh_fast(u);
+  const float du = 0.7978845608028654f * (1.f + 3.f * 0.044715f * x * x);
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
+}
+
 __device__ __forceinline__ uint32_t abs_key(float v) {
   // Monotone key of |v|; NaN maps to 0 so it is never preferred by top-k.
   uint32_t b = __float_as_uint(v) & 0x7fffffffu;

@@ -228,6 +228,84 @@ ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
     y[row * E + j] = __float2bfloat16((xr[j] - mu) * rs * __ldg(gamma + j) + __ldg(beta + j));
 }
 
+// Vector variant for E = 128 * G and 16-byte aligned rows: a lane owns G float4 column groups, the row stays in
+// registers between the statistics and the normalisation (one global read of x / branch, 16-byte accesses).
+template <int G>
+__global__ void __launch_bounds__(256)
+ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                  __nv_bfloat16* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd, int64_t rows,
+                  float eps, const __nv_bfloat16* __restrict__ branch, float* __restrict__ resid_out,
+                  uint32_t drop_thresh, float inv_keep, const unsigned long long* __restrict__ seed_dev, uint32_t salt) {
+  constexpr int E = 128 * G;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float4 v[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) v[g] = *(const float4*)(x + row * E + g * 128 + lane * 4);
+  if (branch) {
+    const uint32_t rowkey = drop_thresh ? ceb_drop_rowkey(seed_dev, salt, (uint32_t)row) : 0u;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const uint2 raw = *(const uint2*)(branch + row * E + g * 128 + lane * 4);
+      const float2 b01 = __bfloat1622float2(*(const __nv_bfloat162*)&raw.x);
+      const float2 b23 = __bfloat1622float2(*(const __nv_bfloat162*)&raw.y);
+      float k0 = 1.f, k1 = 1.f, k2 = 1.f, k3 = 1.f;
+      if (drop_thresh) {
+        const uint32_t key = rowkey + (uint32_t)(g * 128 + lane * 4);
+        k0 = ceb_hash32(key) >= drop_thresh ? inv_keep : 0.f;
+        k1 = ceb_hash32(key + 1) >= drop_thresh ? inv_keep : 0.f;
+        k2 = ceb_hash32(key + 2) >= drop_thresh ? inv_keep : 0.f;
+        k3 = ceb_hash32(key + 3) >= drop_thresh ? inv_keep : 0.f;
+      }
+      v[g].x = fmaf(b01.x, k0, v[g].x); v[g].y = fmaf(b01.y, k1, v[g].y);
+      v[g].z = fmaf(b23.x, k2, v[g].z); v[g].w = fmaf(b23.y, k3, v[g].w);
+      *(float4*)(resid_out + row * E + g * 128 + lane * 4) = v[g];
+    }
+  }
+  float s = 0.f, ss = 0.f;
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    s += (v[g].x + v[g].y) + (v[g].z + v[g].w);
+    ss = fmaf(v[g].x, v[g].x, fmaf(v[g].y, v[g].y, fmaf(v[g].z, v[g].z, fmaf(v[g].w, v[g].w, ss))));
+  }
+  s = warp_sum(s); ss = warp_sum(ss);
+  const float mu = s * (1.f / E);
+  const float rs = rsqrtf(fmaxf(ss * (1.f / E) - mu * mu, 0.f) + eps);
+  if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const float4 gm = __ldg((const float4*)(gamma + g * 128 + lane * 4));
+    const float4 bt = __ldg((const float4*)(beta + g * 128 + lane * 4));
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(fmaf((v[g].x - mu) * rs, gm.x, bt.x), fmaf((v[g].y - mu) * rs, gm.y, bt.y));
+    const __nv_bfloat162 hi = __floats2bfloat162_rn(fmaf((v[g].z - mu) * rs, gm.z, bt.z), fmaf((v[g].w - mu) * rs, gm.w, bt.w));
+    uint2 pk; pk.x = *(const uint32_t*)&lo; pk.y = *(const uint32_t*)&hi;
+    *(uint2*)(y + row * E + g * 128 + lane * 4) = pk;
+  }
+}
+
+static bool ln_vec_width(int E) { return E == 128 || E == 256 || E == 512 || E == 768 || E == 1024 || E == 1280; }
+
+// launches the vector kernel when the width and the alignment allow it, else the scalar one
+static void launch_ln_fwd(const float* x, const float* gamma, const float* beta, __nv_bfloat16* y, float* mean, float* rstd,
+                          int64_t rows, int E, float eps, const __nv_bfloat16* branch, float* resid_out, uint32_t th,
+                          float inv_keep, const unsigned long long* seed_dev, uint32_t salt, cudaStream_t st) {
+  const unsigned grid = (unsigned)ceb_cdiv(rows, 8);
+  const bool aligned = ((((uintptr_t)x | (uintptr_t)gamma | (uintptr_t)beta | (uintptr_t)y | (uintptr_t)branch |
+                          (uintptr_t)resid_out) & 15) == 0);
+#define CEB_LN_FWD_CASE(G_)                                                                                          \
+  case G_: ln_fwd_vec_kernel<G_><<<grid, 256, 0, st>>>(x, gamma, beta, y, mean, rstd, rows, eps, branch, resid_out, \
+                                                       th, inv_keep, seed_dev, salt); return;
+  if (aligned && ln_vec_width(E)) {
+    switch (E / 128) {
+      CEB_LN_FWD_CASE(1) CEB_LN_FWD_CASE(2) CEB_LN_FWD_CASE(4) CEB_LN_FWD_CASE(6) CEB_LN_FWD_CASE(8) CEB_LN_FWD_CASE(10)
+    }
+  }
+#undef CEB_LN_FWD_CASE
+  ln_fwd_kernel<<<grid, 256, 0, st>>>(x, gamma, beta, y, mean, rstd, rows, E, eps, branch, resid_out, th, inv_keep, seed_dev,
+                                      salt);
+}
+
 // dx = rstd * (g - mean(g) - xhat * mean(g * xhat)), g = dy * gamma ; dgamma += dy * xhat ; dbeta += dy
 __global__ void __launch_bounds__(256)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
@@ -269,8 +347,8 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x,
 CEB_API int ceb_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* y_bf16, float* mean,
                               float* rstd, int64_t rows, int E, float eps, void* stream) {
   CEB_REQUIRE(x && gamma && beta && y_bf16 && mean && rstd && rows > 0 && E > 0, "ceb_layernorm_fwd: bad arguments");
-  ln_fwd_kernel<<<(unsigned)ceb_cdiv(rows, 8), 256, 0, (cudaStream_t)stream>>>(x, gamma, beta, (__nv_bfloat16*)y_bf16,
-                                                                                mean, rstd, rows, E, eps, nullptr, nullptr);
+  launch_ln_fwd(x, gamma, beta, (__nv_bfloat16*)y_bf16, mean, rstd, rows, E, eps, nullptr, nullptr, 0, 1.f, nullptr, 0,
+                (cudaStream_t)stream);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -294,9 +372,9 @@ CEB_API int ceb_add_layernorm_drop_fwd(const float* x, const void* branch_bf16, 
               "ceb_add_layernorm_fwd: bad arguments");
   CEB_REQUIRE(p_drop >= 0.f && p_drop < 1.f && rows < (1ll << 32), "ceb_add_layernorm_fwd: p_drop=%f rows=%lld", p_drop, (long long)rows);
   const uint32_t th = ceb_drop_thresh(p_drop);
-  ln_fwd_kernel<<<(unsigned)ceb_cdiv(rows, 8), 256, 0, (cudaStream_t)stream>>>(
-      x, gamma, beta, (__nv_bfloat16*)y_bf16, mean, rstd, rows, E, eps, (const __nv_bfloat16*)branch_bf16, resid_out,
-      th, th ? 1.f / (1.f - p_drop) : 1.f, (const unsigned long long*)seed_dev, salt);
+  launch_ln_fwd(x, gamma, beta, (__nv_bfloat16*)y_bf16, mean, rstd, rows, E, eps, (const __nv_bfloat16*)branch_bf16,
+                resid_out, th, th ? 1.f / (1.f - p_drop) : 1.f, (const unsigned long long*)seed_dev, salt,
+                (cudaStream_t)stream);
   CEB_COUNT_LAUNCH(1);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -408,7 +486,6 @@ static void launch_ln_bwd_vec(const void* dy, const float* x, const float* gamma
                                               dres, (__nv_bfloat16*)dx_bf16, drop_thresh, inv_keep, seed_dev, salt);
 }
 
-static bool ln_vec_width(int E) { return E == 128 || E == 256 || E == 512 || E == 768 || E == 1024 || E == 1280; }
 
 template <typename... A>
 static void dispatch_ln_bwd_vec(int E, A... args) {
@@ -483,21 +560,9 @@ CEB_API int ceb_layernorm_bwd(const void* dy_bf16, const float* x, const float* 
 
 // ------------------------------------------------------------------ tanh-GELU (bf16)
 // tanh.approx.f32 (one MUFU op, relative error ~2^-11) is below bf16's 2^-8 output precision.
-__device__ __forceinline__ float tanh_fast(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float gelu_tanh(float x) {
-  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-  return 0.5f * x * (1.f + tanh_fast(u));
-}
-__device__ __forceinline__ float gelu_tanh_grad(float x) {
-  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-  const float t = tanh_fast(u);
-  const float du = 0.7978845608028654f * (1.f + 3.f * 0.044715f * x * x);
-  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
-}
+// (ceb_gelu_tanh / ceb_gelu_tanh_grad live in common.cuh: the GEMM epilogues apply them too)
+__device__ __forceinline__ float gelu_tanh(float x) { return ceb_gelu_tanh(x); }
+__device__ __forceinline__ float gelu_tanh_grad(float x) { return ceb_gelu_tanh_grad(x); }
 __device__ __forceinline__ uint32_t gelu_pair(uint32_t xr, uint32_t gr, bool bwd) {
   const float2 v = __bfloat1622float2(*(const __nv_bfloat162*)&xr);
   float2 r;
@@ -892,10 +957,27 @@ __device__ __forceinline__ uint4 segbn_pack(const float (&f)[8]) {
   return u;
 }
 
+// 8 consecutive channels of one pixel: one 16-byte access for bf16, two for fp32 (the tf32 / fp32 paths keep
+// fp32 activations)
+__device__ __forceinline__ void segbn_load8(const __nv_bfloat16* p, float (&f)[8]) {
+  segbn_unpack(*reinterpret_cast<const uint4*>(p), f);
+}
+__device__ __forceinline__ void segbn_load8(const float* p, float (&f)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ void segbn_store8(__nv_bfloat16* p, const float (&f)[8]) {
+  *reinterpret_cast<uint4*>(p) = segbn_pack(f);
+}
+__device__ __forceinline__ void segbn_store8(float* p, const float (&f)[8]) {
+  *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(f[4], f[5], f[6], f[7]);
+}
+
 // MODE 0: a[s][c] += sum x, b[s][c] += sum x^2.   MODE 1 (backward): a += sum dy, b += sum dy * xhat.
-template <int MODE>
+template <int MODE, typename T>
 __global__ void __launch_bounds__(256)
-segbn_sums_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+segbn_sums_kernel(const T* __restrict__ x, const T* __restrict__ dy,
                   const int64_t* __restrict__ seg, int L, int C, int chunks, const float* __restrict__ mean,
                   const float* __restrict__ rstd, float* __restrict__ a, float* __restrict__ b) {
   __shared__ float sa[32][65], sb[32][65];
@@ -915,13 +997,13 @@ segbn_sums_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __re
     for (int p = chunk * SEGBN_PIX + pl; p < p_end; p += 32) {
       const size_t off = ((size_t)n * L + p) * C + c0;
       float xv[8];
-      segbn_unpack(*reinterpret_cast<const uint4*>(x + off), xv);
+      segbn_load8(x + off, xv);
       if (MODE == 0) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) { acc_a[j] += xv[j]; acc_b[j] = fmaf(xv[j], xv[j], acc_b[j]); }
       } else {
         float dv[8];
-        segbn_unpack(*reinterpret_cast<const uint4*>(dy + off), dv);
+        segbn_load8(dy + off, dv);
 #pragma unroll
         for (int j = 0; j < 8; ++j) { acc_a[j] += dv[j]; acc_b[j] = fmaf(dv[j], (xv[j] - mu[j]) * rs[j], acc_b[j]); }
       }
@@ -955,13 +1037,13 @@ __global__ void segbn_finalize_kernel(const float* __restrict__ a, const float* 
 
 // MODE 0: y = (x - mean) * rstd * gamma + beta.
 // MODE 1: dx = gamma * rstd * (dy - A/cnt - xhat * B/cnt)   (A, B from segbn_sums_kernel<1>)
-template <int MODE>
+template <int MODE, typename T>
 __global__ void __launch_bounds__(256)
-segbn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+segbn_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy,
                    const int64_t* __restrict__ seg, int L, int C, int64_t total8, const float* __restrict__ mean,
                    const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
                    const float* __restrict__ A, const float* __restrict__ B, const float* __restrict__ samples,
-                   __nv_bfloat16* __restrict__ out) {
+                   T* __restrict__ out) {
   const int c8 = C >> 3;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total8; i += stride) {
@@ -971,14 +1053,14 @@ segbn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
     const int s = (int)seg[n];
     const size_t off = (size_t)pix * C + c0, so = (size_t)s * C + c0;
     float xv[8], o[8];
-    segbn_unpack(*reinterpret_cast<const uint4*>(x + off), xv);
+    segbn_load8(x + off, xv);
     if (MODE == 0) {
 #pragma unroll
       for (int j = 0; j < 8; ++j)
         o[j] = fmaf((xv[j] - mean[so + j]) * rstd[so + j], __ldg(gamma + c0 + j), __ldg(beta + c0 + j));
     } else {
       float dv[8];
-      segbn_unpack(*reinterpret_cast<const uint4*>(dy + off), dv);
+      segbn_load8(dy + off, dv);
       const float inv = 1.f / fmaxf(samples[s] * (float)L, 1.f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -987,7 +1069,7 @@ segbn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
         o[j] = __ldg(gamma + c0 + j) * rs * (dv[j] - A[so + j] * inv - xh * B[so + j] * inv);
       }
     }
-    *reinterpret_cast<uint4*>(out + off) = segbn_pack(o);
+    segbn_store8(out + off, o);
   }
 }
 
@@ -999,23 +1081,22 @@ static int segbn_check(const char* who, const void* x, int64_t N, int L, int C, 
 
 // Forward.  sums: [2][S][C] fp32 scratch (zeroed here); mean / var / rstd: [S][C] outputs; samples: [S]
 // fp32 samples per segment; seg: [N] int64 segment of every sample.
-CEB_API int ceb_segment_bn_fwd(const void* x_bf16, const int64_t* seg, const float* samples, int64_t N, int L, int C,
-                               int S, const float* gamma, const float* beta, float eps, float* sums, float* mean,
-                               float* var, float* rstd, void* y_bf16, void* stream) {
-  if (int e = segbn_check("ceb_segment_bn_fwd", x_bf16, N, L, C, S)) return e;
-  CEB_REQUIRE(seg && samples && gamma && beta && sums && mean && var && rstd && y_bf16, "ceb_segment_bn_fwd: null pointer");
+template <typename T>
+static int segbn_fwd_impl(const char* who, const T* x, const int64_t* seg, const float* samples, int64_t N, int L, int C,
+                          int S, const float* gamma, const float* beta, float eps, float* sums, float* mean, float* var,
+                          float* rstd, T* y, void* stream) {
+  if (int e = segbn_check(who, x, N, L, C, S)) return e;
+  CEB_REQUIRE(seg && samples && gamma && beta && sums && mean && var && rstd && y, "%s: null pointer", who);
   cudaStream_t st = (cudaStream_t)stream;
   const int chunks = (int)ceb_cdiv(L, SEGBN_PIX);
   CEB_CHECK_CUDA(cudaMemsetAsync(sums, 0, (size_t)2 * S * C * sizeof(float), st));
   dim3 grid((unsigned)(N * chunks), (unsigned)ceb_cdiv(C, 64));
-  segbn_sums_kernel<0><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x_bf16, nullptr, seg, L, C, chunks, nullptr, nullptr,
-                                             sums, sums + (size_t)S * C);
+  segbn_sums_kernel<0, T><<<grid, 256, 0, st>>>(x, nullptr, seg, L, C, chunks, nullptr, nullptr, sums, sums + (size_t)S * C);
   segbn_finalize_kernel<<<(unsigned)ceb_cdiv((int64_t)S * C, 256), 256, 0, st>>>(sums, sums + (size_t)S * C, samples, L, S,
                                                                                C, eps, mean, var, rstd);
   const int64_t total8 = N * L * (C / 8);
-  segbn_apply_kernel<0><<<ceb_grid_for(total8, 256), 256, 0, st>>>((const __nv_bfloat16*)x_bf16, nullptr, seg, L, C, total8,
-                                                                  mean, rstd, gamma, beta, nullptr, nullptr, samples,
-                                                                  (__nv_bfloat16*)y_bf16);
+  segbn_apply_kernel<0, T><<<ceb_grid_for(total8, 256), 256, 0, st>>>(x, nullptr, seg, L, C, total8, mean, rstd, gamma, beta,
+                                                                     nullptr, nullptr, samples, y);
   CEB_COUNT_LAUNCH(3);
   CEB_CHECK_LAUNCH();
   return 0;
@@ -1023,23 +1104,47 @@ CEB_API int ceb_segment_bn_fwd(const void* x_bf16, const int64_t* seg, const flo
 
 // Backward.  sums: [2][S][C] scratch; on return sums[0] = per-segment sum of dy (dbeta = its sum over
 // segments), sums[1] = per-segment sum of dy * xhat (dgamma likewise).
-CEB_API int ceb_segment_bn_bwd(const void* dy_bf16, const void* x_bf16, const int64_t* seg, const float* samples,
-                               int64_t N, int L, int C, int S, const float* gamma, const float* mean, const float* rstd,
-                               float* sums, void* dx_bf16, void* stream) {
-  if (int e = segbn_check("ceb_segment_bn_bwd", x_bf16, N, L, C, S)) return e;
-  CEB_REQUIRE(dy_bf16 && seg && samples && gamma && mean && rstd && sums && dx_bf16 && (((uintptr_t)dy_bf16) & 15) == 0,
-              "ceb_segment_bn_bwd: null or misaligned pointer");
+template <typename T>
+static int segbn_bwd_impl(const char* who, const T* dy, const T* x, const int64_t* seg, const float* samples, int64_t N,
+                          int L, int C, int S, const float* gamma, const float* mean, const float* rstd, float* sums, T* dx,
+                          void* stream) {
+  if (int e = segbn_check(who, x, N, L, C, S)) return e;
+  CEB_REQUIRE(dy && seg && samples && gamma && mean && rstd && sums && dx && (((uintptr_t)dy) & 15) == 0,
+              "%s: null or misaligned pointer", who);
   cudaStream_t st = (cudaStream_t)stream;
   const int chunks = (int)ceb_cdiv(L, SEGBN_PIX);
   CEB_CHECK_CUDA(cudaMemsetAsync(sums, 0, (size_t)2 * S * C * sizeof(float), st));
   dim3 grid((unsigned)(N * chunks), (unsigned)ceb_cdiv(C, 64));
-  segbn_sums_kernel<1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x_bf16, (const __nv_bfloat16*)dy_bf16, seg, L, C, chunks,
-                                             mean, rstd, sums, sums + (size_t)S * C);
+  segbn_sums_kernel<1, T><<<grid, 256, 0, st>>>(x, dy, seg, L, C, chunks, mean, rstd, sums, sums + (size_t)S * C);
   const int64_t total8 = N * L * (C / 8);
-  segbn_apply_kernel<1><<<ceb_grid_for(total8, 256), 256, 0, st>>>((const __nv_bfloat16*)x_bf16, (const __nv_bfloat16*)dy_bf16,
-                                                                  seg, L, C, total8, mean, rstd, gamma, nullptr, sums,
-                                                                  sums + (size_t)S * C, samples, (__nv_bfloat16*)dx_bf16);
+  segbn_apply_kernel<1, T><<<ceb_grid_for(total8, 256), 256, 0, st>>>(x, dy, seg, L, C, total8, mean, rstd, gamma, nullptr,
+                                                                     sums, sums + (size_t)S * C, samples, dx);
   CEB_COUNT_LAUNCH(2);
   CEB_CHECK_LAUNCH();
   return 0;
+}
+
+CEB_API int ceb_segment_bn_fwd(const void* x_bf16, const int64_t* seg, const float* samples, int64_t N, int L, int C,
+                               int S, const float* gamma, const float* beta, float eps, float* sums, float* mean,
+                               float* var, float* rstd, void* y_bf16, void* stream) {
+  return segbn_fwd_impl("ceb_segment_bn_fwd", (const __nv_bfloat16*)x_bf16, seg, samples, N, L, C, S, gamma, beta, eps,
+                        sums, mean, var, rstd, (__nv_bfloat16*)y_bf16, stream);
+}
+CEB_API int ceb_segment_bn_bwd(const void* dy_bf16, const void* x_bf16, const int64_t* seg, const float* samples,
+                               int64_t N, int L, int C, int S, const float* gamma, const float* mean, const float* rstd,
+                               float* sums, void* dx_bf16, void* stream) {
+  return segbn_bwd_impl("ceb_segment_bn_bwd", (const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16, seg, samples, N,
+                        L, C, S, gamma, mean, rstd, sums, (__nv_bfloat16*)dx_bf16, stream);
+}
+// fp32 activations (the tf32 / fp32 precision modes): same kernels, two 16-byte accesses per thread
+CEB_API int ceb_segment_bn_f32_fwd(const float* x, const int64_t* seg, const float* samples, int64_t N, int L, int C,
+                                   int S, const float* gamma, const float* beta, float eps, float* sums, float* mean,
+                                   float* var, float* rstd, float* y, void* stream) {
+  return segbn_fwd_impl("ceb_segment_bn_f32_fwd", x, seg, samples, N, L, C, S, gamma, beta, eps, sums, mean, var, rstd, y,
+                        stream);
+}
+CEB_API int ceb_segment_bn_f32_bwd(const float* dy, const float* x, const int64_t* seg, const float* samples, int64_t N,
+                                   int L, int C, int S, const float* gamma, const float* mean, const float* rstd,
+                                   float* sums, float* dx, void* stream) {
+  return segbn_bwd_impl("ceb_segment_bn_f32_bwd", dy, x, seg, samples, N, L, C, S, gamma, mean, rstd, sums, dx, stream);
 }

@@ -33,7 +33,8 @@ struct TcParams {
   const void* mask;      // bf16 [M][ldc] (nullable): output is zeroed where mask <= 0 (ReLU backward)
   int M, N, ldc;
   int k_steps;
-  int relu;
+  int relu;              // 0: none, 1: ReLU, 2: tanh-GELU with both outputs (C = pre-activation, C2 = GELU of it),
+                         // 3: multiply by GELU'(mask) (mask = the saved pre-activation); 2 and 3: bf16 direct path only
   int out_fp32;          // 0: bf16 store, 1: fp32 store, 2: fp32 atomic add
   int m_tiles, n_tiles;
   // convolution geometry
@@ -346,7 +347,7 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j) if (n0 + j < p.N) v[j] += __ldg(p.bias + n0 + j);
         }
-        if (p.relu) {
+        if (p.relu == 1) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
@@ -405,12 +406,36 @@ tc_tile_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
             for (int h2 = 0; h2 < 2; ++h2) {
               uint32_t w[8];
+              if (p.relu == 3) {
+                // GELU backward fused into the data-gradient GEMM: d_pre = d_act * GELU'(pre)
+                uint32_t pr[8];
+                ld_global_nc_v8((const __nv_bfloat16*)p.mask + off + h2 * 16, pr);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float2 x2 = __bfloat1622float2(*(const __nv_bfloat162*)&pr[j]);
+                  v[h2 * 16 + 2 * j] *= ceb_gelu_tanh_grad(x2.x);
+                  v[h2 * 16 + 2 * j + 1] *= ceb_gelu_tanh_grad(x2.y);
+                }
+              }
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 __nv_bfloat162 hh = __floats2bfloat162_rn(v[h2 * 16 + 2 * j], v[h2 * 16 + 2 * j + 1]);
                 w[j] = *(uint32_t*)&hh;
               }
-              if (p.mask) {
+              if (p.relu == 2) {
+                // GELU forward fused into the producing GEMM: the pre-activation is kept for the backward and the
+                // activation is computed from its ROUNDED value (what a separate GELU kernel would read)
+                st_global_v8((__nv_bfloat16*)p.C + off + h2 * 16, w);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float2 x2 = __bfloat1622float2(*(const __nv_bfloat162*)&w[j]);
+                  const __nv_bfloat162 a2 = __floats2bfloat162_rn(ceb_gelu_tanh(x2.x), ceb_gelu_tanh(x2.y));
+                  w[j] = *(const uint32_t*)&a2;
+                }
+                st_global_v8((__nv_bfloat16*)p.C2 + off + h2 * 16, w);
+                continue;
+              }
+              if (p.mask && p.relu != 3) {
                 // ReLU backward: keep a gradient only where the forward activation was positive
                 // (bf16 > 0  <=>  sign bit clear and magnitude bits non-zero)
                 uint32_t mk[8];
@@ -715,7 +740,8 @@ static int dispatch_tile(int bn, int mode, const CUtensorMap& ta, const CUtensor
 // embedding matrix (logits live in a buffer with ldc = 50 264).
 // out_mode 0: bf16 C, 1: fp32 C, 2: fp32 C += (atomic).
 static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
-                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream, int tf = 0);
+                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream, int tf = 0,
+                        void* c2 = nullptr, const void* aux = nullptr);
 
 CEB_API int ceb_gemm_bf16_tn_ld(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M,
                                 int N, int K, const float* bias, int relu, int out_mode, void* stream) {
@@ -733,7 +759,8 @@ CEB_API int ceb_gemm_bf16_tn_rows(const void* A, int64_t lda, const void* B, int
 }
 
 static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
-                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream, int tf) {
+                        const float* bias, int relu, int out_mode, const int* m_limit, void* stream, int tf, void* c2,
+                        const void* aux) {
   const int esz = tf ? 4 : 2, bke = 128 / esz, al = 16 / esz;     // element bytes, elements per k-step, 16-byte granule
   CEB_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "ceb_gemm_tn: bad arguments");
   CEB_REQUIRE(lda % al == 0 && ldb % al == 0 && lda >= K && ldb >= K,
@@ -754,7 +781,7 @@ static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, 
   if (int e = ceb_make_tmap(&tb, esz, B, 2, db, sb, bb, nullptr)) return e;
   TcParams p{};
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.ldc = (int)ldc; p.k_steps = (int)ceb_cdiv(K, bke);
-  p.relu = relu; p.out_fp32 = out_mode; p.conv = 0; p.m_limit = m_limit;
+  p.relu = relu; p.out_fp32 = out_mode; p.conv = 0; p.m_limit = m_limit; p.C2 = c2; p.mask = aux;
   if (out_mode == 2 && !relu) {
     // accumulate semantics allow split-K: pick the split that minimises (waves) x (k-steps per item + fixed cost)
     const int64_t units = pair ? ceb_cdiv(ceb_cdiv(M, BM), 2) * ceb_cdiv(N, bn) : ceb_cdiv(M, BM) * ceb_cdiv(N, bn);
@@ -776,6 +803,22 @@ static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, 
     if (m_limit) { p.auto_split = 1; p.k_total = kt; if (p.k_split < 1) p.k_split = 1; }
   }
   return dispatch_tile(bn, 0, ta, tb, p, (cudaStream_t)stream, pair, tf);
+}
+
+// GEMM with a tanh-GELU in the epilogue (bf16 [M][ldc] outputs, N % 32 == 0, ldc % 16 == 0, 32-byte aligned):
+//   act = 2: C = A B^T + bias (the pre-activation, kept for the backward), C2 = GELU(C)        (aux unused)
+//   act = 3: C = (A B^T) * GELU'(aux)        (aux = a saved pre-activation [M][ldc]; C2 unused)
+// One pass over the [M, 4E] MLP activations each way instead of a GEMM plus an element-wise kernel.
+CEB_API int ceb_gemm_bf16_tn_gelu(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, void* C2,
+                                  const void* aux, int64_t ldc, int M, int N, int K, const float* bias, int act,
+                                  void* stream) {
+  CEB_REQUIRE(act == 2 || act == 3, "ceb_gemm_bf16_tn_gelu: act=%d (2: forward, 3: backward)", act);
+  CEB_REQUIRE(A && B && C && (act == 2 ? C2 != nullptr : aux != nullptr), "ceb_gemm_bf16_tn_gelu: null pointer");
+  CEB_REQUIRE(N % 32 == 0 && ldc % 16 == 0 && ((((uintptr_t)C) | ((uintptr_t)C2) | ((uintptr_t)aux)) & 31) == 0,
+              "ceb_gemm_bf16_tn_gelu: need N %% 32 == 0, ldc %% 16 == 0 and 32-byte aligned outputs (N=%d ldc=%lld)", N,
+              (long long)ldc);
+  return gemm_tn_impl(A, lda, B, ldb, C, ldc, M, N, K, bias, act, 0, nullptr, stream, 0, act == 2 ? C2 : nullptr,
+                      act == 3 ? aux : nullptr);
 }
 
 // fp32 operands on the TF32 tensor-core path: C[M,N] (fp32) = act(A[M,K] * B[N,K]^T + bias).  lda, ldb

@@ -181,6 +181,11 @@ int ceb_cast_transpose_f32_bf16(const float* src, void* dst_bf16, int R, int C, 
  * bounded).  All three bases 16-byte aligned. */
 int ceb_gemm_bf16_tn_ld(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N,
                         int K, const float* bias, int relu, int out_mode, void* stream);
+/* The same GEMM with a tanh-GELU in its epilogue (bf16 [M][ldc] outputs; N % 32 == 0, ldc % 16 == 0, 32-byte
+ * aligned).  act = 2: C = A B^T + bias (pre-activation) and C2 = GELU(C); act = 3: C = (A B^T) * GELU'(aux) with
+ * aux a saved pre-activation [M][ldc] (the transformer MLP forward / backward without element-wise passes). */
+int ceb_gemm_bf16_tn_gelu(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, void* C2, const void* aux,
+                          int64_t ldc, int M, int N, int K, const float* bias, int act, void* stream);
 /* Same, computing only rows [0, *m_limit_dev) (whole 128-row tiles, never past M); m_limit_dev is a
  * DEVICE int read by the kernel, so a captured launch follows a data-dependent row count. */
 int ceb_gemm_bf16_tn_rows(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N,
@@ -256,6 +261,13 @@ int ceb_segment_bn_fwd(const void* x_bf16, const int64_t* seg, const float* samp
 int ceb_segment_bn_bwd(const void* dy_bf16, const void* x_bf16, const int64_t* seg, const float* samples, int64_t N,
                        int L, int C, int S, const float* gamma, const float* mean, const float* rstd, float* sums,
                        void* dx_bf16, void* stream);
+/* The same with fp32 activations (tf32 / fp32 precision modes). */
+int ceb_segment_bn_f32_fwd(const float* x, const int64_t* seg, const float* samples, int64_t N, int L, int C, int S,
+                           const float* gamma, const float* beta, float eps, float* sums, float* mean, float* var,
+                           float* rstd, float* y, void* stream);
+int ceb_segment_bn_f32_bwd(const float* dy, const float* x, const int64_t* seg, const float* samples, int64_t N, int L,
+                           int C, int S, const float* gamma, const float* mean, const float* rstd, float* sums, float* dx,
+                           void* stream);
 /* Classifier head + cross-entropy in one kernel: logits = scale * feat (bf16 [N][F]) @ W^T (fp32 [C][F]),
  * C <= 32, F % 64 == 0, F <= 2048.  g == NULL: forward, writes loss[N] and correct[N] (1.0 where the
  * arg-max equals the label).  g != NULL: backward of sum_s g[s] * loss[s]: writes dfeat (bf16 [N][F]) and

@@ -441,13 +441,15 @@ def test_conv3x3_fused_residual(n, h, cin, cout):
     assert torch.equal(masked, tc.conv3x3_nhwc(x, w, relu_mask=mask) + res)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("sizes,C,H", [([8] * 16, 64, 32), ([3, 5, 1, 7], 128, 8), ([2, 2, 2], 72, 5), ([6] * 4, 256, 4)])
-def test_segment_batchnorm_native_matches_reference(sizes, C, H):
-    """ceb_segment_bn_fwd / bwd vs per-client nn.BatchNorm2d in fp32."""
+def test_segment_batchnorm_native_matches_reference(sizes, C, H, dtype):
+    """ceb_segment_bn(_f32)_fwd / bwd vs per-client nn.BatchNorm2d in fp32."""
     from commefficient_b200.ops import tfm
     torch.manual_seed(C + H)
     N, S = sum(sizes), len(sizes)
-    x = (torch.randn(N, C, H, H, device=DEV) * 1.5 + 0.3).bfloat16().contiguous(memory_format=torch.channels_last)
+    lo = dtype == torch.bfloat16
+    x = (torch.randn(N, C, H, H, device=DEV) * 1.5 + 0.3).to(dtype).contiguous(memory_format=torch.channels_last)
     x.requires_grad_(True)
     w = torch.nn.Parameter(torch.randn(C, device=DEV) * 0.2 + 1.0)
     b = torch.nn.Parameter(torch.randn(C, device=DEV) * 0.2)
@@ -456,7 +458,8 @@ def test_segment_batchnorm_native_matches_reference(sizes, C, H):
     assert tfm.segment_bn_supported(x, seg, samples)
     y, mean, var = tfm.segment_batch_norm(x, w, b, seg, samples, S, 1e-5)
     assert y.is_contiguous(memory_format=torch.channels_last)
-    dy = torch.randn(N, C, H, H, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+    assert y.dtype == dtype
+    dy = torch.randn(N, C, H, H, device=DEV).to(dtype).contiguous(memory_format=torch.channels_last)
     y.backward(dy)
 
     xr = x.detach().float().requires_grad_(True)
@@ -469,11 +472,12 @@ def test_segment_batchnorm_native_matches_reference(sizes, C, H):
         bounds.append(bounds[-1] + n_)
     yr = torch.cat([ref(xr[a:c]) for a, c in zip(bounds[:-1], bounds[1:])])
     yr.backward(dy.float())
-    assert _rel_err(y, yr) < 1e-2
+    assert _rel_err(y, yr) < (1e-2 if lo else 1e-5)
     mr = torch.stack([xr[a:c].mean(dim=(0, 2, 3)) for a, c in zip(bounds[:-1], bounds[1:])])
     torch.testing.assert_close(mean, mr.detach(), rtol=1e-3, atol=1e-3)
-    assert _rel_err(x.grad, xr.grad) < 2e-2
-    assert _rel_err(w.grad, ref.weight.grad) < 1e-2 and _rel_err(b.grad, ref.bias.grad) < 1e-2
+    assert _rel_err(x.grad, xr.grad) < (2e-2 if lo else 1e-4)
+    tol = 1e-2 if lo else 1e-4
+    assert _rel_err(w.grad, ref.weight.grad) < tol and _rel_err(b.grad, ref.bias.grad) < tol
 
 
 @pytest.mark.parametrize("E", [128, 768, 1024])
@@ -522,3 +526,59 @@ def test_gemm_accumulate_split_k_matches_fp32(M, N, K):
     acc = torch.ones(M, N, device=DEV)
     tc.gemm_tn(a, b, out=acc, accumulate=True)
     assert _rel_err(acc, 1 + a.float() @ b.float().t()) < 2e-5
+
+
+@pytest.mark.parametrize("M,K,N", [(1000, 768, 3072), (257, 128, 256), (4096, 256, 64)])
+def test_gemm_gelu_epilogues_match_separate_kernels(M, K, N):
+    """ceb_gemm_bf16_tn_gelu: act 2 == GEMM followed by the GELU kernel (bit-exact: the activation is computed
+    from the rounded pre-activation); act 3 == GEMM then GELU backward within bf16 rounding; both vs fp32 torch."""
+    from commefficient_b200.ops import tfm
+    torch.manual_seed(M + N)
+    a = (torch.randn(M, K, device=DEV) * 0.5).bfloat16()
+    b = (torch.randn(N, K, device=DEV) * 0.05).bfloat16()
+    bias = torch.randn(N, device=DEV) * 0.1
+    pre, act = tc.gemm_tn_gelu(a, b, bias)
+    pre_ref = tc.gemm_tn(a, b, bias=bias)
+    assert torch.equal(pre, pre_ref)
+    assert torch.equal(act, tfm.gelu_tanh(pre_ref))
+    want = torch.nn.functional.gelu(a.float() @ b.float().t() + bias, approximate="tanh")
+    assert _rel_err(act, want) < 1e-2
+
+    g = (torch.randn(M, K, device=DEV) * 0.5).bfloat16()
+    d = tc.gemm_tn_gelu_grad(g, b, pre)
+    x = pre.float().requires_grad_(True)
+    torch.nn.functional.gelu(x, approximate="tanh").backward(g.float() @ b.float().t())
+    assert _rel_err(d, x.grad) < 1e-2
+
+
+def test_mlp_gelu_fused_matches_unfused():
+    """_MLPGeluFn (GELU inside the GEMM epilogues) against the linear -> gelu -> linear chain on the same kernels and
+    against fp32 torch: outputs and all five gradients."""
+    from commefficient_b200.ops import nn as nnops
+    torch.manual_seed(5)
+    E, rows = 256, 640
+    x = torch.randn(rows, E, device=DEV)
+    w_fc = torch.nn.Parameter(torch.randn(E, 4 * E, device=DEV) * 0.05)      # Conv1D storage [in, out]
+    b_fc = torch.nn.Parameter(torch.randn(4 * E, device=DEV) * 0.1)
+    w_pr = torch.nn.Parameter(torch.randn(4 * E, E, device=DEV) * 0.05)
+    b_pr = torch.nn.Parameter(torch.randn(E, device=DEV) * 0.1)
+    dy = torch.randn(rows, E, device=DEV)
+    params = (w_fc, b_fc, w_pr, b_pr)
+
+    def run(fn):
+        for p in params:
+            p.grad = None
+        xi = x.clone().requires_grad_(True)
+        y = fn(xi)
+        y.float().backward(dy)
+        return [y.float(), xi.grad.float()] + [p.grad.float().clone() for p in params]
+
+    nnops.set_native(True)
+    nnops.set_precision("bf16")
+    assert tc.mlp_gelu_supported(x, w_fc.t(), w_pr.t())
+    fused = run(lambda xi: nnops.mlp_gelu(xi, w_fc.t(), b_fc, w_pr.t(), b_pr))
+    chain = run(lambda xi: nnops.linear(nnops.gelu_tanh(nnops.linear(xi, w_fc.t(), b_fc)), w_pr.t(), b_pr))
+    ref = run(lambda xi: torch.nn.functional.gelu(xi @ w_fc + b_fc, approximate="tanh") @ w_pr + b_pr)
+    for f, c, r in zip(fused, chain, ref):
+        assert _rel_err(f, c) < 5e-3
+        assert _rel_err(f, r) < 2e-2
