@@ -269,6 +269,21 @@ _finish_client_grad.noise_calls = 0
 
 
 # ----------------------------------------------------------------------------- the per-rank worker
+def _client_aligned_chunks(sizes, limit):
+    """``[(lo, hi), ...]`` sample ranges of at most ``limit`` samples that never split a client (a client larger
+    than the limit gets a chunk of its own): losses that normalise per client (mean over a client's tokens,
+    gpt2_train.py:78-97 in the reference) see every client whole."""
+    out, lo, n = [], 0, 0
+    for sz in sizes:
+        if n and n + sz > limit:
+            out.append((lo, lo + n))
+            lo, n = lo + n, 0
+        n += sz
+    if n:
+        out.append((lo, lo + n))
+    return out
+
+
 class ClientWorker:
     """Owns this rank's model replica (flat buffers), client-state stores and the
     rank-local transmit accumulator."""
@@ -449,7 +464,8 @@ class ClientWorker:
         # on a second stream: the accumulate is L2-atomic bound, the backward tensor-pipe bound.
         early = []
         side = None
-        single_chunk = total <= self.MAX_BATCHED_SAMPLES
+        chunks = _client_aligned_chunks(sizes, self.MAX_BATCHED_SAMPLES)
+        single_chunk = len(chunks) <= 1
         if (a.mode == "sketch" and self.device.type == "cuda" and single_chunk
                 and not getattr(a, "p2", 0) and not getattr(a, "no_sketch_overlap", False)):
             side = self._side_stream()
@@ -462,8 +478,8 @@ class ClientWorker:
                                         wd=wd_total)
                 early.append((lo, hi))
             fp.on_range_final = on_final
-        for lo in range(0, total, self.MAX_BATCHED_SAMPLES):
-            chunk = [t[lo:lo + self.MAX_BATCHED_SAMPLES] for t in cat]
+        for lo, hi in chunks:
+            chunk = [t[lo:hi] for t in cat]
             from .ops import nn as nnops
             equal = len(set(sizes)) == 1 and self.device.type != "cuda"   # (CUDA: seg ids feed the native kernels)
             bn_ctx = (nnops.bn_segments(0) if not self.has_bn else
@@ -476,7 +492,7 @@ class ClientWorker:
                     # get the client index of every sample and return values v_s with
                     # sum_{s in client i} v_s = n_i * loss_i
                     loss_vec, *metric_vecs = self.compute_loss_train.per_sample(
-                        self.model, chunk, a, seg=seg[lo:lo + self.MAX_BATCHED_SAMPLES], num_segments=len(sizes))
+                        self.model, chunk, a, seg=seg[lo:hi], num_segments=len(sizes))
                 else:
                     loss_vec, *metric_vecs = self.compute_loss_train.per_sample(self.model, chunk, a)
             loss_vec.float().sum().backward()

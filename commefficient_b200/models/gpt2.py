@@ -50,6 +50,7 @@ class GPT2Config:
     layer_norm_epsilon: float = 1e-5
     initializer_range: float = 0.02
     summary_first_dropout: float = 0.1
+    post_ln: bool = False          # GPT-1 block order: x = ln_1(x + attn(x)); x = ln_2(x + mlp(x)); no final LayerNorm
 
     def to_json_file(self, path):
         with open(path, "w") as f:
@@ -119,8 +120,11 @@ class Block(nn.Module):
         self.ln_2 = nn.LayerNorm(cfg.n_embd, eps=cfg.layer_norm_epsilon)
         self.mlp = MLP(cfg)
 
-    def forward(self, x):
+    def forward(self, x, post_ln=False):
         ln1, ln2 = self.ln_1, self.ln_2
+        if post_ln:                                                   # GPT-1 order
+            x = nnops.layer_norm(x + self.attn(x), ln1.weight, ln1.bias, ln1.eps)
+            return nnops.layer_norm(x + self.mlp(x), ln2.weight, ln2.bias, ln2.eps)
         x = x + self.attn(nnops.layer_norm(x, ln1.weight, ln1.bias, ln1.eps))
         return x + self.mlp(nnops.layer_norm(x, ln2.weight, ln2.bias, ln2.eps))
 
@@ -132,7 +136,9 @@ class GPT2Model(nn.Module):
         self.wpe = nn.Embedding(cfg.n_positions, cfg.n_embd)
         self.drop = nn.Dropout(cfg.embd_pdrop)
         self.h = nn.ModuleList([Block(cfg) for _ in range(cfg.n_layer)])
-        self.ln_f = nn.LayerNorm(cfg.n_embd, eps=cfg.layer_norm_epsilon)
+        self.post_ln = bool(getattr(cfg, "post_ln", False))
+        if not self.post_ln:
+            self.ln_f = nn.LayerNorm(cfg.n_embd, eps=cfg.layer_norm_epsilon)
         nn.init.normal_(self.wte.weight, 0.0, cfg.initializer_range)
         nn.init.normal_(self.wpe.weight, 0.0, cfg.initializer_range)
 
@@ -150,6 +156,18 @@ class GPT2Model(nn.Module):
         # x + attn(ln_1(x)) feeds ln_2 of the same block, x + mlp(ln_2(x)) feeds ln_1 of the next block
         # (or ln_f after the last one).
         blocks = list(self.h)
+        if self.post_ln:
+            # GPT-1 (OpenAIGPTDoubleHeadsModel): the LayerNorm FOLLOWS each residual add and its output is the
+            # stream; the same fused add + LayerNorm kernel serves, its normalised output is what is carried on
+            for i, block in enumerate(blocks):
+                pr = block.attn.resid_dropout.p if fused else 0.0
+                _, x = nnops.add_layer_norm(x, block.attn(x, salt=16 * i + 2, fuse_resid_dropout=fused),
+                                            block.ln_1.weight, block.ln_1.bias, block.ln_1.eps, p_drop=pr, salt=16 * i + 3)
+                pr = block.mlp.dropout.p if fused else 0.0
+                _, h = nnops.add_layer_norm(x.float(), block.mlp(x, fuse_resid_dropout=fused), block.ln_2.weight,
+                                            block.ln_2.bias, block.ln_2.eps, p_drop=pr, salt=16 * i + 4)
+                x = h.float() if i + 1 < len(blocks) else h
+            return x
         first = blocks[0].ln_1 if blocks else self.ln_f
         h = nnops.layer_norm(x, first.weight, first.bias, first.eps)
         report = (flat_params is not None and flat_params.on_range_final is not None and torch.is_grad_enabled()
@@ -314,8 +332,10 @@ def shifted_lm_rows(lm_logits, lm_labels):
 
 class OpenAIGPTDoubleHeadsModel(GPT2DoubleHeadsModel):
     """The reference falls back to the GPT-1 class when ``--model_checkpoint`` does not
-    contain "gpt2" (gpt2_train.py:263-268).  Same double-head interface; the GPT-1
-    sizes (40 478 BPE tokens, 512 positions) are the defaults."""
+    contain "gpt2" (gpt2_train.py:263-268).  Same double-head interface; GPT-1's architecture: 40 478 BPE
+    tokens, 512 positions, LayerNorm AFTER each residual add (``post_ln``) and no final LayerNorm."""
 
     def __init__(self, config: Optional[GPT2Config] = None):
-        super().__init__(config or GPT2Config(vocab_size=40478, n_positions=512, n_ctx=512))
+        config = config or GPT2Config(vocab_size=40478, n_positions=512, n_ctx=512, post_ln=True)
+        config.post_ln = True
+        super().__init__(config)

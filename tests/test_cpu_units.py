@@ -223,3 +223,20 @@ def test_gpt2_label_sparse_loss_equals_full_logits_loss():
     torch.testing.assert_close(sparse[1], full[1])
     rows, mask = m.lm_rows(sparse[-1], labels)
     assert int(mask.sum()) == 3 * 7 and bool((rows[~mask] == 0).all())      # labels 9..15 -> 7 scored positions
+
+
+def test_batched_chunks_never_split_a_client():
+    """Chunking of a large batched round (ClientWorker.MAX_BATCHED_SAMPLES) keeps every client whole, so losses
+    normalised per client (the reference's per-client token mean, gpt2_train.py:78-97) are unaffected."""
+    from commefficient_b200.fed_worker import _client_aligned_chunks as chunks
+    assert chunks((3, 3, 3, 3), 6) == [(0, 6), (6, 12)]
+    assert chunks((10, 2, 2), 4) == [(0, 10), (10, 14)]          # an oversized client stays whole
+    assert chunks((5,), 100) == [(0, 5)] and chunks((), 4) == []
+    sizes = (7, 1, 4, 4, 9, 2, 2, 2)
+    got = chunks(sizes, 8)
+    bounds = {0}
+    for s in sizes:
+        bounds.add(max(bounds) + s)
+    assert got[0][0] == 0 and got[-1][1] == sum(sizes)
+    assert all(a[1] == b[0] for a, b in zip(got, got[1:]))
+    assert all(lo in bounds and hi in bounds for lo, hi in got)
