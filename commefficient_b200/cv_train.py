@@ -263,6 +263,8 @@ def main(argv=None):
         args.num_clients = train_loader.dataset.num_clients
     base_opt = torch.optim.SGD(groups, lr=1)
     fed_model = FedModel(model, compute_loss_train, args, compute_loss_val)
+    # each rank's loader decodes / augments only the clients that rank simulates
+    fed_model.attach_sampler(train_loader.batch_sampler)
     opt = FedOptimizer(base_opt, args)
     if args.resume:
         fed_model.load_fedstate(args.resume, opt)

@@ -2,25 +2,55 @@
 and takes up to ``local_batch_size`` samples from each (all remaining samples when
 ``local_batch_size == -1``); an epoch ends when every client is exhausted.
 
-Semantics of /root/reference/CommEfficient/data_utils/fed_sampler.py:5-71.  Two
-additions used by the SPMD runtime: an explicit ``seed`` (every rank constructs
-the identical schedule without communication) and ``plan_round`` which exposes
-the (client, count) structure of a round without materialising sample indices.
+Semantics of /root/reference/CommEfficient/data_utils/fed_sampler.py:5-71.  Additions used by the SPMD
+runtime:
+
+  * an explicit ``seed``: every rank constructs the identical schedule without communication;
+  * ``rank`` / ``world_size``: a rank's loader only LOADS the samples of the clients that rank will simulate
+    (the reference has one loader in one process; with one process per GPU an unsharded loader would decode
+    and augment the whole round N times).  The schedule itself -- which clients, how many samples each --
+    is still computed in full on every rank (index arithmetic only) and handed to the aggregator through
+    ``rounds``, a FIFO with one ``RoundMeta`` per yielded batch, so no collective is needed to learn the
+    other ranks' client ids and sample counts.
 """
 from __future__ import annotations
 
+from collections import deque
+from typing import List, NamedTuple
+
 import numpy as np
 
-__all__ = ["FedSampler"]
+__all__ = ["FedSampler", "RoundMeta", "assign_clients"]
+
+
+def assign_clients(unique_sorted: np.ndarray, world_size: int, by_owner: bool) -> List[np.ndarray]:
+    """Clients (ascending ids) -> ranks.  ``by_owner``: a client always runs on the rank that owns its
+    per-client state rows (id mod world size); otherwise contiguous balanced chunks.  Every client is
+    processed (the reference drops W mod P clients, quirk Q1)."""
+    unique_sorted = np.asarray(unique_sorted, dtype=np.int64)
+    if by_owner:
+        return [unique_sorted[unique_sorted % world_size == r] for r in range(world_size)]
+    return [np.asarray(c, dtype=np.int64) for c in np.array_split(unique_sorted, world_size)]
+
+
+class RoundMeta(NamedTuple):
+    ids: np.ndarray        # the round's client ids, ascending
+    counts: np.ndarray     # samples taken from each of them
+    sharded: bool          # the yielded batch holds only this rank's clients (else: the whole round)
 
 
 class FedSampler:
-    def __init__(self, dataset, num_workers, local_batch_size, shuffle_clients=True, seed=None):
+    def __init__(self, dataset, num_workers, local_batch_size, shuffle_clients=True, seed=None, rank=0,
+                 world_size=1, by_owner=False):
         self.dataset = dataset
         self.num_workers = int(num_workers)
         self.local_batch_size = int(local_batch_size)
         self.shuffle_clients = shuffle_clients
         self.seed = seed
+        self.rank, self.world_size, self.by_owner = int(rank), int(world_size), bool(by_owner)
+        if self.world_size > 1 and seed is None:
+            raise ValueError("a rank-sharded FedSampler needs a seed (all ranks must draw the same schedule)")
+        self.rounds: "deque[RoundMeta]" = deque()
         self._epoch = 0
 
     def _rng(self):
@@ -32,6 +62,7 @@ class FedSampler:
     def __iter__(self):
         rng = self._rng()
         self._epoch += 1
+        self.rounds.clear()          # batches prefetched by an abandoned iterator are gone with it
         per_client = np.asarray(self.dataset.data_per_client, dtype=np.int64)
         starts = np.concatenate([[0], np.cumsum(per_client)[:-1]])
         # shuffled order of each client's samples, laid out client after client
@@ -45,8 +76,19 @@ class FedSampler:
             chosen = rng.choice(alive, min(self.num_workers, alive.size), replace=False)
             left = per_client[chosen] - used[chosen]
             take = left if self.local_batch_size == -1 else np.minimum(left, self.local_batch_size)
-            batch = np.concatenate([order[starts[c] + used[c]: starts[c] + used[c] + t]
-                                    for c, t in zip(chosen, take)])
+            if self.world_size > 1:
+                by_id = np.argsort(chosen, kind="stable")
+                ids, counts = chosen[by_id], take[by_id]
+                parts = assign_clients(ids, self.world_size, self.by_owner)
+                sharded = all(len(p) for p in parts)     # a rank without clients still needs a non-empty batch
+                self.rounds.append(RoundMeta(ids, counts, sharded))
+                mine = parts[self.rank] if sharded else ids
+                sel = np.searchsorted(ids, mine)
+                batch = np.concatenate([order[starts[c] + used[c]: starts[c] + used[c] + t]
+                                        for c, t in zip(ids[sel], counts[sel])])
+            else:
+                batch = np.concatenate([order[starts[c] + used[c]: starts[c] + used[c] + t]
+                                        for c, t in zip(chosen, take)])
             used[chosen] += take
             yield batch
 

@@ -28,6 +28,7 @@ import numpy as np
 import torch
 
 from . import fed_worker as worker
+from .data_utils.fed_sampler import assign_clients
 from .ops import dense as dn
 from .ops import sketch as sk
 from .ops.topk import topk_sparse
@@ -299,6 +300,7 @@ class FedModel:
         self._fault = parse_fault()
         self._result_ring = {}
         self._copy_stream = None
+        self.round_source = None          # a rank-sharded FedSampler (attach_sampler)
         self.tracer = PhaseTracer(getattr(args, "trace_phases", "") or "", getattr(args, "trace_every", 50),
                                   self.rt.rank, self._trace_max, self.device.type)
         _CURRENT = self
@@ -357,11 +359,19 @@ class FedModel:
         """Clients -> ranks.  With per-client state a client always runs on the rank that
         owns its rows (client id mod world size); otherwise contiguous balanced chunks.
         Every client is processed (the reference drops W mod P clients, quirk Q1)."""
-        ws = self.rt.world_size
+        return assign_clients(unique, self.rt.world_size, self._by_owner())
+
+    def _by_owner(self) -> bool:
         w = self.worker
-        if w.velocities is not None or w.errors is not None or w.client_weights is not None:
-            return [unique[unique % ws == r] for r in range(ws)]
-        return [np.asarray(c, dtype=np.int64) for c in np.array_split(unique, ws)]
+        return w.velocities is not None or w.errors is not None or w.client_weights is not None
+
+    def attach_sampler(self, sampler) -> None:
+        """Tell the model that its training batches come from a rank-sharded ``FedSampler`` (one whose loader
+        only materialises this rank's clients): the round's global client ids / sample counts are then read
+        from ``sampler.rounds`` instead of from the batch.  Call before the first iteration."""
+        sampler.rank, sampler.world_size = self.rt.rank, self.rt.world_size
+        sampler.by_owner = self._by_owner()
+        self.round_source = sampler if self.rt.world_size > 1 else None
 
     def _to_device(self, t: torch.Tensor) -> torch.Tensor:
         """Inputs from pinned host memory are copied on a dedicated stream, so the transfer of round t+1
@@ -397,14 +407,30 @@ class FedModel:
             order = np.argsort(inverse, kind="stable")
             counts = np.bincount(inverse, minlength=len(unique))
             starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
-        mine = self._assign(unique)[self.rt.rank]
+        # rows of `starts` / `counts` (this batch's clients) that this rank simulates, and the round as a whole
+        total_samples = int(ids.shape[0])
+        meta = None
+        if getattr(self, "round_source", None) is not None:
+            if not self.round_source.rounds:
+                raise RuntimeError("attach_sampler: the sampler has no pending round for this batch")
+            meta = self.round_source.rounds.popleft()
+        if meta is not None and meta.sharded:
+            # the loader produced only this rank's clients; the schedule gives the rest of the round
+            mine = self._assign(meta.ids)[self.rt.rank]
+            if not np.array_equal(np.sort(unique), mine):
+                raise RuntimeError("rank-sharded batch does not hold the clients assigned to rank %d" % self.rt.rank)
+            local_unique, unique = unique, meta.ids
+            total_samples = int(meta.counts.sum())
+            pos = np.searchsorted(local_unique, mine)
+        else:
+            mine = self._assign(unique)[self.rt.rank]
+            pos = np.searchsorted(unique, mine)
         cols = batch[1:]
         client_batches = worker.ClientBatches()
         tr = self.tracer
         h2d_phase = tr.phase("h2d")
         h2d_phase.__enter__()
         if len(mine):
-            pos = np.searchsorted(unique, mine)
             if sorted_already and int(pos[-1] - pos[0]) + 1 == len(pos):
                 # this rank's clients are one contiguous run of samples: slice (views of the
                 # caller's -- ideally pinned -- tensors), then one async H2D per column
@@ -429,7 +455,7 @@ class FedModel:
         else:
             with tr.phase("reduce"):
                 self.rt.all_reduce_sum_(self.worker.transmit)
-        self.pending_samples = int(ids.shape[0])
+        self.pending_samples = total_samples
         self.last_unique_clients = unique
         self.rounds += 1
 

@@ -266,6 +266,7 @@ def train(argv=None):
         args.num_clients = train_loader.dataset.num_clients
 
     fed_model = FedModel(model, compute_loss_train, args, compute_loss_val)
+    fed_model.attach_sampler(train_loader.batch_sampler)      # a rank's loader tokenises only its own clients
     fed_opt = FedOptimizer(optimizer, args)
     if args.resume:
         fed_model.load_fedstate(args.resume, fed_opt)

@@ -302,3 +302,80 @@ def test_dp_noise_differs_across_ranks_and_rounds():
     assert float((a - b).std()) == pytest.approx(2 ** 0.5, rel=0.1)      # the difference does not cancel
     seeds = {fed_worker.noise_seed(5, c, r) for c in range(50) for r in range(50)}
     assert len(seeds) == 2500
+
+
+# ------------------------------------------------------------------ rank-sharded data loading
+class _CountingClients(torch.utils.data.Dataset):
+    """12 clients x 5 samples of 3x32x32 noise; remembers which samples were actually loaded."""
+
+    def __init__(self):
+        g = torch.Generator().manual_seed(7)
+        self.data_per_client = [5] * 12
+        self.num_clients = 12
+        self.x = torch.randn(60, 3, 32, 32, generator=g)
+        self.y = torch.randint(0, 10, (60,), generator=g)
+        self.loaded = []
+
+    def __len__(self):
+        return 60
+
+    def __getitem__(self, i):
+        i = int(i)
+        self.loaded.append(i)
+        return i // 5, self.x[i], self.y[i]
+
+
+def _sharded_loader_run(device, backend, attach):
+    from torch.utils.data import DataLoader
+    from commefficient_b200 import models
+    from commefficient_b200.cv_train import compute_loss_train, compute_loss_val
+    from commefficient_b200.data_utils import FedSampler
+    from commefficient_b200.fed_aggregator import FedModel, FedOptimizer
+    from commefficient_b200.utils import make_args
+    torch.manual_seed(0)
+    args = make_args(mode="sketch", num_workers=4, num_clients=12, local_batch_size=3, k=300, num_cols=4000, num_rows=5,
+                     num_blocks=4, device=device, dataset_name="CIFAR10", precision="fp32", weight_decay=5e-4,
+                     local_momentum=0.0, virtual_momentum=0.9, flat_layout="reference", backend=backend,
+                     error_type="virtual")
+    model = models.ResNet9(num_classes=10, channels=SMALL, do_batchnorm=False)
+    fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+    opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+    opt.param_groups[0]["lr"] = 0.05
+    ds = _CountingClients()
+    sampler = FedSampler(ds, args.num_workers, args.local_batch_size, seed=3)
+    loader = DataLoader(ds, batch_sampler=sampler, num_workers=0)
+    if attach:
+        fed.attach_sampler(sampler)
+    losses, rounds = [], 0
+    fed.train(True)
+    for batch in loader:
+        out = fed(batch)
+        opt.step()
+        losses.append(sorted(float(x) for x in out[0]))
+        rounds += 1
+    w = fed.fp.to_reference_order(fed.fp.flat).detach().cpu()
+    return w, losses, sorted(ds.loaded), fed
+
+
+def _sharded_rank_main(rank, world, out_dir):
+    rt = runtime.init_runtime(rank=rank, world_size=world, device="cpu", backend="gloo")
+    w, losses, loaded, _fed = _sharded_loader_run("cpu", "gloo", attach=True)
+    torch.save({"w": w, "losses": losses, "loaded": loaded}, os.path.join(out_dir, "r%d.pt" % rank))
+    rt.shutdown()
+
+
+def test_rank_sharded_loader_loads_each_sample_once_and_matches_single_rank():
+    """With ``attach_sampler`` each rank's DataLoader materialises only its own clients (the two ranks' loaded
+    sets partition the epoch) and the run equals the single-rank one."""
+    out_dir = tempfile.mkdtemp()
+    runtime.spawn(_sharded_rank_main, 2, args=(out_dir,), device="cpu")
+    r0, r1 = (torch.load(os.path.join(out_dir, "r%d.pt" % r)) for r in range(2))
+    torch.testing.assert_close(r0["w"], r1["w"], rtol=0, atol=0)
+    assert r0["losses"] == r1["losses"]
+    assert sorted(r0["loaded"] + r1["loaded"]) == list(range(60)), "every sample loaded by exactly one rank"
+    assert 20 <= len(r0["loaded"]) <= 40
+    w1, l1, loaded1, fed = _sharded_loader_run("cpu", "auto", attach=False)
+    fed.rt.shutdown()
+    assert loaded1 == list(range(60))
+    np.testing.assert_allclose(r0["losses"], l1, rtol=1e-4, atol=1e-5)
+    assert (r0["w"] - w1).norm() / w1.norm() < 1e-3
