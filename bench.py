@@ -56,6 +56,8 @@ def parse():
                          "of --defer_results")
     ap.add_argument("--no_cuda_graphs", action="store_true",
                     help="launch the round's kernels one by one (for ncu launch lists; a graph replay hides them)")
+    ap.add_argument("--client_lanes", type=int, default=int(os.environ.get("CEB_CLIENT_LANES", "8")),
+                    help="per-client modes: clients simulated concurrently per GPU (model replicas on their own streams)")
     ap.add_argument("--clients_per_gpu", type=int, default=0, help="override the configuration's clients per GPU")
     ap.add_argument("--phases", action="store_true", help="also print a per-phase breakdown to stderr")
     ap.add_argument("--profile", action="store_true",
@@ -235,7 +237,7 @@ def run_ours(cfg):
         args = make_args(num_workers=clients, num_clients=bc["num_clients"],
                          local_batch_size=bc["per_client"] if gpt2 else -1, num_epochs=1.0, dataset_name=bc["dataset"],
                          device="cuda", precision=precision, backend=cfg.backend, model=bc["model"],
-                         no_native_nn=cfg.no_native_nn, no_cuda_graphs=cfg.no_cuda_graphs,
+                         no_native_nn=cfg.no_native_nn, no_cuda_graphs=cfg.no_cuda_graphs, client_lanes=cfg.client_lanes,
                          defer_results=not cfg.sync_results, num_results_train=1 if gpt2 else 2, **flags)
         rt = init_runtime(args)
         torch.manual_seed(args.seed)

@@ -388,11 +388,79 @@ class ClientWorker:
         self.model.train()
         if self.args.do_test:
             return self._round_test(client_batches)
-        if self.args.mode == "fedavg":
-            return self._round_fedavg(client_batches, fedavg_lr)
-        if self.can_batch_clients(client_batches.sizes):
+        if self.args.mode != "fedavg" and self.can_batch_clients(client_batches.sizes):
             return self._round_batched(client_batches)
-        return torch.stack([self._one_client(cid, batch) for cid, batch in client_batches])
+        return self._round_per_client(client_batches, fedavg_lr)
+
+    # -- per-client modes: concurrent lanes ------------------------------------------------
+    def _make_lane(self):
+        """A replica of this worker for one more concurrent client: its own model copy, flat weight / gradient
+        buffers, transmit accumulator, graph cache and stream; the per-client state stores, the sketch plan and
+        the arguments are shared.  BatchNorm running statistics are advanced by lane 0 only (the reference
+        never federates them -- SURVEY Q12 -- so they are an average over whichever clients pass through)."""
+        import copy
+        fp0 = self.model.__dict__.pop("_flat_params", None)
+        try:
+            model = copy.deepcopy(self.model)
+        finally:
+            if fp0 is not None:
+                self.model._flat_params = fp0
+        for m in model.modules():
+            if isinstance(m, torch.nn.modules.batchnorm._BatchNorm):
+                m.momentum = 0.0
+        lane = copy.copy(self)
+        lane.model = model
+        lane.fp = FlatParams(model, self.device, layout=self.fp.layout)
+        model._flat_params = lane.fp
+        lane.peer = lane.weights_buf = lane.transmit_buf = None
+        lane.transmit = torch.zeros(self.transmit_shape, dtype=torch.float32, device=self.device)
+        lane._tmp_table = lane._ps_copy = None
+        lane._graphs = graphs.GraphCache()
+        lane._lane_list = None
+        lane.stream = torch.cuda.Stream(device=self.device)
+        return lane
+
+    def _lanes(self, n_clients: int):
+        want = 1
+        if self.device.type == "cuda":
+            want = max(1, min(int(getattr(self.args, "client_lanes", 1) or 1), n_clients))
+        lanes = getattr(self, "_lane_list", None) or [self]
+        while len(lanes) < want:
+            lanes.append(self._make_lane())
+        self._lane_list = lanes
+        return lanes[:want]
+
+    def _round_per_client(self, client_batches, fedavg_lr: float = 0.0):
+        """One backward per client (the modes that are not linear in the client gradients: local top-k, local
+        momentum / error, clipping, DP noise, stale weights, FedAvg's local SGD -- reference
+        fed_worker.py:61-113,184-230).  The clients of a round are independent, and one client's kernels are far
+        too small to fill 148 SMs, so up to ``--client_lanes`` of them run at the same time, each on its own
+        model replica and stream; the lanes' uploads are summed when the streams join."""
+        fedavg = self.args.mode == "fedavg"
+        lanes = self._lanes(len(client_batches))
+        if len(lanes) == 1:
+            run = (lambda c, b: self._fedavg_client(c, b, fedavg_lr)) if fedavg else self._one_client
+            return torch.stack([run(cid, batch) for cid, batch in client_batches])
+        main = torch.cuda.current_stream(self.device)
+        for lane in lanes[1:]:
+            lane.stream.wait_stream(main)
+            with torch.cuda.stream(lane.stream):
+                lane.fp.flat.copy_(self.fp.flat, non_blocking=True)
+                lane.transmit.zero_()
+            lane.round_no = self.round_no
+            lane.model.train()
+        out = [None] * len(client_batches)
+        for i, (cid, batch) in enumerate(client_batches):
+            lane = lanes[i % len(lanes)]
+            if lane is self:
+                out[i] = self._fedavg_client(cid, batch, fedavg_lr) if fedavg else self._one_client(cid, batch)
+            else:
+                with torch.cuda.stream(lane.stream):
+                    out[i] = lane._fedavg_client(cid, batch, fedavg_lr) if fedavg else lane._one_client(cid, batch)
+        for lane in lanes[1:]:
+            main.wait_stream(lane.stream)
+            self.transmit.add_(lane.transmit)
+        return torch.stack(out)
 
     def _round_test(self, client_batches):
         """``--test`` smoke mode: every client transmits an all-ones gradient
@@ -611,29 +679,29 @@ class ClientWorker:
             fp.flat.copy_(self._ps_copy)
         return results
 
-    def _round_fedavg(self, client_batches, lr: float):
-        """Local SGD per client (fed_worker.py:61-113): ``num_fedavg_epochs`` passes over
+    def _fedavg_client(self, cid, batch, lr: float):
+        """Local SGD of one client (fed_worker.py:61-113): ``num_fedavg_epochs`` passes over
         the client's data in chunks of ``fedavg_batch_size``, step size
         ``lr * fedavg_lr_decay**step``; the client uploads ``(w - w_local) * n_i``."""
         a, fp = self.args, self.fp
-        w0 = fp.flat.clone()
-        out = []
-        for cid, batch in client_batches:
-            n_i = batch[0].shape[0]
-            bs = n_i if a.fedavg_batch_size == -1 else a.fedavg_batch_size
-            batch = self._prep(batch)
-            chunks = [[t[lo:lo + bs] for t in batch] for lo in range(0, n_i, bs)]
-            step, acc = 0, None
-            for _epoch in range(a.num_fedavg_epochs):
-                for chunk in chunks:
-                    res = self._client_backward(chunk, noise_key=(cid, self.round_no * 4096 + step))
-                    fp.flat.add_(fp.grad, alpha=-float(lr) * a.fedavg_lr_decay ** step)
-                    acc = res if acc is None else acc + res
-                    step += 1
-            out.append(acc / max(1, step))
-            dn.fedavg_delta(self.transmit, w0, fp.flat, float(n_i))
-            fp.flat.copy_(w0)
-        return torch.stack(out)
+        if self._ps_copy is None:
+            self._ps_copy = torch.empty_like(fp.flat)
+        w0 = self._ps_copy
+        w0.copy_(fp.flat)
+        n_i = batch[0].shape[0]
+        bs = n_i if a.fedavg_batch_size == -1 else a.fedavg_batch_size
+        batch = self._prep(batch)
+        chunks = [[t[lo:lo + bs] for t in batch] for lo in range(0, n_i, bs)]
+        step, acc = 0, None
+        for _epoch in range(a.num_fedavg_epochs):
+            for chunk in chunks:
+                res = self._client_backward(chunk, noise_key=(cid, self.round_no * 4096 + step))
+                fp.flat.add_(fp.grad, alpha=-float(lr) * a.fedavg_lr_decay ** step)
+                acc = res if acc is None else acc + res
+                step += 1
+        dn.fedavg_delta(self.transmit, w0, fp.flat, float(n_i))
+        fp.flat.copy_(w0)
+        return acc / max(1, step)
 
     # -- validation ------------------------------------------------------------------
     def run_val(self, shards: List[List[torch.Tensor]]):

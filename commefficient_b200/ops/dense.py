@@ -144,7 +144,7 @@ def clip_by_norm(x: torch.Tensor, clip: float, eps: float = 0.0) -> None:
         if coef != 1.0:
             x.mul_(coef)
         return
-    key = x.device.index
+    key = (x.device.index, torch.cuda.current_stream(x.device).cuda_stream)    # (concurrent client lanes)
     buf = _sumsq_cache.get(key)
     if buf is None:
         buf = torch.zeros(1, dtype=torch.float32, device=x.device)

@@ -127,6 +127,9 @@ _FLAGS = [
               help="reproduce reference Q3: local momentum/error never persist on GPU"),
         _flag("no_client_batching", store_true=True,
               help="always run one backward per client (disables the linearity fast path)"),
+        _flag("client_lanes", 8, int,
+              help="per-client modes (local_topk, fedavg, clipping, DP, topk_down): number of clients simulated "
+                   "concurrently, each on its own model replica and CUDA stream (1 = one after the other)"),
         _flag("resume", None, str, help="path of a *.fedstate.pt sidecar to resume from"),
         _flag("watchdog_timeout", 600.0, float, help="seconds before a hung round aborts all ranks"),
         _flag("flat_layout", "auto", str, choices=("auto", "reference", "nhwc"),

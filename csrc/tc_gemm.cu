@@ -691,7 +691,14 @@ static bool use_pair(int mode, int M, int N, int bn, int rows_per_cta_tile, int 
   return k_steps >= 4;
 }
 
-static int pick_bn(int N) { return N <= 64 ? 64 : (N <= 128 ? 128 : 256); }
+// Widest tile that covers N -- unless the problem has so few row tiles that wide tiles would leave most SMs idle
+// (one client's 8 images through a 512-channel layer: 1 row tile; every CTA then streams its whole slice of the
+// weight matrix at one SM's L2 bandwidth, ~40 us with two 256-wide tiles): narrower tiles spread that read.
+static int pick_bn(int N, int64_t m_tiles = 1 << 20) {
+  int bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+  while (bn > 64 && m_tiles * ceb_cdiv(N, bn) * 2 <= ceb_num_sms()) bn >>= 1;
+  return bn;
+}
 
 template <int TF>
 static int dispatch_tile_t(int bn, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st,
@@ -770,7 +777,7 @@ static int gemm_tn_impl(const void* A, int64_t lda, const void* B, int64_t ldb, 
   CEB_REQUIRE(ldc >= N && ldc % (out_mode == 0 ? 8 : 4) == 0 && ldc < (1ll << 31),
               "ceb_gemm_tn: ldc=%lld must be >= N=%d and a multiple of %d", (long long)ldc, N, out_mode == 0 ? 8 : 4);
   CEB_REQUIRE((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0, "ceb_gemm_tn: operands must be 16-byte aligned");
-  const int bn = pick_bn(N);
+  const int bn = pick_bn(N, ceb_cdiv(M, BM));
   CUtensorMap ta, tb;
   uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * esz};
   uint32_t ba[2] = {(uint32_t)bke, BM};
@@ -906,7 +913,7 @@ static int conv_impl(const void* x, const void* w, void* y, int Nimg, int H, int
   if (tile_n < 1) tile_n = 1;
   if (tile_n > Nimg) tile_n = Nimg;
   const int tile_pix = tile_h * Wo * tile_n;
-  const int bn = pick_bn(Cout);
+  const int bn = pick_bn(Cout, ceb_cdiv((int64_t)Nimg * Ho * Wo, tile_pix));
   // halo mode: 3x3 / stride 1, 256-pixel tiles that stay inside one image, weights tile <= 128 wide
   static const bool force_v1 = getenv("CEB_CONV_V1") != nullptr;
   const int rows256 = (Wo > 0 && 256 % Wo == 0) ? 256 / Wo : 0;

@@ -210,3 +210,22 @@ def test_failed_capture_with_rng_ops_leaves_the_generator_usable():
     assert torch.isfinite(y).all()
     cap = graphs.try_capture("cuda", lambda: torch.randn(1000, device="cuda"), what="rng test 2")
     assert cap is not None and torch.isfinite(cap.replay()).all()
+
+
+@pytest.mark.parametrize("mode,kw", [
+    ("local_topk", {"error_type": "local", "local_momentum": 0.9}),
+    ("fedavg", {"num_fedavg_epochs": 2, "fedavg_batch_size": 3}),
+    ("sketch", {"max_grad_norm": 1.0}),
+    ("true_topk", {"do_topk_down": True}),
+    ("uncompressed", {"do_dp": True, "dp_mode": "worker", "l2_norm_clip": 1.0, "noise_multiplier": 0.01}),
+])
+@pytest.mark.parametrize("layout,precision", [("reference", "fp32"), ("auto", "tf32")])
+def test_concurrent_client_lanes_equal_sequential_clients(mode, kw, layout, precision):
+    """--client_lanes N (clients of a round on N model replicas / streams at once, graphs replayed per lane) gives
+    the round the one-after-the-other loop gives: same per-client losses, same weights up to the order of the
+    floating-point sum over clients.  Five rounds, so rounds 3-5 run from the per-lane CUDA graphs."""
+    seq_w, seq_l, seq_out = _run("cuda", mode, rounds=5, client_lanes=1, flat_layout=layout, precision=precision, **kw)
+    par_w, par_l, par_out = _run("cuda", mode, rounds=5, client_lanes=3, flat_layout=layout, precision=precision, **kw)
+    np.testing.assert_allclose(par_l, seq_l, rtol=2e-4, atol=1e-5)
+    np.testing.assert_allclose(np.asarray(par_out[0]), np.asarray(seq_out[0]), rtol=2e-4, atol=1e-5)
+    assert (par_w - seq_w).norm() / seq_w.norm() < 2e-4
