@@ -49,8 +49,18 @@ def main():
         t_nccl = timed(lambda: dist.all_reduce(x), rt)
         t_peer = timed(lambda: peer.all_reduce_buffer_(buf), rt)
         t_fused = timed(lambda: peer.fused_sketch(buf, gathered, Vv[lo:], gathered.tensor[lo:], 0.01, 0.9, "virtual"), rt)
+        variants = {}
+        if peer.nvls:      # both data paths on the same buffers: in-switch reduction + multicast vs peer loads / stores
+            default = peer.use_nvls
+            for name_v, flag in (("nvls", True), ("p2p", False)):
+                peer.use_nvls = flag
+                variants[name_v] = {
+                    "allreduce_us": timed(lambda: peer.all_reduce_buffer_(buf), rt),
+                    "fused_us": timed(lambda: peer.fused_sketch(buf, gathered, Vv[lo:], gathered.tensor[lo:], 0.01, 0.9,
+                                                                "virtual"), rt)}
+            peer.use_nvls = default
         sweep = {}
-        if W == 8:        # float4s in flight per thread and peer (CEB_PEER_U, read by the library at every launch)
+        if W == 8 and not peer.use_nvls:        # float4s in flight per thread and peer (CEB_PEER_U, read by the library at every launch)
             for u in (1, 2, 4):
                 os.environ["CEB_PEER_U"] = str(u)
                 sweep["U%d" % u] = timed(lambda: peer.fused_sketch(buf, gathered, Vv[lo:], gathered.tensor[lo:], 0.01, 0.9,
@@ -66,7 +76,8 @@ def main():
         t_unfused = timed(unfused, rt)
         ideal = 2 * (W - 1) / W * n * 4 / (LINK_GBS * 1e9) * 1e6
         rows.append({"buffer": name, "bytes": n * 4, "nccl_allreduce_us": t_nccl, "peer_allreduce_us": t_peer,
-                     "peer_fused_rs_update_ag_us": t_fused, "nccl_plus_update_us": t_unfused,
+                     "peer_fused_rs_update_ag_us": t_fused, "nvls_default": bool(peer.use_nvls), "variants": variants,
+                     "nccl_plus_update_us": t_unfused,
                      "ideal_us": ideal, "fused_fraction_of_roofline": ideal / t_fused, "fused_us_by_U": sweep})
         for b in (buf, gathered):
             b.close()

@@ -121,6 +121,49 @@ peer_rs_op_ag_kernel(CebPeerCtx c, int64_t lo, int64_t hi, Op op) {
   }
 }
 
+// NVLS variant: the reduce-scatter is ONE multimem.ld_reduce per 16 bytes (the switch adds the W copies and
+// returns the sum: this GPU receives 1/W of the bytes the peer-load version pulls), the all-gather ONE
+// multimem.st (the switch replicates the store into every rank's copy: 1/W of the bytes leave this GPU).
+// Same barriers, same Op functors, no dependence on W at compile time.
+template <class Op, int U, bool GATHER = true>
+__global__ void __launch_bounds__(kPeerThreads)
+peer_rs_op_ag_nvls_kernel(CebPeerCtx c, int64_t lo, int64_t hi, Op op) {
+  __shared__ bool is_last;
+  if (blockIdx.x == 0) peer_signal_all(c, 0);
+  peer_wait_all(c, 0);
+  const int64_t lane_step = (int64_t)blockDim.x * 4;
+  const int64_t stride = (int64_t)gridDim.x * lane_step * U;
+  for (int64_t base = lo + (int64_t)blockIdx.x * lane_step * U + (int64_t)threadIdx.x * 4; base < hi;
+       base += stride) {
+    float4 s[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = base + u * lane_step;
+      s[u] = i < hi ? multimem_ld_reduce_f4(c.mc_src + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = base + u * lane_step;
+      if (i >= hi) break;
+      const float4 out = op(i, s[u]);
+      if (GATHER) multimem_st_f4(c.mc_dst + i, out);
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = atomicAdd(c.ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+    if (is_last) *c.ticket = 0;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence_system();
+    peer_signal_all(c, 1);
+    peer_wait_all(c, 1);
+  }
+}
+
 template <class Op, bool GATHER = true>
 static void launch_peer(const CebPeerCtx& c, int64_t lo, int64_t hi, Op op, cudaStream_t st) {
   auto grid_for = [&](int U) {
@@ -129,6 +172,10 @@ static void launch_peer(const CebPeerCtx& c, int64_t lo, int64_t hi, Op op, cuda
     if (need < 1) need = 1;
     return (int)(need < cap ? need : cap);
   };
+  if (c.mc_src && (c.mc_dst || !GATHER)) {
+    peer_rs_op_ag_nvls_kernel<Op, 4, GATHER><<<grid_for(4), kPeerThreads, 0, st>>>(c, lo, hi, op);
+    return;
+  }
   // CEB_PEER_U=1|2|4 overrides the float4s in flight per thread and peer for the 8-rank kernels (A/B timing)
   int u8 = 1;
   if (c.world == 8) {
@@ -164,6 +211,7 @@ static int fill_ctx(CebPeerCtx& c, const void* const* src, const void* const* ds
   c.rank = rank;
   c.world = world;
   c.epoch = epoch;
+  c.mc_src = c.mc_dst = nullptr;
   return 0;
 }
 
@@ -182,14 +230,43 @@ CEB_API int64_t ceb_peer_shard_elems(int64_t n, int world) {
 // mode 1: sketch -- Vv,Ve shards updated, dst = Ve             (error_mode 0: dst = Vv)
 // mode 2: dense  -- Vv shard updated, dst (= weights) -= lr*Vv
 // mode 3: true_topk state -- Vv, Ve shards updated (Ve += Vv), nothing gathered (dst unused; pass src)
+static int fused_reduce_impl(int mode, const void* const* src, const void* const* dst, const void* const* flags,
+                             void* ticket, int rank, int world, unsigned int epoch, int64_t n, float* Vv_shard,
+                             float* Ve_shard, float inv_n, float rho, int error_mode, float lr, const float* lr_vec,
+                             void* mc_src, void* mc_dst, void* stream);
+
 CEB_API int ceb_peer_fused_reduce(int mode, const void* const* src, const void* const* dst,
                                   const void* const* flags, void* ticket, int rank, int world,
                                   unsigned int epoch, int64_t n, float* Vv_shard, float* Ve_shard,
                                   float inv_n, float rho, int error_mode, float lr, const float* lr_vec,
                                   void* stream) {
+  return fused_reduce_impl(mode, src, dst, flags, ticket, rank, world, epoch, n, Vv_shard, Ve_shard, inv_n, rho,
+                           error_mode, lr, lr_vec, nullptr, nullptr, stream);
+}
+
+// The same collective through the NVSwitch's multicast / in-switch reduction (NVLS): mc_src / mc_dst are the
+// multicast addresses of the buffers whose per-rank addresses are src[] / dst[] (both bound to a multicast
+// object spanning all `world` GPUs).  The flag barriers still run over the per-rank mappings.
+CEB_API int ceb_peer_fused_reduce_nvls(int mode, const void* const* src, const void* const* dst,
+                                       const void* const* flags, void* ticket, int rank, int world,
+                                       unsigned int epoch, int64_t n, float* Vv_shard, float* Ve_shard,
+                                       float inv_n, float rho, int error_mode, float lr, const float* lr_vec,
+                                       void* mc_src, void* mc_dst, void* stream) {
+  CEB_REQUIRE(mc_src && (mc_dst || mode == 3), "ceb_peer_fused_reduce_nvls: null multicast address");
+  CEB_REQUIRE(((((uintptr_t)mc_src) | ((uintptr_t)mc_dst)) & 15) == 0, "ceb_peer_fused_reduce_nvls: multicast addresses must be 16-byte aligned");
+  return fused_reduce_impl(mode, src, dst, flags, ticket, rank, world, epoch, n, Vv_shard, Ve_shard, inv_n, rho,
+                           error_mode, lr, lr_vec, mc_src, mc_dst, stream);
+}
+
+static int fused_reduce_impl(int mode, const void* const* src, const void* const* dst, const void* const* flags,
+                             void* ticket, int rank, int world, unsigned int epoch, int64_t n, float* Vv_shard,
+                             float* Ve_shard, float inv_n, float rho, int error_mode, float lr, const float* lr_vec,
+                             void* mc_src, void* mc_dst, void* stream) {
   CEB_REQUIRE(n > 0 && n % 4 == 0, "ceb_peer_fused_reduce: n=%lld must be a positive multiple of 4", (long long)n);
   CebPeerCtx c;
   if (int e = fill_ctx(c, src, dst, flags, ticket, rank, world, epoch)) return e;
+  c.mc_src = (float*)mc_src;
+  c.mc_dst = (float*)mc_dst;
   int64_t lo, hi;
   shard_bounds(n, rank, world, &lo, &hi);
   cudaStream_t st = (cudaStream_t)stream;

@@ -18,6 +18,11 @@ struct CebPeerCtx {
   uint32_t* ticket;             // local: finished-block counter; ticket[2] = error word (0 = fine)
   int rank, world;
   uint32_t epoch;
+  // NVLS: multicast addresses of the same two buffers (NULL when the buffers are not bound to a multicast
+  // object).  A multimem load through mc_src returns the SUM over all ranks' copies, reduced inside the
+  // NVSwitch; a multimem store through mc_dst lands in every rank's copy.
+  float* mc_src;
+  float* mc_dst;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -37,6 +42,17 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
 __device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
   asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
                ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
 // serial-number comparison so the 32-bit epoch may wrap

@@ -140,6 +140,30 @@ def _peer_kernel_main(rank, world, out_dir):
     peer.fused_dense(tr2, wb, Vv[lo:], 0.5, 0.9, 0.1)
     torch.cuda.synchronize()
     ok["dense_w"] = float((wb.tensor[:n] - w_ref).abs().max())
+    # the NVLS variant (multimem.ld_reduce / multimem.st through the switch) against the peer-load variant on the
+    # same buffers; where the box has no multicast support the group reports nvls = False and only the latter runs
+    ok["info_nvls"] = 1.0 if peer.nvls else 0.0
+    if peer.nvls:
+        assert tr2.mc_ptr and wb.mc_ptr
+        n = 100_003
+        src = torch.randn(n, device=dev, generator=gen)
+        w0 = torch.randn(n, device=dev, generator=g2)
+        v0 = torch.randn(peer.padded(n) + 4, device=dev, generator=g2)[:peer.padded(n)]
+        outs = []
+        default = peer.use_nvls
+        for use_nvls in (True, False):
+            peer.use_nvls = use_nvls
+            tr2.tensor[:n].copy_(src)
+            wb.tensor[:n].copy_(w0)
+            Vv = v0.clone()
+            torch.cuda.synchronize()
+            torch.distributed.barrier()
+            peer.fused_dense(tr2, wb, Vv[lo:], 0.5, 0.9, 0.1)
+            torch.cuda.synchronize()
+            torch.distributed.barrier()
+            outs.append(wb.tensor[:n].clone())
+        peer.use_nvls = default
+        ok["nvls_vs_p2p_dense"] = float((outs[0] - outs[1]).abs().max())
     # distributed exact top-k over per-rank slices (with ties at the threshold) against the single-GPU select
     from commefficient_b200.ops import native
     from commefficient_b200.ops.topk import topk_sparse
@@ -177,6 +201,9 @@ def test_peer_kernels_two_gpus():
     for r in range(2):
         res = torch.load(os.path.join(out_dir, "r%d.pt" % r))
         for name, err in res.items():
+            if name.startswith("info_"):
+                print("rank %d %s = %s" % (r, name, err))
+                continue
             assert err < 1e-4, (r, name, err)
 
 
