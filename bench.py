@@ -371,6 +371,9 @@ def _phase_breakdown(fed, opt, rounds, torch, report=True):
 
 
 def main():
+    if os.environ.get("CEB_HANG_DUMP"):          # debugging aid: Python stacks of every rank after N seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["CEB_HANG_DUMP"]), repeat=False, exit=True)
     cfg = parse()
     if cfg.impl == "reference":
         return run_reference(cfg)

@@ -169,14 +169,17 @@ class _DeferredRound:
     copy into a pinned buffer plus the event that completes it.  ``get()`` blocks on the event the
     first time anything looks at a value."""
 
-    def __init__(self, host, event, watchdog=None):
+    def __init__(self, host, event, watchdog=None, peer=None, peer_flag=None):
         self.host, self.event, self.watchdog = host, event, watchdog
+        self.peer, self.peer_flag = peer, peer_flag
         self.array = None
 
     def get(self) -> np.ndarray:
         if self.array is None:
             if self.event is not None:
                 self.event.synchronize()
+            if self.peer_flag is not None and float(self.peer_flag[0]) != 0.0:
+                self.peer.check()          # a device-side barrier of an earlier collective gave up: raise it here
             self.array = self.host.numpy().copy()
             if self.watchdog is not None:
                 self.watchdog.idle()
@@ -500,13 +503,20 @@ class FedModel:
             # before anything waits for the values, so the GPU never idles behind the host
             host = self._result_buffer(packed_dev.shape)
             host.copy_(packed_dev, non_blocking=True)
+            peer, flag = self.rt.peer, None
+            if peer is not None:
+                # the error word of the peer-memory barriers rides along with the round's one D2H
+                flag = self._result_buffer((1,))
+                flag.copy_((peer.ticket[2:3] != 0).float(), non_blocking=True)
             ev = torch.cuda.Event()
             ev.record()
             res_phase.__exit__(None, None, None)
-            rnd = _DeferredRound(host, ev, self.watchdog)
+            rnd = _DeferredRound(host, ev, self.watchdog, peer, flag)
             results = [DeferredArray(rnd, (lambda pk, i=i: pk[:, i].copy())) for i in range(n_res)]
             return results + [DeferredTensor(rnd, _download), DeferredTensor(rnd, _upload)]
         packed = packed_dev.cpu().numpy()   # the round's one D2H
+        if self.rt.peer is not None:
+            self.rt.peer.check()            # (the device is idle here: reading the barrier error word costs nothing)
         res_phase.__exit__(None, None, None)
         self.watchdog.idle()
         results = [packed[:, i].copy() for i in range(n_res)]

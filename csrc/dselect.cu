@@ -48,9 +48,10 @@ __device__ __forceinline__ void dsel_barrier(const DselCtx& c, int phase) {
   if ((int)threadIdx.x < c.world) {
     const uint32_t* slot = c.flags[c.rank] + phase * kFlagStride + threadIdx.x;
     unsigned long long polls = 0;
+    const unsigned long long t0 = peer_now_ns();
     while (!epoch_reached(ld_acquire_sys(slot), epoch)) {
       __nanosleep(20);
-      if (++polls > kPeerSpinBudget) {
+      if (peer_spin_expired(polls, t0)) {
         atomicExch(c.err, 0x40000000u | ((uint32_t)phase << 8) | (uint32_t)threadIdx.x);
         break;
       }

@@ -1,6 +1,6 @@
 // Device helpers shared by the peer-memory kernels (peer.cu, dselect.cu): system-scope flag barriers over
 // CUDA-IPC-mapped memory with a BOUNDED wait -- a rank that died before signalling must not leave the other
-// GPUs spinning until the host watchdog fires: after kPeerSpinBudget polls (a few seconds) the waiter records
+// GPUs spinning until the host watchdog fires: after kPeerSpinNs of wall time (%globaltimer) the waiter records
 // the phase in an error word and gives up, which the host reports (parallel/symm.py:PeerGroup.check).
 #pragma once
 #include "common.cuh"
@@ -9,7 +9,17 @@ constexpr int kMaxPeers = 8;
 constexpr int kPeerThreads = 256;
 constexpr int kFlagStride = 32;   // uint32 slots per phase (>= kMaxPeers, keeps phases on separate lines)
 
-constexpr unsigned long long kPeerSpinBudget = 1ull << 27;     // x ~40 ns per poll: about five seconds
+constexpr unsigned long long kPeerSpinNs = 120ull * 1000 * 1000 * 1000;   // two minutes: ranks legitimately arrive seconds apart (graph captures, first-touch allocations)
+
+__device__ __forceinline__ unsigned long long peer_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// true once a wait that began at t0 has used up its budget (the clock is only read every 256 polls)
+__device__ __forceinline__ bool peer_spin_expired(unsigned long long& polls, unsigned long long t0) {
+  return ((++polls & 255u) == 0) && (peer_now_ns() - t0 > kPeerSpinNs);
+}
 
 struct CebPeerCtx {
   float* src[kMaxPeers];        // every rank's transmit (staging) buffer, peer-mapped
@@ -62,9 +72,10 @@ __device__ __forceinline__ void peer_wait_all(const CebPeerCtx& c, int phase) {
   if ((int)threadIdx.x < c.world) {
     const uint32_t* slot = c.flags[c.rank] + phase * kFlagStride + threadIdx.x;
     unsigned long long polls = 0;
+    const unsigned long long t0 = peer_now_ns();
     while (!epoch_reached(ld_acquire_sys(slot), c.epoch)) {
       __nanosleep(20);
-      if (++polls > kPeerSpinBudget) {          // the peer never arrived: say so and stop waiting
+      if (peer_spin_expired(polls, t0)) {       // the peer never arrived: say so and stop waiting
         atomicExch(c.ticket + 2, 0x80000000u | ((uint32_t)phase << 8) | (uint32_t)threadIdx.x);
         break;
       }
