@@ -51,9 +51,13 @@ def _deterministic_inputs(request):
 def _default_nn_state():
     """The tensor-core switch and the precision are process-wide: start every test from the same state
     (native layers off, bf16 operands) so that no test's result depends on which test ran before it."""
+    import torch
     from commefficient_b200.ops import nn as nnops
     nnops.set_native(False)
     nnops._precision = "bf16"
+    # (set_precision("tf32") turns TF32 on for the library matmuls as well: a test's fp32 oracle must not inherit that)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = True
     try:
         from commefficient_b200.ops import tc
         tc._PRECISION = "bf16"
