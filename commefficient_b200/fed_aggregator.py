@@ -393,8 +393,18 @@ class FedModel:
         dev.record_stream(main)
         return dev
 
+    def check_replicas(self) -> None:
+        """Raise if the ranks' weight replicas are not bit-identical.  Every rank applies the same deterministic
+        server update to its own replica and weights are never re-broadcast (module docstring), so a divergence --
+        a non-deterministic tie-break, a missed collective -- would otherwise go unnoticed."""
+        if not self.rt.replicas_agree(self.fp.flat):
+            raise RuntimeError("weight replicas differ across ranks after %d rounds (rank %d)" % (self.rounds, self.rt.rank))
+
     def _call_train(self, batch):
         args = self.args
+        every = int(getattr(args, "replica_check_every", 0) or 0)
+        if every > 0 and self.rounds > 0 and self.rounds % every == 0:
+            self.check_replicas()
         ids_t = batch[0]
         ids = ids_t.cpu().numpy() if torch.is_tensor(ids_t) else np.asarray(ids_t)
         sorted_already = bool(ids.size <= 1 or np.all(ids[1:] >= ids[:-1]))

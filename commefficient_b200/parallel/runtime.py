@@ -84,6 +84,29 @@ class Runtime:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def replicas_agree(self, t: torch.Tensor) -> bool:
+        """Whether every rank holds bit-identical ``t`` (a float32 tensor): a 64-bit checksum of the bit
+        patterns (sum and position-weighted sum, so permutations show as well) is MIN- and MAX-reduced.
+        One pass over ``t``, one tiny collective, one host sync: meant for every N-th round."""
+        if self.world_size == 1:
+            return True
+        flat = t.detach().reshape(-1).view(torch.int32)
+        chunk = 1 << 24                                        # bounds the int64 temporaries to 128 MB each
+        pos = torch.arange(1, min(chunk, flat.numel()) + 1, device=flat.device, dtype=torch.int64) % 65521
+        s0 = torch.zeros((), dtype=torch.int64, device=flat.device)
+        s1 = torch.zeros((), dtype=torch.int64, device=flat.device)
+        for lo in range(0, flat.numel(), chunk):
+            bits = flat[lo:lo + chunk].to(torch.int64)
+            s0 += bits.sum()
+            s1 += (bits * pos[:bits.numel()]).sum() * (lo // chunk + 1)
+        # float64 carries 53 bits exactly: reduce the two 64-bit sums in three 26-bit-wide limbs
+        sums = torch.stack([s0, s1])
+        limbs = torch.stack([(sums >> s) & 0x3FFFFFF for s in (0, 26, 52)]).reshape(-1).to(torch.float64)
+        lo, hi = limbs.clone(), limbs.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        return bool(torch.equal(lo, hi))
+
     def shutdown(self):
         global _RUNTIME
         if self.peer is not None:

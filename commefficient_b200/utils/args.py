@@ -130,6 +130,9 @@ _FLAGS = [
         _flag("client_lanes", 8, int,
               help="per-client modes (local_topk, fedavg, clipping, DP, topk_down): number of clients simulated "
                    "concurrently, each on its own model replica and CUDA stream (1 = one after the other)"),
+        _flag("replica_check_every", 0, int,
+              help="multi-GPU: every N rounds compare a checksum of the weight replicas across ranks and abort on a "
+                   "mismatch (0 = never); the SPMD design never re-broadcasts weights, so drift would be silent"),
         _flag("resume", None, str, help="path of a *.fedstate.pt sidecar to resume from"),
         _flag("watchdog_timeout", 600.0, float, help="seconds before a hung round aborts all ranks"),
         _flag("flat_layout", "auto", str, choices=("auto", "reference", "nhwc"),

@@ -406,3 +406,35 @@ def test_rank_sharded_loader_loads_each_sample_once_and_matches_single_rank():
     assert loaded1 == list(range(60))
     np.testing.assert_allclose(r0["losses"], l1, rtol=1e-4, atol=1e-5)
     assert (r0["w"] - w1).norm() / w1.norm() < 1e-3
+
+
+def _replica_check_main(rank, world, out_dir):
+    rt = runtime.init_runtime(rank=rank, world_size=world, device="cpu", backend="gloo")
+    torch.manual_seed(0)
+    t = torch.randn(100_003)
+    same = rt.replicas_agree(t)
+    if rank == 1:
+        t[77_777] = torch.nextafter(t[77_777], torch.tensor(10.0))       # one ulp on one rank
+    one_ulp = rt.replicas_agree(t)
+    u = torch.randn(1000, generator=torch.Generator().manual_seed(5))
+    if rank == 1:
+        u = u.flip(0).contiguous().flip(0).contiguous()                   # same values
+        u[[3, 4]] = u[[4, 3]]                                             # ... two of them swapped
+    swapped = rt.replicas_agree(u)
+    torch.save({"same": same, "one_ulp": one_ulp, "swapped": swapped}, os.path.join(out_dir, "r%d.pt" % rank))
+    rt.shutdown()
+
+
+def test_replica_checksum_sees_one_ulp_and_permutations():
+    out_dir = tempfile.mkdtemp()
+    runtime.spawn(_replica_check_main, 2, args=(out_dir,), device="cpu")
+    for r in range(2):
+        res = torch.load(os.path.join(out_dir, "r%d.pt" % r))
+        assert res["same"] is True and res["one_ulp"] is False and res["swapped"] is False
+
+
+def test_gloo_two_ranks_with_replica_check_every_round():
+    """--replica_check_every 1: the check runs before every round and passes (the replicas of a correct run are
+    bit-identical)."""
+    ranks = _spawn(2, "cpu", "sketch", "gloo", replica_check_every=1)
+    torch.testing.assert_close(ranks[0]["w"], ranks[1]["w"], rtol=0, atol=0)
