@@ -8,7 +8,7 @@ import sys
 
 PAT = re.compile(r"\b(UTCHMMA[\w.]*|UTMALDG[\w.]*|UTMASTG[\w.]*|UTCBAR[\w.]*|UTCATOMSWS[\w.]*|LDTM[\w.]*|UCGABAR_\w+|"
                  r"SYNCS[\w.]*|RED\.[\w.]*|ATOM[\w.]*|REDG[\w.]*|LDG\.E[\w.]*\.SYS|STG\.E[\w.]*\.SYS|"
-                 r"STG\.E\.ENL2\.256|LDG\.E\.ENL2\.256[\w.]*|MUFU\.TANH)")
+                 r"STG\.E\.ENL2\.256|LDG\.E\.ENL2\.256[\w.]*|MUFU\.TANH|LDGMC[\w.]*|STGMC[\w.]*|REDGMC[\w.]*|STG\.E\.MC[\w.]*)")
 
 
 def main():
@@ -37,7 +37,8 @@ def main():
           "barrier), `LDTM` = tcgen05.ld (TMEM), `UTCBAR` = tcgen05.commit (`.2CTA.MULTICAST` = arrive in both "
           "CTAs), `UTCATOMSWS` = tcgen05.alloc/dealloc, `UCGABAR_*` = cluster barrier, `SYNCS` = mbarrier, "
           "`STG.E.ENL2.256` = 256-bit global store, `RED*` = reduction atomics, `*.SYS` = system-scope (peer) "
-          "accesses, `MUFU.TANH` = tanh.approx.  `tcgen05.mma.kind::tf32` assembles to the same `UTCHMMA` mnemonic as "
+          "accesses, `LDGMC...ADD` = multimem.ld_reduce (in-switch reduction, NVLS), multimem.st assembles to a plain `STG.E.128.STRONG.SYS` (the "
+          "multicast is a property of the address), `MUFU.TANH` = tanh.approx.  `tcgen05.mma.kind::tf32` assembles to the same `UTCHMMA` mnemonic as "
           "`kind::f16` (the operand kind travels in the instruction descriptor): the TF32 kernels are the "
           "instantiations whose last template argument is 1 (`tc_tile_kernel<..., 1>`, `tc_wgrad_kernel<..., 1>`).\n")
     for name, cnt in per.items():
