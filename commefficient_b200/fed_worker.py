@@ -415,7 +415,10 @@ class ClientWorker:
         lane.peer = lane.weights_buf = lane.transmit_buf = None
         lane.transmit = torch.zeros(self.transmit_shape, dtype=torch.float32, device=self.device)
         lane._tmp_table = lane._ps_copy = None
-        lane._graphs = graphs.GraphCache()
+        # every cached graph owns a private pool with one client's activations: keep the total over all lanes at
+        # about what the single-lane cache may hold (rarely seen shapes then simply stay eager)
+        lanes = max(1, int(getattr(self.args, "client_lanes", 1) or 1))
+        lane._graphs = graphs.GraphCache(capacity=max(2, 12 // lanes))
         lane._lane_list = None
         lane.stream = torch.cuda.Stream(device=self.device)
         return lane
