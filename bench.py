@@ -47,6 +47,9 @@ def parse():
                     help="tf32 (headline): fp32 activations, tcgen05 kind::tf32 -- the precision the reference's fp32 "
                          "convolutions get from cuDNN; bf16: the fast path (reported as the extra key \"bf16\")")
     ap.add_argument("--no_extra", action="store_true", help="skip the extra bf16 measurement")
+    ap.add_argument("--set", action="append", default=[], metavar="FLAG=VALUE",
+                    help="override a training flag of the configuration (ours only; e.g. --set max_grad_norm=1.0): the "
+                         "JSON line then carries the overrides in config.overrides and is NOT a BASELINE number")
     ap.add_argument("--ref_timeout", type=int, default=1500, help="seconds before the reference arm is abandoned")
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--no_native_nn", action="store_true",
@@ -234,6 +237,12 @@ def run_ours(cfg):
 
     def measure(precision, steps, warmup, e2e=True, profile=False):
         flags = dict(bc["flags"])
+        for item in cfg.set:
+            k, _, v = item.partition("=")
+            try:
+                flags[k] = json.loads(v)
+            except ValueError:
+                flags[k] = v
         args = make_args(num_workers=clients, num_clients=bc["num_clients"],
                          local_batch_size=bc["per_client"] if gpt2 else -1, num_epochs=1.0, dataset_name=bc["dataset"],
                          device="cuda", precision=precision, backend=cfg.backend, model=bc["model"],
@@ -333,6 +342,7 @@ def run_ours(cfg):
                        "images_per_client": bc["per_client"], "seq_len": bc.get("seq"),
                        "parallelism": "dp%d" % cfg.gpus, "backend": main["backend"],
                        "client_batching": main["client_batching"], "native_nn": main["native_nn"],
+                       "client_lanes": cfg.client_lanes, **({"overrides": list(cfg.set)} if cfg.set else {}),
                        "precision_note": "tf32 = fp32 activations / weights, tcgen05 kind::tf32 MMAs with fp32 "
                                          "accumulation, fp32 head: what the reference's fp32 model gets from cuDNN "
                                          "(allow_tf32 defaults to True)",
