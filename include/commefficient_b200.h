@@ -289,13 +289,24 @@ int ceb_colsum_bf16(const void* x_bf16, int64_t ld, int64_t rows, int cols, floa
  *    mode 1  Vv = rho*Vv + sum/N; Ve += Vv (error_mode 2) or Ve = Vv (1); dst = Ve (or Vv)
  *    mode 2  Vv = rho*Vv + sum/N; dst (= every replica's weights) -= lr * Vv
  *    mode 3  true_topk state: Vv = rho*Vv + sum/N; Ve += Vv on the shard, nothing gathered (pass dst = src)
- *  Barrier waits are bounded: after ~5 s without a peer the waiter writes a code into ticket[2] and goes on.
+ *  Barrier waits are bounded: after two minutes (globaltimer) without a peer the waiter writes a code into
+ *  ticket[2] and goes on.
  *  Vv_shard / Ve_shard hold this rank's ceb_peer_shard_elems(n, world) entries. */
 int64_t ceb_peer_shard_elems(int64_t n, int world);
 int ceb_peer_fused_reduce(int mode, const void* const* src, const void* const* dst,
                           const void* const* flags, void* ticket, int rank, int world, unsigned int epoch,
                           int64_t n, float* Vv_shard, float* Ve_shard, float inv_n, float rho,
                           int error_mode, float lr, const float* lr_vec, void* stream);
+/* The same collective through the NVSwitch (NVLS): mc_src / mc_dst are the MULTICAST addresses of the buffers whose
+ * per-rank mappings are src[] / dst[] (memory bound to one multicast object spanning all `world` GPUs:
+ * cuMulticastCreate / cuMulticastBindMem, or torch.distributed._symmetric_memory).  The reduce-scatter is one
+ * multimem.ld_reduce.add.v4.f32 per 16 bytes (summed inside the switch), the all-gather one multimem.st; flags /
+ * ticket / epoch and the modes are those of ceb_peer_fused_reduce (mode 3 needs no mc_dst). */
+int ceb_peer_fused_reduce_nvls(int mode, const void* const* src, const void* const* dst,
+                               const void* const* flags, void* ticket, int rank, int world, unsigned int epoch,
+                               int64_t n, float* Vv_shard, float* Ve_shard, float inv_n, float rho,
+                               int error_mode, float lr, const float* lr_vec, void* mc_src, void* mc_dst,
+                               void* stream);
 /* Symmetric buffers (the only allocating entry points: CUDA IPC needs whole cudaMalloc
  * allocations).  handle: ceb_peer_handle_bytes() (= 64) bytes, host memory. */
 int ceb_peer_handle_bytes(void);
