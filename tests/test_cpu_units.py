@@ -240,3 +240,22 @@ def test_batched_chunks_never_split_a_client():
     assert got[0][0] == 0 and got[-1][1] == sum(sizes)
     assert all(a[1] == b[0] for a, b in zip(got, got[1:]))
     assert all(lo in bounds and hi in bounds for lo, hi in got)
+
+
+def test_public_header_declares_every_exported_entry_point():
+    """include/commefficient_b200.h is the C ABI's contract: every `ceb_*` symbol the library exports is declared
+    there (and nothing is declared that the library does not export)."""
+    import os
+    import re
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = os.path.join(root, "commefficient_b200", "lib", "libceb200.so")
+    if not os.path.exists(lib) or shutil.which("nm") is None:
+        pytest.skip("native library or nm not available")
+    out = subprocess.run(["nm", "-D", "--defined-only", lib], stdout=subprocess.PIPE, text=True, check=True).stdout
+    exported = {ln.split()[-1] for ln in out.splitlines() if ln.split()[-1].startswith("ceb_")}
+    header = open(os.path.join(root, "include", "commefficient_b200.h")).read()
+    declared = set(re.findall(r"\b(ceb_[a-z0-9_]+)\s*\(", header))
+    assert exported - declared == set(), "exported but not declared: %s" % sorted(exported - declared)
+    assert declared - exported == set(), "declared but not exported: %s" % sorted(declared - exported)
