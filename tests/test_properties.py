@@ -96,3 +96,50 @@ def test_native_sketch_equals_oracle(d, c, r, nb, seed):
     torch.testing.assert_close(val.cpu(), est[idx.cpu().long()], rtol=1e-5, atol=1e-6)
     thresh = est.abs().topk(k).values[-1]
     assert float(val.abs().min()) >= float(thresh) - 1e-6
+
+
+class _Sizes:
+    def __init__(self, sizes):
+        self.data_per_client = list(sizes)
+        self.num_clients = len(sizes)
+
+    def __len__(self):
+        return int(sum(self.data_per_client))
+
+
+@settings(max_examples=40, deadline=None)
+@given(st.lists(st.integers(min_value=1, max_value=9), min_size=1, max_size=30), st.integers(min_value=1, max_value=8),
+       st.sampled_from([-1, 1, 3]), st.integers(min_value=2, max_value=4), st.booleans(), st.integers(min_value=0, max_value=99))
+def test_rank_sharded_sampler_partitions_the_unsharded_schedule(sizes, num_workers, local_bs, world, by_owner, seed):
+    """For every round the ranks' batches of a sharded FedSampler are a partition of the unsharded sampler's batch
+    (or, when some rank would be left without a client, each rank gets the whole batch and the round says so), and
+    the published schedule (client ids ascending, sample counts) agrees with the samples drawn."""
+    from commefficient_b200.data_utils.fed_sampler import FedSampler, assign_clients
+    ds = _Sizes(sizes)
+    starts = np.concatenate([[0], np.cumsum(sizes)])
+    owner = np.repeat(np.arange(len(sizes)), sizes)
+    plain = list(FedSampler(ds, num_workers, local_bs, seed=seed))
+    shards = [FedSampler(ds, num_workers, local_bs, seed=seed, rank=r, world_size=world, by_owner=by_owner)
+              for r in range(world)]
+    per_rank, metas = [], []
+    for s in shards:
+        per_rank.append(list(s))
+        metas.append(list(s.rounds))
+    assert all(len(b) == len(plain) for b in per_rank)
+    seen = np.zeros(int(sum(sizes)), dtype=np.int64)
+    for t, full in enumerate(plain):
+        meta = metas[0][t]
+        assert all(np.array_equal(m[t].ids, meta.ids) and np.array_equal(m[t].counts, meta.counts) for m in metas)
+        assert np.all(np.diff(meta.ids) > 0) and int(meta.counts.sum()) == len(full)
+        assert sorted(np.unique(owner[full])) == list(meta.ids)
+        parts = assign_clients(meta.ids, world, by_owner)
+        if meta.sharded:
+            got = np.concatenate([per_rank[r][t] for r in range(world)])
+            assert sorted(got) == sorted(full)
+            for r in range(world):
+                assert sorted(np.unique(owner[per_rank[r][t]])) == list(parts[r])
+        else:
+            assert any(len(p) == 0 for p in parts)
+            assert all(sorted(per_rank[r][t]) == sorted(full) for r in range(world))
+        seen[full] += 1
+    assert np.all(seen == 1) and starts[-1] == len(seen)          # an epoch visits every sample exactly once
