@@ -450,6 +450,11 @@ class ClientWorker:
             with torch.cuda.stream(lane.stream):
                 lane.fp.flat.copy_(self.fp.flat, non_blocking=True)
                 lane.transmit.zero_()
+                copied = torch.cuda.Event()
+                copied.record()
+            # lane 0 may rewrite its weights while it simulates a client (FedAvg's local SGD, --topk_down's stale
+            # weights): not before every lane has taken its copy of the server's
+            main.wait_event(copied)
             lane.round_no = self.round_no
             lane.model.train()
         out = [None] * len(client_batches)
