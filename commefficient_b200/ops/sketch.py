@@ -33,8 +33,7 @@ class SketchPlan:
             blk = torch.where(neg, blk | torch.tensor(-2 ** 31, dtype=torch.int32), blk)
             self.blk = blk.contiguous().to(self.device)
             self._est = None
-            self._rowsq = torch.zeros(self.r, dtype=torch.float32, device=self.device)
-            self._scale2 = torch.zeros(2, dtype=torch.float32, device=self.device)
+            self._l2_bufs = {}              # per stream: (row sums of squares, [scale, l2]) -- see l2_scale
 
     @classmethod
     def get(cls, d, c, r, num_blocks, device) -> "SketchPlan":
@@ -108,9 +107,17 @@ def l2_scale(plan: SketchPlan, table: torch.Tensor, clip: float = 0.0) -> torch.
         l2 = ref.l2estimate_ref(table)
         s = clip / l2 if (clip > 0 and l2 >= clip) else 1.0
         return torch.tensor([s, l2], dtype=torch.float32)
+    # the result stays on the device and is consumed by a later kernel of the same stream: one buffer pair per
+    # stream, so clients simulated concurrently (fed_worker.py: client lanes) cannot overwrite each other's scale
+    key = torch.cuda.current_stream(plan.device).cuda_stream
+    bufs = plan._l2_bufs.get(key)
+    if bufs is None:
+        bufs = (torch.zeros(plan.r, dtype=torch.float32, device=plan.device),
+                torch.zeros(2, dtype=torch.float32, device=plan.device))
+        plan._l2_bufs[key] = bufs
     native.call("ceb_sketch_l2_scale", native.ptr(table), plan.r, plan.c, float(clip),
-                native.ptr(plan._rowsq), native.ptr(plan._scale2), native.stream_ptr(plan.device))
-    return plan._scale2
+                native.ptr(bufs[0]), native.ptr(bufs[1]), native.stream_ptr(plan.device))
+    return bufs[1]
 
 
 def axpy(y: torch.Tensor, x: torch.Tensor, alpha: float = 1.0, dev_scale: Optional[torch.Tensor] = None,
