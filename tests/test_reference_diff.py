@@ -1,0 +1,25 @@
+"""Function-by-function differential test against the UNMODIFIED reference (``baseline/_ref``) on the CPU:
+the server rules of all five modes and the client step (momentum, error feedback, local top-k, clipping,
+sketching, microbatches).  The comparison runs in a subprocess (``baseline/diff_rules.py``) because the
+reference's modules are top-level names."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_rules_match_the_reference_function_by_function():
+    if not os.path.isdir(os.path.join(ROOT, "baseline", "_ref", "CommEfficient")):
+        pytest.skip("baseline/_ref is not installed (python baseline/install_ref.py)")
+    proc = subprocess.run([sys.executable, os.path.join(ROOT, "baseline", "diff_rules.py")], stdout=subprocess.PIPE,
+                          stderr=subprocess.PIPE, text=True, timeout=600)
+    assert proc.returncode == 0, proc.stderr[-2000:]
+    res = json.loads(proc.stdout.strip().splitlines()[-1])
+    assert "unavailable" not in res, res
+    assert len(res) >= 14
+    for case, err in res.items():
+        assert isinstance(err, float) and err < 1e-4, (case, err)
