@@ -10,7 +10,10 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * client rules: ``local_step`` (reference fed_worker.py:184-230) on a small MLP: plain, local momentum,
     local error, local top-k with momentum-factor masking, gradient clipping, sketching and sketch-space
     clipping, microbatches (the reference sums microbatch means -- quirk Q6 -- ours under
-    ``--compat_microbatch_sum``).
+    ``--compat_microbatch_sum``);
+  * models: ResNet9 (plain / BatchNorm / 1-channel 62-class), ResNet18, FixupResNet9, FixupResNet18, ResNet101LN --
+    the reference's ``state_dict`` loads with ``strict=True`` and output and parameter gradients agree;
+  * ``FedSampler``: with the same numpy seed both draw the same clients and samples in every round.
 
 Usage: python baseline/diff_rules.py   (exit code 0 even when differences are large: the caller judges)
 """
@@ -136,6 +139,64 @@ def main():
             if need_e:
                 worst = max(worst, float((re_ - oe).abs().max()))
         out[name] = skipped if skipped is not None else worst
+    # ---- models: same weights, same input -> same output and same parameter gradients ---------------------
+    import models as ref_models
+    from commefficient_b200 import models as our_models
+    model_cases = [("ResNet9", dict(num_classes=10), (2, 3, 32, 32)),
+                   ("ResNet9", dict(num_classes=10, do_batchnorm=True), (4, 3, 32, 32)),
+                   ("ResNet9", dict(num_classes=62, initial_channels=1), (2, 1, 32, 32)),
+                   ("ResNet18", dict(num_classes=100), (2, 3, 32, 32)),
+                   ("FixupResNet9", {}, (2, 3, 32, 32)),
+                   ("FixupResNet18", dict(num_classes=10), (2, 3, 32, 32)),
+                   ("ResNet101LN", {}, (1, 1, 28, 28))]
+    import contextlib
+    import io
+    for cls, kw, shape in model_cases:
+        torch.manual_seed(0)
+        with contextlib.redirect_stdout(io.StringIO()):          # (the reference's ResNet9 prints its BatchNorm flag)
+            r, o = getattr(ref_models, cls)(**kw), getattr(our_models, cls)(**kw)
+        with torch.no_grad():
+            for p in r.parameters():                              # (Fixup zero-initialises some layers)
+                p.add_(torch.randn_like(p) * 0.05)
+        o.load_state_dict(r.state_dict(), strict=True)            # identical parameter / buffer names and shapes
+        x = torch.randn(*shape)
+        r.train()
+        o.train()
+        yr, yo = r(x), o(x)
+        gr = torch.autograd.grad(yr.square().sum(), list(r.parameters()), allow_unused=True)
+        go = torch.autograd.grad(yo.square().sum(), list(o.parameters()), allow_unused=True)
+        err = float((yr - yo).abs().max() / yr.abs().max())
+        for a, b in zip(gr, go):
+            if a is not None:
+                err = max(err, float((a - b).abs().max() / (a.abs().max() + 1e-12)))
+        tag = "models/%s%s" % (cls, "" if not kw else "(" + ",".join("%s=%s" % kv for kv in sorted(kw.items())) + ")")
+        out[tag] = err
+
+    # ---- FedSampler: the same numpy seed draws the same rounds ---------------------------------------------
+    from data_utils.fed_sampler import FedSampler as RefSampler
+    from commefficient_b200.data_utils import FedSampler as OurSampler
+
+    class Sizes:
+        def __init__(self, sizes):
+            self.data_per_client = np.asarray(sizes)
+            self.num_clients = len(sizes)
+
+        def __len__(self):
+            return int(np.sum(self.data_per_client))
+
+    worst = 0.0
+    for sizes, workers, bs in (([5] * 12, 4, -1), ([3, 9, 1, 7, 4, 4, 6, 2], 3, 2), ([10] * 6, 6, 4)):
+        ds = Sizes(sizes)
+        np.random.seed(11)
+        ref_rounds = [np.asarray(b) for b in RefSampler(ds, workers, bs)]
+        np.random.seed(11)
+        our_rounds = [np.asarray(b) for b in OurSampler(ds, workers, bs)]
+        if len(ref_rounds) != len(our_rounds):
+            worst = max(worst, 1e9)
+            continue
+        for a, b in zip(ref_rounds, our_rounds):
+            worst = max(worst, 0.0 if (len(a) == len(b) and np.array_equal(np.sort(a), np.sort(b))) else 1.0)
+    out["data/fed_sampler_rounds"] = worst
     print(json.dumps(out))
     return 0
 
