@@ -13,7 +13,10 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
     ``--compat_microbatch_sum``);
   * models: ResNet9 (plain / BatchNorm / 1-channel 62-class), ResNet18, FixupResNet9, FixupResNet18, ResNet101LN --
     the reference's ``state_dict`` loads with ``strict=True`` and output and parameter gradients agree;
-  * ``FedSampler``: with the same numpy seed both draw the same clients and samples in every round.
+  * ``FedSampler``: with the same numpy seed both draw the same clients and samples in every round;
+  * datasets: FedCIFAR10 / FedEMNIST / FedPERSONA (+ collate) over the same client files return the same items,
+    iid and non-iid (PersonaChat with more than one personality permutation and validation indexing are the
+    documented departures Q14 / Q15 and are not compared).
 
 Usage: python baseline/diff_rules.py   (exit code 0 even when differences are large: the caller judges)
 """
@@ -197,6 +200,72 @@ def main():
         for a, b in zip(ref_rounds, our_rounds):
             worst = max(worst, 0.0 if (len(a) == len(b) and np.array_equal(np.sort(a), np.sort(b))) else 1.0)
     out["data/fed_sampler_rounds"] = worst
+
+    # ---- datasets: both read the same on-disk client files; every item, iid and non-iid --------------------
+    import random
+    import tempfile
+    import data_utils as ref_data
+    from commefficient_b200 import data_utils as our_data
+
+    def same(x, y):
+        if isinstance(x, (list, tuple)):
+            return len(x) == len(y) and all(same(a, b) for a, b in zip(x, y))
+        if torch.is_tensor(x) or torch.is_tensor(y):
+            return torch.equal(torch.as_tensor(x), torch.as_tensor(y))
+        return bool(np.all(np.asarray(x) == np.asarray(y)))
+
+    def compare_sets(make_ref, make_ours, variants):
+        bad = 0
+        for kw in variants:
+            np.random.seed(3)
+            r = make_ref(**kw)
+            np.random.seed(3)
+            o = make_ours(**kw)
+            bad += int(len(r) != len(o) or r.num_clients != o.num_clients)
+            if kw.get("train", True):
+                bad += int(not np.array_equal(np.asarray(r.data_per_client), np.asarray(o.data_per_client)))
+            for i in range(min(len(r), len(o))):
+                random.seed(i)
+                a = r[i]
+                random.seed(i)
+                b = o[i]
+                bad += int(not same(a, b))
+        return float(bad)
+
+    tmp = tempfile.mkdtemp()
+    our_data.write_synthetic_cifar(tmp, num_classes=10, images_per_class=12, num_val=30, seed=0)
+    out["data/fed_cifar10_items"] = compare_sets(
+        lambda **kw: ref_data.FedCIFAR10(tmp, "CIFAR10", None, kw["iid"], kw["n"], train=kw["train"], download=False),
+        lambda **kw: our_data.FedCIFAR10(tmp, "CIFAR10", None, kw["iid"], kw["n"], train=kw["train"], download=False),
+        [dict(iid=False, n=10, train=True), dict(iid=False, n=20, train=True), dict(iid=True, n=7, train=True),
+         dict(iid=False, n=None, train=False)])
+    tmp = tempfile.mkdtemp()
+    our_data.write_synthetic_emnist(tmp, num_clients=12, images_per_client=6, num_classes=62, seed=0)
+    out["data/fed_emnist_items"] = compare_sets(
+        lambda **kw: ref_data.FedEMNIST(tmp, "EMNIST", None, kw["iid"], kw["n"], train=kw["train"], download=False),
+        lambda **kw: our_data.FedEMNIST(tmp, "EMNIST", None, kw["iid"], kw["n"], train=kw["train"], download=False),
+        [dict(iid=False, n=12, train=True), dict(iid=False, n=24, train=True), dict(iid=True, n=5, train=True),
+         dict(iid=False, n=None, train=False)])
+    # PersonaChat: training items with one personality permutation (more than one, and validation indexing, are the
+    # documented departures Q14 / Q15), then the collate function on the same items
+    tmp = tempfile.mkdtemp()
+    our_data.write_synthetic_persona(tmp, num_clients=6, num_candidates=2, seed=0)
+    tok = our_data.SimpleTokenizer()
+    tok.add_special_tokens(our_data.ATTR_TO_SPECIAL_TOKEN)
+    mk_ref = lambda **kw: ref_data.FedPERSONA(tok, 2, 2, 1, tmp, "PERSONA", None, kw["iid"], kw["n"], train=True,  # noqa: E731
+                                              download=False)
+    mk_our = lambda **kw: our_data.FedPERSONA(tokenizer=tok, num_candidates=2, max_history=2,                      # noqa: E731
+                                              personality_permutations=1, dataset_dir=tmp, dataset_name="PERSONA",
+                                              do_iid=kw["iid"], num_clients=kw["n"], train=True)
+    variants = [dict(iid=False, n=None, train=True), dict(iid=True, n=4, train=True)]
+    bad = compare_sets(mk_ref, mk_our, variants)
+    np.random.seed(3)
+    r, o = mk_ref(**variants[0]), mk_our(**variants[0])
+    random.seed(0)
+    br = ref_data.personachat_collate_fn([r[i] for i in range(5)])
+    random.seed(0)
+    bo = our_data.personachat_collate_fn([o[i] for i in range(5)])
+    out["data/fed_persona_items_and_collate"] = bad + float(not same(list(br), list(bo)))
     print(json.dumps(out))
     return 0
 

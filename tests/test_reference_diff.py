@@ -1,7 +1,7 @@
 """Function-by-function differential test against the UNMODIFIED reference (``baseline/_ref``) on the CPU:
 the server rules of all five modes, the client step (momentum, error feedback, local top-k, clipping,
-sketching, microbatches), every CV model class (same weights and input -> same output and gradients) and the
-round sampler (same numpy seed -> same rounds).  The comparison runs in a subprocess (``baseline/diff_rules.py``) because the
+sketching, microbatches), every CV model class (same weights and input -> same output and gradients), the
+round sampler (same numpy seed -> same rounds) and the federated datasets (same client files -> same items).  The comparison runs in a subprocess (``baseline/diff_rules.py``) because the
 reference's modules are top-level names."""
 import json
 import os
@@ -21,6 +21,6 @@ def test_rules_match_the_reference_function_by_function():
     assert proc.returncode == 0, proc.stderr[-2000:]
     res = json.loads(proc.stdout.strip().splitlines()[-1])
     assert "unavailable" not in res, res
-    assert len(res) >= 23 and any(c.startswith("models/") for c in res) and "data/fed_sampler_rounds" in res
+    assert len(res) >= 26 and "data/fed_persona_items_and_collate" in res and any(c.startswith("models/") for c in res) and "data/fed_sampler_rounds" in res
     for case, err in res.items():
         assert isinstance(err, float) and err < 1e-4, (case, err)
