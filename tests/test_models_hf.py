@@ -43,3 +43,38 @@ def test_gpt1_class_is_post_ln_without_final_layernorm():
     ids = torch.randint(0, 50, (2, 2, 9))
     out = m(ids, token_type_ids=ids, mc_token_ids=torch.full((2, 2), 8), lm_labels=ids, mc_labels=torch.zeros(2, dtype=torch.long))
     assert torch.isfinite(out[0]) and torch.isfinite(out[1])
+
+
+def test_double_heads_model_matches_transformers():
+    """GPT2DoubleHeadsModel: LM loss, multiple-choice loss and both logits against transformers' class of the same
+    name with copied weights (labels: -1 here = -100 there; the reference calls the pytorch_transformers ancestor of
+    that class, /root/reference/CommEfficient/gpt2_train.py:76-99)."""
+    from commefficient_b200.models.gpt2 import GPT2DoubleHeadsModel
+    torch.manual_seed(1)
+    kw = dict(vocab_size=101, n_positions=32, n_embd=64, n_layer=2, n_head=4, resid_pdrop=0.0, embd_pdrop=0.0,
+              attn_pdrop=0.0)
+    hf = transformers.GPT2DoubleHeadsModel(transformers.GPT2Config(summary_first_dropout=0.0, num_labels=1, **kw)).eval()
+    ours = GPT2DoubleHeadsModel(GPT2Config(vocab_size=101, n_positions=32, n_ctx=32, n_embd=64, n_layer=2, n_head=4,
+                                           summary_first_dropout=0.0)).eval()
+    mine = ours.state_dict()
+    src = hf.state_dict()
+    loaded = {k: src[k] for k in mine if k in src and src[k].shape == mine[k].shape}
+    assert sorted(loaded) == sorted(mine), sorted(set(mine) - set(loaded))
+    ours.load_state_dict(loaded)
+    B, C, T = 3, 2, 13
+    ids = torch.randint(0, 101, (B, C, T))
+    types = torch.randint(0, 101, (B, C, T))
+    mc_ids = torch.randint(0, T, (B, C))
+    lm = torch.randint(0, 101, (B, C, T))
+    lm[:, 0] = -1                                   # only the last candidate carries LM labels
+    lm[:, :, :4] = -1
+    mc = torch.randint(0, C, (B,))
+    with torch.no_grad():
+        want = hf(input_ids=ids, token_type_ids=types, mc_token_ids=mc_ids, labels=lm.masked_fill(lm == -1, -100),
+                  mc_labels=mc)
+        lm_loss, mc_loss, lm_logits, mc_logits = ours(ids, token_type_ids=types, mc_token_ids=mc_ids, lm_labels=lm,
+                                                      mc_labels=mc)
+    torch.testing.assert_close(lm_logits, want.logits, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(mc_logits, want.mc_logits, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(lm_loss, want.loss, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(mc_loss, want.mc_loss, rtol=1e-4, atol=1e-5)
