@@ -16,7 +16,9 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * ``FedSampler``: with the same numpy seed both draw the same clients and samples in every round;
   * datasets: FedCIFAR10 / FedEMNIST / FedPERSONA (+ collate) over the same client files return the same items,
     iid and non-iid (PersonaChat with more than one personality permutation and validation indexing are the
-    documented departures Q14 / Q15 and are not compared).
+    documented departures Q14 / Q15 and are not compared);
+  * CLI: all 55 reference flags exist with the same dest and default and parse the same command line;
+  * utilities: LR schedules, ``steps_per_epoch``, ``_topk``, ``get_param_vec`` / ``set_param_vec``.
 
 Usage: python baseline/diff_rules.py   (exit code 0 even when differences are large: the caller judges)
 """
@@ -266,6 +268,64 @@ def main():
     random.seed(0)
     bo = our_data.personachat_collate_fn([o[i] for i in range(5)])
     out["data/fed_persona_items_and_collate"] = bad + float(not same(list(br), list(bo)))
+    # ---- CLI: every reference flag exists with the same dest and default, and parses to the same value -------
+    import utils as ref_utils
+    from commefficient_b200 import utils as our_utils
+    from commefficient_b200.utils.args import build_parser
+
+    def parse_both(argv):
+        old = sys.argv
+        sys.argv = ["prog"] + list(argv)
+        try:
+            ra = vars(ref_utils.parse_args())
+        finally:
+            sys.argv = old
+        oa = vars(build_parser(None, our_models.model_names()).parse_args(list(argv)))
+        return ra, oa
+
+    bad = 0
+    ra, oa = parse_both([])
+    bad += len([k for k in ra if k not in oa])
+    bad += len([k for k in ra if k in oa and ra[k] != oa[k] and k != "device"])     # (device: resolved later here)
+    argv = ["--mode", "true_topk", "--k", "123", "--num_workers", "7", "--local_momentum", "0.5", "--error_type",
+            "virtual", "--topk_down", "--dp", "--num_clients", "50", "--iid", "--local_batch_size", "3", "--model",
+            "ResNet18", "--dataset_name", "CIFAR100", "--lr_scale", "0.3", "--pivot_epoch", "2", "--num_epochs", "3",
+            "--fedavg_batch_size", "5", "--max_grad_norm", "2.5", "--microbatch_size", "4", "--num_rows", "3",
+            "--num_cols", "1000", "--num_blocks", "5", "--share_ps_gpu", "--device", "cpu", "--weight_decay", "1e-3",
+            "--valid_batch_size", "9", "--test", "--tensorboard", "--seed", "5", "--fedavg_lr_decay", "0.9",
+            "--num_fedavg_epochs", "2", "--virtual_momentum", "0.7"]
+    ra, oa = parse_both(argv)
+    bad += len([k for k in ra if ra[k] != oa.get(k)])
+    out["cli/flags_dests_defaults"] = float(bad)
+
+    # ---- small utilities --------------------------------------------------------------------------------------
+    worst = 0.0
+    rs = ref_utils.PiecewiseLinear([0, 5, 24], [0, 0.4, 0])
+    os_ = our_utils.PiecewiseLinear([0, 5, 24], [0, 0.4, 0])
+    for t in np.linspace(0, 24, 97):
+        worst = max(worst, abs(float(rs(t)) - float(os_(t))))
+    if hasattr(ref_utils, "Exp") and hasattr(our_utils, "Exp"):
+        re_, oe_ = ref_utils.Exp(2, 0.3, 5), our_utils.Exp(2, 0.3, 5)
+        for t in np.linspace(0, 12, 49):
+            worst = max(worst, abs(float(re_(t)) - float(oe_(t))))
+    for name_ds in ("CIFAR10", "CIFAR100", "EMNIST", "ImageNet", "PERSONA"):
+        try:
+            want = ref_utils.num_classes_of_dataset(name_ds)
+        except Exception:               # noqa: BLE001 -- a name the reference does not know
+            continue
+        worst = max(worst, float(want != our_utils.num_classes_of_dataset(name_ds)))
+    ds6 = Sizes([4] * 10)
+    for lbs, nw in ((-1, 3), (2, 3), (5, 4)):
+        worst = max(worst, abs(float(ref_utils.steps_per_epoch(lbs, ds6, nw)) - float(our_utils.steps_per_epoch(lbs, ds6, nw))))
+    v = torch.randn(500, generator=torch.Generator().manual_seed(9))
+    worst = max(worst, float((ref_utils._topk(v.clone(), 37) - our_utils._topk(v.clone(), 37)).abs().max()))
+    m1, m2 = make_model(3), make_model(3)
+    worst = max(worst, float((ref_utils.get_param_vec(m1) - our_utils.get_param_vec(m2)).abs().max()))
+    newv = torch.randn(n_par, generator=torch.Generator().manual_seed(10))
+    ref_utils.set_param_vec(m1, newv.clone())
+    our_utils.set_param_vec(m2, newv.clone())
+    worst = max(worst, max(float((a - b).abs().max()) for a, b in zip(m1.parameters(), m2.parameters())))
+    out["utils/schedules_topk_flat_vectors"] = worst
     print(json.dumps(out))
     return 0
 
