@@ -10,7 +10,8 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * client rules: ``local_step`` (reference fed_worker.py:184-230) on a small MLP: plain, local momentum,
     local error, local top-k with momentum-factor masking, gradient clipping, sketching and sketch-space
     clipping, microbatches (the reference sums microbatch means -- quirk Q6 -- ours under
-    ``--compat_microbatch_sum``);
+    ``--compat_microbatch_sum``); ``process_batch`` (reference fed_worker.py:140-182) for a training client, a client
+    with stale weights (``--topk_down``), a client with local momentum / error rows, and a validation shard;
   * models: ResNet9 (plain / BatchNorm / 1-channel 62-class), ResNet18, FixupResNet9, FixupResNet18, ResNet101LN --
     the reference's ``state_dict`` loads with ``strict=True`` and output and parameter gradients agree;
   * ``FedSampler``: with the same numpy seed both draw the same clients and samples in every round;
@@ -104,6 +105,9 @@ def main():
         return loss, acc
 
     n_par = sum(p.numel() for p in make_model(0).parameters())
+
+    def ref_utils_get(model):
+        return torch.cat([p.data.reshape(-1) for p in model.parameters()])
     client_cases = {
         "client/uncompressed": base(mode="uncompressed", grad_size=n_par),
         "client/uncompressed_clip": base(mode="uncompressed", grad_size=n_par, max_grad_norm=0.05),
@@ -144,6 +148,42 @@ def main():
             if need_e:
                 worst = max(worst, float((re_ - oe).abs().max()))
         out[name] = skipped if skipped is not None else worst
+    # ---- process_batch: weights in, (transmit, results) out; stale client weights (--topk_down); validation -----
+    pb_cases = {
+        "client/process_batch_train": base(mode="uncompressed", grad_size=n_par),
+        "client/process_batch_topk_down": base(mode="true_topk", error_type="virtual", grad_size=n_par, do_topk_down=True, k=23),
+        "client/process_batch_local_state": base(mode="local_topk", error_type="local", local_momentum=0.9, grad_size=n_par),
+        "client/process_batch_validation": base(mode="uncompressed", grad_size=n_par),
+    }
+    for name, args in pb_cases.items():
+        worst = 0.0
+        for seed in range(3):
+            gen = torch.Generator().manual_seed(900 + seed)
+            x = torch.randn(6, 10, generator=gen)
+            y = torch.randint(0, 4, (6,), generator=gen)
+            cid = -1 if name.endswith("validation") else 2
+            ids = torch.full((6,), cid, dtype=torch.long)
+            ps = torch.randn(n_par, generator=gen) * 0.3
+            cw = torch.randn(4, n_par, generator=gen) * 0.3 if args.do_topk_down else None
+            need_state = args.local_momentum > 0
+            cv = torch.randn(4, n_par, generator=gen) * 0.1 if need_state else None
+            ce = torch.randn(4, n_par, generator=gen) * 0.1 if args.error_type == "local" else None
+            rm, om = make_model(seed), make_model(seed)
+            om._flat_params = FlatParams(om, "cpu", layout="reference")
+            clone = lambda t: None if t is None else t.clone()      # noqa: E731
+            r_cv, r_ce, o_cv, o_ce = clone(cv), clone(ce), clone(cv), clone(ce)
+            r_tx, r_res = ref_worker.process_batch([ids, x, y], rm, ps.clone(), clone(cw), r_ce, r_cv, compute_loss,
+                                                   compute_loss, args)
+            o_tx, o_res = our_worker.process_batch([ids, x, y], om, ps.clone(), clone(cw), o_ce, o_cv, compute_loss,
+                                                   compute_loss, args)
+            if cid != -1:
+                worst = max(worst, float((r_tx.reshape(-1) - o_tx.reshape(-1)).abs().max()))
+            worst = max(worst, float(np.abs(np.asarray(r_res, dtype=np.float64)
+                                            - np.asarray([float(t) for t in o_res], dtype=np.float64)).max()))
+            # the weights the client actually computed with
+            worst = max(worst, float((ref_utils_get(rm) - ref_utils_get(om)).abs().max()))
+        out[name] = worst
+
     # ---- models: same weights, same input -> same output and same parameter gradients ---------------------
     import models as ref_models
     from commefficient_b200 import models as our_models
