@@ -372,6 +372,8 @@ class FedModel:
         """Tell the model that its training batches come from a rank-sharded ``FedSampler`` (one whose loader
         only materialises this rank's clients): the round's global client ids / sample counts are then read
         from ``sampler.rounds`` instead of from the batch.  Call before the first iteration."""
+        if self.rt.world_size > 1 and getattr(sampler, "seed", None) is None:
+            raise ValueError("attach_sampler: a rank-sharded FedSampler needs a seed (every rank must draw the same rounds)")
         sampler.rank, sampler.world_size = self.rt.rank, self.rt.world_size
         sampler.by_owner = self._by_owner()
         self.round_source = sampler if self.rt.world_size > 1 else None
