@@ -23,5 +23,21 @@ for _ in range(3):
     g = tfm.gelu_tanh(x)
     g.backward(torch.ones_like(g))
     tc.colsum_acc(x.detach(), torch.zeros(4 * E, device="cuda"))
+# round-2 additions: GELU inside the MLP GEMM epilogues, segment BatchNorm on fp32 activations
+a = (torch.randn(8192, E, device="cuda") * 0.5).bfloat16()
+wfc = (torch.randn(4 * E, E, device="cuda") * 0.05).bfloat16()
+bias = torch.zeros(4 * E, device="cuda")
+gdy = (torch.randn(8192, E, device="cuda") * 0.5).bfloat16()
+wpr = (torch.randn(4 * E, E, device="cuda") * 0.05).bfloat16()
+xbn = torch.randn(128, 64, 32, 32, device="cuda").contiguous(memory_format=torch.channels_last).requires_grad_(True)
+seg = torch.repeat_interleave(torch.arange(16, device="cuda"), 8)
+cnt = torch.full((16,), 8.0, device="cuda")
+gam = torch.ones(64, device="cuda", requires_grad=True)
+bet = torch.zeros(64, device="cuda", requires_grad=True)
+for _ in range(2):
+    pre, act = tc.gemm_tn_gelu(a, wfc, bias)
+    tc.gemm_tn_gelu_grad(gdy, wpr, pre)
+    ybn, _m, _v = tfm.segment_batch_norm(xbn, gam, bet, seg, cnt, 16, 1e-5)
+    ybn.backward(torch.ones_like(ybn))
 torch.cuda.synchronize()
 print("ok")
