@@ -15,7 +15,7 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * models: ResNet9 (plain / BatchNorm / 1-channel 62-class), ResNet18, FixupResNet9, FixupResNet18, ResNet101LN --
     the reference's ``state_dict`` loads with ``strict=True`` and output and parameter gradients agree;
   * ``FedSampler``: with the same numpy seed both draw the same clients and samples in every round;
-  * datasets: FedCIFAR10 / FedEMNIST / FedPERSONA (+ collate) over the same client files return the same items,
+  * datasets: FedCIFAR10 / FedEMNIST / FedImageNet / FedPERSONA (+ collate) over the same client files return the same items,
     iid and non-iid (PersonaChat with more than one personality permutation and validation indexing are the
     documented departures Q14 / Q15 and are not compared);
   * CLI: all 55 reference flags exist with the same dest and default and parse the same command line;
@@ -288,6 +288,12 @@ def main():
         lambda **kw: our_data.FedEMNIST(tmp, "EMNIST", None, kw["iid"], kw["n"], train=kw["train"], download=False),
         [dict(iid=False, n=12, train=True), dict(iid=False, n=24, train=True), dict(iid=True, n=5, train=True),
          dict(iid=False, n=None, train=False)])
+    tmp = tempfile.mkdtemp()
+    our_data.write_synthetic_imagenet(tmp, num_classes=4, images_per_class=3, val_per_class=2)
+    out["data/fed_imagenet_items"] = compare_sets(
+        lambda **kw: ref_data.FedImageNet(tmp, "ImageNet", None, kw["iid"], kw["n"], train=kw["train"], download=False),
+        lambda **kw: our_data.FedImageNet(tmp, "ImageNet", None, kw["iid"], kw["n"], train=kw["train"], download=False),
+        [dict(iid=False, n=4, train=True), dict(iid=True, n=3, train=True), dict(iid=False, n=None, train=False)])
     # PersonaChat: training items with one personality permutation (more than one, and validation indexing, are the
     # documented departures Q14 / Q15), then the collate function on the same items
     tmp = tempfile.mkdtemp()

@@ -175,6 +175,12 @@ def _ensure_synthetic(args):
                                          seed=args.seed)
     elif args.dataset_name == "EMNIST":
         data_utils.write_synthetic_emnist(d, num_clients=args.num_clients or 3500, seed=args.seed)
+    elif args.dataset_name == "ImageNet":
+        # one client per class (wnid), as in the real tree; a handful of small JPEGs per class
+        data_utils.write_synthetic_imagenet(d, num_classes=args.num_clients or 8, images_per_class=4, val_per_class=2,
+                                            seed=args.seed)
+        # (FedImageNet derives stats.json from the tree on first use: do that once, here, before the other ranks look)
+        data_utils.FedImageNet(d, "ImageNet", None, train=True, download=False)
     else:
         raise ValueError("no synthetic generator for dataset %r" % args.dataset_name)
 

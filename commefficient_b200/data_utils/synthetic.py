@@ -15,7 +15,7 @@ import os
 import numpy as np
 import torch
 
-__all__ = ["write_synthetic_cifar", "write_synthetic_emnist", "write_synthetic_persona",
+__all__ = ["write_synthetic_cifar", "write_synthetic_emnist", "write_synthetic_persona", "write_synthetic_imagenet",
            "synthetic_image_batch"]
 
 
@@ -126,6 +126,27 @@ def write_synthetic_persona(dataset_dir, num_clients=64, dialogs_per_client=2, u
                    "train_utterances_per_dialog": train_upd,
                    "val_utterances_per_dialog": [len(d["utterances"]) for d in val]}, f)
     return dataset_dir
+
+
+def write_synthetic_imagenet(dataset_dir, num_classes=4, images_per_class=3, val_per_class=2, size=(48, 40), seed=0):
+    """An ImageNet-shaped folder tree that ``torchvision.datasets.ImageNet`` (and therefore ``FedImageNet``, ours and
+    the reference's: data_utils/fed_imagenet.py:11-75) opens: ``meta.bin`` plus ``train/<wnid>/*.JPEG`` and
+    ``val/<wnid>/*.JPEG`` -- class-prototype + noise images, one client per wnid."""
+    from PIL import Image
+    rng = np.random.RandomState(seed)
+    wnids = ["n%08d" % (1000 + 7 * c) for c in range(num_classes)]
+    protos = rng.randint(0, 256, size=(num_classes, size[1], size[0], 3)).astype(np.float32)
+    for split, per in (("train", images_per_class), ("val", val_per_class)):
+        for c, wnid in enumerate(wnids):
+            d = os.path.join(dataset_dir, split, wnid)
+            os.makedirs(d, exist_ok=True)
+            for i in range(per):
+                img = np.clip(protos[c] + rng.normal(0, 24.0, protos[c].shape), 0, 255).astype(np.uint8)
+                Image.fromarray(img).save(os.path.join(d, "%s_%d.JPEG" % (wnid, i)), quality=90)
+    wnid_to_classes = {w: ("synthetic class %d" % c,) for c, w in enumerate(wnids)}
+    val_wnids = [w for w in wnids for _ in range(val_per_class)]
+    torch.save((wnid_to_classes, val_wnids), os.path.join(dataset_dir, "meta.bin"))
+    return wnids
 
 
 def synthetic_image_batch(num_clients, per_client, num_classes=10, shape=(3, 32, 32), seed=0,

@@ -259,3 +259,24 @@ def test_public_header_declares_every_exported_entry_point():
     declared = set(re.findall(r"\b(ceb_[a-z0-9_]+)\s*\(", header))
     assert exported - declared == set(), "exported but not declared: %s" % sorted(exported - declared)
     assert declared - exported == set(), "declared but not exported: %s" % sorted(declared - exported)
+
+
+def test_fed_imagenet_on_a_synthetic_folder_tree(tmp_path):
+    """FedImageNet (one client per wnid) over an ImageNet-shaped tree written by write_synthetic_imagenet: natural and
+    iid partitions, the ImageNet train / val transforms, and a round through FedSampler + DataLoader."""
+    from torch.utils.data import DataLoader
+    from commefficient_b200 import data_utils
+    root = str(tmp_path)
+    wnids = data_utils.write_synthetic_imagenet(root, num_classes=4, images_per_class=3, val_per_class=2)
+    assert len(wnids) == 4
+    train = data_utils.FedImageNet(root, "ImageNet", data_utils.imagenet_train_transforms, False, 4, train=True, download=False)
+    assert len(train) == 12 and train.num_clients == 4 and list(train.data_per_client) == [3, 3, 3, 3]
+    cid, img, target = train[7]
+    assert int(cid) == 2 and int(target) == 2 and tuple(img.shape) == (3, 224, 224)
+    val = data_utils.FedImageNet(root, "ImageNet", data_utils.imagenet_val_transforms, train=False, download=False)
+    assert len(val) == 8 and tuple(val[0][1].shape) == (3, 224, 224) and int(val[0][0]) == -1
+    iid = data_utils.FedImageNet(root, "ImageNet", data_utils.imagenet_val_transforms, True, 3, train=True, download=False)
+    assert iid.num_clients == 3 and sorted(iid.data_per_client) == [4, 4, 4]
+    sampler = data_utils.FedSampler(train, num_workers=2, local_batch_size=2, seed=0)
+    ids, x, y = next(iter(DataLoader(train, batch_sampler=sampler)))
+    assert x.shape == (4, 3, 224, 224) and len(set(ids.tolist())) == 2 and torch.equal(ids, y)
