@@ -87,11 +87,12 @@ def run_batches(model, opt, lr_scheduler, loader, training, epoch_fraction, args
         lr_scheduler.step()
         if lr_scheduler.get_last_lr()[0] == 0:
             opt.step()          # publishes the LR for fedavg (no-op otherwise)
-        if args.local_batch_size == -1:
-            if torch.unique(batch[0]).numel() < args.num_workers:
-                continue        # not enough clients left in this epoch
-        elif batch[0].numel() < args.num_workers * args.local_batch_size:
-            continue            # incomplete round
+        # (the round as a whole: with rank-sharded loading the batch is only this rank's share of it)
+        round_clients, round_samples = model.round_shape(batch)
+        if (round_clients < args.num_workers if args.local_batch_size == -1
+                else round_samples < args.num_workers * args.local_batch_size):
+            model.skip_round()  # not enough clients left in this epoch / incomplete round
+            continue
         loss, acc, dl, ul = model(batch)
         deferred = getattr(args, "defer_results", False)
         if deferred:

@@ -395,6 +395,24 @@ class FedModel:
         dev.record_stream(main)
         return dev
 
+    def round_shape(self, batch):
+        """``(clients, samples)`` of the WHOLE round ``batch`` belongs to.  With a rank-sharded sampler the batch
+        holds only this rank's share, so a driver that decides "incomplete round, skip it" (the reference's loop:
+        cv_train.py:196-204) must ask here, not count the batch."""
+        src = self.round_source
+        if src is not None and src.rounds:
+            meta = src.rounds[0]
+            return len(meta.ids), int(meta.counts.sum())
+        ids = batch[0]
+        ids = ids if torch.is_tensor(ids) else torch.as_tensor(np.asarray(ids))
+        return int(torch.unique(ids).numel()), int(ids.numel())
+
+    def skip_round(self) -> None:
+        """The driver drops the batch it just fetched without running it: drop its schedule entry too."""
+        src = self.round_source
+        if src is not None and src.rounds:
+            src.rounds.popleft()
+
     def check_replicas(self) -> None:
         """Raise if the ranks' weight replicas are not bit-identical.  Every rank applies the same deterministic
         server update to its own replica and weights are never re-broadcast (module docstring), so a divergence --

@@ -131,16 +131,18 @@ def run_batches(model, opt, lr_scheduler, loader, args, timer, training, epoch=N
     losses = []
     for i, batch in enumerate(loader):
         if i > 2 and args.do_test and i < spe - 10:
+            model.skip_round()
             continue
         if i > spe * epoch_fraction:
             break
         lr_scheduler.step()
         if lr_scheduler.get_last_lr()[0] == 0:
             opt.step()
-        if args.local_batch_size == -1:
-            if torch.unique(batch[0]).numel() < args.num_workers:
-                continue
-        elif batch[0].numel() < args.num_workers * args.local_batch_size:
+        # (the round as a whole: with rank-sharded loading the batch is only this rank's share of it)
+        round_clients, round_samples = model.round_shape(batch)
+        if (round_clients < args.num_workers if args.local_batch_size == -1
+                else round_samples < args.num_workers * args.local_batch_size):
+            model.skip_round()
             continue
         loss, dl, ul = model(batch)
         opt.step()              # before the byte counts / loss are read: with --defer_results those are lazy

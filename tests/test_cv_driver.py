@@ -61,3 +61,37 @@ def test_checkpoint_resume_and_finetune_through_the_driver(tmp_path):
                           "--local_batch_size", "2", "--finetune", "--finetuned_from", "CIFAR10", "--finetune_path", ck]
                          + sketch)
     assert fine is not None and "nan" not in str(fine).lower()
+
+
+def _two_rank_driver(rank, world, out_dir, argv):
+    from commefficient_b200.parallel import runtime
+    runtime.init_runtime(rank=rank, world_size=world, device="cpu", backend="gloo")
+    summary = cv_train.main(argv)
+    torch.save({"summary": summary}, os.path.join(out_dir, "r%d.pt" % rank))
+
+
+def test_driver_on_two_gloo_ranks_matches_one_rank(tmp_path):
+    """The whole driver as an SPMD job (two gloo ranks, rank-sharded data loading through attach_sampler; the replica
+    checksum runs every second round) ends close to where the one-rank run ends: not bit-equal, because the random
+    crops / flips of the training transform are drawn per loaded sample, and each rank now loads only its own."""
+    from commefficient_b200.parallel import runtime
+    argv = ["--synthetic", "--dataset_dir", str(tmp_path / "data"), "--device", "cpu", "--num_epochs", "1",
+            "--pivot_epoch", "0.5", "--lr_scale", "0.05", "--num_cols", "2000", "--num_rows", "3", "--k", "300",
+            "--valid_batch_size", "8", "--train_dataloader_workers", "0", "--val_dataloader_workers", "0",
+            "--dataset_name", "CIFAR10", "--model", "ResNet9", "--num_clients", "10", "--num_workers", "4",
+            "--local_batch_size", "4", "--mode", "sketch", "--error_type", "virtual", "--local_momentum", "0",
+            "--virtual_momentum", "0.9", "--checkpoint"]
+    one = str(tmp_path / "one")
+    cv_train.main(argv + ["--checkpoint_path", one])
+    two = str(tmp_path / "two")
+    out_dir = str(tmp_path / "out")
+    os.makedirs(out_dir)
+    runtime.spawn(_two_rank_driver, 2, args=(out_dir, argv + ["--checkpoint_path", two, "--replica_check_every", "2"]),
+                  device="cpu")
+    w1 = torch.load(os.path.join(one, "ResNet9.pt"))
+    w2 = torch.load(os.path.join(two, "ResNet9.pt"))
+    assert os.path.exists(os.path.join(two, "ResNet9.fedstate.pt.rank0")) and os.path.exists(
+        os.path.join(two, "ResNet9.fedstate.pt.rank1"))
+    num = sum(float((w1[k].float() - w2[k].float()).pow(2).sum()) for k in w1 if w1[k].is_floating_point())
+    den = sum(float(w1[k].float().pow(2).sum()) for k in w1 if w1[k].is_floating_point())
+    assert math.sqrt(num / den) < 1e-2
