@@ -80,3 +80,38 @@ def test_gpt2_client_batching_equals_per_client_rounds():
     l_c, w_c = run(True)
     np.testing.assert_allclose(l_b, l_c, rtol=1e-5)
     torch.testing.assert_close(w_b, w_c, rtol=1e-4, atol=1e-6)
+
+
+def _two_rank_gpt2(rank, world, out_dir, argv):
+    from commefficient_b200.parallel import runtime
+    runtime.init_runtime(rank=rank, world_size=world, device="cpu", backend="gloo")
+    os.chdir(out_dir)
+    out = train(argv)
+    torch.save(out, os.path.join(out_dir, "r%d.pt" % rank))
+
+
+def test_gpt2_driver_on_two_gloo_ranks(tmp_path):
+    """The PersonaChat driver as a two-rank SPMD job: each rank tokenises only its own clients (rank-sharded
+    FedSampler), rounds are not skipped, and the validation numbers are those of the one-rank run (no dropout, no
+    data augmentation: the two runs see the same gradients)."""
+    from commefficient_b200.parallel import runtime
+    argv = ["--dataset_name", "PERSONA", "--synthetic", "--dataset_dir", str(tmp_path / "persona"),
+            "--num_clients", "8", "--model_checkpoint", "gpt2-tiny", "--num_workers", "2",
+            "--local_batch_size", "2", "--mode", "uncompressed", "--error_type", "none", "--local_momentum", "0",
+            "--virtual_momentum", "0.9", "--num_epochs", "1", "--device", "cpu", "--valid_batch_size", "2",
+            "--lr_scale", "0.1", "--seed", "7"]
+    one_dir = tmp_path / "one"
+    one_dir.mkdir()
+    cwd = os.getcwd()
+    os.chdir(one_dir)
+    try:
+        one = train(argv)
+    finally:
+        os.chdir(cwd)
+    out_dir = tmp_path / "two"
+    out_dir.mkdir()
+    runtime.spawn(_two_rank_gpt2, 2, args=(str(out_dir), argv), device="cpu")
+    r0 = torch.load(out_dir / "r0.pt", weights_only=False)
+    r1 = torch.load(out_dir / "r1.pt", weights_only=False)
+    assert abs(r0["val_ppl"] - r1["val_ppl"]) < 1e-6
+    assert abs(r0["val_ppl"] - one["val_ppl"]) / one["val_ppl"] < 0.05
