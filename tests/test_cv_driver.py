@@ -95,3 +95,35 @@ def test_driver_on_two_gloo_ranks_matches_one_rank(tmp_path):
     num = sum(float((w1[k].float() - w2[k].float()).pow(2).sum()) for k in w1 if w1[k].is_floating_point())
     den = sum(float(w1[k].float().pow(2).sum()) for k in w1 if w1[k].is_floating_point())
     assert math.sqrt(num / den) < 1e-2
+
+
+_SKETCH = ["--mode", "sketch", "--error_type", "virtual", "--local_momentum", "0", "--virtual_momentum", "0.9"]
+_C10 = ["--dataset_name", "CIFAR10", "--num_clients", "10", "--local_batch_size", "4", "--model", "ResNet9", "--num_workers", "4"]
+
+
+@pytest.mark.parametrize("name,flags", [
+    ("whole_client_batches", _C10 + ["--local_batch_size", "-1"] + _SKETCH),
+    ("true_topk_local_momentum", _C10 + ["--mode", "true_topk", "--error_type", "virtual", "--local_momentum", "0.9",
+                                         "--virtual_momentum", "0"]),
+    ("topk_down", _C10 + ["--mode", "true_topk", "--error_type", "virtual", "--local_momentum", "0",
+                          "--virtual_momentum", "0.9", "--topk_down"]),
+    ("dp_worker", _C10 + ["--mode", "uncompressed", "--error_type", "none", "--local_momentum", "0", "--dp",
+                          "--dp_mode", "worker", "--noise_multiplier", "0.01", "--l2_norm_clip", "1.0"]),
+    ("dp_server", _C10 + ["--mode", "uncompressed", "--error_type", "none", "--local_momentum", "0", "--dp",
+                          "--dp_mode", "server", "--noise_multiplier", "0.01"]),
+    ("iid_eval_before_start", _C10 + ["--iid", "--eval_before_start"] + _SKETCH),
+    ("emnist_whole_clients", ["--dataset_name", "EMNIST", "--num_clients", "12", "--local_batch_size", "-1", "--model",
+                              "ResNet9", "--num_workers", "4"] + _SKETCH),
+    ("fixup_resnet9_clipped", _C10 + ["--model", "FixupResNet9", "--max_grad_norm", "1.0"] + _SKETCH),
+    ("microbatches", _C10 + ["--microbatch_size", "2", "--mode", "uncompressed", "--error_type", "none",
+                             "--local_momentum", "0"]),
+    ("batchnorm_resnet9", _C10 + ["--batchnorm"] + _SKETCH),
+    ("test_mode", _C10 + ["--test"] + _SKETCH),
+])
+def test_driver_flag_combinations(tmp_path, name, flags):
+    """One epoch through the driver for the flag combinations the reference's README / scripts use: nothing raises,
+    the summary row is finite."""
+    summary = _run(tmp_path, flags)
+    assert summary is not None, name
+    for key in ("train_loss", "test_loss", "test_acc"):
+        assert math.isfinite(float(summary[key])), (name, key, summary[key])

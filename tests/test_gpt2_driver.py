@@ -115,3 +115,30 @@ def test_gpt2_driver_on_two_gloo_ranks(tmp_path):
     r1 = torch.load(out_dir / "r1.pt", weights_only=False)
     assert abs(r0["val_ppl"] - r1["val_ppl"]) < 1e-6
     assert abs(r0["val_ppl"] - one["val_ppl"]) / one["val_ppl"] < 0.05
+
+
+import pytest  # noqa: E402
+
+_GPT2_BASE = ["--dataset_name", "PERSONA", "--synthetic", "--num_clients", "8", "--model_checkpoint", "gpt2-tiny",
+              "--num_workers", "2", "--num_epochs", "1", "--device", "cpu", "--valid_batch_size", "2", "--lr_scale", "0.1",
+              "--k", "2000", "--num_cols", "20000"]
+
+
+@pytest.mark.parametrize("name,flags", [
+    ("local_topk", ["--local_batch_size", "2", "--mode", "local_topk", "--error_type", "local", "--local_momentum", "0.9",
+                    "--virtual_momentum", "0"]),
+    ("true_topk", ["--local_batch_size", "2", "--mode", "true_topk", "--error_type", "virtual", "--local_momentum", "0",
+                   "--virtual_momentum", "0.9"]),
+    ("fedavg", ["--local_batch_size", "-1", "--mode", "fedavg", "--error_type", "none", "--local_momentum", "0",
+                "--fedavg_batch_size", "2", "--num_fedavg_epochs", "1"]),
+    ("microbatched_whole_clients", ["--local_batch_size", "-1", "--microbatch_size", "2", "--mode", "sketch", "--error_type",
+                                    "virtual", "--local_momentum", "0", "--virtual_momentum", "0.9"]),
+    ("four_candidates_two_permutations", ["--local_batch_size", "2", "--num_candidates", "4", "--personality_permutations",
+                                          "2", "--mode", "uncompressed", "--error_type", "none", "--local_momentum", "0"]),
+    ("test_mode", ["--local_batch_size", "2", "--test", "--mode", "sketch", "--error_type", "virtual", "--local_momentum",
+                   "0", "--virtual_momentum", "0.9"]),
+])
+def test_gpt2_driver_flag_combinations(tmp_path, monkeypatch, name, flags):
+    monkeypatch.chdir(tmp_path)
+    out = train(_GPT2_BASE + ["--dataset_dir", str(tmp_path / "persona")] + flags)
+    assert out["val_ppl"] == out["val_ppl"] and out["val_ppl"] < 1e4 and 0.0 <= out["val_acc"] <= 1.0, (name, out)
