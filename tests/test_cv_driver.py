@@ -127,3 +127,28 @@ def test_driver_flag_combinations(tmp_path, name, flags):
     assert summary is not None, name
     for key in ("train_loss", "test_loss", "test_acc"):
         assert math.isfinite(float(summary[key])), (name, key, summary[key])
+
+
+def test_driver_two_ranks_with_per_client_state(tmp_path):
+    """local_topk with local momentum / error on two gloo ranks through the driver: clients are assigned to the rank
+    that owns their state rows (id mod 2), the sampler shards by the same rule, whole-client batches; the replicas
+    stay identical (checked every round) and the resume sidecars hold each rank's rows."""
+    from commefficient_b200.parallel import runtime
+    argv = ["--synthetic", "--dataset_dir", str(tmp_path / "data"), "--device", "cpu", "--num_epochs", "1",
+            "--pivot_epoch", "0.5", "--lr_scale", "0.05", "--k", "300", "--valid_batch_size", "8",
+            "--train_dataloader_workers", "0", "--val_dataloader_workers", "0", "--dataset_name", "CIFAR10", "--model",
+            "ResNet9", "--num_clients", "10", "--num_workers", "4", "--local_batch_size", "-1", "--mode", "local_topk",
+            "--error_type", "local", "--local_momentum", "0.9", "--virtual_momentum", "0", "--checkpoint",
+            "--checkpoint_path", str(tmp_path / "ck"), "--replica_check_every", "1"]
+    out_dir = str(tmp_path / "out")
+    os.makedirs(out_dir)
+    runtime.spawn(_two_rank_driver, 2, args=(out_dir, argv), device="cpu")
+    s0 = torch.load(os.path.join(out_dir, "r0.pt"), weights_only=False)["summary"]
+    s1 = torch.load(os.path.join(out_dir, "r1.pt"), weights_only=False)["summary"]
+    assert s0 is not None and math.isfinite(float(s0["train_loss"]))
+    assert float(s0["train_loss"]) == float(s1["train_loss"]) and float(s0["test_acc"]) == float(s1["test_acc"])
+    side = [torch.load(os.path.join(str(tmp_path / "ck"), "ResNet9.fedstate.pt.rank%d" % r), weights_only=False)
+            for r in range(2)]
+    owned = [set(int(c) for c in s["client_velocities"].keys()) for s in side]
+    assert owned[0] and owned[1] and all(c % 2 == 0 for c in owned[0]) and all(c % 2 == 1 for c in owned[1])
+    assert [set(int(c) for c in s["client_errors"].keys()) for s in side] == owned
