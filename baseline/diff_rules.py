@@ -12,6 +12,10 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
     clipping, microbatches (the reference sums microbatch means -- quirk Q6 -- ours under
     ``--compat_microbatch_sum``); ``process_batch`` (reference fed_worker.py:140-182) for a training client, a client
     with stale weights (``--topk_down``), a client with local momentum / error rows, and a validation shard;
+  * whole rounds: the reference's functions assembled the way its FedModel / FedOptimizer drive them (per-client
+    ``process_batch``, sum, divide by the round's samples, ``get_server_update``, subtract) against this framework's
+    ``FedModel`` / ``FedOptimizer`` over four rounds with recurring clients: uncompressed + momentum, sketch, true_topk,
+    local_topk with persistent per-client momentum / error rows, clipping + weight decay, FedAvg local SGD;
   * models: ResNet9 (plain / BatchNorm / 1-channel 62-class), ResNet18, FixupResNet9, FixupResNet18, ResNet101LN --
     the reference's ``state_dict`` loads with ``strict=True`` and output and parameter gradients agree;
   * ``FedSampler``: with the same numpy seed both draw the same clients and samples in every round;
@@ -182,6 +186,90 @@ def main():
                                             - np.asarray([float(t) for t in o_res], dtype=np.float64)).max()))
             # the weights the client actually computed with
             worst = max(worst, float((ref_utils_get(rm) - ref_utils_get(om)).abs().max()))
+        out[name] = worst
+
+    # ---- whole rounds: the reference's own functions assembled the way its FedModel / FedOptimizer drive them
+    #      (process_batch per client, sum, / round samples, get_server_update, weights -= update:
+    #      fed_aggregator.py:213-335,429-458) against this framework's FedModel / FedOptimizer, several rounds
+    from commefficient_b200.fed_aggregator import FedModel as OurFedModel, FedOptimizer as OurFedOptimizer
+    from commefficient_b200.utils import make_args
+
+    loop_cases = {
+        "rounds/uncompressed_momentum": dict(mode="uncompressed", error_type="none", virtual_momentum=0.9),
+        "rounds/sketch_virtual": dict(mode="sketch", error_type="virtual", virtual_momentum=0.9, num_cols=4096, num_rows=3,
+                                      num_blocks=2, k=23),
+        "rounds/true_topk_virtual": dict(mode="true_topk", error_type="virtual", virtual_momentum=0.9, k=23),
+        "rounds/local_topk_local_state": dict(mode="local_topk", error_type="local", local_momentum=0.9,
+                                              virtual_momentum=0.0, k=23),
+        "rounds/uncompressed_clip_wd": dict(mode="uncompressed", error_type="none", virtual_momentum=0.0,
+                                            max_grad_norm=0.05, weight_decay=5e-4),
+    }
+    loop_cases["rounds/fedavg_local_sgd"] = dict(mode="fedavg", error_type="none", virtual_momentum=0.9,
+                                                 num_fedavg_epochs=2, fedavg_batch_size=2, fedavg_lr_decay=0.9)
+    n_clients, per_round, lr = 6, 3, 0.1
+    for name, kw in loop_cases.items():
+        rargs = base(grad_size=n_par, num_workers=per_round, **kw)
+        torch.manual_seed(42)
+        rm = make_model(7)
+        ps = ref_utils_get(rm).clone()
+        shape = (rargs.num_rows, rargs.num_cols) if rargs.mode == "sketch" else (n_par,)
+        Vv, Ve = torch.zeros(shape), torch.zeros(shape)
+        need_v, need_e = rargs.local_momentum > 0, rargs.error_type == "local"
+        cv = torch.zeros(n_clients, n_par) if need_v else None
+        ce = torch.zeros(n_clients, n_par) if need_e else None
+        oargs = make_args(device="cpu", dataset_name="CIFAR10", num_clients=n_clients, num_workers=per_round,
+                          local_batch_size=-1, precision="fp32", flat_layout="reference", num_results_train=2,
+                          num_results_val=2, weight_decay=kw.get("weight_decay", 0.0), watchdog_timeout=0.0,
+                          **{"local_momentum": 0.0, **{k_: v_ for k_, v_ in kw.items() if k_ != "weight_decay"}})
+        om = make_model(7)
+        fed = OurFedModel(om, compute_loss, oargs, compute_loss)
+        opt = OurFedOptimizer(torch.optim.SGD(om.parameters(), lr=1), oargs)
+        opt.param_groups[0]["lr"] = lr
+        fedavg = rargs.mode == "fedavg"
+        if fedavg:
+            for k_ in ("num_fedavg_epochs", "fedavg_batch_size", "fedavg_lr_decay"):
+                setattr(rargs, k_, kw[k_])
+            opt.step()                                   # publishes the LR the clients' local SGD uses
+        fed.train(True)
+        gen = torch.Generator().manual_seed(77)
+        worst = 0.0
+        for rnd in range(4):
+            clients = [(rnd * 2 + j) % n_clients for j in range(per_round)]
+            sizes = [3, 5, 4]
+            xs = [torch.randn(n, 10, generator=gen) for n in sizes]
+            ys = [torch.randint(0, 4, (n,), generator=gen) for n in sizes]
+            # reference side
+            total = torch.zeros(shape)
+            for c, x, y in zip(clients, xs, ys):
+                ids = torch.full((x.shape[0],), c, dtype=torch.long)
+                if fedavg:
+                    # the reference's local SGD (fed_worker.py:61-113), restated: chunks of fedavg_batch_size,
+                    # num_fedavg_epochs passes, step size lr * decay^step on the mean gradient; upload (w0 - w) * n
+                    w_local, step = ps.clone(), 0
+                    for _ep in range(rargs.num_fedavg_epochs):
+                        for lo in range(0, x.shape[0], rargs.fedavg_batch_size):
+                            xc, yc = x[lo:lo + rargs.fedavg_batch_size], y[lo:lo + rargs.fedavg_batch_size]
+                            g_sum, _r = ref_worker.process_batch([ids[:xc.shape[0]], xc, yc], rm, w_local.clone(), None,
+                                                                 None, None, compute_loss, compute_loss, rargs)
+                            w_local = w_local - (g_sum / xc.shape[0]) * lr * rargs.fedavg_lr_decay ** step
+                            step += 1
+                    total += (ps - w_local) * x.shape[0]
+                    continue
+                tx, _res = ref_worker.process_batch([ids, x, y], rm, ps.clone(), None, ce, cv, compute_loss, compute_loss,
+                                                    rargs)
+                total += tx.reshape(shape)
+                # (the reference's worker loop writes the client rows back: fed_worker.py:124-134 via shared memory)
+            grad = total / float(sum(sizes))
+            upd, Vv, Ve = ref_agg.get_server_update(grad, Vv, Ve, rargs, 1 if fedavg else lr)
+            ps = ps - upd.reshape(-1)
+            # this framework
+            order = np.argsort(clients, kind="stable")
+            ids = torch.cat([torch.full((sizes[i],), clients[i], dtype=torch.long) for i in order])
+            fed((ids, torch.cat([xs[i] for i in order]), torch.cat([ys[i] for i in order])))
+            opt.step()
+            ours = fed.fp.to_reference_order(fed.fp.flat).detach()
+            worst = max(worst, float((ours - ps).abs().max()))
+        fed.rt.shutdown()
         out[name] = worst
 
     # ---- models: same weights, same input -> same output and same parameter gradients ---------------------
