@@ -438,3 +438,19 @@ def test_gloo_two_ranks_with_replica_check_every_round():
     bit-identical)."""
     ranks = _spawn(2, "cpu", "sketch", "gloo", replica_check_every=1)
     torch.testing.assert_close(ranks[0]["w"], ranks[1]["w"], rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("world,mode,kw", [(4, "sketch", {}), (8, "sketch", {}),
+                                           (8, "local_topk", {"error_type": "local", "local_momentum": 0.9})])
+def test_gloo_more_ranks_than_clients_per_rank(world, mode, kw):
+    """Six clients a round over four ranks (2, 2, 1, 1) and over eight ranks (two of them idle; with per-client state
+    the owner rule leaves ranks 6 and 7 without a client): replicas stay identical and equal the one-rank run."""
+    ranks = _spawn(world, "cpu", mode, "gloo", **kw)
+    for r in ranks[1:]:
+        torch.testing.assert_close(ranks[0]["w"], r["w"], rtol=0, atol=0)
+        assert r["losses"] == ranks[0]["losses"]
+    w1, l1, v1, fed = _fed_run("cpu", mode, "auto", **kw)
+    fed.rt.shutdown()
+    np.testing.assert_allclose(ranks[0]["losses"], l1, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(ranks[0]["val"], v1, rtol=1e-4, atol=1e-5)
+    assert (ranks[0]["w"] - w1).norm() / w1.norm() < 1e-5
