@@ -352,7 +352,7 @@ class _CountingClients(torch.utils.data.Dataset):
         return i // 5, self.x[i], self.y[i]
 
 
-def _sharded_loader_run(device, backend, attach):
+def _sharded_loader_run(device, backend, attach, workers=4):
     from torch.utils.data import DataLoader
     from commefficient_b200 import models
     from commefficient_b200.cv_train import compute_loss_train, compute_loss_val
@@ -360,7 +360,7 @@ def _sharded_loader_run(device, backend, attach):
     from commefficient_b200.fed_aggregator import FedModel, FedOptimizer
     from commefficient_b200.utils import make_args
     torch.manual_seed(0)
-    args = make_args(mode="sketch", num_workers=4, num_clients=12, local_batch_size=3, k=300, num_cols=4000, num_rows=5,
+    args = make_args(mode="sketch", num_workers=workers, num_clients=12, local_batch_size=3, k=300, num_cols=4000, num_rows=5,
                      num_blocks=4, device=device, dataset_name="CIFAR10", precision="fp32", weight_decay=5e-4,
                      local_momentum=0.0, virtual_momentum=0.9, flat_layout="reference", backend=backend,
                      error_type="virtual")
@@ -384,9 +384,9 @@ def _sharded_loader_run(device, backend, attach):
     return w, losses, sorted(ds.loaded), fed
 
 
-def _sharded_rank_main(rank, world, out_dir):
+def _sharded_rank_main(rank, world, out_dir, workers=4):
     rt = runtime.init_runtime(rank=rank, world_size=world, device="cpu", backend="gloo")
-    w, losses, loaded, _fed = _sharded_loader_run("cpu", "gloo", attach=True)
+    w, losses, loaded, _fed = _sharded_loader_run("cpu", "gloo", attach=True, workers=workers)
     torch.save({"w": w, "losses": losses, "loaded": loaded}, os.path.join(out_dir, "r%d.pt" % rank))
     rt.shutdown()
 
@@ -454,3 +454,17 @@ def test_gloo_more_ranks_than_clients_per_rank(world, mode, kw):
     np.testing.assert_allclose(ranks[0]["losses"], l1, rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(ranks[0]["val"], v1, rtol=1e-4, atol=1e-5)
     assert (ranks[0]["w"] - w1).norm() / w1.norm() < 1e-5
+
+
+def test_rank_sharded_loader_with_one_client_per_round():
+    """One client per round on two ranks: sharding would leave a rank without a batch, so the sampler hands every rank
+    the whole round (and says so in the schedule); the run still equals the single-rank one."""
+    out_dir = tempfile.mkdtemp()
+    runtime.spawn(_sharded_rank_main, 2, args=(out_dir, 1), device="cpu")
+    r0, r1 = (torch.load(os.path.join(out_dir, "r%d.pt" % r)) for r in range(2))
+    torch.testing.assert_close(r0["w"], r1["w"], rtol=0, atol=0)
+    assert r0["loaded"] == list(range(60)) and r1["loaded"] == list(range(60))
+    w1, l1, _loaded, fed = _sharded_loader_run("cpu", "auto", attach=False, workers=1)
+    fed.rt.shutdown()
+    np.testing.assert_allclose(r0["losses"], l1, rtol=1e-4, atol=1e-5)
+    assert (r0["w"] - w1).norm() / w1.norm() < 1e-3
