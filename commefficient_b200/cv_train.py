@@ -67,7 +67,8 @@ def run_batches(model, opt, lr_scheduler, loader, training, epoch_fraction, args
     losses, accs = [], []
     if not training:
         for batch in loader:
-            if batch[0].numel() < args.valid_batch_size:
+            if model.val_batch_size(batch) < args.valid_batch_size:
+                model.skip_val_batch()
                 continue
             loss, acc = model(batch)
             losses.extend(loss)
@@ -206,8 +207,10 @@ def get_data_loaders(args, rank=0):
     # every rank builds the identical round schedule from the shared seed
     sampler = data_utils.FedSampler(train_ds, args.num_workers, args.local_batch_size, seed=args.seed)
     train_loader = DataLoader(train_ds, batch_sampler=sampler, num_workers=args.train_dataloader_workers)
-    test_loader = DataLoader(test_ds, batch_size=args.valid_batch_size * args.num_workers, shuffle=False,
-                             num_workers=args.val_dataloader_workers)
+    # sequential validation batches of valid_batch_size * num_workers samples; a rank loads only its own shards
+    val_sampler = data_utils.ShardedEvalSampler(len(test_ds), args.valid_batch_size * args.num_workers,
+                                                args.valid_batch_size)
+    test_loader = DataLoader(test_ds, batch_sampler=val_sampler, num_workers=args.val_dataloader_workers)
     return train_loader, test_loader
 
 
@@ -272,6 +275,7 @@ def main(argv=None):
     fed_model = FedModel(model, compute_loss_train, args, compute_loss_val)
     # each rank's loader decodes / augments only the clients that rank simulates
     fed_model.attach_sampler(train_loader.batch_sampler)
+    fed_model.attach_val_sampler(test_loader.batch_sampler)
     opt = FedOptimizer(base_opt, args)
     if args.resume:
         fed_model.load_fedstate(args.resume, opt)

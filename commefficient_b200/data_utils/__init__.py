@@ -1,7 +1,7 @@
 """Federated datasets, the round sampler, transforms and synthetic-data writers
 (reference package: /root/reference/CommEfficient/data_utils/)."""
 from .fed_dataset import FedDataset
-from .fed_sampler import FedSampler
+from .fed_sampler import FedSampler, ShardedEvalSampler
 from .fed_vision import FedCIFAR10, FedCIFAR100, FedEMNIST, FedImageNet
 from .fed_persona import (FedPERSONA, personachat_collate_fn, SimpleTokenizer, SPECIAL_TOKENS,
                           MODEL_INPUTS, ATTR_TO_SPECIAL_TOKEN)

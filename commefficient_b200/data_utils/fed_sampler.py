@@ -20,7 +20,7 @@ from typing import List, NamedTuple
 
 import numpy as np
 
-__all__ = ["FedSampler", "RoundMeta", "assign_clients"]
+__all__ = ["FedSampler", "RoundMeta", "assign_clients", "ShardedEvalSampler", "EvalMeta"]
 
 
 def assign_clients(unique_sorted: np.ndarray, world_size: int, by_owner: bool) -> List[np.ndarray]:
@@ -95,3 +95,48 @@ class FedSampler:
     def __len__(self):
         # number of samples, not rounds -- kept as in the reference (:70-71)
         return len(self.dataset)
+
+
+class EvalMeta(NamedTuple):
+    total: int             # samples of the whole validation batch
+    sharded: bool          # the yielded batch holds only this rank's shards, in order (else: the whole batch)
+
+
+class ShardedEvalSampler:
+    """Batch sampler for validation: sequential batches of ``batch_size`` samples (what
+    ``DataLoader(batch_size=valid_batch_size * num_workers, shuffle=False)`` yields in the reference's drivers),
+    of which a rank only loads the ``shard_size``-sample shards it will evaluate -- the same contiguous split of the
+    shard list over the ranks that ``FedModel._call_val`` uses.  ``rounds`` carries the size of every whole batch.
+    With one rank this is exactly the plain sequential loader."""
+
+    def __init__(self, num_items: int, batch_size: int, shard_size: int, rank: int = 0, world_size: int = 1):
+        self.num_items, self.batch_size, self.shard_size = int(num_items), int(batch_size), int(shard_size)
+        self.rank, self.world_size = int(rank), int(world_size)
+        self.rounds: "deque[EvalMeta]" = deque()
+
+    @staticmethod
+    def shard_bounds(total: int, shard_size: int):
+        return [(lo, min(total, lo + shard_size)) for lo in range(0, total, shard_size)]
+
+    def __iter__(self):
+        self.rounds.clear()
+        for start in range(0, self.num_items, self.batch_size):
+            total = min(self.batch_size, self.num_items - start)
+            if self.world_size == 1:
+                yield list(range(start, start + total))
+                continue
+            bounds = self.shard_bounds(total, self.shard_size)
+            parts = np.array_split(np.arange(len(bounds)), self.world_size)
+            sharded = all(len(p) for p in parts)
+            self.rounds.append(EvalMeta(total, sharded))
+            if not sharded:
+                yield list(range(start, start + total))
+                continue
+            idx = []
+            for si in parts[self.rank]:
+                lo, hi = bounds[int(si)]
+                idx.extend(range(start + lo, start + hi))
+            yield idx
+
+    def __len__(self):
+        return -(-self.num_items // self.batch_size)

@@ -304,6 +304,7 @@ class FedModel:
         self._result_ring = {}
         self._copy_stream = None
         self.round_source = None          # a rank-sharded FedSampler (attach_sampler)
+        self.val_source = None            # a rank-sharded ShardedEvalSampler (attach_val_sampler)
         self.tracer = PhaseTracer(getattr(args, "trace_phases", "") or "", getattr(args, "trace_every", 50),
                                   self.rt.rank, self._trace_max, self.device.type)
         _CURRENT = self
@@ -394,6 +395,23 @@ class FedModel:
         main.wait_stream(self._copy_stream)
         dev.record_stream(main)
         return dev
+
+    def attach_val_sampler(self, sampler) -> None:
+        """Validation batches come from a ``ShardedEvalSampler``: each rank loads only the shards it evaluates."""
+        sampler.rank, sampler.world_size = self.rt.rank, self.rt.world_size
+        self.val_source = sampler if self.rt.world_size > 1 else None
+
+    def val_batch_size(self, batch) -> int:
+        """Samples of the WHOLE validation batch ``batch`` belongs to (see ``round_shape``)."""
+        src = self.val_source
+        if src is not None and src.rounds:
+            return int(src.rounds[0].total)
+        return int(batch[0].shape[0])
+
+    def skip_val_batch(self) -> None:
+        src = self.val_source
+        if src is not None and src.rounds:
+            src.rounds.popleft()
 
     def round_shape(self, batch):
         """``(clients, samples)`` of the WHOLE round ``batch`` belongs to.  With a rank-sharded sampler the batch
@@ -569,12 +587,25 @@ class FedModel:
         args = self.args
         n = batch[0].shape[0]
         vb = args.valid_batch_size
+        meta = None
+        if self.val_source is not None:
+            if not self.val_source.rounds:
+                raise RuntimeError("attach_val_sampler: the sampler has no pending entry for this batch")
+            meta = self.val_source.rounds.popleft()
+            n = int(meta.total)
         shard_bounds = [(lo, min(n, lo + vb)) for lo in range(0, n, vb)]
         mine = np.array_split(np.arange(len(shard_bounds)), self.rt.world_size)[self.rt.rank]
         shards = []
+        offset = 0
         for si in mine:
             lo, hi = shard_bounds[si]
+            if meta is not None and meta.sharded:
+                # the loader produced only this rank's shards, one after the other
+                lo, hi = offset, offset + (hi - lo)
+                offset = hi
             shards.append([self._to_device(t[lo:hi]) for t in batch[1:]])
+        if meta is not None and meta.sharded and offset != batch[0].shape[0]:
+            raise RuntimeError("rank-sharded validation batch has %d rows, expected %d" % (batch[0].shape[0], offset))
         local = self.worker.run_val(shards)
         if self.rt.world_size > 1:
             sizes = [len(c) for c in np.array_split(np.arange(len(shard_bounds)), self.rt.world_size)]

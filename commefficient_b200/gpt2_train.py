@@ -119,6 +119,7 @@ def run_batches(model, opt, lr_scheduler, loader, args, timer, training, epoch=N
         nlls, accs = [], []
         for i, batch in enumerate(loader):
             if i > 5 and args.do_test and i < spe - 5:
+                model.skip_val_batch()
                 continue
             nll, acc = model(batch)
             nlls.append(np.mean(nll))
@@ -216,8 +217,10 @@ def get_data_loaders(args, tokenizer, rank=0):
     sampler = FedSampler(train_ds, args.num_workers, args.local_batch_size, seed=args.seed)
     train_loader = DataLoader(train_ds, batch_sampler=sampler, collate_fn=personachat_collate_fn,
                               num_workers=args.train_dataloader_workers)
-    val_loader = DataLoader(val_ds, batch_size=args.valid_batch_size * args.num_workers, shuffle=False,
-                            collate_fn=personachat_collate_fn, num_workers=args.val_dataloader_workers)
+    from .data_utils import ShardedEvalSampler
+    val_sampler = ShardedEvalSampler(len(val_ds), args.valid_batch_size * args.num_workers, args.valid_batch_size)
+    val_loader = DataLoader(val_ds, batch_sampler=val_sampler, collate_fn=personachat_collate_fn,
+                            num_workers=args.val_dataloader_workers)
     return train_loader, val_loader
 
 
@@ -269,6 +272,7 @@ def train(argv=None):
 
     fed_model = FedModel(model, compute_loss_train, args, compute_loss_val)
     fed_model.attach_sampler(train_loader.batch_sampler)      # a rank's loader tokenises only its own clients
+    fed_model.attach_val_sampler(val_loader.batch_sampler)
     fed_opt = FedOptimizer(optimizer, args)
     if args.resume:
         fed_model.load_fedstate(args.resume, fed_opt)

@@ -82,7 +82,7 @@ def test_driver_on_two_gloo_ranks_matches_one_rank(tmp_path):
             "--local_batch_size", "4", "--mode", "sketch", "--error_type", "virtual", "--local_momentum", "0",
             "--virtual_momentum", "0.9", "--checkpoint"]
     one = str(tmp_path / "one")
-    cv_train.main(argv + ["--checkpoint_path", one])
+    one_summary = cv_train.main(argv + ["--checkpoint_path", one])
     two = str(tmp_path / "two")
     out_dir = str(tmp_path / "out")
     os.makedirs(out_dir)
@@ -95,6 +95,11 @@ def test_driver_on_two_gloo_ranks_matches_one_rank(tmp_path):
     num = sum(float((w1[k].float() - w2[k].float()).pow(2).sum()) for k in w1 if w1[k].is_floating_point())
     den = sum(float(w1[k].float().pow(2).sum()) for k in w1 if w1[k].is_floating_point())
     assert math.sqrt(num / den) < 1e-2
+    # validation: every rank evaluated only its own shards (ShardedEvalSampler) and all ranks report the whole set
+    two_summary = [torch.load(os.path.join(out_dir, "r%d.pt" % r), weights_only=False)["summary"] for r in range(2)]
+    assert float(two_summary[0]["test_loss"]) == float(two_summary[1]["test_loss"])
+    assert abs(float(two_summary[0]["test_loss"]) - float(one_summary["test_loss"])) < 1e-2
+    assert abs(float(two_summary[0]["test_acc"]) - float(one_summary["test_acc"])) < 0.05
 
 
 _SKETCH = ["--mode", "sketch", "--error_type", "virtual", "--local_momentum", "0", "--virtual_momentum", "0.9"]

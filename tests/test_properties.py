@@ -143,3 +143,28 @@ def test_rank_sharded_sampler_partitions_the_unsharded_schedule(sizes, num_worke
             assert all(sorted(per_rank[r][t]) == sorted(full) for r in range(world))
         seen[full] += 1
     assert np.all(seen == 1) and starts[-1] == len(seen)          # an epoch visits every sample exactly once
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.integers(min_value=1, max_value=200), st.integers(min_value=1, max_value=40), st.integers(min_value=1, max_value=9),
+       st.integers(min_value=1, max_value=5))
+def test_sharded_eval_sampler_partitions_every_batch(num_items, batch_size, shard_size, world):
+    """Per validation batch the ranks' index lists are, in rank order, exactly the sequential batch (or, when some rank
+    would get no shard, every rank gets the whole batch and the entry says so); one rank = the plain sequential loader."""
+    from commefficient_b200.data_utils.fed_sampler import ShardedEvalSampler
+    plain = list(ShardedEvalSampler(num_items, batch_size, shard_size))
+    assert [i for b in plain for i in b] == list(range(num_items))
+    assert all(len(b) == batch_size for b in plain[:-1]) and len(plain) == -(-num_items // batch_size)
+    samplers = [ShardedEvalSampler(num_items, batch_size, shard_size, r, world) for r in range(world)]
+    per_rank = [list(s) for s in samplers]
+    for t, full in enumerate(plain):
+        if world == 1:
+            assert per_rank[0][t] == full
+            continue
+        meta = samplers[0].rounds[t]
+        assert meta.total == len(full) and all(s.rounds[t] == meta for s in samplers)
+        if meta.sharded:
+            assert [i for r in range(world) for i in per_rank[r][t]] == full
+            assert all(len(per_rank[r][t]) > 0 for r in range(world))
+        else:
+            assert all(per_rank[r][t] == full for r in range(world))
