@@ -3,7 +3,7 @@
 from .fed_dataset import FedDataset
 from .fed_sampler import FedSampler, ShardedEvalSampler
 from .fed_vision import FedCIFAR10, FedCIFAR100, FedEMNIST, FedImageNet
-from .fed_persona import (FedPERSONA, personachat_collate_fn, SimpleTokenizer, SPECIAL_TOKENS,
+from .fed_persona import (FedPERSONA, personachat_collate_fn, SimpleTokenizer, BPETokenizer, load_tokenizer, SPECIAL_TOKENS,
                           MODEL_INPUTS, ATTR_TO_SPECIAL_TOKEN)
 from .synthetic import (write_synthetic_cifar, write_synthetic_emnist, write_synthetic_persona, write_synthetic_imagenet,
                         synthetic_image_batch)

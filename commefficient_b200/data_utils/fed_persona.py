@@ -97,6 +97,124 @@ class SimpleTokenizer:
         return [self._id(t) for t in tokens]
 
 
+def _bytes_to_unicode():
+    """GPT-2's reversible byte -> printable-unicode table: the 188 printable latin-1 bytes map to themselves, the
+    other 68 to code points 256, 257, ... (so that no byte becomes whitespace / a control character in the vocabulary)."""
+    keep = list(range(ord("!"), ord("~") + 1)) + list(range(0xA1, 0xAD)) + list(range(0xAE, 0x100))
+    table, extra = {}, 0
+    for b in range(256):
+        if b in keep:
+            table[b] = chr(b)
+        else:
+            table[b] = chr(256 + extra)
+            extra += 1
+    return table
+
+
+class BPETokenizer:
+    """Byte-level BPE tokenizer reading GPT-2's published files (``vocab.json`` + ``merges.txt``): the tokenizer the
+    reference gets from ``pytorch_transformers.GPT2Tokenizer`` (gpt2_train.py:259-262), restated without that
+    dependency.  Same surface as ``SimpleTokenizer``.  Used whenever ``--model_checkpoint`` / ``--finetune_path`` is a
+    directory holding the two files (they cannot be downloaded on this machine; ``tests/test_cpu_units.py`` checks
+    this implementation against ``transformers``' on a generated vocabulary)."""
+
+    VOCAB, MERGES, SPECIAL = "vocab.json", "merges.txt", "added_tokens.json"
+
+    def __init__(self, vocab_file, merges_file, special=None):
+        import regex
+        with open(vocab_file, encoding="utf-8") as f:
+            self.encoder = json.load(f)
+        with open(merges_file, encoding="utf-8") as f:
+            lines = [ln.rstrip("\n") for ln in f]
+        merges = [tuple(ln.split()) for ln in lines if ln and not ln.startswith("#version") and len(ln.split()) == 2]
+        self.ranks = {pair: i for i, pair in enumerate(merges)}
+        self.byte_table = _bytes_to_unicode()
+        self.special = dict(special or {})
+        self.pattern = regex.compile(
+            r"'s|'t|'re|'ve|'m|'ll|'d| ?\p{L}+| ?\p{N}+| ?[^\s\p{L}\p{N}]+|\s+(?!\S)|\s+")
+        self._cache = {}
+        self._merges_text = "\n".join(lines)
+
+    # -- persistence ---------------------------------------------------------------------
+    @classmethod
+    def has_files(cls, directory) -> bool:
+        d = str(directory)
+        return os.path.exists(os.path.join(d, cls.VOCAB)) and os.path.exists(os.path.join(d, cls.MERGES))
+
+    @classmethod
+    def from_pretrained(cls, directory, **_kw):
+        d = str(directory)
+        special = {}
+        fn = os.path.join(d, cls.SPECIAL)
+        if os.path.exists(fn):
+            with open(fn, encoding="utf-8") as f:
+                special = json.load(f)
+        return cls(os.path.join(d, cls.VOCAB), os.path.join(d, cls.MERGES), special)
+
+    def save_pretrained(self, directory):
+        os.makedirs(directory, exist_ok=True)
+        with open(os.path.join(directory, self.VOCAB), "w", encoding="utf-8") as f:
+            json.dump(self.encoder, f, ensure_ascii=False)
+        with open(os.path.join(directory, self.MERGES), "w", encoding="utf-8") as f:
+            f.write(self._merges_text + "\n")
+        with open(os.path.join(directory, self.SPECIAL), "w", encoding="utf-8") as f:
+            json.dump(self.special, f)
+
+    def __len__(self):
+        return len(self.encoder) + len(self.special)
+
+    def add_special_tokens(self, mapping):
+        added = 0
+        for value in mapping.values():
+            for tok in ([value] if isinstance(value, str) else value):
+                if tok not in self.special and tok not in self.encoder:
+                    self.special[tok] = len(self.encoder) + len(self.special)
+                    added += 1
+        return added
+
+    # -- BPE -------------------------------------------------------------------------------
+    def _bpe(self, word: str):
+        cached = self._cache.get(word)
+        if cached is not None:
+            return cached
+        parts = list(word)
+        while len(parts) > 1:
+            best, best_rank = None, None
+            for i in range(len(parts) - 1):
+                r = self.ranks.get((parts[i], parts[i + 1]))
+                if r is not None and (best_rank is None or r < best_rank):
+                    best, best_rank = (parts[i], parts[i + 1]), r
+            if best is None:
+                break
+            merged, i = [], 0
+            while i < len(parts):
+                if i + 1 < len(parts) and (parts[i], parts[i + 1]) == best:
+                    merged.append(parts[i] + parts[i + 1])
+                    i += 2
+                else:
+                    merged.append(parts[i])
+                    i += 1
+            parts = merged
+        self._cache[word] = parts
+        return parts
+
+    def tokenize(self, text):
+        out = []
+        for piece in self.pattern.findall(text):
+            out.extend(self._bpe("".join(self.byte_table[b] for b in piece.encode("utf-8"))))
+        return out
+
+    def _id(self, token):
+        if token in self.special:
+            return self.special[token]
+        return self.encoder[token]
+
+    def convert_tokens_to_ids(self, tokens):
+        if isinstance(tokens, str):
+            return self._id(tokens)
+        return [self._id(t) for t in tokens]
+
+
 class _RangeDict:
     """len()-only stand-in for the HF ``encoder`` dict (avoids a 50k-entry dict)."""
 
@@ -105,6 +223,13 @@ class _RangeDict:
 
     def __len__(self):
         return self.n
+
+
+def load_tokenizer(directory):
+    """The tokenizer saved in ``directory``: GPT-2 BPE files if present, else the hashed whitespace stand-in."""
+    if BPETokenizer.has_files(directory):
+        return BPETokenizer.from_pretrained(directory)
+    return SimpleTokenizer.from_pretrained(directory)
 
 
 def tokenize(obj, tokenizer):

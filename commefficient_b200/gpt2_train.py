@@ -23,7 +23,8 @@ from torch.optim.lr_scheduler import LambdaLR
 from torch.utils.data import DataLoader
 
 from . import data_utils
-from .data_utils import ATTR_TO_SPECIAL_TOKEN, FedPERSONA, FedSampler, SimpleTokenizer, personachat_collate_fn
+from .data_utils import (ATTR_TO_SPECIAL_TOKEN, FedPERSONA, FedSampler, SimpleTokenizer, load_tokenizer,
+                         personachat_collate_fn)
 from .fed_aggregator import FedModel, FedOptimizer
 from .models.gpt2 import GPT2Config, GPT2DoubleHeadsModel, OpenAIGPTDoubleHeadsModel
 from .parallel.runtime import init_runtime
@@ -228,7 +229,7 @@ def build_model_and_tokenizer(args):
     ckpt = args.finetune_path if (args.do_finetune and not args.do_test) else args.model_checkpoint
     cls = GPT2DoubleHeadsModel if "gpt2" in args.model_checkpoint else OpenAIGPTDoubleHeadsModel
     if os.path.isdir(str(ckpt)):
-        tokenizer = SimpleTokenizer.from_pretrained(ckpt)
+        tokenizer = load_tokenizer(ckpt)           # GPT-2 BPE files when the directory has them
         model = cls.from_pretrained(ckpt)
     elif args.model_checkpoint == "gpt2-tiny":
         tokenizer = SimpleTokenizer(TINY["vocab_size"])

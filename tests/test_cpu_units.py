@@ -280,3 +280,80 @@ def test_fed_imagenet_on_a_synthetic_folder_tree(tmp_path):
     sampler = data_utils.FedSampler(train, num_workers=2, local_batch_size=2, seed=0)
     ids, x, y = next(iter(DataLoader(train, batch_sampler=sampler)))
     assert x.shape == (4, 3, 224, 224) and len(set(ids.tolist())) == 2 and torch.equal(ids, y)
+
+
+def _write_tiny_bpe(directory, corpus, n_merges=120):
+    """vocab.json + merges.txt in GPT-2's format, learned on ``corpus`` by plain pair-frequency BPE."""
+    import collections
+    import json
+    import os
+    import regex
+    from commefficient_b200.data_utils.fed_persona import _bytes_to_unicode
+    table = _bytes_to_unicode()
+    pat = regex.compile(r"'s|'t|'re|'ve|'m|'ll|'d| ?\p{L}+| ?\p{N}+| ?[^\s\p{L}\p{N}]+|\s+(?!\S)|\s+")
+    words = collections.Counter("".join(table[b] for b in w.encode("utf-8")) for w in pat.findall(corpus))
+    splits = {w: list(w) for w in words}
+    merges = []
+    for _ in range(n_merges):
+        pairs = collections.Counter()
+        for w, parts in splits.items():
+            for a, b in zip(parts, parts[1:]):
+                pairs[(a, b)] += words[w]
+        if not pairs:
+            break
+        best = max(sorted(pairs), key=lambda p: pairs[p])
+        merges.append(best)
+        for w, parts in splits.items():
+            out, i = [], 0
+            while i < len(parts):
+                if i + 1 < len(parts) and (parts[i], parts[i + 1]) == best:
+                    out.append(parts[i] + parts[i + 1])
+                    i += 2
+                else:
+                    out.append(parts[i])
+                    i += 1
+            splits[w] = out
+    vocab = {ch: i for i, ch in enumerate(table.values())}
+    for a, b in merges:
+        vocab.setdefault(a + b, len(vocab))
+    vocab["<|endoftext|>"] = len(vocab)
+    os.makedirs(directory, exist_ok=True)
+    with open(os.path.join(directory, "vocab.json"), "w", encoding="utf-8") as f:
+        json.dump(vocab, f, ensure_ascii=False)
+    with open(os.path.join(directory, "merges.txt"), "w", encoding="utf-8") as f:
+        f.write("#version: 0.2\n" + "\n".join("%s %s" % m for m in merges) + "\n")
+
+
+def test_bpe_tokenizer_matches_transformers_on_generated_files(tmp_path):
+    """BPETokenizer (GPT-2 byte-level BPE over vocab.json + merges.txt) against transformers' GPT2Tokenizer on the
+    same files: tokens and ids, including contractions, digits, punctuation runs, repeated spaces and non-ASCII."""
+    transformers = pytest.importorskip("transformers")
+    from commefficient_b200.data_utils import ATTR_TO_SPECIAL_TOKEN, BPETokenizer, load_tokenizer
+    corpus = ("i like to remodel homes. i like to go hunting. i'm a vegan and i don't eat meat! my favorite season is "
+              "winter, and my 2 dogs love the snow... what do you do for a living? i work at a café in 1999 - 2003. ") * 3
+    d = str(tmp_path / "tok")
+    _write_tiny_bpe(d, corpus)
+    ours = load_tokenizer(d)
+    assert isinstance(ours, BPETokenizer)
+    try:
+        try:
+            hf = transformers.GPT2Tokenizer(vocab=d + "/vocab.json", merges=d + "/merges.txt")      # transformers >= 5
+        except TypeError:
+            hf = transformers.GPT2Tokenizer(vocab_file=d + "/vocab.json", merges_file=d + "/merges.txt")
+    except Exception as exc:          # noqa: BLE001
+        pytest.skip("transformers cannot build GPT2Tokenizer from these files here: %s" % exc)
+    if not hf.tokenize("i like"):
+        pytest.skip("this transformers build ignores the vocabulary files passed to GPT2Tokenizer")
+    samples = ["i like to go hunting.", "I'm a vegan, and I don't eat meat!", "my  2 dogs   love the snow...",
+               "what do you do for a living?  ", "café naïve — résumé \U0001F600 ok", "1999-2003: we've said 'hello'"]
+    for text in samples:
+        mine = ours.tokenize(text)
+        assert mine == hf.tokenize(text), text
+        assert ours.convert_tokens_to_ids(mine) == hf.convert_tokens_to_ids(mine)
+    base = len(ours)
+    assert ours.add_special_tokens(ATTR_TO_SPECIAL_TOKEN) == 5 and len(ours) == base + 5
+    assert ours.add_special_tokens(ATTR_TO_SPECIAL_TOKEN) == 0
+    ours.save_pretrained(str(tmp_path / "saved"))
+    again = load_tokenizer(str(tmp_path / "saved"))
+    assert len(again) == len(ours) and again.tokenize(samples[1]) == ours.tokenize(samples[1])
+    assert again.convert_tokens_to_ids("<bos>") == ours.convert_tokens_to_ids("<bos>") >= base

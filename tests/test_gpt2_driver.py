@@ -142,3 +142,29 @@ def test_gpt2_driver_flag_combinations(tmp_path, monkeypatch, name, flags):
     monkeypatch.chdir(tmp_path)
     out = train(_GPT2_BASE + ["--dataset_dir", str(tmp_path / "persona")] + flags)
     assert out["val_ppl"] == out["val_ppl"] and out["val_ppl"] < 1e4 and 0.0 <= out["val_acc"] <= 1.0, (name, out)
+
+
+def test_gpt2_driver_from_a_checkpoint_directory_with_bpe_files(tmp_path, monkeypatch):
+    """--model_checkpoint pointing at a directory in the published GPT-2 layout (config.json, pytorch_model.bin,
+    vocab.json, merges.txt): weights load, the byte-level BPE tokenizer is used, the five dialogue tokens are added
+    and the embedding matrix grows with them."""
+    import json
+    from commefficient_b200 import data_utils
+    from tests.test_cpu_units import _write_tiny_bpe
+    monkeypatch.chdir(tmp_path)
+    ck = tmp_path / "gpt2-local"
+    corpus = "i like to remodel homes. i like to go hunting. my favorite season is winter. what do you do for a living? " * 4
+    _write_tiny_bpe(str(ck), corpus, n_merges=60)
+    vocab = json.load(open(ck / "vocab.json"))
+    # (a 60-merge vocabulary tokenises almost character by character: sequences run to several hundred tokens)
+    cfg = models.GPT2Config(vocab_size=len(vocab), n_positions=1024, n_ctx=1024, n_embd=32, n_layer=2, n_head=2)
+    models.GPT2DoubleHeadsModel(cfg).save_pretrained(str(ck))
+    assert isinstance(data_utils.load_tokenizer(str(ck)), data_utils.BPETokenizer)
+    out = train(["--dataset_name", "PERSONA", "--synthetic", "--dataset_dir", str(tmp_path / "persona"),
+                 "--num_clients", "8", "--model_checkpoint", str(ck), "--num_workers", "2", "--local_batch_size", "2",
+                 "--mode", "uncompressed", "--error_type", "none", "--local_momentum", "0", "--num_epochs", "1",
+                 "--device", "cpu", "--valid_batch_size", "2", "--lr_scale", "0.1"])
+    assert out["val_ppl"] == out["val_ppl"] and 0.0 <= out["val_acc"] <= 1.0
+    run = sorted((tmp_path / "runs").iterdir())[-1]
+    saved = [p.name for p in run.rglob("*") if p.is_file()]
+    assert "vocab.json" in saved and "merges.txt" in saved and "added_tokens.json" in saved
