@@ -243,15 +243,37 @@ class GPT2DoubleHeadsModel(nn.Module):
 
     @classmethod
     def from_pretrained(cls, path_or_name, **kw):
-        """Load ``config.json`` + ``pytorch_model.bin`` from a directory; any other
-        argument (e.g. the hub name ``gpt2`` -- there is no network) builds a
-        randomly initialised GPT-2 small."""
+        """Load a checkpoint directory in the published layout: ``config.json`` plus ``pytorch_model.bin`` or
+        ``model.safetensors``, with or without the ``transformer.`` key prefix (``GPT2Model`` checkpoints, such as
+        the original ``gpt2`` files, have none).  Heads the checkpoint lacks keep their fresh initialisation.  Any
+        other argument (e.g. the hub name ``gpt2`` -- there is no network) builds a randomly initialised model."""
         if isinstance(path_or_name, str) and os.path.isdir(path_or_name):
             cfg = GPT2Config.from_json_file(os.path.join(path_or_name, CONFIG_NAME))
             model = cls(cfg)
-            state = torch.load(os.path.join(path_or_name, WEIGHTS_NAME), map_location="cpu")
+            bin_fn = os.path.join(path_or_name, WEIGHTS_NAME)
+            st_fn = os.path.join(path_or_name, "model.safetensors")
+            if os.path.exists(bin_fn):
+                state = torch.load(bin_fn, map_location="cpu")
+            elif os.path.exists(st_fn):
+                from safetensors.torch import load_file
+                state = load_file(st_fn, device="cpu")
+            else:
+                raise FileNotFoundError("no %s or model.safetensors in %s" % (WEIGHTS_NAME, path_or_name))
             state = {k: v for k, v in state.items() if not k.endswith(".attn.bias")
                      and not k.endswith(".attn.masked_bias")}
+            if not any(k.startswith("transformer.") for k in state):
+                state = {("transformer." + k if k.split(".")[0] in ("wte", "wpe", "h", "ln_f") else k): v
+                         for k, v in state.items()}
+            if "lm_head.weight" not in state and "transformer.wte.weight" in state:
+                state["lm_head.weight"] = state["transformer.wte.weight"]          # tied
+            own = model.state_dict()
+            trunk = [k for k in own if k.startswith("transformer.")]
+            missing = [k for k in trunk if k not in state]
+            if missing:
+                raise KeyError("checkpoint %s lacks %d trunk tensors, e.g. %s" % (path_or_name, len(missing), missing[:3]))
+            bad = [k for k in own if k in state and tuple(state[k].shape) != tuple(own[k].shape)]
+            if bad:
+                raise ValueError("checkpoint %s: shape mismatch for %s" % (path_or_name, bad[:3]))
             model.load_state_dict(state, strict=False)
             model.tie_weights()
             return model

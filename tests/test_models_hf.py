@@ -78,3 +78,32 @@ def test_double_heads_model_matches_transformers():
     torch.testing.assert_close(mc_logits, want.mc_logits, rtol=1e-4, atol=1e-4)
     torch.testing.assert_close(lm_loss, want.loss, rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(mc_loss, want.mc_loss, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("hf_cls", ["GPT2DoubleHeadsModel", "GPT2LMHeadModel", "GPT2Model"])
+def test_from_pretrained_reads_transformers_checkpoints(tmp_path, hf_cls):
+    """A directory written by transformers' ``save_pretrained`` (safetensors; with or without the ``transformer.``
+    prefix; with or without the heads) loads, and the trunk computes what the saved model computes."""
+    from commefficient_b200.models.gpt2 import GPT2DoubleHeadsModel
+    torch.manual_seed(2)
+    kw = dict(vocab_size=101, n_positions=32, n_embd=64, n_layer=2, n_head=4, resid_pdrop=0.0, embd_pdrop=0.0,
+              attn_pdrop=0.0)
+    hf = getattr(transformers, hf_cls)(transformers.GPT2Config(**kw)).eval()
+    hf.save_pretrained(str(tmp_path))
+    ours = GPT2DoubleHeadsModel.from_pretrained(str(tmp_path)).eval()
+    ids = torch.randint(0, 101, (3, 11))
+    with torch.no_grad():
+        base = hf.transformer if hasattr(hf, "transformer") else hf
+        want = base(input_ids=ids).last_hidden_state
+        got = ours.transformer(ids)
+    torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-5)
+    assert ours.lm_head.weight.data_ptr() == ours.transformer.wte.weight.data_ptr()
+
+
+def test_from_pretrained_refuses_a_checkpoint_without_the_trunk(tmp_path):
+    from commefficient_b200.models.gpt2 import GPT2DoubleHeadsModel
+    cfg = GPT2Config(vocab_size=50, n_positions=16, n_ctx=16, n_embd=32, n_layer=1, n_head=2)
+    cfg.to_json_file(str(tmp_path / "config.json"))
+    torch.save({"unrelated.weight": torch.zeros(3)}, str(tmp_path / "pytorch_model.bin"))
+    with pytest.raises(KeyError):
+        GPT2DoubleHeadsModel.from_pretrained(str(tmp_path))
