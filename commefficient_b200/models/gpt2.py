@@ -261,6 +261,8 @@ class GPT2DoubleHeadsModel(nn.Module):
                 raise FileNotFoundError("no %s or model.safetensors in %s" % (WEIGHTS_NAME, path_or_name))
             state = {k: v for k, v in state.items() if not k.endswith(".attn.bias")
                      and not k.endswith(".attn.masked_bias")}
+            # GPT-1 checkpoints name the two embedding tables differently
+            state = {k.replace("tokens_embed.", "wte.").replace("positions_embed.", "wpe."): v for k, v in state.items()}
             if not any(k.startswith("transformer.") for k in state):
                 state = {("transformer." + k if k.split(".")[0] in ("wte", "wpe", "h", "ln_f") else k): v
                          for k, v in state.items()}

@@ -107,3 +107,18 @@ def test_from_pretrained_refuses_a_checkpoint_without_the_trunk(tmp_path):
     torch.save({"unrelated.weight": torch.zeros(3)}, str(tmp_path / "pytorch_model.bin"))
     with pytest.raises(KeyError):
         GPT2DoubleHeadsModel.from_pretrained(str(tmp_path))
+
+
+def test_gpt1_from_pretrained_reads_a_transformers_checkpoint(tmp_path):
+    torch.manual_seed(3)
+    kw = dict(vocab_size=97, n_positions=32, n_embd=64, n_layer=2, n_head=4, resid_pdrop=0.0, embd_pdrop=0.0,
+              attn_pdrop=0.0)
+    hf = transformers.OpenAIGPTLMHeadModel(transformers.OpenAIGPTConfig(afn="gelu", **kw)).eval()
+    hf.save_pretrained(str(tmp_path))
+    ours = OpenAIGPTDoubleHeadsModel.from_pretrained(str(tmp_path)).eval()
+    assert ours.config.post_ln and not hasattr(ours.transformer, "ln_f")
+    ids = torch.randint(0, 97, (2, 9))
+    with torch.no_grad():
+        want = hf.transformer(input_ids=ids).last_hidden_state
+        got = ours.transformer(ids)
+    torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-5)
