@@ -19,6 +19,7 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * models: ResNet9 (plain / BatchNorm / 1-channel 62-class), ResNet18, FixupResNet9, FixupResNet18, ResNet101LN --
     the reference's ``state_dict`` loads with ``strict=True`` and output and parameter gradients agree;
   * ``FedSampler``: with the same numpy seed both draw the same clients and samples in every round;
+  * dataset preparation from raw files: EMNIST from LEAF json, PersonaChat from ``personachat_self_original.json``;
   * datasets: FedCIFAR10 / FedEMNIST / FedImageNet / FedPERSONA (+ collate) over the same client files return the same items,
     iid and non-iid (PersonaChat with more than one personality permutation and validation indexing are the
     documented departures Q14 / Q15 and are not compared);
@@ -376,6 +377,33 @@ def main():
         lambda **kw: our_data.FedEMNIST(tmp, "EMNIST", None, kw["iid"], kw["n"], train=kw["train"], download=False),
         [dict(iid=False, n=12, train=True), dict(iid=False, n=24, train=True), dict(iid=True, n=5, train=True),
          dict(iid=False, n=None, train=False)])
+    # EMNIST from the raw LEAF json (prepare_datasets: fed_emnist.py:82-130), each implementation in its own copy
+    def write_leaf(root, seed):
+        rng = np.random.RandomState(seed)
+        for split, users, per in (("train", 5, 4), ("test", 3, 2)):
+            os.makedirs(os.path.join(root, split), exist_ok=True)
+            blob = {"users": [], "num_samples": [], "user_data": {}}
+            for u in range(users):
+                name = "f%04d_%02d" % (u * 7, u)
+                blob["users"].append(name)
+                blob["num_samples"].append(per + u)
+                blob["user_data"][name] = {"x": rng.rand(per + u, 784).round(4).tolist(),
+                                           "y": rng.randint(0, 62, per + u).tolist()}
+            with open(os.path.join(root, split, "all_data_0_niid.json"), "w") as f:
+                json.dump(blob, f)
+    leaf_r, leaf_o = tempfile.mkdtemp(), tempfile.mkdtemp()
+    write_leaf(leaf_r, 5)
+    write_leaf(leaf_o, 5)
+    bad = 0
+    for iid, n, train in ((False, 5, True), (True, 3, True), (False, None, False)):
+        np.random.seed(3)
+        r = ref_data.FedEMNIST(leaf_r, "EMNIST", None, iid, n, train=train, download=False)
+        np.random.seed(3)
+        o = our_data.FedEMNIST(leaf_o, "EMNIST", None, iid, n, train=train, download=False)
+        bad += int(len(r) != len(o))
+        for i in range(min(len(r), len(o))):
+            bad += int(not same(r[i], o[i]))
+    out["data/fed_emnist_prepared_from_leaf_json"] = float(bad)
     tmp = tempfile.mkdtemp()
     our_data.write_synthetic_imagenet(tmp, num_classes=4, images_per_class=3, val_per_class=2)
     out["data/fed_imagenet_items"] = compare_sets(
@@ -395,6 +423,31 @@ def main():
                                               do_iid=kw["iid"], num_clients=kw["n"], train=True)
     variants = [dict(iid=False, n=None, train=True), dict(iid=True, n=4, train=True)]
     bad = compare_sets(mk_ref, mk_our, variants)
+    # the raw corpus file split by personality (reference split_dataset: fed_persona.py:128-170) against our
+    # prepare_datasets on a directory that holds personachat_self_original.json
+    raw_dir = tempfile.mkdtemp()
+    rng = np.random.RandomState(4)
+    personas = [["i like %s ." % w, "my dog is %s ." % w] for w in ("red", "blue", "green")]
+    def dialog(p):
+        return {"personality": list(p), "utterances": [
+            {"candidates": ["reply %d %d" % (u, c) for c in range(3)], "history": ["turn %d" % t for t in range(2 * u + 1)]}
+            for u in range(int(rng.randint(1, 4)))]}
+    raw = {"train": [dialog(personas[i % 3]) for i in range(7)], "valid": [dialog(personas[i % 3]) for i in range(3)]}
+    with open(os.path.join(raw_dir, "personachat_self_original.json"), "w") as f:
+        json.dump(raw, f)
+    (ref_clients, ref_val), (ref_dpc, ref_tupd, ref_vupd) = ref_data.FedPERSONA.split_dataset(
+        None, os.path.join(raw_dir, "personachat_self_original.json"))
+    ours_ds = our_data.FedPERSONA(tokenizer=tok, num_candidates=2, max_history=2, personality_permutations=1,
+                                  dataset_dir=raw_dir, dataset_name="PERSONA", do_iid=False, num_clients=None, train=True)
+    with open(ours_ds.stats_fn()) as f:
+        st_ = json.load(f)
+    bad += float(st_["dialogs_per_client"] != list(ref_dpc) or st_["train_utterances_per_dialog"] != list(ref_tupd)
+                 or st_["val_utterances_per_dialog"] != list(ref_vupd))
+    for cid, dialogs in enumerate(ref_clients.values()):
+        with open(ours_ds.client_fn(cid)) as f:
+            bad += float(json.load(f) != dialogs)
+    with open(ours_ds.validation_fn()) as f:
+        bad += float(json.load(f) != ref_val)
     np.random.seed(3)
     r, o = mk_ref(**variants[0]), mk_our(**variants[0])
     random.seed(0)

@@ -370,10 +370,18 @@ class FedPERSONA(FedDataset):
         return raw_to_input(self.tokenizer, personality, history, cands[-n:])
 
     # -- files ---------------------------------------------------------------------
+    RAW_NAME = "personachat_self_original.json"
+
     def prepare_datasets(self, download=True):
+        """First use of a directory: split the original corpus file, if it has been placed there, into the
+        per-client files (the reference downloads it first, fed_persona.py:86-126; there is no network here)."""
+        raw = os.path.join(self.dataset_dir, self.RAW_NAME)
+        if os.path.exists(raw):
+            self.split_dataset(raw)
+            return
         raise RuntimeError(
-            "PersonaChat is not present in %s and cannot be downloaded (no network); write a "
-            "synthetic corpus with data_utils.synthetic.write_synthetic_persona()" % self.dataset_dir)
+            "PersonaChat is not present in %s and cannot be downloaded (no network): put %s there, or write a "
+            "synthetic corpus with data_utils.synthetic.write_synthetic_persona()" % (self.dataset_dir, self.RAW_NAME))
 
     def split_dataset(self, dataset_path):
         """Partition the original ``personachat_self_original.json`` by personality and write
