@@ -113,7 +113,19 @@ class Runtime:
             self.peer.close()
             self.peer = None
         if self.world_size > 1 and dist.is_initialized():
-            dist.destroy_process_group()
+            # leave together: a rank that tears its sockets down while a peer is still finishing its last collective
+            # makes that peer's transport throw (gloo: "connection closed by peer") -- seen as a bare non-zero exit
+            # (gloo only, and bounded: a peer that already died must not hold the others' exit)
+            if self.backend == "gloo":
+                try:
+                    import datetime
+                    dist.monitored_barrier(timeout=datetime.timedelta(seconds=60))
+                except Exception:         # noqa: BLE001
+                    pass
+            try:
+                dist.destroy_process_group()
+            except Exception:             # noqa: BLE001
+                pass
         _RUNTIME = None
 
 
@@ -196,15 +208,14 @@ def spawn(fn, nprocs: int, args=(), port: Optional[int] = None, device: str = "c
         p = ctx.Process(target=_spawn_entry, args=(fn, rank, nprocs, port, device, args, err_q))
         p.start()
         procs.append(p)
-    failed = False
     for p in procs:
         p.join()
-        failed = failed or p.exitcode != 0
-    if failed:
+    codes = [p.exitcode for p in procs]
+    if any(c != 0 for c in codes):
         msgs = []
         while not err_q.empty():
             msgs.append(err_q.get())
-        raise RuntimeError("spawned rank failed:\n" + "\n".join(msgs))
+        raise RuntimeError("spawned rank failed (exit codes %s):\n%s" % (codes, "\n".join(msgs)))
 
 
 def _spawn_entry(fn, rank, world_size, port, device, args, err_q):
