@@ -230,3 +230,39 @@ def _spawn_entry(fn, rank, world_size, port, device, args, err_q):
         import traceback
         err_q.put("rank %d:\n%s" % (rank, traceback.format_exc()))
         raise
+
+
+def _driver_rank(rank, world_size, module_name, fn_name, argv):
+    import importlib
+    getattr(importlib.import_module(module_name), fn_name)(list(argv))
+
+
+def run_driver(module_name: str, fn_name: str, argv=None):
+    """Entry point of the reference-named scripts.  The reference starts its own worker processes from one
+    ``python cv_train.py --num_devices N`` invocation (fed_aggregator.py:130-160); here ``--num_devices N`` with N > 1,
+    when the process was not started by torchrun (no WORLD_SIZE in the environment), starts N ranks of the same
+    program -- one per GPU -- and waits for them.  Under torchrun, or with ``--num_devices 1``, the driver simply runs
+    in this process."""
+    import importlib
+    import sys
+    argv = list(sys.argv[1:] if argv is None else argv)
+    n = 1
+    for i, a in enumerate(argv):
+        if a == "--num_devices" and i + 1 < len(argv):
+            n = int(argv[i + 1])
+        elif a.startswith("--num_devices="):
+            n = int(a.split("=", 1)[1])
+    if n > 1 and "WORLD_SIZE" not in os.environ:
+        device = None
+        for i, a in enumerate(argv):
+            if a == "--device" and i + 1 < len(argv):
+                device = argv[i + 1]
+            elif a.startswith("--device="):
+                device = a.split("=", 1)[1]
+        if device is None:
+            device = "cuda" if torch.cuda.is_available() else "cpu"
+        if device.startswith("cuda") and torch.cuda.device_count() < n:
+            raise SystemExit("--num_devices %d: only %d CUDA devices are visible" % (n, torch.cuda.device_count()))
+        spawn(_driver_rank, n, args=(module_name, fn_name, argv), device="cuda" if device.startswith("cuda") else "cpu")
+        return None
+    return getattr(importlib.import_module(module_name), fn_name)(argv)

@@ -11,7 +11,8 @@ Differences from the reference, all deliberate:
     ``assert`` and also rejects the combinations that the reference only trips
     over deep inside a worker (sketch + local momentum, sketch + ``error_type
     none`` which yields an all-zero update forever -- Q8);
-  * ``--num_devices`` means "ranks" (one per GPU); there is no parameter-server
+  * ``--num_devices`` means "ranks" (one per GPU): ``python cv_train.py --num_devices N`` starts N ranks itself
+    unless torchrun already did (``parallel/runtime.py:run_driver``); there is no parameter-server
     GPU, so ``--share_ps_gpu`` is accepted and ignored;
   * ``--port`` probing is done by the launcher, not at parse time.
 """

@@ -157,3 +157,24 @@ def test_driver_two_ranks_with_per_client_state(tmp_path):
     owned = [set(int(c) for c in s["client_velocities"].keys()) for s in side]
     assert owned[0] and owned[1] and all(c % 2 == 0 for c in owned[0]) and all(c % 2 == 1 for c in owned[1])
     assert [set(int(c) for c in s["client_errors"].keys()) for s in side] == owned
+
+
+def test_num_devices_flag_starts_that_many_ranks(tmp_path):
+    """``python cv_train.py --num_devices 2`` (the reference's way of asking for two devices) starts two ranks of the
+    driver by itself; rank 0 prints the table once and both ranks write their resume sidecars."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ck = tmp_path / "ck"
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_PORT")}
+    res = subprocess.run(
+        [sys.executable, os.path.join(root, "cv_train.py"), "--num_devices", "2", "--device", "cpu", "--synthetic",
+         "--dataset_dir", str(tmp_path / "data"), "--dataset_name", "CIFAR10", "--model", "ResNet9", "--num_clients", "10",
+         "--num_workers", "4", "--local_batch_size", "4", "--num_epochs", "1", "--pivot_epoch", "0.5", "--lr_scale", "0.05",
+         "--num_cols", "2000", "--num_rows", "3", "--k", "300", "--valid_batch_size", "8", "--mode", "sketch",
+         "--error_type", "virtual", "--local_momentum", "0", "--virtual_momentum", "0.9", "--checkpoint",
+         "--checkpoint_path", str(ck)],
+        cwd=str(tmp_path), env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert res.stdout.count("Total Upload (MiB)") == 1
+    assert (ck / "ResNet9.fedstate.pt.rank0").exists() and (ck / "ResNet9.fedstate.pt.rank1").exists()
