@@ -357,3 +357,16 @@ def test_bpe_tokenizer_matches_transformers_on_generated_files(tmp_path):
     again = load_tokenizer(str(tmp_path / "saved"))
     assert len(again) == len(ours) and again.tokenize(samples[1]) == ours.tokenize(samples[1])
     assert again.convert_tokens_to_ids("<bos>") == ours.convert_tokens_to_ids("<bos>") >= base
+
+
+def test_reference_package_name_is_importable():
+    """Code written against the reference's package layout imports unchanged."""
+    from CommEfficient.fed_aggregator import FedModel, FedOptimizer, get_server_update      # noqa: F401
+    from CommEfficient.fed_worker import forward_grad, local_step, process_batch           # noqa: F401
+    from CommEfficient.utils import PiecewiseLinear, TableLogger, Timer, parse_args, steps_per_epoch  # noqa: F401
+    from CommEfficient.data_utils import FedCIFAR10, FedEMNIST, FedImageNet, FedPERSONA, FedSampler    # noqa: F401
+    from CommEfficient.data_utils.fed_sampler import FedSampler as S2
+    from CommEfficient.models import FixupResNet50, ResNet9, ResNet18                      # noqa: F401
+    import CommEfficient.cv_train as drv
+    import commefficient_b200.fed_aggregator as ours
+    assert FedModel is ours.FedModel and S2 is FedSampler and hasattr(drv, "main")
