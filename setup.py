@@ -43,7 +43,7 @@ setup(
     name="commefficient_b200",
     version="0.1.0",
     description="Blackwell-native communication-efficient federated learning (FetchSGD sketching, top-k, FedAvg)",
-    packages=find_packages(include=["commefficient_b200", "commefficient_b200.*"]),
+    packages=find_packages(include=["commefficient_b200", "commefficient_b200.*", "CommEfficient"]),
     package_data={"commefficient_b200": ["lib/*.so"]},
     py_modules=["cv_train", "gpt2_train"],
     python_requires=">=3.10",
