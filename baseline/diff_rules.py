@@ -23,6 +23,7 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * datasets: FedCIFAR10 / FedEMNIST / FedImageNet / FedPERSONA (+ collate) over the same client files return the same items,
     iid and non-iid (PersonaChat with more than one personality permutation and validation indexing are the
     documented departures Q14 / Q15 and are not compared);
+  * the eight named transform pipelines (same image, same RNG state -> same tensor) and the table / TSV loggers;
   * CLI: all 55 reference flags exist with the same dest and default and parse the same command line;
   * utilities: LR schedules, ``steps_per_epoch``, ``_topk``, ``get_param_vec`` / ``set_param_vec``.
 
@@ -455,6 +456,50 @@ def main():
     random.seed(0)
     bo = our_data.personachat_collate_fn([o[i] for i in range(5)])
     out["data/fed_persona_items_and_collate"] = bad + float(not same(list(br), list(bo)))
+    # ---- transforms: the eight named pipelines on the same image with the same RNG state ------------------------
+    from PIL import Image
+    worst = 0.0
+    rng = np.random.RandomState(8)
+    rgb32 = Image.fromarray(rng.randint(0, 256, (32, 32, 3)).astype(np.uint8))
+    gray28 = Image.fromarray(rng.rand(28, 28).astype(np.float32))               # EMNIST images are float 'F' mode
+    rgb_big = Image.fromarray(rng.randint(0, 256, (300, 260, 3)).astype(np.uint8))
+    for tname, img in (("cifar10_train_transforms", rgb32), ("cifar10_test_transforms", rgb32),
+                       ("cifar100_train_transforms", rgb32), ("cifar100_test_transforms", rgb32),
+                       ("femnist_train_transforms", gray28), ("femnist_test_transforms", gray28),
+                       ("imagenet_train_transforms", rgb_big), ("imagenet_val_transforms", rgb_big)):
+        for seed in range(3):
+            torch.manual_seed(seed)
+            random.seed(seed)
+            a = getattr(ref_data, tname)(img)
+            torch.manual_seed(seed)
+            random.seed(seed)
+            b = getattr(our_data, tname)(img)
+            worst = max(worst, 1e9 if a.shape != b.shape else float((a - b).abs().max()))
+    out["data/transforms"] = worst
+
+    # ---- loggers: the printed table and the TSV file --------------------------------------------------------------
+    import utils as ref_utils
+    from commefficient_b200 import utils as our_utils
+    import contextlib as _ctx
+    import io as _io
+    rows = [{"epoch": 1, "lr": 0.123456, "train_loss": 2.30258, "note": "x"}, {"epoch": 2, "lr": 0.05, "train_loss": 1.5,
+                                                                                     "note": "y"}]
+    def table_text(mod):
+        buf = _io.StringIO()
+        with _ctx.redirect_stdout(buf):
+            tl = mod.TableLogger()
+            for r in rows:
+                tl.append(dict(r))
+        return buf.getvalue()
+    bad = float(table_text(ref_utils) != table_text(our_utils))
+    def tsv_text(mod):
+        t = mod.TSVLogger()
+        for e, (hours, acc) in enumerate(((0.5, 0.91), (1.25, 0.9342))):
+            t.append({"epoch": e + 1, "total_time": hours * 3600, "test_acc": acc})
+        return str(t)
+    bad += float(tsv_text(ref_utils) != tsv_text(our_utils))
+    out["utils/table_and_tsv_loggers"] = bad
+
     # ---- CLI: every reference flag exists with the same dest and default, and parses to the same value -------
     import utils as ref_utils
     from commefficient_b200 import utils as our_utils
