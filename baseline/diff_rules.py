@@ -23,6 +23,8 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * datasets: FedCIFAR10 / FedEMNIST / FedImageNet / FedPERSONA (+ collate) over the same client files return the same items,
     iid and non-iid (PersonaChat with more than one personality permutation and validation indexing are the
     documented departures Q14 / Q15 and are not compared);
+  * GPT-2: the reference's ``compute_loss_train`` / ``compute_loss_val`` (gpt2_train.py:56-99) on its model class
+    (through the ``pytorch_transformers`` shim over the installed ``transformers``) against ours with the same weights;
   * the eight named transform pipelines (same image, same RNG state -> same tensor) and the table / TSV loggers;
   * CLI: all 55 reference flags exist with the same dest and default and parse the same command line;
   * utilities: LR schedules, ``steps_per_epoch``, ``_topk``, ``get_param_vec`` / ``set_param_vec``.
@@ -43,6 +45,7 @@ def main():
     if not os.path.isdir(REF):
         print(json.dumps({"unavailable": "baseline/_ref is not installed"}))
         return 0
+    os.environ["CEB_REF_GPT2"] = "1"          # the pytorch_transformers shim then builds its GPT-2 classes
     sys.path.insert(0, os.path.join(HERE, "shims"))
     sys.path.insert(0, REF)
     sys.path.insert(0, ROOT)
@@ -456,6 +459,46 @@ def main():
     random.seed(0)
     bo = our_data.personachat_collate_fn([o[i] for i in range(5)])
     out["data/fed_persona_items_and_collate"] = bad + float(not same(list(br), list(bo)))
+    # ---- GPT-2: the reference's loss callbacks (gpt2_train.py:56-99) on its model class against ours, same weights ---
+    try:
+        import importlib.util
+        import transformers
+        import pytorch_transformers as ref_pt                       # the shim over the installed transformers
+        spec = importlib.util.spec_from_file_location("ref_gpt2_train", os.path.join(REF, "gpt2_train.py"))
+        ref_gpt2 = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(ref_gpt2)
+        from commefficient_b200 import gpt2_train as our_gpt2
+        from commefficient_b200.models.gpt2 import GPT2Config as OurGPT2Config, GPT2DoubleHeadsModel as OurGPT2
+        torch.manual_seed(0)
+        gkw = dict(vocab_size=101, n_positions=32, n_embd=64, n_layer=2, n_head=4, resid_pdrop=0.0, embd_pdrop=0.0,
+                   attn_pdrop=0.0)
+        rg = ref_pt.GPT2DoubleHeadsModel(transformers.GPT2Config(summary_first_dropout=0.0, num_labels=1, **gkw))
+        og = OurGPT2(OurGPT2Config(vocab_size=101, n_positions=32, n_ctx=32, n_embd=64, n_layer=2, n_head=4,
+                                   resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0, summary_first_dropout=0.0))
+        src = rg.state_dict()
+        og.load_state_dict({k_: src[k_] for k_ in og.state_dict()})
+        gen = torch.Generator().manual_seed(1)
+        B_, C_, T_ = 4, 2, 12
+        ids = torch.randint(0, 101, (B_, C_, T_), generator=gen)
+        types = torch.randint(0, 101, (B_, C_, T_), generator=gen)
+        mc_ids = torch.randint(0, T_, (B_, C_), generator=gen)
+        lm = torch.randint(0, 101, (B_, C_, T_), generator=gen)
+        lm[:, 0] = -1
+        lm[:, :, :3] = -1
+        mc = torch.randint(0, C_, (B_,), generator=gen)
+        gbatch = (ids, mc_ids, lm, mc, types)
+        gargs = NS(lm_coef=1.0, mc_coef=0.7, device="cpu")
+        rg.train()
+        og.train()
+        worst = abs(float(ref_gpt2.compute_loss_train(rg, gbatch, gargs)[0])
+                    - float(our_gpt2.compute_loss_train(og, gbatch, gargs)[0]))
+        rv = ref_gpt2.compute_loss_val(rg, gbatch, gargs)
+        ov = our_gpt2.compute_loss_val(og, gbatch, gargs)
+        worst = max(worst, max(abs(float(a) - float(b)) for a, b in zip(rv, ov)))
+        out["gpt2/compute_loss_train_and_val"] = worst
+    except ImportError as exc:                                       # no transformers on this machine
+        out["gpt2/compute_loss_train_and_val"] = "skipped: %s" % exc
+
     # ---- transforms: the eight named pipelines on the same image with the same RNG state ------------------------
     from PIL import Image
     worst = 0.0
