@@ -459,6 +459,26 @@ def main():
     random.seed(0)
     bo = our_data.personachat_collate_fn([o[i] for i in range(5)])
     out["data/fed_persona_items_and_collate"] = bad + float(not same(list(br), list(bo)))
+    # ---- CV: the reference's loss callbacks (cv_train.py:67-83) on a ResNet-9 against ours, same weights --------------
+    import importlib.util as _ilu
+    spec = _ilu.spec_from_file_location("ref_cv_train", os.path.join(REF, "cv_train.py"))
+    ref_cv = _ilu.module_from_spec(spec)
+    spec.loader.exec_module(ref_cv)
+    from commefficient_b200 import cv_train as our_cv
+    torch.manual_seed(0)
+    with contextlib.redirect_stdout(io.StringIO()):
+        rnet, onet = ref_models.ResNet9(num_classes=10), our_models.ResNet9(num_classes=10)
+    onet.load_state_dict(rnet.state_dict())
+    cx = torch.randn(6, 3, 32, 32)
+    cy = torch.randint(0, 10, (6,))
+    cargs = NS(device="cpu", do_mixup=False)
+    worst = 0.0
+    for fn in ("compute_loss_train", "compute_loss_val"):
+        ra_ = getattr(ref_cv, fn)(rnet, (cx, cy), cargs)
+        oa_ = getattr(our_cv, fn)(onet, (cx, cy), cargs)
+        worst = max(worst, max(abs(float(a) - float(b)) for a, b in zip(ra_, oa_)))
+    out["cv/compute_loss_train_and_val"] = worst
+
     # ---- GPT-2: the reference's loss callbacks (gpt2_train.py:56-99) on its model class against ours, same weights ---
     try:
         import importlib.util
