@@ -23,7 +23,9 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * datasets: FedCIFAR10 / FedEMNIST / FedImageNet / FedPERSONA (+ collate) over the same client files return the same items,
     iid and non-iid (PersonaChat with more than one personality permutation and validation indexing are the
     documented departures Q14 / Q15 and are not compared);
-  * GPT-2: the reference's ``compute_loss_train`` / ``compute_loss_val`` (gpt2_train.py:56-99) on its model class
+  * drop-in use: the reference's own training loop (``cv_train.train`` / ``run_batches``) driving this framework's
+    ``FedModel`` / ``FedOptimizer`` / loaders gives the epoch summary this framework's loop gives;
+  * CV and GPT-2: the reference's ``compute_loss_train`` / ``compute_loss_val`` (gpt2_train.py:56-99) on its model class
     (through the ``pytorch_transformers`` shim over the installed ``transformers``) against ours with the same weights;
   * the eight named transform pipelines (same image, same RNG state -> same tensor) and the table / TSV loggers;
   * CLI: all 55 reference flags exist with the same dest and default and parse the same command line;
@@ -58,6 +60,8 @@ def main():
     from commefficient_b200 import fed_aggregator as our_agg
     from commefficient_b200 import fed_worker as our_worker
     from commefficient_b200.utils import FlatParams
+    import utils as ref_utils
+    from commefficient_b200 import utils as our_utils
 
     out = {}
     d, k = 300, 17
@@ -479,6 +483,40 @@ def main():
         worst = max(worst, max(abs(float(a) - float(b)) for a, b in zip(ra_, oa_)))
     out["cv/compute_loss_train_and_val"] = worst
 
+    # ---- drop-in: the REFERENCE's training loop (cv_train.py:85-160, run_batches :171-252) driving THIS framework's
+    #      FedModel / FedOptimizer / loaders, against this framework's own loop on the same setup
+    from torch.optim.lr_scheduler import LambdaLR
+    loop_dir = tempfile.mkdtemp()
+    our_data.write_synthetic_cifar(loop_dir, num_classes=10, images_per_class=10, num_val=40, seed=0)
+
+    def run_loop(train_fn, logger_cls, timer_cls):
+        torch.manual_seed(5)
+        np.random.seed(5)
+        random.seed(5)
+        largs = our_utils.parse_args(argv=[
+            "--dataset_name", "CIFAR10", "--dataset_dir", loop_dir, "--device", "cpu", "--num_epochs", "1", "--pivot_epoch",
+            "0.5", "--lr_scale", "0.05", "--num_cols", "2000", "--num_rows", "3", "--k", "300", "--valid_batch_size", "8",
+            "--model", "ResNet9", "--num_clients", "10", "--num_workers", "4", "--local_batch_size", "4", "--mode", "sketch",
+            "--error_type", "virtual", "--local_momentum", "0", "--virtual_momentum", "0.9",
+            "--train_dataloader_workers", "0", "--val_dataloader_workers", "0"])
+        largs.do_mixup = False
+        net, groups = our_cv.build_model_and_groups(largs)
+        tr_loader, te_loader = our_cv.get_data_loaders(largs)
+        fm = OurFedModel(net, our_cv.compute_loss_train, largs, our_cv.compute_loss_val)
+        fo = OurFedOptimizer(torch.optim.SGD(groups, lr=1), largs)
+        sched = our_utils.PiecewiseLinear([0, largs.pivot_epoch, largs.num_epochs], [0, largs.lr_scale, 0])
+        spe_ = our_utils.steps_per_epoch(largs.local_batch_size, tr_loader.dataset, largs.num_workers)
+        lrs = LambdaLR(fo, lr_lambda=lambda step: sched(step / spe_))
+        with contextlib.redirect_stdout(io.StringIO()):
+            summ = train_fn(fm, fo, lrs, tr_loader, te_loader, largs, None, loggers=(logger_cls(),), timer=timer_cls())
+        fm.rt.shutdown()
+        return summ
+
+    ref_summary = run_loop(ref_cv.train, ref_utils.TableLogger, ref_utils.Timer)
+    our_summary = run_loop(our_cv.train, our_utils.TableLogger, our_utils.Timer)
+    out["loop/reference_train_loop_drives_our_classes"] = max(
+        abs(float(ref_summary[k_]) - float(our_summary[k_])) for k_ in ("train_loss", "train_acc", "test_loss", "test_acc"))
+
     # ---- GPT-2: the reference's loss callbacks (gpt2_train.py:56-99) on its model class against ours, same weights ---
     try:
         import importlib.util
@@ -541,8 +579,6 @@ def main():
     out["data/transforms"] = worst
 
     # ---- loggers: the printed table and the TSV file --------------------------------------------------------------
-    import utils as ref_utils
-    from commefficient_b200 import utils as our_utils
     import contextlib as _ctx
     import io as _io
     rows = [{"epoch": 1, "lr": 0.123456, "train_loss": 2.30258, "note": "x"}, {"epoch": 2, "lr": 0.05, "train_loss": 1.5,
@@ -564,8 +600,6 @@ def main():
     out["utils/table_and_tsv_loggers"] = bad
 
     # ---- CLI: every reference flag exists with the same dest and default, and parses to the same value -------
-    import utils as ref_utils
-    from commefficient_b200 import utils as our_utils
     from commefficient_b200.utils.args import build_parser
 
     def parse_both(argv):
