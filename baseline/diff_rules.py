@@ -23,8 +23,8 @@ repo's package, feeds both the same random inputs and prints one JSON object ``{
   * datasets: FedCIFAR10 / FedEMNIST / FedImageNet / FedPERSONA (+ collate) over the same client files return the same items,
     iid and non-iid (PersonaChat with more than one personality permutation and validation indexing are the
     documented departures Q14 / Q15 and are not compared);
-  * drop-in use: the reference's own training loop (``cv_train.train`` / ``run_batches``) driving this framework's
-    ``FedModel`` / ``FedOptimizer`` / loaders gives the epoch summary this framework's loop gives;
+  * drop-in use: the reference's own training loops (``cv_train.train`` / ``run_batches``, ``gpt2_train.run_batches``)
+    driving this framework's ``FedModel`` / ``FedOptimizer`` / loaders give the numbers this framework's loops give;
   * CV and GPT-2: the reference's ``compute_loss_train`` / ``compute_loss_val`` (gpt2_train.py:56-99) on its model class
     (through the ``pytorch_transformers`` shim over the installed ``transformers``) against ours with the same weights;
   * the eight named transform pipelines (same image, same RNG state -> same tensor) and the table / TSV loggers;
@@ -516,6 +516,59 @@ def main():
     our_summary = run_loop(our_cv.train, our_utils.TableLogger, our_utils.Timer)
     out["loop/reference_train_loop_drives_our_classes"] = max(
         abs(float(ref_summary[k_]) - float(our_summary[k_])) for k_ in ("train_loss", "train_acc", "test_loss", "test_acc"))
+
+    # ---- drop-in, PersonaChat: the reference's run_batches (gpt2_train.py:169-251) over our classes, one training
+    #      epoch and one validation pass, against our run_batches on the same setup
+    try:
+        import importlib.util as _ilu2
+        spec = _ilu2.spec_from_file_location("ref_gpt2_loops", os.path.join(REF, "gpt2_train.py"))
+        ref_gl = _ilu2.module_from_spec(spec)
+        spec.loader.exec_module(ref_gl)
+        from commefficient_b200 import gpt2_train as our_gl
+        pdir = tempfile.mkdtemp()
+        our_data.write_synthetic_persona(pdir, num_clients=8, num_candidates=2, seed=0)
+
+        class _NoWriter:
+            def add_scalar(self, *a, **k):
+                pass
+
+        def run_gpt2(loop_mod, logger_cls, timer_cls):
+            torch.manual_seed(6)
+            np.random.seed(6)
+            random.seed(6)
+            ga = our_utils.parse_args(default_lr=4e-2, argv=[
+                "--dataset_name", "PERSONA", "--dataset_dir", pdir, "--num_clients", "8", "--model_checkpoint", "gpt2-tiny",
+                "--num_workers", "2", "--local_batch_size", "2", "--mode", "uncompressed", "--error_type", "none",
+                "--local_momentum", "0", "--virtual_momentum", "0.9", "--num_epochs", "1", "--device", "cpu",
+                "--valid_batch_size", "2", "--lr_scale", "0.1"])
+            ga.num_results_train = 1
+            gm, gtok = our_gl.build_model_and_tokenizer(ga)
+            for mod_ in gm.modules():                       # (no dropout: both loops must see the same numbers)
+                if isinstance(mod_, torch.nn.Dropout):
+                    mod_.p = 0.0
+            our_gl.add_special_tokens_(gm, gtok)
+            trl, val = our_gl.get_data_loaders(ga, gtok)
+            gfm = OurFedModel(gm, our_gl.compute_loss_train, ga, our_gl.compute_loss_val)
+            gfo = OurFedOptimizer(torch.optim.SGD(gm.parameters(), lr=1), ga)
+            spe_ = our_utils.steps_per_epoch(ga.local_batch_size, trl.dataset, ga.num_workers)
+            sch = our_utils.PiecewiseLinear([0, ga.num_epochs * spe_], [ga.lr_scale, 0.0])
+            lrs = LambdaLR(gfo, lr_lambda=lambda step: sch(step))
+            with contextlib.redirect_stdout(io.StringIO()):
+                tr_loss, _dl, _ul = loop_mod.run_batches(gfm, gfo, lrs, trl, ga, timer_cls(), True, epoch=0, epoch_fraction=1,
+                                                         logger=logger_cls(), writer=_NoWriter())
+                nll, acc, ppl = loop_mod.run_batches(gfm, None, None, val, ga, timer_cls(), False, epoch_fraction=1,
+                                                     logger=logger_cls(), writer=_NoWriter())
+            gfm.rt.shutdown()
+            return [float(tr_loss), float(nll), float(acc), float(ppl)]
+
+        import warnings as _w
+        with _w.catch_warnings():
+            _w.simplefilter("ignore")
+            a_ = run_gpt2(ref_gl, ref_utils.TableLogger, ref_utils.Timer)
+            b_ = run_gpt2(our_gl, our_utils.TableLogger, our_utils.Timer)
+        out["loop/reference_gpt2_loop_drives_our_classes"] = max(abs(x - y) / max(1.0, abs(x)) for x, y in zip(a_, b_))
+    except ImportError as exc:
+        out["loop/reference_gpt2_loop_drives_our_classes"] = "skipped: %s" % exc
 
     # ---- GPT-2: the reference's loss callbacks (gpt2_train.py:56-99) on its model class against ours, same weights ---
     try:

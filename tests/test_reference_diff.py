@@ -21,7 +21,7 @@ def test_rules_match_the_reference_function_by_function():
     assert proc.returncode == 0, proc.stderr[-2000:]
     res = json.loads(proc.stdout.strip().splitlines()[-1])
     assert "unavailable" not in res, res
-    assert len(res) >= 45 and "loop/reference_train_loop_drives_our_classes" in res and "data/transforms" in res and "data/fed_emnist_prepared_from_leaf_json" in res and "rounds/fedavg_local_sgd" in res and "data/fed_imagenet_items" in res and "client/process_batch_topk_down" in res and "cli/flags_dests_defaults" in res and "data/fed_persona_items_and_collate" in res and any(c.startswith("models/") for c in res) and "data/fed_sampler_rounds" in res
+    assert len(res) >= 46 and "loop/reference_gpt2_loop_drives_our_classes" in res and "loop/reference_train_loop_drives_our_classes" in res and "data/transforms" in res and "data/fed_emnist_prepared_from_leaf_json" in res and "rounds/fedavg_local_sgd" in res and "data/fed_imagenet_items" in res and "client/process_batch_topk_down" in res and "cli/flags_dests_defaults" in res and "data/fed_persona_items_and_collate" in res and any(c.startswith("models/") for c in res) and "data/fed_sampler_rounds" in res
     for case, err in res.items():
         if isinstance(err, str) and err.startswith("skipped"):
             continue
