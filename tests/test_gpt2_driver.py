@@ -168,3 +168,47 @@ def test_gpt2_driver_from_a_checkpoint_directory_with_bpe_files(tmp_path, monkey
     run = sorted((tmp_path / "runs").iterdir())[-1]
     saved = [p.name for p in run.rglob("*") if p.is_file()]
     assert "vocab.json" in saved and "merges.txt" in saved and "added_tokens.json" in saved
+
+
+def test_gpt2_batched_round_in_client_aligned_chunks(monkeypatch):
+    """A batched round larger than MAX_BATCHED_SAMPLES is cut at client boundaries: the per-client token-normalised
+    loss (gpt2_train.py:78-97 in the reference) and the weights equal the one-chunk round."""
+    import numpy as np
+    from commefficient_b200 import fed_worker
+    from commefficient_b200.fed_aggregator import FedModel, FedOptimizer
+    from commefficient_b200.gpt2_train import compute_loss_train, compute_loss_val
+    from commefficient_b200.utils import make_args
+
+    def run(limit):
+        monkeypatch.setattr(fed_worker.ClientWorker, "MAX_BATCHED_SAMPLES", limit)
+        torch.manual_seed(0)
+        cfg = models.GPT2Config(vocab_size=64, n_positions=32, n_ctx=32, n_embd=32, n_layer=1, n_head=2,
+                                resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0, summary_first_dropout=0.0)
+        model = models.GPT2DoubleHeadsModel(cfg)
+        args = make_args(mode="uncompressed", num_workers=3, num_clients=6, local_batch_size=-1, device="cpu",
+                         dataset_name="PERSONA", local_momentum=0.0, num_results_train=1, weight_decay=0.0,
+                         watchdog_timeout=0.0)
+        fed = FedModel(model, compute_loss_train, args, compute_loss_val)
+        opt = FedOptimizer(torch.optim.SGD(model.parameters(), lr=1), args)
+        opt.param_groups[0]["lr"] = 0.1
+        g = torch.Generator().manual_seed(3)
+        n = 3 + 2 + 3                                      # three clients with 3, 2 and 3 dialogs
+        ids = torch.randint(0, 64, (n, 2, 12), generator=g)
+        labels = ids.clone()
+        labels[:, 0] = -1
+        labels[1, 1, :9] = -1                              # uneven numbers of target tokens inside a client
+        labels[6, 1, :4] = -1
+        batch = (torch.tensor([0, 0, 0, 1, 1, 2, 2, 2]), ids, torch.full((n, 2), 11), labels,
+                 torch.randint(0, 2, (n,), generator=g), ids)
+        assert fed.worker.can_batch_clients([3, 2, 3])
+        out = fed(batch)
+        opt.step()
+        w = fed.fp.flat.clone()
+        fed.rt.shutdown()
+        return np.asarray(out[0]), w
+
+    l_one, w_one = run(4096)
+    l_cut, w_cut = run(4)                                  # chunks: clients {0}, {1}, {2} (3 + 2 > 4, 2 + 3 > 4)
+    assert fed_worker._client_aligned_chunks((3, 2, 3), 4) == [(0, 3), (3, 5), (5, 8)]
+    np.testing.assert_allclose(l_cut, l_one, rtol=1e-5)
+    torch.testing.assert_close(w_cut, w_one, rtol=1e-4, atol=1e-6)
