@@ -333,3 +333,34 @@ def test_round_is_invariant_to_sample_order_in_the_batch():
     np.testing.assert_allclose(np.asarray(acc_a), np.asarray(acc_b))
     torch.testing.assert_close(w_a, w_b, rtol=1e-5, atol=1e-6)
     assert torch.equal(torch.as_tensor(ul_a), torch.as_tensor(ul_b))
+
+
+@pytest.mark.parametrize("mode", ["true_topk", "sketch", "uncompressed"])
+def test_download_bytes_equal_the_reference_rule(mode):
+    """The reference charges a participating client 4 bytes for every weight that differs between the current server
+    weights and the weights of the last round that client took part in (fed_aggregator.py:240-287; a client that has
+    never taken part holds the initial weights); ours counts coordinates by the round of their last update.  Seven
+    rounds with recurring clients, oracle restated here from the weight history.  Sparse modes agree exactly; a dense
+    round is booked as "every coordinate changed", which exceeds the reference's count only by the coordinates whose
+    update happened to be exactly zero."""
+    fed, opt, args = _make(mode)
+    history = [fed.fp.flat.detach().clone()]           # history[t] = weights before round t
+    last_seen = {}
+    for step in range(7):
+        first = (4 * step) % 12
+        clients = list(range(first, first + 4))
+        out = _round(fed, opt, step)
+        download = np.asarray(out[-2])
+        cur = history[-1]                               # the weights this round's clients download
+        for c in clients:
+            prev = history[last_seen.get(c, 0)]
+            want = 4.0 * float((cur != prev).sum())
+            if mode == "uncompressed":
+                assert want <= float(download[c]) <= max(want, 4.0 * cur.numel() * float(last_seen.get(c, 0) != step))
+                assert float(download[c]) - want <= 4.0 * 8, (step, c, float(download[c]), want)
+            else:
+                assert float(download[c]) == want, (mode, step, c, float(download[c]), want)
+            last_seen[c] = step
+        assert float(download.sum()) == sum(float(download[c]) for c in clients)
+        history.append(fed.fp.flat.detach().clone())
+    fed.rt.shutdown()
