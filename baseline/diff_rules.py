@@ -650,6 +650,11 @@ def main():
             t.append({"epoch": e + 1, "total_time": hours * 3600, "test_acc": acc})
         return str(t)
     bad += float(tsv_text(ref_utils) != tsv_text(our_utils))
+    for m_, extra in (("sketch", {}), ("true_topk", {}), ("uncompressed", {})):
+        la = NS(num_rows=5, num_cols=500000, k=50000, mode=m_, num_workers=100, num_clients=10000)
+        ra_, oa_ = ref_utils.make_logdir(la), our_utils.make_logdir(la)
+        strip = lambda p_: p_.split("_", 2)[-1]          # noqa: E731 -- drop "runs/<date>_<time>"
+        bad += float(strip(ra_) != strip(oa_) or not oa_.startswith("runs" + os.sep))
     out["utils/table_and_tsv_loggers"] = bad
 
     # ---- CLI: every reference flag exists with the same dest and default, and parses to the same value -------
